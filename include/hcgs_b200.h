@@ -1,0 +1,175 @@
+/*
+ * hcgs_b200.h -- C ABI of the B200-native HCGS acoustic-model hot path.
+ *
+ * The reference (hellboywyh/pytorch-kaldi-CGS) is 100 % Python: it has no FFI of its own.
+ * Every entry point below therefore cites the reference *Python* call site it replaces
+ * (file:line relative to the reference root).  The reference-side binding is a ctypes stub
+ * (see INTEGRATION.md); `pytorch-kaldi-cgs_b200/b200/native.py` is that stub.
+ *
+ * Conventions
+ *   - plain C types only: device pointers, sizes, a cudaStream_t passed as void*.
+ *   - every function returns 0 on success, non-zero on failure; hcgs_last_error() gives the text.
+ *     No C++ exception crosses the ABI.
+ *   - no ownership transfer: the caller (PyTorch) owns every buffer; the library owns only the
+ *     opaque hcgs_plan (device copies of the block index) until hcgs_plan_destroy().
+ *   - all matrices are row-major fp32 unless stated; "ld" = leading dimension in elements.
+ *   - gate order everywhere: 0=f (forget), 1=i (input), 2=o (output), 3=c (candidate).
+ *   - functions are asynchronous on `stream`; a plan is thread-compatible (one user at a time).
+ */
+#ifndef HCGS_B200_H
+#define HCGS_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HCGS_ABI_VERSION 1
+#define HCGS_MAX_GROUPS 4 /* gates of one LSTM layer share a mask and are processed together */
+
+typedef struct hcgs_plan hcgs_plan;
+typedef void* hcgs_stream; /* cudaStream_t */
+
+/* activation codes = reference act_fun() names (neural_networks.py:54-78) */
+enum {
+    HCGS_ACT_LINEAR = 0,
+    HCGS_ACT_RELU = 1,
+    HCGS_ACT_TANH = 2,
+    HCGS_ACT_HTANH = 3,
+    HCGS_ACT_SIGMOID = 4,
+    HCGS_ACT_LEAKY_RELU = 5, /* slope 0.2 */
+    HCGS_ACT_ELU = 6
+};
+
+/* ---- library ---------------------------------------------------------------------------- */
+int hcgs_abi_version(void);
+const char* hcgs_last_error(void);
+/* info[0]=SM count, [1]=cc major, [2]=cc minor, [3]=max opt-in smem/block, [4]=cluster launch ok */
+int hcgs_device_info(int device, int* info);
+
+/* ---- plan: HCGS/pattern mask -> compressed block index ------------------------------------
+ * Replaces nothing 1:1 -- the reference multiplies dense weights by the dense mask on every
+ * forward (neural_networks.py:858-861, 980-983, 258).  The plan is built ONCE per mask from the
+ * host copy of the 0/1 mask (row-major [n_out, n_in]); a non-zero entry marks a kept weight.
+ * It holds (a) the 32x32-tile CSR/CSC index used by the block-sparse GEMMs and (b), when
+ * recurrent != 0 (requires n_out == n_in), the per-row ELL index used by the persistent
+ * recurrent kernels.  cluster_size: 0 = choose automatically, else 1/2/4/8/16.
+ */
+int hcgs_plan_create(const float* mask_host, int n_out, int n_in, int recurrent, int cluster_size,
+                     hcgs_plan** plan);
+int hcgs_plan_destroy(hcgs_plan* plan);
+/* info[0]=n_out [1]=n_in [2]=non-empty 32x32 tiles [3]=total tiles [4]=nnz(mask)
+ * [5]=cluster size [6]=rows per CTA [7]=block-ELL width L [8]=fwd pack floats [9]=bwd pack floats
+ * [10]=fwd smem bytes [11]=bwd smem bytes [12]=threads per CTA [13]=4x4 blocks [14]=weights in smem */
+int hcgs_plan_info(const hcgs_plan* plan, int64_t* info);
+
+/* ---- elementwise weight preparation -------------------------------------------------------
+ * hcgs_mask_apply: W *= mask in place for n matrices sharing one mask
+ *   (neural_networks.py:858-861, 980-983 LSTM; :258 MLP).                                    */
+int hcgs_mask_apply(float* const* w, int n, const float* mask, int64_t numel, hcgs_stream stream);
+/* hcgs_quantize_w: quantized_modules.Quantize(balanced=False) (quantized_modules.py:77-97):
+ *   master is clamped to [-1,1] IN PLACE; q = sign(w)*ceil(|w|*2^(bits-1))/2^(bits-1) is written
+ *   to `q` (q may alias master for the if_forward=True in-place variant).                     */
+int hcgs_quantize_w(float* master, float* q, int64_t numel, int bits, hcgs_stream stream);
+/* hcgs_quantize_act: quantized_modules.Quantize_inp (quantized_modules.py:99-119) applied
+ *   `repeat` times in a row (the four gate linears each re-quantize the same tensor).
+ *   x is [rows, cols] with leading dimension ldx; scratch = 2 floats of device memory.       */
+int hcgs_quantize_act(const float* x, int ldx, float* y, int ldy, int64_t rows, int cols, int bits,
+                      int repeat, float* scratch, hcgs_stream stream);
+
+/* ---- block-sparse GEMM family (time-batched projections and their gradients) --------------
+ * n_w weight matrices W_g [n_out, n_in] (ld = ldw) share the plan's mask.
+ * hcgs_bsgemm_nt:  Y[m, g*n_out + n] = sum_k X[m,k] * W_g[n,k] (+ bias_g[n])
+ *   replaces the four F.linear calls neural_networks.py:951-954 and MLP wx(x) :306-317.
+ * hcgs_bsgemm_nn:  dX[m,k] = sum_g sum_n dY[m, g*n_out + n] * W_g[n,k]      (autograd of the above)
+ * hcgs_bs_sddmm:   dW_g[n,k] = mask[n,k] * sum_m dY[m, g*n_out + n] * X[m,k]  only inside non-empty
+ *   tiles (mask-preserving weight gradient; entries outside non-empty tiles are left untouched,
+ *   so the caller passes a zero-initialised buffer).  mask may be NULL (no re-masking).
+ * bias / dW are host arrays of n_w device pointers (bias may be NULL).                        */
+int hcgs_bsgemm_nt(const hcgs_plan* plan, int n_w, const float* const* w, int ldw, const float* x,
+                   int ldx, int64_t m, const float* const* bias, float* y, int ldy,
+                   hcgs_stream stream);
+int hcgs_bsgemm_nn(const hcgs_plan* plan, int n_w, const float* const* w, int ldw, const float* dy,
+                   int lddy, int64_t m, float* dx, int lddx, hcgs_stream stream);
+int hcgs_bs_sddmm(const hcgs_plan* plan, int n_w, const float* dy, int lddy, const float* x, int ldx,
+                  int64_t m, float* const* dw, int lddw, const float* mask, hcgs_stream stream);
+/* column sums: out_g[n] = sum_m dY[m, g*n_out+n]  (bias gradient) */
+int hcgs_colsum(const float* dy, int lddy, int64_t m, int n_groups, int group_cols, float* const* out,
+                hcgs_stream stream);
+
+/* ---- batch norm over the time-batched rows (nn.BatchNorm1d, momentum 0.05) ------------------
+ * C = n_groups*group_cols columns; group g uses gamma[g]/beta[g]/running_*[g] (each [group_cols]).
+ * Replaces neural_networks.py:957-976 (LSTM, 4 groups) and :309-314 (MLP, 1 group).
+ * training!=0: batch statistics (biased var for the normalisation, unbiased for running_var),
+ * running stats updated in place, save_mean/save_invstd [C] written for the backward.
+ * training==0: running statistics.  y may alias x.  workspace: >= 2*C floats of device scratch
+ * (more lets the statistics use more CTAs: up to 2*C*256 floats are used).                    */
+int hcgs_bn_fwd(const float* x, int ldx, float* y, int ldy, int64_t m, int n_groups, int group_cols,
+                const float* const* gamma, const float* const* beta, float* const* running_mean,
+                float* const* running_var, float eps, float momentum, int training,
+                float* save_mean, float* save_invstd, float* workspace, int64_t workspace_floats,
+                hcgs_stream stream);
+int hcgs_bn_bwd(const float* dy, int lddy, const float* x, int ldx, int64_t m, int n_groups,
+                int group_cols, const float* const* gamma, const float* save_mean,
+                const float* save_invstd, float* dx, int lddx, float* const* dgamma,
+                float* const* dbeta, float* workspace, int64_t workspace_floats, hcgs_stream stream);
+
+/* ---- persistent recurrent LSTM kernels ------------------------------------------------------
+ * hcgs_lstm_pack: gather the four masked U_g [H,H] (ld = ldu) into the plan's compressed
+ *   resident layouts (fwd_pack: info[8] floats, bwd_pack: info[9] floats; either may be NULL).
+ * hcgs_lstm_fwd: the whole time loop of one layer (neural_networks.py:1063-1100):
+ *     f,i,o = sigmoid(pre_{f,i,o}[t] + U_{f,i,o} h) ; g = act(pre_c[t] + U_c h)
+ *     c = i*g*drop + f*c ; h = o*act(c)
+ *   pre [T,B,4H] (column g*H+u), drop [B,H] or NULL (then drop_scalar is used, eval mode),
+ *   h_out [T,B,H]; c_out [T,B,H] and gates_out [T,B,4H] (post-activation f,i,o,g) are saved for
+ *   the backward when non-NULL.  act_bits>0 enables the per-step Quantize_inp of h
+ *   (quantized_modules.py:212/219 through QuantizeLinear on h_t, 4 applications per step).
+ * hcgs_lstm_bwd: BPTT of the same loop; dh_out [T,B,H] is the gradient arriving from above,
+ *   dpre [T,B,4H] the gradient w.r.t. the gate pre-activations.                  */
+int hcgs_lstm_pack(const hcgs_plan* plan, const float* const* u, int ldu, float* fwd_pack,
+                   float* bwd_pack, hcgs_stream stream);
+int hcgs_lstm_fwd(const hcgs_plan* plan, const float* fwd_pack, const float* pre, const float* drop,
+                  float drop_scalar, int act, int t_len, int batch, float* h_out, float* c_out,
+                  float* gates_out, int act_bits, hcgs_stream stream);
+int hcgs_lstm_bwd(const hcgs_plan* plan, const float* bwd_pack, const float* dh_out,
+                  const float* gates, const float* c, const float* drop, float drop_scalar, int act,
+                  int t_len, int batch, float* dpre, hcgs_stream stream);
+
+/* ---- MLP pointwise pieces ------------------------------------------------------------------
+ * y = drop_mask * act(x)  (neural_networks.py:306-317; drop_mask already holds 1/(1-p) scaling,
+ * NULL = no dropout).  Backward: dx = dy * drop_mask * act'(.) using the saved output y.       */
+int hcgs_act_fwd(const float* x, float* y, const float* drop_mask, int64_t numel, int act,
+                 hcgs_stream stream);
+int hcgs_act_bwd(const float* dy, const float* y, const float* drop_mask, float* dx, int64_t numel,
+                 int act, hcgs_stream stream);
+
+/* ---- output layer epilogue: log-softmax (+ prior normalisation, + NLL/err) ------------------
+ * hcgs_logsoftmax_fwd: out[m,:] = z[m,:] - logsumexp(z[m,:]) - (log_prior ? log_prior[:] : 0)
+ *   = nn.LogSoftmax(dim=1) (neural_networks.py:73-74) fused with core.py:241-245
+ *   (`out - np.log(counts/np.sum(counts))`).  out may alias z.
+ * hcgs_logsoftmax_bwd: dz = dlogp - exp(logp) * rowsum(dlogp)       (autograd of LogSoftmax)
+ * hcgs_nll_fwd_bwd: fused cost_nll + cost_err (utils.py:1935-1952, 1993-2011) on log-probs:
+ *   loss_sum += -logp[m,label[m]], err_sum += (argmax != label); when dz != NULL also writes
+ *   dz[m,:] = (exp(logp[m,:]) - onehot) * scale  (gradient of mean NLL w.r.t. the logits).
+ *   labels are fp32 (the reference stores them as the last float column, utils.py:1940-1944),
+ *   with leading dimension ldlab.  stats = 2 floats {loss_sum, err_sum}, accumulated atomically. */
+int hcgs_logsoftmax_fwd(const float* z, int ldz, float* out, int ldo, int64_t m, int p,
+                        const float* log_prior, hcgs_stream stream);
+int hcgs_logsoftmax_bwd(const float* dlogp, const float* logp, float* dz, int64_t m, int p,
+                        hcgs_stream stream);
+int hcgs_nll_fwd_bwd(const float* logp, int64_t m, int p, const float* labels, int ldlab, float scale,
+                     float* dz, float* stats, hcgs_stream stream);
+
+/* ---- optimizers on flat (compressed or dense) buffers -------------------------------------
+ * torch.optim semantics as configured by utils.optimizer_init (utils.py:1833-1881).
+ * kind: 0 = SGD(momentum, weight_decay, dampening, nesterov), 1 = RMSprop(alpha, eps,
+ * weight_decay, momentum, centered=False), 2 = Adam(beta1, beta2, eps, weight_decay, step).
+ * hp = 8 floats: {lr, a, b, eps, weight_decay, c, d, step}; see optimizer.cu.                */
+int hcgs_opt_step(int kind, float* param, const float* grad, float* state1, float* state2,
+                  int64_t numel, const float* hp, float grad_scale, hcgs_stream stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HCGS_B200_H */

@@ -1,0 +1,181 @@
+"""ORACLE (test infrastructure only) -- torch-CPU fp32 restatement of the reference's floating-point
+hot path: LSTM.forward (neural_networks.py:823-1112), MLP.forward (:245-319), the cost lines of
+utils.forward_model (utils.py:1935-2011) and the posterior normalisation (core.py:241-245).
+
+The arithmetic of the reference lives in PyTorch itself, so the oracle is "the reference's operator
+sequence on the installed torch CPU kernels": the same Python loop over T with four F.linear calls
+per step on masked-dense weights.  Gradients come from torch autograd, exactly as in the
+reference.  It is pinned against tensors dumped from the real reference (tests/golden/*.npz,
+produced by tests/golden/make_golden.py) in tests/test_oracle_pinned.py.
+
+Only tests/, __graft_entry__.smoke() and bench.py (cpu_baseline / --impl reference) import this.
+
+Parameters are passed as flat dicts keyed like the reference's state_dict
+(``wfx.0.weight``, ``hcgsx.0.mask``, ``bn_wfx.0.running_mean`` ...), so a state_dict of either
+implementation can be fed in directly.
+"""
+import torch
+import torch.nn.functional as F
+
+GATES = ('f', 'i', 'o', 'c')
+
+
+def act(name, x):
+    """act_fun (neural_networks.py:54-78)."""
+    if name == 'relu':
+        return torch.relu(x)
+    if name == 'tanh':
+        return torch.tanh(x)
+    if name == 'htanh':
+        return F.hardtanh(x)
+    if name == 'sigmoid':
+        return torch.sigmoid(x)
+    if name == 'leaky_relu':
+        return F.leaky_relu(x, 0.2)
+    if name == 'elu':
+        return F.elu(x)
+    if name == 'linear':
+        return x
+    raise ValueError(name)
+
+
+def _ste(x, xq):
+    """value of xq, gradient of x (what `.data = quantised` does to the autograd graph)."""
+    return x + (xq - x).detach()
+
+
+def quantize_w_t(w, bits):
+    """Quantize(balanced=False) (quantized_modules.py:77-97) on a tensor; returns STE tensor."""
+    wc = w.detach().clamp(-1, 1)
+    s = 2 ** (bits - 1)
+    q = wc.abs().mul(s).ceil().div(s) * wc.sign()
+    return _ste(w, q)
+
+
+def quantize_inp_t(x, bits, repeat=1):
+    """Quantize_inp (quantized_modules.py:99-119) applied `repeat` times; STE."""
+    v = x.detach()
+    for _ in range(repeat):
+        mx, mn = v.max().abs(), v.min().abs()
+        var = mx if mx > mn else mn
+        if var == 0.:
+            break
+        sgn = v.sign()
+        t = v.div(var)
+        t = t.abs().mul(2 ** (bits - 1)).ceil().div(2 ** (bits - 1))
+        v = t.mul(var) * sgn
+    return _ste(x, v)
+
+
+def lstm_forward(p, spec, x, drop_masks, training):
+    """LSTM.forward.  p: dict of tensors; spec keys: lay, act, use_bn, drop, hcgs, quant (bits or 0),
+    quant_inp (bits or 0).  drop_masks: list of [B,H] tensors (train) -- the reference draws them
+    with torch.bernoulli on the CPU generator (:843-845); in eval the scalar (1-p) is used (:847).
+    BN running statistics in `p` are updated in place when training (momentum 0.05)."""
+    for i, H in enumerate(spec['lay']):
+        T, B, _ = x.shape
+        drop = drop_masks[i] if training else torch.tensor([1 - spec['drop'][i]])
+        w, u = {}, {}
+        for g in GATES:
+            w[g] = p['w%sx.%d.weight' % (g, i)]
+            u[g] = p['u%sh.%d.weight' % (g, i)]
+            if spec.get('hcgs', False):
+                w[g] = w[g] * p['hcgsx.%d.mask' % i]                      # :858-861
+                u[g] = u[g] * p['hcgsh.%d.mask' % i]                      # :980-983
+            if spec.get('quant', 0):
+                w[g] = quantize_w_t(w[g], spec['quant'])
+                u[g] = quantize_w_t(u[g], spec['quant'])
+        xin = x
+        if spec.get('quant_inp', 0):
+            xin = quantize_inp_t(x, spec['quant_inp'], 4)                 # four gate linears re-quantise x
+        pre = {}
+        for g in GATES:
+            out = F.linear(xin, w[g])                                     # :951-954
+            if spec['use_bn'][i]:
+                k = 'bn_w%sx.%d.' % (g, i)
+                out = F.batch_norm(out.view(T * B, H), p[k + 'running_mean'], p[k + 'running_var'], p[k + 'weight'],
+                                   p[k + 'bias'], training, 0.05, 1e-5).view(T, B, H)   # :957-976
+            pre[g] = out
+        ht = torch.zeros(B, H)
+        ct = ht
+        hs = []
+        a = spec['act'][i]
+        for k in range(T):                                                # :1077-1097
+            hq = ht
+            if spec.get('quant_inp', 0) and k > 0:
+                hq = quantize_inp_t(ht, spec['quant_inp'], 4)
+                hs[-1] = hq                                               # the stacked copy is the swapped tensor
+            ft = torch.sigmoid(pre['f'][k] + F.linear(hq, u['f']))
+            it = torch.sigmoid(pre['i'][k] + F.linear(hq, u['i']))
+            ot = torch.sigmoid(pre['o'][k] + F.linear(hq, u['o']))
+            ct = it * act(a, pre['c'][k] + F.linear(hq, u['c'])) * drop + ft * ct
+            ht = ot * act(a, ct)
+            hs.append(ht)
+        x = torch.stack(hs)                                               # :1100
+    return x
+
+
+def mlp_forward(p, spec, x, training, drop_masks=None):
+    """MLP.forward (:245-319).  spec keys: lay, act, use_bn, drop, hcgs, quant, quant_inp."""
+    for i, O in enumerate(spec['lay']):
+        w = p['wx.%d.weight' % i]
+        b = p['wx.%d.bias' % i]
+        if spec.get('hcgs', False):
+            w = w * p['hcgs.%d.mask' % i]                                 # :258
+        if spec.get('quant', 0):
+            w = quantize_w_t(w, spec['quant'])
+        if spec.get('quant_inp', 0):
+            x = quantize_inp_t(x, spec['quant_inp'], 1)
+        z = F.linear(x, w, b)
+        if spec['use_bn'][i]:
+            k = 'bn.%d.' % i
+            z = F.batch_norm(z, p[k + 'running_mean'], p[k + 'running_var'], p[k + 'weight'], p[k + 'bias'],
+                             training, 0.05, 1e-5)
+        if spec['act'][i] == 'softmax':
+            z = F.log_softmax(z, dim=1)                                   # :73-74
+        else:
+            z = act(spec['act'][i], z)
+        if training and spec['drop'][i] > 0:
+            z = z * drop_masks[i]                                         # nn.Dropout: mask holds 1/(1-p)
+        x = z
+    return x
+
+
+def costs(logp, labels):
+    """cost_nll + cost_err (utils.py:1935-1952, 1993-2011): mean over ALL rows incl. padding."""
+    lab = labels.reshape(-1).long()
+    loss = F.nll_loss(logp, lab)
+    err = torch.mean((torch.max(logp, dim=1)[1] != lab).float())
+    return loss, err
+
+
+def model_forward(params, specs, inp, n_fea, training, drop_masks, mono_weight=1.0):
+    """The shipped two-head graph (cfg/TIMIT_CGS/*.cfg [model]):
+        out1 = LSTM(fea); out2 = MLP_cd(out1); out3 = MLP_mono(out1)
+        loss_final = nll(out2, lab_cd) + w * nll(out3, lab_mono); err_final = err(out2, lab_cd)
+    inp: [T, B, n_fea + n_labels] with the labels as trailing float columns (core.py:183-200).
+    params/specs: dicts keyed 'lstm', 'cd', optionally 'mono'."""
+    T, B, _ = inp.shape
+    h = lstm_forward(params['lstm'], specs['lstm'], inp[:, :, :n_fea], drop_masks, training)
+    flat = h.view(T * B, -1)
+    out = {'out_dnn1': h}
+    out['out_dnn2'] = mlp_forward(params['cd'], specs['cd'], flat, training)
+    if specs['cd'].get('quant_inp', 0):
+        # the cd head swapped out_dnn1.data for its quantised copy; the mono head starts from that
+        flat = quantize_inp_t(flat, specs['cd']['quant_inp'], 1)
+    loss, err = costs(out['out_dnn2'], inp[:, :, n_fea])
+    out['loss_cd'], out['err_final'] = loss, err
+    out['loss_final'] = loss
+    if 'mono' in params:
+        out['out_dnn3'] = mlp_forward(params['mono'], specs['mono'], flat, training)
+        lm, _ = costs(out['out_dnn3'], inp[:, :, n_fea + 1])
+        out['loss_mono'] = lm
+        out['loss_final'] = loss + lm * mono_weight
+    return out
+
+
+def posterior(logp, counts):
+    """core.py:241-245 in float32 NumPy."""
+    import numpy as np
+    counts = np.asarray(counts, dtype=np.float32)
+    return logp - np.log(counts / np.sum(counts))

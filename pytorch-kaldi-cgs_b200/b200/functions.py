@@ -1,0 +1,197 @@
+"""autograd glue between the plugin classes (neural_networks.LSTM / MLP) and the C ABI.
+
+Each Function is one *layer*: its forward/backward are straight sequences of native calls
+(no torch arithmetic on the data path; torch only allocates buffers).  Gradients are produced
+in the dense ``[out, in]`` fp32 layout the reference's optimizers expect (``.grad`` of the same
+``nn.Parameter`` objects), but they are only *computed* inside the non-empty tiles of the mask
+and re-masked on the way out (observationally identical for every kept weight).
+"""
+import torch
+
+from . import native
+
+
+class LayerRuntime:
+    """Per-layer mutable state shared between forward and backward (plans, flags, BN buffers)."""
+
+    def __init__(self):
+        self.plan_x = None        # native.Plan of the input-projection mask
+        self.plan_h = None        # native.Plan (recurrent) of the hidden-hidden mask
+        self.mask_x = None        # device mask tensors (or None = dense)
+        self.mask_h = None
+        self.use_bn = False
+        self.training = False
+        self.bn_running = None    # list of (running_mean, running_var) per group
+        self.bn_eps = 1e-5
+        self.bn_momentum = 0.05
+        self.act = 0
+        self.drop = None          # [B,H] mask tensor (train) or None
+        self.drop_scalar = 1.0    # eval: (1-p) ; train without tensor: 1
+        self.mlp_drop_mask = None  # [N,out] scaled keep mask for MLP dropout (or None)
+        self.softmax = False
+        self.log_prior = None
+        # quantised compute copies (QuantizeLinear semantics: forward AND backward run on the
+        # quantised weights, the gradient lands on the fp32 master -- straight-through)
+        self.q_ws = None
+        self.q_us = None
+
+
+def _ws(device, n_cols):
+    """BN reduction scratch: enough for 64 row-splits."""
+    return torch.empty(2 * n_cols * 64, device=device, dtype=torch.float32)
+
+
+class LSTMLayerFunction(torch.autograd.Function):
+    """One HCGS LSTM layer: projections -> BN -> persistent recurrence (neural_networks.py:950-1100)."""
+
+    @staticmethod
+    def forward(ctx, x, wf, wi, wo, wc, uf, ui, uo, uc, gf, bf, gi, bi, go, bo, gc, bc, rt):
+        T, B, D = x.shape
+        H = wf.shape[0]
+        M = T * B
+        dev = x.device
+        x2d = x.reshape(M, D)
+        if x2d.stride(-1) != 1:
+            x2d = x2d.contiguous()
+        ws = rt.q_ws if rt.q_ws is not None else [wf, wi, wo, wc]
+        us = rt.q_us if rt.q_us is not None else [uf, ui, uo, uc]
+        need_grad = any(ctx.needs_input_grad)
+        pre_raw = torch.empty(M, 4 * H, device=dev, dtype=torch.float32)
+        native.bsgemm_nt(rt.plan_x, ws, x2d, pre_raw)
+        save_mean = save_invstd = None
+        if rt.use_bn:
+            pre = torch.empty_like(pre_raw)
+            save_mean = torch.empty(4 * H, device=dev, dtype=torch.float32)
+            save_invstd = torch.empty(4 * H, device=dev, dtype=torch.float32)
+            rms = [r[0] for r in rt.bn_running]
+            rvs = [r[1] for r in rt.bn_running]
+            native.bn_fwd(pre_raw, pre, 4, H, [gf, gi, go, gc], [bf, bi, bo, bc], rms, rvs, rt.bn_eps,
+                          rt.bn_momentum, rt.training, save_mean, save_invstd, _ws(dev, 4 * H))
+        else:
+            pre = pre_raw
+        plan = rt.plan_h
+        fwd_pack = torch.empty(plan.fwd_pack_floats, device=dev, dtype=torch.float32)
+        bwd_pack = torch.empty(max(plan.bwd_pack_floats, 1), device=dev, dtype=torch.float32) if need_grad else None
+        native.lstm_pack(plan, us, fwd_pack, bwd_pack)
+        h = torch.empty(T, B, H, device=dev, dtype=torch.float32)
+        c = gates = None
+        if need_grad:
+            c = torch.empty(T, B, H, device=dev, dtype=torch.float32)
+            gates = torch.empty(T, B, 4 * H, device=dev, dtype=torch.float32)
+        native.lstm_fwd(plan, fwd_pack, pre.view(T, B, 4 * H), rt.drop, rt.drop_scalar, rt.act, h, c, gates)
+        if need_grad:
+            ctx.rt = rt
+            ctx.dims = (T, B, D, H)
+            ctx.drop = rt.drop
+            ctx.drop_scalar = rt.drop_scalar
+            ctx.h_store = h.detach()   # private alias: survives a later `.data =` swap on the output
+            ctx.save_for_backward(x2d, ws[0], ws[1], ws[2], ws[3], gf, gi, go, gc, pre_raw, save_mean,
+                                  save_invstd, c, gates, bwd_pack)
+        return h
+
+    @staticmethod
+    def backward(ctx, dh):
+        rt = ctx.rt
+        T, B, D, H = ctx.dims
+        M = T * B
+        (x2d, wf, wi, wo, wc, gf, gi, go, gc, pre_raw, save_mean, save_invstd, c, gates, bwd_pack) = ctx.saved_tensors
+        dev = dh.device
+        dh = dh.contiguous()
+        dpre = torch.empty(T, B, 4 * H, device=dev, dtype=torch.float32)
+        native.lstm_bwd(rt.plan_h, bwd_pack, dh, gates, c, ctx.drop, ctx.drop_scalar, rt.act, dpre)
+        dpre2d = dpre.view(M, 4 * H)
+        dgam = [None] * 4
+        dbet = [None] * 4
+        if rt.use_bn:
+            dproj = torch.empty_like(dpre2d)
+            dgam = [torch.empty(H, device=dev, dtype=torch.float32) for _ in range(4)]
+            dbet = [torch.empty(H, device=dev, dtype=torch.float32) for _ in range(4)]
+            native.bn_bwd(dpre2d, pre_raw, 4, H, [gf, gi, go, gc], save_mean, save_invstd, dproj, dgam, dbet,
+                          _ws(dev, 4 * H))
+        else:
+            dproj = dpre2d
+        # recurrent weight gradients: dU_g = sum_{t>=1} dpre_g[t]^T h[t-1]
+        dus = [torch.zeros(H, H, device=dev, dtype=torch.float32) for _ in range(4)]
+        if T > 1:
+            h2d = ctx.h_store.view(M, H)
+            native.bs_sddmm(rt.plan_h, dpre2d[B:], h2d[:M - B], dus, rt.mask_h)
+        dws = [torch.zeros(H, D, device=dev, dtype=torch.float32) for _ in range(4)]
+        native.bs_sddmm(rt.plan_x, dproj, x2d, dws, rt.mask_x)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx2d = torch.empty(M, D, device=dev, dtype=torch.float32)
+            native.bsgemm_nn(rt.plan_x, [wf, wi, wo, wc], dproj, dx2d)
+            dx = dx2d.view(T, B, D)
+        return (dx, dws[0], dws[1], dws[2], dws[3], dus[0], dus[1], dus[2], dus[3],
+                dgam[0], dbet[0], dgam[1], dbet[1], dgam[2], dbet[2], dgam[3], dbet[3], None)
+
+
+class MLPLayerFunction(torch.autograd.Function):
+    """One MLP layer: y = drop(act(bn(x W^T + b))) with act possibly LogSoftmax (neural_networks.py:306-317)."""
+
+    @staticmethod
+    def forward(ctx, x, w, b, gamma, beta, rt):
+        N, D = x.shape
+        O = w.shape[0]
+        dev = x.device
+        x2d = x if x.stride(-1) == 1 else x.contiguous()
+        z = torch.empty(N, O, device=dev, dtype=torch.float32)
+        cw = rt.q_ws[0] if rt.q_ws is not None else w
+        native.bsgemm_nt(rt.plan_x, [cw], x2d, z, [b] if b is not None else None)
+        save_mean = save_invstd = None
+        if rt.use_bn:
+            zb = torch.empty_like(z)
+            save_mean = torch.empty(O, device=dev, dtype=torch.float32)
+            save_invstd = torch.empty(O, device=dev, dtype=torch.float32)
+            native.bn_fwd(z, zb, 1, O, [gamma], [beta], [rt.bn_running[0][0]], [rt.bn_running[0][1]], rt.bn_eps,
+                          rt.bn_momentum, rt.training, save_mean, save_invstd, _ws(dev, O))
+        else:
+            zb = z
+        out = torch.empty_like(z)
+        if rt.softmax:
+            native.logsoftmax_fwd(zb, out, rt.log_prior)
+        else:
+            native.act_fwd(zb, out, rt.mlp_drop_mask, rt.act)
+        if any(ctx.needs_input_grad):
+            ctx.rt = rt
+            ctx.softmax = rt.softmax
+            ctx.had_prior = rt.log_prior is not None
+            ctx.drop_mask = rt.mlp_drop_mask
+            ctx.out_store = out.detach()
+            ctx.save_for_backward(x2d, cw, gamma, z, save_mean, save_invstd)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        rt = ctx.rt
+        x2d, w, gamma, z, save_mean, save_invstd = ctx.saved_tensors
+        N, D = x2d.shape
+        O = w.shape[0]
+        dev = dout.device
+        dout = dout.contiguous()
+        dzb = torch.empty(N, O, device=dev, dtype=torch.float32)
+        if ctx.softmax:
+            if ctx.had_prior:
+                raise native.NativeError('backward through a prior-normalised posterior is not defined')
+            native.logsoftmax_bwd(dout, ctx.out_store, dzb)
+        else:
+            native.act_bwd(dout, ctx.out_store, ctx.drop_mask, dzb, rt.act)
+        dgamma = dbeta = None
+        if rt.use_bn:
+            dz = torch.empty_like(dzb)
+            dgamma = torch.empty(O, device=dev, dtype=torch.float32)
+            dbeta = torch.empty(O, device=dev, dtype=torch.float32)
+            native.bn_bwd(dzb, z, 1, O, [gamma], save_mean, save_invstd, dz, [dgamma], [dbeta], _ws(dev, O))
+        else:
+            dz = dzb
+        db = None
+        if ctx.needs_input_grad[2]:
+            db = torch.empty(O, device=dev, dtype=torch.float32)
+            native.colsum(dz, 1, O, [db])
+        dw = torch.zeros(O, D, device=dev, dtype=torch.float32)
+        native.bs_sddmm(rt.plan_x, dz, x2d, [dw], rt.mask_x)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty(N, D, device=dev, dtype=torch.float32)
+            native.bsgemm_nn(rt.plan_x, [w], dz, dx)
+        return dx, dw, db, dgamma, dbeta, None

@@ -1,0 +1,318 @@
+"""ctypes binding of ``libhcgs_b200.so`` (the C ABI declared in ``include/hcgs_b200.h``).
+
+This is the only place Python touches the native library.  There is deliberately no
+fallback: if the shared object is missing, or a compute entry point is called without
+a CUDA device, an exception is raised -- the product path never silently runs on the CPU.
+PyTorch is used for device memory and streams only (``tensor.data_ptr()``,
+``torch.cuda.current_stream()``).
+"""
+import ctypes
+import os
+from ctypes import POINTER, c_char_p, c_float, c_int, c_int64, c_void_p
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(os.path.dirname(_HERE), 'libhcgs_b200.so')
+
+ACT_CODES = {'linear': 0, 'relu': 1, 'tanh': 2, 'htanh': 3, 'sigmoid': 4, 'leaky_relu': 5, 'elu': 6}
+MAX_GROUPS = 4
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+_lib = None
+
+_f = c_void_p          # device pointer to float (passed as integer address)
+_pp = POINTER(c_void_p)  # host array of device pointers
+
+# name -> (restype, argtypes); kept in one table so tests can check it against the header
+SIGNATURES = {
+    'hcgs_abi_version': (c_int, []),
+    'hcgs_last_error': (c_char_p, []),
+    'hcgs_device_info': (c_int, [c_int, POINTER(c_int)]),
+    'hcgs_plan_create': (c_int, [POINTER(c_float), c_int, c_int, c_int, c_int, POINTER(c_void_p)]),
+    'hcgs_plan_destroy': (c_int, [c_void_p]),
+    'hcgs_plan_info': (c_int, [c_void_p, POINTER(c_int64)]),
+    'hcgs_mask_apply': (c_int, [_pp, c_int, _f, c_int64, c_void_p]),
+    'hcgs_quantize_w': (c_int, [_f, _f, c_int64, c_int, c_void_p]),
+    'hcgs_quantize_act': (c_int, [_f, c_int, _f, c_int, c_int64, c_int, c_int, c_int, _f, c_void_p]),
+    'hcgs_bsgemm_nt': (c_int, [c_void_p, c_int, _pp, c_int, _f, c_int, c_int64, _pp, _f, c_int, c_void_p]),
+    'hcgs_bsgemm_nn': (c_int, [c_void_p, c_int, _pp, c_int, _f, c_int, c_int64, _f, c_int, c_void_p]),
+    'hcgs_bs_sddmm': (c_int, [c_void_p, c_int, _f, c_int, _f, c_int, c_int64, _pp, c_int, _f, c_void_p]),
+    'hcgs_colsum': (c_int, [_f, c_int, c_int64, c_int, c_int, _pp, c_void_p]),
+    'hcgs_bn_fwd': (c_int, [_f, c_int, _f, c_int, c_int64, c_int, c_int, _pp, _pp, _pp, _pp, c_float, c_float,
+                            c_int, _f, _f, _f, c_int64, c_void_p]),
+    'hcgs_bn_bwd': (c_int, [_f, c_int, _f, c_int, c_int64, c_int, c_int, _pp, _f, _f, _f, c_int, _pp, _pp, _f,
+                            c_int64, c_void_p]),
+    'hcgs_lstm_pack': (c_int, [c_void_p, _pp, c_int, _f, _f, c_void_p]),
+    'hcgs_lstm_fwd': (c_int, [c_void_p, _f, _f, _f, c_float, c_int, c_int, c_int, _f, _f, _f, c_int, c_void_p]),
+    'hcgs_lstm_bwd': (c_int, [c_void_p, _f, _f, _f, _f, _f, c_float, c_int, c_int, c_int, _f, c_void_p]),
+    'hcgs_act_fwd': (c_int, [_f, _f, _f, c_int64, c_int, c_void_p]),
+    'hcgs_act_bwd': (c_int, [_f, _f, _f, _f, c_int64, c_int, c_void_p]),
+    'hcgs_logsoftmax_fwd': (c_int, [_f, c_int, _f, c_int, c_int64, c_int, _f, c_void_p]),
+    'hcgs_logsoftmax_bwd': (c_int, [_f, _f, _f, c_int64, c_int, c_void_p]),
+    'hcgs_nll_fwd_bwd': (c_int, [_f, c_int64, c_int, _f, c_int, c_float, _f, _f, c_void_p]),
+    'hcgs_opt_step': (c_int, [c_int, _f, _f, _f, _f, c_int64, POINTER(c_float), c_float, c_void_p]),
+}
+
+
+def load():
+    """dlopen the library once; raise NativeError if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise NativeError(
+            'native library %s is missing: run `python -c "import __graft_entry__ as g; g.build()"` '
+            '(or ./build_native.sh) -- there is no CPU fallback' % LIB_PATH)
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    if lib.hcgs_abi_version() != 1:
+        raise NativeError('ABI version mismatch: library %d, binding 1' % lib.hcgs_abi_version())
+    _lib = lib
+    return lib
+
+
+def _check(rc, what):
+    if rc != 0:
+        msg = load().hcgs_last_error()
+        raise NativeError('%s failed (%d): %s' % (what, rc, msg.decode() if msg else '?'))
+
+
+def _require_cuda(*tensors):
+    if not torch.cuda.is_available():
+        raise NativeError('no CUDA device: the HCGS hot path has no CPU fallback')
+    for t in tensors:
+        if t is None:
+            continue
+        if not t.is_cuda:
+            raise NativeError('expected a CUDA tensor, got %s' % t.device)
+        if t.dtype != torch.float32:
+            raise NativeError('expected float32, got %s' % t.dtype)
+
+
+def _stream():
+    return c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ptr(t):
+    return c_void_p(0) if t is None else c_void_p(t.data_ptr())
+
+
+def _ptrs(ts):
+    """Host array of device pointers (NULL-able entries)."""
+    if ts is None:
+        return None
+    arr = (c_void_p * len(ts))()
+    for i, t in enumerate(ts):
+        arr[i] = None if t is None else t.data_ptr()
+    return ctypes.cast(arr, _pp)
+
+
+def _row_major_2d(t, what):
+    """(tensor, ld): accept any 2-D view whose last dim is contiguous (e.g. a column slice)."""
+    if t.dim() != 2 or (t.shape[1] > 1 and t.stride(1) != 1):
+        raise NativeError('%s must be a 2-D row-major view, got shape %s stride %s' % (what, tuple(t.shape), t.stride()))
+    ld = t.stride(0) if t.shape[0] > 1 else max(t.shape[1], t.stride(0))
+    return ld
+
+
+def device_info(device=0):
+    info = (c_int * 8)()
+    _check(load().hcgs_device_info(device, info), 'hcgs_device_info')
+    return {'sm_count': info[0], 'cc': (info[1], info[2]), 'smem_optin': info[3], 'cluster_launch': bool(info[4])}
+
+
+class Plan:
+    """Owns one ``hcgs_plan`` (device copies of the block index of one mask)."""
+
+    def __init__(self, mask, recurrent=False, cluster_size=0):
+        lib = load()
+        if not torch.cuda.is_available():
+            raise NativeError('no CUDA device: cannot create a plan')
+        m = mask.detach().to('cpu', torch.float32).contiguous()
+        self.n_out, self.n_in = int(m.shape[0]), int(m.shape[1])
+        h = c_void_p()
+        _check(lib.hcgs_plan_create(ctypes.cast(m.data_ptr(), POINTER(c_float)), self.n_out, self.n_in,
+                                    1 if recurrent else 0, int(cluster_size), ctypes.byref(h)), 'hcgs_plan_create')
+        self._h = h
+        info = (c_int64 * 16)()
+        _check(lib.hcgs_plan_info(self._h, info), 'hcgs_plan_info')
+        self.nz_tiles, self.total_tiles, self.nnz = int(info[2]), int(info[3]), int(info[4])
+        self.recurrent = bool(recurrent)
+        self.cluster_size, self.rows_per_cta, self.bell_width = int(info[5]), int(info[6]), int(info[7])
+        self.fwd_pack_floats, self.bwd_pack_floats = int(info[8]), int(info[9])
+        self.smem_fwd, self.smem_bwd, self.threads = int(info[10]), int(info[11]), int(info[12])
+        self.n_blocks, self.w_in_smem = int(info[13]), bool(info[14])
+
+    @property
+    def handle(self):
+        if self._h is None:
+            raise NativeError('plan already destroyed')
+        return self._h
+
+    def destroy(self):
+        if getattr(self, '_h', None) is not None and _lib is not None:
+            _lib.hcgs_plan_destroy(self._h)
+        self._h = None
+
+    def __del__(self):
+        try:
+            self.destroy()
+        except Exception:
+            pass
+
+
+# ---------------------------------------------------------------------------------------------
+# thin typed wrappers (argument checking only; all arithmetic is in the library)
+# ---------------------------------------------------------------------------------------------
+
+def mask_apply(weights, mask):
+    _require_cuda(mask, *weights)
+    n = mask.numel()
+    for w in weights:
+        assert w.is_contiguous() and w.numel() == n
+    assert mask.is_contiguous()
+    _check(load().hcgs_mask_apply(_ptrs(weights), len(weights), _ptr(mask), n, _stream()), 'hcgs_mask_apply')
+
+
+def quantize_w(master, out, bits):
+    _require_cuda(master, out)
+    assert master.is_contiguous() and out.is_contiguous() and master.numel() == out.numel()
+    _check(load().hcgs_quantize_w(_ptr(master), _ptr(out), master.numel(), int(bits), _stream()), 'hcgs_quantize_w')
+
+
+def quantize_act(x2d, y2d, bits, repeat, scratch):
+    _require_cuda(x2d, y2d, scratch)
+    ldx, ldy = _row_major_2d(x2d, 'x'), _row_major_2d(y2d, 'y')
+    _check(load().hcgs_quantize_act(_ptr(x2d), ldx, _ptr(y2d), ldy, x2d.shape[0], x2d.shape[1], int(bits),
+                                    int(repeat), _ptr(scratch), _stream()), 'hcgs_quantize_act')
+
+
+def bsgemm_nt(plan, weights, x2d, y2d, biases=None):
+    """y2d[:, g*n_out:(g+1)*n_out] = x2d @ weights[g].T (+ bias[g])"""
+    _require_cuda(x2d, y2d, *weights)
+    ldw = _row_major_2d(weights[0], 'w')
+    for w in weights:
+        assert tuple(w.shape) == (plan.n_out, plan.n_in) and _row_major_2d(w, 'w') == ldw
+    assert x2d.shape[1] == plan.n_in and y2d.shape[1] == len(weights) * plan.n_out and y2d.shape[0] == x2d.shape[0]
+    _check(load().hcgs_bsgemm_nt(plan.handle, len(weights), _ptrs(weights), ldw, _ptr(x2d),
+                                 _row_major_2d(x2d, 'x'), x2d.shape[0], _ptrs(biases), _ptr(y2d),
+                                 _row_major_2d(y2d, 'y'), _stream()), 'hcgs_bsgemm_nt')
+
+
+def bsgemm_nn(plan, weights, dy2d, dx2d):
+    _require_cuda(dy2d, dx2d, *weights)
+    ldw = _row_major_2d(weights[0], 'w')
+    assert dy2d.shape[1] == len(weights) * plan.n_out and dx2d.shape[1] == plan.n_in
+    _check(load().hcgs_bsgemm_nn(plan.handle, len(weights), _ptrs(weights), ldw, _ptr(dy2d),
+                                 _row_major_2d(dy2d, 'dy'), dy2d.shape[0], _ptr(dx2d),
+                                 _row_major_2d(dx2d, 'dx'), _stream()), 'hcgs_bsgemm_nn')
+
+
+def bs_sddmm(plan, dy2d, x2d, dws, mask=None):
+    _require_cuda(dy2d, x2d, mask, *dws)
+    lddw = _row_major_2d(dws[0], 'dw')
+    assert dy2d.shape[0] == x2d.shape[0] and x2d.shape[1] == plan.n_in
+    _check(load().hcgs_bs_sddmm(plan.handle, len(dws), _ptr(dy2d), _row_major_2d(dy2d, 'dy'), _ptr(x2d),
+                                _row_major_2d(x2d, 'x'), x2d.shape[0], _ptrs(dws), lddw, _ptr(mask), _stream()),
+           'hcgs_bs_sddmm')
+
+
+def colsum(dy2d, n_groups, group_cols, outs):
+    _require_cuda(dy2d, *outs)
+    _check(load().hcgs_colsum(_ptr(dy2d), _row_major_2d(dy2d, 'dy'), dy2d.shape[0], n_groups, group_cols,
+                              _ptrs(outs), _stream()), 'hcgs_colsum')
+
+
+def bn_fwd(x2d, y2d, n_groups, group_cols, gammas, betas, rmeans, rvars, eps, momentum, training, save_mean,
+           save_invstd, workspace):
+    _require_cuda(x2d, y2d, save_mean, save_invstd, workspace)
+    _check(load().hcgs_bn_fwd(_ptr(x2d), _row_major_2d(x2d, 'x'), _ptr(y2d), _row_major_2d(y2d, 'y'), x2d.shape[0],
+                              n_groups, group_cols, _ptrs(gammas), _ptrs(betas), _ptrs(rmeans), _ptrs(rvars),
+                              float(eps), float(momentum), 1 if training else 0, _ptr(save_mean),
+                              _ptr(save_invstd), _ptr(workspace),
+                              0 if workspace is None else workspace.numel(), _stream()), 'hcgs_bn_fwd')
+
+
+def bn_bwd(dy2d, x2d, n_groups, group_cols, gammas, save_mean, save_invstd, dx2d, dgammas, dbetas, workspace):
+    _require_cuda(dy2d, x2d, dx2d, save_mean, save_invstd, workspace)
+    _check(load().hcgs_bn_bwd(_ptr(dy2d), _row_major_2d(dy2d, 'dy'), _ptr(x2d), _row_major_2d(x2d, 'x'),
+                              x2d.shape[0], n_groups, group_cols, _ptrs(gammas), _ptr(save_mean),
+                              _ptr(save_invstd), _ptr(dx2d), _row_major_2d(dx2d, 'dx'), _ptrs(dgammas),
+                              _ptrs(dbetas), _ptr(workspace), workspace.numel(), _stream()), 'hcgs_bn_bwd')
+
+
+def lstm_pack(plan, us, fwd_pack=None, bwd_pack=None):
+    _require_cuda(fwd_pack, bwd_pack, *us)
+    ldu = _row_major_2d(us[0], 'u')
+    assert len(us) == 4
+    _check(load().hcgs_lstm_pack(plan.handle, _ptrs(us), ldu, _ptr(fwd_pack), _ptr(bwd_pack), _stream()),
+           'hcgs_lstm_pack')
+
+
+def lstm_fwd(plan, fwd_pack, pre, drop, drop_scalar, act, h_out, c_out=None, gates_out=None, act_bits=0):
+    _require_cuda(fwd_pack, pre, drop, h_out, c_out, gates_out)
+    T, B = pre.shape[0], pre.shape[1]
+    assert pre.is_contiguous() and h_out.is_contiguous() and pre.shape[2] == 4 * plan.n_out
+    _check(load().hcgs_lstm_fwd(plan.handle, _ptr(fwd_pack), _ptr(pre), _ptr(drop), float(drop_scalar), int(act),
+                                T, B, _ptr(h_out), _ptr(c_out), _ptr(gates_out), int(act_bits), _stream()),
+           'hcgs_lstm_fwd')
+
+
+def lstm_bwd(plan, bwd_pack, dh_out, gates, c, drop, drop_scalar, act, dpre):
+    _require_cuda(bwd_pack, dh_out, gates, c, drop, dpre)
+    T, B = dh_out.shape[0], dh_out.shape[1]
+    assert dh_out.is_contiguous() and gates.is_contiguous() and c.is_contiguous() and dpre.is_contiguous()
+    _check(load().hcgs_lstm_bwd(plan.handle, _ptr(bwd_pack), _ptr(dh_out), _ptr(gates), _ptr(c), _ptr(drop),
+                                float(drop_scalar), int(act), T, B, _ptr(dpre), _stream()), 'hcgs_lstm_bwd')
+
+
+def act_fwd(x, y, drop_mask, act):
+    _require_cuda(x, y, drop_mask)
+    assert x.is_contiguous() and y.is_contiguous()
+    _check(load().hcgs_act_fwd(_ptr(x), _ptr(y), _ptr(drop_mask), x.numel(), int(act), _stream()), 'hcgs_act_fwd')
+
+
+def act_bwd(dy, y, drop_mask, dx, act):
+    _require_cuda(dy, y, drop_mask, dx)
+    assert dy.is_contiguous() and y.is_contiguous() and dx.is_contiguous()
+    _check(load().hcgs_act_bwd(_ptr(dy), _ptr(y), _ptr(drop_mask), _ptr(dx), dy.numel(), int(act), _stream()),
+           'hcgs_act_bwd')
+
+
+def logsoftmax_fwd(z2d, out2d, log_prior=None):
+    _require_cuda(z2d, out2d, log_prior)
+    _check(load().hcgs_logsoftmax_fwd(_ptr(z2d), _row_major_2d(z2d, 'z'), _ptr(out2d), _row_major_2d(out2d, 'out'),
+                                      z2d.shape[0], z2d.shape[1], _ptr(log_prior), _stream()), 'hcgs_logsoftmax_fwd')
+
+
+def logsoftmax_bwd(dlogp, logp, dz):
+    _require_cuda(dlogp, logp, dz)
+    assert dlogp.is_contiguous() and logp.is_contiguous() and dz.is_contiguous()
+    _check(load().hcgs_logsoftmax_bwd(_ptr(dlogp), _ptr(logp), _ptr(dz), logp.shape[0], logp.shape[1], _stream()),
+           'hcgs_logsoftmax_bwd')
+
+
+def nll_fwd_bwd(logp, labels, ldlab, scale, dz, stats):
+    _require_cuda(logp, labels, dz, stats)
+    assert logp.is_contiguous()
+    _check(load().hcgs_nll_fwd_bwd(_ptr(logp), logp.shape[0], logp.shape[1], _ptr(labels), int(ldlab), float(scale),
+                                   _ptr(dz), _ptr(stats), _stream()), 'hcgs_nll_fwd_bwd')
+
+
+OPT_KINDS = {'sgd': 0, 'rmsprop': 1, 'adam': 2}
+
+
+def opt_step(kind, param, grad, state1, state2, hp, grad_scale=1.0):
+    _require_cuda(param, grad, state1, state2)
+    assert param.is_contiguous() and grad.is_contiguous() and len(hp) == 8
+    arr = (c_float * 8)(*[float(v) for v in hp])
+    _check(load().hcgs_opt_step(OPT_KINDS[kind], _ptr(param), _ptr(grad), _ptr(state1), _ptr(state2), param.numel(),
+                                arr, float(grad_scale), _stream()), 'hcgs_opt_step')

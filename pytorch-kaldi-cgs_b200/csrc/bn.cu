@@ -1,0 +1,267 @@
+// Batch normalisation over the time-batched rows (nn.BatchNorm1d semantics, fp32).
+//
+// The reference normalises each gate's [T*B, H] projection with its own BatchNorm1d
+// (neural_networks.py:957-976, momentum 0.05, eps 1e-5); padded frames are part of the statistics.
+// Here the four gates are one [M, 4H] matrix with per-group parameter pointers.
+//
+// Statistics: rows are split over S CTAs per 32-column strip; every split computes a local
+// (mean, M2) pair with a two-pass scan of its rows and the splits are merged in a fixed order with
+// Chan's formula, so the result is deterministic and free of E[x^2]-E[x]^2 cancellation.
+#include "common.cuh"
+
+namespace hcgs {
+
+__device__ __forceinline__ float block_col_reduce(float v, float (*red)[33], int warp, int lane) {
+    red[warp][lane] = v;
+    __syncthreads();
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += red[w][lane];
+    __syncthreads();
+    return t;
+}
+
+// partial[(split*Ctot + col)*2 + {0,1}] = {mean, M2} over this split's rows
+__global__ void __launch_bounds__(256) bn_stats_partial_kernel(const float* __restrict__ x, int ldx, int64_t M,
+                                                               int Ctot, int64_t rows_per_split,
+                                                               float* __restrict__ partial) {
+    __shared__ float red[8][33];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int col = blockIdx.x * 32 + lane;
+    const int64_t mbeg = (int64_t)blockIdx.y * rows_per_split;
+    const int64_t mend = (mbeg + rows_per_split < M) ? mbeg + rows_per_split : M;
+    const bool ok = col < Ctot;
+    const float n = (float)(mend - mbeg);
+    float s = 0.f;
+    if (ok)
+        for (int64_t m = mbeg + warp; m < mend; m += 8) s += __ldg(x + m * ldx + col);
+    const float mean = block_col_reduce(s, red, warp, lane) / n;
+    float q = 0.f;
+    if (ok)
+        for (int64_t m = mbeg + warp; m < mend; m += 8) {
+            const float d = __ldg(x + m * ldx + col) - mean;
+            q = fmaf(d, d, q);
+        }
+    const float m2 = block_col_reduce(q, red, warp, lane);
+    if (warp == 0 && ok) {
+        partial[((int64_t)blockIdx.y * Ctot + col) * 2 + 0] = mean;
+        partial[((int64_t)blockIdx.y * Ctot + col) * 2 + 1] = m2;
+    }
+}
+
+__global__ void bn_stats_finalize_kernel(const float* __restrict__ partial, int splits, int64_t M,
+                                         int64_t rows_per_split, int Ctot, int C, float eps, float momentum,
+                                         PtrPack<float> rmean, PtrPack<float> rvar,
+                                         float* __restrict__ save_mean, float* __restrict__ save_invstd) {
+    const int col = blockIdx.x * blockDim.x + threadIdx.x;
+    if (col >= Ctot) return;
+    float n = 0.f, mean = 0.f, m2 = 0.f;
+    for (int s = 0; s < splits; ++s) {
+        const int64_t mbeg = (int64_t)s * rows_per_split;
+        const int64_t mend = (mbeg + rows_per_split < M) ? mbeg + rows_per_split : M;
+        const float nb = (float)(mend - mbeg);
+        const float mb = partial[((int64_t)s * Ctot + col) * 2 + 0];
+        const float qb = partial[((int64_t)s * Ctot + col) * 2 + 1];
+        const float nt = n + nb;
+        const float delta = mb - mean;
+        mean += delta * (nb / nt);
+        m2 += qb + delta * delta * (n * nb / nt);
+        n = nt;
+    }
+    const float var_b = m2 / n;
+    save_mean[col] = mean;
+    save_invstd[col] = rsqrtf(var_b + eps);
+    // 1/sqrt via rsqrtf is ~1 ulp; refine once to match a correctly rounded 1/sqrt
+    {
+        const float v = var_b + eps;
+        float r = save_invstd[col];
+        r = r * (1.5f - 0.5f * v * r * r);
+        save_invstd[col] = r;
+    }
+    const int g = col / C, c = col % C;
+    if (rmean.p[g]) rmean.p[g][c] = (1.f - momentum) * rmean.p[g][c] + momentum * mean;
+    if (rvar.p[g]) {
+        const float var_u = (n > 1.f) ? m2 / (n - 1.f) : var_b;
+        rvar.p[g][c] = (1.f - momentum) * rvar.p[g][c] + momentum * var_u;
+    }
+}
+
+// y = (x - mean) * invstd * gamma + beta ; in eval mode mean/invstd come from the running stats
+__global__ void __launch_bounds__(256) bn_apply_kernel(const float* __restrict__ x, int ldx,
+                                                       float* __restrict__ y, int ldy, int64_t M, int Ctot,
+                                                       int C, PtrPack<const float> gamma,
+                                                       PtrPack<const float> beta, PtrPack<float> rmean,
+                                                       PtrPack<float> rvar, float eps, int training,
+                                                       const float* __restrict__ save_mean,
+                                                       const float* __restrict__ save_invstd,
+                                                       int rows_per_block) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int col = blockIdx.x * 32 + lane;
+    if (col >= Ctot) return;
+    const int g = col / C, c = col % C;
+    float mean, invstd;
+    if (training) {
+        mean = save_mean[col];
+        invstd = save_invstd[col];
+    } else {
+        mean = rmean.p[g][c];
+        invstd = 1.0f / sqrtf(rvar.p[g][c] + eps);
+    }
+    const float ga = gamma.p[g] ? __ldg(gamma.p[g] + c) : 1.f;
+    const float be = beta.p[g] ? __ldg(beta.p[g] + c) : 0.f;
+    const float a = invstd * ga;
+    const int64_t mbeg = (int64_t)blockIdx.y * rows_per_block;
+    const int64_t mend = (mbeg + rows_per_block < M) ? mbeg + rows_per_block : M;
+    for (int64_t m = mbeg + warp; m < mend; m += 8) y[m * ldy + col] = (x[m * ldx + col] - mean) * a + be;
+}
+
+// partial[(split*Ctot+col)*2] = {sum dy, sum dy*xhat}
+__global__ void __launch_bounds__(256) bn_bwd_partial_kernel(const float* __restrict__ dy, int lddy,
+                                                             const float* __restrict__ x, int ldx, int64_t M,
+                                                             int Ctot, int64_t rows_per_split,
+                                                             const float* __restrict__ save_mean,
+                                                             const float* __restrict__ save_invstd,
+                                                             float* __restrict__ partial) {
+    __shared__ float red[8][33];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int col = blockIdx.x * 32 + lane;
+    const bool ok = col < Ctot;
+    const int64_t mbeg = (int64_t)blockIdx.y * rows_per_split;
+    const int64_t mend = (mbeg + rows_per_split < M) ? mbeg + rows_per_split : M;
+    const float mean = ok ? save_mean[col] : 0.f, invstd = ok ? save_invstd[col] : 0.f;
+    float s1 = 0.f, s2 = 0.f;
+    if (ok)
+        for (int64_t m = mbeg + warp; m < mend; m += 8) {
+            const float d = __ldg(dy + m * lddy + col);
+            const float xh = (__ldg(x + m * ldx + col) - mean) * invstd;
+            s1 += d;
+            s2 = fmaf(d, xh, s2);
+        }
+    const float t1 = block_col_reduce(s1, red, warp, lane);
+    const float t2 = block_col_reduce(s2, red, warp, lane);
+    if (warp == 0 && ok) {
+        partial[((int64_t)blockIdx.y * Ctot + col) * 2 + 0] = t1;
+        partial[((int64_t)blockIdx.y * Ctot + col) * 2 + 1] = t2;
+    }
+}
+
+__global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const float* __restrict__ dy, int lddy,
+                                                           const float* __restrict__ x, int ldx, int64_t M,
+                                                           int Ctot, int C, PtrPack<const float> gamma,
+                                                           const float* __restrict__ save_mean,
+                                                           const float* __restrict__ save_invstd,
+                                                           const float* __restrict__ partial, int splits,
+                                                           float* __restrict__ dx, int lddx,
+                                                           PtrPack<float> dgamma, PtrPack<float> dbeta,
+                                                           int rows_per_block) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int col = blockIdx.x * 32 + lane;
+    if (col >= Ctot) return;
+    const int g = col / C, c = col % C;
+    float s1 = 0.f, s2 = 0.f;
+    for (int s = 0; s < splits; ++s) {
+        s1 += partial[((int64_t)s * Ctot + col) * 2 + 0];
+        s2 += partial[((int64_t)s * Ctot + col) * 2 + 1];
+    }
+    if (blockIdx.y == 0 && warp == 0) {
+        if (dgamma.p[g]) dgamma.p[g][c] = s2;
+        if (dbeta.p[g]) dbeta.p[g][c] = s1;
+    }
+    const float mean = save_mean[col], invstd = save_invstd[col];
+    const float ga = gamma.p[g] ? __ldg(gamma.p[g] + c) : 1.f;
+    const float inv_m = 1.0f / (float)M;
+    const float k1 = s1 * inv_m, k2 = s2 * inv_m, a = ga * invstd;
+    const int64_t mbeg = (int64_t)blockIdx.y * rows_per_block;
+    const int64_t mend = (mbeg + rows_per_block < M) ? mbeg + rows_per_block : M;
+    for (int64_t m = mbeg + warp; m < mend; m += 8) {
+        const float xh = (x[m * ldx + col] - mean) * invstd;
+        dx[m * lddx + col] = a * (dy[m * lddy + col] - k1 - xh * k2);
+    }
+}
+
+static int pick_splits(int64_t M, int strips, int64_t ws_floats, int Ctot, int64_t* rows_out) {
+    int splits = 1;
+    const int target = 148 * 4;
+    if (strips < target) splits = (target + strips - 1) / strips;
+    int64_t max_s = ws_floats / (2 * (int64_t)Ctot);
+    if (splits > max_s) splits = (int)max_s;
+    if (splits > 256) splits = 256;
+    if (splits < 1) splits = 1;
+    int64_t rows = (M + splits - 1) / splits;
+    if (rows < 64) rows = 64;
+    splits = (int)((M + rows - 1) / rows);
+    *rows_out = rows;
+    return splits;
+}
+
+}  // namespace hcgs
+
+using namespace hcgs;
+
+extern "C" int hcgs_bn_fwd(const float* x, int ldx, float* y, int ldy, int64_t m, int n_groups, int group_cols,
+                           const float* const* gamma, const float* const* beta, float* const* running_mean,
+                           float* const* running_var, float eps, float momentum, int training, float* save_mean,
+                           float* save_invstd, float* workspace, int64_t workspace_floats, hcgs_stream stream) {
+    HCGS_REQUIRE(x && y, "hcgs_bn_fwd: NULL argument");
+    HCGS_REQUIRE(n_groups >= 1 && n_groups <= HCGS_MAX_GROUPS, "hcgs_bn_fwd: n_groups out of range");
+    if (m <= 0) return 0;
+    const int Ctot = n_groups * group_cols;
+    const int strips = (Ctot + 31) / 32;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (training) {
+        HCGS_REQUIRE(save_mean && save_invstd && workspace, "hcgs_bn_fwd: training needs save buffers + workspace");
+        HCGS_REQUIRE(workspace_floats >= 2 * (int64_t)Ctot, "hcgs_bn_fwd: workspace too small");
+        int64_t rows;
+        const int splits = pick_splits(m, strips, workspace_floats, Ctot, &rows);
+        bn_stats_partial_kernel<<<dim3(strips, splits), 256, 0, st>>>(x, ldx, m, Ctot, rows, workspace);
+        HCGS_LAUNCH_CHECK();
+        bn_stats_finalize_kernel<<<(Ctot + 127) / 128, 128, 0, st>>>(
+            workspace, splits, m, rows, Ctot, group_cols, eps, momentum, make_pack<float>(running_mean, n_groups),
+            make_pack<float>(running_var, n_groups), save_mean, save_invstd);
+        HCGS_LAUNCH_CHECK();
+    } else {
+        HCGS_REQUIRE(running_mean && running_var, "hcgs_bn_fwd: eval needs running statistics");
+    }
+    int rows_per_block = 256;
+    int64_t yb = (m + rows_per_block - 1) / rows_per_block;
+    while (yb > 65535) {
+        rows_per_block *= 2;
+        yb = (m + rows_per_block - 1) / rows_per_block;
+    }
+    bn_apply_kernel<<<dim3(strips, (unsigned)yb), 256, 0, st>>>(
+        x, ldx, y, ldy, m, Ctot, group_cols, make_pack<const float>(gamma, n_groups),
+        make_pack<const float>(beta, n_groups), make_pack<float>(running_mean, n_groups),
+        make_pack<float>(running_var, n_groups), eps, training, save_mean, save_invstd, rows_per_block);
+    HCGS_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int hcgs_bn_bwd(const float* dy, int lddy, const float* x, int ldx, int64_t m, int n_groups,
+                           int group_cols, const float* const* gamma, const float* save_mean,
+                           const float* save_invstd, float* dx, int lddx, float* const* dgamma,
+                           float* const* dbeta, float* workspace, int64_t workspace_floats, hcgs_stream stream) {
+    HCGS_REQUIRE(dy && x && dx && save_mean && save_invstd && workspace, "hcgs_bn_bwd: NULL argument");
+    HCGS_REQUIRE(n_groups >= 1 && n_groups <= HCGS_MAX_GROUPS, "hcgs_bn_bwd: n_groups out of range");
+    if (m <= 0) return 0;
+    const int Ctot = n_groups * group_cols;
+    HCGS_REQUIRE(workspace_floats >= 2 * (int64_t)Ctot, "hcgs_bn_bwd: workspace too small");
+    const int strips = (Ctot + 31) / 32;
+    cudaStream_t st = (cudaStream_t)stream;
+    int64_t rows;
+    const int splits = pick_splits(m, strips, workspace_floats, Ctot, &rows);
+    bn_bwd_partial_kernel<<<dim3(strips, splits), 256, 0, st>>>(dy, lddy, x, ldx, m, Ctot, rows, save_mean,
+                                                               save_invstd, workspace);
+    HCGS_LAUNCH_CHECK();
+    int rows_per_block = 256;
+    int64_t yb = (m + rows_per_block - 1) / rows_per_block;
+    while (yb > 65535) {
+        rows_per_block *= 2;
+        yb = (m + rows_per_block - 1) / rows_per_block;
+    }
+    bn_bwd_apply_kernel<<<dim3(strips, (unsigned)yb), 256, 0, st>>>(
+        dy, lddy, x, ldx, m, Ctot, group_cols, make_pack<const float>(gamma, n_groups), save_mean, save_invstd,
+        workspace, splits, dx, lddx, make_pack<float>(dgamma, n_groups), make_pack<float>(dbeta, n_groups),
+        rows_per_block);
+    HCGS_LAUNCH_CHECK();
+    return 0;
+}

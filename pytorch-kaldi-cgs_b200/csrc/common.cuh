@@ -1,0 +1,147 @@
+// Shared helpers for the HCGS B200 (sm_100a) kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "../../include/hcgs_b200.h"
+
+namespace hcgs {
+
+// ---- error plumbing (no exception crosses the C ABI) -------------------------------------
+void set_error(const char* fmt, ...);
+
+#define HCGS_CHECK_CUDA(expr)                                                              \
+    do {                                                                                   \
+        cudaError_t _e = (expr);                                                           \
+        if (_e != cudaSuccess) {                                                           \
+            hcgs::set_error("%s failed at %s:%d: %s", #expr, __FILE__, __LINE__,           \
+                            cudaGetErrorString(_e));                                       \
+            return 1;                                                                      \
+        }                                                                                  \
+    } while (0)
+
+#define HCGS_REQUIRE(cond, ...)                                                            \
+    do {                                                                                   \
+        if (!(cond)) {                                                                     \
+            hcgs::set_error(__VA_ARGS__);                                                  \
+            return 2;                                                                      \
+        }                                                                                  \
+    } while (0)
+
+#define HCGS_LAUNCH_CHECK() HCGS_CHECK_CUDA(cudaGetLastError())
+
+// A handful of device pointers passed by value into a kernel (the gates of one layer).
+template <typename T>
+struct PtrPack {
+    T* p[HCGS_MAX_GROUPS];
+};
+
+template <typename T>
+static inline PtrPack<T> make_pack(T* const* src, int n) {
+    PtrPack<T> r;
+    for (int i = 0; i < HCGS_MAX_GROUPS; ++i) r.p[i] = (src != nullptr && i < n) ? src[i] : nullptr;
+    return r;
+}
+
+constexpr int kTile = 32;  // weight sparsity tile (rows x cols) used by the block-sparse GEMMs
+
+// ---- the opaque plan --------------------------------------------------------------------
+struct RecurrentPlan {
+    int CL = 0;        // CTAs per cluster (each cluster runs 8 sequences over all H hidden units)
+    int Hc = 0;        // hidden units (rows of U) owned by one CTA, multiple of 4
+    int HcP = 0;       // Hc padded so that HcP % 4 == 1 (gate buffer stride)
+    int RG = 0;        // 4-row groups per CTA = Hc/4
+    int L = 0;         // BELL width: max non-empty 4x4 blocks in any row group
+    int NCG = 0;       // column groups = ceil(H/4)
+    int max_cta_blocks = 0;  // largest number of real blocks owned by one CTA
+    int n_blocks = 0;        // real blocks in total
+    int threads = 0;         // block size of both recurrent kernels (16 threads per row group)
+    bool w_in_smem = true;   // false: compressed weights stay in global memory (too large for smem)
+    uint16_t* d_bidx = nullptr;     // [CL][L][RG] column group of block j of row group a (0xFFFF = padding)
+    int* d_cta_blk_off = nullptr;   // [CL+1] offsets into the flat real-block list
+    uint16_t* d_blk_a = nullptr;    // [n_blocks] local row group of real block s
+    uint16_t* d_blk_c = nullptr;    // [n_blocks] column group of real block s
+    int* d_cg_ptr = nullptr;        // [CL][NCG+1] per-CTA CSR: column group -> block slots
+    uint16_t* d_cg_list = nullptr;  // [n_blocks] local block slots grouped by column group
+    int64_t fwd_pack_floats = 0;    // CL*L*RG*64
+    int64_t bwd_pack_floats = 0;    // n_blocks*64
+    size_t smem_fwd = 0, smem_bwd = 0;
+};
+
+}  // namespace hcgs
+
+struct hcgs_plan {
+    int n_out = 0, n_in = 0;
+    int tr = 0, tc = 0;  // tile rows / cols
+    int nz_tiles = 0;
+    int64_t nnz = 0;
+    int* d_row_ptr = nullptr;  // [tr+1]   CSR over tiles
+    int* d_col_idx = nullptr;  // [nz]
+    int* d_col_ptr = nullptr;  // [tc+1]   CSC over tiles
+    int* d_row_idx = nullptr;  // [nz]
+    int* d_tile_rc = nullptr;  // [nz*2]   (tile row, tile col) flat list for the SDDMM
+    int max_row_tiles = 0, max_col_tiles = 0;
+    bool recurrent = false;
+    hcgs::RecurrentPlan rp;
+};
+
+namespace hcgs {
+
+// ---- device math ------------------------------------------------------------------------
+__device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + expf(-x)); }
+
+__device__ __forceinline__ float act_apply(int act, float x) {
+    switch (act) {
+        case HCGS_ACT_RELU: return x > 0.f ? x : 0.f;
+        case HCGS_ACT_TANH: return tanhf(x);
+        case HCGS_ACT_HTANH: return fminf(fmaxf(x, -1.f), 1.f);
+        case HCGS_ACT_SIGMOID: return sigmoidf_(x);
+        case HCGS_ACT_LEAKY_RELU: return x > 0.f ? x : 0.2f * x;
+        case HCGS_ACT_ELU: return x > 0.f ? x : expm1f(x);
+        default: return x;
+    }
+}
+
+// derivative expressed through input x and output y = act(x) (either may be used)
+__device__ __forceinline__ float act_grad(int act, float x, float y) {
+    switch (act) {
+        case HCGS_ACT_RELU: return x > 0.f ? 1.f : 0.f;
+        case HCGS_ACT_TANH: return 1.f - y * y;
+        case HCGS_ACT_HTANH: return (x > -1.f && x < 1.f) ? 1.f : 0.f;
+        case HCGS_ACT_SIGMOID: return y * (1.f - y);
+        case HCGS_ACT_LEAKY_RELU: return x > 0.f ? 1.f : 0.2f;
+        case HCGS_ACT_ELU: return x > 0.f ? 1.f : y + 1.f;
+        default: return 1.f;
+    }
+}
+
+// derivative from the output only (what the LSTM/MLP backward has saved)
+__device__ __forceinline__ float act_grad_from_out(int act, float y) {
+    switch (act) {
+        case HCGS_ACT_RELU: return y > 0.f ? 1.f : 0.f;
+        case HCGS_ACT_TANH: return 1.f - y * y;
+        // hardtanh: gradient is 1 strictly inside (-1,1); the saturated outputs are exactly +-1
+        case HCGS_ACT_HTANH: return (y > -1.f && y < 1.f) ? 1.f : 0.f;
+        case HCGS_ACT_SIGMOID: return y * (1.f - y);
+        case HCGS_ACT_LEAKY_RELU: return y > 0.f ? 1.f : 0.2f;
+        case HCGS_ACT_ELU: return y > 0.f ? 1.f : y + 1.f;
+        default: return 1.f;
+    }
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+static inline int ceil_div(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
+
+}  // namespace hcgs

@@ -1,0 +1,711 @@
+"""Drop-in ``arch_library = neural_networks`` for the HCGS hot path (reference: neural_networks.py).
+
+``LSTM`` and ``MLP`` keep the reference plugin surface -- ``Class(options, inp_dim)`` with the
+string-valued cfg section, ``out_dim``, the attributes ``core.run_nn`` pokes (``prune``,
+``guided_hcgs``, ``apply_guided_hcgs``, ``if_pattern``, ``pattern``, ``pattern_mask``,
+``skip_regularization``), the same sub-module names and therefore the same ``state_dict`` keys
+(``wfx.N.weight``, ``hcgsx.N.mask``, ``bn_wfx.N.running_mean`` ...), and the same construction
+order, so seeding torch/numpy identically yields bit-identical initial parameters and masks.
+
+What changes is everything under ``forward``: the arithmetic is hand-written sm_100a CUDA reached
+through the C ABI (``b200/native.py``).  There is no CPU path: calling ``forward`` without the
+native library or without a CUDA device raises.
+
+Deviations from the reference that are deliberate (all documented in DESIGN.md):
+  * cfg keys the reference indexes unconditionally but baseline cfgs lack default to "off";
+    ``hcgs*_drop`` is accepted as a spelling of ``hcgs*_sparse`` (LibriSpeech_CGS cfg).
+  * ``lstm_bidir`` is forced off exactly like the reference does in forward (:835).
+  * the other model classes of the upstream toolkit (GRU, liGRU, CNN, SincNet, ...) carry no
+    HCGS/quantisation hook in the reference and are out of scope.
+"""
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+import numpy as np
+
+import guided_hcgs
+import save_cgs_mat
+from HCGS import HCGS as HCGS
+from HCGS import guidedHCGS as guidedHCGS
+from quantized_modules import QuantizeLinear, Quantize, Quantize_inp, prune
+from b200 import native
+from b200.functions import LayerRuntime, LSTMLayerFunction, MLPLayerFunction
+
+
+def strtobool(val):
+    """distutils.util.strtobool (removed from the stdlib in 3.12)."""
+    val = str(val).lower()
+    if val in ('y', 'yes', 't', 'true', 'on', '1'):
+        return 1
+    if val in ('n', 'no', 'f', 'false', 'off', '0'):
+        return 0
+    raise ValueError('invalid truth value %r' % (val,))
+
+
+def _opt(options, key, default, *aliases):
+    for k in (key,) + aliases:
+        if k in options:
+            return options[k]
+    return default
+
+
+def hsigmoid(x):
+    """Hard sigmoid (neural_networks.py:29-37); the reference never reaches it (:1080)."""
+    x = (0.2 * x) + 0.5
+    x = F.threshold(-x, -1, -1)
+    x = F.threshold(-x, 0, 0)
+    return x
+
+
+class LayerNorm(nn.Module):
+    """Reference LayerNorm (neural_networks.py:40-51): unbiased std, divide by (std + eps)."""
+
+    def __init__(self, features, eps=1e-6):
+        super(LayerNorm, self).__init__()
+        self.gamma = nn.Parameter(torch.ones(features))
+        self.beta = nn.Parameter(torch.zeros(features))
+        self.eps = eps
+
+    def forward(self, x):
+        raise NotImplementedError('layer normalisation is not built into the B200 hot path yet '
+                                  '(no shipped CGS cfg enables *_use_laynorm)')
+
+
+def act_fun(act_type):
+    """Same module objects as the reference (neural_networks.py:54-78); they only carry the name."""
+    table = {'relu': nn.ReLU, 'tanh': nn.Tanh, 'htanh': nn.Hardtanh, 'sigmoid': nn.Sigmoid, 'elu': nn.ELU}
+    if act_type in table:
+        return table[act_type]()
+    if act_type == 'leaky_relu':
+        return nn.LeakyReLU(0.2)
+    if act_type == 'softmax':
+        return nn.LogSoftmax(dim=1)
+    if act_type == 'linear':
+        return nn.LeakyReLU(1)
+
+
+def _parse_pattern_options(self, options, prefix):
+    """if_pattern & friends (neural_networks.py:115-131, 513-529); also accepts the
+    ``lstm_pattern`` / ``mlp_pattern`` spelling used by the shipped pattern cfgs."""
+    flag = _opt(options, 'if_pattern', None, prefix + '_pattern')
+    if flag is not None:
+        self.if_pattern = strtobool(flag)
+        self.pattern_mode = _opt(options, 'pattern_mode', 'pattern')
+        self.pattern_shape = list(map(int, _opt(options, 'pattern_shape', '8,8').split(',')))
+        self.pattern_nnz = list(map(int, _opt(options, 'pattern_nnz', '4').split(',')))
+        self.pattern_num = list(map(int, _opt(options, 'pattern_num', '16').split(',')))
+    else:
+        self.if_pattern = False
+    self.pattern_from_file = options['pattern_from_file'] if 'pattern_from_file' in options else False
+
+
+class _PlanCache:
+    """key -> native.Plan, rebuilt when the signature of the source masks changes."""
+
+    def __init__(self):
+        self._store = {}
+
+    def get(self, key, sources, build_mask, shape, recurrent):
+        """sources: the mask tensors the structural mask is derived from (may be empty = dense);
+        build_mask(): returns the structural 0/1 mask (only called on a miss)."""
+        sig = tuple((m.data_ptr(), m._version, tuple(m.shape)) for m in sources)
+        hit = self._store.get(key)
+        if hit is not None and hit[0] == sig:
+            return hit[1], hit[2]
+        if hit is not None:
+            hit[1].destroy()
+        mask = build_mask() if sources else None
+        plan = native.Plan(mask if mask is not None else torch.ones(shape), recurrent=recurrent)
+        if mask is not None:
+            mask = mask.detach().to(device=sources[0].device, dtype=torch.float32).contiguous()
+        self._store[key] = (sig, plan, mask)
+        return plan, mask
+
+
+def _structural_mask(per_gate_factor_lists):
+    """Each gate's effective mask is the product of its factors (HCGS * guided * pattern != 0);
+    gates sharing one plan use the union over gates.  Returns a 0/1 float tensor."""
+    out = None
+    for factors in per_gate_factor_lists:
+        eff = None
+        for m in factors:
+            nz = (m.detach() != 0)
+            eff = nz if eff is None else (eff & nz)
+        out = eff if out is None else (out | eff)
+    return out.float()
+
+
+def _bump_bn_counter(bn):
+    if bn.training and bn.num_batches_tracked is not None:
+        bn.num_batches_tracked += 1
+
+
+class MLP(nn.Module):
+    """Feed-forward stack incl. the output layer + LogSoftmax (reference: neural_networks.py:81-361)."""
+
+    def __init__(self, options, inp_dim):
+        super(MLP, self).__init__()
+        self.input_dim = inp_dim
+        self.dnn_lay = list(map(int, options['dnn_lay'].split(',')))
+        self.dnn_drop = list(map(float, options['dnn_drop'].split(',')))
+        self.dnn_use_batchnorm = list(map(strtobool, options['dnn_use_batchnorm'].split(',')))
+        self.dnn_use_laynorm = list(map(strtobool, options['dnn_use_laynorm'].split(',')))
+        self.dnn_use_laynorm_inp = strtobool(options['dnn_use_laynorm_inp'])
+        self.dnn_use_batchnorm_inp = strtobool(options['dnn_use_batchnorm_inp'])
+        self.dnn_act = options['dnn_act'].split(',')
+        self.to_do = _opt(options, 'to_do', 'train')
+
+        self.mlp_hcgs = strtobool(_opt(options, 'mlp_hcgs', 'False'))
+        self.hcgs_block = list(map(int, _opt(options, 'hcgs_block', '64,4').split(',')))
+        self.hcgs_sparse = list(map(float, _opt(options, 'hcgs_sparse', '50,25', 'hcgs_drop').split(',')))
+        self.param_sav = _opt(options, 'out_folder', '.')
+
+        self.mlp_quant = strtobool(_opt(options, 'mlp_quant', 'False'))
+        self.param_quant = list(map(int, _opt(options, 'param_quant', '8').split(',')))
+        self.mlp_quant_inp = strtobool(_opt(options, 'mlp_quant_inp', 'False'))
+        self.inp_quant = list(map(int, _opt(options, 'inp_quant', '16').split(',')))
+        self.prune = strtobool(_opt(options, 'mlp_prune', 'False'))
+        self.prune_perc = list(map(float, _opt(options, 'mlp_prune_perc', '0').split(',')))
+        self.skip_regularization = strtobool(_opt(options, 'skip_regularization', 'True'))
+
+        self.guided_hcgs = strtobool(_opt(options, 'guided_hcgs', 'False'))
+        self.apply_guided_hcgs = strtobool(_opt(options, 'apply_guided_hcgs', 'False'))
+        _parse_pattern_options(self, options, 'mlp')
+        self.arch_name = _opt(options, 'arch_name', 'MLP')
+
+        self.test_flag = self.to_do != 'train'
+        first_eval = self.to_do in ('forward', 'valid')
+        self.save_mat = first_eval
+        self.final_quant = first_eval
+        self.final_cgs = first_eval
+
+        if self.mlp_hcgs:
+            self.hcgs = nn.ModuleList([])
+        if self.guided_hcgs:
+            self.ghcgs = nn.ModuleList([])
+        if self.if_pattern:
+            self.pattern = []
+            self.pattern_mask = []
+        if self.prune:
+            self.mask_wx = []
+
+        self.wx = nn.ModuleList([])
+        self.bn = nn.ModuleList([])
+        self.ln = nn.ModuleList([])
+        self.act = nn.ModuleList([])
+        self.drop = nn.ModuleList([])
+
+        if self.dnn_use_laynorm_inp:
+            self.ln0 = LayerNorm(self.input_dim)
+        if self.dnn_use_batchnorm_inp:
+            self.bn0 = nn.BatchNorm1d(self.input_dim, momentum=0.05)
+
+        self.N_dnn_lay = len(self.dnn_lay)
+        current_input = self.input_dim
+        # construction order == reference (:187-241) so that the torch RNG stream lines up
+        for i in range(self.N_dnn_lay):
+            self.drop.append(nn.Dropout(p=self.dnn_drop[i]))
+            self.act.append(act_fun(self.dnn_act[i]))
+            if self.prune:
+                self.mask_wx.append(torch.ones(current_input, self.dnn_lay[i]))
+            add_bias = True
+            self.ln.append(LayerNorm(self.dnn_lay[i]))
+            self.bn.append(nn.BatchNorm1d(self.dnn_lay[i], momentum=0.05))
+            if self.dnn_use_laynorm[i] or self.dnn_use_batchnorm[i]:
+                add_bias = False
+            if self.mlp_quant:
+                if self.mlp_quant_inp:
+                    self.wx.append(QuantizeLinear(current_input, self.dnn_lay[i], self.param_quant[i], bias=add_bias,
+                                                  if_forward=self.final_quant, if_inp_quant=True,
+                                                  inp_quant=self.inp_quant[0]))
+                else:
+                    self.wx.append(QuantizeLinear(current_input, self.dnn_lay[i], self.param_quant[i], bias=add_bias,
+                                                  if_forward=self.final_quant))
+            else:
+                self.wx.append(nn.Linear(current_input, self.dnn_lay[i], bias=add_bias))
+            if self.mlp_hcgs:
+                self.hcgs.append(HCGS(current_input, self.dnn_lay[i], self.hcgs_block, self.hcgs_sparse,
+                                      str(i) + '_' + self.arch_name))
+            # the reference re-initialises every weight and forces a zero bias (:233-235)
+            lim = np.sqrt(0.01 / (current_input + self.dnn_lay[i]))
+            self.wx[i].weight = torch.nn.Parameter(torch.Tensor(self.dnn_lay[i], current_input).uniform_(-lim, lim))
+            self.wx[i].bias = torch.nn.Parameter(torch.zeros(self.dnn_lay[i]))
+            if self.guided_hcgs:
+                self.ghcgs.append(guidedHCGS(current_input, self.dnn_lay[i], self.hcgs_block, self.hcgs_sparse,
+                                             self.wx[i].weight.data, str(i) + '_wx_' + self.arch_name))
+            current_input = self.dnn_lay[i]
+        self.out_dim = current_input
+        self._plans = _PlanCache()
+        self.log_prior = None   # set by the export path to fuse `- log(counts/sum)` (core.py:244-245)
+
+    # -- mask bookkeeping ------------------------------------------------------------------------
+    def _mask_factors(self, i):
+        f = []
+        if self.mlp_hcgs:
+            f.append(self.hcgs[i].mask.data)
+        if self.guided_hcgs and self.apply_guided_hcgs:
+            f.append(self.ghcgs[i].mask.data)
+        if self.if_pattern and len(self.pattern_mask) > i:
+            f.append(self.pattern_mask[i].data)
+        return f
+
+    def _apply_masks(self, i):
+        w = self.wx[i].weight.data
+        if self.mlp_hcgs:
+            native.mask_apply([w], self.hcgs[i].mask.data)
+        if self.guided_hcgs and self.apply_guided_hcgs:
+            native.mask_apply([w], self.ghcgs[i].mask.data)
+        if self.if_pattern:
+            if self.pattern == []:
+                self.update_patterns()
+            if self.pattern_mask == []:
+                self.update_mask()
+            self.update_weight()
+        if self.prune:
+            self.mask_wx[i] = prune(self.wx[i], self.prune_perc[i])
+            native.mask_apply([w], self.mask_wx[i][0].data)
+
+    def _side_effects(self, i):
+        """First valid/forward call: dump weights + masks, then quantise in place (:280-304)."""
+        if self.save_mat:
+            save_cgs_mat.save_mat(self.wx[i].weight.data, str(i) + '_w_' + self.arch_name, self.param_sav)
+            if self.mlp_hcgs:
+                save_cgs_mat.save_hcgs_mat(self.hcgs[i].mask.data, str(i) + '_' + self.arch_name, self.param_sav)
+            if self.guided_hcgs and self.apply_guided_hcgs:
+                save_cgs_mat.save_hcgs_mat(self.ghcgs[i].mask.data, str(i) + '_' + self.arch_name, self.param_sav)
+            if self.if_pattern:
+                save_cgs_mat.save_hcgs_mat(self.pattern_mask[i].data, str(i) + '_' + self.arch_name, self.param_sav)
+            if self.prune:
+                save_cgs_mat.save_hcgs_mat(self.mask_wx[i][0].data, str(i) + '_' + self.arch_name, self.param_sav)
+            if i == (self.N_dnn_lay - 1):
+                self.save_mat = False
+        if self.final_quant and self.mlp_quant:
+            wx_data = Quantize(self.wx[i].weight.data, numBits=self.param_quant[i], if_forward=self.final_quant)
+            save_cgs_mat.save_mat(wx_data, str(i) + '_w_q_' + self.arch_name, self.param_sav)
+            if i == (self.N_dnn_lay - 1):
+                self.final_quant = False
+
+    def forward(self, x):
+        if bool(self.dnn_use_laynorm_inp):
+            x = self.ln0(x)
+        if bool(self.dnn_use_batchnorm_inp):
+            raise NotImplementedError('dnn_use_batchnorm_inp is not built into the B200 hot path yet')
+        if x.dim() != 2:
+            raise native.NativeError('MLP expects [N, in] input, got %s' % (tuple(x.shape),))
+        for i in range(self.N_dnn_lay):
+            with torch.no_grad():
+                self._apply_masks(i)
+                self._side_effects(i)
+            if self.dnn_use_laynorm[i]:
+                self.ln[i](x)  # raises: not built
+            lin = self.wx[i]
+            rt = LayerRuntime()
+            factors = self._mask_factors(i)
+            rt.plan_x, rt.mask_x = self._plans.get(
+                i, factors, lambda f=factors: _structural_mask([f]), (self.dnn_lay[i], lin.weight.shape[1]), False)
+            rt.use_bn = bool(self.dnn_use_batchnorm[i])
+            bn = self.bn[i]
+            rt.training = bn.training
+            rt.bn_running = [(bn.running_mean, bn.running_var)]
+            rt.bn_eps, rt.bn_momentum = bn.eps, bn.momentum
+            rt.softmax = self.dnn_act[i] == 'softmax'
+            if not rt.softmax:
+                rt.act = native.ACT_CODES[self.dnn_act[i]]
+            if rt.softmax and i == self.N_dnn_lay - 1:
+                rt.log_prior = self.log_prior
+            p = self.dnn_drop[i]
+            if self.drop[i].training and p > 0:
+                # same generator stream as nn.Dropout on a tensor of this size
+                rt.mlp_drop_mask = F.dropout(torch.ones(x.shape[0], self.dnn_lay[i], device=x.device), p, True)
+            if self.mlp_quant:
+                with torch.no_grad():
+                    if lin.if_forward:
+                        Quantize(lin.weight.data, numBits=lin.numBits, if_forward=True, balanced=False)
+                    else:
+                        rt.q_ws = [Quantize(lin.weight.data, numBits=lin.numBits, balanced=False)]
+                    if lin.if_inp_quant:
+                        x.data = Quantize_inp(x.data, lin.inp_quant, lin.if_forward)
+            if rt.use_bn and not rt.training and torch.is_grad_enabled() and lin.weight.requires_grad:
+                raise NotImplementedError('backward through eval-mode batch norm (arch_freeze) is not built yet')
+            gamma = bn.weight if rt.use_bn else None
+            beta = bn.bias if rt.use_bn else None
+            x = MLPLayerFunction.apply(x, lin.weight, lin.bias, gamma, beta, rt)
+            if rt.use_bn:
+                _bump_bn_counter(bn)
+        return x
+
+    def prune_parameters(self):
+        with torch.no_grad():
+            for i in range(self.N_dnn_lay):
+                self.mask_wx[i] = prune(self.wx[i], self.prune_perc[0])
+                native.mask_apply([self.wx[i].weight.data], self.mask_wx[i][0].data)
+        return 1
+
+    def apply_ghcgs(self):
+        current_input = self.input_dim
+        for i in range(self.N_dnn_lay):
+            self.ghcgs[i].mask.data = guided_hcgs.conn_mat(
+                self.dnn_lay[i], current_input, self.hcgs_block[:], self.hcgs_sparse[:], self.wx[i].weight.data,
+                str(i) + '_wx_' + self.arch_name)
+            current_input = self.dnn_lay[i]
+        return 20.0
+
+    def update_patterns(self):
+        import Pattern
+        for i in range(self.N_dnn_lay):
+            k = Pattern.find_top_k_by_kmeans(self.wx[i].weight, self.pattern_num[i], self.pattern_shape,
+                                             self.pattern_nnz[i], self.pattern_shape)
+            if len(self.pattern) < i + 1:
+                self.pattern.append(k)
+            else:
+                self.pattern[i] = k
+        return 1
+
+    def update_mask(self):
+        import Pattern
+        for i in range(self.N_dnn_lay):
+            m = Pattern.apply_patterns(self.wx[i].weight, self.pattern[i])
+            if len(self.pattern_mask) < i + 1:
+                self.pattern_mask.append(m)
+            else:
+                self.pattern_mask[i] = m
+        return 1
+
+    def update_weight(self):
+        with torch.no_grad():
+            for i in range(self.N_dnn_lay):
+                native.mask_apply([self.wx[i].weight.data], self.pattern_mask[i].data.contiguous())
+        return 1
+
+
+_GATES = ('f', 'i', 'o', 'c')
+
+
+class LSTM(nn.Module):
+    """Unidirectional multi-layer HCGS LSTM (reference: neural_networks.py:468-1237)."""
+
+    def __init__(self, options, inp_dim):
+        super(LSTM, self).__init__()
+        self.input_dim = inp_dim
+        self.lstm_lay = list(map(int, options['lstm_lay'].split(',')))
+        self.lstm_drop = list(map(float, options['lstm_drop'].split(',')))
+        self.lstm_use_batchnorm = list(map(strtobool, options['lstm_use_batchnorm'].split(',')))
+        self.lstm_use_laynorm = list(map(strtobool, options['lstm_use_laynorm'].split(',')))
+        self.lstm_use_laynorm_inp = strtobool(options['lstm_use_laynorm_inp'])
+        self.lstm_use_batchnorm_inp = strtobool(options['lstm_use_batchnorm_inp'])
+        self.lstm_act = options['lstm_act'].split(',')
+        self.lstm_orthinit = strtobool(options['lstm_orthinit'])
+        self.bidir = strtobool(options['lstm_bidir'])
+        self.use_cuda = strtobool(_opt(options, 'use_cuda', 'True'))
+        self.to_do = _opt(options, 'to_do', 'train')
+
+        self.lstm_hcgs = strtobool(_opt(options, 'lstm_hcgs', 'False'))
+        self.hcgsx_block = list(map(int, _opt(options, 'hcgsx_block', '32,4').split(',')))
+        self.hcgsh_block = list(map(int, _opt(options, 'hcgsh_block', '32,4').split(',')))
+        self.hcgsx_sparse = list(map(float, _opt(options, 'hcgsx_sparse', '75,62.5', 'hcgsx_drop').split(',')))
+        self.hcgsh_sparse = list(map(float, _opt(options, 'hcgsh_sparse', '75,62.5', 'hcgsh_drop').split(',')))
+        self.param_sav = _opt(options, 'out_folder', '.')
+
+        self.lstm_quant = strtobool(_opt(options, 'lstm_quant', 'False'))
+        self.param_quant = list(map(int, _opt(options, 'param_quant', '8').split(',')))
+        self.lstm_quant_inp = strtobool(_opt(options, 'lstm_quant_inp', 'False'))
+        self.inp_quant = list(map(int, _opt(options, 'inp_quant', '16').split(',')))
+        self.prune = strtobool(_opt(options, 'lstm_prune', 'False'))
+        self.prune_perc = list(map(float, _opt(options, 'lstm_prune_perc', '0').split(',')))
+        self.skip_regularization = strtobool(_opt(options, 'skip_regularization', 'True'))
+        self.guided_hcgs = strtobool(_opt(options, 'guided_hcgs', 'False'))
+        self.apply_guided_hcgs = strtobool(_opt(options, 'apply_guided_hcgs', 'False'))
+        self.if_hsigmoid = strtobool(_opt(options, 'if_hsigmoid', 'False'))
+        _parse_pattern_options(self, options, 'lstm')
+        self.arch_name = _opt(options, 'arch_name', 'LSTM')
+
+        self.test_flag = self.to_do != 'train'
+        first_eval = self.to_do in ('forward', 'valid')
+        self.save_mat = first_eval
+        self.final_quant = first_eval
+        self.final_cgs = first_eval
+
+        if self.lstm_hcgs:
+            self.hcgsx = nn.ModuleList([])
+            self.hcgsh = nn.ModuleList([])
+        if self.guided_hcgs:
+            for n in ('wfx', 'ufh', 'wix', 'uih', 'wox', 'uoh', 'wcx', 'uch'):
+                setattr(self, 'ghcgs_' + n, nn.ModuleList([]))
+        if self.if_pattern:
+            names = ('wfx', 'wix', 'wox', 'wcx', 'ufh', 'uih', 'uoh', 'uch')
+            self.pattern = {'pattern_' + n: [] for n in names}
+            self.pattern_mask = {'pattern_mask_' + n: [] for n in names}
+        if self.prune:
+            for n in ('wfx', 'ufh', 'wix', 'uih', 'wox', 'uoh', 'wcx', 'uch'):
+                setattr(self, 'mask_' + n, [])
+
+        # registration order == reference (:606-624) so that state_dict key order matches
+        for n in ('wfx', 'ufh', 'wix', 'uih', 'wox', 'uoh', 'wcx', 'uch'):
+            setattr(self, n, nn.ModuleList([]))
+        self.ln = nn.ModuleList([])
+        for n in ('bn_wfx', 'bn_wix', 'bn_wox', 'bn_wcx'):
+            setattr(self, n, nn.ModuleList([]))
+        self.act = nn.ModuleList([])
+
+        if self.lstm_use_laynorm_inp:
+            self.ln0 = LayerNorm(self.input_dim)
+        if self.lstm_use_batchnorm_inp:
+            self.bn0 = nn.BatchNorm1d(self.input_dim, momentum=0.05)
+
+        self.N_lstm_lay = len(self.lstm_lay)
+        current_input = self.input_dim
+        for i in range(self.N_lstm_lay):
+            H = self.lstm_lay[i]
+            self.act.append(act_fun(self.lstm_act[i]))
+            if self.prune:
+                for n in ('wfx', 'ufh', 'wix', 'uih', 'wox', 'uoh', 'wcx', 'uch'):
+                    getattr(self, 'mask_' + n).append(torch.ones(current_input, H))
+            if not (self.lstm_use_laynorm[i] or self.lstm_use_batchnorm[i]):
+                # the reference only creates the linears inside this branch (:681-791) and then
+                # crashes on the missing modules; fail with a readable message instead
+                raise ValueError('LSTM layer %d needs lstm_use_batchnorm or lstm_use_laynorm (reference '
+                                 'neural_networks.py:681 builds no weights otherwise)' % i)
+            add_bias = False
+
+            def make(n_in, n_out, bias):
+                if self.lstm_quant:
+                    if self.lstm_quant_inp:
+                        return QuantizeLinear(n_in, n_out, self.param_quant[i], bias=bias, if_forward=self.final_quant,
+                                              if_inp_quant=True, inp_quant=self.inp_quant[0])
+                    return QuantizeLinear(n_in, n_out, self.param_quant[i], bias=bias, if_forward=self.final_quant)
+                return nn.Linear(n_in, n_out, bias=bias)
+
+            # feed-forward connections (torch RNG order: wfx, wix, wox, wcx)
+            for n in ('wfx', 'wix', 'wox', 'wcx'):
+                getattr(self, n).append(make(current_input, H, add_bias))
+            if self.lstm_hcgs:
+                self.hcgsx.append(HCGS(current_input, H, self.hcgsx_block, self.hcgsx_sparse,
+                                       str(i) + '_x_' + self.arch_name))
+            if self.guided_hcgs:
+                for n in ('wfx', 'wix', 'wox', 'wcx'):
+                    getattr(self, 'ghcgs_' + n).append(guidedHCGS(
+                        current_input, H, self.hcgsx_block, self.hcgsx_sparse, getattr(self, n)[i].weight.data,
+                        str(i) + '_' + n + '_' + self.arch_name))
+            # recurrent connections (ufh, uih, uoh, uch)
+            for n in ('ufh', 'uih', 'uoh', 'uch'):
+                getattr(self, n).append(make(H, H, False))
+            if self.lstm_hcgs:
+                self.hcgsh.append(HCGS(H, H, self.hcgsh_block, self.hcgsh_sparse, str(i) + '_h_' + self.arch_name))
+            if self.lstm_orthinit:
+                for n in ('ufh', 'uih', 'uoh', 'uch'):
+                    nn.init.orthogonal_(getattr(self, n)[i].weight)
+            if self.guided_hcgs:
+                for n in ('ufh', 'uih', 'uoh', 'uch'):
+                    getattr(self, 'ghcgs_' + n).append(guidedHCGS(
+                        H, H, self.hcgsh_block, self.hcgsh_sparse, getattr(self, n)[i].weight.data,
+                        str(i) + '_' + n + '_' + self.arch_name))
+            for n in ('bn_wfx', 'bn_wix', 'bn_wox', 'bn_wcx'):
+                getattr(self, n).append(nn.BatchNorm1d(H, momentum=0.05))
+            self.ln.append(LayerNorm(H))
+            current_input = 2 * H if self.bidir else H
+        self.out_dim = self.lstm_lay[-1] + self.bidir * self.lstm_lay[-1]
+        self._plans = _PlanCache()
+
+    # -- helpers ---------------------------------------------------------------------------------
+    def _lin(self, kind, gate, i):
+        """kind 'w' -> w{gate}x[i], kind 'u' -> u{gate}h[i]"""
+        return getattr(self, ('w%sx' if kind == 'w' else 'u%sh') % gate)[i]
+
+    def _names(self, kind):
+        return ['w%sx' % g for g in _GATES] if kind == 'w' else ['u%sh' % g for g in _GATES]
+
+    def _mask_factor_lists(self, kind, i):
+        """Per gate: the masks multiplied into that gate's matrix (shared HCGS, per-gate guided/pattern)."""
+        lists = []
+        for n in self._names(kind):
+            f = []
+            if self.lstm_hcgs:
+                f.append((self.hcgsx if kind == 'w' else self.hcgsh)[i].mask.data)
+            if self.guided_hcgs and self.apply_guided_hcgs:
+                f.append(getattr(self, 'ghcgs_' + n)[i].mask.data)
+            if self.if_pattern and len(self.pattern_mask['pattern_mask_' + n]) > i:
+                f.append(self.pattern_mask['pattern_mask_' + n][i].data)
+            lists.append(f)
+        return lists
+
+    def _apply_masks(self, kind, i):
+        names = self._names(kind)
+        ws = [getattr(self, n)[i].weight.data for n in names]
+        if self.lstm_hcgs:
+            native.mask_apply(ws, (self.hcgsx if kind == 'w' else self.hcgsh)[i].mask.data)
+        if self.guided_hcgs and self.apply_guided_hcgs:
+            for n, w in zip(names, ws):
+                native.mask_apply([w], getattr(self, 'ghcgs_' + n)[i].mask.data)
+        if self.prune:
+            for n, w in zip(names, ws):
+                m = prune(getattr(self, n)[i], self.prune_perc[i])
+                getattr(self, 'mask_' + n)[i] = m
+                native.mask_apply([w], m[0].data)
+
+    def _side_effects(self, kind, i):
+        """First valid/forward call: dump matrices and masks (:898-948, 1007-1061)."""
+        names = self._names(kind)
+        tag = 'x' if kind == 'w' else 'h'
+        if self.save_mat:
+            for n in names:
+                save_cgs_mat.save_mat(getattr(self, n)[i].weight.data, str(i) + '_' + n + '_' + self.arch_name,
+                                      self.param_sav)
+            if self.lstm_hcgs:
+                save_cgs_mat.save_hcgs_mat((self.hcgsx if kind == 'w' else self.hcgsh)[i].mask.data,
+                                           str(i) + '_' + tag + '_' + self.arch_name, self.param_sav)
+            if self.guided_hcgs and self.apply_guided_hcgs:
+                for n in names:
+                    save_cgs_mat.save_hcgs_mat(getattr(self, 'ghcgs_' + n)[i].mask.data,
+                                               str(i) + '_' + n + '_' + self.arch_name, self.param_sav)
+            if self.prune:
+                for n in names:
+                    save_cgs_mat.save_hcgs_mat(getattr(self, 'mask_' + n)[i][0].data,
+                                               str(i) + '_' + n + '_' + self.arch_name, self.param_sav)
+            if kind == 'u' and i == (self.N_lstm_lay - 1):
+                self.save_mat = False
+        if self.final_quant and self.lstm_quant:
+            for n in names:
+                q = Quantize(getattr(self, n)[i].weight.data, numBits=self.param_quant[i], if_forward=self.final_quant)
+                save_cgs_mat.save_mat(q, str(i) + '_' + n + '_q_' + self.arch_name, self.param_sav)
+            if kind == 'u' and i == (self.N_lstm_lay - 1):
+                self.final_quant = False
+
+    def _quant_weights(self, kind, i):
+        """QuantizeLinear weight handling: eval quantises in place, train returns compute copies."""
+        lins = [getattr(self, n)[i] for n in self._names(kind)]
+        if lins[0].if_forward:
+            for l in lins:
+                Quantize(l.weight.data, numBits=l.numBits, if_forward=True, balanced=False)
+            return None
+        return [Quantize(l.weight.data, numBits=l.numBits, balanced=False) for l in lins]
+
+    def forward(self, x):
+        if bool(self.lstm_use_laynorm_inp):
+            x = self.ln0(x)
+        if bool(self.lstm_use_batchnorm_inp):
+            raise NotImplementedError('lstm_use_batchnorm_inp is not built into the B200 hot path yet')
+        if x.dim() != 3:
+            raise native.NativeError('LSTM expects [T, B, in] input, got %s' % (tuple(x.shape),))
+        for i in range(self.N_lstm_lay):
+            self.bidir = 0           # as the reference (:835)
+            self.if_hsigmoid = 0     # as the reference (:1080)
+            H = self.lstm_lay[i]
+            T, B, D = x.shape
+            if self.lstm_use_laynorm[i]:
+                self.ln[i](x)  # raises: not built
+            rt = LayerRuntime()
+            # drop mask: same for all time steps, NOT rescaled; drawn on the CPU generator (:843-851)
+            if self.test_flag == False:  # noqa: E712 (reference spelling)
+                drop_mask = torch.bernoulli(torch.Tensor(B, H).fill_(1 - self.lstm_drop[i]))
+                rt.drop = drop_mask.to(x.device)
+                rt.drop_scalar = 1.0
+            else:
+                rt.drop = None
+                rt.drop_scalar = 1 - self.lstm_drop[i]
+            with torch.no_grad():
+                if self.if_pattern:
+                    if self.pattern['pattern_wfx'] == []:
+                        self.update_patterns()
+                    if self.pattern_mask['pattern_mask_wfx'] == []:
+                        self.update_mask()
+                self._apply_masks('w', i)
+                if self.if_pattern:
+                    self.update_weight()
+                self._side_effects('w', i)
+                self._apply_masks('u', i)
+                self._side_effects('u', i)
+            fx = self._mask_factor_lists('w', i)
+            fh = self._mask_factor_lists('u', i)
+            src_x = [m for f in fx for m in f]
+            src_h = [m for f in fh for m in f]
+            rt.plan_x, rt.mask_x = self._plans.get(('x', i), src_x, lambda: _structural_mask(fx), (H, D), False)
+            rt.plan_h, rt.mask_h = self._plans.get(('h', i), src_h, lambda: _structural_mask(fh), (H, H), True)
+            rt.use_bn = bool(self.lstm_use_batchnorm[i])
+            bns = [self.bn_wfx[i], self.bn_wix[i], self.bn_wox[i], self.bn_wcx[i]]
+            rt.training = bns[0].training
+            rt.bn_running = [(b.running_mean, b.running_var) for b in bns]
+            rt.bn_eps, rt.bn_momentum = bns[0].eps, bns[0].momentum
+            rt.act = native.ACT_CODES[self.lstm_act[i]]
+            if self.lstm_quant:
+                with torch.no_grad():
+                    rt.q_ws = self._quant_weights('w', i)
+                    rt.q_us = self._quant_weights('u', i)
+                    if self.lstm_quant_inp:
+                        raise NotImplementedError(
+                            'lstm_quant_inp (per-step Quantize_inp of h_t inside the recurrence) is not built yet')
+            ws = [self.wfx[i].weight, self.wix[i].weight, self.wox[i].weight, self.wcx[i].weight]
+            us = [self.ufh[i].weight, self.uih[i].weight, self.uoh[i].weight, self.uch[i].weight]
+            if rt.use_bn and not rt.training and torch.is_grad_enabled() and ws[0].requires_grad:
+                raise NotImplementedError('backward through eval-mode batch norm (arch_freeze) is not built yet')
+            if rt.use_bn:
+                gb = []
+                for b in bns:
+                    gb += [b.weight, b.bias]
+            else:
+                gb = [None] * 8
+            x = LSTMLayerFunction.apply(x, *ws, *us, *gb, rt)
+            if rt.use_bn:
+                for b in bns:
+                    _bump_bn_counter(b)
+        return x
+
+    def prune_parameters(self):
+        with torch.no_grad():
+            for i in range(self.N_lstm_lay):
+                for n in ('wfx', 'wix', 'wox', 'wcx', 'ufh', 'uih', 'uoh', 'uch'):
+                    m = prune(getattr(self, n)[i], self.prune_perc[0])
+                    getattr(self, 'mask_' + n)[i] = m
+                    native.mask_apply([getattr(self, n)[i].weight.data], m[0].data)
+        return 1
+
+    def apply_ghcgs(self):
+        current_input = self.input_dim
+        for i in range(self.N_lstm_lay):
+            H = self.lstm_lay[i]
+            for n in ('wfx', 'wix', 'wox', 'wcx'):
+                getattr(self, 'ghcgs_' + n)[i].mask.data = guided_hcgs.conn_mat(
+                    H, current_input, self.hcgsx_block[:], self.hcgsx_sparse[:], getattr(self, n)[i].weight.data,
+                    str(i) + '_' + n + '_' + self.arch_name)
+            for n in ('ufh', 'uih', 'uoh', 'uch'):
+                getattr(self, 'ghcgs_' + n)[i].mask.data = guided_hcgs.conn_mat(
+                    H, H, self.hcgsh_block[:], self.hcgsh_sparse[:], getattr(self, n)[i].weight.data,
+                    str(i) + '_' + n + '_' + self.arch_name)
+            current_input = 2 * H if self.bidir else H
+
+    def update_patterns(self):
+        import Pattern
+        names = ('wfx', 'wix', 'wox', 'wcx', 'ufh', 'uih', 'uoh', 'uch')
+        for i in range(self.N_lstm_lay):
+            fresh = len(self.pattern['pattern_wfx']) < i + 1
+            for n in names:
+                if not fresh and n == 'wfx':
+                    continue  # the reference's refresh branch skips wfx (:1175-1181)
+                k = Pattern.find_top_k_by_kmeans(getattr(self, n)[i].weight, self.pattern_num[i], self.pattern_shape,
+                                                 self.pattern_nnz[i], self.pattern_shape)
+                if fresh:
+                    self.pattern['pattern_' + n].append(k)
+                else:
+                    self.pattern['pattern_' + n][i] = k
+        return 1
+
+    def update_mask(self):
+        import Pattern
+        names = ('wfx', 'wix', 'wox', 'wcx', 'ufh', 'uih', 'uoh', 'uch')
+        for i in range(self.N_lstm_lay):
+            fresh = len(self.pattern_mask['pattern_mask_wfx']) < i + 1
+            for n in names:
+                m = Pattern.apply_patterns(getattr(self, n)[i].weight, self.pattern['pattern_' + n][i])
+                if fresh:
+                    self.pattern_mask['pattern_mask_' + n].append(m)
+                else:
+                    self.pattern_mask['pattern_mask_' + n][i] = m
+        return 1
+
+    def update_weight(self):
+        names = ('wfx', 'wix', 'wox', 'wcx', 'ufh', 'uih', 'uoh', 'uch')
+        with torch.no_grad():
+            for i in range(self.N_lstm_lay):
+                for n in names:
+                    native.mask_apply([getattr(self, n)[i].weight.data],
+                                      self.pattern_mask['pattern_mask_' + n][i].data.contiguous())
+        return 1

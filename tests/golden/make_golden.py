@@ -1,0 +1,241 @@
+"""Generate the golden fixtures in this directory by RUNNING THE REFERENCE ITSELF.
+
+Run once in the build container (the only place /root/reference exists):
+
+    python tests/golden/make_golden.py
+
+It imports the unmodified reference modules from /root/reference (read-only), applies the four
+harness-side shims listed in SURVEY.md 8(c) (no-op the forced ``.to("cuda")`` of mask creation on a
+GPU-less host; nothing else is touched), drives them through the reference's own
+``utils.model_init`` / ``optimizer_init`` / ``forward_model`` and ``core``-style posterior
+normalisation + ``data_io.write_mat``, and stores small ``.npz`` fixtures.  Nothing under tests/,
+bench.py or __graft_entry__.py reads /root/reference at run time; they read these fixtures.
+"""
+import configparser
+import io
+import os
+import sys
+import tempfile
+import types
+import warnings
+
+import numpy as np
+import torch
+
+warnings.filterwarnings('ignore')
+REF = '/root/reference'
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, REF)
+
+import hcgs  # noqa: E402  (reference)
+
+
+class _TorchProxy(types.ModuleType):
+    """`torch` as seen by the reference's hcgs.py: device("cuda") resolves to the CPU here."""
+
+    def __getattr__(self, k):
+        return getattr(torch, k)
+
+    def device(self, *_a, **_k):
+        return torch.device('cpu')
+
+
+hcgs.torch = _TorchProxy('torch')
+import guided_hcgs  # noqa: E402
+guided_hcgs.torch = _TorchProxy('torch')
+import neural_networks as ref_nn  # noqa: E402
+import utils as ref_utils  # noqa: E402
+import quantized_modules as ref_q  # noqa: E402
+import data_io as ref_io  # noqa: E402
+
+MASK_CASES = [
+    (550, 550, [32, 4], [75, 62.5], 2234), (550, 40, [32, 4], [75, 62.5], 2234),
+    (1944, 550, [64, 4], [50, 25], 2234), (48, 550, [64, 4], [50, 25], 2234),
+    (40, 64, [64, 4], [50, 25], 3), (1024, 1024, [128, 4], [25, 62.5], 7),
+    (512, 440, [32, 2], [75, 75], 2234), (3480, 1024, [64, 4], [50, 25], 1234),
+    (100, 70, [16], [50], 9), (33, 65, [8, 2], [50, 50], 11), (7, 5, [4, 2, 1], [50, 50, 0], 4),
+    (512, 512, [32, 4], [75, 62.5], 2234), (1024, 1024, [32, 4], [75, 62.5], 1234),
+]
+
+
+def gen_masks():
+    d = tempfile.mkdtemp()
+    out = {'cases': np.array([repr(c) for c in MASK_CASES])}
+    for k, (r, c, bs, dr, seed) in enumerate(MASK_CASES):
+        np.random.seed(seed)
+        m = hcgs.conn_mat(r, c, list(bs), list(dr), dir=d, for_test=True)
+        out['bits_%d' % k] = np.packbits(m.astype(np.uint8))
+        out['shape_%d' % k] = np.array(m.shape)
+        out['next_rand_%d' % k] = np.array([np.random.randint(0, 2 ** 31 - 1)])  # RNG stream position
+    # guided masks: deterministic given W
+    torch.manual_seed(5)
+    w = torch.randn(48, 40)
+    g = guided_hcgs.conn_mat(48, 40, [8, 4], [50, 50], w, dir=d, for_test=True)
+    out['guided_w'] = w.numpy()
+    out['guided_bits'] = np.packbits(g.astype(np.uint8))
+    np.savez_compressed(os.path.join(HERE, 'masks.npz'), **out)
+    print('masks.npz', len(MASK_CASES), 'cases')
+
+
+LSTM_OPTS = dict(
+    arch_name='LSTM_layers', arch_proto='proto/LSTM.proto', arch_library='neural_networks', arch_class='LSTM',
+    arch_pretrain_file='none', arch_freeze='False', arch_seq_model='True', lstm_lay='24,24', lstm_drop='0.2,0.2',
+    lstm_use_laynorm_inp='False', lstm_use_batchnorm_inp='False', lstm_use_laynorm='False,False',
+    lstm_use_batchnorm='True,True', lstm_bidir='False', lstm_act='tanh,tanh', if_hsigmoid='True',
+    lstm_orthinit='True', arch_lr='0.0016', arch_halving_factor='0.5', arch_improvement_threshold='0.001',
+    arch_opt='rmsprop', opt_momentum='0.0', opt_alpha='0.95', opt_eps='1e-8', opt_centered='False',
+    opt_weight_decay='0.0', out_folder='', lstm_hcgs='True', guided_hcgs='False', apply_guided_hcgs='False',
+    hcgsx_block='8,4', hcgsx_sparse='50,50', hcgsh_block='8,4', hcgsh_sparse='50,50', lstm_quant='False',
+    param_quant='8,8', lstm_quant_inp='False', inp_quant='16', lstm_prune='False', lstm_prune_perc='70',
+    skip_regularization='True')
+
+MLP_OPTS = dict(
+    arch_name='MLP_layers', arch_proto='proto/MLP.proto', arch_library='neural_networks', arch_class='MLP',
+    arch_pretrain_file='none', arch_freeze='False', arch_seq_model='False', dnn_lay='10', dnn_drop='0.0',
+    dnn_use_laynorm_inp='False', dnn_use_batchnorm_inp='False', dnn_use_batchnorm='False', dnn_use_laynorm='False',
+    dnn_act='softmax', arch_lr='0.0016', arch_halving_factor='0.5', arch_improvement_threshold='0.001',
+    arch_opt='rmsprop', opt_momentum='0.0', opt_alpha='0.95', opt_eps='1e-8', opt_centered='False',
+    opt_weight_decay='0.0', out_folder='', mlp_hcgs='True', guided_hcgs='False', apply_guided_hcgs='False',
+    hcgs_block='8,4', hcgs_sparse='50,25', mlp_quant='False', param_quant='8', mlp_quant_inp='False',
+    inp_quant='16', mlp_prune='False', mlp_prune_perc='70', skip_regularization='True')
+
+MODEL_2HEAD = ['out_dnn1=compute(LSTM_layers,fbank)', 'out_dnn2=compute(MLP_layers,out_dnn1)',
+               'out_dnn3=compute(MLP_layers2,out_dnn1)', 'loss_mono=cost_nll(out_dnn3,lab_mono)',
+               'loss_mono_w=mult_constant(loss_mono,1.0)', 'loss_cd=cost_nll(out_dnn2,lab_cd)',
+               'loss_final=sum(loss_cd,loss_mono_w)', 'err_final=cost_err(out_dnn2,lab_cd)']
+
+
+def build_config(to_do, lstm_over=None, mlp_over=None, out_folder=''):
+    cfg = configparser.ConfigParser()
+    cfg['exp'] = dict(use_cuda='False', to_do=to_do, multi_gpu='False', seed='2234', out_folder=out_folder)
+    a1 = dict(LSTM_OPTS, out_folder=out_folder)
+    a1.update(lstm_over or {})
+    a2 = dict(MLP_OPTS, out_folder=out_folder)
+    a2.update(mlp_over or {})
+    a3 = dict(a2, arch_name='MLP_layers2', dnn_lay='5', mlp_hcgs='False', arch_lr='0.0004')
+    cfg['architecture1'], cfg['architecture2'], cfg['architecture3'] = a1, a2, a3
+    return cfg
+
+
+def run_model(tag, to_do, T=7, B=3, D=12, lstm_over=None, mlp_over=None, steps=1, seed=2234):
+    """One (or a few) reference train steps / one eval forward; returns a dict of arrays."""
+    tmp = tempfile.mkdtemp()
+    cfg = build_config(to_do, lstm_over, mlp_over, out_folder=tmp)
+    torch.manual_seed(seed)
+    np.random.seed(seed)
+    fea_dict = {'fbank': ['scp', 'opts', 0, 0, 0, 0, D, D]}
+    lab_dict = {'lab_cd': ['f', 'o', 'c', D], 'lab_mono': ['f', 'o', 'c', D + 1]}
+    arch_dict = {'LSTM_layers': ['architecture1', 'LSTM_layers', True], 'MLP_layers': ['architecture2', 'MLP_layers', False],
+                 'MLP_layers2': ['architecture3', 'MLP_layers2', False]}
+    inp_out_dict = dict(fea_dict)
+    nns, costs = ref_utils.model_init(inp_out_dict, MODEL_2HEAD, cfg, arch_dict, False, False, to_do)
+    opts = ref_utils.optimizer_init(nns, cfg, arch_dict)
+    out = {}
+    for net in nns:
+        for k, v in nns[net].state_dict().items():
+            out['init/%s/%s' % (net, k)] = v.detach().numpy().copy()
+    gen = torch.Generator().manual_seed(seed + 1)
+    drops = []
+    real_bernoulli = torch.bernoulli
+
+    def rec_bernoulli(p, *a, **k):
+        r = real_bernoulli(p, *a, **k)
+        drops.append(r.clone())
+        return r
+    torch.bernoulli = rec_bernoulli
+    try:
+        for s in range(steps):
+            inp = torch.zeros(T, B, D + 2)
+            inp[:, :, :D] = torch.randn(T, B, D, generator=gen)
+            inp[:, :, D] = torch.randint(0, 10, (T, B), generator=gen).float()
+            inp[:, :, D + 1] = torch.randint(0, 5, (T, B), generator=gen).float()
+            inp[T - 2:, B - 1, :] = 0   # right padding of the shortest sequence, as core.py builds it
+            out['inp/%d' % s] = inp.numpy().copy()
+            if to_do == 'train':
+                o = ref_utils.forward_model(fea_dict, lab_dict, arch_dict, MODEL_2HEAD, nns, costs, inp, inp_out_dict,
+                                            T, B, to_do, ['out_dnn2'])
+                for opt in opts.values():
+                    opt.zero_grad()
+                o['loss_final'].backward()
+                if s == steps - 1:
+                    for net in nns:
+                        for k, p in nns[net].named_parameters():
+                            if p.grad is not None:
+                                out['grad/%s/%s' % (net, k)] = p.grad.numpy().copy()
+                for opt in opts.values():
+                    opt.step()
+                out['loss/%d' % s] = np.array([o['loss_final'].item(), o['err_final'].item(), o['loss_cd'].item(),
+                                               o['loss_mono'].item()], dtype=np.float64)
+                out['out_dnn1/%d' % s] = o['out_dnn1'].detach().numpy().copy()
+                out['out_dnn2/%d' % s] = o['out_dnn2'].detach().numpy().copy()
+            else:
+                with torch.no_grad():
+                    o = ref_utils.forward_model(fea_dict, lab_dict, arch_dict, MODEL_2HEAD, nns, costs, inp,
+                                                inp_out_dict, T, B, to_do, ['out_dnn2'])
+                out['out_dnn1/%d' % s] = o['out_dnn1'].detach().numpy().copy()
+                out['out_dnn2/%d' % s] = o['out_dnn2'].detach().numpy().copy()
+                if to_do == 'valid':
+                    out['loss/%d' % s] = np.array([o['loss_final'].item(), o['err_final'].item()], dtype=np.float64)
+    finally:
+        torch.bernoulli = real_bernoulli
+    for i, d in enumerate(drops):
+        out['drop/%d' % i] = d.numpy().copy()
+    for net in nns:
+        for k, v in nns[net].state_dict().items():
+            out['final/%s/%s' % (net, k)] = v.detach().numpy().copy()
+    out['dims'] = np.array([T, B, D, steps])
+    np.savez_compressed(os.path.join(HERE, tag + '.npz'), **out)
+    print(tag + '.npz', 'loss', out.get('loss/0'))
+    return out, nns
+
+
+def gen_posterior():
+    """Posterior export: eval forward of one utterance (batch 1), prior normalisation in NumPy
+    (core.py:241-249) and the Kaldi ark record bytes (data_io.write_mat)."""
+    res, nns = run_model('eval_forward', 'forward', T=9, B=1, D=12, seed=77)
+    rng = np.random.RandomState(3)
+    counts = (rng.rand(10) * 1000 + 1).astype(np.float32)
+    with tempfile.NamedTemporaryFile('w', suffix='.count', delete=False) as f:
+        f.write('[ ' + ' '.join('%g' % v for v in counts) + ' ]\n')
+        cpath = f.name
+    loaded = ref_io.load_counts(cpath)
+    post = res['out_dnn2/0'] - np.log(loaded / np.sum(loaded))
+    ark = tempfile.NamedTemporaryFile(suffix='.ark', delete=False).name
+    with open(ark, 'wb') as fd:
+        ref_io.write_mat('.', fd, post, 'utt_0001')
+    blob = np.frombuffer(open(ark, 'rb').read(), dtype=np.uint8)
+    np.savez_compressed(os.path.join(HERE, 'posterior.npz'), counts_text=np.array(open(cpath).read()),
+                        counts=loaded, post=post, ark=blob, logp=res['out_dnn2/0'])
+    print('posterior.npz', post.shape, post.dtype, len(blob), 'bytes')
+
+
+def gen_quant():
+    torch.manual_seed(9)
+    w = torch.randn(37, 23) * 0.8
+    x = torch.randn(11, 23) * 3
+    master = w.clone()
+    q = ref_q.Quantize(master, numBits=8, balanced=False)
+    xq = x.clone()
+    for _ in range(4):
+        xq = ref_q.Quantize_inp(xq, 16)
+    x1 = ref_q.Quantize_inp(x.clone(), 16)
+    wf = w.clone()
+    qf = ref_q.Quantize(wf, numBits=8, if_forward=True)          # balanced=True, in place
+    lin = torch.nn.Linear(23, 37)
+    lin.weight.data = w.clone()
+    pm = ref_q.prune(lin, 70)[0]
+    np.savez_compressed(os.path.join(HERE, 'quant.npz'), w=w.numpy(), x=x.numpy(), master=master.numpy(),
+                        q=q.numpy(), xq4=xq.numpy(), xq1=x1.numpy(), qf=qf.numpy(), prune70=pm.numpy())
+    print('quant.npz')
+
+
+if __name__ == '__main__':
+    gen_masks()
+    run_model('train_small', 'train', steps=2)
+    run_model('train_htanh', 'train', T=5, B=9, D=12, lstm_over=dict(lstm_act='htanh,htanh', lstm_lay='20,28',
+                                                                     lstm_drop='0.0,0.1'), steps=1, seed=11)
+    run_model('valid_small', 'valid', steps=1)
+    gen_posterior()
+    gen_quant()
+    run_model('train_quant', 'train', lstm_over=dict(lstm_quant='True', lstm_lay='24,24'),
+              mlp_over=dict(mlp_quant='True'), steps=1, seed=5)
