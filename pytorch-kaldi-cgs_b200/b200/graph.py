@@ -1,0 +1,111 @@
+"""Host-side mirror of the reference's graph interpreter for the hot path
+(utils.model_init :1749-1830, utils.forward_model :1884-2050, utils.optimizer_init :1833-1881).
+
+In a pytorch-kaldi checkout the reference's own ``utils.py``/``core.py`` drive the plugin classes
+unchanged (cfg ``arch_library = neural_networks``).  This module is the same interpreter for use
+*outside* such a checkout (tests, bench.py, export tooling): it understands the ``[model]`` lines
+the CGS cfgs use -- compute, cost_nll, cost_err, sum, mult_constant, sum_constant, mult, avg,
+concatenate, mse -- with the same tensor reshaping rules between sequential and frame-level nets.
+``cost_l1/l2/gl`` need the regularisation helpers of utils.py and are not on the hot path.
+"""
+import re
+
+import torch
+import torch.nn as nn
+import torch.optim as optim
+
+_LINE = re.compile(r'(.*)=(.*)\((.*),(.*)\)')
+
+
+def parse_model(model):
+    lines = [l.strip() for l in (model.split('\n') if isinstance(model, str) else model) if l.strip()]
+    return [tuple(s.strip() for s in _LINE.findall(l)[0]) for l in lines]
+
+
+class Graph:
+    """nets: name -> module; seq: name -> bool (arch_seq_model); fea: name -> (start, end) column
+    range in the minibatch tensor; lab: name -> label column (core.py packs labels as float columns)."""
+
+    def __init__(self, model, nets, seq, fea, lab):
+        self.ops = parse_model(model)
+        self.nets, self.seq, self.fea, self.lab = nets, seq, fea, lab
+        self.nll = nn.NLLLoss()
+
+    def _labels(self, inp, name):
+        col = self.lab[name]
+        lab = inp[:, :, col] if inp.dim() == 3 else inp[:, col]
+        return lab.reshape(-1).long()
+
+    def forward(self, inp, max_len, batch_size, to_do='train', forward_outs=()):
+        outs = {}
+        for f, (a, b) in self.fea.items():
+            outs[f] = inp[:, :, a:b] if inp.dim() == 3 else inp[:, a:b]
+        last = forward_outs[-1] if len(forward_outs) else None
+        for out_name, op, a, b in self.ops:
+            stop = to_do == 'forward' and out_name == last
+            if op == 'compute':
+                x = outs[b]
+                if b in self.fea:
+                    if inp.dim() == 3 and not self.seq[a]:
+                        x = x.reshape(max_len * batch_size, -1)
+                    if inp.dim() == 2 and self.seq[a]:
+                        x = x.view(max_len, batch_size, -1)
+                else:
+                    if not self.seq[a] and x.dim() == 3:
+                        x = outs[b] = x.view(max_len * batch_size, -1)
+                    if self.seq[a] and x.dim() == 2:
+                        x = outs[b] = x.view(max_len, batch_size, -1)
+                outs[out_name] = self.nets[a](x)
+            elif op == 'cost_nll':
+                if to_do != 'forward':
+                    o = outs[a]
+                    if o.dim() == 3:
+                        o = o.view(max_len * batch_size, -1)
+                    outs[out_name] = self.nll(o, self._labels(inp, b))
+            elif op == 'cost_err':
+                if to_do != 'forward':
+                    o = outs[a]
+                    if o.dim() == 3:
+                        o = o.view(max_len * batch_size, -1)
+                    pred = torch.max(o, dim=1)[1]
+                    outs[out_name] = torch.mean((pred != self._labels(inp, b)).float())
+            elif op == 'concatenate':
+                outs[out_name] = torch.cat((outs[a], outs[b]), outs[a].dim() - 1)
+            elif op == 'mult':
+                outs[out_name] = outs[a] * outs[b]
+            elif op == 'sum':
+                outs[out_name] = outs[a] + outs[b]
+            elif op == 'mult_constant':
+                outs[out_name] = outs[a] * float(b)
+            elif op == 'sum_constant':
+                outs[out_name] = outs[a] + float(b)
+            elif op == 'avg':
+                outs[out_name] = (outs[a] + outs[b]) / 2
+            elif op == 'mse':
+                outs[out_name] = torch.mean((outs[a] - outs[b]) ** 2)
+            else:
+                raise NotImplementedError('model operation %r is not on the HCGS hot path' % op)
+            if stop and op != 'cost_nll' and op != 'cost_err':
+                break
+        return outs
+
+
+def make_optimizer(net, opts):
+    """utils.optimizer_init for one net; ``opts`` is the cfg section (string values)."""
+    from neural_networks import strtobool
+    lr = float(opts['arch_lr'])
+    kind = opts['arch_opt']
+    if kind == 'sgd':
+        return optim.SGD(net.parameters(), lr=lr, momentum=float(opts['opt_momentum']),
+                         weight_decay=float(opts['opt_weight_decay']), dampening=float(opts['opt_dampening']),
+                         nesterov=bool(strtobool(opts['opt_nesterov'])))
+    if kind == 'adam':
+        betas = list(map(float, opts['opt_betas'].split(',')))
+        return optim.Adam(net.parameters(), lr=lr, betas=betas, eps=float(opts['opt_eps']),
+                          weight_decay=float(opts['opt_weight_decay']), amsgrad=bool(strtobool(opts['opt_amsgrad'])))
+    if kind == 'rmsprop':
+        return optim.RMSprop(net.parameters(), lr=lr, momentum=float(opts['opt_momentum']),
+                             alpha=float(opts['opt_alpha']), eps=float(opts['opt_eps']),
+                             centered=bool(strtobool(opts['opt_centered'])),
+                             weight_decay=float(opts['opt_weight_decay']))
+    raise ValueError('unknown arch_opt %r' % kind)

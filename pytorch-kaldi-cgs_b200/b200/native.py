@@ -79,7 +79,24 @@ def load():
     return lib
 
 
+# kernels launched by each entry point (our own kernels only; memsets are not counted)
+KERNELS_PER_CALL = {'hcgs_mask_apply': 1, 'hcgs_quantize_w': 1, 'hcgs_quantize_act': 2, 'hcgs_bsgemm_nt': 1,
+                    'hcgs_bsgemm_nn': 1, 'hcgs_bs_sddmm': 1, 'hcgs_colsum': 1, 'hcgs_bn_fwd': 3, 'hcgs_bn_bwd': 2,
+                    'hcgs_lstm_pack': 2, 'hcgs_lstm_fwd': 1, 'hcgs_lstm_bwd': 1, 'hcgs_act_fwd': 1, 'hcgs_act_bwd': 1,
+                    'hcgs_logsoftmax_fwd': 1, 'hcgs_logsoftmax_bwd': 1, 'hcgs_nll_fwd_bwd': 1, 'hcgs_opt_step': 1}
+LAUNCHES = {'total': 0}
+
+
+def reset_launch_count():
+    LAUNCHES.clear()
+    LAUNCHES['total'] = 0
+
+
 def _check(rc, what):
+    n = KERNELS_PER_CALL.get(what, 0)
+    if n:
+        LAUNCHES['total'] += n
+        LAUNCHES[what] = LAUNCHES.get(what, 0) + n
     if rc != 0:
         msg = load().hcgs_last_error()
         raise NativeError('%s failed (%d): %s' % (what, rc, msg.decode() if msg else '?'))

@@ -1,0 +1,270 @@
+"""Model-level parity on the B200: the plugin classes (through the C ABI) against
+ (a) tensors dumped from the reference itself (tests/golden/*.npz) and
+ (b) the CPU oracle on seeded inputs at the cfg shapes (4x550 HCGS LSTM, 1944 pdfs).
+
+Tolerances (north_star): fp32 path rel <= 1e-5 on loss and posteriors; gradients are compared
+with rel 1e-4 of the tensor's max magnitude (their fp32 summation order differs over T*B rows)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from helpers import (NETS, build_product_nets, golden_state, load_golden, make_graph)  # noqa: E402
+from oracle import hcgs_oracle, model_oracle  # noqa: E402
+from test_oracle_pinned import golden_specs  # noqa: E402
+
+
+def close(a, b, rtol, what):
+    a = torch.as_tensor(a).detach().cpu().double()
+    b = torch.as_tensor(b).detach().cpu().double()
+    scale = max(b.abs().max().item(), 1e-30)
+    err = (a - b).abs().max().item()
+    assert err <= rtol * scale + 1e-7, '%s: max err %.3e (scale %.3e)' % (what, err, scale)
+
+
+class _ReplayBernoulli:
+    """Feed the drop masks the reference drew (recorded in the fixture) to the product."""
+
+    def __init__(self, masks):
+        self.masks, self.i, self.real = masks, 0, torch.bernoulli
+
+    def __enter__(self):
+        def fake(p, *a, **k):
+            m = self.masks[self.i]
+            self.i += 1
+            assert tuple(m.shape) == tuple(p.shape)
+            return m.clone()
+        torch.bernoulli = fake
+        return self
+
+    def __exit__(self, *exc):
+        torch.bernoulli = self.real
+
+
+def _mask_of(net, name):
+    if name.startswith('w') and name.endswith('x.0.weight') or name[0] in 'wu' and '.weight' in name and hasattr(net, 'hcgsx'):
+        idx = name.split('.')[1]
+        return (net.hcgsx if name[0] == 'w' else net.hcgsh)[int(idx)].mask
+    return None
+
+
+@pytest.mark.parametrize('name,kw', [
+    ('train_small', {}),
+    ('train_htanh', dict(seed=11, lstm_over=dict(lstm_act='htanh,htanh', lstm_lay='20,28', lstm_drop='0.0,0.1'))),
+])
+def test_train_steps_match_reference_fixture(name, kw):
+    g = load_golden(name)
+    T, B, D, steps = [int(v) for v in g['dims']]
+    nets, sections = build_product_nets('train', device='cuda', **kw)
+    for n, net in nets.items():
+        net.load_state_dict(golden_state(g, 'init', n))
+    graph = make_graph(nets, D)
+    from b200.graph import make_optimizer
+    opts = {n: make_optimizer(nets[n], sec) for n, sec in zip(nets, sections)}
+    nl = nets['LSTM_layers'].N_lstm_lay
+    drops = [torch.from_numpy(g['drop/%d' % i]) for i in range(steps * nl)]
+    with _ReplayBernoulli(drops):
+        for s in range(steps):
+            inp = torch.from_numpy(g['inp/%d' % s]).cuda()
+            out = graph.forward(inp, T, B, 'train', ['out_dnn2'])
+            for o in opts.values():
+                o.zero_grad()
+            out['loss_final'].backward()
+            ref = g['loss/%d' % s]
+            assert abs(out['loss_final'].item() - ref[0]) <= 1e-5 * abs(ref[0]), (s, out['loss_final'].item(), ref[0])
+            assert abs(out['err_final'].item() - ref[1]) < 1e-6
+            close(out['out_dnn1'].reshape(T * B, -1), g['out_dnn1/%d' % s], 1e-5, 'out_dnn1')
+            close(out['out_dnn2'], g['out_dnn2/%d' % s], 1e-5, 'out_dnn2')
+            if s == steps - 1:
+                for n, net in nets.items():
+                    masks = {}
+                    if n == 'LSTM_layers':
+                        for k, _ in net.named_parameters():
+                            if k[0] in 'wu' and k.endswith('.weight') and not k.startswith('bn'):
+                                i = int(k.split('.')[1])
+                                masks[k] = (net.hcgsx if k[0] == 'w' else net.hcgsh)[i].mask.detach().cpu()
+                    if n == 'MLP_layers':
+                        masks['wx.0.weight'] = net.hcgs[0].mask.detach().cpu()
+                    for k, p in net.named_parameters():
+                        key = 'grad/%s/%s' % (n, k)
+                        if key not in g.files:
+                            assert p.grad is None or k.endswith('mask'), k
+                            continue
+                        refg = torch.from_numpy(g[key])
+                        if k in masks:
+                            refg = refg * masks[k]      # kept weights only
+                        close(p.grad, refg, 1e-4, key)
+            for o in opts.values():
+                o.step()
+    # parameters after the optimizer steps, on kept entries; BN running statistics
+    for n, net in nets.items():
+        sd = net.state_dict()
+        for k, v in sd.items():
+            ref = torch.from_numpy(g['final/%s/%s' % (n, k)])
+            if k.endswith('num_batches_tracked'):
+                assert int(v.item()) == int(ref.item()), k
+                continue
+            mine = v.detach().cpu()
+            mk = None
+            if n == 'LSTM_layers' and k[0] in 'wu' and k.endswith('.weight'):
+                mk = sd[('hcgsx.%s.mask' if k[0] == 'w' else 'hcgsh.%s.mask') % k.split('.')[1]].cpu()
+            if n == 'MLP_layers' and k == 'wx.0.weight':
+                mk = sd['hcgs.0.mask'].cpu()
+            if mk is not None:
+                mine, ref = mine * mk, ref * mk
+            close(mine, ref, 1e-4, 'final %s/%s' % (n, k))
+
+
+@pytest.mark.parametrize('name,to_do,seed', [('valid_small', 'valid', 2234), ('eval_forward', 'forward', 77)])
+def test_eval_matches_reference_fixture(name, to_do, seed, tmp_path):
+    g = load_golden(name)
+    T, B, D, _ = [int(v) for v in g['dims']]
+    nets, _ = build_product_nets(to_do, seed=seed, device='cuda', out_folder=str(tmp_path))
+    for n, net in nets.items():
+        net.load_state_dict(golden_state(g, 'init', n))
+    graph = make_graph(nets, D)
+    inp = torch.from_numpy(g['inp/0']).cuda()
+    with torch.no_grad():
+        out = graph.forward(inp, T, B, to_do, ['out_dnn2'])
+    close(out['out_dnn2'], g['out_dnn2/0'], 1e-5, 'posterior log-probs')
+    if to_do == 'valid':
+        assert abs(out['loss_final'].item() - g['loss/0'][0]) <= 1e-5 * abs(g['loss/0'][0])
+    # side effect of the first valid/forward call: weight + mask dumps (save_cgs_mat.py)
+    files = os.listdir(str(tmp_path))
+    assert 'mat0_wfx_LSTM_layers.mat' in files and 'conn_mat0_x_LSTM_layers.mat' in files
+    assert 'mat0_w_MLP_layers.mat' in files and 'conn_mat1_h_LSTM_layers.mat' in files
+
+
+def test_posterior_export_bytes_match_reference(tmp_path):
+    """Fused log-softmax - log-prior on the GPU -> Kaldi ark record, against the reference's bytes."""
+    import posterior_io
+    g = load_golden('eval_forward')
+    gp = load_golden('posterior')
+    T, B, D, _ = [int(v) for v in g['dims']]
+    nets, _ = build_product_nets('forward', seed=77, device='cuda', out_folder=str(tmp_path))
+    for n, net in nets.items():
+        net.load_state_dict(golden_state(g, 'init', n))
+    nets['MLP_layers'].log_prior = posterior_io.log_prior_tensor(gp['counts'], 'cuda')
+    graph = make_graph(nets, D)
+    with torch.no_grad():
+        out = graph.forward(torch.from_numpy(g['inp/0']).cuda(), T, B, 'forward', ['out_dnn2'])
+    post = out['out_dnn2'].cpu().numpy()
+    assert post.dtype == np.float32 and post.shape == gp['post'].shape
+    assert np.abs(post - gp['post']).max() <= 1e-5 * np.abs(gp['post']).max()
+    rec = posterior_io.mat_record(post, 'utt_0001')
+    ref = bytes(gp['ark'])
+    assert rec[:rec.index(b'FM ') + 13] == ref[:ref.index(b'FM ') + 13]     # key + header bytes identical
+    assert len(rec) == len(ref)
+
+
+def _state_to_cpu(nets):
+    params = {}
+    for k, n in NETS.items():
+        params[k] = {a: b.detach().cpu().clone() for a, b in nets[n].state_dict().items()}
+    return params
+
+
+@pytest.mark.parametrize('H,layers,T,B,P', [(550, 4, 60, 8, 1944), (512, 2, 40, 5, 1944)])
+def test_cfg_shape_train_step_matches_oracle(H, layers, T, B, P):
+    """TIMIT_CGS shape: 40-dim input, HCGS 32,4/75,62.5 LSTM, 64,4/50,25 output layer, two heads."""
+    D = 40
+    lay = ','.join([str(H)] * layers)
+    lstm_over = dict(lstm_lay=lay, lstm_drop=','.join(['0.2'] * layers), lstm_use_laynorm=','.join(['False'] * layers),
+                     lstm_use_batchnorm=','.join(['True'] * layers), lstm_act=','.join(['tanh'] * layers),
+                     hcgsx_block='32,4', hcgsx_sparse='75,62.5', hcgsh_block='32,4', hcgsh_sparse='75,62.5')
+    mlp_over = dict(dnn_lay=str(P), hcgs_block='64,4', hcgs_sparse='50,25')
+    nets, _ = build_product_nets('train', D=D, seed=2234, lstm_over=lstm_over, mlp_over=mlp_over, device='cuda')
+    nets['MLP_layers2'] = nets['MLP_layers2']  # mono head built with dnn_lay=5 by the helper
+    params = _state_to_cpu(nets)
+    gen = torch.Generator().manual_seed(1)
+    inp = torch.zeros(T, B, D + 2)
+    inp[:, :, :D] = torch.randn(T, B, D, generator=gen)
+    inp[:, :, D] = torch.randint(0, P, (T, B), generator=gen).float()
+    inp[:, :, D + 1] = torch.randint(0, 5, (T, B), generator=gen).float()
+    inp[T - 7:, B - 1, :] = 0
+    drops = [torch.bernoulli(torch.full((B, H), 0.8), generator=gen) for _ in range(layers)]
+    # oracle (CPU)
+    for d in params.values():
+        for k, v in d.items():
+            if v.dtype == torch.float32 and not k.endswith(('running_mean', 'running_var', 'mask')):
+                v.requires_grad_(True)
+    specs = golden_specs(dict(lay=[H] * layers, act=['tanh'] * layers, use_bn=[True] * layers, drop=[0.2] * layers))
+    specs['cd']['lay'] = [P]
+    ref = model_oracle.model_forward(params, specs, inp, D, True, drops)
+    ref['loss_final'].backward()
+    # product (GPU)
+    graph = make_graph(nets, D)
+    with _ReplayBernoulli(drops):
+        out = graph.forward(inp.cuda(), T, B, 'train', ['out_dnn2'])
+    out['loss_final'].backward()
+    assert abs(out['loss_final'].item() - ref['loss_final'].item()) <= 1e-5 * abs(ref['loss_final'].item())
+    close(out['out_dnn2'], ref['out_dnn2'], 1e-5, 'log-posteriors')
+    close(out['out_dnn1'].reshape(T, B, -1), ref['out_dnn1'], 1e-5, 'lstm output')
+    for k, n in NETS.items():
+        for name, p in nets[n].named_parameters():
+            rg = params[k][name].grad
+            if rg is None:
+                assert p.grad is None or name.endswith('mask')
+                continue
+            close(p.grad, rg, 1e-4, 'grad %s/%s' % (n, name))
+    # the BN running statistics were updated identically
+    close(nets['LSTM_layers'].bn_wfx[0].running_var, params['lstm']['bn_wfx.0.running_var'], 1e-5, 'running_var')
+
+
+def test_mlp_baseline_cfg_matches_oracle():
+    """cfg 1 (TIMIT_MLP_mfcc_basic): 429 -> 4x1024 (BN, ReLU, dropout .15) -> 1944 log-softmax, batch 128, dense."""
+    import neural_networks as nb
+    torch.manual_seed(1234)
+    np.random.seed(1234)
+    opts = dict(dnn_lay='1024,1024,1024,1024,1944', dnn_drop='0.15,0.15,0.15,0.15,0.0',
+                dnn_use_batchnorm='True,True,True,True,False', dnn_use_laynorm='False,False,False,False,False',
+                dnn_use_laynorm_inp='False', dnn_use_batchnorm_inp='False', dnn_act='relu,relu,relu,relu,softmax',
+                to_do='train', arch_name='MLP_layers1')
+    net = nb.MLP(opts, 429).cuda().train()
+    params = {k: v.detach().cpu().clone() for k, v in net.state_dict().items()}
+    for k, v in params.items():
+        if v.dtype == torch.float32 and not k.endswith(('running_mean', 'running_var')):
+            v.requires_grad_(True)
+    spec = dict(lay=[1024] * 4 + [1944], act=['relu'] * 4 + ['softmax'], use_bn=[True] * 4 + [False],
+                drop=[0.15] * 4 + [0.0], hcgs=False)
+    x = torch.randn(128, 429)
+    labels = torch.randint(0, 1944, (128,))
+    # identical dropout masks: the product draws them with F.dropout on the CUDA generator
+    torch.cuda.manual_seed(7)
+    masks = [torch.nn.functional.dropout(torch.ones(128, 1024, device='cuda'), 0.15, True).cpu() for _ in range(4)]
+    ref = model_oracle.mlp_forward(params, spec, x, True, masks + [None])
+    loss_ref = torch.nn.functional.nll_loss(ref, labels)
+    loss_ref.backward()
+    torch.cuda.manual_seed(7)
+    out = net(x.cuda())
+    loss = torch.nn.functional.nll_loss(out, labels.cuda())
+    loss.backward()
+    assert abs(loss.item() - loss_ref.item()) <= 1e-5 * abs(loss_ref.item())
+    close(out, ref, 1e-5, 'mlp log-posteriors')
+    for name, p in net.named_parameters():
+        if params[name].grad is not None:
+            close(p.grad, params[name].grad, 1e-4, 'grad ' + name)
+
+
+def test_quantised_weights_train_step_matches_reference_fixture():
+    g = load_golden('train_quant')
+    T, B, D, _ = [int(v) for v in g['dims']]
+    nets, _ = build_product_nets('train', seed=5, lstm_over=dict(lstm_quant='True'), mlp_over=dict(mlp_quant='True'),
+                                 device='cuda')
+    for n, net in nets.items():
+        net.load_state_dict(golden_state(g, 'init', n))
+    graph = make_graph(nets, D)
+    drops = [torch.from_numpy(g['drop/%d' % i]) for i in range(2)]
+    with _ReplayBernoulli(drops):
+        out = graph.forward(torch.from_numpy(g['inp/0']).cuda(), T, B, 'train', ['out_dnn2'])
+    out['loss_final'].backward()
+    assert abs(out['loss_final'].item() - g['loss/0'][0]) <= 1e-5 * abs(g['loss/0'][0])
+    close(out['out_dnn2'], g['out_dnn2/0'], 1e-5, 'out_dnn2 (8-bit weights)')
+    lstm = nets['LSTM_layers']
+    for k in ('ufh.0.weight', 'wcx.1.weight', 'uoh.1.weight'):
+        i = int(k.split('.')[1])
+        mask = (lstm.hcgsx if k[0] == 'w' else lstm.hcgsh)[i].mask.detach().cpu()
+        close(dict(lstm.named_parameters())[k].grad, torch.from_numpy(g['grad/LSTM_layers/' + k]) * mask, 1e-4, k)

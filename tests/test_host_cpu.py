@@ -1,0 +1,93 @@
+"""CPU-only checks of the product's host side: drop-in construction parity, state_dict surface,
+option handling, graph interpreter parsing, the C-ABI symbol table, and the no-fallback rule."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import ROOT
+from helpers import NETS, build_product_nets, golden_state, load_golden
+
+
+@pytest.mark.parametrize('name,to_do,kw', [
+    ('train_small', 'train', {}),
+    ('train_htanh', 'train', dict(seed=11, lstm_over=dict(lstm_act='htanh,htanh', lstm_lay='20,28', lstm_drop='0.0,0.1'))),
+    ('eval_forward', 'forward', dict(seed=77)),
+    ('train_quant', 'train', dict(seed=5, lstm_over=dict(lstm_quant='True'), mlp_over=dict(mlp_quant='True'))),
+])
+def test_construction_is_bit_identical_to_reference(name, to_do, kw):
+    """Same seed -> same initial weights, masks, BN buffers, under the same state_dict keys."""
+    g = load_golden(name)
+    nets, _ = build_product_nets(to_do, **kw)
+    for net_name, net in nets.items():
+        ref = golden_state(g, 'init', net_name)
+        sd = net.state_dict()
+        assert list(sd.keys()) == list(ref.keys()), net_name
+        for k, v in sd.items():
+            assert torch.equal(v.cpu(), ref[k]), (net_name, k)
+
+
+def test_state_dict_roundtrip_and_plugin_surface():
+    nets, _ = build_product_nets('train')
+    lstm, cd = nets['LSTM_layers'], nets['MLP_layers']
+    assert lstm.out_dim == 24 and cd.out_dim == 10
+    for n in (lstm, cd):
+        for attr in ('prune', 'guided_hcgs', 'apply_guided_hcgs', 'if_pattern', 'skip_regularization'):
+            assert hasattr(n, attr)
+    sd = {k: v.clone() for k, v in lstm.state_dict().items()}
+    nets2, _ = build_product_nets('train', seed=1)
+    nets2['LSTM_layers'].load_state_dict(sd)
+    for k, v in nets2['LSTM_layers'].state_dict().items():
+        assert torch.equal(v, sd[k])
+    # masks are parameters (travel in checkpoints) but the optimizer never sees a gradient for them
+    assert 'hcgsx.0.mask' in dict(lstm.named_parameters())
+
+
+def test_missing_cgs_keys_default_off_and_alias_spelling():
+    import neural_networks as nb
+    base = dict(dnn_lay='16,8', dnn_drop='0.1,0.0', dnn_use_batchnorm='True,False', dnn_use_laynorm='False,False',
+                dnn_use_laynorm_inp='False', dnn_use_batchnorm_inp='False', dnn_act='relu,softmax', to_do='train')
+    m = nb.MLP(base, 12)           # TIMIT_MLP_mfcc_basic style section: no CGS keys at all
+    assert not m.mlp_hcgs and not m.mlp_quant and not m.prune and not m.if_pattern
+    np.random.seed(0)
+    m2 = nb.MLP(dict(base, mlp_hcgs='True', hcgs_block='8,4', hcgs_drop='50,25'), 12)   # LibriSpeech_CGS spelling
+    assert m2.hcgs_sparse == [50.0, 25.0] and tuple(m2.hcgs[0].mask.shape) == (16, 12)
+    with pytest.raises(ValueError):
+        nb.LSTM(dict(lstm_lay='8', lstm_drop='0', lstm_use_batchnorm='False', lstm_use_laynorm='False',
+                     lstm_use_laynorm_inp='False', lstm_use_batchnorm_inp='False', lstm_act='tanh',
+                     lstm_orthinit='True', lstm_bidir='False'), 4)
+
+
+def test_no_cpu_fallback():
+    """Without a CUDA device the compute entry points must raise, never compute on the host."""
+    if torch.cuda.is_available():
+        pytest.skip('GPU present')
+    from b200 import native
+    nets, _ = build_product_nets('train')
+    with pytest.raises(native.NativeError):
+        nets['LSTM_layers'](torch.zeros(3, 2, 12))
+    with pytest.raises(native.NativeError):
+        nets['MLP_layers'](torch.zeros(6, 24))
+
+
+def test_graph_parser():
+    from b200.graph import parse_model
+    ops = parse_model('out_dnn1=compute(LSTM_layers,fbank)\n\tloss_final=sum(loss_cd,loss_mono_w)\n'
+                      '\tloss_mono_w=mult_constant(loss_mono,1.0)')
+    assert ops[0] == ('out_dnn1', 'compute', 'LSTM_layers', 'fbank')
+    assert ops[2] == ('loss_mono_w', 'mult_constant', 'loss_mono', '1.0')
+
+
+def test_c_abi_exports_every_declared_symbol():
+    from b200 import native
+    header = open(os.path.join(ROOT, 'include', 'hcgs_b200.h')).read()
+    declared = set(re.findall(r'^\s*(?:int|const char\*)\s+(hcgs_\w+)\s*\(', header, flags=re.M))
+    assert len(declared) >= 20
+    lib = ctypes.CDLL(native.LIB_PATH)
+    for name in declared:
+        assert hasattr(lib, name), 'library does not export %s' % name
+    assert declared == set(native.SIGNATURES), declared ^ set(native.SIGNATURES)
+    assert native.load().hcgs_abi_version() == 1
