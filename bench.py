@@ -1,0 +1,415 @@
+#!/usr/bin/env python
+"""Headline benchmark: HCGS-LSTM train frames/s on B200 (BASELINE.json configs[1], TIMIT_CGS LSTM).
+
+    python bench.py --gpus N --steps K --warmup W            # our arm (one rank per GPU under torchrun)
+    python bench.py --impl reference --gpus N --steps K ...   # reference arm: CPU path on the host cores
+
+One "step" = one minibatch through the whole hot path: forward (4x550 HCGS LSTM + 1944-way and
+48-way MLP heads), loss, backward, RMSprop step -- the body of core.run_nn's training loop.
+Prints ONE JSON line (rank 0).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (os.path.join(ROOT, 'pytorch-kaldi-cgs_b200'), ROOT, os.path.join(ROOT, 'tests')):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+D_FEA, N_PDF, N_MONO = 40, 1944, 48
+LAYERS, HID = 4, 550
+
+
+def cfg_sections(to_do='train'):
+    lay = ','.join([str(HID)] * LAYERS)
+    rep = lambda v: ','.join([v] * LAYERS)  # noqa: E731
+    lstm = dict(arch_name='LSTM_layers', lstm_lay=lay, lstm_drop=rep('0.2'), lstm_use_laynorm_inp='False',
+                lstm_use_batchnorm_inp='False', lstm_use_laynorm=rep('False'), lstm_use_batchnorm=rep('True'),
+                lstm_bidir='False', lstm_act=rep('tanh'), if_hsigmoid='True', lstm_orthinit='True', arch_lr='0.0016',
+                arch_opt='rmsprop', opt_momentum='0.0', opt_alpha='0.95', opt_eps='1e-8', opt_centered='False',
+                opt_weight_decay='0.0', out_folder='', lstm_hcgs='True', guided_hcgs='False',
+                apply_guided_hcgs='False', hcgsx_block='32,4', hcgsx_sparse='75,62.5', hcgsh_block='32,4',
+                hcgsh_sparse='75,62.5', lstm_quant='False', param_quant=rep('8'), lstm_quant_inp='False',
+                inp_quant='16', lstm_prune='False', lstm_prune_perc='70', skip_regularization='True', to_do=to_do,
+                use_cuda='True')
+    mlp = dict(arch_name='MLP_layers', dnn_lay=str(N_PDF), dnn_drop='0.0', dnn_use_laynorm_inp='False',
+               dnn_use_batchnorm_inp='False', dnn_use_batchnorm='False', dnn_use_laynorm='False', dnn_act='softmax',
+               arch_lr='0.0016', arch_opt='rmsprop', opt_momentum='0.0', opt_alpha='0.95', opt_eps='1e-8',
+               opt_centered='False', opt_weight_decay='0.0', out_folder='', mlp_hcgs='True', guided_hcgs='False',
+               apply_guided_hcgs='False', hcgs_block='64,4', hcgs_sparse='50,25', mlp_quant='False', param_quant='8',
+               mlp_quant_inp='False', inp_quant='16', mlp_prune='False', mlp_prune_perc='70',
+               skip_regularization='True', to_do=to_do, use_cuda='True')
+    mono = dict(mlp, arch_name='MLP_layers2', dnn_lay=str(N_MONO), mlp_hcgs='False', arch_lr='0.0004')
+    return lstm, mlp, mono
+
+
+MODEL = ['out_dnn1=compute(LSTM_layers,fbank)', 'out_dnn2=compute(MLP_layers,out_dnn1)',
+         'out_dnn3=compute(MLP_layers2,out_dnn1)', 'loss_mono=cost_nll(out_dnn3,lab_mono)',
+         'loss_mono_w=mult_constant(loss_mono,1.0)', 'loss_cd=cost_nll(out_dnn2,lab_cd)',
+         'loss_final=sum(loss_cd,loss_mono_w)', 'err_final=cost_err(out_dnn2,lab_cd)']
+
+
+def synthetic_minibatch(T, B, seed):
+    """N(0,1) features, uniform pdf labels as trailing float columns, sequence lengths
+    U[T/2, T] sorted ascending, zero padding (random left offset like core.py:193-197)."""
+    g = torch.Generator().manual_seed(seed)
+    inp = torch.zeros(T, B, D_FEA + 2)
+    lens = torch.sort(torch.randint(max(1, T // 2), T + 1, (B,), generator=g))[0]
+    frames = 0
+    for b in range(B):
+        n = int(lens[b])
+        left = int(torch.randint(0, T - n + 1, (1,), generator=g))
+        inp[left:left + n, b, :D_FEA] = torch.randn(n, D_FEA, generator=g)
+        inp[left:left + n, b, D_FEA] = torch.randint(0, N_PDF, (n,), generator=g).float()
+        inp[left:left + n, b, D_FEA + 1] = torch.randint(0, N_MONO, (n,), generator=g).float()
+        frames += n
+    return inp, frames
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ('index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,'
+         'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,'
+         'clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, gpu_index):
+        self.idx, self.proc, self.lines = gpu_index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(['nvidia-smi', '-i', str(self.idx), '--query-gpu=' + self.Q,
+                                          '--format=csv,noheader,nounits', '-lms', '100'],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        for l in self.lines:
+            f = [x.strip() for x in l.split(',')]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx = float(f[2])
+            except ValueError:
+                continue
+            for n, v in zip(names, f[5:9]):
+                if v.lower().startswith('active'):
+                    reasons.add(n)
+        return {'sm_mhz': float(np.median(sm)) if sm else None, 'sm_max_mhz': mx, 'reasons': sorted(reasons),
+                'samples': len(sm)}
+
+
+def build_workload(device, seed=2234):
+    import neural_networks as nb
+    from b200.graph import Graph, make_optimizer
+    torch.manual_seed(seed)
+    np.random.seed(seed)
+    s_lstm, s_cd, s_mono = cfg_sections('train')
+    lstm = nb.LSTM(s_lstm, D_FEA)
+    cd = nb.MLP(s_cd, lstm.out_dim)
+    mono = nb.MLP(s_mono, lstm.out_dim)
+    nets = {'LSTM_layers': lstm, 'MLP_layers': cd, 'MLP_layers2': mono}
+    for n in nets.values():
+        n.to(device).train()
+    graph = Graph(MODEL, nets, {'LSTM_layers': True, 'MLP_layers': False, 'MLP_layers2': False},
+                  {'fbank': (0, D_FEA)}, {'lab_cd': D_FEA, 'lab_mono': D_FEA + 1})
+    opts = {k: make_optimizer(nets[k], s) for k, s in zip(nets, (s_lstm, s_cd, s_mono))}
+    return nets, graph, opts
+
+
+def train_step(graph, opts, inp, T, B, bucket=None):
+    out = graph.forward(inp, T, B, 'train', ['out_dnn2'])
+    for o in opts.values():
+        o.zero_grad(set_to_none=True)
+    out['loss_final'].backward()
+    if bucket is not None:
+        bucket.all_reduce_mean()
+    for o in opts.values():
+        o.step()
+    return out['loss_final']
+
+
+class KernelTimers:
+    """CUDA-event timing of every native entry point inside the timed region (same stream)."""
+
+    NAMES = ['mask_apply', 'bsgemm_nt', 'bsgemm_nn', 'bs_sddmm', 'colsum', 'bn_fwd', 'bn_bwd', 'lstm_pack',
+             'lstm_fwd', 'lstm_bwd', 'logsoftmax_fwd', 'logsoftmax_bwd', 'act_fwd', 'act_bwd', 'quantize_w',
+             'quantize_act']
+
+    def __init__(self):
+        from b200 import native
+        self.native, self.orig, self.events, self.on = native, {}, [], False
+        for n in self.NAMES:
+            self.orig[n] = getattr(native, n)
+            setattr(native, n, self._wrap(n))
+
+    def _wrap(self, name):
+        fn = self.orig[name]
+
+        def timed(*a, **k):
+            if not self.on:
+                return fn(*a, **k)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            r = fn(*a, **k)
+            e1.record()
+            self.events.append((name, e0, e1))
+            return r
+        return timed
+
+    def summary(self):
+        tot, cnt = {}, {}
+        for n, e0, e1 in self.events:
+            tot[n] = tot.get(n, 0.0) + e0.elapsed_time(e1)
+            cnt[n] = cnt.get(n, 0) + 1
+        return tot, cnt
+
+    def restore(self):
+        for n, f in self.orig.items():
+            setattr(self.native, n, f)
+
+
+def oracle_workload(seed=2234):
+    """The reference's CPU path restated (oracle/model_oracle.py): same nets, same init."""
+    import neural_networks as nb
+    torch.manual_seed(seed)
+    np.random.seed(seed)
+    s_lstm, s_cd, s_mono = cfg_sections('train')
+    for s in (s_lstm, s_cd, s_mono):
+        s['use_cuda'] = 'False'
+    nets = {'lstm': nb.LSTM(s_lstm, D_FEA), 'cd': nb.MLP(s_cd, HID), 'mono': nb.MLP(s_mono, HID)}
+    params = {k: {a: b.detach().cpu().clone() for a, b in n.state_dict().items()} for k, n in nets.items()}
+    train = []
+    for k, d in params.items():
+        for n, v in d.items():
+            if v.dtype == torch.float32 and not n.endswith(('running_mean', 'running_var', 'mask')):
+                v.requires_grad_(True)
+    opts = []
+    for k in params:
+        lr = 0.0004 if k == 'mono' else 0.0016
+        opts.append(torch.optim.RMSprop([v for v in params[k].values() if v.requires_grad], lr=lr, alpha=0.95,
+                                        eps=1e-8))
+    specs = {'lstm': dict(lay=[HID] * LAYERS, act=['tanh'] * LAYERS, use_bn=[True] * LAYERS, drop=[0.2] * LAYERS,
+                          hcgs=True),
+             'cd': dict(lay=[N_PDF], act=['softmax'], use_bn=[False], drop=[0.0], hcgs=True),
+             'mono': dict(lay=[N_MONO], act=['softmax'], use_bn=[False], drop=[0.0], hcgs=False)}
+    return params, specs, opts
+
+
+def time_oracle(T, B, steps, warmup, threads):
+    from oracle import model_oracle
+    torch.set_num_threads(threads)
+    params, specs, opts = oracle_workload()
+    times, frames = [], 0
+    for s in range(warmup + steps):
+        inp, fr = synthetic_minibatch(T, B, 100 + s)
+        drops = [torch.bernoulli(torch.full((B, HID), 0.8)) for _ in range(LAYERS)]
+        t0 = time.perf_counter()
+        out = model_oracle.model_forward(params, specs, inp, D_FEA, True, drops)
+        for o in opts:
+            o.zero_grad()
+        out['loss_final'].backward()
+        for o in opts:
+            o.step()
+        dt = time.perf_counter() - t0
+        if s >= warmup:
+            times.append(dt)
+            frames += fr
+    return frames / sum(times), sum(times) / len(times) * 1e3
+
+
+def run_reference_arm(args, rank):
+    """Reference arm: the reference's own CPU implementation of the path (oracle port), all host threads."""
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    T, B = min(args.seq_len, 100), 8
+    steps = max(1, min(args.steps, 5))
+    fps, ms = time_oracle(T, B, steps, min(args.warmup, 1), threads)
+    line = {'impl': 'reference', 'metric': 'hcgs_lstm_train_frames_per_sec', 'value': fps, 'unit': 'frames/s',
+            'n_gpus': args.gpus, 'steps': steps, 'warmup': min(args.warmup, 1), 'ms_per_step': ms,
+            'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'config': workload_config(args, T, B),
+            'cpu_baseline': {'value': fps, 'unit': 'frames/s', 'cores': threads, 'kind': 'port',
+                             'sample': '%d train steps of one [T=%d, B=%d] minibatch (reference cfg batch size), '
+                                       'oracle/model_oracle.py on torch CPU kernels' % (steps, T, B)},
+            'e2e': {'value': fps, 'unit': 'frames/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
+    print(json.dumps(line))
+
+
+def workload_config(args, T, B):
+    return {'workload': 'TIMIT_CGS LSTM train step: 40-dim fbank -> 4x550 HCGS LSTM (32,4 / 75,62.5 masks, BN, tanh, '
+                        'drop 0.2) -> 1944-pdf (64,4 / 50,25) + 48-mono softmax heads, NLL, RMSprop',
+            'seq_len': T, 'batch_per_gpu': B, 'frames_counted': 'real (unpadded) frames',
+            'parallelism': 'dp%d' % args.gpus,
+            'l2_policy': 'per-step working set (~%.1f GB of activations) exceeds the 126 MB L2; no explicit flush'
+                         % (T * B * HID * 4 * 4 * 4 * 10 / 1e9)}
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d.get('hbm_gbs', 6650.0), d.get('bf16_tflops_sustained', 1400.0), 'measured'
+    return 6650.0, 1590.0, 'fallback'
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=10)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+    ap.add_argument('--seq-len', type=int, default=256, help='padded minibatch length T (cfg max_seq_length_train <= 1000)')
+    ap.add_argument('--batch', type=int, default=128, help='sequences per GPU per optimizer step')
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    args = ap.parse_args()
+
+    from b200 import dist as bdist
+    if args.impl == 'reference':
+        rank = int(os.environ.get('RANK', '0'))
+        run_reference_arm(args, rank)
+        return
+    rank, world, local = bdist.init_from_env('nccl')
+    assert torch.cuda.is_available(), 'bench.py needs a CUDA device (no CPU fallback)'
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    from b200 import native
+    T, B = args.seq_len, args.batch
+    W = max(args.warmup, 3)
+    nets, graph, opts = build_workload(dev)
+    bucket = None
+    if world > 1:
+        bucket = bdist.GradBucket(bdist.lstm_mlp_entries(list(nets.values())), dev)
+    n_batches = 4
+    host = []
+    frames_per = []
+    for i in range(n_batches):
+        inp, fr = synthetic_minibatch(T, B, 1000 * (rank + 1) + i)
+        host.append(inp.pin_memory())
+        frames_per.append(fr)
+    resident = [h.to(dev) for h in host]
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            torch.distributed.barrier()
+            torch.cuda.synchronize()
+
+    # ---- device-resident throughput ("value") ---------------------------------------------------
+    for s in range(W):
+        train_step(graph, opts, resident[s % n_batches], T, B, bucket)
+    timers = KernelTimers()
+    sampler = ClockSampler(local)
+    sync_all()
+    sampler.start()
+    native.reset_launch_count()
+    timers.on = True
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    frames = 0
+    for s in range(args.steps):
+        train_step(graph, opts, resident[s % n_batches], T, B, bucket)
+        frames += frames_per[s % n_batches]
+    e1.record()
+    sync_all()
+    timers.on = False
+    clocks = sampler.stop()
+    launches = native.LAUNCHES['total']
+    ms_total = e0.elapsed_time(e1)
+    ktot, kcnt = timers.summary()
+    timers.restore()
+
+    # ---- end to end through the public API: pinned host minibatch -> GPU -> loss on the host ------
+    sync_all()
+    e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e2.record()
+    frames_e2e = 0
+    for s in range(args.steps):
+        inp = host[s % n_batches].to(dev, non_blocking=True)
+        loss = train_step(graph, opts, inp, T, B, bucket)
+        _ = loss.item()                                        # D2H read of the step's result
+        frames_e2e += frames_per[s % n_batches]
+    e3.record()
+    sync_all()
+    ms_e2e = e2.elapsed_time(e3)
+
+    t = torch.tensor([ms_total, ms_e2e, float(frames), float(frames_e2e)], device=dev, dtype=torch.float64)
+    if world > 1:
+        tmax = t.clone()
+        torch.distributed.all_reduce(tmax, op=torch.distributed.ReduceOp.MAX)
+        tsum = t.clone()
+        torch.distributed.all_reduce(tsum, op=torch.distributed.ReduceOp.SUM)
+        ms_total, ms_e2e = tmax[0].item(), tmax[1].item()
+        frames, frames_e2e = tsum[2].item(), tsum[3].item()
+    if rank != 0:
+        return
+
+    value = frames / (ms_total * 1e-3)
+    e2e = frames_e2e / (ms_e2e * 1e-3)
+    hbm_peak, tf_peak, peak_kind = measured_peaks()
+    # dominant kernel = largest share of the timed region among our kernels
+    dom = max(ktot, key=ktot.get)
+    plan_h = nets['LSTM_layers']._plans._store[('h', 1)][1]
+    rows = T * B
+    alg_bytes = {'lstm_fwd': rows * 10 * HID * 4, 'lstm_bwd': rows * 10 * HID * 4}
+    avg_ms = ktot[dom] / kcnt[dom]
+    if dom in alg_bytes:
+        achieved = alg_bytes[dom] / (avg_ms * 1e-3) / 1e9
+        roof = {'kernel': dom, 'bound': 'hbm', 'achieved': achieved, 'peak': hbm_peak, 'unit': 'GB/s',
+                'frac': achieved / hbm_peak, 'traffic': None, 'peak_source': peak_kind,
+                'avg_launch_ms': avg_ms, 'share_of_step': ktot[dom] / ms_total,
+                'algorithmic_bytes_per_launch': alg_bytes[dom],
+                'note': 'persistent recurrent kernel: streams pre/gates/c/h once (10*H*4 B per frame); '
+                        'its floor is step latency x T, not HBM -- see DESIGN.md',
+                'us_per_step': avg_ms * 1e3 / T,
+                'effective_gflops': 2 * 4 * 16 * plan_h.n_blocks * rows / (avg_ms * 1e-3) / 1e9}
+    else:
+        roof = {'kernel': dom, 'bound': 'hbm', 'achieved': None, 'peak': hbm_peak, 'unit': 'GB/s', 'frac': None,
+                'traffic': None, 'avg_launch_ms': avg_ms, 'share_of_step': ktot[dom] / ms_total}
+    line = {'metric': 'hcgs_lstm_train_frames_per_sec', 'value': value, 'unit': 'frames/s', 'n_gpus': world,
+            'steps': args.steps, 'warmup': W, 'ms_per_step': ms_total / args.steps, 'higher_is_better': True,
+            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'config': workload_config(args, T, B), 'clocks': clocks, 'gpu_launches': launches,
+            'e2e': {'value': e2e, 'unit': 'frames/s', 'h2d_bytes_per_step': host[0].numel() * 4,
+                    'd2h_bytes_per_step': 4, 'ms_per_step': ms_e2e / args.steps},
+            'roofline': roof,
+            'kernel_ms_per_step': {k: round(v / args.steps, 4) for k, v in sorted(ktot.items(), key=lambda x: -x[1])}}
+    if not args.no_cpu_baseline and world == 1:
+        threads = os.cpu_count() or 1
+        fps, ms = time_oracle(100, 8, 3, 1, threads)
+        line['cpu_baseline'] = {'value': fps, 'unit': 'frames/s', 'cores': threads, 'kind': 'port',
+                                'sample': '3 train steps of one [T=100, B=8] minibatch (the cfg batch size) with '
+                                          'oracle/model_oracle.py (reference operator sequence on torch CPU kernels)',
+                                'ms_per_step': ms}
+    print(json.dumps(line))
+
+
+if __name__ == '__main__':
+    main()

@@ -1,0 +1,117 @@
+"""Data-parallel plumbing: one process per GPU, torch.distributed (NCCL over NVLink on the GPU box,
+gloo in the CPU tests).
+
+The reference has no working multi-GPU path (utils.py:1783-1784 wraps the nets in nn.DataParallel,
+which core.py:123 then breaks).  The B200 design:
+  * training  -- rank r runs its own minibatches; after backward ONE all-reduce averages a single
+    contiguous buffer that holds the gradients of every trainable parameter (weights only where
+    the HCGS mask keeps them: masked-out entries are structurally zero on every rank and are not
+    sent); BN statistics stay per rank like in the reference (no sync-BN).
+  * export    -- utterances are sharded by length-balanced round robin, no collective.
+"""
+import torch
+import torch.distributed as dist
+
+
+def init_from_env(backend=None):
+    """torchrun-style rendezvous (RANK / WORLD_SIZE / MASTER_ADDR / MASTER_PORT)."""
+    import os
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    rank = int(os.environ.get('RANK', '0'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    if world > 1 and not dist.is_initialized():
+        if backend is None:
+            backend = 'nccl' if torch.cuda.is_available() else 'gloo'
+        dist.init_process_group(backend=backend, rank=rank, world_size=world)
+    return rank, world, local
+
+
+class GradBucket:
+    """Flat gradient buffer over the kept entries of all trainable parameters.
+
+    ``entries`` = list of (param, mask_or_None).  For a masked weight only the indices where the mask
+    is non-zero travel; everything else is copied whole.  The index lists are built once.
+    """
+
+    def __init__(self, entries, device):
+        self.items = []
+        off = 0
+        for p, m in entries:
+            if not p.requires_grad:
+                continue
+            if m is not None:
+                idx = torch.nonzero(m.detach().reshape(-1) != 0, as_tuple=False).reshape(-1).to(device)
+                n = idx.numel()
+            else:
+                idx, n = None, p.numel()
+            self.items.append((p, idx, off, n))
+            off += n
+        self.numel = off
+        self.flat = torch.zeros(off, device=device, dtype=torch.float32)
+
+    def mask_signature(self):
+        """Cheap cross-rank consistency check of the index (masks must be identical on all ranks)."""
+        s = 0
+        for _, idx, off, n in self.items:
+            s = (s * 1000003 + n + (int(idx[:: max(1, n // 64)].sum().item()) if idx is not None and n else 0)) % (2 ** 61 - 1)
+        return s
+
+    def gather(self):
+        for p, idx, off, n in self.items:
+            if p.grad is None:
+                self.flat[off:off + n].zero_()
+            elif idx is None:
+                self.flat[off:off + n].copy_(p.grad.reshape(-1))
+            else:
+                torch.index_select(p.grad.reshape(-1), 0, idx, out=self.flat[off:off + n])
+
+    def scatter(self):
+        for p, idx, off, n in self.items:
+            if p.grad is None:
+                continue
+            if idx is None:
+                p.grad.reshape(-1).copy_(self.flat[off:off + n])
+            else:
+                p.grad.reshape(-1).index_copy_(0, idx, self.flat[off:off + n])
+
+    def all_reduce_mean(self):
+        """gradient <- mean over ranks (what one process would compute on the concatenated batch
+        when every rank's loss is a mean over its own frames)."""
+        if not dist.is_initialized() or dist.get_world_size() == 1:
+            return
+        self.gather()
+        dist.all_reduce(self.flat, op=dist.ReduceOp.SUM)
+        self.flat.div_(dist.get_world_size())
+        self.scatter()
+
+
+def lstm_mlp_entries(nets):
+    """(param, mask) pairs for LSTM / MLP plugin instances."""
+    out = []
+    for net in nets:
+        masks = {}
+        if hasattr(net, 'hcgsx') and getattr(net, 'lstm_hcgs', False):
+            for i in range(net.N_lstm_lay):
+                for g in 'fioc':
+                    masks['w%sx.%d.weight' % (g, i)] = net.hcgsx[i].mask
+                    masks['u%sh.%d.weight' % (g, i)] = net.hcgsh[i].mask
+        if hasattr(net, 'hcgs') and getattr(net, 'mlp_hcgs', False):
+            for i in range(net.N_dnn_lay):
+                masks['wx.%d.weight' % i] = net.hcgs[i].mask
+        for name, p in net.named_parameters():
+            if name.endswith('mask'):
+                continue            # masks never receive a gradient
+            out.append((p, masks.get(name)))
+    return out
+
+
+def shard_utterances(lengths, world):
+    """Length-balanced round robin: sort by length (descending), deal to the least-loaded rank."""
+    order = sorted(range(len(lengths)), key=lambda i: -lengths[i])
+    load = [0] * world
+    shards = [[] for _ in range(world)]
+    for i in order:
+        r = min(range(world), key=lambda k: load[k])
+        shards[r].append(i)
+        load[r] += lengths[i]
+    return [sorted(s) for s in shards]
