@@ -50,6 +50,12 @@ SIGNATURES = {
     'hcgs_lstm_pack': (c_int, [c_void_p, _pp, c_int, _f, _f, c_void_p]),
     'hcgs_lstm_fwd': (c_int, [c_void_p, _f, _f, _f, c_float, c_int, c_int, c_int, _f, _f, _f, c_int, c_void_p]),
     'hcgs_lstm_bwd': (c_int, [c_void_p, _f, _f, _f, _f, _f, c_float, c_int, c_int, c_int, _f, c_void_p]),
+    'hcgs_lstm_tc_info': (c_int, [c_void_p, c_int, c_int, POINTER(c_int64)]),
+    'hcgs_lstm_tc_pack': (c_int, [c_void_p, c_int, _pp, c_int, _f, _f, c_void_p]),
+    'hcgs_lstm_tc_fwd': (c_int, [c_void_p, c_int, c_int, _f, _f, c_int64, c_int, c_int, _f, c_float, c_int, c_int,
+                                 c_int, _f, _f, c_int, _f, _f, c_void_p]),
+    'hcgs_lstm_tc_bwd': (c_int, [c_void_p, c_int, c_int, _f, _f, _f, c_int64, c_int, c_int, _f, _f, c_float, c_int,
+                                 c_int, c_int, _f, _f, c_int64, c_void_p]),
     'hcgs_act_fwd': (c_int, [_f, _f, _f, c_int64, c_int, c_void_p]),
     'hcgs_act_bwd': (c_int, [_f, _f, _f, _f, c_int64, c_int, c_void_p]),
     'hcgs_logsoftmax_fwd': (c_int, [_f, c_int, _f, c_int, c_int64, c_int, _f, c_void_p]),
@@ -82,7 +88,8 @@ def load():
 # kernels launched by each entry point (our own kernels only; memsets are not counted)
 KERNELS_PER_CALL = {'hcgs_mask_apply': 1, 'hcgs_quantize_w': 1, 'hcgs_quantize_act': 2, 'hcgs_bsgemm_nt': 1,
                     'hcgs_bsgemm_nn': 1, 'hcgs_bs_sddmm': 1, 'hcgs_colsum': 1, 'hcgs_bn_fwd': 3, 'hcgs_bn_bwd': 2,
-                    'hcgs_lstm_pack': 2, 'hcgs_lstm_fwd': 1, 'hcgs_lstm_bwd': 1, 'hcgs_act_fwd': 1, 'hcgs_act_bwd': 1,
+                    'hcgs_lstm_pack': 2, 'hcgs_lstm_fwd': 1, 'hcgs_lstm_bwd': 1,
+                    'hcgs_lstm_tc_pack': 2, 'hcgs_lstm_tc_fwd': 1, 'hcgs_lstm_tc_bwd': 1, 'hcgs_act_fwd': 1, 'hcgs_act_bwd': 1,
                     'hcgs_logsoftmax_fwd': 1, 'hcgs_logsoftmax_bwd': 1, 'hcgs_nll_fwd_bwd': 1, 'hcgs_opt_step': 1}
 LAUNCHES = {'total': 0}
 
@@ -289,6 +296,65 @@ def lstm_bwd(plan, bwd_pack, dh_out, gates, c, drop, drop_scalar, act, dpre):
     assert dh_out.is_contiguous() and gates.is_contiguous() and c.is_contiguous() and dpre.is_contiguous()
     _check(load().hcgs_lstm_bwd(plan.handle, _ptr(bwd_pack), _ptr(dh_out), _ptr(gates), _ptr(c), _ptr(drop),
                                 float(drop_scalar), int(act), T, B, _ptr(dpre), _stream()), 'hcgs_lstm_bwd')
+
+
+def _require_cuda_any(*tensors):
+    if not torch.cuda.is_available():
+        raise NativeError('no CUDA device: the HCGS hot path has no CPU fallback')
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise NativeError('expected a CUDA tensor, got %s' % t.device)
+
+
+class TcConfig:
+    """Resolved launch shape of the tensor-core recurrence for one plan (hcgs_lstm_tc_info)."""
+
+    def __init__(self, plan, cluster_size=0, nb=0):
+        info = (c_int64 * 16)()
+        _check(load().hcgs_lstm_tc_info(plan.handle, int(cluster_size), int(nb), info), 'hcgs_lstm_tc_info')
+        self.cluster_size, self.nb = int(info[0]), int(info[1])
+        self.fwd_pack_u32, self.bwd_pack_u32 = int(info[2]), int(info[3])
+        self.smem_fwd, self.smem_bwd = int(info[4]), int(info[5])
+        self.warps, self.strips_per_cta, self.k_steps = int(info[6]), int(info[7]), int(info[8])
+        self.n_blocks, self.strips_per_warp, self.padded_hidden = int(info[9]), int(info[10]), int(info[11])
+
+
+def lstm_tc_pack(plan, cfg, us, fwd_pack=None, bwd_pack=None):
+    """fwd_pack / bwd_pack: int32 CUDA tensors of cfg.fwd_pack_u32 / cfg.bwd_pack_u32 elements."""
+    _require_cuda(*us)
+    _require_cuda_any(fwd_pack, bwd_pack)
+    assert len(us) == 4
+    _check(load().hcgs_lstm_tc_pack(plan.handle, cfg.cluster_size, _ptrs(us), _row_major_2d(us[0], 'u'),
+                                    _ptr(fwd_pack), _ptr(bwd_pack), _stream()), 'hcgs_lstm_tc_pack')
+
+
+def lstm_tc_fwd(plan, cfg, fwd_pack, pre, drop, drop_scalar, act, h_out, c_out=None, gates_out=None, hb_out=None,
+                interleaved=False):
+    """pre / gates_out: [T, B, 4H] fp32, gate-major (column g*H+u) or gate-interleaved (column u*4+g)."""
+    _require_cuda(pre, drop, h_out, c_out, gates_out)
+    _require_cuda_any(fwd_pack, hb_out)
+    T, B = pre.shape[0], pre.shape[1]
+    H = plan.n_out
+    assert pre.is_contiguous() and h_out.is_contiguous() and pre.shape[2] == 4 * H
+    gs, us_ = (1, 4) if interleaved else (H, 1)
+    hb_ld = 0 if hb_out is None else hb_out.stride(0)
+    _check(load().hcgs_lstm_tc_fwd(plan.handle, cfg.cluster_size, cfg.nb, _ptr(fwd_pack), _ptr(pre), 4 * H, gs, us_,
+                                   _ptr(drop), float(drop_scalar), int(act), T, B, _ptr(h_out), _ptr(hb_out), hb_ld,
+                                   _ptr(c_out), _ptr(gates_out), _stream()), 'hcgs_lstm_tc_fwd')
+
+
+def lstm_tc_bwd(plan, cfg, bwd_pack, dh_out, gates, c, drop, drop_scalar, act, dpre, dpre_bf16=None,
+                interleaved=False):
+    _require_cuda(dh_out, gates, c, drop, dpre)
+    _require_cuda_any(bwd_pack, dpre_bf16)
+    T, B = dh_out.shape[0], dh_out.shape[1]
+    H = plan.n_out
+    assert dh_out.is_contiguous() and gates.is_contiguous() and c.is_contiguous() and dpre.is_contiguous()
+    gs, us_ = (1, 4) if interleaved else (H, 1)
+    ldb = 0 if dpre_bf16 is None else dpre_bf16.stride(0)
+    _check(load().hcgs_lstm_tc_bwd(plan.handle, cfg.cluster_size, cfg.nb, _ptr(bwd_pack), _ptr(dh_out), _ptr(gates),
+                                   4 * H, gs, us_, _ptr(c), _ptr(drop), float(drop_scalar), int(act), T, B,
+                                   _ptr(dpre), _ptr(dpre_bf16), ldb, _stream()), 'hcgs_lstm_tc_bwd')
 
 
 def act_fwd(x, y, drop_mask, act):

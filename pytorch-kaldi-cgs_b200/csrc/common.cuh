@@ -70,6 +70,9 @@ struct RecurrentPlan {
     size_t smem_fwd = 0, smem_bwd = 0;
 };
 
+struct TcPlan;                 // tensor-core recurrent layouts of one cluster size (lstm_tc.cu)
+void tc_plan_free(TcPlan* t);  // defined in lstm_tc.cu
+
 }  // namespace hcgs
 
 struct hcgs_plan {
@@ -85,6 +88,11 @@ struct hcgs_plan {
     int max_row_tiles = 0, max_col_tiles = 0;
     bool recurrent = false;
     hcgs::RecurrentPlan rp;
+    // recurrent plans keep the 4x4-block occupancy on the host (ns44 x ns44 bytes) so that the
+    // tensor-core layouts can be derived lazily for whichever cluster size a launch asks for
+    uint8_t* h_blk44 = nullptr;
+    int ns44 = 0;
+    hcgs::TcPlan* tcp[3] = {nullptr, nullptr, nullptr};  // cluster size 4, 8, 16
 };
 
 namespace hcgs {

@@ -6,6 +6,7 @@
 //      128,4), so a 4x4 block is either fully kept or fully dropped; other masks are covered
 //      with zero fill (correct, just less efficient).
 #include <stdarg.h>
+#include <stdlib.h>
 
 #include <algorithm>
 #include <vector>
@@ -238,6 +239,12 @@ extern "C" int hcgs_plan_create(const float* mask, int n_out, int n_in, int recu
             hcgs_plan_destroy(p);
             return 1;
         }
+        p->ns44 = (H + 3) / 4;
+        p->h_blk44 = (uint8_t*)calloc((size_t)p->ns44 * p->ns44, 1);
+        HCGS_REQUIRE(p->h_blk44 != nullptr, "hcgs_plan_create: out of host memory");
+        for (int i = 0; i < H; ++i)
+            for (int j = 0; j < H; ++j)
+                if (mask[(size_t)i * H + j] != 0.f) p->h_blk44[(size_t)(i / 4) * p->ns44 + j / 4] = 1;
         p->recurrent = true;
     }
     *out = p;
@@ -257,6 +264,9 @@ extern "C" int hcgs_plan_destroy(hcgs_plan* p) {
     cudaFree(p->rp.d_blk_c);
     cudaFree(p->rp.d_cg_ptr);
     cudaFree(p->rp.d_cg_list);
+    for (int i = 0; i < 3; ++i)
+        if (p->tcp[i]) tc_plan_free(p->tcp[i]);
+    free(p->h_blk44);
     delete p;
     return 0;
 }

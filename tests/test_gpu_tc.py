@@ -1,0 +1,149 @@
+"""Tensor-core (bf16 operand) recurrent kernels against a torch reference that rounds the SAME
+operands to bf16 (U, h_{t-1} in the forward product; dpre in the backward product) and accumulates
+in fp32 -- the "bf16-accumulate mode" of the north star.  Differences are then summation order
+plus the occasional bf16 rounding flip of an h element, hence a tight mean and a loose max bound."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from oracle import hcgs_oracle, model_oracle  # noqa: E402
+
+
+def dev():
+    return torch.device('cuda', 0)
+
+
+def bf(x):
+    return x.to(torch.bfloat16).to(torch.float32)
+
+
+class _RoundGrad(torch.autograd.Function):
+    """identity whose incoming gradient is rounded to bf16 (the backward kernel's A operand)"""
+
+    @staticmethod
+    def forward(ctx, x):
+        return x.view_as(x)
+
+    @staticmethod
+    def backward(ctx, g):
+        return bf(g)
+
+
+def lstm_layer_oracle_bf16(us_r, pre, drop, act):
+    T, B, H4 = pre.shape
+    H = H4 // 4
+    h = torch.zeros(B, H)
+    c = h
+    hs = []
+    for k in range(T):
+        hr = h + (bf(h) - h).detach()
+        z = [pre[k, :, g * H:(g + 1) * H] + _RoundGrad.apply(hr @ us_r[g].t()) for g in range(4)]
+        c = torch.sigmoid(z[1]) * model_oracle.act(act, z[3]) * drop + torch.sigmoid(z[0]) * c
+        h = torch.sigmoid(z[2]) * model_oracle.act(act, c)
+        hs.append(h)
+    return torch.stack(hs)
+
+
+def check(a, b, mean_tol, max_tol, what):
+    a = a.detach().cpu().double()
+    b = b.detach().cpu().double()
+    scale = max(b.abs().max().item(), 1e-30)
+    err = (a - b).abs()
+    assert err.mean().item() <= mean_tol * scale, '%s: mean err %.3e (scale %.3e)' % (what, err.mean().item(), scale)
+    assert err.max().item() <= max_tol * scale, '%s: max err %.3e (scale %.3e)' % (what, err.max().item(), scale)
+
+
+def random_mask(rows, cols, blocks, drops, seed):
+    np.random.seed(seed)
+    return torch.from_numpy(hcgs_oracle.conn_mat(rows, cols, list(blocks), list(drops)).astype(np.float32))
+
+
+@pytest.mark.parametrize('H,B,T,blocks,drops,act,cl,nb,inter', [
+    (24, 3, 7, [8, 4], [50, 50], 'tanh', 4, 16, False),
+    (40, 19, 9, [8, 4], [50, 50], 'htanh', 4, 32, True),
+    (550, 8, 12, [32, 4], [75, 62.5], 'tanh', 8, 16, False),
+    (550, 20, 6, [32, 4], [75, 62.5], 'tanh', 4, 16, True),
+    (550, 37, 5, [32, 4], [75, 62.5], 'relu', 8, 32, False),
+    (512, 16, 8, [32, 4], [75, 62.5], 'tanh', 0, 0, False),
+    (1024, 9, 5, [32, 4], [75, 62.5], 'tanh', 0, 0, False),
+    (70, 5, 8, [16, 2], [50, 50], 'sigmoid', 4, 16, False),
+])
+def test_tc_recurrent_kernels(H, B, T, blocks, drops, act, cl, nb, inter):
+    from b200 import native
+    torch.manual_seed(H + B + T)
+    mask = random_mask(H, H, blocks, drops, 3)
+    plan = native.Plan(mask, recurrent=True) if H < 1024 else None
+    if plan is None:
+        # the fp32 BELL layout of the legacy kernels may not fit at H=1024; the plan is still valid
+        plan = native.Plan(mask, recurrent=True)
+    cfg = native.TcConfig(plan, cl, nb)
+    assert cfg.cluster_size in (4, 8, 16) and cfg.nb in (16, 32)
+    us = [bf(torch.randn(H, H) * (1.5 / np.sqrt(max(mask.sum(1).mean().item(), 1.0))) * mask).requires_grad_(True)
+          for _ in range(4)]
+    pre = torch.randn(T, B, 4 * H).requires_grad_(True)
+    drop = torch.bernoulli(torch.full((B, H), 0.8))
+    href = lstm_layer_oracle_bf16(us, pre, drop, act)
+    dh = torch.randn(T, B, H)
+    href.backward(dh)
+    d = dev()
+
+    def lay(x):     # gate-major [.., 4H] -> kernel layout
+        if not inter:
+            return x.contiguous()
+        return x.reshape(T, B, 4, H).transpose(2, 3).reshape(T, B, 4 * H).contiguous()
+
+    def unlay(x):
+        if not inter:
+            return x
+        return x.reshape(T, B, H, 4).transpose(2, 3).reshape(T, B, 4 * H)
+
+    ud = [u.detach().to(d) for u in us]
+    fp = torch.empty(cfg.fwd_pack_u32, device=d, dtype=torch.int32)
+    bp = torch.empty(max(cfg.bwd_pack_u32, 1), device=d, dtype=torch.int32)
+    native.lstm_tc_pack(plan, cfg, ud, fp, bp)
+    h = torch.empty(T, B, H, device=d)
+    c = torch.empty(T, B, H, device=d)
+    gates = torch.empty(T, B, 4 * H, device=d)
+    hb = torch.zeros(T * B, ((H + 63) // 64) * 64, device=d, dtype=torch.bfloat16)
+    code = native.ACT_CODES[act]
+    native.lstm_tc_fwd(plan, cfg, fp, lay(pre.detach()).to(d), drop.to(d), 1.0, code, h, c, gates, hb, inter)
+    torch.cuda.synchronize()
+    check(h, href, 2e-5, 1e-2, 'h')
+    assert torch.equal(hb[:, :H].float().cpu(), bf(h.cpu()).view(T * B, H)), 'bf16 copy of h'
+    assert hb[:, H:].abs().max().item() == 0 if hb.shape[1] > H else True
+    dpre = torch.empty(T, B, 4 * H, device=d)
+    dpb = torch.zeros(T * B, 4 * H, device=d, dtype=torch.bfloat16)
+    native.lstm_tc_bwd(plan, cfg, bp, dh.to(d), gates, c, drop.to(d), 1.0, code, dpre, dpb, inter)
+    torch.cuda.synchronize()
+    check(unlay(dpre.cpu()), pre.grad, 1e-4, 3e-2, 'dpre')
+    assert torch.equal(dpb.float().cpu().view(T, B, 4 * H), bf(dpre.cpu())), 'bf16 copy of dpre'
+    # eval variant: scalar drop, nothing saved
+    h2 = torch.empty(T, B, H, device=d)
+    native.lstm_tc_fwd(plan, cfg, fp, lay(pre.detach()).to(d), None, 0.8, code, h2, None, None, None, inter)
+    href2 = lstm_layer_oracle_bf16([u.detach() for u in us], pre.detach(), torch.tensor([0.8]), act)
+    check(h2, href2, 2e-5, 1e-2, 'h eval')
+    plan.destroy()
+
+
+def test_tc_matches_fp32_kernels_on_bf16_exact_inputs():
+    """With weights on the 8-bit grid (bf16-exact, cfg 3) and T=1 (h_0 = 0) the two builds must agree to fp32."""
+    from b200 import native
+    H, B, T = 64, 16, 1
+    mask = random_mask(H, H, [8, 4], [50, 50], 5)
+    plan = native.Plan(mask, recurrent=True)
+    cfg = native.TcConfig(plan)
+    d = dev()
+    torch.manual_seed(1)
+    us = [(torch.randint(-128, 129, (H, H)).float() / 128 * mask).to(d) for _ in range(4)]
+    pre = torch.randn(T, B, 4 * H, device=d)
+    fp = torch.empty(cfg.fwd_pack_u32, device=d, dtype=torch.int32)
+    native.lstm_tc_pack(plan, cfg, us, fp, None)
+    h = torch.empty(T, B, H, device=d)
+    native.lstm_tc_fwd(plan, cfg, fp, pre, None, 1.0, 2, h)
+    fp32 = torch.empty(plan.fwd_pack_floats, device=d)
+    native.lstm_pack(plan, us, fp32, None)
+    h32 = torch.empty(T, B, H, device=d)
+    native.lstm_fwd(plan, fp32, pre, None, 1.0, 2, h32)
+    assert (h - h32).abs().max().item() <= 1e-6
