@@ -141,25 +141,25 @@ int hcgs_lstm_bwd(const hcgs_plan* plan, const float* bwd_pack, const float* dh_
  * the "bf16 train" configurations: U and h_{t-1} are rounded to bf16 for the product, gates, cell
  * state and all saved tensors stay fp32.  A cluster of `cluster_size` CTAs (4, 8 or 16; 0 = the
  * smallest that fits) runs `nb` sequences (16 or 32; 0 = 16) through all T steps.
- * Addressing of the gate tensors is parametric: element (row, gate g, unit u) lives at
- *   base[row*ld + g*gate_stride + u*unit_stride]
- * (gate-major [T*B,4H]: gate_stride = H, unit_stride = 1; gate-interleaved: 1 and 4).
+ * Layout of this build's tensors (ld_h = H rounded up to a multiple of 8, pad columns zero):
+ *   pre / gates / dpre : [T*B, 4*ld_h] fp32, gate-INTERLEAVED: (row, unit u, gate g) at row*4*ld_h + u*4 + g
+ *   c                  : [T*B, ld_h] fp32          hb (bf16 copy of h for the GEMMs): [T*B, ld_h]
+ *   h_out, dh_out      : [T*B, H] fp32 (the reference's [T,B,H] tensors), drop: [B,H]
  * hcgs_lstm_tc_info: info[0]=cluster size [1]=nb [2]=fwd pack uint32s [3]=bwd pack uint32s
  *   [4]=fwd smem bytes [5]=bwd smem bytes [6]=fwd warps [7]=strips/CTA [8]=k-steps [9]=4x4 blocks
- *   [10]=strips/warp [11]=padded hidden size.
- * hcgs_lstm_tc_fwd also writes hb_out (optional): a bf16 copy of h [T*B, hb_ld] for the
- * tensor-core GEMMs; hcgs_lstm_tc_bwd likewise an optional bf16 copy of dpre (row stride ld_bf16). */
+ *   [10]=strips/warp [11]=padded hidden size of the cluster.
+ * In hcgs_lstm_tc_fwd h_out, hb_out, c_out, gates_out are each optional (at least one of h_out /
+ * hb_out); hcgs_lstm_tc_bwd optionally writes a bf16 copy of dpre (same layout) for the GEMMs. */
 int hcgs_lstm_tc_info(const hcgs_plan* plan, int cluster_size, int nb, int64_t* info);
 int hcgs_lstm_tc_pack(const hcgs_plan* plan, int cluster_size, const float* const* u, int ldu,
                       uint32_t* fwd_pack, uint32_t* bwd_pack, hcgs_stream stream);
 int hcgs_lstm_tc_fwd(const hcgs_plan* plan, int cluster_size, int nb, const uint32_t* fwd_pack,
-                     const float* pre, int64_t ld, int gate_stride, int unit_stride, const float* drop,
-                     float drop_scalar, int act, int t_len, int batch, float* h_out, void* hb_out,
-                     int hb_ld, float* c_out, float* gates_out, hcgs_stream stream);
+                     const float* pre, int ld_h, const float* drop, float drop_scalar, int act,
+                     int t_len, int batch, float* h_out, void* hb_out, float* c_out, float* gates_out,
+                     hcgs_stream stream);
 int hcgs_lstm_tc_bwd(const hcgs_plan* plan, int cluster_size, int nb, const uint32_t* bwd_pack,
-                     const float* dh_out, const float* gates, int64_t ld, int gate_stride,
-                     int unit_stride, const float* c, const float* drop, float drop_scalar, int act,
-                     int t_len, int batch, float* dpre, void* dpre_bf16, int64_t ld_bf16,
+                     const float* dh_out, const float* gates, const float* c, int ld_h, const float* drop,
+                     float drop_scalar, int act, int t_len, int batch, float* dpre, void* dpre_bf16,
                      hcgs_stream stream);
 
 /* ---- MLP pointwise pieces ------------------------------------------------------------------

@@ -52,10 +52,10 @@ SIGNATURES = {
     'hcgs_lstm_bwd': (c_int, [c_void_p, _f, _f, _f, _f, _f, c_float, c_int, c_int, c_int, _f, c_void_p]),
     'hcgs_lstm_tc_info': (c_int, [c_void_p, c_int, c_int, POINTER(c_int64)]),
     'hcgs_lstm_tc_pack': (c_int, [c_void_p, c_int, _pp, c_int, _f, _f, c_void_p]),
-    'hcgs_lstm_tc_fwd': (c_int, [c_void_p, c_int, c_int, _f, _f, c_int64, c_int, c_int, _f, c_float, c_int, c_int,
-                                 c_int, _f, _f, c_int, _f, _f, c_void_p]),
-    'hcgs_lstm_tc_bwd': (c_int, [c_void_p, c_int, c_int, _f, _f, _f, c_int64, c_int, c_int, _f, _f, c_float, c_int,
-                                 c_int, c_int, _f, _f, c_int64, c_void_p]),
+    'hcgs_lstm_tc_fwd': (c_int, [c_void_p, c_int, c_int, _f, _f, c_int, _f, c_float, c_int, c_int, c_int, _f, _f, _f,
+                                 _f, c_void_p]),
+    'hcgs_lstm_tc_bwd': (c_int, [c_void_p, c_int, c_int, _f, _f, _f, _f, c_int, _f, c_float, c_int, c_int, c_int, _f,
+                                 _f, c_void_p]),
     'hcgs_act_fwd': (c_int, [_f, _f, _f, c_int64, c_int, c_void_p]),
     'hcgs_act_bwd': (c_int, [_f, _f, _f, _f, c_int64, c_int, c_void_p]),
     'hcgs_logsoftmax_fwd': (c_int, [_f, c_int, _f, c_int, c_int64, c_int, _f, c_void_p]),
@@ -317,6 +317,7 @@ class TcConfig:
         self.smem_fwd, self.smem_bwd = int(info[4]), int(info[5])
         self.warps, self.strips_per_cta, self.k_steps = int(info[6]), int(info[7]), int(info[8])
         self.n_blocks, self.strips_per_warp, self.padded_hidden = int(info[9]), int(info[10]), int(info[11])
+        self.max_clusters_fwd, self.max_clusters_bwd = int(info[12]), int(info[13])
 
 
 def lstm_tc_pack(plan, cfg, us, fwd_pack=None, bwd_pack=None):
@@ -328,33 +329,38 @@ def lstm_tc_pack(plan, cfg, us, fwd_pack=None, bwd_pack=None):
                                     _ptr(fwd_pack), _ptr(bwd_pack), _stream()), 'hcgs_lstm_tc_pack')
 
 
-def lstm_tc_fwd(plan, cfg, fwd_pack, pre, drop, drop_scalar, act, h_out, c_out=None, gates_out=None, hb_out=None,
-                interleaved=False):
-    """pre / gates_out: [T, B, 4H] fp32, gate-major (column g*H+u) or gate-interleaved (column u*4+g)."""
+def pad8(n):
+    return (n + 7) // 8 * 8
+
+
+def lstm_tc_fwd(plan, cfg, fwd_pack, pre, drop, drop_scalar, act, T, B, h_out=None, hb_out=None, c_out=None,
+                gates_out=None):
+    """pre / gates_out: [T*B, 4*ldH] fp32 gate-interleaved (column u*4+g), ldH = pad8(H);
+    c_out [T*B, ldH] fp32, hb_out [T*B, ldH] bf16, h_out [T*B, H] fp32 (all optional but one of h/hb)."""
     _require_cuda(pre, drop, h_out, c_out, gates_out)
     _require_cuda_any(fwd_pack, hb_out)
-    T, B = pre.shape[0], pre.shape[1]
     H = plan.n_out
-    assert pre.is_contiguous() and h_out.is_contiguous() and pre.shape[2] == 4 * H
-    gs, us_ = (1, 4) if interleaved else (H, 1)
-    hb_ld = 0 if hb_out is None else hb_out.stride(0)
-    _check(load().hcgs_lstm_tc_fwd(plan.handle, cfg.cluster_size, cfg.nb, _ptr(fwd_pack), _ptr(pre), 4 * H, gs, us_,
-                                   _ptr(drop), float(drop_scalar), int(act), T, B, _ptr(h_out), _ptr(hb_out), hb_ld,
-                                   _ptr(c_out), _ptr(gates_out), _stream()), 'hcgs_lstm_tc_fwd')
+    ldH = pre.shape[-1] // 4
+    assert pre.is_contiguous() and pre.numel() == T * B * 4 * ldH and ldH % 8 == 0 and ldH >= H
+    for t, n in ((h_out, H), (hb_out, ldH), (c_out, ldH), (gates_out, 4 * ldH)):
+        assert t is None or (t.is_contiguous() and t.numel() == T * B * n)
+    _check(load().hcgs_lstm_tc_fwd(plan.handle, cfg.cluster_size, cfg.nb, _ptr(fwd_pack), _ptr(pre), ldH, _ptr(drop),
+                                   float(drop_scalar), int(act), T, B, _ptr(h_out), _ptr(hb_out), _ptr(c_out),
+                                   _ptr(gates_out), _stream()), 'hcgs_lstm_tc_fwd')
 
 
-def lstm_tc_bwd(plan, cfg, bwd_pack, dh_out, gates, c, drop, drop_scalar, act, dpre, dpre_bf16=None,
-                interleaved=False):
+def lstm_tc_bwd(plan, cfg, bwd_pack, dh_out, gates, c, drop, drop_scalar, act, T, B, dpre, dpre_bf16=None):
+    """gates / dpre / dpre_bf16: [T*B, 4*ldH] gate-interleaved; c [T*B, ldH]; dh_out [T*B, H]."""
     _require_cuda(dh_out, gates, c, drop, dpre)
     _require_cuda_any(bwd_pack, dpre_bf16)
-    T, B = dh_out.shape[0], dh_out.shape[1]
     H = plan.n_out
+    ldH = gates.shape[-1] // 4
     assert dh_out.is_contiguous() and gates.is_contiguous() and c.is_contiguous() and dpre.is_contiguous()
-    gs, us_ = (1, 4) if interleaved else (H, 1)
-    ldb = 0 if dpre_bf16 is None else dpre_bf16.stride(0)
+    assert dh_out.numel() == T * B * H and gates.numel() == T * B * 4 * ldH and c.numel() == T * B * ldH
+    assert dpre.numel() == gates.numel() and (dpre_bf16 is None or dpre_bf16.numel() == gates.numel())
     _check(load().hcgs_lstm_tc_bwd(plan.handle, cfg.cluster_size, cfg.nb, _ptr(bwd_pack), _ptr(dh_out), _ptr(gates),
-                                   4 * H, gs, us_, _ptr(c), _ptr(drop), float(drop_scalar), int(act), T, B,
-                                   _ptr(dpre), _ptr(dpre_bf16), ldb, _stream()), 'hcgs_lstm_tc_bwd')
+                                   _ptr(c), ldH, _ptr(drop), float(drop_scalar), int(act), T, B, _ptr(dpre),
+                                   _ptr(dpre_bf16), _stream()), 'hcgs_lstm_tc_bwd')
 
 
 def act_fwd(x, y, drop_mask, act):

@@ -164,9 +164,9 @@ __host__ __device__ static inline size_t tc_align16(size_t x) { return (x + 15) 
 static size_t tc_fwd_smem(const TcPlan& t, int NB) {
     size_t b = 0;
     b += tc_align16((size_t)t.SPC * t.KS * 2 * 32 * 8);               // B fragments
-    b += tc_align16((size_t)t.SPC * t.KS * 4 * 2);                    // column groups
-    b += tc_align16((size_t)t.SPC);                                   // k-steps per strip
     b += tc_align16((size_t)2 * NB * (t.HP + TC_HPAD) * 2);           // h double buffer (bf16)
+    b += tc_align16((size_t)2 * NB * (t.Hc * 4 + 16) * 4);            // pre-activation / gate stages (TC_NSTG)
+    b += 2 * tc_align16((size_t)NB * (t.Hc + 4) * 4);                 // c and h output stages
     b += 64;                                                          // mbarriers
     return b;
 }
@@ -246,47 +246,80 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 }
 
 // ---- forward -----------------------------------------------------------------------------------
+// Fast transcendental forms for the bf16 build (MUFU.EX2 / MUFU.RCP; abs. error ~1e-6, far below
+// the bf16 operand rounding): the libm tanhf/expf of the fp32 parity kernels cost ~200 issue slots
+// per (unit, sequence) item and were the largest share of a step.
+__device__ __forceinline__ float fast_sigmoid(float x) { return __fdividef(1.f, 1.f + __expf(-x)); }
+__device__ __forceinline__ float fast_tanh(float x) { return 1.f - __fdividef(2.f, 1.f + __expf(2.f * x)); }
+__device__ __forceinline__ float act_apply_fast(int act, float x) {
+    if (act == HCGS_ACT_TANH) return fast_tanh(x);
+    if (act == HCGS_ACT_SIGMOID) return fast_sigmoid(x);
+    return act_apply(act, x);
+}
+
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+constexpr int TC_NSTG = 2;  // shared-memory stages of the pre-activation stream (refilled right after B1)
+
 struct TcFwdArgs {
     const uint2* wfrag;   // [CL][SPC][KS][2][32]
     const uint16_t* cg;   // [CL][SPC][KS*4]
     const uint8_t* nks;   // [CL][SPC]
-    const float* pre;     // element (row, g, u) at pre[row*ld + g*gs + u*us]
-    int64_t ld;
-    int gs, us;
+    const float* pre;     // [T*B][4*ldH] gate-interleaved: (row, u, g) at pre[row*4*ldH + u*4 + g]
     const float* drop;    // [B,H] or NULL
     float drop_scalar;
-    float* h_out;         // [T,B,H] fp32
-    __nv_bfloat16* hb_out;  // [T*B, hb_ld] bf16 copy for the tensor-core GEMMs, or NULL
-    int hb_ld;
-    float* c_out;         // [T,B,H] or NULL
-    float* gates_out;     // same addressing as pre, or NULL
-    int T, B, H, CL, SPC, SPW, KS, HP, act;
-    int dbg;  // timing experiments only (HCGS_TC_DEBUG): 1 = no global stores, 2 = no prefetch loads, 4 = no MMA
+    float* h_out;           // [T*B][H] fp32 or NULL
+    __nv_bfloat16* hb_out;  // [T*B][ldH] bf16 copy for the tensor-core GEMMs, or NULL
+    float* c_out;           // [T*B][ldH] or NULL
+    float* gates_out;       // [T*B][4*ldH] gate-interleaved, or NULL
+    int T, B, H, ldH, CL, SPC, KS, HP, act;
+    int dbg;  // timing experiments only (HCGS_TC_DEBUG): 1 = no global stores, 2 = no prefetch, 4 = no MMA
 };
 
-// SPW = strips per warp (compile time so that the per-item state lives in registers)
-template <int NT, int SPW>
+// NT m16 tiles of sequences per cluster, SPW strips per warp, KSM >= k-steps per strip (compile time
+// so that the gather offsets and the per-item state live in registers).
+template <int ACT>
+__device__ __forceinline__ float act_fwd_t(int act, float x) {
+    if (ACT == HCGS_ACT_TANH) return fast_tanh(x);
+    return act_apply_fast(act, x);
+}
+
+// ACT = HCGS_ACT_TANH compiles the (default) tanh cell without the activation switch; -1 = generic
+template <int NT, int SPW, int KSM, int ACT>
 __global__ void __launch_bounds__(TC_MAX_WARPS * 32, 1) lstm_tc_fwd_kernel(const TcFwdArgs a) {
     constexpr int NB = NT * 16;
     cg::cluster_group cluster = cg::this_cluster();
     const int rank = (int)cluster.block_rank();
-    const int CL = a.CL, SPC = a.SPC, KS = a.KS, H = a.H;
+    const int CL = a.CL, SPC = a.SPC, KS = a.KS, H = a.H, ldH = a.ldH;
     const int b0 = (blockIdx.x / CL) * NB;
     const int Hc = SPC * 4;
     const int u0 = rank * Hc;
+    const int nv = max(0, min(Hc, ldH - u0));  // units of this CTA inside the padded tensors (multiple of 8)
+    const int nh = max(0, min(Hc, H - u0));    // real units
     const int HPs = a.HP + TC_HPAD;
+    const int PRS = Hc * 4 + 16;  // floats per staged row: 64 B of padding keep float4 reads conflict free
+    const int CS = Hc + 4;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nthreads = blockDim.x;
 
     extern __shared__ __align__(16) unsigned char smem_raw[];
     unsigned char* sp = smem_raw;
     uint2* wf_s = reinterpret_cast<uint2*>(sp);
     sp += tc_align16((size_t)SPC * KS * 2 * 32 * 8);
-    uint16_t* cg_s = reinterpret_cast<uint16_t*>(sp);
-    sp += tc_align16((size_t)SPC * KS * 4 * 2);
-    uint8_t* nks_s = sp;
-    sp += tc_align16((size_t)SPC);
     __nv_bfloat16* hbuf = reinterpret_cast<__nv_bfloat16*>(sp);
     sp += tc_align16((size_t)2 * NB * HPs * 2);
+    float* pre_s = reinterpret_cast<float*>(sp);
+    sp += tc_align16((size_t)TC_NSTG * NB * PRS * 4);
+    float* c_s = reinterpret_cast<float*>(sp);
+    sp += tc_align16((size_t)NB * CS * 4);
+    float* h_s = reinterpret_cast<float*>(sp);
+    sp += tc_align16((size_t)NB * CS * 4);
     uint64_t* mbar = reinterpret_cast<uint64_t*>(sp);
 
     // ---- one-time loads ------------------------------------------------------------------------
@@ -294,30 +327,52 @@ __global__ void __launch_bounds__(TC_MAX_WARPS * 32, 1) lstm_tc_fwd_kernel(const
         const uint4* s4 = reinterpret_cast<const uint4*>(a.wfrag + (size_t)rank * SPC * KS * 64);
         uint4* d4 = reinterpret_cast<uint4*>(wf_s);
         for (int i = tid; i < SPC * KS * 32; i += nthreads) d4[i] = __ldg(s4 + i);
-        for (int i = tid; i < SPC * KS * 4; i += nthreads) {
-            const uint16_t c = a.cg[(size_t)rank * SPC * KS * 4 + i];
-            cg_s[i] = (c == 0xFFFF) ? (uint16_t)0 : c;  // padded blocks carry zero weights
-        }
-        for (int i = tid; i < SPC; i += nthreads) nks_s[i] = a.nks[(size_t)rank * SPC + i];
         uint32_t* hz = reinterpret_cast<uint32_t*>(hbuf);
         for (int i = tid; i < NB * HPs; i += nthreads) hz[i] = 0u;  // both buffers (2*NB*HPs bf16)
+        for (int i = tid; i < NB * CS; i += nthreads) c_s[i] = h_s[i] = 0.f;
         if (tid == 0) {
-            mbar_init(smem_u32(&mbar[0]), (uint32_t)(CL * (nthreads >> 5)));
-            mbar_init(smem_u32(&mbar[1]), (uint32_t)(CL * (nthreads >> 5)));
+            mbar_init(smem_u32(&mbar[0]), (uint32_t)CL);
+            mbar_init(smem_u32(&mbar[1]), (uint32_t)CL);
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         }
     }
-    __syncthreads();
-    cluster.sync();
 
-    // ---- per-thread items: strip i of this warp, m16 tile nt, row half hh ----------------------
+    // staged, coalesced stream of the pre-activations: 16-byte cp.async chunks, one commit per step
+    const int pchunks = NB * nv;  // one chunk = the four gates of one (sequence, unit) item
+    const int nwarps = nthreads >> 5;
+    auto issue_pre = [&](int step) {
+        if (step < a.T && !(a.dbg & 2)) {
+            float* dst = pre_s + (size_t)(step % TC_NSTG) * NB * PRS;
+            for (int b = warp; b < NB; b += nwarps) {  // one warp per staged row: no index division
+                if (b0 + b >= a.B) continue;
+                const float* src = a.pre + ((size_t)step * a.B + b0 + b) * 4 * ldH + (size_t)u0 * 4;
+                for (int q = lane; q < nv; q += 32) cp_async16(dst + (size_t)b * PRS + q * 4, src + q * 4);
+            }
+        }
+        cp_async_commit();
+    };
+    issue_pre(0);
+
+    // ---- per-thread constants: gather offsets of this warp's strips, item state ----------------
     const int ui = lane & 3;   // unit inside the strip
     const int br = lane >> 2;  // batch row inside the m16 tile (and +8)
-    float c_reg[SPW][NT][2], dr[SPW][NT][2], pf[SPW][NT][2][4];
+    int off0[SPW][KSM], off2[SPW][KSM], nk[SPW];
+    float c_reg[SPW][NT][2], dr[SPW][NT][2];
     bool ok[SPW][NT][2];
 #pragma unroll
     for (int i = 0; i < SPW; ++i) {
         const int sl = warp * SPW + i;
+        nk[i] = (sl < SPC && !(a.dbg & 4)) ? a.nks[(size_t)rank * SPC + sl] : 0;
+#pragma unroll
+        for (int ks = 0; ks < KSM; ++ks) {
+            off0[i][ks] = off2[i][ks] = 0;
+            if (sl < SPC && ks < KS) {
+                const uint16_t* cgp = a.cg + ((size_t)(rank * SPC + sl) * KS + ks) * 4 + (ui >> 1);
+                const uint16_t c0 = cgp[0], c2 = cgp[2];
+                off0[i][ks] = (c0 == 0xFFFF ? 0 : c0 * 4) + (lane & 1) * 2;  // padded blocks carry zero weights
+                off2[i][ks] = (c2 == 0xFFFF ? 0 : c2 * 4) + (lane & 1) * 2;
+            }
+        }
         const int u = u0 + sl * 4 + ui;
 #pragma unroll
         for (int nt = 0; nt < NT; ++nt)
@@ -328,132 +383,126 @@ __global__ void __launch_bounds__(TC_MAX_WARPS * 32, 1) lstm_tc_fwd_kernel(const
                 c_reg[i][nt][hh] = 0.f;
                 dr[i][nt][hh] = a.drop_scalar;
                 if (ok[i][nt][hh] && a.drop) dr[i][nt][hh] = __ldg(a.drop + (size_t)b * H + u);
-#pragma unroll
-                for (int g = 0; g < 4; ++g) pf[i][nt][hh][g] = 0.f;
-                if (ok[i][nt][hh] && a.T > 0) {
-                    const float* p = a.pre + (size_t)b * a.ld + (size_t)u * a.us;
-#pragma unroll
-                    for (int g = 0; g < 4; ++g) pf[i][nt][hh][g] = __ldg(p + (size_t)g * a.gs);
-                }
             }
     }
-    const int chunks = Hc / 8;  // 16-byte chunks of one bf16 slice row
+    __syncthreads();
+    cluster.sync();
+
     const uint32_t hbuf_addr = smem_u32(hbuf);
     const uint32_t mbar_addr = smem_u32(mbar);
+    const int hchunks = Hc / 8;  // 16-byte chunks of one bf16 slice row
 
     for (int k = 0; k < a.T; ++k) {
         const int cur = k & 1, nxt = cur ^ 1;
-        if (k > 0) mbar_wait(mbar_addr + cur * 8, (uint32_t)(((k - 1) >> 1) & 1));
         const __nv_bfloat16* hc = hbuf + (size_t)cur * NB * HPs;
         __nv_bfloat16* hn = hbuf + (size_t)nxt * NB * HPs;
-        float o_h[SPW][NT][2], o_c[SPW][NT][2], o_g[SPW][NT][2][4];
+        float* stage = pre_s + (size_t)(k % TC_NSTG) * NB * PRS;
+        cp_async_wait<0>();  // this thread's chunks of step k have landed
+        if (k > 0) mbar_wait(mbar_addr + cur * 8, (uint32_t)(((k - 1) >> 1) & 1));
+        // ---- U h_{k-1}: gather A fragments from the h buffer, B fragments resident ---------------
+        float acc[SPW][2][NT][4];
 #pragma unroll
         for (int i = 0; i < SPW; ++i) {
-            const int sl = warp * SPW + i;
-            if (sl >= SPC) continue;  // warp-uniform
-            float acc[2][NT][4];
 #pragma unroll
             for (int gp = 0; gp < 2; ++gp)
 #pragma unroll
                 for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
-                    for (int q = 0; q < 4; ++q) acc[gp][nt][q] = 0.f;
-            const int nk = (a.dbg & 4) ? 0 : nks_s[sl];
-            for (int ks = 0; ks < nk; ++ks) {
-                const uint2 bA = wf_s[((size_t)(sl * KS + ks) * 2 + 0) * 32 + lane];
-                const uint2 bB = wf_s[((size_t)(sl * KS + ks) * 2 + 1) * 32 + lane];
-                const uint16_t* cgp = cg_s + (sl * KS + ks) * 4 + (ui >> 1);
-                const int c0 = cgp[0] * 4 + (lane & 1) * 2, c2 = cgp[2] * 4 + (lane & 1) * 2;
+                    for (int q = 0; q < 4; ++q) acc[i][gp][nt][q] = 0.f;
+            const int sl = warp * SPW + i;
 #pragma unroll
-                for (int nt = 0; nt < NT; ++nt) {
-                    const __nv_bfloat16* row = hc + (size_t)(nt * 16 + br) * HPs;
-                    const uint32_t a0 = *reinterpret_cast<const uint32_t*>(row + c0);
-                    const uint32_t a1 = *reinterpret_cast<const uint32_t*>(row + 8 * HPs + c0);
-                    const uint32_t a2 = *reinterpret_cast<const uint32_t*>(row + c2);
-                    const uint32_t a3 = *reinterpret_cast<const uint32_t*>(row + 8 * HPs + c2);
-                    mma_bf16_16816(acc[0][nt], a0, a1, a2, a3, bA.x, bA.y);
-                    mma_bf16_16816(acc[1][nt], a0, a1, a2, a3, bB.x, bB.y);
+            for (int ks = 0; ks < KSM; ++ks) {
+                if (ks < nk[i]) {  // warp-uniform
+                    const uint2 bA = wf_s[((size_t)(sl * KS + ks) * 2 + 0) * 32 + lane];
+                    const uint2 bB = wf_s[((size_t)(sl * KS + ks) * 2 + 1) * 32 + lane];
+#pragma unroll
+                    for (int nt = 0; nt < NT; ++nt) {
+                        const __nv_bfloat16* row = hc + (size_t)(nt * 16 + br) * HPs;
+                        const uint32_t a0 = *reinterpret_cast<const uint32_t*>(row + off0[i][ks]);
+                        const uint32_t a1 = *reinterpret_cast<const uint32_t*>(row + 8 * HPs + off0[i][ks]);
+                        const uint32_t a2 = *reinterpret_cast<const uint32_t*>(row + off2[i][ks]);
+                        const uint32_t a3 = *reinterpret_cast<const uint32_t*>(row + 8 * HPs + off2[i][ks]);
+                        mma_bf16_16816(acc[i][0][nt], a0, a1, a2, a3, bA.x, bA.y);
+                        mma_bf16_16816(acc[i][1][nt], a0, a1, a2, a3, bB.x, bB.y);
+                    }
                 }
             }
-            // fused gates / cell / hidden for this thread's items of the strip
+        }
+        __syncthreads();  // B1: every thread's cp.async chunks of step k are visible
+        issue_pre(k + 1);  // the other stage was drained (stored out) before anybody reached B1
+        // ---- fused gates / cell / hidden; gates overwrite the staged pre-activations in place ---
+#pragma unroll
+        for (int i = 0; i < SPW; ++i) {
+            const int sl = warp * SPW + i;
+            if (sl >= SPC) continue;  // warp-uniform
             const int ul = sl * 4 + ui;
 #pragma unroll
             for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
                 for (int hh = 0; hh < 2; ++hh) {
+                    const int bl = nt * 16 + br + 8 * hh;
                     float hval = 0.f;
                     if (ok[i][nt][hh]) {
-                        const float zf = acc[0][nt][hh * 2 + 0] + pf[i][nt][hh][0];
-                        const float zi = acc[0][nt][hh * 2 + 1] + pf[i][nt][hh][1];
-                        const float zo = acc[1][nt][hh * 2 + 0] + pf[i][nt][hh][2];
-                        const float zc = acc[1][nt][hh * 2 + 1] + pf[i][nt][hh][3];
-                        const float fg = sigmoidf_(zf), ig = sigmoidf_(zi), og = sigmoidf_(zo);
-                        const float gg = act_apply(a.act, zc);
+                        float4* pz = reinterpret_cast<float4*>(stage + (size_t)bl * PRS + ul * 4);
+                        const float4 p = *pz;
+                        const float zf = acc[i][0][nt][hh * 2 + 0] + p.x;
+                        const float zi = acc[i][0][nt][hh * 2 + 1] + p.y;
+                        const float zo = acc[i][1][nt][hh * 2 + 0] + p.z;
+                        const float zc = acc[i][1][nt][hh * 2 + 1] + p.w;
+                        const float fg = fast_sigmoid(zf), ig = fast_sigmoid(zi), og = fast_sigmoid(zo);
+                        const float gg = act_fwd_t<ACT>(a.act, zc);
                         const float cn = ig * gg * dr[i][nt][hh] + fg * c_reg[i][nt][hh];
                         c_reg[i][nt][hh] = cn;
-                        hval = og * act_apply(a.act, cn);
-                        o_c[i][nt][hh] = cn;
-                        o_g[i][nt][hh][0] = fg;
-                        o_g[i][nt][hh][1] = ig;
-                        o_g[i][nt][hh][2] = og;
-                        o_g[i][nt][hh][3] = gg;
+                        hval = og * act_fwd_t<ACT>(a.act, cn);
+                        *pz = make_float4(fg, ig, og, gg);
+                        c_s[bl * CS + ul] = cn;
+                        h_s[bl * CS + ul] = hval;
                     }
-                    o_h[i][nt][hh] = hval;
-                    hn[(size_t)(nt * 16 + br + 8 * hh) * HPs + u0 + ul] = __float2bfloat16_rn(hval);
+                    hn[(size_t)bl * HPs + u0 + ul] = __float2bfloat16_rn(hval);
                 }
         }
+        __syncthreads();  // B2: this CTA's slice of h_k (and the output stages) are complete
         if (k + 1 < a.T) {
-            __syncthreads();  // this CTA's slice of h_k is complete in the local buffer
             // push the slice into every peer (coalesced 16-byte DSMEM stores)
-            for (int idx = tid; idx < NB * chunks; idx += nthreads) {
-                const int b = idx / chunks, q = idx - b * chunks;
-                const uint32_t off = (uint32_t)(((size_t)nxt * NB * HPs + (size_t)b * HPs + u0 + q * 8) * 2);
-                const uint4 v = *reinterpret_cast<const uint4*>(reinterpret_cast<const unsigned char*>(hbuf) + off);
-                for (int d = 1; d < CL; ++d) st_cluster_v4(mapa_u32(hbuf_addr + off, (uint32_t)((rank + d) % CL)), v);
-            }
-            __syncwarp();
-            if (lane == 0) {
-                if (a.dbg & 8) {
-                    for (int d = 0; d < CL; ++d)
-                        mbar_arrive_cluster(mapa_u32(mbar_addr + nxt * 8, (uint32_t)((rank + d) % CL)));
-                } else {
-                    fence_release_cluster();
-                    for (int d = 0; d < CL; ++d)
-                        mbar_arrive_cluster_relaxed(mapa_u32(mbar_addr + nxt * 8, (uint32_t)((rank + d) % CL)));
+            for (int b = warp; b < NB; b += nwarps)
+                for (int q = lane; q < hchunks; q += 32) {
+                    const uint32_t off = (uint32_t)(((size_t)nxt * NB * HPs + (size_t)b * HPs + u0 + q * 8) * 2);
+                    const uint4 v =
+                        *reinterpret_cast<const uint4*>(reinterpret_cast<const unsigned char*>(hbuf) + off);
+                    for (int d = 1; d < CL; ++d)
+                        st_cluster_v4(mapa_u32(hbuf_addr + off, (uint32_t)((rank + d) % CL)), v);
                 }
+            __syncthreads();  // B3: all pushes of this CTA are issued
+            if (tid < CL) {   // one arrival per (source CTA, destination CTA)
+                fence_release_cluster();
+                mbar_arrive_cluster_relaxed(mapa_u32(mbar_addr + nxt * 8, (uint32_t)((rank + tid) % CL)));
             }
         }
-        // ---- global stores of step k (after the signal: the release never waits for them) and the
-        //      prefetch of step k+1's pre-activations ---------------------------------------------
-#pragma unroll
-        for (int i = 0; i < SPW; ++i) {
-            const int sl = warp * SPW + i;
-            const int u = u0 + sl * 4 + ui;
-#pragma unroll
-            for (int nt = 0; nt < NT; ++nt)
-#pragma unroll
-                for (int hh = 0; hh < 2; ++hh) {
-                    if (!ok[i][nt][hh]) continue;
-                    const int b = b0 + nt * 16 + br + 8 * hh;
-                    const size_t row = (size_t)k * a.B + b;
-                    if (!(a.dbg & 1)) {
-                        a.h_out[row * H + u] = o_h[i][nt][hh];
-                        if (a.hb_out) a.hb_out[row * a.hb_ld + u] = __float2bfloat16_rn(o_h[i][nt][hh]);
-                        if (a.c_out) a.c_out[row * H + u] = o_c[i][nt][hh];
-                        if (a.gates_out) {
-                            float* gp = a.gates_out + row * a.ld + (size_t)u * a.us;
-#pragma unroll
-                            for (int g = 0; g < 4; ++g) gp[(size_t)g * a.gs] = o_g[i][nt][hh][g];
-                        }
-                    }
-                    if (k + 1 < a.T && !(a.dbg & 2)) {
-                        const float* p = a.pre + (row + a.B) * a.ld + (size_t)u * a.us;
-#pragma unroll
-                        for (int g = 0; g < 4; ++g) pf[i][nt][hh][g] = __ldg(p + (size_t)g * a.gs);
-                    }
+        // ---- coalesced global stores of step k (after the signal) and the prefetch of step k+2 --
+        if (!(a.dbg & 1)) {
+            const size_t row0 = (size_t)k * a.B + b0;
+            for (int b = warp; b < NB; b += nwarps) {
+                if (b0 + b >= a.B) continue;
+                if (a.gates_out) {
+                    float* dst = a.gates_out + (row0 + b) * 4 * ldH + (size_t)u0 * 4;
+                    for (int q = lane; q < nv; q += 32)
+                        *reinterpret_cast<float4*>(dst + q * 4) =
+                            *reinterpret_cast<const float4*>(stage + (size_t)b * PRS + q * 4);
                 }
+                if (a.c_out)
+                    for (int q = lane; q < nv / 4; q += 32)
+                        *reinterpret_cast<float4*>(a.c_out + (row0 + b) * ldH + u0 + q * 4) =
+                            *reinterpret_cast<const float4*>(c_s + b * CS + q * 4);
+                if (a.hb_out)
+                    for (int q = lane; q < nv / 8; q += 32)
+                        *reinterpret_cast<uint4*>(a.hb_out + (row0 + b) * ldH + u0 + q * 8) =
+                            *reinterpret_cast<const uint4*>(hn + (size_t)b * HPs + u0 + q * 8);
+                if (a.h_out)
+                    for (int q = lane; q < nh; q += 32) a.h_out[(row0 + b) * H + u0 + q] = h_s[b * CS + q];
+            }
         }
     }
+    cp_async_wait<0>();
     cluster.sync();  // nobody exits while peers may still write into its shared memory
 }
 
@@ -463,17 +512,14 @@ struct TcBwdArgs {
     const int* blk_off;      // [CL+1]
     const int* cs_ptr;       // [CL][NS+1]
     const uint16_t* blk_rs;  // [n_blocks]
-    const float* dh_out;     // [T,B,H]
-    const float* gates;      // element (row, g, u) at gates[row*ld + g*gs + u*us]
-    int64_t ld;
-    int gs, us;
-    const float* c;          // [T,B,H]
+    const float* dh_out;     // [T*B][H]
+    const float* gates;      // [T*B][4*ldH] gate-interleaved
+    const float* c;          // [T*B][ldH]
     const float* drop;
     float drop_scalar;
-    float* dpre;             // fp32, same addressing as gates
-    __nv_bfloat16* dpreb;    // optional bf16 copy, same addressing with row stride ldb
-    int64_t ldb;
-    int T, B, H, CL, SPC, NS, HP, max_blocks, act;
+    float* dpre;             // [T*B][4*ldH] gate-interleaved fp32
+    __nv_bfloat16* dpreb;    // optional bf16 copy, same layout
+    int T, B, H, ldH, CL, SPC, NS, HP, max_blocks, act;
 };
 
 template <int NT, int IT>
@@ -481,7 +527,7 @@ __global__ void __launch_bounds__(512, 1) lstm_tc_bwd_kernel(const TcBwdArgs a) 
     constexpr int NB = NT * 16;
     cg::cluster_group cluster = cg::this_cluster();
     const int rank = (int)cluster.block_rank();
-    const int CL = a.CL, SPC = a.SPC, NS = a.NS, H = a.H;
+    const int CL = a.CL, SPC = a.SPC, NS = a.NS, H = a.H, ldH = a.ldH;
     const int b0 = (blockIdx.x / CL) * NB;
     const int Hc = SPC * 4;
     const int u0 = rank * Hc;
@@ -517,19 +563,20 @@ __global__ void __launch_bounds__(512, 1) lstm_tc_bwd_kernel(const TcBwdArgs a) 
         uint32_t* dz = reinterpret_cast<uint32_t*>(dpre_s);
         for (int i = tid; i < NB * DPS / 2; i += nthreads) dz[i] = 0u;
         if (tid == 0) {
-            mbar_init(smem_u32(&mbar[0]), (uint32_t)(CL * nwarps));
-            mbar_init(smem_u32(&mbar[1]), (uint32_t)(CL * nwarps));
+            mbar_init(smem_u32(&mbar[0]), (uint32_t)CL);
+            mbar_init(smem_u32(&mbar[1]), (uint32_t)CL);
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         }
     }
     __syncthreads();
     cluster.sync();
 
-    // ---- pointwise items (unit fastest => coalesced global traffic) ----------------------------
+    // ---- pointwise items (unit fastest => coalesced 16-byte global traffic) --------------------
     int it_b[IT], it_ul[IT];
     bool it_in[IT], it_ok[IT];
     float dc_carry[IT], dr[IT];
-    float p_g[IT][4], p_c[IT], p_cm1[IT], p_dh[IT];
+    float4 p_g[IT];
+    float p_c[IT], p_cm1[IT], p_dh[IT];
 #pragma unroll
     for (int j = 0; j < IT; ++j) {
         const int idx = tid + j * nthreads;
@@ -540,18 +587,15 @@ __global__ void __launch_bounds__(512, 1) lstm_tc_bwd_kernel(const TcBwdArgs a) 
         dc_carry[j] = 0.f;
         dr[j] = a.drop_scalar;
         p_c[j] = p_cm1[j] = p_dh[j] = 0.f;
-#pragma unroll
-        for (int g = 0; g < 4; ++g) p_g[j][g] = 0.f;
+        p_g[j] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (it_ok[j]) {
             const int u = u0 + it_ul[j];
             if (a.drop) dr[j] = __ldg(a.drop + (size_t)(b0 + it_b[j]) * H + u);
             if (a.T > 0) {
                 const size_t row = (size_t)(a.T - 1) * a.B + b0 + it_b[j];
-                const float* gp = a.gates + row * a.ld + (size_t)u * a.us;
-#pragma unroll
-                for (int g = 0; g < 4; ++g) p_g[j][g] = __ldg(gp + (size_t)g * a.gs);
-                p_c[j] = __ldg(a.c + row * H + u);
-                p_cm1[j] = (a.T > 1) ? __ldg(a.c + (row - a.B) * H + u) : 0.f;
+                p_g[j] = __ldg(reinterpret_cast<const float4*>(a.gates + row * 4 * ldH + (size_t)u * 4));
+                p_c[j] = __ldg(a.c + row * ldH + u);
+                p_cm1[j] = (a.T > 1) ? __ldg(a.c + (row - a.B) * ldH + u) : 0.f;
                 p_dh[j] = __ldg(a.dh_out + row * H + u);
             }
         }
@@ -569,48 +613,48 @@ __global__ void __launch_bounds__(512, 1) lstm_tc_bwd_kernel(const TcBwdArgs a) 
         for (int j = 0; j < IT; ++j) {
             if (!it_in[j]) continue;
             const int b = it_b[j], ul = it_ul[j];
-            float dp[4] = {0.f, 0.f, 0.f, 0.f};
+            float4 dp = make_float4(0.f, 0.f, 0.f, 0.f);
             if (it_ok[j]) {
                 float dh = p_dh[j];
                 if (k < a.T - 1) {
                     const float* sl = slots + ((size_t)rd * CL * NB + b) * Hc + ul;
                     for (int src = 0; src < CL; ++src) dh += sl[(size_t)src * NB * Hc];
                 }
-                const float fg = p_g[j][0], ig = p_g[j][1], og = p_g[j][2], gg = p_g[j][3];
-                const float tc = act_apply(a.act, p_c[j]);
+                const float fg = p_g[j].x, ig = p_g[j].y, og = p_g[j].z, gg = p_g[j].w;
+                const float tc = act_apply_fast(a.act, p_c[j]);
                 const float dog = dh * tc;
                 const float dct = dh * og * act_grad_from_out(a.act, tc) + dc_carry[j];
                 const float dig = dct * gg * dr[j];
                 const float dgg = dct * ig * dr[j];
                 const float dfg = dct * p_cm1[j];
                 dc_carry[j] = dct * fg;
-                dp[0] = dfg * fg * (1.f - fg);
-                dp[1] = dig * ig * (1.f - ig);
-                dp[2] = dog * og * (1.f - og);
-                dp[3] = dgg * act_grad_from_out(a.act, gg);
+                dp.x = dfg * fg * (1.f - fg);
+                dp.y = dig * ig * (1.f - ig);
+                dp.z = dog * og * (1.f - og);
+                dp.w = dgg * act_grad_from_out(a.act, gg);
                 const size_t row = (size_t)k * a.B + b0 + b;
                 const int u = u0 + ul;
-                float* o = a.dpre + row * a.ld + (size_t)u * a.us;
-#pragma unroll
-                for (int g = 0; g < 4; ++g) o[(size_t)g * a.gs] = dp[g];
-                if (a.dpreb) {
-                    __nv_bfloat16* ob = a.dpreb + row * a.ldb + (size_t)u * a.us;
-#pragma unroll
-                    for (int g = 0; g < 4; ++g) ob[(size_t)g * a.gs] = __float2bfloat16_rn(dp[g]);
-                }
+                *reinterpret_cast<float4*>(a.dpre + row * 4 * ldH + (size_t)u * 4) = dp;
+                if (a.dpreb)
+                    *reinterpret_cast<uint2*>(a.dpreb + row * 4 * ldH + (size_t)u * 4) =
+                        make_uint2(pack_bf16x2(dp.x, dp.y), pack_bf16x2(dp.z, dp.w));
                 if (k > 0) {
                     const size_t rowp = row - a.B;
-                    const float* gp = a.gates + rowp * a.ld + (size_t)u * a.us;
-#pragma unroll
-                    for (int g = 0; g < 4; ++g) p_g[j][g] = __ldg(gp + (size_t)g * a.gs);
+                    p_g[j] = __ldg(reinterpret_cast<const float4*>(a.gates + rowp * 4 * ldH + (size_t)u * 4));
                     p_c[j] = p_cm1[j];
-                    p_cm1[j] = (k > 1) ? __ldg(a.c + (rowp - a.B) * H + u) : 0.f;
+                    p_cm1[j] = (k > 1) ? __ldg(a.c + (rowp - a.B) * ldH + u) : 0.f;
                     p_dh[j] = __ldg(a.dh_out + rowp * H + u);
                 }
+            } else if (u0 + ul < ldH && b0 + b < a.B) {  // pad columns of the padded tensors stay zero
+                const size_t row = (size_t)k * a.B + b0 + b;
+                *reinterpret_cast<float4*>(a.dpre + row * 4 * ldH + (size_t)(u0 + ul) * 4) = dp;
+                if (a.dpreb) *reinterpret_cast<uint2*>(a.dpreb + row * 4 * ldH + (size_t)(u0 + ul) * 4) = make_uint2(0u, 0u);
             }
             __nv_bfloat16* d = dpre_s + (size_t)b * DPS + (ul >> 2) * 16 + (ul & 3);
-#pragma unroll
-            for (int g = 0; g < 4; ++g) d[g * 4] = __float2bfloat16_rn(dp[g]);
+            d[0] = __float2bfloat16_rn(dp.x);
+            d[4] = __float2bfloat16_rn(dp.y);
+            d[8] = __float2bfloat16_rn(dp.z);
+            d[12] = __float2bfloat16_rn(dp.w);
         }
         if (k == 0) break;  // dh_{-1} is not needed
         __syncthreads();
@@ -622,7 +666,7 @@ __global__ void __launch_bounds__(512, 1) lstm_tc_bwd_kernel(const TcBwdArgs a) 
 #pragma unroll
                 for (int q = 0; q < 4; ++q) acc[nt][q] = 0.f;
             const int e1 = csp_s[cs + 1];
-            const int koff = ((lane & 3) >> 1) * 4 + (lane & 1) * 2;  // (gate, row) pair inside the block
+            const int koff = (lane & 3) * 2;  // k = gate*4 + row inside the block
             for (int e = csp_s[cs]; e < e1; ++e) {
                 const int rs = rs_s[e];
                 uint2 bw = make_uint2(0u, 0u);
@@ -648,20 +692,20 @@ __global__ void __launch_bounds__(512, 1) lstm_tc_bwd_kernel(const TcBwdArgs a) 
         }
         __syncthreads();
         // ---- reduce-scatter: column slice d of the partial sums goes to CTA d -------------------
-        for (int idx = tid; idx < CL * NB * chunks; idx += nthreads) {
-            const int d = idx / (NB * chunks), rem = idx - d * (NB * chunks);
-            const int b = rem / chunks, q = rem - b * chunks;
-            const int col = d * Hc + q * 4;
-            uint4 v = make_uint4(0u, 0u, 0u, 0u);
-            if (col < NS * 4) v = *reinterpret_cast<const uint4*>(partial + (size_t)b * HPp + col);
-            const uint32_t off = (uint32_t)((((size_t)(wr * CL + rank) * NB + b) * Hc + q * 4) * 4);
-            st_cluster_v4(mapa_u32(slots_addr + off, (uint32_t)d), v);
+        for (int db = warp; db < CL * NB; db += nwarps) {  // one warp per (destination, sequence) row
+            const int d = db / NB, b = db - d * NB;
+            for (int q = lane; q < chunks; q += 32) {
+                const int col = d * Hc + q * 4;
+                uint4 v = make_uint4(0u, 0u, 0u, 0u);
+                if (col < NS * 4) v = *reinterpret_cast<const uint4*>(partial + (size_t)b * HPp + col);
+                const uint32_t off = (uint32_t)((((size_t)(wr * CL + rank) * NB + b) * Hc + q * 4) * 4);
+                st_cluster_v4(mapa_u32(slots_addr + off, (uint32_t)d), v);
+            }
         }
-        __syncwarp();
-        if (lane == 0) {
+        __syncthreads();
+        if (tid < CL) {  // one arrival per (source CTA, destination CTA)
             fence_release_cluster();
-            for (int d = 0; d < CL; ++d)
-                mbar_arrive_cluster_relaxed(mapa_u32(mbar_addr + wr * 8, (uint32_t)((rank + d) % CL)));
+            mbar_arrive_cluster_relaxed(mapa_u32(mbar_addr + wr * 8, (uint32_t)((rank + tid) % CL)));
         }
     }
     cluster.sync();
@@ -743,7 +787,7 @@ static int tc_smem_limit() {
 
 // Resolve (cluster size, sequences per cluster): 0 = choose.  Smallest cluster whose layouts fit.
 static int tc_resolve(const hcgs_plan* plan, int cluster_size, int nb, TcPlan** out, int* nb_out) {
-    HCGS_REQUIRE(nb == 0 || nb == 16 || nb == 32, "tensor-core recurrence: nb must be 0, 16 or 32");
+    HCGS_REQUIRE(nb == 0 || nb == 16, "tensor-core recurrence: nb must be 0 or 16 sequences per cluster");
     const int NB = nb ? nb : 16;
     const int limit = tc_smem_limit();
     const int cands[3] = {4, 8, 16};
@@ -752,7 +796,7 @@ static int tc_resolve(const hcgs_plan* plan, int cluster_size, int nb, TcPlan** 
         TcPlan* t = nullptr;
         if (tc_plan_get(plan, cands[ci], &t)) return 1;
         const bool fits = tc_fwd_smem(*t, NB) <= (size_t)limit && tc_bwd_smem(*t, NB) <= (size_t)limit &&
-                          t->SPW <= 4 && (NB == 16 || t->SPW <= 2) && (t->Hc * NB + 511) / 512 <= 10;
+                          t->SPW <= 4 && t->KS <= 8 && (t->Hc * NB + 511) / 512 <= 8;
         if (fits) {
             *out = t;
             *nb_out = NB;
@@ -766,6 +810,10 @@ static int tc_resolve(const hcgs_plan* plan, int cluster_size, int nb, TcPlan** 
 }  // namespace hcgs
 
 using namespace hcgs;
+
+namespace hcgs {
+static int tc_max_active_clusters(const TcPlan& t, int NB, int* fwd_clusters, int* bwd_clusters);
+}
 
 extern "C" int hcgs_lstm_tc_info(const hcgs_plan* plan, int cluster_size, int nb, int64_t* info) {
     HCGS_REQUIRE(plan && info, "hcgs_lstm_tc_info: NULL argument");
@@ -785,6 +833,11 @@ extern "C" int hcgs_lstm_tc_info(const hcgs_plan* plan, int cluster_size, int nb
     info[9] = t->n_blocks;
     info[10] = t->SPW;
     info[11] = t->HP;
+    int fc = 0, bc = 0;
+    if (tc_max_active_clusters(*t, NB, &fc, &bc) == 0) {
+        info[12] = fc;
+        info[13] = bc;
+    }
     return 0;
 }
 
@@ -816,72 +869,103 @@ namespace hcgs {
 typedef void (*TcFwdKernel)(const TcFwdArgs);
 typedef void (*TcBwdKernel)(const TcBwdArgs);
 
-static TcFwdKernel tc_pick_fwd(int NT, int SPW) {
-    if (NT == 1) {
-        switch (SPW) {
-            case 1: return lstm_tc_fwd_kernel<1, 1>;
-            case 2: return lstm_tc_fwd_kernel<1, 2>;
-            case 3: return lstm_tc_fwd_kernel<1, 3>;
-            case 4: return lstm_tc_fwd_kernel<1, 4>;
-        }
-    } else if (NT == 2) {
-        switch (SPW) {
-            case 1: return lstm_tc_fwd_kernel<2, 1>;
-            case 2: return lstm_tc_fwd_kernel<2, 2>;
-        }
+template <int SPW, int ACT>
+static TcFwdKernel tc_pick_fwd_ks(int KS) {
+    if (KS <= 4) return lstm_tc_fwd_kernel<1, SPW, 4, ACT>;
+    if (KS <= 8) return lstm_tc_fwd_kernel<1, SPW, 8, ACT>;
+    return nullptr;
+}
+
+template <int ACT>
+static TcFwdKernel tc_pick_fwd_act(int SPW, int KS) {
+    switch (SPW) {
+        case 1: return tc_pick_fwd_ks<1, ACT>(KS);
+        case 2: return tc_pick_fwd_ks<2, ACT>(KS);
+        case 3: return tc_pick_fwd_ks<3, ACT>(KS);
+        case 4: return tc_pick_fwd_ks<4, ACT>(KS);
     }
     return nullptr;
 }
 
+static TcFwdKernel tc_pick_fwd(int NT, int SPW, int KS, int act) {
+    if (NT != 1) return nullptr;
+    return act == HCGS_ACT_TANH ? tc_pick_fwd_act<HCGS_ACT_TANH>(SPW, KS) : tc_pick_fwd_act<-1>(SPW, KS);
+}
+
 static TcBwdKernel tc_pick_bwd(int NT, int items) {
-    if (NT == 1) {
-        if (items <= 2) return lstm_tc_bwd_kernel<1, 2>;
-        if (items <= 4) return lstm_tc_bwd_kernel<1, 4>;
-        if (items <= 6) return lstm_tc_bwd_kernel<1, 6>;
-        if (items <= 8) return lstm_tc_bwd_kernel<1, 8>;
-        if (items <= 10) return lstm_tc_bwd_kernel<1, 10>;
-    } else if (NT == 2) {
-        if (items <= 2) return lstm_tc_bwd_kernel<2, 2>;
-        if (items <= 4) return lstm_tc_bwd_kernel<2, 4>;
-        if (items <= 6) return lstm_tc_bwd_kernel<2, 6>;
-        if (items <= 8) return lstm_tc_bwd_kernel<2, 8>;
-        if (items <= 10) return lstm_tc_bwd_kernel<2, 10>;
-    }
+    if (NT != 1) return nullptr;
+    if (items <= 2) return lstm_tc_bwd_kernel<1, 2>;
+    if (items <= 4) return lstm_tc_bwd_kernel<1, 4>;
+    if (items <= 6) return lstm_tc_bwd_kernel<1, 6>;
+    if (items <= 8) return lstm_tc_bwd_kernel<1, 8>;
     return nullptr;
+}
+
+// co-resident clusters of the two kernels on the current device (0 when the query is unavailable)
+static int tc_max_active_clusters(const TcPlan& t, int NB, int* fwd_clusters, int* bwd_clusters) {
+    *fwd_clusters = *bwd_clusters = 0;
+    const void* ks[2] = {(const void*)tc_pick_fwd(NB / 16, t.SPW, t.KS, HCGS_ACT_TANH),
+                         (const void*)tc_pick_bwd(NB / 16, (t.Hc * NB + 511) / 512)};
+    const size_t smem[2] = {tc_fwd_smem(t, NB), tc_bwd_smem(t, NB)};
+    const int threads[2] = {t.WARPS * 32, 512};
+    int* outs[2] = {fwd_clusters, bwd_clusters};
+    for (int i = 0; i < 2; ++i) {
+        if (!ks[i]) continue;
+        if (cudaFuncSetAttribute(ks[i], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem[i]) != cudaSuccess) {
+            cudaGetLastError();
+            continue;
+        }
+        if (t.CL > 8) cudaFuncSetAttribute(ks[i], cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+        cudaLaunchConfig_t cfg;
+        memset(&cfg, 0, sizeof(cfg));
+        cfg.gridDim = dim3((unsigned)(t.CL * 64), 1, 1);
+        cfg.blockDim = dim3((unsigned)threads[i], 1, 1);
+        cfg.dynamicSmemBytes = smem[i];
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = (unsigned)t.CL;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        int n = 0;
+        if (cudaOccupancyMaxActiveClusters(&n, ks[i], &cfg) == cudaSuccess) *outs[i] = n;
+        else cudaGetLastError();
+    }
+    return 0;
 }
 
 }  // namespace hcgs
 
 extern "C" int hcgs_lstm_tc_fwd(const hcgs_plan* plan, int cluster_size, int nb, const uint32_t* fwd_pack,
-                                const float* pre, int64_t ld, int gate_stride, int unit_stride, const float* drop,
-                                float drop_scalar, int act, int t_len, int batch, float* h_out, void* hb_out,
-                                int hb_ld, float* c_out, float* gates_out, hcgs_stream stream) {
-    HCGS_REQUIRE(plan && fwd_pack && pre && h_out, "hcgs_lstm_tc_fwd: NULL argument");
+                                const float* pre, int ld_h, const float* drop, float drop_scalar, int act,
+                                int t_len, int batch, float* h_out, void* hb_out, float* c_out, float* gates_out,
+                                hcgs_stream stream) {
+    HCGS_REQUIRE(plan && fwd_pack && pre, "hcgs_lstm_tc_fwd: NULL argument");
+    HCGS_REQUIRE(h_out || hb_out, "hcgs_lstm_tc_fwd: no output requested");
     if (t_len <= 0 || batch <= 0) return 0;
     TcPlan* t = nullptr;
     int NB = 0;
     if (int rc = tc_resolve(plan, cluster_size, nb, &t, &NB)) return rc;
+    HCGS_REQUIRE(ld_h >= t->H && ld_h % 8 == 0, "hcgs_lstm_tc_fwd: ld_h=%d must be a multiple of 8 and >= H=%d", ld_h,
+                 t->H);
     TcFwdArgs a;
     a.wfrag = reinterpret_cast<const uint2*>(fwd_pack);
     a.cg = t->d_cg;
     a.nks = t->d_nks;
     a.pre = pre;
-    a.ld = ld;
-    a.gs = gate_stride;
-    a.us = unit_stride;
     a.drop = drop;
     a.drop_scalar = drop_scalar;
     a.h_out = h_out;
     a.hb_out = reinterpret_cast<__nv_bfloat16*>(hb_out);
-    a.hb_ld = hb_ld;
     a.c_out = c_out;
     a.gates_out = gates_out;
     a.T = t_len;
     a.B = batch;
     a.H = t->H;
+    a.ldH = ld_h;
     a.CL = t->CL;
     a.SPC = t->SPC;
-    a.SPW = t->SPW;
     a.KS = t->KS;
     a.HP = t->HP;
     a.act = act;
@@ -889,22 +973,23 @@ extern "C" int hcgs_lstm_tc_fwd(const hcgs_plan* plan, int cluster_size, int nb,
         const char* e = getenv("HCGS_TC_DEBUG");
         a.dbg = e ? atoi(e) : 0;
     }
-    TcFwdKernel k = tc_pick_fwd(NB / 16, t->SPW);
-    HCGS_REQUIRE(k != nullptr, "hcgs_lstm_tc_fwd: no kernel for nb=%d strips/warp=%d", NB, t->SPW);
+    TcFwdKernel k = tc_pick_fwd(NB / 16, t->SPW, t->KS, act);
+    HCGS_REQUIRE(k != nullptr, "hcgs_lstm_tc_fwd: no kernel for nb=%d strips/warp=%d k-steps=%d", NB, t->SPW, t->KS);
     const int n_clusters = (batch + NB - 1) / NB;
     return tc_launch(k, a, n_clusters, t->CL, t->WARPS * 32, tc_fwd_smem(*t, NB), (cudaStream_t)stream);
 }
 
 extern "C" int hcgs_lstm_tc_bwd(const hcgs_plan* plan, int cluster_size, int nb, const uint32_t* bwd_pack,
-                                const float* dh_out, const float* gates, int64_t ld, int gate_stride,
-                                int unit_stride, const float* c, const float* drop, float drop_scalar, int act,
-                                int t_len, int batch, float* dpre, void* dpre_bf16, int64_t ld_bf16,
-                                hcgs_stream stream) {
+                                const float* dh_out, const float* gates, const float* c, int ld_h,
+                                const float* drop, float drop_scalar, int act, int t_len, int batch, float* dpre,
+                                void* dpre_bf16, hcgs_stream stream) {
     HCGS_REQUIRE(plan && bwd_pack && dh_out && gates && c && dpre, "hcgs_lstm_tc_bwd: NULL argument");
     if (t_len <= 0 || batch <= 0) return 0;
     TcPlan* t = nullptr;
     int NB = 0;
     if (int rc = tc_resolve(plan, cluster_size, nb, &t, &NB)) return rc;
+    HCGS_REQUIRE(ld_h >= t->H && ld_h % 8 == 0, "hcgs_lstm_tc_bwd: ld_h=%d must be a multiple of 8 and >= H=%d", ld_h,
+                 t->H);
     TcBwdArgs a;
     a.wfrag = reinterpret_cast<const uint2*>(bwd_pack);
     a.blk_off = t->d_blk_off;
@@ -912,18 +997,15 @@ extern "C" int hcgs_lstm_tc_bwd(const hcgs_plan* plan, int cluster_size, int nb,
     a.blk_rs = t->d_blk_rs;
     a.dh_out = dh_out;
     a.gates = gates;
-    a.ld = ld;
-    a.gs = gate_stride;
-    a.us = unit_stride;
     a.c = c;
     a.drop = drop;
     a.drop_scalar = drop_scalar;
     a.dpre = dpre;
     a.dpreb = reinterpret_cast<__nv_bfloat16*>(dpre_bf16);
-    a.ldb = ld_bf16;
     a.T = t_len;
     a.B = batch;
     a.H = t->H;
+    a.ldH = ld_h;
     a.CL = t->CL;
     a.SPC = t->SPC;
     a.NS = t->NS;

@@ -60,26 +60,33 @@ def random_mask(rows, cols, blocks, drops, seed):
     return torch.from_numpy(hcgs_oracle.conn_mat(rows, cols, list(blocks), list(drops)).astype(np.float32))
 
 
-@pytest.mark.parametrize('H,B,T,blocks,drops,act,cl,nb,inter', [
-    (24, 3, 7, [8, 4], [50, 50], 'tanh', 4, 16, False),
-    (40, 19, 9, [8, 4], [50, 50], 'htanh', 4, 32, True),
-    (550, 8, 12, [32, 4], [75, 62.5], 'tanh', 8, 16, False),
-    (550, 20, 6, [32, 4], [75, 62.5], 'tanh', 4, 16, True),
-    (550, 37, 5, [32, 4], [75, 62.5], 'relu', 8, 32, False),
-    (512, 16, 8, [32, 4], [75, 62.5], 'tanh', 0, 0, False),
-    (1024, 9, 5, [32, 4], [75, 62.5], 'tanh', 0, 0, False),
-    (70, 5, 8, [16, 2], [50, 50], 'sigmoid', 4, 16, False),
+def to_inter(x, T, B, H, ldH):
+    """gate-major [T,B,4H] -> gate-interleaved, padded [T*B, 4*ldH] (pad columns zero)"""
+    out = torch.zeros(T * B, ldH, 4)
+    out[:, :H, :] = x.reshape(T * B, 4, H).transpose(1, 2)
+    return out.reshape(T * B, 4 * ldH).contiguous()
+
+
+def from_inter(x, T, B, H, ldH):
+    return x.reshape(T * B, ldH, 4)[:, :H, :].transpose(1, 2).reshape(T, B, 4 * H)
+
+
+@pytest.mark.parametrize('H,B,T,blocks,drops,act,cl,nb', [
+    (24, 3, 7, [8, 4], [50, 50], 'tanh', 4, 16),
+    (40, 19, 9, [8, 4], [50, 50], 'htanh', 4, 16),
+    (550, 8, 12, [32, 4], [75, 62.5], 'tanh', 8, 16),
+    (550, 20, 6, [32, 4], [75, 62.5], 'tanh', 0, 0),
+    (550, 37, 5, [32, 4], [75, 62.5], 'relu', 16, 16),
+    (512, 16, 8, [32, 4], [75, 62.5], 'tanh', 0, 0),
+    (70, 5, 8, [16, 2], [50, 50], 'sigmoid', 4, 16),
 ])
-def test_tc_recurrent_kernels(H, B, T, blocks, drops, act, cl, nb, inter):
+def test_tc_recurrent_kernels(H, B, T, blocks, drops, act, cl, nb):
     from b200 import native
     torch.manual_seed(H + B + T)
     mask = random_mask(H, H, blocks, drops, 3)
-    plan = native.Plan(mask, recurrent=True) if H < 1024 else None
-    if plan is None:
-        # the fp32 BELL layout of the legacy kernels may not fit at H=1024; the plan is still valid
-        plan = native.Plan(mask, recurrent=True)
+    plan = native.Plan(mask, recurrent=True)
     cfg = native.TcConfig(plan, cl, nb)
-    assert cfg.cluster_size in (4, 8, 16) and cfg.nb in (16, 32)
+    assert cfg.cluster_size in (4, 8, 16) and cfg.nb == 16
     us = [bf(torch.randn(H, H) * (1.5 / np.sqrt(max(mask.sum(1).mean().item(), 1.0))) * mask).requires_grad_(True)
           for _ in range(4)]
     pre = torch.randn(T, B, 4 * H).requires_grad_(True)
@@ -88,42 +95,37 @@ def test_tc_recurrent_kernels(H, B, T, blocks, drops, act, cl, nb, inter):
     dh = torch.randn(T, B, H)
     href.backward(dh)
     d = dev()
-
-    def lay(x):     # gate-major [.., 4H] -> kernel layout
-        if not inter:
-            return x.contiguous()
-        return x.reshape(T, B, 4, H).transpose(2, 3).reshape(T, B, 4 * H).contiguous()
-
-    def unlay(x):
-        if not inter:
-            return x
-        return x.reshape(T, B, H, 4).transpose(2, 3).reshape(T, B, 4 * H)
-
+    ldH = native.pad8(H)
     ud = [u.detach().to(d) for u in us]
     fp = torch.empty(cfg.fwd_pack_u32, device=d, dtype=torch.int32)
     bp = torch.empty(max(cfg.bwd_pack_u32, 1), device=d, dtype=torch.int32)
     native.lstm_tc_pack(plan, cfg, ud, fp, bp)
-    h = torch.empty(T, B, H, device=d)
-    c = torch.empty(T, B, H, device=d)
-    gates = torch.empty(T, B, 4 * H, device=d)
-    hb = torch.zeros(T * B, ((H + 63) // 64) * 64, device=d, dtype=torch.bfloat16)
+    pre_d = to_inter(pre.detach(), T, B, H, ldH).to(d)
+    h = torch.empty(T * B, H, device=d)
+    c = torch.zeros(T * B, ldH, device=d)
+    gates = torch.zeros(T * B, 4 * ldH, device=d)
+    hb = torch.full((T * B, ldH), 7.0, device=d, dtype=torch.bfloat16)
     code = native.ACT_CODES[act]
-    native.lstm_tc_fwd(plan, cfg, fp, lay(pre.detach()).to(d), drop.to(d), 1.0, code, h, c, gates, hb, inter)
+    native.lstm_tc_fwd(plan, cfg, fp, pre_d, drop.to(d), 1.0, code, T, B, h, hb, c, gates)
     torch.cuda.synchronize()
-    check(h, href, 2e-5, 1e-2, 'h')
-    assert torch.equal(hb[:, :H].float().cpu(), bf(h.cpu()).view(T * B, H)), 'bf16 copy of h'
-    assert hb[:, H:].abs().max().item() == 0 if hb.shape[1] > H else True
-    dpre = torch.empty(T, B, 4 * H, device=d)
-    dpb = torch.zeros(T * B, 4 * H, device=d, dtype=torch.bfloat16)
-    native.lstm_tc_bwd(plan, cfg, bp, dh.to(d), gates, c, drop.to(d), 1.0, code, dpre, dpb, inter)
+    # fast transcendental forms (abs err ~1e-6) + occasional bf16 rounding flips of h
+    check(h.view(T, B, H), href, 3e-5, 1e-2, 'h')
+    assert torch.equal(hb[:, :H].float().cpu(), bf(h.cpu())), 'bf16 copy of h'
+    if ldH > H:
+        assert hb[:, H:].float().abs().max().item() == 0, 'pad columns of hb must be zero'
+    dpre = torch.full((T * B, 4 * ldH), 3.0, device=d)
+    dpb = torch.full((T * B, 4 * ldH), 3.0, device=d, dtype=torch.bfloat16)
+    native.lstm_tc_bwd(plan, cfg, bp, dh.to(d).view(T * B, H), gates, c, drop.to(d), 1.0, code, T, B, dpre, dpb)
     torch.cuda.synchronize()
-    check(unlay(dpre.cpu()), pre.grad, 1e-4, 3e-2, 'dpre')
-    assert torch.equal(dpb.float().cpu().view(T, B, 4 * H), bf(dpre.cpu())), 'bf16 copy of dpre'
-    # eval variant: scalar drop, nothing saved
-    h2 = torch.empty(T, B, H, device=d)
-    native.lstm_tc_fwd(plan, cfg, fp, lay(pre.detach()).to(d), None, 0.8, code, h2, None, None, None, inter)
+    check(from_inter(dpre.cpu(), T, B, H, ldH), pre.grad, 1e-4, 3e-2, 'dpre')
+    assert torch.equal(dpb.float().cpu(), bf(dpre.cpu())), 'bf16 copy of dpre'
+    if ldH > H:
+        assert dpre.view(T * B, ldH, 4)[:, H:, :].abs().max().item() == 0, 'pad columns of dpre must be zero'
+    # eval variant: scalar drop, only the bf16 output
+    hb2 = torch.zeros(T * B, ldH, device=d, dtype=torch.bfloat16)
+    native.lstm_tc_fwd(plan, cfg, fp, pre_d, None, 0.8, code, T, B, None, hb2)
     href2 = lstm_layer_oracle_bf16([u.detach() for u in us], pre.detach(), torch.tensor([0.8]), act)
-    check(h2, href2, 2e-5, 1e-2, 'h eval')
+    check(hb2[:, :H].float().view(T, B, H), href2, 2e-3, 2e-2, 'h eval (bf16 output)')
     plan.destroy()
 
 
@@ -140,10 +142,10 @@ def test_tc_matches_fp32_kernels_on_bf16_exact_inputs():
     pre = torch.randn(T, B, 4 * H, device=d)
     fp = torch.empty(cfg.fwd_pack_u32, device=d, dtype=torch.int32)
     native.lstm_tc_pack(plan, cfg, us, fp, None)
-    h = torch.empty(T, B, H, device=d)
-    native.lstm_tc_fwd(plan, cfg, fp, pre, None, 1.0, 2, h)
+    h = torch.empty(T * B, H, device=d)
+    native.lstm_tc_fwd(plan, cfg, fp, to_inter(pre.cpu(), T, B, H, H).to(d), None, 1.0, 2, T, B, h)
     fp32 = torch.empty(plan.fwd_pack_floats, device=d)
     native.lstm_pack(plan, us, fp32, None)
     h32 = torch.empty(T, B, H, device=d)
     native.lstm_fwd(plan, fp32, pre, None, 1.0, 2, h32)
-    assert (h - h32).abs().max().item() <= 1e-6
+    assert (h.view(T, B, H) - h32).abs().max().item() <= 5e-6   # fast exp forms vs libm

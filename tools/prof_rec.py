@@ -1,0 +1,29 @@
+"""One launch each of the tensor-core recurrent kernels at the bench shape (for ncu)."""
+import os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, 'pytorch-kaldi-cgs_b200')); sys.path.insert(0, ROOT)
+import numpy as np, torch
+from b200 import native
+from oracle import hcgs_oracle
+H, T, B = 550, 256, int(sys.argv[1]) if len(sys.argv) > 1 else 128
+cl = int(sys.argv[2]) if len(sys.argv) > 2 else 8
+d = torch.device('cuda', 0)
+np.random.seed(3)
+mask = torch.from_numpy(hcgs_oracle.conn_mat(H, H, [32, 4], [75, 62.5]).astype(np.float32))
+plan = native.Plan(mask, recurrent=True)
+us = [(torch.randn(H, H) * 0.1 * mask).to(d) for _ in range(4)]
+cfg = native.TcConfig(plan, cl, 16)
+ldH = native.pad8(H)
+pre = torch.randn(T * B, 4 * ldH, device=d); drop = torch.bernoulli(torch.full((B, H), 0.8, device=d))
+h = torch.empty(T * B, H, device=d); c = torch.empty(T * B, ldH, device=d); gates = torch.empty(T * B, 4 * ldH, device=d)
+hb = torch.empty(T * B, ldH, device=d, dtype=torch.bfloat16)
+dh = torch.randn(T * B, H, device=d); dpre = torch.empty(T * B, 4 * ldH, device=d)
+dpb = torch.empty(T * B, 4 * ldH, device=d, dtype=torch.bfloat16)
+fp = torch.empty(cfg.fwd_pack_u32, device=d, dtype=torch.int32)
+bp = torch.empty(max(cfg.bwd_pack_u32, 1), device=d, dtype=torch.int32)
+native.lstm_tc_pack(plan, cfg, us, fp, bp)
+for _ in range(2):
+    native.lstm_tc_fwd(plan, cfg, fp, pre, drop, 1.0, 2, T, B, h, hb, c, gates)
+    native.lstm_tc_bwd(plan, cfg, bp, dh, gates, c, drop, 1.0, 2, T, B, dpre, dpb)
+torch.cuda.synchronize()
+print('ok')
