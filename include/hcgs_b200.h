@@ -162,6 +162,21 @@ int hcgs_lstm_tc_bwd(const hcgs_plan* plan, int cluster_size, int nb, const uint
                      float drop_scalar, int act, int t_len, int batch, float* dpre, void* dpre_bf16,
                      hcgs_stream stream);
 
+/* ---- tcgen05 block-sparse bf16 GEMM family (tensor-core build) ------------------------------
+ * Same products as hcgs_bsgemm_nt / _nn / hcgs_bs_sddmm with bf16 operands and fp32 accumulation
+ * in TMEM.  Activations are bf16 row-major [m, ld] (ld*2 a multiple of 16 bytes, pad columns
+ * zero), loaded by TMA; weights are re-packed per step into pre-swizzled bf16 tiles.
+ * With n_w = 4 (LSTM gates) the output / dY columns are gate-INTERLEAVED: (unit u, gate g) at
+ * column u*4+g; with n_w = 1 (MLP) they are the plain unit index.
+ * hcgs_tc_pack_nt: wpack needs nz_tiles * 32*n_w * 32 bf16 (plan info[2] tiles).
+ * hcgs_cast_bf16 : fp32 [rows, cols] -> bf16 [rows, ldo], pad columns zeroed.                  */
+int hcgs_tc_pack_nt(const hcgs_plan* plan, int n_w, const float* const* w, int ldw, void* wpack,
+                    hcgs_stream stream);
+int hcgs_tc_gemm_nt(const hcgs_plan* plan, int n_w, const void* wpack, const void* x_bf16, int64_t ldx,
+                    int64_t m, const float* const* bias, float* y, int64_t ldy, hcgs_stream stream);
+int hcgs_cast_bf16(const float* x, int64_t ldx, int64_t rows, int cols, void* out, int64_t ldo,
+                   hcgs_stream stream);
+
 /* ---- MLP pointwise pieces ------------------------------------------------------------------
  * y = drop_mask * act(x)  (neural_networks.py:306-317; drop_mask already holds 1/(1-p) scaling,
  * NULL = no dropout).  Backward: dx = dy * drop_mask * act'(.) using the saved output y.       */

@@ -56,6 +56,9 @@ SIGNATURES = {
                                  _f, c_void_p]),
     'hcgs_lstm_tc_bwd': (c_int, [c_void_p, c_int, c_int, _f, _f, _f, _f, c_int, _f, c_float, c_int, c_int, c_int, _f,
                                  _f, c_void_p]),
+    'hcgs_tc_pack_nt': (c_int, [c_void_p, c_int, _pp, c_int, _f, c_void_p]),
+    'hcgs_tc_gemm_nt': (c_int, [c_void_p, c_int, _f, _f, c_int64, c_int64, _pp, _f, c_int64, c_void_p]),
+    'hcgs_cast_bf16': (c_int, [_f, c_int64, c_int64, c_int, _f, c_int64, c_void_p]),
     'hcgs_act_fwd': (c_int, [_f, _f, _f, c_int64, c_int, c_void_p]),
     'hcgs_act_bwd': (c_int, [_f, _f, _f, _f, c_int64, c_int, c_void_p]),
     'hcgs_logsoftmax_fwd': (c_int, [_f, c_int, _f, c_int, c_int64, c_int, _f, c_void_p]),
@@ -89,7 +92,8 @@ def load():
 KERNELS_PER_CALL = {'hcgs_mask_apply': 1, 'hcgs_quantize_w': 1, 'hcgs_quantize_act': 2, 'hcgs_bsgemm_nt': 1,
                     'hcgs_bsgemm_nn': 1, 'hcgs_bs_sddmm': 1, 'hcgs_colsum': 1, 'hcgs_bn_fwd': 3, 'hcgs_bn_bwd': 2,
                     'hcgs_lstm_pack': 2, 'hcgs_lstm_fwd': 1, 'hcgs_lstm_bwd': 1,
-                    'hcgs_lstm_tc_pack': 2, 'hcgs_lstm_tc_fwd': 1, 'hcgs_lstm_tc_bwd': 1, 'hcgs_act_fwd': 1, 'hcgs_act_bwd': 1,
+                    'hcgs_lstm_tc_pack': 2, 'hcgs_lstm_tc_fwd': 1, 'hcgs_lstm_tc_bwd': 1,
+                    'hcgs_tc_pack_nt': 1, 'hcgs_tc_gemm_nt': 1, 'hcgs_cast_bf16': 1, 'hcgs_act_fwd': 1, 'hcgs_act_bwd': 1,
                     'hcgs_logsoftmax_fwd': 1, 'hcgs_logsoftmax_bwd': 1, 'hcgs_nll_fwd_bwd': 1, 'hcgs_opt_step': 1}
 LAUNCHES = {'total': 0}
 
@@ -361,6 +365,32 @@ def lstm_tc_bwd(plan, cfg, bwd_pack, dh_out, gates, c, drop, drop_scalar, act, T
     _check(load().hcgs_lstm_tc_bwd(plan.handle, cfg.cluster_size, cfg.nb, _ptr(bwd_pack), _ptr(dh_out), _ptr(gates),
                                    _ptr(c), ldH, _ptr(drop), float(drop_scalar), int(act), T, B, _ptr(dpre),
                                    _ptr(dpre_bf16), _stream()), 'hcgs_lstm_tc_bwd')
+
+
+def tc_pack_nt(plan, weights, wpack):
+    """wpack: bf16 CUDA tensor of plan.nz_tiles * 32*len(weights) * 32 elements."""
+    _require_cuda(*weights)
+    _require_cuda_any(wpack)
+    assert wpack.dtype == torch.bfloat16 and wpack.numel() >= plan.nz_tiles * 32 * len(weights) * 32
+    _check(load().hcgs_tc_pack_nt(plan.handle, len(weights), _ptrs(weights), _row_major_2d(weights[0], 'w'),
+                                  _ptr(wpack), _stream()), 'hcgs_tc_pack_nt')
+
+
+def tc_gemm_nt(plan, n_w, wpack, x_bf16, y, biases=None):
+    """y[:, (u, g)] = x @ W_g^T ; x_bf16 [m, ldx] bf16 (pad columns zero), y [m, ldy] fp32."""
+    _require_cuda(y)
+    _require_cuda_any(wpack, x_bf16)
+    assert x_bf16.dtype == torch.bfloat16 and x_bf16.dim() == 2 and x_bf16.stride(1) == 1
+    _check(load().hcgs_tc_gemm_nt(plan.handle, int(n_w), _ptr(wpack), _ptr(x_bf16), x_bf16.stride(0), x_bf16.shape[0],
+                                  _ptrs(biases), _ptr(y), y.stride(0), _stream()), 'hcgs_tc_gemm_nt')
+
+
+def cast_bf16(x2d, out):
+    _require_cuda(x2d)
+    _require_cuda_any(out)
+    assert out.dtype == torch.bfloat16 and out.shape[0] == x2d.shape[0] and out.stride(1) == 1
+    _check(load().hcgs_cast_bf16(_ptr(x2d), _row_major_2d(x2d, 'x'), x2d.shape[0], x2d.shape[1], _ptr(out),
+                                 out.stride(0), _stream()), 'hcgs_cast_bf16')
 
 
 def act_fwd(x, y, drop_mask, act):

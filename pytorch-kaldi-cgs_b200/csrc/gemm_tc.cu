@@ -1,0 +1,418 @@
+// Block-sparse bf16 GEMM family on the 5th-generation tensor cores (tcgen05 + TMEM), fed by TMA.
+//
+//   nt   : Y[m, (r,u,g)]  = sum_k X[m,k] W_g[r*32+u, k]          time-batched input projections
+//          (reference: the four F.linear calls neural_networks.py:951-954, MLP :306)
+//   nn   : dX[m, k]       = sum_{r,u,g} dY[m,(r,u,g)] W_g[r*32+u,k]   data gradient
+//   sddmm: dW_g[r*32+u,k] = mask * sum_m dY[m,(r,u,g)] X[m,k]      weight gradient, kept tiles only
+//
+// Sparsity: the plan's 32x32 tile index (HCGS level-1 blocks); a masked tile is never loaded,
+// multiplied or written.  The NG gates of an LSTM layer share one mask, so one accumulator tile is
+// 128 = 32 units x 4 gates wide with the gate index fastest ("gate-interleaved", the layout the
+// recurrent kernels stream as one float4 per (sequence, unit) item).
+//
+// Operands: activations are bf16 row-major with a padded leading dimension and reach shared
+// memory through 2-D TMA tensor maps (SWIZZLE_64B / SWIZZLE_128B boxes); weights are re-packed
+// every step (they change every optimizer step) into pre-swizzled bf16 tiles that one
+// cp.async.bulk brings in.  Accumulators live in TMEM; one elected thread issues tcgen05.mma;
+// smem stages are recycled through tcgen05.commit -> mbarrier; the epilogue reads TMEM with
+// tcgen05.ld.  Every mbarrier wait is bounded (trap, never hang).
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include <algorithm>
+
+#include "common.cuh"
+
+namespace hcgs {
+
+// ---- PTX helpers -----------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t g_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void g_mbar_init(uint32_t addr, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(addr), "r"(count) : "memory");
+}
+__device__ __forceinline__ void g_mbar_expect_tx(uint32_t addr, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(addr), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ uint32_t g_mbar_try_wait(uint32_t addr, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(addr), "r"(parity)
+        : "memory");
+    return ok;
+}
+__device__ __forceinline__ void g_mbar_wait(uint32_t addr, uint32_t parity) {
+    for (int spin = 0; spin < (1 << 24); ++spin)
+        if (g_mbar_try_wait(addr, parity)) return;
+    __trap();  // a pipeline bug must surface as a launch error, never as a hang
+}
+
+__device__ __forceinline__ void tma_load_2d(uint32_t smem_dst, const CUtensorMap* map, int c0, int c1, uint32_t mbar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+        ::"r"(smem_dst), "l"(map), "r"(c0), "r"(c1), "r"(mbar)
+        : "memory");
+}
+__device__ __forceinline__ void bulk_load_1d(uint32_t smem_dst, const void* gsrc, uint32_t bytes, uint32_t mbar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_dst),
+                 "l"(gsrc), "r"(bytes), "r"(mbar)
+                 : "memory");
+}
+
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// whole warp; NCOLS power of two >= 32
+template <int NCOLS>
+__device__ __forceinline__ void tmem_alloc(uint32_t smem_result_addr) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_result_addr),
+                 "n"(NCOLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+template <int NCOLS>
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(NCOLS) : "memory");
+}
+
+// D[tmem] (+)= A[smem] * B[smem], bf16 operands, fp32 accumulate; issued by ONE thread
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                          uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// all previously issued MMAs of this thread arrive on the mbarrier when they have completed
+__device__ __forceinline__ void umma_commit(uint32_t mbar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(mbar)
+                 : "memory");
+}
+
+// 32 lanes x 32 consecutive fp32 columns: thread i of the warp receives TMEM lane (base lane + i)
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
+    uint32_t r[32];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+          "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// ---- UMMA descriptors (cute/arch/mma_sm100_desc.hpp bit layout) --------------------------------
+// shared-memory matrix descriptor: start address, leading / stride byte offsets (all >> 4),
+// version 1 (Blackwell), swizzle mode in bits [61,64): 2 = 128B, 4 = 64B, 6 = 32B, 0 = none.
+__device__ __forceinline__ uint64_t umma_smem_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes,
+                                                   uint32_t layout_type) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+    d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+    d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)(layout_type & 7) << 61;
+    return d;
+}
+constexpr uint32_t UMMA_SW128 = 2, UMMA_SW64 = 4;
+
+// instruction descriptor, kind::f16: fp32 accumulate, bf16 A and B; a_mn / b_mn = 1 for MN-major
+__host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N, int a_mn, int b_mn) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16) |
+           ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+// ---- host: TMA tensor maps --------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (fn) return fn;
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+        return nullptr;
+    fn = (EncodeTiledFn)p;
+    return fn;
+}
+
+// bf16 row-major [rows, cols] with leading dimension ld (elements); box = box_cols x box_rows
+static int make_tmap_bf16(CUtensorMap* map, const void* base, int64_t rows, int64_t cols, int64_t ld, int box_cols,
+                          int box_rows, CUtensorMapSwizzle swz) {
+    EncodeTiledFn fn = get_encode_fn();
+    HCGS_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled is not available from this driver");
+    HCGS_REQUIRE(((uintptr_t)base & 15) == 0 && (ld * 2) % 16 == 0,
+                 "TMA operand must be 16-byte aligned with a 16-byte multiple row pitch (ld=%lld)", (long long)ld);
+    cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t gstr[1] = {(cuuint64_t)ld * 2};
+    cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstr, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    HCGS_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed (%d) rows=%lld cols=%lld ld=%lld", (int)r,
+                 (long long)rows, (long long)cols, (long long)ld);
+    return 0;
+}
+
+// ---- weight packing: masked dense fp32 -> pre-swizzled bf16 tiles ------------------------------
+// nt tiles, CSR order (tile t = (r, c) from the plan's flat list): [32*NG rows n = u*NG+g][32 k],
+// 64-byte rows in the SWIZZLE_64B pattern (16-byte chunk index ^= (row >> 1) & 3).
+template <int NG>
+__global__ void tc_pack_nt_kernel(const int* __restrict__ tile_rc, int nz, PtrPack<const float> W, int ldw,
+                                  int n_out, int n_in, __nv_bfloat16* __restrict__ out) {
+    const int64_t total = (int64_t)nz * 32 * NG * 4;  // 16-byte chunks
+    for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+         idx += (int64_t)gridDim.x * blockDim.x) {
+        const int c16 = idx & 3;
+        const int n = (int)((idx >> 2) % (32 * NG));
+        const int t = (int)(idx / (4 * 32 * NG));
+        const int r = tile_rc[2 * t], c = tile_rc[2 * t + 1];
+        const int u = n / NG, g = n % NG;
+        const int row = r * 32 + u, col0 = c * 32 + c16 * 8;
+        uint32_t w[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            float lo = 0.f, hi = 0.f;
+            if (row < n_out) {
+                if (col0 + 2 * j < n_in) lo = __ldg(W.p[g] + (int64_t)row * ldw + col0 + 2 * j);
+                if (col0 + 2 * j + 1 < n_in) hi = __ldg(W.p[g] + (int64_t)row * ldw + col0 + 2 * j + 1);
+            }
+            const __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+            w[j] = *reinterpret_cast<const uint32_t*>(&v);
+        }
+        unsigned char* dst = reinterpret_cast<unsigned char*>(out) + (size_t)t * (32 * NG * 64) + n * 64 +
+                             ((c16 ^ ((n >> 1) & 3)) << 4);
+        *reinterpret_cast<uint4*>(dst) = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+}
+
+// ---- nt: Y = X W^T ------------------------------------------------------------------------------
+struct TcNtArgs {
+    const __nv_bfloat16* wpack;  // nt tiles, CSR order
+    const int* row_ptr;          // [tr+1]
+    const int* col_idx;          // [nz]
+    float* y;                    // [M, ldy] fp32; column of (r, u, g) = (r*32+u)*NG + g
+    int64_t ldy;
+    int64_t M;
+    int n_out;                   // output units (rows of one W_g)
+    PtrPack<const float> bias;   // per gate [n_out] or NULL
+};
+
+constexpr int NT_STAGES = 4;
+constexpr int NT_A_BYTES = 128 * 64;  // 128 rows x 32 bf16, SWIZZLE_64B
+
+template <int NG>
+__host__ __device__ constexpr int nt_smem_bytes() {
+    return 1024 + NT_STAGES * (NT_A_BYTES + 32 * NG * 64) + 256;
+}
+
+template <int NG>
+__global__ void __launch_bounds__(128) tc_gemm_nt_kernel(const __grid_constant__ CUtensorMap tmX, const TcNtArgs a) {
+    constexpr int BN = 32 * NG;
+    constexpr int B_BYTES = BN * 64;
+    constexpr int TCOLS = BN < 32 ? 32 : BN;
+    constexpr uint32_t IDESC = umma_idesc_bf16(128, BN, 0, 0);
+    extern __shared__ unsigned char smem_dyn[];
+    unsigned char* smem = reinterpret_cast<unsigned char*>(((uintptr_t)smem_dyn + 1023) & ~(uintptr_t)1023);
+    unsigned char* sA = smem;
+    unsigned char* sB = smem + NT_STAGES * NT_A_BYTES;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + NT_STAGES * (NT_A_BYTES + B_BYTES));
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * NT_STAGES + 1);
+    const uint32_t full0 = g_smem_u32(bars), empty0 = g_smem_u32(bars + NT_STAGES),
+                   done = g_smem_u32(bars + 2 * NT_STAGES);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int r = blockIdx.x;
+    const int64_t m0 = (int64_t)blockIdx.y * 128;
+    const int k0 = a.row_ptr[r], nk = a.row_ptr[r + 1] - k0;
+
+    if (warp == 0 && lane == 0) {
+        for (int s = 0; s < NT_STAGES; ++s) {
+            g_mbar_init(full0 + 8 * s, 1);
+            g_mbar_init(empty0 + 8 * s, 1);
+        }
+        g_mbar_init(done, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) tmem_alloc<TCOLS>(g_smem_u32(tmem_slot));
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp == 0 && lane == 0) {
+        // ---- TMA producer ----------------------------------------------------------------------
+        for (int i = 0; i < nk; ++i) {
+            const int s = i % NT_STAGES;
+            if (i >= NT_STAGES) g_mbar_wait(empty0 + 8 * s, (uint32_t)(((i / NT_STAGES) - 1) & 1));
+            g_mbar_expect_tx(full0 + 8 * s, NT_A_BYTES + B_BYTES);
+            tma_load_2d(g_smem_u32(sA + s * NT_A_BYTES), &tmX, a.col_idx[k0 + i] * 32, (int)m0, full0 + 8 * s);
+            bulk_load_1d(g_smem_u32(sB + s * B_BYTES),
+                         reinterpret_cast<const unsigned char*>(a.wpack) + (size_t)(k0 + i) * B_BYTES, B_BYTES,
+                         full0 + 8 * s);
+        }
+    } else if (warp == 1 && lane == 0) {
+        // ---- MMA issuer ------------------------------------------------------------------------
+        for (int i = 0; i < nk; ++i) {
+            const int s = i % NT_STAGES;
+            g_mbar_wait(full0 + 8 * s, (uint32_t)((i / NT_STAGES) & 1));
+            tc_fence_after();
+            const uint32_t aaddr = g_smem_u32(sA + s * NT_A_BYTES), baddr = g_smem_u32(sB + s * B_BYTES);
+#pragma unroll
+            for (int kk = 0; kk < 2; ++kk) {  // 32 k per stage = 2 x (K = 16); +32 bytes inside the swizzle atom
+                const uint64_t ad = umma_smem_desc(aaddr + kk * 32, 16, 512, UMMA_SW64);
+                const uint64_t bd = umma_smem_desc(baddr + kk * 32, 16, 512, UMMA_SW64);
+                umma_bf16(tmem, ad, bd, IDESC, (i > 0 || kk > 0) ? 1u : 0u);
+            }
+            umma_commit(empty0 + 8 * s);  // stage reusable once these MMAs have read it
+        }
+        umma_commit(done);
+    }
+    // ---- epilogue: TMEM -> registers -> global ------------------------------------------------------
+    __syncwarp();
+    if (nk > 0) {
+        g_mbar_wait(done, 0);
+        tc_fence_after();
+    }
+    const int64_t m = m0 + warp * 32 + lane;
+#pragma unroll 1
+    for (int cb = 0; cb < BN / 32; ++cb) {
+        float v[32];
+        if (nk > 0) {
+            tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + cb * 32, v);
+        } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = 0.f;
+        }
+        if (m < a.M) {
+            const int col0 = r * 32 * NG + cb * 32;  // output column of v[0]
+            float* dst = a.y + m * a.ldy + col0;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                const int n = cb * 32 + i, u = r * 32 + n / NG, g = n % NG;
+                if (u < a.n_out) {
+                    float o = v[i];
+                    if (a.bias.p[g]) o += __ldg(a.bias.p[g] + u);
+                    v[i] = o;
+                }
+            }
+            const bool vec = ((a.ldy & 3) == 0) && ((reinterpret_cast<uintptr_t>(a.y) & 15) == 0) &&
+                             (r * 32 + 32 <= a.n_out);
+            if (vec) {
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+                    *reinterpret_cast<float4*>(dst + 4 * i) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+            } else {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    const int u = r * 32 + (cb * 32 + i) / NG;
+                    if (u < a.n_out) dst[i] = v[i];
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc<TCOLS>(tmem);
+}
+
+}  // namespace hcgs
+
+using namespace hcgs;
+
+extern "C" int hcgs_tc_pack_nt(const hcgs_plan* plan, int n_w, const float* const* w, int ldw, void* wpack,
+                               hcgs_stream stream) {
+    HCGS_REQUIRE(plan && w && wpack, "hcgs_tc_pack_nt: NULL argument");
+    HCGS_REQUIRE(n_w == 1 || n_w == 4, "hcgs_tc_pack_nt: n_w must be 1 or 4");
+    if (plan->nz_tiles == 0) return 0;
+    const int64_t total = (int64_t)plan->nz_tiles * 32 * n_w * 4;
+    const int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 8);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n_w == 4)
+        tc_pack_nt_kernel<4><<<blocks, 256, 0, st>>>(plan->d_tile_rc, plan->nz_tiles, make_pack<const float>(w, 4), ldw,
+                                                     plan->n_out, plan->n_in, (__nv_bfloat16*)wpack);
+    else
+        tc_pack_nt_kernel<1><<<blocks, 256, 0, st>>>(plan->d_tile_rc, plan->nz_tiles, make_pack<const float>(w, 1), ldw,
+                                                     plan->n_out, plan->n_in, (__nv_bfloat16*)wpack);
+    HCGS_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int hcgs_tc_gemm_nt(const hcgs_plan* plan, int n_w, const void* wpack, const void* x_bf16, int64_t ldx,
+                               int64_t m, const float* const* bias, float* y, int64_t ldy, hcgs_stream stream) {
+    HCGS_REQUIRE(plan && wpack && x_bf16 && y, "hcgs_tc_gemm_nt: NULL argument");
+    HCGS_REQUIRE(n_w == 1 || n_w == 4, "hcgs_tc_gemm_nt: n_w must be 1 or 4");
+    if (m <= 0) return 0;
+    HCGS_REQUIRE(ldy >= (int64_t)plan->tr * 32 * n_w || ldy >= (int64_t)plan->n_out * n_w,
+                 "hcgs_tc_gemm_nt: ldy too small");
+    CUtensorMap tm;
+    if (int rc = make_tmap_bf16(&tm, x_bf16, m, plan->n_in, ldx, 32, 128, CU_TENSOR_MAP_SWIZZLE_64B)) return rc;
+    TcNtArgs a;
+    a.wpack = (const __nv_bfloat16*)wpack;
+    a.row_ptr = plan->d_row_ptr;
+    a.col_idx = plan->d_col_idx;
+    a.y = y;
+    a.ldy = ldy;
+    a.M = m;
+    a.n_out = plan->n_out;
+    a.bias = make_pack<const float>(bias, n_w);
+    const int64_t mt = (m + 127) / 128;
+    HCGS_REQUIRE(mt <= 65535, "hcgs_tc_gemm_nt: too many rows (%lld)", (long long)m);
+    dim3 grid(plan->tr, (unsigned)mt, 1);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n_w == 4) {
+        HCGS_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm_nt_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             nt_smem_bytes<4>()));
+        tc_gemm_nt_kernel<4><<<grid, 128, nt_smem_bytes<4>(), st>>>(tm, a);
+    } else {
+        HCGS_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm_nt_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             nt_smem_bytes<1>()));
+        tc_gemm_nt_kernel<1><<<grid, 128, nt_smem_bytes<1>(), st>>>(tm, a);
+    }
+    HCGS_LAUNCH_CHECK();
+    return 0;
+}
+
+// fp32 [rows, cols] (ld = ldx) -> bf16 [rows, ldo] with zero pad columns (cols <= ldo)
+namespace hcgs {
+__global__ void cast_bf16_kernel(const float* __restrict__ x, int64_t ldx, int64_t rows, int cols,
+                                 __nv_bfloat16* __restrict__ out, int64_t ldo) {
+    const int64_t total = rows * (ldo / 2);
+    for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+         idx += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = idx / (ldo / 2);
+        const int c = (int)(idx - r * (ldo / 2)) * 2;
+        const float lo = c < cols ? __ldg(x + r * ldx + c) : 0.f;
+        const float hi = c + 1 < cols ? __ldg(x + r * ldx + c + 1) : 0.f;
+        *reinterpret_cast<__nv_bfloat162*>(out + r * ldo + c) = __floats2bfloat162_rn(lo, hi);
+    }
+}
+}  // namespace hcgs
+
+extern "C" int hcgs_cast_bf16(const float* x, int64_t ldx, int64_t rows, int cols, void* out, int64_t ldo,
+                              hcgs_stream stream) {
+    HCGS_REQUIRE(x && out, "hcgs_cast_bf16: NULL argument");
+    HCGS_REQUIRE(ldo >= cols && (ldo & 1) == 0, "hcgs_cast_bf16: ldo must be even and >= cols");
+    if (rows <= 0) return 0;
+    const int64_t total = rows * (ldo / 2);
+    const int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 16);
+    cast_bf16_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(x, ldx, rows, cols, (__nv_bfloat16*)out, ldo);
+    HCGS_LAUNCH_CHECK();
+    return 0;
+}
