@@ -176,6 +176,17 @@ int hcgs_tc_gemm_nt(const hcgs_plan* plan, int n_w, const void* wpack, const voi
                     int64_t m, const float* const* bias, float* y, int64_t ldy, hcgs_stream stream);
 int hcgs_cast_bf16(const float* x, int64_t ldx, int64_t rows, int cols, void* out, int64_t ldo,
                    hcgs_stream stream);
+/* hcgs_tc_pack_nn / hcgs_tc_gemm_nn: dX[m,k] = sum_{u,g} dY[m,(u,g)] W_g[u,k]; wpack same size as for nt;
+ *   dY bf16 [m, lddy] (lddy = padded n_out * n_w, pad columns zero); dX fp32 [m, lddx].
+ * hcgs_tc_sddmm: dW_g[u,k] += mask[u,k] * sum_m dY[m,(u,g)] X[m,k] inside kept tiles only (fp32 atomics:
+ *   the caller zero-initialises dW; entries outside kept tiles stay untouched).                  */
+int hcgs_tc_pack_nn(const hcgs_plan* plan, int n_w, const float* const* w, int ldw, void* wpack,
+                    hcgs_stream stream);
+int hcgs_tc_gemm_nn(const hcgs_plan* plan, int n_w, const void* wpack, const void* dy_bf16, int64_t lddy,
+                    int64_t m, float* dx, int64_t lddx, hcgs_stream stream);
+int hcgs_tc_sddmm(const hcgs_plan* plan, int n_w, const void* dy_bf16, int64_t lddy, const void* x_bf16,
+                  int64_t ldx, int64_t m, float* const* dw, int64_t lddw, const float* mask,
+                  hcgs_stream stream);
 
 /* ---- MLP pointwise pieces ------------------------------------------------------------------
  * y = drop_mask * act(x)  (neural_networks.py:306-317; drop_mask already holds 1/(1-p) scaling,

@@ -59,6 +59,9 @@ SIGNATURES = {
     'hcgs_tc_pack_nt': (c_int, [c_void_p, c_int, _pp, c_int, _f, c_void_p]),
     'hcgs_tc_gemm_nt': (c_int, [c_void_p, c_int, _f, _f, c_int64, c_int64, _pp, _f, c_int64, c_void_p]),
     'hcgs_cast_bf16': (c_int, [_f, c_int64, c_int64, c_int, _f, c_int64, c_void_p]),
+    'hcgs_tc_pack_nn': (c_int, [c_void_p, c_int, _pp, c_int, _f, c_void_p]),
+    'hcgs_tc_gemm_nn': (c_int, [c_void_p, c_int, _f, _f, c_int64, c_int64, _f, c_int64, c_void_p]),
+    'hcgs_tc_sddmm': (c_int, [c_void_p, c_int, _f, c_int64, _f, c_int64, c_int64, _pp, c_int64, _f, c_void_p]),
     'hcgs_act_fwd': (c_int, [_f, _f, _f, c_int64, c_int, c_void_p]),
     'hcgs_act_bwd': (c_int, [_f, _f, _f, _f, c_int64, c_int, c_void_p]),
     'hcgs_logsoftmax_fwd': (c_int, [_f, c_int, _f, c_int, c_int64, c_int, _f, c_void_p]),
@@ -93,7 +96,8 @@ KERNELS_PER_CALL = {'hcgs_mask_apply': 1, 'hcgs_quantize_w': 1, 'hcgs_quantize_a
                     'hcgs_bsgemm_nn': 1, 'hcgs_bs_sddmm': 1, 'hcgs_colsum': 1, 'hcgs_bn_fwd': 3, 'hcgs_bn_bwd': 2,
                     'hcgs_lstm_pack': 2, 'hcgs_lstm_fwd': 1, 'hcgs_lstm_bwd': 1,
                     'hcgs_lstm_tc_pack': 2, 'hcgs_lstm_tc_fwd': 1, 'hcgs_lstm_tc_bwd': 1,
-                    'hcgs_tc_pack_nt': 1, 'hcgs_tc_gemm_nt': 1, 'hcgs_cast_bf16': 1, 'hcgs_act_fwd': 1, 'hcgs_act_bwd': 1,
+                    'hcgs_tc_pack_nt': 1, 'hcgs_tc_gemm_nt': 1, 'hcgs_cast_bf16': 1,
+                    'hcgs_tc_pack_nn': 1, 'hcgs_tc_gemm_nn': 1, 'hcgs_tc_sddmm': 1, 'hcgs_act_fwd': 1, 'hcgs_act_bwd': 1,
                     'hcgs_logsoftmax_fwd': 1, 'hcgs_logsoftmax_bwd': 1, 'hcgs_nll_fwd_bwd': 1, 'hcgs_opt_step': 1}
 LAUNCHES = {'total': 0}
 
@@ -383,6 +387,35 @@ def tc_gemm_nt(plan, n_w, wpack, x_bf16, y, biases=None):
     assert x_bf16.dtype == torch.bfloat16 and x_bf16.dim() == 2 and x_bf16.stride(1) == 1
     _check(load().hcgs_tc_gemm_nt(plan.handle, int(n_w), _ptr(wpack), _ptr(x_bf16), x_bf16.stride(0), x_bf16.shape[0],
                                   _ptrs(biases), _ptr(y), y.stride(0), _stream()), 'hcgs_tc_gemm_nt')
+
+
+def tc_pack_nn(plan, weights, wpack):
+    _require_cuda(*weights)
+    _require_cuda_any(wpack)
+    assert wpack.dtype == torch.bfloat16 and wpack.numel() >= plan.nz_tiles * 32 * len(weights) * 32
+    _check(load().hcgs_tc_pack_nn(plan.handle, len(weights), _ptrs(weights), _row_major_2d(weights[0], 'w'),
+                                  _ptr(wpack), _stream()), 'hcgs_tc_pack_nn')
+
+
+def tc_gemm_nn(plan, n_w, wpack, dy_bf16, dx):
+    """dx[m, k] = sum_(u,g) dy[m, (u,g)] W_g[u, k]; dy_bf16 [m, lddy] bf16, dx [m, >= n_in] fp32."""
+    _require_cuda(dx)
+    _require_cuda_any(wpack, dy_bf16)
+    assert dy_bf16.dtype == torch.bfloat16 and dy_bf16.dim() == 2 and dy_bf16.stride(1) == 1
+    assert dx.shape[0] == dy_bf16.shape[0]
+    _check(load().hcgs_tc_gemm_nn(plan.handle, int(n_w), _ptr(wpack), _ptr(dy_bf16), dy_bf16.stride(0),
+                                  dy_bf16.shape[0], _ptr(dx), dx.stride(0), _stream()), 'hcgs_tc_gemm_nn')
+
+
+def tc_sddmm(plan, n_w, dy_bf16, x_bf16, dws, mask=None):
+    """dws[g][u, k] += mask * sum_m dy[m, (u,g)] x[m, k]   (dws zero-initialised by the caller)"""
+    _require_cuda(mask, *dws)
+    _require_cuda_any(dy_bf16, x_bf16)
+    assert dy_bf16.dtype == torch.bfloat16 and x_bf16.dtype == torch.bfloat16
+    assert dy_bf16.shape[0] == x_bf16.shape[0] and len(dws) == n_w
+    _check(load().hcgs_tc_sddmm(plan.handle, int(n_w), _ptr(dy_bf16), dy_bf16.stride(0), _ptr(x_bf16),
+                                x_bf16.stride(0), x_bf16.shape[0], _ptrs(dws), _row_major_2d(dws[0], 'dw'),
+                                _ptr(mask), _stream()), 'hcgs_tc_sddmm')
 
 
 def cast_bf16(x2d, out):

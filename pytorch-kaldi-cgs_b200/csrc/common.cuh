@@ -85,6 +85,9 @@ struct hcgs_plan {
     int* d_col_ptr = nullptr;  // [tc+1]   CSC over tiles
     int* d_row_idx = nullptr;  // [nz]
     int* d_tile_rc = nullptr;  // [nz*2]   (tile row, tile col) flat list for the SDDMM
+    int* d_csc_rc = nullptr;   // [nz*2]   (tile row, tile col) in CSC order (tensor-core nn GEMM weight tiles)
+    int* d_sd_items = nullptr; // [n_sd_items*3] (tile row, first CSR tile, count<=4): tensor-core SDDMM work items
+    int n_sd_items = 0;
     int max_row_tiles = 0, max_col_tiles = 0;
     bool recurrent = false;
     hcgs::RecurrentPlan rp;

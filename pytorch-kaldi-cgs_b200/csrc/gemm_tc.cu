@@ -416,3 +416,383 @@ extern "C" int hcgs_cast_bf16(const float* x, int64_t ldx, int64_t rows, int col
     HCGS_LAUNCH_CHECK();
     return 0;
 }
+
+namespace hcgs {
+
+// ---- nn: dX = dY W ------------------------------------------------------------------------------
+// Work item = (column block c of W, 128-row tile of dY).  The reduction runs over the kept tile
+// rows r of that column (CSC) and the 32*NG (unit, gate) columns of dY that belong to r.
+//   A = dY box [128 rows x KCH k] K-major (TMA), B = W^T tile [32 kcols x KCH k] K-major (pre-swizzled)
+//   NG = 4: KCH = 64 (SWIZZLE_128B), two sub-tiles per r;  NG = 1: KCH = 32 (SWIZZLE_64B).
+template <int NG>
+struct NnCfg {
+    static constexpr int KCH = NG == 4 ? 64 : 32;
+    static constexpr int NSUB = NG == 4 ? 2 : 1;
+    static constexpr int A_SUB = 128 * KCH * 2;
+    static constexpr int B_SUB = 32 * KCH * 2;
+    static constexpr int STAGE = NSUB * (A_SUB + B_SUB);
+    static constexpr int STAGES = NG == 4 ? 2 : 4;
+    static constexpr uint32_t SW = NG == 4 ? UMMA_SW128 : UMMA_SW64;
+    static constexpr uint32_t SBO = 8 * KCH * 2;
+    static constexpr int SMEM = 1024 + STAGES * STAGE + 256;
+};
+
+template <int NG>
+__global__ void tc_pack_nn_kernel(const int* __restrict__ csc_rc, int nz, PtrPack<const float> W, int ldw, int n_out,
+                                  int n_in, __nv_bfloat16* __restrict__ out) {
+    using C = NnCfg<NG>;
+    constexpr int CPR = C::KCH / 8;  // 16-byte chunks per row
+    const int64_t total = (int64_t)nz * C::NSUB * 32 * CPR;
+    for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+         idx += (int64_t)gridDim.x * blockDim.x) {
+        const int c16 = (int)(idx % CPR);
+        const int kc = (int)((idx / CPR) % 32);
+        const int h = (int)((idx / (CPR * 32)) % C::NSUB);
+        const int e = (int)(idx / (CPR * 32 * C::NSUB));
+        const int r = csc_rc[2 * e], c = csc_rc[2 * e + 1];
+        const int col = c * 32 + kc;
+        float v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int n = h * C::KCH + c16 * 8 + j;
+            const int u = n / NG, g = n % NG;
+            const int row = r * 32 + u;
+            v[j] = (row < n_out && col < n_in) ? __ldg(W.p[g] + (int64_t)row * ldw + col) : 0.f;
+        }
+        uint32_t w[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const __nv_bfloat162 p = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+            w[j] = *reinterpret_cast<const uint32_t*>(&p);
+        }
+        const int sw = (NG == 4) ? (kc & 7) : ((kc >> 1) & 3);
+        unsigned char* dst = reinterpret_cast<unsigned char*>(out) + (size_t)e * (C::NSUB * C::B_SUB) + h * C::B_SUB +
+                             kc * (C::KCH * 2) + ((c16 ^ sw) << 4);
+        *reinterpret_cast<uint4*>(dst) = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+}
+
+struct TcNnArgs {
+    const __nv_bfloat16* wpack;  // nn tiles, CSC order
+    const int* col_ptr;          // [tc+1]
+    const int* row_idx;          // [nz]
+    float* dx;                   // [M, lddx]
+    int64_t lddx;
+    int64_t M;
+    int n_in;
+};
+
+template <int NG>
+__global__ void __launch_bounds__(128) tc_gemm_nn_kernel(const __grid_constant__ CUtensorMap tmDY, const TcNnArgs a) {
+    using C = NnCfg<NG>;
+    constexpr uint32_t IDESC = umma_idesc_bf16(128, 32, 0, 0);
+    extern __shared__ unsigned char smem_dyn[];
+    unsigned char* smem = reinterpret_cast<unsigned char*>(((uintptr_t)smem_dyn + 1023) & ~(uintptr_t)1023);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::STAGES * C::STAGE);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * C::STAGES + 1);
+    const uint32_t full0 = g_smem_u32(bars), empty0 = g_smem_u32(bars + C::STAGES),
+                   done = g_smem_u32(bars + 2 * C::STAGES);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int c = blockIdx.x;
+    const int64_t m0 = (int64_t)blockIdx.y * 128;
+    const int k0 = a.col_ptr[c], nk = a.col_ptr[c + 1] - k0;
+
+    if (warp == 0 && lane == 0) {
+        for (int s = 0; s < C::STAGES; ++s) {
+            g_mbar_init(full0 + 8 * s, 1);
+            g_mbar_init(empty0 + 8 * s, 1);
+        }
+        g_mbar_init(done, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) tmem_alloc<32>(g_smem_u32(tmem_slot));
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp == 0 && lane == 0) {
+        for (int i = 0; i < nk; ++i) {
+            const int s = i % C::STAGES;
+            if (i >= C::STAGES) g_mbar_wait(empty0 + 8 * s, (uint32_t)(((i / C::STAGES) - 1) & 1));
+            g_mbar_expect_tx(full0 + 8 * s, C::STAGE);
+            const int r = a.row_idx[k0 + i];
+            unsigned char* st = smem + s * C::STAGE;
+#pragma unroll
+            for (int h = 0; h < C::NSUB; ++h)
+                tma_load_2d(g_smem_u32(st + h * C::A_SUB), &tmDY, r * 32 * NG + h * C::KCH, (int)m0, full0 + 8 * s);
+            bulk_load_1d(g_smem_u32(st + C::NSUB * C::A_SUB),
+                         reinterpret_cast<const unsigned char*>(a.wpack) + (size_t)(k0 + i) * (C::NSUB * C::B_SUB),
+                         C::NSUB * C::B_SUB, full0 + 8 * s);
+        }
+    } else if (warp == 1 && lane == 0) {
+        for (int i = 0; i < nk; ++i) {
+            const int s = i % C::STAGES;
+            g_mbar_wait(full0 + 8 * s, (uint32_t)((i / C::STAGES) & 1));
+            tc_fence_after();
+            const uint32_t base = g_smem_u32(smem + s * C::STAGE);
+#pragma unroll
+            for (int h = 0; h < C::NSUB; ++h)
+#pragma unroll
+                for (int kk = 0; kk < C::KCH / 16; ++kk) {
+                    const uint64_t ad = umma_smem_desc(base + h * C::A_SUB + kk * 32, 16, C::SBO, C::SW);
+                    const uint64_t bd =
+                        umma_smem_desc(base + C::NSUB * C::A_SUB + h * C::B_SUB + kk * 32, 16, C::SBO, C::SW);
+                    umma_bf16(tmem, ad, bd, IDESC, (i > 0 || h > 0 || kk > 0) ? 1u : 0u);
+                }
+            umma_commit(empty0 + 8 * s);
+        }
+        umma_commit(done);
+    }
+    __syncwarp();
+    float v[32];
+    if (nk > 0) {
+        g_mbar_wait(done, 0);
+        tc_fence_after();
+        tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16), v);
+    } else {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = 0.f;
+    }
+    const int64_t m = m0 + warp * 32 + lane;
+    if (m < a.M) {
+        float* dst = a.dx + m * a.lddx + c * 32;
+        const bool vec = ((a.lddx & 3) == 0) && ((reinterpret_cast<uintptr_t>(a.dx) & 15) == 0) && (c * 32 + 32 <= a.n_in);
+        if (vec) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+                *reinterpret_cast<float4*>(dst + 4 * i) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+        } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+                if (c * 32 + i < a.n_in) dst[i] = v[i];
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc<32>(tmem);
+}
+
+}  // namespace hcgs
+
+extern "C" int hcgs_tc_pack_nn(const hcgs_plan* plan, int n_w, const float* const* w, int ldw, void* wpack,
+                               hcgs_stream stream) {
+    HCGS_REQUIRE(plan && w && wpack, "hcgs_tc_pack_nn: NULL argument");
+    HCGS_REQUIRE(n_w == 1 || n_w == 4, "hcgs_tc_pack_nn: n_w must be 1 or 4");
+    if (plan->nz_tiles == 0) return 0;
+    const int64_t total = (int64_t)plan->nz_tiles * 32 * n_w * 4;
+    const int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 8);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n_w == 4)
+        tc_pack_nn_kernel<4><<<blocks, 256, 0, st>>>(plan->d_csc_rc, plan->nz_tiles, make_pack<const float>(w, 4), ldw,
+                                                     plan->n_out, plan->n_in, (__nv_bfloat16*)wpack);
+    else
+        tc_pack_nn_kernel<1><<<blocks, 256, 0, st>>>(plan->d_csc_rc, plan->nz_tiles, make_pack<const float>(w, 1), ldw,
+                                                     plan->n_out, plan->n_in, (__nv_bfloat16*)wpack);
+    HCGS_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int hcgs_tc_gemm_nn(const hcgs_plan* plan, int n_w, const void* wpack, const void* dy_bf16, int64_t lddy,
+                               int64_t m, float* dx, int64_t lddx, hcgs_stream stream) {
+    HCGS_REQUIRE(plan && wpack && dy_bf16 && dx, "hcgs_tc_gemm_nn: NULL argument");
+    HCGS_REQUIRE(n_w == 1 || n_w == 4, "hcgs_tc_gemm_nn: n_w must be 1 or 4");
+    if (m <= 0) return 0;
+    CUtensorMap tm;
+    const int kch = n_w == 4 ? 64 : 32;
+    // global width = lddy: pad columns of dY are zero by contract, tiles past n_out*n_w read zeros / OOB zero fill
+    if (int rc = make_tmap_bf16(&tm, dy_bf16, m, lddy, lddy, kch, 128,
+                                n_w == 4 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B))
+        return rc;
+    TcNnArgs a;
+    a.wpack = (const __nv_bfloat16*)wpack;
+    a.col_ptr = plan->d_col_ptr;
+    a.row_idx = plan->d_row_idx;
+    a.dx = dx;
+    a.lddx = lddx;
+    a.M = m;
+    a.n_in = plan->n_in;
+    const int64_t mt = (m + 127) / 128;
+    HCGS_REQUIRE(mt <= 65535, "hcgs_tc_gemm_nn: too many rows (%lld)", (long long)m);
+    dim3 grid(plan->tc, (unsigned)mt, 1);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n_w == 4) {
+        HCGS_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm_nn_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             NnCfg<4>::SMEM));
+        tc_gemm_nn_kernel<4><<<grid, 128, NnCfg<4>::SMEM, st>>>(tm, a);
+    } else {
+        HCGS_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm_nn_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             NnCfg<1>::SMEM));
+        tc_gemm_nn_kernel<1><<<grid, 128, NnCfg<1>::SMEM, st>>>(tm, a);
+    }
+    HCGS_LAUNCH_CHECK();
+    return 0;
+}
+
+namespace hcgs {
+
+// ---- sddmm: dW = mask .* (dY^T X) on the kept tiles ------------------------------------------------
+// Work item = (tile row r, group of <= 4 kept tile columns, split of the m rows).  Both operands are
+// MN-major (the reduction index m is the slow dimension of the row-major activations):
+//   A = X^T  : M = 128 = 4 kept column blocks x 32, each block one TMA box [32 cols x RK rows] (SWIZZLE_64B atom)
+//   B = dY^T : N = 32*NG (unit, gate) columns of tile row r; NG = 4: two boxes [64 x RK] (SWIZZLE_128B atoms)
+//   D[kc, (u,g)] = dW_g[r*32+u, c*32+kc]  (transposed tile) -> fp32 atomics, re-masked on the way out.
+constexpr int SD_RK = 64;       // m rows per stage
+constexpr int SD_STAGES = 4;
+constexpr int SD_A_ATOM = SD_RK * 64;
+
+template <int NG>
+struct SdCfg {
+    static constexpr int BN = 32 * NG;
+    static constexpr int B_BYTES = SD_RK * BN * 2;
+    static constexpr int STAGE = 4 * SD_A_ATOM + B_BYTES;
+    static constexpr int SMEM = 1024 + SD_STAGES * STAGE + 256;
+    static constexpr int TCOLS = BN < 32 ? 32 : BN;
+};
+
+struct TcSdArgs {
+    const int* items;    // [n_items][3] (tile row, first CSR tile, count)
+    const int* col_idx;  // [nz]
+    PtrPack<float> dw;   // per gate [n_out, lddw] fp32, accumulated atomically
+    int64_t lddw;
+    const float* mask;   // [n_out, n_in] or NULL
+    int64_t M, rows_per_split;
+    int n_out, n_in;
+};
+
+template <int NG>
+__global__ void __launch_bounds__(128) tc_sddmm_kernel(const __grid_constant__ CUtensorMap tmX,
+                                                       const __grid_constant__ CUtensorMap tmDY, const TcSdArgs a) {
+    using C = SdCfg<NG>;
+    constexpr uint32_t IDESC = umma_idesc_bf16(128, C::BN, 1, 1);
+    extern __shared__ unsigned char smem_dyn[];
+    unsigned char* smem = reinterpret_cast<unsigned char*>(((uintptr_t)smem_dyn + 1023) & ~(uintptr_t)1023);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + SD_STAGES * C::STAGE);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * SD_STAGES + 1);
+    const uint32_t full0 = g_smem_u32(bars), empty0 = g_smem_u32(bars + SD_STAGES),
+                   done = g_smem_u32(bars + 2 * SD_STAGES);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int r = a.items[3 * blockIdx.x], t0 = a.items[3 * blockIdx.x + 1], cnt = a.items[3 * blockIdx.x + 2];
+    const int64_t mbeg = (int64_t)blockIdx.y * a.rows_per_split;
+    const int64_t mend = (mbeg + a.rows_per_split < a.M) ? mbeg + a.rows_per_split : a.M;
+    const int nk = mend > mbeg ? (int)((mend - mbeg + SD_RK - 1) / SD_RK) : 0;
+
+    if (warp == 0 && lane == 0) {
+        for (int s = 0; s < SD_STAGES; ++s) {
+            g_mbar_init(full0 + 8 * s, 1);
+            g_mbar_init(empty0 + 8 * s, 1);
+        }
+        g_mbar_init(done, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) tmem_alloc<C::TCOLS>(g_smem_u32(tmem_slot));
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp == 0 && lane == 0) {
+        for (int i = 0; i < nk; ++i) {
+            const int s = i % SD_STAGES;
+            if (i >= SD_STAGES) g_mbar_wait(empty0 + 8 * s, (uint32_t)(((i / SD_STAGES) - 1) & 1));
+            g_mbar_expect_tx(full0 + 8 * s, cnt * SD_A_ATOM + C::B_BYTES);
+            unsigned char* st = smem + s * C::STAGE;
+            const int row = (int)(mbeg + (int64_t)i * SD_RK);
+            // splits are multiples of SD_RK rows (host), so only the global tail is ragged: TMA zero-fills it
+            for (int j = 0; j < cnt; ++j)
+                tma_load_2d(g_smem_u32(st + j * SD_A_ATOM), &tmX, a.col_idx[t0 + j] * 32, row, full0 + 8 * s);
+            if (NG == 4) {
+                tma_load_2d(g_smem_u32(st + 4 * SD_A_ATOM), &tmDY, r * 128, row, full0 + 8 * s);
+                tma_load_2d(g_smem_u32(st + 4 * SD_A_ATOM + SD_RK * 128), &tmDY, r * 128 + 64, row, full0 + 8 * s);
+            } else {
+                tma_load_2d(g_smem_u32(st + 4 * SD_A_ATOM), &tmDY, r * 32, row, full0 + 8 * s);
+            }
+        }
+    } else if (warp == 1 && lane == 0) {
+        for (int i = 0; i < nk; ++i) {
+            const int s = i % SD_STAGES;
+            g_mbar_wait(full0 + 8 * s, (uint32_t)((i / SD_STAGES) & 1));
+            tc_fence_after();
+            const uint32_t abase = g_smem_u32(smem + s * C::STAGE), bbase = abase + 4 * SD_A_ATOM;
+#pragma unroll
+            for (int kk = 0; kk < SD_RK / 16; ++kk) {  // 16 m rows per MMA = two 8-row groups
+                const uint64_t ad = umma_smem_desc(abase + kk * 1024, SD_A_ATOM, 512, UMMA_SW64);
+                const uint64_t bd = (NG == 4) ? umma_smem_desc(bbase + kk * 2048, SD_RK * 128, 1024, UMMA_SW128)
+                                              : umma_smem_desc(bbase + kk * 1024, SD_A_ATOM, 512, UMMA_SW64);
+                umma_bf16(tmem, ad, bd, IDESC, (i > 0 || kk > 0) ? 1u : 0u);
+            }
+            umma_commit(empty0 + 8 * s);
+        }
+        umma_commit(done);
+    }
+    __syncwarp();
+    if (nk > 0 && warp < cnt) {  // warp w owns kept column block w of the group; lane = column inside it
+        g_mbar_wait(done, 0);
+        tc_fence_after();
+        const int col = a.col_idx[t0 + warp] * 32 + lane;
+#pragma unroll 1
+        for (int cb = 0; cb < C::BN / 32; ++cb) {
+            float v[32];
+            tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + cb * 32, v);
+            if (col < a.n_in) {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    const int n = cb * 32 + i, u = n / NG, g = n % NG;
+                    const int row = r * 32 + u;
+                    if (row < a.n_out) {
+                        float o = v[i];
+                        if (a.mask) o *= __ldg(a.mask + (int64_t)row * a.n_in + col);
+                        if (o != 0.f) atomicAdd(a.dw.p[g] + (int64_t)row * a.lddw + col, o);
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc<C::TCOLS>(tmem);
+}
+
+}  // namespace hcgs
+
+extern "C" int hcgs_tc_sddmm(const hcgs_plan* plan, int n_w, const void* dy_bf16, int64_t lddy, const void* x_bf16,
+                             int64_t ldx, int64_t m, float* const* dw, int64_t lddw, const float* mask,
+                             hcgs_stream stream) {
+    HCGS_REQUIRE(plan && dy_bf16 && x_bf16 && dw, "hcgs_tc_sddmm: NULL argument");
+    HCGS_REQUIRE(n_w == 1 || n_w == 4, "hcgs_tc_sddmm: n_w must be 1 or 4");
+    if (m <= 0 || plan->n_sd_items == 0) return 0;
+    CUtensorMap tmx, tmdy;
+    if (int rc = make_tmap_bf16(&tmx, x_bf16, m, plan->n_in, ldx, 32, SD_RK, CU_TENSOR_MAP_SWIZZLE_64B)) return rc;
+    if (int rc = make_tmap_bf16(&tmdy, dy_bf16, m, lddy, lddy, n_w == 4 ? 64 : 32, SD_RK,
+                                n_w == 4 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B))
+        return rc;
+    // enough CTAs for ~4 per SM; a split is a multiple of SD_RK rows
+    int splits = std::max(1, (148 * 4 + plan->n_sd_items - 1) / plan->n_sd_items);
+    int64_t rows = (m + splits - 1) / splits;
+    rows = std::max<int64_t>((rows + SD_RK - 1) / SD_RK * SD_RK, 4 * SD_RK);
+    splits = (int)((m + rows - 1) / rows);
+    HCGS_REQUIRE(splits <= 65535, "hcgs_tc_sddmm: too many splits");
+    TcSdArgs a;
+    a.items = plan->d_sd_items;
+    a.col_idx = plan->d_col_idx;
+    a.dw = make_pack<float>(dw, n_w);
+    a.lddw = lddw;
+    a.mask = mask;
+    a.M = m;
+    a.rows_per_split = rows;
+    a.n_out = plan->n_out;
+    a.n_in = plan->n_in;
+    dim3 grid(plan->n_sd_items, splits, 1);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n_w == 4) {
+        HCGS_CHECK_CUDA(cudaFuncSetAttribute(tc_sddmm_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             SdCfg<4>::SMEM));
+        tc_sddmm_kernel<4><<<grid, 128, SdCfg<4>::SMEM, st>>>(tmx, tmdy, a);
+    } else {
+        HCGS_CHECK_CUDA(cudaFuncSetAttribute(tc_sddmm_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             SdCfg<1>::SMEM));
+        tc_sddmm_kernel<1><<<grid, 128, SdCfg<1>::SMEM, st>>>(tmx, tmdy, a);
+    }
+    HCGS_LAUNCH_CHECK();
+    return 0;
+}

@@ -174,7 +174,22 @@ extern "C" int hcgs_plan_create(const float* mask, int n_out, int n_in, int recu
     }
     col_ptr[p->tc] = (int)row_idx.size();
     p->nz_tiles = (int)col_idx.size();
+    std::vector<int> csc_rc, sd_items;
+    for (int j = 0; j < p->tc; ++j)
+        for (int e = col_ptr[j]; e < col_ptr[j + 1]; ++e) {
+            csc_rc.push_back(row_idx[e]);
+            csc_rc.push_back(j);
+        }
+    for (int i = 0; i < p->tr; ++i)
+        for (int t0 = row_ptr[i]; t0 < row_ptr[i + 1]; t0 += 4) {
+            sd_items.push_back(i);
+            sd_items.push_back(t0);
+            sd_items.push_back(std::min(4, row_ptr[i + 1] - t0));
+        }
+    p->n_sd_items = (int)sd_items.size() / 3;
     int rc = 0;
+    rc |= upload(csc_rc, &p->d_csc_rc);
+    rc |= upload(sd_items, &p->d_sd_items);
     rc |= upload(row_ptr, &p->d_row_ptr);
     rc |= upload(col_idx, &p->d_col_idx);
     rc |= upload(col_ptr, &p->d_col_ptr);
@@ -258,6 +273,8 @@ extern "C" int hcgs_plan_destroy(hcgs_plan* p) {
     cudaFree(p->d_col_ptr);
     cudaFree(p->d_row_idx);
     cudaFree(p->d_tile_rc);
+    cudaFree(p->d_csc_rc);
+    cudaFree(p->d_sd_items);
     cudaFree(p->rp.d_bidx);
     cudaFree(p->rp.d_cta_blk_off);
     cudaFree(p->rp.d_blk_a);

@@ -52,3 +52,58 @@ def test_tc_gemm_nt(n_out, n_in, blocks, drops, n_w, M):
     got = y.cpu().view(M, ldo, n_w)[:, :n_out, :]
     close(got, ref, 2e-5, 'nt')
     plan.destroy()
+
+
+def _dy_layout(dy_list, M, n_out, n_w, ld_units):
+    """list of per-gate [M, n_out] -> bf16-able fp32 [M, ld_units*n_w], column u*n_w+g, pad columns zero"""
+    out = torch.zeros(M, ld_units, n_w)
+    for g, t in enumerate(dy_list):
+        out[:, :n_out, g] = t
+    return out.view(M, ld_units * n_w)
+
+
+@pytest.mark.parametrize('n_out,n_in,blocks,drops,n_w,M', CASES)
+def test_tc_gemm_nn_and_sddmm(n_out, n_in, blocks, drops, n_w, M):
+    from b200 import native
+    torch.manual_seed(n_out + n_in + M + 1)
+    mask = random_mask(n_out, n_in, blocks, drops, 7) if blocks else torch.ones(n_out, n_in)
+    plan = native.Plan(mask)
+    d = dev()
+    ws = [torch.randn(n_out, n_in) * mask for _ in range(n_w)]
+    x = torch.randn(M, n_in)
+    dys = [torch.randn(M, n_out) for _ in range(n_w)]
+    ldu = native.pad8(n_out)
+    dyb = torch.empty(M, ldu * n_w, device=d, dtype=torch.bfloat16)
+    native.cast_bf16(_dy_layout(dys, M, n_out, n_w, ldu).to(d), dyb)
+    xb = torch.empty(M, native.pad8(n_in), device=d, dtype=torch.bfloat16)
+    native.cast_bf16(x.to(d), xb)
+    # data gradient
+    wpack = torch.empty(max(plan.nz_tiles, 1) * 32 * n_w * 32, device=d, dtype=torch.bfloat16)
+    native.tc_pack_nn(plan, [w.to(d) for w in ws], wpack)
+    dx = torch.full((M, n_in), 9.0, device=d)
+    native.tc_gemm_nn(plan, n_w, wpack, dyb, dx)
+    torch.cuda.synchronize()
+    ref = sum(bf(dys[g]) @ bf(ws[g]) for g in range(n_w))
+    close(dx, ref, 3e-5, 'nn')
+    # weight gradient (two launches accumulate: atomics into a caller-zeroed buffer)
+    dws = [torch.zeros(n_out, n_in, device=d) for _ in range(n_w)]
+    native.tc_sddmm(plan, n_w, dyb, xb, dws, mask.to(d))
+    torch.cuda.synchronize()
+    for g in range(n_w):
+        refw = (bf(dys[g]).t() @ bf(x)) * mask
+        close(dws[g], refw, 3e-5, 'sddmm gate %d' % g)
+    # shifted operands = the recurrent weight gradient dU = sum_t dpre[t]^T h[t-1]
+    if M > 40:
+        dws2 = [torch.zeros(n_out, n_in, device=d) for _ in range(n_w)]
+        native.tc_sddmm(plan, n_w, dyb[8:], xb[:M - 8], dws2, None)
+        torch.cuda.synchronize()
+        keep = torch.zeros(n_out, n_in)
+        tr, tc_ = (n_out + 31) // 32, (n_in + 31) // 32
+        for i in range(tr):
+            for j in range(tc_):
+                if mask[i * 32:(i + 1) * 32, j * 32:(j + 1) * 32].any():
+                    keep[i * 32:(i + 1) * 32, j * 32:(j + 1) * 32] = 1
+        for g in range(n_w):
+            refw = (bf(dys[g])[8:].t() @ bf(x)[:M - 8]) * keep
+            close(dws2[g], refw, 3e-5, 'sddmm shifted gate %d' % g)
+    plan.destroy()
