@@ -44,6 +44,32 @@ def _ste(x, xq):
     return x + (xq - x).detach()
 
 
+def _bf(x):
+    return x.to(torch.bfloat16).to(torch.float32)
+
+
+class _RoundGrad(torch.autograd.Function):
+    """identity whose incoming gradient is rounded to bf16"""
+
+    @staticmethod
+    def forward(ctx, x):
+        return x.view_as(x)
+
+    @staticmethod
+    def backward(ctx, g):
+        return _bf(g)
+
+
+def linear(x, w, b=None, bf16=False):
+    """F.linear; with bf16=True the three matrix products of the layer (forward, dX, dW) take bf16-rounded
+    operands (x, w, and the incoming gradient) and accumulate in fp32 -- the arithmetic of the tensor-core
+    build (spec key 'bf16_operands').  Bias and its gradient stay fp32."""
+    if not bf16:
+        return F.linear(x, w, b)
+    y = _RoundGrad.apply(F.linear(_ste(x, _bf(x.detach())), _ste(w, _bf(w.detach()))))
+    return y if b is None else y + b
+
+
 def quantize_w_t(w, bits):
     """Quantize(balanced=False) (quantized_modules.py:77-97) on a tensor; returns STE tensor."""
     wc = w.detach().clamp(-1, 1)
@@ -72,6 +98,7 @@ def lstm_forward(p, spec, x, drop_masks, training):
     quant_inp (bits or 0).  drop_masks: list of [B,H] tensors (train) -- the reference draws them
     with torch.bernoulli on the CPU generator (:843-845); in eval the scalar (1-p) is used (:847).
     BN running statistics in `p` are updated in place when training (momentum 0.05)."""
+    bfo = bool(spec.get('bf16_operands', False))
     for i, H in enumerate(spec['lay']):
         T, B, _ = x.shape
         drop = drop_masks[i] if training else torch.tensor([1 - spec['drop'][i]])
@@ -90,7 +117,7 @@ def lstm_forward(p, spec, x, drop_masks, training):
             xin = quantize_inp_t(x, spec['quant_inp'], 4)                 # four gate linears re-quantise x
         pre = {}
         for g in GATES:
-            out = F.linear(xin, w[g])                                     # :951-954
+            out = linear(xin, w[g], None, bfo)                            # :951-954
             if spec['use_bn'][i]:
                 k = 'bn_w%sx.%d.' % (g, i)
                 out = F.batch_norm(out.view(T * B, H), p[k + 'running_mean'], p[k + 'running_var'], p[k + 'weight'],
@@ -105,10 +132,10 @@ def lstm_forward(p, spec, x, drop_masks, training):
             if spec.get('quant_inp', 0) and k > 0:
                 hq = quantize_inp_t(ht, spec['quant_inp'], 4)
                 hs[-1] = hq                                               # the stacked copy is the swapped tensor
-            ft = torch.sigmoid(pre['f'][k] + F.linear(hq, u['f']))
-            it = torch.sigmoid(pre['i'][k] + F.linear(hq, u['i']))
-            ot = torch.sigmoid(pre['o'][k] + F.linear(hq, u['o']))
-            ct = it * act(a, pre['c'][k] + F.linear(hq, u['c'])) * drop + ft * ct
+            ft = torch.sigmoid(pre['f'][k] + linear(hq, u['f'], None, bfo))
+            it = torch.sigmoid(pre['i'][k] + linear(hq, u['i'], None, bfo))
+            ot = torch.sigmoid(pre['o'][k] + linear(hq, u['o'], None, bfo))
+            ct = it * act(a, pre['c'][k] + linear(hq, u['c'], None, bfo)) * drop + ft * ct
             ht = ot * act(a, ct)
             hs.append(ht)
         x = torch.stack(hs)                                               # :1100
@@ -126,7 +153,7 @@ def mlp_forward(p, spec, x, training, drop_masks=None):
             w = quantize_w_t(w, spec['quant'])
         if spec.get('quant_inp', 0):
             x = quantize_inp_t(x, spec['quant_inp'], 1)
-        z = F.linear(x, w, b)
+        z = linear(x, w, b, bool(spec.get('bf16_operands', False)))
         if spec['use_bn'][i]:
             k = 'bn.%d.' % i
             z = F.batch_norm(z, p[k + 'running_mean'], p[k + 'running_var'], p[k + 'weight'], p[k + 'bias'],

@@ -34,6 +34,10 @@ class LayerRuntime:
         # quantised weights, the gradient lands on the fp32 master -- straight-through)
         self.q_ws = None
         self.q_us = None
+        # tensor-core build: bf16 copy of the layer input handed over by the previous layer, and of
+        # this layer's output for the next one (saves a cast pass per layer)
+        self.xb_in = None
+        self.hb_out = None
 
 
 def _ws(device, n_cols):
@@ -194,4 +198,223 @@ class MLPLayerFunction(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             dx = torch.empty(N, D, device=dev, dtype=torch.float32)
             native.bsgemm_nn(rt.plan_x, [w], dz, dx)
+        return dx, dw, db, dgamma, dbeta, None
+
+
+# ---------------------------------------------------------------------------------------------
+# bf16 tensor-core build (b200_precision = bf16): tcgen05 block-sparse GEMMs + mma.sync recurrence.
+# Operands (x, W, U, h_{t-1}, dpre) are rounded to bf16, every accumulation and all gate / cell /
+# BN / softmax math stays fp32.  Buffers are gate-interleaved and padded (column u*4+g, ldH = pad8(H)).
+# ---------------------------------------------------------------------------------------------
+
+def tc_config_for(plan, batch):
+    """Cluster shape of the tensor-core recurrence.  Cluster 8 has the lower step latency; cluster 4 keeps
+    twice as many groups of 16 sequences co-resident, so it wins as soon as cluster 8 would run in waves."""
+    cache = plan.__dict__.setdefault('_tc_cfgs', {})
+
+    def get(cl):
+        if cl not in cache:
+            try:
+                cfg = native.TcConfig(plan, cl, 16 if cl else 0)
+                cache[cl] = cfg if (cl == 0 or cfg.cluster_size == cl) else None
+            except native.NativeError:
+                if cl == 0:
+                    raise
+                cache[cl] = None
+        return cache[cl]
+
+    groups = (batch + 15) // 16
+    c8, c4 = get(8), get(4)
+    if c8 is not None and (c4 is None or groups <= min(c8.max_clusters_fwd, c8.max_clusters_bwd)):
+        return c8
+    if c4 is not None:
+        return c4
+    return get(0)   # raises with the library's message if no cluster shape fits
+
+
+def _bf16_rows(x2d, ld):
+    out = torch.empty(x2d.shape[0], ld, device=x2d.device, dtype=torch.bfloat16)
+    native.cast_bf16(x2d, out)
+    return out
+
+
+class LSTMLayerTCFunction(torch.autograd.Function):
+    """One HCGS LSTM layer on the tensor-core build (same math as LSTMLayerFunction)."""
+
+    @staticmethod
+    def forward(ctx, x, wf, wi, wo, wc, uf, ui, uo, uc, gf, bf, gi, bi, go, bo, gc, bc, rt):
+        T, B, D = x.shape
+        H = wf.shape[0]
+        M = T * B
+        ldH = native.pad8(H)
+        ldD = native.pad8(D)
+        dev = x.device
+        ws = rt.q_ws if rt.q_ws is not None else [wf, wi, wo, wc]
+        us = rt.q_us if rt.q_us is not None else [uf, ui, uo, uc]
+        need_grad = any(ctx.needs_input_grad)
+        xb = rt.xb_in
+        if xb is None or xb.shape != (M, ldD):
+            x2d = x.reshape(M, D)
+            if x2d.stride(-1) != 1:
+                x2d = x2d.contiguous()
+            xb = _bf16_rows(x2d, ldD)
+        px = rt.plan_x
+        wpack = torch.empty(px.nz_tiles * 32 * 4 * 32, device=dev, dtype=torch.bfloat16)
+        native.tc_pack_nt(px, ws, wpack)
+        pre_raw = torch.empty(M, 4 * ldH, device=dev, dtype=torch.float32)
+        native.tc_gemm_nt(px, 4, wpack, xb, pre_raw)
+        save_mean = save_invstd = None
+        if rt.use_bn:
+            pre = torch.empty_like(pre_raw)
+            save_mean = torch.empty(4 * ldH, device=dev, dtype=torch.float32)
+            save_invstd = torch.empty(4 * ldH, device=dev, dtype=torch.float32)
+            rms = [r[0] for r in rt.bn_running]
+            rvs = [r[1] for r in rt.bn_running]
+            native.bn_fwd_il(pre_raw, pre, 4, H, ldH, [gf, gi, go, gc], [bf, bi, bo, bc], rms, rvs, rt.bn_eps,
+                             rt.bn_momentum, rt.training, save_mean, save_invstd, _ws(dev, 4 * ldH))
+        else:
+            pre = pre_raw
+        ph = rt.plan_h
+        cfg = tc_config_for(ph, B)
+        fwd_pack = torch.empty(cfg.fwd_pack_u32, device=dev, dtype=torch.int32)
+        bwd_pack = torch.empty(max(cfg.bwd_pack_u32, 1), device=dev, dtype=torch.int32) if need_grad else None
+        native.lstm_tc_pack(ph, cfg, us, fwd_pack, bwd_pack)
+        h = torch.empty(T, B, H, device=dev, dtype=torch.float32)
+        hb = torch.empty(M, ldH, device=dev, dtype=torch.bfloat16)
+        c = gates = None
+        if need_grad:
+            c = torch.empty(M, ldH, device=dev, dtype=torch.float32)
+            gates = torch.empty(M, 4 * ldH, device=dev, dtype=torch.float32)
+        native.lstm_tc_fwd(ph, cfg, fwd_pack, pre, rt.drop, rt.drop_scalar, rt.act, T, B, h.view(M, H), hb, c, gates)
+        rt.hb_out = hb
+        if need_grad:
+            ctx.rt = rt
+            ctx.cfg = cfg
+            ctx.dims = (T, B, D, H)
+            ctx.drop = rt.drop
+            ctx.drop_scalar = rt.drop_scalar
+            ctx.save_for_backward(xb, ws[0], ws[1], ws[2], ws[3], gf, gi, go, gc, pre_raw, save_mean, save_invstd,
+                                  c, gates, bwd_pack, hb)
+        return h
+
+    @staticmethod
+    def backward(ctx, dh):
+        rt = ctx.rt
+        T, B, D, H = ctx.dims
+        M = T * B
+        ldH = native.pad8(H)
+        (xb, wf, wi, wo, wc, gf, gi, go, gc, pre_raw, save_mean, save_invstd, c, gates, bwd_pack,
+         hb) = ctx.saved_tensors
+        dev = dh.device
+        dh = dh.contiguous()
+        dpre = torch.empty(M, 4 * ldH, device=dev, dtype=torch.float32)
+        dpre_b = torch.empty(M, 4 * ldH, device=dev, dtype=torch.bfloat16)
+        native.lstm_tc_bwd(rt.plan_h, ctx.cfg, bwd_pack, dh.view(M, H), gates, c, ctx.drop, ctx.drop_scalar, rt.act,
+                           T, B, dpre, dpre_b)
+        dgam = [None] * 4
+        dbet = [None] * 4
+        if rt.use_bn:
+            dproj_b = torch.empty(M, 4 * ldH, device=dev, dtype=torch.bfloat16)
+            dgam = [torch.empty(H, device=dev, dtype=torch.float32) for _ in range(4)]
+            dbet = [torch.empty(H, device=dev, dtype=torch.float32) for _ in range(4)]
+            native.bn_bwd_il(dpre, pre_raw, 4, H, ldH, [gf, gi, go, gc], save_mean, save_invstd, None, dproj_b,
+                             dgam, dbet, _ws(dev, 4 * ldH))
+        else:
+            dproj_b = dpre_b
+        del dpre
+        dus = [torch.zeros(H, H, device=dev, dtype=torch.float32) for _ in range(4)]
+        if T > 1:
+            native.tc_sddmm(rt.plan_h, 4, dpre_b[B:], hb[:M - B], dus, rt.mask_h)
+        dws = [torch.zeros(H, D, device=dev, dtype=torch.float32) for _ in range(4)]
+        native.tc_sddmm(rt.plan_x, 4, dproj_b, xb, dws, rt.mask_x)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            px = rt.plan_x
+            wpack = torch.empty(px.nz_tiles * 32 * 4 * 32, device=dev, dtype=torch.bfloat16)
+            native.tc_pack_nn(px, [wf, wi, wo, wc], wpack)
+            dx2d = torch.empty(M, D, device=dev, dtype=torch.float32)
+            native.tc_gemm_nn(px, 4, wpack, dproj_b, dx2d)
+            dx = dx2d.view(T, B, D)
+        return (dx, dws[0], dws[1], dws[2], dws[3], dus[0], dus[1], dus[2], dus[3],
+                dgam[0], dbet[0], dgam[1], dbet[1], dgam[2], dbet[2], dgam[3], dbet[3], None)
+
+
+class MLPLayerTCFunction(torch.autograd.Function):
+    """One MLP layer on the tensor-core build: tcgen05 GEMM with bf16 operands, fp32 everything else."""
+
+    @staticmethod
+    def forward(ctx, x, w, b, gamma, beta, rt):
+        N, D = x.shape
+        O = w.shape[0]
+        dev = x.device
+        xb = rt.xb_in
+        if xb is None or xb.shape != (N, native.pad8(D)):
+            xb = _bf16_rows(x if x.stride(-1) == 1 else x.contiguous(), native.pad8(D))
+        cw = rt.q_ws[0] if rt.q_ws is not None else w
+        px = rt.plan_x
+        wpack = torch.empty(px.nz_tiles * 32 * 32, device=dev, dtype=torch.bfloat16)
+        native.tc_pack_nt(px, [cw], wpack)
+        z = torch.empty(N, O, device=dev, dtype=torch.float32)
+        native.tc_gemm_nt(px, 1, wpack, xb, z, [b] if b is not None else None)
+        save_mean = save_invstd = None
+        if rt.use_bn:
+            zb = torch.empty_like(z)
+            save_mean = torch.empty(O, device=dev, dtype=torch.float32)
+            save_invstd = torch.empty(O, device=dev, dtype=torch.float32)
+            native.bn_fwd(z, zb, 1, O, [gamma], [beta], [rt.bn_running[0][0]], [rt.bn_running[0][1]], rt.bn_eps,
+                          rt.bn_momentum, rt.training, save_mean, save_invstd, _ws(dev, O))
+        else:
+            zb = z
+        out = torch.empty_like(z)
+        if rt.softmax:
+            native.logsoftmax_fwd(zb, out, rt.log_prior)
+        else:
+            native.act_fwd(zb, out, rt.mlp_drop_mask, rt.act)
+        if any(ctx.needs_input_grad):
+            ctx.rt = rt
+            ctx.softmax = rt.softmax
+            ctx.had_prior = rt.log_prior is not None
+            ctx.drop_mask = rt.mlp_drop_mask
+            ctx.out_store = out.detach()
+            ctx.save_for_backward(xb, cw, gamma, z if rt.use_bn else None, save_mean, save_invstd)
+            ctx.dims = (N, D, O)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        rt = ctx.rt
+        xb, w, gamma, z, save_mean, save_invstd = ctx.saved_tensors
+        N, D, O = ctx.dims
+        dev = dout.device
+        dout = dout.contiguous()
+        dzb = torch.empty(N, O, device=dev, dtype=torch.float32)
+        if ctx.softmax:
+            if ctx.had_prior:
+                raise native.NativeError('backward through a prior-normalised posterior is not defined')
+            native.logsoftmax_bwd(dout, ctx.out_store, dzb)
+        else:
+            native.act_bwd(dout, ctx.out_store, ctx.drop_mask, dzb, rt.act)
+        dgamma = dbeta = None
+        if rt.use_bn:
+            dz = torch.empty_like(dzb)
+            dgamma = torch.empty(O, device=dev, dtype=torch.float32)
+            dbeta = torch.empty(O, device=dev, dtype=torch.float32)
+            native.bn_bwd(dzb, z, 1, O, [gamma], save_mean, save_invstd, dz, [dgamma], [dbeta], _ws(dev, O))
+        else:
+            dz = dzb
+        db = None
+        if ctx.needs_input_grad[2]:
+            db = torch.empty(O, device=dev, dtype=torch.float32)
+            native.colsum(dz, 1, O, [db])
+        dz_b = _bf16_rows(dz, native.pad8(O))
+        del dz, dzb
+        dw = torch.zeros(O, D, device=dev, dtype=torch.float32)
+        native.tc_sddmm(rt.plan_x, 1, dz_b, xb, [dw], rt.mask_x)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            px = rt.plan_x
+            wpack = torch.empty(px.nz_tiles * 32 * 32, device=dev, dtype=torch.bfloat16)
+            native.tc_pack_nn(px, [w], wpack)
+            dx = torch.empty(N, D, device=dev, dtype=torch.float32)
+            native.tc_gemm_nn(px, 1, wpack, dz_b, dx)
         return dx, dw, db, dgamma, dbeta, None

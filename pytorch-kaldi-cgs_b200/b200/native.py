@@ -47,6 +47,10 @@ SIGNATURES = {
                             c_int, _f, _f, _f, c_int64, c_void_p]),
     'hcgs_bn_bwd': (c_int, [_f, c_int, _f, c_int, c_int64, c_int, c_int, _pp, _f, _f, _f, c_int, _pp, _pp, _f,
                             c_int64, c_void_p]),
+    'hcgs_bn_fwd_il': (c_int, [_f, _f, c_int64, c_int, c_int, c_int, _pp, _pp, _pp, _pp, c_float, c_float, c_int, _f,
+                               _f, _f, c_int64, c_void_p]),
+    'hcgs_bn_bwd_il': (c_int, [_f, _f, c_int64, c_int, c_int, c_int, _pp, _f, _f, _f, _f, _pp, _pp, _f, c_int64,
+                               c_void_p]),
     'hcgs_lstm_pack': (c_int, [c_void_p, _pp, c_int, _f, _f, c_void_p]),
     'hcgs_lstm_fwd': (c_int, [c_void_p, _f, _f, _f, c_float, c_int, c_int, c_int, _f, _f, _f, c_int, c_void_p]),
     'hcgs_lstm_bwd': (c_int, [c_void_p, _f, _f, _f, _f, _f, c_float, c_int, c_int, c_int, _f, c_void_p]),
@@ -93,7 +97,7 @@ def load():
 
 # kernels launched by each entry point (our own kernels only; memsets are not counted)
 KERNELS_PER_CALL = {'hcgs_mask_apply': 1, 'hcgs_quantize_w': 1, 'hcgs_quantize_act': 2, 'hcgs_bsgemm_nt': 1,
-                    'hcgs_bsgemm_nn': 1, 'hcgs_bs_sddmm': 1, 'hcgs_colsum': 1, 'hcgs_bn_fwd': 3, 'hcgs_bn_bwd': 2,
+                    'hcgs_bsgemm_nn': 1, 'hcgs_bs_sddmm': 1, 'hcgs_colsum': 1, 'hcgs_bn_fwd': 3, 'hcgs_bn_bwd': 2, 'hcgs_bn_fwd_il': 3, 'hcgs_bn_bwd_il': 2,
                     'hcgs_lstm_pack': 2, 'hcgs_lstm_fwd': 1, 'hcgs_lstm_bwd': 1,
                     'hcgs_lstm_tc_pack': 2, 'hcgs_lstm_tc_fwd': 1, 'hcgs_lstm_tc_bwd': 1,
                     'hcgs_tc_pack_nt': 1, 'hcgs_tc_gemm_nt': 1, 'hcgs_cast_bf16': 1,
@@ -279,6 +283,27 @@ def bn_bwd(dy2d, x2d, n_groups, group_cols, gammas, save_mean, save_invstd, dx2d
                               x2d.shape[0], n_groups, group_cols, _ptrs(gammas), _ptr(save_mean),
                               _ptr(save_invstd), _ptr(dx2d), _row_major_2d(dx2d, 'dx'), _ptrs(dgammas),
                               _ptrs(dbetas), _ptr(workspace), workspace.numel(), _stream()), 'hcgs_bn_bwd')
+
+
+def bn_fwd_il(x2d, y2d, n_groups, units, ld_units, gammas, betas, rmeans, rvars, eps, momentum, training,
+              save_mean, save_invstd, workspace):
+    """gate-interleaved BN over [m, n_groups*ld_units] (tensor-core build); y2d may alias x2d"""
+    _require_cuda(x2d, y2d, save_mean, save_invstd, workspace)
+    assert x2d.is_contiguous() and y2d.is_contiguous() and x2d.shape[1] == n_groups * ld_units
+    _check(load().hcgs_bn_fwd_il(_ptr(x2d), _ptr(y2d), x2d.shape[0], n_groups, units, ld_units, _ptrs(gammas),
+                                 _ptrs(betas), _ptrs(rmeans), _ptrs(rvars), float(eps), float(momentum),
+                                 1 if training else 0, _ptr(save_mean), _ptr(save_invstd), _ptr(workspace),
+                                 0 if workspace is None else workspace.numel(), _stream()), 'hcgs_bn_fwd_il')
+
+
+def bn_bwd_il(dy2d, x2d, n_groups, units, ld_units, gammas, save_mean, save_invstd, dx2d, dx_bf16, dgammas, dbetas,
+              workspace):
+    _require_cuda(dy2d, x2d, dx2d, save_mean, save_invstd, workspace)
+    _require_cuda_any(dx_bf16)
+    assert dy2d.is_contiguous() and x2d.is_contiguous() and dy2d.shape[1] == n_groups * ld_units
+    _check(load().hcgs_bn_bwd_il(_ptr(dy2d), _ptr(x2d), x2d.shape[0], n_groups, units, ld_units, _ptrs(gammas),
+                                 _ptr(save_mean), _ptr(save_invstd), _ptr(dx2d), _ptr(dx_bf16), _ptrs(dgammas),
+                                 _ptrs(dbetas), _ptr(workspace), workspace.numel(), _stream()), 'hcgs_bn_bwd_il')
 
 
 def lstm_pack(plan, us, fwd_pack=None, bwd_pack=None):

@@ -7,9 +7,25 @@
 // Statistics: rows are split over S CTAs per 32-column strip; every split computes a local
 // (mean, M2) pair with a two-pass scan of its rows and the splits are merged in a fixed order with
 // Chan's formula, so the result is deterministic and free of E[x^2]-E[x]^2 cancellation.
+#include <cuda_bf16.h>
+
 #include "common.cuh"
 
 namespace hcgs {
+
+// column -> (parameter group, index inside the group).  Gate-major: col = g*C + c.  Gate-interleaved (il, the
+// tensor-core build): col = c*G + g over a padded unit count; pad units (c >= C) have no parameters.
+__device__ __forceinline__ void bn_map(int col, int C, int G, int il, int& g, int& c, bool& valid) {
+    if (il) {
+        g = col % G;
+        c = col / G;
+        valid = c < C;
+    } else {
+        g = col / C;
+        c = col % C;
+        valid = true;
+    }
+}
 
 __device__ __forceinline__ float block_col_reduce(float v, float (*red)[33], int warp, int lane) {
     red[warp][lane] = v;
@@ -50,7 +66,8 @@ __global__ void __launch_bounds__(256) bn_stats_partial_kernel(const float* __re
 }
 
 __global__ void bn_stats_finalize_kernel(const float* __restrict__ partial, int splits, int64_t M,
-                                         int64_t rows_per_split, int Ctot, int C, float eps, float momentum,
+                                         int64_t rows_per_split, int Ctot, int C, int G, int il, float eps,
+                                         float momentum,
                                          PtrPack<float> rmean, PtrPack<float> rvar,
                                          float* __restrict__ save_mean, float* __restrict__ save_invstd) {
     const int col = blockIdx.x * blockDim.x + threadIdx.x;
@@ -78,7 +95,10 @@ __global__ void bn_stats_finalize_kernel(const float* __restrict__ partial, int 
         r = r * (1.5f - 0.5f * v * r * r);
         save_invstd[col] = r;
     }
-    const int g = col / C, c = col % C;
+    int g, c;
+    bool valid;
+    bn_map(col, C, G, il, g, c, valid);
+    if (!valid) return;
     if (rmean.p[g]) rmean.p[g][c] = (1.f - momentum) * rmean.p[g][c] + momentum * mean;
     if (rvar.p[g]) {
         const float var_u = (n > 1.f) ? m2 / (n - 1.f) : var_b;
@@ -89,7 +109,7 @@ __global__ void bn_stats_finalize_kernel(const float* __restrict__ partial, int 
 // y = (x - mean) * invstd * gamma + beta ; in eval mode mean/invstd come from the running stats
 __global__ void __launch_bounds__(256) bn_apply_kernel(const float* __restrict__ x, int ldx,
                                                        float* __restrict__ y, int ldy, int64_t M, int Ctot,
-                                                       int C, PtrPack<const float> gamma,
+                                                       int C, int G, int il, PtrPack<const float> gamma,
                                                        PtrPack<const float> beta, PtrPack<float> rmean,
                                                        PtrPack<float> rvar, float eps, int training,
                                                        const float* __restrict__ save_mean,
@@ -98,17 +118,21 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const float* __restrict__
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int col = blockIdx.x * 32 + lane;
     if (col >= Ctot) return;
-    const int g = col / C, c = col % C;
-    float mean, invstd;
-    if (training) {
-        mean = save_mean[col];
-        invstd = save_invstd[col];
-    } else {
-        mean = rmean.p[g][c];
-        invstd = 1.0f / sqrtf(rvar.p[g][c] + eps);
+    int g, c;
+    bool valid;
+    bn_map(col, C, G, il, g, c, valid);
+    float mean = 0.f, invstd = 0.f, ga = 0.f, be = 0.f;  // pad columns: y = 0
+    if (valid) {
+        if (training) {
+            mean = save_mean[col];
+            invstd = save_invstd[col];
+        } else {
+            mean = rmean.p[g][c];
+            invstd = 1.0f / sqrtf(rvar.p[g][c] + eps);
+        }
+        ga = gamma.p[g] ? __ldg(gamma.p[g] + c) : 1.f;
+        be = beta.p[g] ? __ldg(beta.p[g] + c) : 0.f;
     }
-    const float ga = gamma.p[g] ? __ldg(gamma.p[g] + c) : 1.f;
-    const float be = beta.p[g] ? __ldg(beta.p[g] + c) : 0.f;
     const float a = invstd * ga;
     const int64_t mbeg = (int64_t)blockIdx.y * rows_per_block;
     const int64_t mend = (mbeg + rows_per_block < M) ? mbeg + rows_per_block : M;
@@ -147,17 +171,30 @@ __global__ void __launch_bounds__(256) bn_bwd_partial_kernel(const float* __rest
 
 __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const float* __restrict__ dy, int lddy,
                                                            const float* __restrict__ x, int ldx, int64_t M,
-                                                           int Ctot, int C, PtrPack<const float> gamma,
+                                                           int Ctot, int C, int G, int il,
+                                                           PtrPack<const float> gamma,
                                                            const float* __restrict__ save_mean,
                                                            const float* __restrict__ save_invstd,
                                                            const float* __restrict__ partial, int splits,
                                                            float* __restrict__ dx, int lddx,
+                                                           __nv_bfloat16* __restrict__ dxb, int lddxb,
                                                            PtrPack<float> dgamma, PtrPack<float> dbeta,
                                                            int rows_per_block) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int col = blockIdx.x * 32 + lane;
     if (col >= Ctot) return;
-    const int g = col / C, c = col % C;
+    int g, c;
+    bool valid;
+    bn_map(col, C, G, il, g, c, valid);
+    const int64_t mbeg = (int64_t)blockIdx.y * rows_per_block;
+    const int64_t mend = (mbeg + rows_per_block < M) ? mbeg + rows_per_block : M;
+    if (!valid) {  // pad columns of the padded tensors stay zero
+        for (int64_t m = mbeg + warp; m < mend; m += 8) {
+            if (dx) dx[m * lddx + col] = 0.f;
+            if (dxb) dxb[m * lddxb + col] = __float2bfloat16_rn(0.f);
+        }
+        return;
+    }
     float s1 = 0.f, s2 = 0.f;
     for (int s = 0; s < splits; ++s) {
         s1 += partial[((int64_t)s * Ctot + col) * 2 + 0];
@@ -171,11 +208,11 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const float* __restri
     const float ga = gamma.p[g] ? __ldg(gamma.p[g] + c) : 1.f;
     const float inv_m = 1.0f / (float)M;
     const float k1 = s1 * inv_m, k2 = s2 * inv_m, a = ga * invstd;
-    const int64_t mbeg = (int64_t)blockIdx.y * rows_per_block;
-    const int64_t mend = (mbeg + rows_per_block < M) ? mbeg + rows_per_block : M;
     for (int64_t m = mbeg + warp; m < mend; m += 8) {
         const float xh = (x[m * ldx + col] - mean) * invstd;
-        dx[m * lddx + col] = a * (dy[m * lddy + col] - k1 - xh * k2);
+        const float o = a * (dy[m * lddy + col] - k1 - xh * k2);
+        if (dx) dx[m * lddx + col] = o;
+        if (dxb) dxb[m * lddxb + col] = __float2bfloat16_rn(o);
     }
 }
 
@@ -198,14 +235,15 @@ static int pick_splits(int64_t M, int strips, int64_t ws_floats, int Ctot, int64
 
 using namespace hcgs;
 
-extern "C" int hcgs_bn_fwd(const float* x, int ldx, float* y, int ldy, int64_t m, int n_groups, int group_cols,
-                           const float* const* gamma, const float* const* beta, float* const* running_mean,
-                           float* const* running_var, float eps, float momentum, int training, float* save_mean,
-                           float* save_invstd, float* workspace, int64_t workspace_floats, hcgs_stream stream) {
+static int bn_fwd_impl(const float* x, int ldx, float* y, int ldy, int64_t m, int n_groups, int group_cols,
+                       int ld_units, int il, const float* const* gamma, const float* const* beta,
+                       float* const* running_mean, float* const* running_var, float eps, float momentum,
+                       int training, float* save_mean, float* save_invstd, float* workspace,
+                       int64_t workspace_floats, hcgs_stream stream) {
     HCGS_REQUIRE(x && y, "hcgs_bn_fwd: NULL argument");
     HCGS_REQUIRE(n_groups >= 1 && n_groups <= HCGS_MAX_GROUPS, "hcgs_bn_fwd: n_groups out of range");
     if (m <= 0) return 0;
-    const int Ctot = n_groups * group_cols;
+    const int Ctot = n_groups * (il ? ld_units : group_cols);
     const int strips = (Ctot + 31) / 32;
     cudaStream_t st = (cudaStream_t)stream;
     if (training) {
@@ -216,7 +254,8 @@ extern "C" int hcgs_bn_fwd(const float* x, int ldx, float* y, int ldy, int64_t m
         bn_stats_partial_kernel<<<dim3(strips, splits), 256, 0, st>>>(x, ldx, m, Ctot, rows, workspace);
         HCGS_LAUNCH_CHECK();
         bn_stats_finalize_kernel<<<(Ctot + 127) / 128, 128, 0, st>>>(
-            workspace, splits, m, rows, Ctot, group_cols, eps, momentum, make_pack<float>(running_mean, n_groups),
+            workspace, splits, m, rows, Ctot, group_cols, n_groups, il, eps, momentum,
+            make_pack<float>(running_mean, n_groups),
             make_pack<float>(running_var, n_groups), save_mean, save_invstd);
         HCGS_LAUNCH_CHECK();
     } else {
@@ -229,21 +268,42 @@ extern "C" int hcgs_bn_fwd(const float* x, int ldx, float* y, int ldy, int64_t m
         yb = (m + rows_per_block - 1) / rows_per_block;
     }
     bn_apply_kernel<<<dim3(strips, (unsigned)yb), 256, 0, st>>>(
-        x, ldx, y, ldy, m, Ctot, group_cols, make_pack<const float>(gamma, n_groups),
+        x, ldx, y, ldy, m, Ctot, group_cols, n_groups, il, make_pack<const float>(gamma, n_groups),
         make_pack<const float>(beta, n_groups), make_pack<float>(running_mean, n_groups),
         make_pack<float>(running_var, n_groups), eps, training, save_mean, save_invstd, rows_per_block);
     HCGS_LAUNCH_CHECK();
     return 0;
 }
 
-extern "C" int hcgs_bn_bwd(const float* dy, int lddy, const float* x, int ldx, int64_t m, int n_groups,
-                           int group_cols, const float* const* gamma, const float* save_mean,
-                           const float* save_invstd, float* dx, int lddx, float* const* dgamma,
-                           float* const* dbeta, float* workspace, int64_t workspace_floats, hcgs_stream stream) {
-    HCGS_REQUIRE(dy && x && dx && save_mean && save_invstd && workspace, "hcgs_bn_bwd: NULL argument");
+extern "C" int hcgs_bn_fwd(const float* x, int ldx, float* y, int ldy, int64_t m, int n_groups, int group_cols,
+                           const float* const* gamma, const float* const* beta, float* const* running_mean,
+                           float* const* running_var, float eps, float momentum, int training, float* save_mean,
+                           float* save_invstd, float* workspace, int64_t workspace_floats, hcgs_stream stream) {
+    return bn_fwd_impl(x, ldx, y, ldy, m, n_groups, group_cols, group_cols, 0, gamma, beta, running_mean,
+                       running_var, eps, momentum, training, save_mean, save_invstd, workspace, workspace_floats,
+                       stream);
+}
+
+extern "C" int hcgs_bn_fwd_il(const float* x, float* y, int64_t m, int n_groups, int units, int ld_units,
+                              const float* const* gamma, const float* const* beta, float* const* running_mean,
+                              float* const* running_var, float eps, float momentum, int training,
+                              float* save_mean, float* save_invstd, float* workspace, int64_t workspace_floats,
+                              hcgs_stream stream) {
+    HCGS_REQUIRE(ld_units >= units, "hcgs_bn_fwd_il: ld_units < units");
+    return bn_fwd_impl(x, n_groups * ld_units, y, n_groups * ld_units, m, n_groups, units, ld_units, 1, gamma, beta,
+                       running_mean, running_var, eps, momentum, training, save_mean, save_invstd, workspace,
+                       workspace_floats, stream);
+}
+
+static int bn_bwd_impl(const float* dy, int lddy, const float* x, int ldx, int64_t m, int n_groups, int group_cols,
+                       int ld_units, int il, const float* const* gamma, const float* save_mean,
+                       const float* save_invstd, float* dx, int lddx, void* dx_bf16, int lddxb,
+                       float* const* dgamma, float* const* dbeta, float* workspace, int64_t workspace_floats,
+                       hcgs_stream stream) {
+    HCGS_REQUIRE(dy && x && (dx || dx_bf16) && save_mean && save_invstd && workspace, "hcgs_bn_bwd: NULL argument");
     HCGS_REQUIRE(n_groups >= 1 && n_groups <= HCGS_MAX_GROUPS, "hcgs_bn_bwd: n_groups out of range");
     if (m <= 0) return 0;
-    const int Ctot = n_groups * group_cols;
+    const int Ctot = n_groups * (il ? ld_units : group_cols);
     HCGS_REQUIRE(workspace_floats >= 2 * (int64_t)Ctot, "hcgs_bn_bwd: workspace too small");
     const int strips = (Ctot + 31) / 32;
     cudaStream_t st = (cudaStream_t)stream;
@@ -259,9 +319,26 @@ extern "C" int hcgs_bn_bwd(const float* dy, int lddy, const float* x, int ldx, i
         yb = (m + rows_per_block - 1) / rows_per_block;
     }
     bn_bwd_apply_kernel<<<dim3(strips, (unsigned)yb), 256, 0, st>>>(
-        dy, lddy, x, ldx, m, Ctot, group_cols, make_pack<const float>(gamma, n_groups), save_mean, save_invstd,
-        workspace, splits, dx, lddx, make_pack<float>(dgamma, n_groups), make_pack<float>(dbeta, n_groups),
-        rows_per_block);
+        dy, lddy, x, ldx, m, Ctot, group_cols, n_groups, il, make_pack<const float>(gamma, n_groups), save_mean,
+        save_invstd, workspace, splits, dx, lddx, (__nv_bfloat16*)dx_bf16, lddxb, make_pack<float>(dgamma, n_groups),
+        make_pack<float>(dbeta, n_groups), rows_per_block);
     HCGS_LAUNCH_CHECK();
     return 0;
+}
+
+extern "C" int hcgs_bn_bwd(const float* dy, int lddy, const float* x, int ldx, int64_t m, int n_groups,
+                           int group_cols, const float* const* gamma, const float* save_mean,
+                           const float* save_invstd, float* dx, int lddx, float* const* dgamma,
+                           float* const* dbeta, float* workspace, int64_t workspace_floats, hcgs_stream stream) {
+    return bn_bwd_impl(dy, lddy, x, ldx, m, n_groups, group_cols, group_cols, 0, gamma, save_mean, save_invstd, dx,
+                       lddx, nullptr, 0, dgamma, dbeta, workspace, workspace_floats, stream);
+}
+
+extern "C" int hcgs_bn_bwd_il(const float* dy, const float* x, int64_t m, int n_groups, int units, int ld_units,
+                              const float* const* gamma, const float* save_mean, const float* save_invstd,
+                              float* dx, void* dx_bf16, float* const* dgamma, float* const* dbeta,
+                              float* workspace, int64_t workspace_floats, hcgs_stream stream) {
+    const int ld = n_groups * ld_units;
+    return bn_bwd_impl(dy, ld, x, ld, m, n_groups, units, ld_units, 1, gamma, save_mean, save_invstd, dx, ld, dx_bf16,
+                       ld, dgamma, dbeta, workspace, workspace_floats, stream);
 }

@@ -323,6 +323,7 @@ __global__ void __launch_bounds__(128) tc_gemm_nt_kernel(const __grid_constant__
                 for (int i = 0; i < 32; ++i) {
                     const int u = r * 32 + (cb * 32 + i) / NG;
                     if (u < a.n_out) dst[i] = v[i];
+                    else if (col0 + i < a.ldy) dst[i] = 0.f;  // pad columns of a padded output stay zero
                 }
             }
         }

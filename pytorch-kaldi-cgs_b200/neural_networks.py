@@ -29,7 +29,8 @@ from HCGS import HCGS as HCGS
 from HCGS import guidedHCGS as guidedHCGS
 from quantized_modules import QuantizeLinear, Quantize, Quantize_inp, prune
 from b200 import native
-from b200.functions import LayerRuntime, LSTMLayerFunction, MLPLayerFunction
+from b200.functions import (LayerRuntime, LSTMLayerFunction, MLPLayerFunction, LSTMLayerTCFunction,
+                            MLPLayerTCFunction)
 
 
 def strtobool(val):
@@ -47,6 +48,14 @@ def _opt(options, key, default, *aliases):
         if k in options:
             return options[k]
     return default
+
+
+def _precision(net):
+    """'fp32' (bit-comparable CUDA-core build) or 'bf16' (tensor-core build); cfg key b200_precision."""
+    p = str(getattr(net, 'b200_precision', 'fp32')).lower()
+    if p not in ('fp32', 'bf16'):
+        raise ValueError("b200_precision must be 'fp32' or 'bf16', got %r" % p)
+    return p
 
 
 def hsigmoid(x):
@@ -172,6 +181,7 @@ class MLP(nn.Module):
         self.apply_guided_hcgs = strtobool(_opt(options, 'apply_guided_hcgs', 'False'))
         _parse_pattern_options(self, options, 'mlp')
         self.arch_name = _opt(options, 'arch_name', 'MLP')
+        self.b200_precision = _opt(options, 'b200_precision', 'fp32')
 
         self.test_flag = self.to_do != 'train'
         first_eval = self.to_do in ('forward', 'valid')
@@ -329,7 +339,8 @@ class MLP(nn.Module):
                 raise NotImplementedError('backward through eval-mode batch norm (arch_freeze) is not built yet')
             gamma = bn.weight if rt.use_bn else None
             beta = bn.bias if rt.use_bn else None
-            x = MLPLayerFunction.apply(x, lin.weight, lin.bias, gamma, beta, rt)
+            fn = MLPLayerTCFunction if _precision(self) == 'bf16' else MLPLayerFunction
+            x = fn.apply(x, lin.weight, lin.bias, gamma, beta, rt)
             if rt.use_bn:
                 _bump_bn_counter(bn)
         return x
@@ -418,6 +429,7 @@ class LSTM(nn.Module):
         self.if_hsigmoid = strtobool(_opt(options, 'if_hsigmoid', 'False'))
         _parse_pattern_options(self, options, 'lstm')
         self.arch_name = _opt(options, 'arch_name', 'LSTM')
+        self.b200_precision = _opt(options, 'b200_precision', 'fp32')
 
         self.test_flag = self.to_do != 'train'
         first_eval = self.to_do in ('forward', 'valid')
@@ -586,6 +598,7 @@ class LSTM(nn.Module):
             raise NotImplementedError('lstm_use_batchnorm_inp is not built into the B200 hot path yet')
         if x.dim() != 3:
             raise native.NativeError('LSTM expects [T, B, in] input, got %s' % (tuple(x.shape),))
+        prev_hb = None
         for i in range(self.N_lstm_lay):
             self.bidir = 0           # as the reference (:835)
             self.if_hsigmoid = 0     # as the reference (:1080)
@@ -643,7 +656,12 @@ class LSTM(nn.Module):
                     gb += [b.weight, b.bias]
             else:
                 gb = [None] * 8
-            x = LSTMLayerFunction.apply(x, *ws, *us, *gb, rt)
+            if _precision(self) == 'bf16':
+                rt.xb_in = prev_hb
+                x = LSTMLayerTCFunction.apply(x, *ws, *us, *gb, rt)
+                prev_hb = rt.hb_out
+            else:
+                x = LSTMLayerFunction.apply(x, *ws, *us, *gb, rt)
             if rt.use_bn:
                 for b in bns:
                     _bump_bn_counter(b)

@@ -1,0 +1,200 @@
+"""Tensor-core build (b200_precision = bf16) at model level.
+
+Oracle: oracle/model_oracle.py with spec['bf16_operands'] = True, i.e. the reference's operator sequence in
+which every matrix product (forward, dX, dW) takes bf16-rounded operands and accumulates in fp32 -- exactly
+what the tcgen05 / mma.sync kernels compute.  What is left is summation order, the fast exp forms of the
+recurrent kernel (abs 1e-6) and the occasional flip of a bf16 rounding of h, hence the tolerances below:
+
+    log-posteriors      max-abs <= 1e-4 (the north star's bf16 bound; measured 4e-5 at 4x550/1944)
+    loss                rel <= 1e-4
+    gradients           mean-abs <= 2e-3 of the tensor max, max-abs <= 5e-2 of the tensor max
+
+Against the fp32 oracle the same run differs by the bf16 operand rounding itself; that gap is measured and
+bounded too (loss rel <= 2e-2) so a gross error in the rounding points cannot hide."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from helpers import NETS, build_product_nets, make_graph  # noqa: E402
+from oracle import model_oracle  # noqa: E402
+from test_gpu_model import _ReplayBernoulli, _state_to_cpu  # noqa: E402
+from test_oracle_pinned import golden_specs  # noqa: E402
+
+REPORT = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), 'gpurun_out')
+
+
+def _err(a, b):
+    a = torch.as_tensor(a).detach().cpu().double()
+    b = torch.as_tensor(b).detach().cpu().double()
+    e = (a - b).abs()
+    return e.max().item(), e.mean().item(), max(b.abs().max().item(), 1e-30)
+
+
+@pytest.mark.parametrize('M,units,ld', [(200, 24, 24), (4097, 550, 552), (333, 70, 72)])
+def test_batch_norm_interleaved(M, units, ld):
+    from b200 import native
+    d = torch.device('cuda', 0)
+    torch.manual_seed(M)
+    x = torch.zeros(M, ld, 4)
+    x[:, :units, :] = torch.randn(M, units, 4) * 2 + 0.5
+    dy = torch.zeros(M, ld, 4)
+    dy[:, :units, :] = torch.randn(M, units, 4)
+    gam = [torch.rand(units) + 0.5 for _ in range(4)]
+    bet = [torch.randn(units) for _ in range(4)]
+    rm = [torch.zeros(units, device=d) for _ in range(4)]
+    rv = [torch.ones(units, device=d) for _ in range(4)]
+    xd = x.reshape(M, 4 * ld).to(d)
+    y = torch.full((M, 4 * ld), 9.0, device=d)
+    sm = torch.empty(4 * ld, device=d)
+    si = torch.empty(4 * ld, device=d)
+    ws = torch.empty(2 * 4 * ld * 64, device=d)
+    gd = [g.to(d) for g in gam]
+    bd = [b.to(d) for b in bet]
+    native.bn_fwd_il(xd, y, 4, units, ld, gd, bd, rm, rv, 1e-5, 0.05, True, sm, si, ws)
+    dxf = torch.full((M, 4 * ld), 9.0, device=d)
+    dxb = torch.full((M, 4 * ld), 9.0, device=d, dtype=torch.bfloat16)
+    dg = [torch.empty(units, device=d) for _ in range(4)]
+    db = [torch.empty(units, device=d) for _ in range(4)]
+    native.bn_bwd_il(dy.reshape(M, 4 * ld).to(d), xd, 4, units, ld, gd, sm, si, dxf, dxb, dg, db, ws)
+    torch.cuda.synchronize()
+    y3 = y.view(M, ld, 4).cpu()
+    dx3 = dxf.view(M, ld, 4).cpu()
+    for g in range(4):
+        xg = x[:, :units, g].clone().requires_grad_(True)
+        gg = gam[g].clone().requires_grad_(True)
+        bg = bet[g].clone().requires_grad_(True)
+        r_m, r_v = torch.zeros(units), torch.ones(units)
+        ref = torch.nn.functional.batch_norm(xg, r_m, r_v, gg, bg, True, 0.05, 1e-5)
+        ref.backward(dy[:, :units, g])
+        for got, want, what in ((y3[:, :units, g], ref, 'y'), (dx3[:, :units, g], xg.grad, 'dx'),
+                                (dg[g].cpu(), gg.grad, 'dgamma'), (db[g].cpu(), bg.grad, 'dbeta'),
+                                (rm[g].cpu(), r_m, 'running_mean'), (rv[g].cpu(), r_v, 'running_var')):
+            mx, _, sc = _err(got, want)
+            assert mx <= 2e-5 * sc + 1e-6, '%s gate %d: %.3e (scale %.3e)' % (what, g, mx, sc)
+    if ld > units:
+        assert y3[:, units:, :].abs().max().item() == 0 and dx3[:, units:, :].abs().max().item() == 0
+    assert torch.equal(dxb.float().cpu(), dxf.cpu().to(torch.bfloat16).float())
+    # eval mode uses the running statistics
+    y2 = torch.empty_like(y)
+    native.bn_fwd_il(xd, y2, 4, units, ld, gd, bd, rm, rv, 1e-5, 0.05, False, sm, si, ws)
+    ref = torch.nn.functional.batch_norm(x[:, :units, 1], rm[1].cpu(), rv[1].cpu(), gam[1], bet[1], False, 0.05, 1e-5)
+    mx, _, sc = _err(y2.view(M, ld, 4)[:, :units, 1], ref)
+    assert mx <= 2e-5 * sc
+
+
+@pytest.mark.parametrize('H,layers,T,B,P', [(550, 4, 60, 8, 1944), (512, 2, 40, 21, 1944), (72, 2, 9, 3, 100)])
+def test_bf16_train_step_matches_bf16_operand_oracle(H, layers, T, B, P):
+    D = 40
+    lay = ','.join([str(H)] * layers)
+    blk = '32,4' if H >= 128 else '8,4'
+    sp = '75,62.5' if H >= 128 else '50,50'
+    lstm_over = dict(lstm_lay=lay, lstm_drop=','.join(['0.2'] * layers), lstm_use_laynorm=','.join(['False'] * layers),
+                     lstm_use_batchnorm=','.join(['True'] * layers), lstm_act=','.join(['tanh'] * layers),
+                     hcgsx_block=blk, hcgsx_sparse=sp, hcgsh_block=blk, hcgsh_sparse=sp, b200_precision='bf16')
+    mlp_over = dict(dnn_lay=str(P), hcgs_block='64,4' if P > 1000 else '4,2', hcgs_sparse='50,25',
+                    b200_precision='bf16')
+    nets, _ = build_product_nets('train', D=D, seed=2234, lstm_over=lstm_over, mlp_over=mlp_over, device='cuda')
+    assert all(n.b200_precision == 'bf16' for n in nets.values())
+    params = _state_to_cpu(nets)
+    gen = torch.Generator().manual_seed(1)
+    inp = torch.zeros(T, B, D + 2)
+    inp[:, :, :D] = torch.randn(T, B, D, generator=gen)
+    inp[:, :, D] = torch.randint(0, P, (T, B), generator=gen).float()
+    inp[:, :, D + 1] = torch.randint(0, 5, (T, B), generator=gen).float()
+    inp[T - 3:, B - 1, :] = 0
+    drops = [torch.bernoulli(torch.full((B, H), 0.8), generator=gen) for _ in range(layers)]
+    for d in params.values():
+        for k, v in d.items():
+            if v.dtype == torch.float32 and not k.endswith(('running_mean', 'running_var', 'mask')):
+                v.requires_grad_(True)
+    specs = golden_specs(dict(lay=[H] * layers, act=['tanh'] * layers, use_bn=[True] * layers, drop=[0.2] * layers))
+    specs['cd']['lay'] = [P]
+    for s in specs.values():
+        s['bf16_operands'] = True
+    ref = model_oracle.model_forward(params, specs, inp, D, True, drops)
+    ref['loss_final'].backward()
+    from b200 import native
+    native.reset_launch_count()
+    graph = make_graph(nets, D)
+    with _ReplayBernoulli(drops):
+        out = graph.forward(inp.cuda(), T, B, 'train', ['out_dnn2'])
+    out['loss_final'].backward()
+    torch.cuda.synchronize()
+    assert native.LAUNCHES.get('hcgs_lstm_tc_fwd', 0) == layers and native.LAUNCHES.get('hcgs_tc_gemm_nt', 0) > 0
+    assert 'hcgs_lstm_fwd' not in native.LAUNCHES and 'hcgs_bsgemm_nt' not in native.LAUNCHES
+    rep = {}
+    rep['loss'] = (out['loss_final'].item(), ref['loss_final'].item())
+    rep['logp'] = _err(out['out_dnn2'], ref['out_dnn2'])
+    rep['h'] = _err(out['out_dnn1'].reshape(T, B, -1), ref['out_dnn1'])
+    worst = (0.0, 0.0, '')
+    for k, n in NETS.items():
+        for name, p in nets[n].named_parameters():
+            rg = params[k][name].grad
+            if rg is None:
+                continue
+            mx, mean, sc = _err(p.grad, rg)
+            rep['grad %s/%s' % (n, name)] = (mx / sc, mean / sc)
+            if mx / sc > worst[0]:
+                worst = (mx / sc, mean / sc, name)
+            assert mean <= 2e-3 * sc, 'grad %s/%s mean err %.3e of max' % (n, name, mean / sc)
+            assert mx <= 5e-2 * sc, 'grad %s/%s max err %.3e of max' % (n, name, mx / sc)
+    # the fp32 oracle on the same inputs: bounds the operand rounding itself
+    for s in specs.values():
+        s['bf16_operands'] = False
+    with torch.no_grad():
+        ref32 = model_oracle.model_forward(params, specs, inp, D, True, drops)
+    rep['loss_fp32'] = ref32['loss_final'].item()
+    rep['logp_vs_fp32'] = _err(out['out_dnn2'], ref32['out_dnn2'])
+    try:
+        os.makedirs(REPORT, exist_ok=True)
+        with open(os.path.join(REPORT, 'bf16_parity_H%d_L%d.json' % (H, layers)), 'w') as f:
+            json.dump(rep, f, indent=1)
+    except OSError:
+        pass
+    assert abs(rep['loss'][0] - rep['loss'][1]) <= 1e-4 * abs(rep['loss'][1]), rep['loss']
+    # north star: bf16-accumulate posteriors max-abs <= 1e-4
+    assert rep['logp'][0] <= 1e-4, 'log-posteriors max-abs %.3e (mean %.3e)' % rep['logp'][:2]
+    # h: a bf16 rounding flip of one h element is 2^-9 relative, hence the loose max and the tight mean
+    assert rep['h'][1] <= 2e-4 and rep['h'][0] <= 2e-2, 'lstm output max-abs %.3e mean-abs %.3e' % rep['h'][:2]
+    assert abs(rep['loss'][0] - rep['loss_fp32']) <= 2e-2 * abs(rep['loss_fp32'])
+
+
+def test_bf16_eval_forward_with_prior():
+    """forward (posterior export) on the tensor-core build: eval BN, scalar drop, fused log-prior."""
+    D, H, T, B, P = 40, 550, 30, 5, 1944
+    lstm_over = dict(lstm_lay='550,550', lstm_drop='0.2,0.2', lstm_use_laynorm='False,False',
+                     lstm_use_batchnorm='True,True', lstm_act='tanh,tanh', hcgsx_block='32,4', hcgsx_sparse='75,62.5',
+                     hcgsh_block='32,4', hcgsh_sparse='75,62.5', b200_precision='bf16')
+    mlp_over = dict(dnn_lay=str(P), hcgs_block='64,4', hcgs_sparse='50,25', b200_precision='bf16')
+    nets, _ = build_product_nets('forward', D=D, seed=5, lstm_over=lstm_over, mlp_over=mlp_over, device='cuda')
+    for n in nets.values():
+        n.save_mat = False
+    # non-trivial running statistics
+    with torch.no_grad():
+        for name, buf in nets['LSTM_layers'].named_buffers():
+            if name.endswith('running_var'):
+                buf.uniform_(0.5, 2.0)
+            elif name.endswith('running_mean'):
+                buf.normal_(0, 0.3)
+    params = _state_to_cpu(nets)
+    counts = torch.rand(P) * 100 + 1
+    x = torch.randn(T, B, D)
+    specs = golden_specs(dict(lay=[H, H], act=['tanh'] * 2, use_bn=[True] * 2, drop=[0.2] * 2))
+    specs['cd']['lay'] = [P]
+    for s in specs.values():
+        s['bf16_operands'] = True
+    with torch.no_grad():
+        h = model_oracle.lstm_forward(params['lstm'], specs['lstm'], x, None, False)
+        ref = model_oracle.mlp_forward(params['cd'], specs['cd'], h.view(T * B, -1), False)
+    ref = model_oracle.posterior(ref.numpy(), counts.numpy())
+    nets['MLP_layers'].log_prior = torch.log(counts / counts.sum()).cuda()
+    with torch.no_grad():
+        hh = nets['LSTM_layers'](x.cuda())
+        got = nets['MLP_layers'](hh.view(T * B, -1))
+    mx, mean, sc = _err(got, ref)
+    assert mean <= 2e-5 and mx <= 2e-4, 'posterior max-abs %.3e mean-abs %.3e' % (mx, mean)
