@@ -28,7 +28,7 @@ D_FEA, N_PDF, N_MONO = 40, 1944, 48
 LAYERS, HID = 4, 550
 
 
-def cfg_sections(to_do='train'):
+def cfg_sections(to_do='train', precision='bf16'):
     lay = ','.join([str(HID)] * LAYERS)
     rep = lambda v: ','.join([v] * LAYERS)  # noqa: E731
     lstm = dict(arch_name='LSTM_layers', lstm_lay=lay, lstm_drop=rep('0.2'), lstm_use_laynorm_inp='False',
@@ -39,14 +39,14 @@ def cfg_sections(to_do='train'):
                 apply_guided_hcgs='False', hcgsx_block='32,4', hcgsx_sparse='75,62.5', hcgsh_block='32,4',
                 hcgsh_sparse='75,62.5', lstm_quant='False', param_quant=rep('8'), lstm_quant_inp='False',
                 inp_quant='16', lstm_prune='False', lstm_prune_perc='70', skip_regularization='True', to_do=to_do,
-                use_cuda='True')
+                use_cuda='True', b200_precision=precision)
     mlp = dict(arch_name='MLP_layers', dnn_lay=str(N_PDF), dnn_drop='0.0', dnn_use_laynorm_inp='False',
                dnn_use_batchnorm_inp='False', dnn_use_batchnorm='False', dnn_use_laynorm='False', dnn_act='softmax',
                arch_lr='0.0016', arch_opt='rmsprop', opt_momentum='0.0', opt_alpha='0.95', opt_eps='1e-8',
                opt_centered='False', opt_weight_decay='0.0', out_folder='', mlp_hcgs='True', guided_hcgs='False',
                apply_guided_hcgs='False', hcgs_block='64,4', hcgs_sparse='50,25', mlp_quant='False', param_quant='8',
                mlp_quant_inp='False', inp_quant='16', mlp_prune='False', mlp_prune_perc='70',
-               skip_regularization='True', to_do=to_do, use_cuda='True')
+               skip_regularization='True', to_do=to_do, use_cuda='True', b200_precision=precision)
     mono = dict(mlp, arch_name='MLP_layers2', dnn_lay=str(N_MONO), mlp_hcgs='False', arch_lr='0.0004')
     return lstm, mlp, mono
 
@@ -125,12 +125,12 @@ class ClockSampler:
                 'samples': len(sm)}
 
 
-def build_workload(device, seed=2234):
+def build_workload(device, seed=2234, precision='bf16'):
     import neural_networks as nb
     from b200.graph import Graph, make_optimizer
     torch.manual_seed(seed)
     np.random.seed(seed)
-    s_lstm, s_cd, s_mono = cfg_sections('train')
+    s_lstm, s_cd, s_mono = cfg_sections('train', precision)
     lstm = nb.LSTM(s_lstm, D_FEA)
     cd = nb.MLP(s_cd, lstm.out_dim)
     mono = nb.MLP(s_mono, lstm.out_dim)
@@ -155,12 +155,45 @@ def train_step(graph, opts, inp, T, B, bucket=None):
     return out['loss_final']
 
 
+def algorithmic_work(name, a):
+    """(bytes, flops) one call of a native entry point has to move / compute:
+    every operand and result counted once at its stored width, products only inside kept 32x32 tiles."""
+    try:
+        if name == 'lstm_tc_fwd':        # (plan, cfg, pack, pre, drop, scalar, act, T, B, h, hb, c, gates)
+            plan, pre, T, B = a[0], a[3], a[7], a[8]
+            ld, H, rows = pre.shape[-1] // 4, plan.n_out, a[7] * a[8]
+            byts = rows * (16 * ld + sum(n for t, n in zip(a[9:13], (4 * H, 2 * ld, 4 * ld, 16 * ld)) if t is not None))
+            return byts, 2 * 4 * 16 * plan.n_blocks * rows
+        if name == 'lstm_tc_bwd':        # (plan, cfg, pack, dh, gates, c, drop, scalar, act, T, B, dpre, dpre_b)
+            plan, gates = a[0], a[4]
+            ld, H, rows = gates.shape[-1] // 4, plan.n_out, a[9] * a[10]
+            byts = rows * (4 * H + 16 * ld + 4 * ld + 16 * ld + (8 * ld if len(a) > 12 and a[12] is not None else 0))
+            return byts, 2 * 4 * 16 * plan.n_blocks * rows
+        if name in ('tc_gemm_nt', 'tc_gemm_nn'):   # (plan, n_w, wpack, x_bf16 | dy_bf16, y | dx)
+            plan, n_w, src, dst = a[0], a[1], a[3], a[4]
+            m = src.shape[0]
+            return m * (src.shape[1] * 2 + dst.shape[1] * 4), 2 * m * plan.nz_tiles * 1024 * n_w
+        if name == 'tc_sddmm':           # (plan, n_w, dy_bf16, x_bf16, dws, mask)
+            plan, n_w, dy, x = a[0], a[1], a[2], a[3]
+            m = dy.shape[0]
+            return m * (dy.shape[1] + x.shape[1]) * 2, 2 * m * plan.nz_tiles * 1024 * n_w
+        if name in ('lstm_fwd', 'lstm_bwd'):
+            plan = a[0]
+            t = a[2] if name == 'lstm_fwd' else a[3]
+            rows = t.shape[0] * t.shape[1]
+            return rows * 10 * plan.n_out * 4, 2 * 4 * 16 * plan.n_blocks * rows
+    except Exception:
+        return None
+    return None
+
+
 class KernelTimers:
     """CUDA-event timing of every native entry point inside the timed region (same stream)."""
 
     NAMES = ['mask_apply', 'bsgemm_nt', 'bsgemm_nn', 'bs_sddmm', 'colsum', 'bn_fwd', 'bn_bwd', 'lstm_pack',
              'lstm_fwd', 'lstm_bwd', 'logsoftmax_fwd', 'logsoftmax_bwd', 'act_fwd', 'act_bwd', 'quantize_w',
-             'quantize_act']
+             'quantize_act', 'nll_fwd_bwd', 'bn_fwd_il', 'bn_bwd_il', 'lstm_tc_pack', 'lstm_tc_fwd', 'lstm_tc_bwd',
+             'tc_pack_nt', 'tc_gemm_nt', 'tc_pack_nn', 'tc_gemm_nn', 'tc_sddmm', 'cast_bf16']
 
     def __init__(self):
         from b200 import native
@@ -179,16 +212,19 @@ class KernelTimers:
             e0.record()
             r = fn(*a, **k)
             e1.record()
-            self.events.append((name, e0, e1))
+            self.events.append((name, e0, e1, algorithmic_work(name, a)))
             return r
         return timed
 
     def summary(self):
-        tot, cnt = {}, {}
-        for n, e0, e1 in self.events:
+        tot, cnt, work = {}, {}, {}
+        for n, e0, e1, w in self.events:
             tot[n] = tot.get(n, 0.0) + e0.elapsed_time(e1)
             cnt[n] = cnt.get(n, 0) + 1
-        return tot, cnt
+            if w is not None:
+                b, f = work.get(n, (0, 0))
+                work[n] = (b + w[0], f + w[1])
+        return tot, cnt, work
 
     def restore(self):
         for n, f in self.orig.items():
@@ -266,6 +302,7 @@ def run_reference_arm(args, rank):
 def workload_config(args, T, B):
     return {'workload': 'TIMIT_CGS LSTM train step: 40-dim fbank -> 4x550 HCGS LSTM (32,4 / 75,62.5 masks, BN, tanh, '
                         'drop 0.2) -> 1944-pdf (64,4 / 50,25) + 48-mono softmax heads, NLL, RMSprop',
+            'precision': getattr(args, 'precision', 'bf16') if getattr(args, 'impl', 'b200') == 'b200' else 'fp32',
             'seq_len': T, 'batch_per_gpu': B, 'frames_counted': 'real (unpadded) frames',
             'parallelism': 'dp%d' % args.gpus,
             'l2_policy': 'per-step working set (~%.1f GB of activations) exceeds the 126 MB L2; no explicit flush'
@@ -287,7 +324,9 @@ def main():
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
     ap.add_argument('--seq-len', type=int, default=256, help='padded minibatch length T (cfg max_seq_length_train <= 1000)')
-    ap.add_argument('--batch', type=int, default=128, help='sequences per GPU per optimizer step')
+    ap.add_argument('--batch', type=int, default=512, help='sequences per GPU per optimizer step')
+    ap.add_argument('--precision', default='bf16', choices=['bf16', 'fp32'],
+                    help='bf16 = tensor-core build (BASELINE configs[1] "bf16 train"), fp32 = CUDA-core parity build')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     args = ap.parse_args()
 
@@ -303,7 +342,7 @@ def main():
     from b200 import native
     T, B = args.seq_len, args.batch
     W = max(args.warmup, 3)
-    nets, graph, opts = build_workload(dev)
+    nets, graph, opts = build_workload(dev, precision=args.precision)
     bucket = None
     if world > 1:
         bucket = bdist.GradBucket(bdist.lstm_mlp_entries(list(nets.values())), dev)
@@ -343,7 +382,7 @@ def main():
     clocks = sampler.stop()
     launches = native.LAUNCHES['total']
     ms_total = e0.elapsed_time(e1)
-    ktot, kcnt = timers.summary()
+    ktot, kcnt, kwork = timers.summary()
     timers.restore()
 
     # ---- end to end through the public API: pinned host minibatch -> GPU -> loss on the host ------
@@ -376,31 +415,40 @@ def main():
     hbm_peak, tf_peak, peak_kind = measured_peaks()
     # dominant kernel = largest share of the timed region among our kernels
     dom = max(ktot, key=ktot.get)
-    plan_h = nets['LSTM_layers']._plans._store[('h', 1)][1]
-    rows = T * B
-    alg_bytes = {'lstm_fwd': rows * 10 * HID * 4, 'lstm_bwd': rows * 10 * HID * 4}
     avg_ms = ktot[dom] / kcnt[dom]
-    if dom in alg_bytes:
-        achieved = alg_bytes[dom] / (avg_ms * 1e-3) / 1e9
-        roof = {'kernel': dom, 'bound': 'hbm', 'achieved': achieved, 'peak': hbm_peak, 'unit': 'GB/s',
-                'frac': achieved / hbm_peak, 'traffic': None, 'peak_source': peak_kind,
-                'avg_launch_ms': avg_ms, 'share_of_step': ktot[dom] / ms_total,
-                'algorithmic_bytes_per_launch': alg_bytes[dom],
-                'note': 'persistent recurrent kernel: streams pre/gates/c/h once (10*H*4 B per frame); '
-                        'its floor is step latency x T, not HBM -- see DESIGN.md',
-                'us_per_step': avg_ms * 1e3 / T,
-                'effective_gflops': 2 * 4 * 16 * plan_h.n_blocks * rows / (avg_ms * 1e-3) / 1e9}
-    else:
-        roof = {'kernel': dom, 'bound': 'hbm', 'achieved': None, 'peak': hbm_peak, 'unit': 'GB/s', 'frac': None,
-                'traffic': None, 'avg_launch_ms': avg_ms, 'share_of_step': ktot[dom] / ms_total}
+    roof = {'kernel': dom, 'bound': 'hbm', 'achieved': None, 'peak': hbm_peak, 'unit': 'GB/s', 'frac': None,
+            'traffic': None, 'peak_source': peak_kind, 'avg_launch_ms': avg_ms, 'launches_per_step': kcnt[dom] / args.steps,
+            'share_of_step': ktot[dom] / ms_total}
+    if dom in kwork:
+        byts, flops = kwork[dom][0] / kcnt[dom], kwork[dom][1] / kcnt[dom]
+        roof['algorithmic_bytes_per_launch'] = byts
+        roof['algorithmic_flops_per_launch'] = flops
+        if dom in ('tc_gemm_nt', 'tc_gemm_nn', 'tc_sddmm'):
+            ach = flops / (avg_ms * 1e-3) / 1e12
+            roof.update(bound='tensor', achieved=ach, peak=tf_peak, unit='TFLOP/s', frac=ach / tf_peak)
+        else:
+            ach = byts / (avg_ms * 1e-3) / 1e9
+            roof.update(achieved=ach, frac=ach / hbm_peak)
+            if dom.startswith('lstm'):
+                roof['us_per_time_step'] = avg_ms * 1e3 / T
+                roof['effective_tflops'] = flops / (avg_ms * 1e-3) / 1e12
+                roof['note'] = ('persistent recurrent kernel: streams its operands once; the floor is the serial '
+                                'chain of T time steps (cluster exchange of h_t per step), not HBM -- DESIGN.md 3.3')
+    per_kernel = {}
+    for k in sorted(ktot, key=lambda x: -ktot[x]):
+        e = {'ms_per_step': round(ktot[k] / args.steps, 4), 'launches_per_step': kcnt[k] / args.steps}
+        if k in kwork:
+            e['GB_per_s'] = round(kwork[k][0] / (ktot[k] * 1e-3) / 1e9, 1)
+            e['TFLOP_per_s'] = round(kwork[k][1] / (ktot[k] * 1e-3) / 1e12, 2)
+        per_kernel[k] = e
     line = {'metric': 'hcgs_lstm_train_frames_per_sec', 'value': value, 'unit': 'frames/s', 'n_gpus': world,
             'steps': args.steps, 'warmup': W, 'ms_per_step': ms_total / args.steps, 'higher_is_better': True,
-            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-            'config': workload_config(args, T, B), 'clocks': clocks, 'gpu_launches': launches,
+            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'bf16' if args.precision == 'bf16' else 'f32',
+            'data': 'synthetic', 'config': workload_config(args, T, B), 'clocks': clocks, 'gpu_launches': launches,
             'e2e': {'value': e2e, 'unit': 'frames/s', 'h2d_bytes_per_step': host[0].numel() * 4,
                     'd2h_bytes_per_step': 4, 'ms_per_step': ms_e2e / args.steps},
             'roofline': roof,
-            'kernel_ms_per_step': {k: round(v / args.steps, 4) for k, v in sorted(ktot.items(), key=lambda x: -x[1])}}
+            'kernels': per_kernel}
     if not args.no_cpu_baseline and world == 1:
         threads = os.cpu_count() or 1
         fps, ms = time_oracle(100, 8, 3, 1, threads)
