@@ -127,6 +127,14 @@ int hcgs_bn_bwd_il(const float* dy, const float* x, int64_t m, int n_groups, int
                    void* dx_bf16, float* const* dgamma, float* const* dbeta, float* workspace,
                    int64_t workspace_floats, hcgs_stream stream);
 
+/* statistics only (tensor-core build; the recurrent kernel applies them): training != 0 merges `splits`
+ * per-tile {mean, M2} partials ([splits][n_groups*ld_units][2], rows_per_split rows each, m rows in all)
+ * with Chan's formula in a fixed order, writes save_mean / save_invstd ([n_groups*ld_units]) and updates the
+ * running statistics like nn.BatchNorm1d; training == 0 writes the running statistics into save_*.   */
+int hcgs_bn_stats_il(const float* partial, int64_t splits, int64_t rows_per_split, int64_t m, int n_groups,
+                     int units, int ld_units, float* const* running_mean, float* const* running_var, float eps,
+                     float momentum, int training, float* save_mean, float* save_invstd, hcgs_stream stream);
+
 /* ---- persistent recurrent LSTM kernels ------------------------------------------------------
  * hcgs_lstm_pack: gather the four masked U_g [H,H] (ld = ldu) into the plan's compressed
  *   resident layouts (fwd_pack: info[8] floats, bwd_pack: info[9] floats; either may be NULL).
@@ -161,14 +169,19 @@ int hcgs_lstm_bwd(const hcgs_plan* plan, const float* bwd_pack, const float* dh_
  *   [4]=fwd smem bytes [5]=bwd smem bytes [6]=fwd warps [7]=strips/CTA [8]=k-steps [9]=4x4 blocks
  *   [10]=strips/warp [11]=padded hidden size of the cluster.
  * In hcgs_lstm_tc_fwd h_out, hb_out, c_out, gates_out are each optional (at least one of h_out /
- * hb_out); hcgs_lstm_tc_bwd optionally writes a bf16 copy of dpre (same layout) for the GEMMs. */
+ * hb_out); hcgs_lstm_tc_bwd optionally writes a bf16 copy of dpre (same layout) for the GEMMs.
+ * Fused batch norm (neural_networks.py:957-976): with bn_mean / bn_invstd ([4*ld_h], gate-interleaved, from
+ * hcgs_bn_stats_il) the kernel uses (pre - mean) * invstd * gamma_g + beta_g in place of pre, so the
+ * normalised projections never touch HBM; bn_gamma / bn_beta are four per-gate [H] pointers (NULL = 1 / 0).
+ * All four NULL = pre is taken as is.                                                             */
 int hcgs_lstm_tc_info(const hcgs_plan* plan, int cluster_size, int nb, int64_t* info);
 int hcgs_lstm_tc_pack(const hcgs_plan* plan, int cluster_size, const float* const* u, int ldu,
                       uint32_t* fwd_pack, uint32_t* bwd_pack, hcgs_stream stream);
 int hcgs_lstm_tc_fwd(const hcgs_plan* plan, int cluster_size, int nb, const uint32_t* fwd_pack,
                      const float* pre, int ld_h, const float* drop, float drop_scalar, int act,
                      int t_len, int batch, float* h_out, void* hb_out, float* c_out, float* gates_out,
-                     hcgs_stream stream);
+                     const float* bn_mean, const float* bn_invstd, const float* const* bn_gamma,
+                     const float* const* bn_beta, hcgs_stream stream);
 int hcgs_lstm_tc_bwd(const hcgs_plan* plan, int cluster_size, int nb, const uint32_t* bwd_pack,
                      const float* dh_out, const float* gates, const float* c, int ld_h, const float* drop,
                      float drop_scalar, int act, int t_len, int batch, float* dpre, void* dpre_bf16,
@@ -181,11 +194,15 @@ int hcgs_lstm_tc_bwd(const hcgs_plan* plan, int cluster_size, int nb, const uint
  * With n_w = 4 (LSTM gates) the output / dY columns are gate-INTERLEAVED: (unit u, gate g) at
  * column u*4+g; with n_w = 1 (MLP) they are the plain unit index.
  * hcgs_tc_pack_nt: wpack needs nz_tiles * 32*n_w * 32 bf16 (plan info[2] tiles).
+ * hcgs_tc_gemm_nt stats (optional, n_w = 4 only): [ceil(m/128)][ldy][2] floats; the epilogue writes, per
+ *   128-row tile and output column, {mean, M2} of that tile's rows -- the batch-norm statistics of the
+ *   projections at no extra pass over them (merged by hcgs_bn_stats_il).
  * hcgs_cast_bf16 : fp32 [rows, cols] -> bf16 [rows, ldo], pad columns zeroed.                  */
 int hcgs_tc_pack_nt(const hcgs_plan* plan, int n_w, const float* const* w, int ldw, void* wpack,
                     hcgs_stream stream);
 int hcgs_tc_gemm_nt(const hcgs_plan* plan, int n_w, const void* wpack, const void* x_bf16, int64_t ldx,
-                    int64_t m, const float* const* bias, float* y, int64_t ldy, hcgs_stream stream);
+                    int64_t m, const float* const* bias, float* y, int64_t ldy, float* stats,
+                    hcgs_stream stream);
 int hcgs_cast_bf16(const float* x, int64_t ldx, int64_t rows, int cols, void* out, int64_t ldo,
                    hcgs_stream stream);
 /* hcgs_tc_pack_nn / hcgs_tc_gemm_nn: dX[m,k] = sum_{u,g} dY[m,(u,g)] W_g[u,k]; wpack same size as for nt;

@@ -262,18 +262,21 @@ class LSTMLayerTCFunction(torch.autograd.Function):
         wpack = torch.empty(px.nz_tiles * 32 * 4 * 32, device=dev, dtype=torch.bfloat16)
         native.tc_pack_nt(px, ws, wpack)
         pre_raw = torch.empty(M, 4 * ldH, device=dev, dtype=torch.float32)
-        native.tc_gemm_nt(px, 4, wpack, xb, pre_raw)
-        save_mean = save_invstd = None
+        save_mean = save_invstd = bn = None
         if rt.use_bn:
-            pre = torch.empty_like(pre_raw)
+            # statistics come out of the GEMM epilogue (per 128-row tile), the normalisation itself is
+            # applied inside the recurrent kernel: the projections are written once and read once
+            part = torch.empty((M + 127) // 128, 4 * ldH, 2, device=dev, dtype=torch.float32) if rt.training else None
+            native.tc_gemm_nt(px, 4, wpack, xb, pre_raw, None, part)
             save_mean = torch.empty(4 * ldH, device=dev, dtype=torch.float32)
             save_invstd = torch.empty(4 * ldH, device=dev, dtype=torch.float32)
             rms = [r[0] for r in rt.bn_running]
             rvs = [r[1] for r in rt.bn_running]
-            native.bn_fwd_il(pre_raw, pre, 4, H, ldH, [gf, gi, go, gc], [bf, bi, bo, bc], rms, rvs, rt.bn_eps,
-                             rt.bn_momentum, rt.training, save_mean, save_invstd, _ws(dev, 4 * ldH))
+            native.bn_stats_il(part, 128, M, 4, H, ldH, rms, rvs, rt.bn_eps, rt.bn_momentum, rt.training,
+                               save_mean, save_invstd)
+            bn = (save_mean, save_invstd, [gf, gi, go, gc], [bf, bi, bo, bc])
         else:
-            pre = pre_raw
+            native.tc_gemm_nt(px, 4, wpack, xb, pre_raw)
         ph = rt.plan_h
         cfg = tc_config_for(ph, B)
         fwd_pack = torch.empty(cfg.fwd_pack_u32, device=dev, dtype=torch.int32)
@@ -285,7 +288,8 @@ class LSTMLayerTCFunction(torch.autograd.Function):
         if need_grad:
             c = torch.empty(M, ldH, device=dev, dtype=torch.float32)
             gates = torch.empty(M, 4 * ldH, device=dev, dtype=torch.float32)
-        native.lstm_tc_fwd(ph, cfg, fwd_pack, pre, rt.drop, rt.drop_scalar, rt.act, T, B, h.view(M, H), hb, c, gates)
+        native.lstm_tc_fwd(ph, cfg, fwd_pack, pre_raw, rt.drop, rt.drop_scalar, rt.act, T, B, h.view(M, H), hb, c, gates,
+                           bn)
         rt.hb_out = hb
         if need_grad:
             ctx.rt = rt

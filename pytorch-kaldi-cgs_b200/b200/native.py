@@ -51,17 +51,19 @@ SIGNATURES = {
                                _f, _f, c_int64, c_void_p]),
     'hcgs_bn_bwd_il': (c_int, [_f, _f, c_int64, c_int, c_int, c_int, _pp, _f, _f, _f, _f, _pp, _pp, _f, c_int64,
                                c_void_p]),
+    'hcgs_bn_stats_il': (c_int, [_f, c_int64, c_int64, c_int64, c_int, c_int, c_int, _pp, _pp, c_float, c_float, c_int,
+                                 _f, _f, c_void_p]),
     'hcgs_lstm_pack': (c_int, [c_void_p, _pp, c_int, _f, _f, c_void_p]),
     'hcgs_lstm_fwd': (c_int, [c_void_p, _f, _f, _f, c_float, c_int, c_int, c_int, _f, _f, _f, c_int, c_void_p]),
     'hcgs_lstm_bwd': (c_int, [c_void_p, _f, _f, _f, _f, _f, c_float, c_int, c_int, c_int, _f, c_void_p]),
     'hcgs_lstm_tc_info': (c_int, [c_void_p, c_int, c_int, POINTER(c_int64)]),
     'hcgs_lstm_tc_pack': (c_int, [c_void_p, c_int, _pp, c_int, _f, _f, c_void_p]),
     'hcgs_lstm_tc_fwd': (c_int, [c_void_p, c_int, c_int, _f, _f, c_int, _f, c_float, c_int, c_int, c_int, _f, _f, _f,
-                                 _f, c_void_p]),
+                                 _f, _f, _f, _pp, _pp, c_void_p]),
     'hcgs_lstm_tc_bwd': (c_int, [c_void_p, c_int, c_int, _f, _f, _f, _f, c_int, _f, c_float, c_int, c_int, c_int, _f,
                                  _f, c_void_p]),
     'hcgs_tc_pack_nt': (c_int, [c_void_p, c_int, _pp, c_int, _f, c_void_p]),
-    'hcgs_tc_gemm_nt': (c_int, [c_void_p, c_int, _f, _f, c_int64, c_int64, _pp, _f, c_int64, c_void_p]),
+    'hcgs_tc_gemm_nt': (c_int, [c_void_p, c_int, _f, _f, c_int64, c_int64, _pp, _f, c_int64, _f, c_void_p]),
     'hcgs_cast_bf16': (c_int, [_f, c_int64, c_int64, c_int, _f, c_int64, c_void_p]),
     'hcgs_tc_pack_nn': (c_int, [c_void_p, c_int, _pp, c_int, _f, c_void_p]),
     'hcgs_tc_gemm_nn': (c_int, [c_void_p, c_int, _f, _f, c_int64, c_int64, _f, c_int64, c_void_p]),
@@ -97,7 +99,7 @@ def load():
 
 # kernels launched by each entry point (our own kernels only; memsets are not counted)
 KERNELS_PER_CALL = {'hcgs_mask_apply': 1, 'hcgs_quantize_w': 1, 'hcgs_quantize_act': 2, 'hcgs_bsgemm_nt': 1,
-                    'hcgs_bsgemm_nn': 1, 'hcgs_bs_sddmm': 1, 'hcgs_colsum': 1, 'hcgs_bn_fwd': 3, 'hcgs_bn_bwd': 2, 'hcgs_bn_fwd_il': 3, 'hcgs_bn_bwd_il': 2,
+                    'hcgs_bsgemm_nn': 1, 'hcgs_bs_sddmm': 1, 'hcgs_colsum': 1, 'hcgs_bn_fwd': 3, 'hcgs_bn_bwd': 2, 'hcgs_bn_fwd_il': 3, 'hcgs_bn_bwd_il': 2, 'hcgs_bn_stats_il': 1,
                     'hcgs_lstm_pack': 2, 'hcgs_lstm_fwd': 1, 'hcgs_lstm_bwd': 1,
                     'hcgs_lstm_tc_pack': 2, 'hcgs_lstm_tc_fwd': 1, 'hcgs_lstm_tc_bwd': 1,
                     'hcgs_tc_pack_nt': 1, 'hcgs_tc_gemm_nt': 1, 'hcgs_cast_bf16': 1,
@@ -306,6 +308,17 @@ def bn_bwd_il(dy2d, x2d, n_groups, units, ld_units, gammas, save_mean, save_invs
                                  _ptrs(dbetas), _ptr(workspace), workspace.numel(), _stream()), 'hcgs_bn_bwd_il')
 
 
+def bn_stats_il(partial, rows_per_split, m, n_groups, units, ld_units, rmeans, rvars, eps, momentum, training,
+                save_mean, save_invstd):
+    """statistics only (no apply pass): merge the GEMM epilogue's per-tile partials (training) or hand over the
+    running statistics (eval) as save_mean / save_invstd for the fused normalisation in lstm_tc_fwd"""
+    _require_cuda(partial, save_mean, save_invstd)
+    splits = 0 if partial is None else partial.shape[0]
+    _check(load().hcgs_bn_stats_il(_ptr(partial), splits, int(rows_per_split), int(m), n_groups, units, ld_units,
+                                   _ptrs(rmeans), _ptrs(rvars), float(eps), float(momentum), 1 if training else 0,
+                                   _ptr(save_mean), _ptr(save_invstd), _stream()), 'hcgs_bn_stats_il')
+
+
 def lstm_pack(plan, us, fwd_pack=None, bwd_pack=None):
     _require_cuda(fwd_pack, bwd_pack, *us)
     ldu = _row_major_2d(us[0], 'u')
@@ -367,10 +380,16 @@ def pad8(n):
 
 
 def lstm_tc_fwd(plan, cfg, fwd_pack, pre, drop, drop_scalar, act, T, B, h_out=None, hb_out=None, c_out=None,
-                gates_out=None):
+                gates_out=None, bn=None):
     """pre / gates_out: [T*B, 4*ldH] fp32 gate-interleaved (column u*4+g), ldH = pad8(H);
-    c_out [T*B, ldH] fp32, hb_out [T*B, ldH] bf16, h_out [T*B, H] fp32 (all optional but one of h/hb)."""
+    c_out [T*B, ldH] fp32, hb_out [T*B, ldH] bf16, h_out [T*B, H] fp32 (all optional but one of h/hb).
+    bn = (mean, invstd, gammas, betas): batch norm of `pre` fused into the kernel (bn_stats_il)."""
     _require_cuda(pre, drop, h_out, c_out, gates_out)
+    bn_mean = bn_invstd = bn_g = bn_b = None
+    if bn is not None:
+        bn_mean, bn_invstd, bn_g, bn_b = bn
+        _require_cuda(bn_mean, bn_invstd, *bn_g, *bn_b)
+        assert bn_mean.numel() == pre.shape[-1] and bn_invstd.numel() == pre.shape[-1] and len(bn_g) == 4
     _require_cuda_any(fwd_pack, hb_out)
     H = plan.n_out
     ldH = pre.shape[-1] // 4
@@ -379,7 +398,8 @@ def lstm_tc_fwd(plan, cfg, fwd_pack, pre, drop, drop_scalar, act, T, B, h_out=No
         assert t is None or (t.is_contiguous() and t.numel() == T * B * n)
     _check(load().hcgs_lstm_tc_fwd(plan.handle, cfg.cluster_size, cfg.nb, _ptr(fwd_pack), _ptr(pre), ldH, _ptr(drop),
                                    float(drop_scalar), int(act), T, B, _ptr(h_out), _ptr(hb_out), _ptr(c_out),
-                                   _ptr(gates_out), _stream()), 'hcgs_lstm_tc_fwd')
+                                   _ptr(gates_out), _ptr(bn_mean), _ptr(bn_invstd), _ptrs(bn_g), _ptrs(bn_b),
+                                   _stream()), 'hcgs_lstm_tc_fwd')
 
 
 def lstm_tc_bwd(plan, cfg, bwd_pack, dh_out, gates, c, drop, drop_scalar, act, T, B, dpre, dpre_bf16=None):
@@ -405,13 +425,15 @@ def tc_pack_nt(plan, weights, wpack):
                                   _ptr(wpack), _stream()), 'hcgs_tc_pack_nt')
 
 
-def tc_gemm_nt(plan, n_w, wpack, x_bf16, y, biases=None):
-    """y[:, (u, g)] = x @ W_g^T ; x_bf16 [m, ldx] bf16 (pad columns zero), y [m, ldy] fp32."""
-    _require_cuda(y)
+def tc_gemm_nt(plan, n_w, wpack, x_bf16, y, biases=None, stats=None):
+    """y[:, (u, g)] = x @ W_g^T ; x_bf16 [m, ldx] bf16 (pad columns zero), y [m, ldy] fp32.
+    stats (n_w = 4): fp32 [ceil(m/128), ldy, 2] per-tile column {mean, M2} for bn_stats_il."""
+    _require_cuda(y, stats)
+    assert stats is None or (stats.is_contiguous() and stats.numel() == (x_bf16.shape[0] + 127) // 128 * y.stride(0) * 2)
     _require_cuda_any(wpack, x_bf16)
     assert x_bf16.dtype == torch.bfloat16 and x_bf16.dim() == 2 and x_bf16.stride(1) == 1
     _check(load().hcgs_tc_gemm_nt(plan.handle, int(n_w), _ptr(wpack), _ptr(x_bf16), x_bf16.stride(0), x_bf16.shape[0],
-                                  _ptrs(biases), _ptr(y), y.stride(0), _stream()), 'hcgs_tc_gemm_nt')
+                                  _ptrs(biases), _ptr(y), y.stride(0), _ptr(stats), _stream()), 'hcgs_tc_gemm_nt')
 
 
 def tc_pack_nn(plan, weights, wpack):

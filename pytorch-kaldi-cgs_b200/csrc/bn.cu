@@ -106,6 +106,94 @@ __global__ void bn_stats_finalize_kernel(const float* __restrict__ partial, int 
     }
 }
 
+// Same merge for many splits (the per-128-row-tile partials written by the tensor-core GEMM epilogue):
+// block = 32 columns x 8 warps; warp w merges splits w, w+8, ... in order, then the eight partial
+// results are merged in warp order -- deterministic.  training == 0: the saved statistics are the
+// running ones (eval mode), nothing is merged or updated.
+__global__ void __launch_bounds__(256) bn_stats_merge_kernel(const float* __restrict__ partial, int64_t splits,
+                                                             int64_t M, int64_t rows_per_split, int Ctot, int C,
+                                                             int G, int il, float eps, float momentum, int training,
+                                                             PtrPack<float> rmean, PtrPack<float> rvar,
+                                                             float* __restrict__ save_mean,
+                                                             float* __restrict__ save_invstd) {
+    __shared__ float sn[8][33], sm[8][33], sq[8][33];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int col = blockIdx.x * 32 + lane;
+    const bool ok = col < Ctot;
+    int g = 0, c = 0;
+    bool valid = false;
+    if (ok) bn_map(col, C, G, il, g, c, valid);
+    if (!training) {
+        if (warp == 0 && ok) {
+            float mean = 0.f, invstd = 0.f;
+            if (valid) {
+                mean = rmean.p[g][c];
+                invstd = 1.0f / sqrtf(rvar.p[g][c] + eps);
+            }
+            save_mean[col] = mean;
+            save_invstd[col] = invstd;
+        }
+        return;
+    }
+    float n = 0.f, mean = 0.f, m2 = 0.f;
+    if (ok) {
+        for (int64_t s0 = warp; s0 < splits; s0 += 32) {  // four independent loads in flight per trip
+            float2 v[4];
+            float nb[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int64_t sidx = s0 + 8 * q;
+                nb[q] = 0.f;
+                v[q] = make_float2(0.f, 0.f);
+                if (sidx < splits) {
+                    const int64_t mbeg = sidx * rows_per_split;
+                    const int64_t mend = (mbeg + rows_per_split < M) ? mbeg + rows_per_split : M;
+                    nb[q] = (float)(mend - mbeg);
+                    v[q] = __ldg(reinterpret_cast<const float2*>(partial + (sidx * Ctot + col) * 2));
+                }
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                if (nb[q] > 0.f) {
+                    const float nt = n + nb[q];
+                    const float delta = v[q].x - mean;
+                    mean += delta * (nb[q] / nt);
+                    m2 += v[q].y + delta * delta * (n * nb[q] / nt);
+                    n = nt;
+                }
+            }
+        }
+    }
+    sn[warp][lane] = n;
+    sm[warp][lane] = mean;
+    sq[warp][lane] = m2;
+    __syncthreads();
+    if (warp != 0 || !ok) return;
+    n = 0.f, mean = 0.f, m2 = 0.f;
+    for (int w = 0; w < 8; ++w) {
+        const float nb = sn[w][lane];
+        if (nb > 0.f) {
+            const float nt = n + nb;
+            const float delta = sm[w][lane] - mean;
+            mean += delta * (nb / nt);
+            m2 += sq[w][lane] + delta * delta * (n * nb / nt);
+            n = nt;
+        }
+    }
+    const float var_b = m2 / n;
+    const float v = var_b + eps;
+    float r = rsqrtf(v);
+    r = r * (1.5f - 0.5f * v * r * r);
+    save_mean[col] = mean;
+    save_invstd[col] = r;
+    if (!valid) return;
+    if (rmean.p[g]) rmean.p[g][c] = (1.f - momentum) * rmean.p[g][c] + momentum * mean;
+    if (rvar.p[g]) {
+        const float var_u = (n > 1.f) ? m2 / (n - 1.f) : var_b;
+        rvar.p[g][c] = (1.f - momentum) * rvar.p[g][c] + momentum * var_u;
+    }
+}
+
 // y = (x - mean) * invstd * gamma + beta ; in eval mode mean/invstd come from the running stats
 __global__ void __launch_bounds__(256) bn_apply_kernel(const float* __restrict__ x, int ldx,
                                                        float* __restrict__ y, int ldy, int64_t M, int Ctot,
@@ -341,4 +429,31 @@ extern "C" int hcgs_bn_bwd_il(const float* dy, const float* x, int64_t m, int n_
     const int ld = n_groups * ld_units;
     return bn_bwd_impl(dy, ld, x, ld, m, n_groups, units, ld_units, 1, gamma, save_mean, save_invstd, dx, ld, dx_bf16,
                        ld, dgamma, dbeta, workspace, workspace_floats, stream);
+}
+
+// Batch-norm statistics for the tensor-core build, without an apply pass (the recurrent kernel
+// normalises on the fly): training = merge the per-tile {mean, M2} partials of hcgs_tc_gemm_nt
+// and update the running statistics; eval = hand the running statistics over as mean / invstd.
+extern "C" int hcgs_bn_stats_il(const float* partial, int64_t splits, int64_t rows_per_split, int64_t m, int n_groups,
+                                int units, int ld_units, float* const* running_mean, float* const* running_var,
+                                float eps, float momentum, int training, float* save_mean, float* save_invstd,
+                                hcgs_stream stream) {
+    HCGS_REQUIRE(save_mean && save_invstd, "hcgs_bn_stats_il: NULL output");
+    HCGS_REQUIRE(n_groups >= 1 && n_groups <= HCGS_MAX_GROUPS && units >= 1 && ld_units >= units,
+                 "hcgs_bn_stats_il: bad shape");
+    if (training) {
+        HCGS_REQUIRE(partial && splits >= 1 && rows_per_split >= 1 && m >= 1 &&
+                         (splits - 1) * rows_per_split < m && splits * rows_per_split >= m,
+                     "hcgs_bn_stats_il: partials do not cover m=%lld rows", (long long)m);
+    } else {
+        HCGS_REQUIRE(running_mean && running_var, "hcgs_bn_stats_il: eval mode needs running statistics");
+        for (int g = 0; g < n_groups; ++g)
+            HCGS_REQUIRE(running_mean[g] && running_var[g], "hcgs_bn_stats_il: eval mode needs running statistics");
+    }
+    const int Ctot = n_groups * ld_units;
+    bn_stats_merge_kernel<<<(Ctot + 31) / 32, 256, 0, (cudaStream_t)stream>>>(
+        partial, splits, m, rows_per_split, Ctot, units, n_groups, 1, eps, momentum, training,
+        make_pack<float>(running_mean, n_groups), make_pack<float>(running_var, n_groups), save_mean, save_invstd);
+    HCGS_LAUNCH_CHECK();
+    return 0;
 }

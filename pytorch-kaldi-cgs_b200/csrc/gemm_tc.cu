@@ -213,14 +213,19 @@ struct TcNtArgs {
     int64_t M;
     int n_out;                   // output units (rows of one W_g)
     PtrPack<const float> bias;   // per gate [n_out] or NULL
+    float* stats;                // optional [m-tiles][ldy][2]: per 128-row tile and column {mean, M2} (batch norm)
 };
 
 constexpr int NT_STAGES = 4;
 constexpr int NT_A_BYTES = 128 * 64;  // 128 rows x 32 bf16, SWIZZLE_64B
+constexpr int NT_EST = 132;           // floats per staged output row (NG = 4): 16-byte aligned, conflict free
 
 template <int NG>
 __host__ __device__ constexpr int nt_smem_bytes() {
-    return 1024 + NT_STAGES * (NT_A_BYTES + 32 * NG * 64) + 256;
+    // NG = 4: the drained pipeline stages are reused as the [128][NT_EST] fp32 staging tile of the epilogue
+    return 1024 + (NG == 4 ? (NT_STAGES * (NT_A_BYTES + 32 * NG * 64) > 128 * NT_EST * 4
+                                  ? NT_STAGES * (NT_A_BYTES + 32 * NG * 64) : 128 * NT_EST * 4) + 128
+                           : NT_STAGES * (NT_A_BYTES + 32 * NG * 64)) + 256;
 }
 
 template <int NG>
@@ -233,7 +238,9 @@ __global__ void __launch_bounds__(128) tc_gemm_nt_kernel(const __grid_constant__
     unsigned char* smem = reinterpret_cast<unsigned char*>(((uintptr_t)smem_dyn + 1023) & ~(uintptr_t)1023);
     unsigned char* sA = smem;
     unsigned char* sB = smem + NT_STAGES * NT_A_BYTES;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + NT_STAGES * (NT_A_BYTES + B_BYTES));
+    constexpr int STAGE_BYTES = NT_STAGES * (NT_A_BYTES + B_BYTES);
+    constexpr int BAR_OFF = (NG == 4 && 128 * NT_EST * 4 > STAGE_BYTES) ? ((128 * NT_EST * 4 + 127) & ~127) : STAGE_BYTES;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + BAR_OFF);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * NT_STAGES + 1);
     const uint32_t full0 = g_smem_u32(bars), empty0 = g_smem_u32(bars + NT_STAGES),
                    done = g_smem_u32(bars + 2 * NT_STAGES);
@@ -289,6 +296,77 @@ __global__ void __launch_bounds__(128) tc_gemm_nt_kernel(const __grid_constant__
     if (nk > 0) {
         g_mbar_wait(done, 0);
         tc_fence_after();
+    }
+    if constexpr (NG == 4) {
+        // ---- staged epilogue: TMEM -> shared tile -> (column statistics) -> coalesced 512-byte row stores ----
+        float* st = reinterpret_cast<float*>(smem);
+        const int rows = (int)((a.M - m0 < 128) ? (a.M - m0) : 128);
+        const int row = warp * 32 + lane;
+#pragma unroll 1
+        for (int cb = 0; cb < 4; ++cb) {
+            float v[32];
+            if (nk > 0) {
+                tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + cb * 32, v);
+            } else {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] = 0.f;
+            }
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                const int n = cb * 32 + i, u = r * 32 + (n >> 2), g = n & 3;
+                if (u >= a.n_out) v[i] = 0.f;  // pad units stay zero
+                else if (a.bias.p[g]) v[i] += __ldg(a.bias.p[g] + u);
+            }
+            float4* d4 = reinterpret_cast<float4*>(st + (size_t)row * NT_EST + cb * 32);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) d4[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+        }
+        __syncthreads();
+        const int col_t = r * 128 + (int)threadIdx.x;  // this thread's output column for the statistics
+        if (a.stats && col_t < a.ldy) {
+            // fixed summation order (four interleaved chains) => deterministic
+            const float* colp = st + threadIdx.x;
+            float s4[4] = {0.f, 0.f, 0.f, 0.f};
+            int i = 0;
+            for (; i + 4 <= rows; i += 4) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) s4[q] += colp[(size_t)(i + q) * NT_EST];
+            }
+            for (; i < rows; ++i) s4[0] += colp[(size_t)i * NT_EST];
+            const float mean = ((s4[0] + s4[1]) + (s4[2] + s4[3])) / (float)rows;
+            float q4[4] = {0.f, 0.f, 0.f, 0.f};
+            for (i = 0; i + 4 <= rows; i += 4) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const float d = colp[(size_t)(i + q) * NT_EST] - mean;
+                    q4[q] = fmaf(d, d, q4[q]);
+                }
+            }
+            for (; i < rows; ++i) {
+                const float d = colp[(size_t)i * NT_EST] - mean;
+                q4[0] = fmaf(d, d, q4[0]);
+            }
+            const float m2 = (q4[0] + q4[1]) + (q4[2] + q4[3]);
+            *reinterpret_cast<float2*>(a.stats + ((size_t)blockIdx.y * a.ldy + col_t) * 2) = make_float2(mean, m2);
+        }
+        const int c4 = r * 128 + lane * 4;  // first of this lane's four output columns
+        const bool vec = ((a.ldy & 3) == 0) && ((reinterpret_cast<uintptr_t>(a.y) & 15) == 0);
+        for (int i = warp; i < rows; i += 4) {
+            const float4 v = *reinterpret_cast<const float4*>(st + (size_t)i * NT_EST + lane * 4);
+            float* dst = a.y + (m0 + i) * a.ldy + c4;
+            if (vec && c4 + 4 <= a.ldy) {
+                *reinterpret_cast<float4*>(dst) = v;
+            } else {
+                const float e[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    if (c4 + q < a.ldy) dst[q] = e[q];
+            }
+        }
+        tc_fence_before();
+        __syncthreads();
+        if (warp == 1) tmem_dealloc<TCOLS>(tmem);
+        return;
     }
     const int64_t m = m0 + warp * 32 + lane;
 #pragma unroll 1
@@ -356,8 +434,10 @@ extern "C" int hcgs_tc_pack_nt(const hcgs_plan* plan, int n_w, const float* cons
 }
 
 extern "C" int hcgs_tc_gemm_nt(const hcgs_plan* plan, int n_w, const void* wpack, const void* x_bf16, int64_t ldx,
-                               int64_t m, const float* const* bias, float* y, int64_t ldy, hcgs_stream stream) {
+                               int64_t m, const float* const* bias, float* y, int64_t ldy, float* stats,
+                               hcgs_stream stream) {
     HCGS_REQUIRE(plan && wpack && x_bf16 && y, "hcgs_tc_gemm_nt: NULL argument");
+    HCGS_REQUIRE(stats == nullptr || n_w == 4, "hcgs_tc_gemm_nt: fused column statistics need n_w = 4");
     HCGS_REQUIRE(n_w == 1 || n_w == 4, "hcgs_tc_gemm_nt: n_w must be 1 or 4");
     if (m <= 0) return 0;
     HCGS_REQUIRE(ldy >= (int64_t)plan->tr * 32 * n_w || ldy >= (int64_t)plan->n_out * n_w,
@@ -373,6 +453,7 @@ extern "C" int hcgs_tc_gemm_nt(const hcgs_plan* plan, int n_w, const void* wpack
     a.M = m;
     a.n_out = plan->n_out;
     a.bias = make_pack<const float>(bias, n_w);
+    a.stats = stats;
     const int64_t mt = (m + 127) / 128;
     HCGS_REQUIRE(mt <= 65535, "hcgs_tc_gemm_nt: too many rows (%lld)", (long long)m);
     dim3 grid(plan->tr, (unsigned)mt, 1);

@@ -167,6 +167,7 @@ static size_t tc_fwd_smem(const TcPlan& t, int NB) {
     b += tc_align16((size_t)2 * NB * (t.HP + TC_HPAD) * 2);           // h double buffer (bf16)
     b += tc_align16((size_t)2 * NB * (t.Hc * 4 + 16) * 4);            // pre-activation / gate stages (TC_NSTG)
     b += 2 * tc_align16((size_t)NB * (t.Hc + 4) * 4);                 // c and h output stages
+    b += 3 * tc_align16((size_t)t.Hc * 16);                           // fused batch-norm coefficients
     b += 64;                                                          // mbarriers
     return b;
 }
@@ -279,6 +280,10 @@ struct TcFwdArgs {
     __nv_bfloat16* hb_out;  // [T*B][ldH] bf16 copy for the tensor-core GEMMs, or NULL
     float* c_out;           // [T*B][ldH] or NULL
     float* gates_out;       // [T*B][4*ldH] gate-interleaved, or NULL
+    // fused batch norm of the pre-activations (all NULL = pre is used as is): z = (pre - mean) * invstd * gamma + beta
+    const float* bn_mean;    // [4*ldH] gate-interleaved (column u*4+g)
+    const float* bn_invstd;  // [4*ldH]
+    PtrPack<const float> bn_gamma, bn_beta;  // per gate [H] (NULL = 1 / 0)
     int T, B, H, ldH, CL, SPC, KS, HP, act;
     int dbg;  // timing experiments only (HCGS_TC_DEBUG): 1 = no global stores, 2 = no prefetch, 4 = no MMA
 };
@@ -320,9 +325,30 @@ __global__ void __launch_bounds__(TC_MAX_WARPS * 32, 1) lstm_tc_fwd_kernel(const
     sp += tc_align16((size_t)NB * CS * 4);
     float* h_s = reinterpret_cast<float*>(sp);
     sp += tc_align16((size_t)NB * CS * 4);
+    float4* bn_m = reinterpret_cast<float4*>(sp);  // per local unit: the four gates' mean / scale / shift
+    sp += tc_align16((size_t)Hc * 16);
+    float4* bn_a = reinterpret_cast<float4*>(sp);
+    sp += tc_align16((size_t)Hc * 16);
+    float4* bn_b = reinterpret_cast<float4*>(sp);
+    sp += tc_align16((size_t)Hc * 16);
     uint64_t* mbar = reinterpret_cast<uint64_t*>(sp);
+    const bool use_bn = a.bn_mean != nullptr;
 
     // ---- one-time loads ------------------------------------------------------------------------
+    if (use_bn) {
+        for (int i = tid; i < Hc * 4; i += nthreads) {
+            const int ul = i >> 2, g = i & 3, u = u0 + ul;
+            float m = 0.f, sc = 0.f, sh = 0.f;
+            if (u < H) {
+                m = __ldg(a.bn_mean + (size_t)u * 4 + g);
+                sc = __ldg(a.bn_invstd + (size_t)u * 4 + g) * (a.bn_gamma.p[g] ? __ldg(a.bn_gamma.p[g] + u) : 1.f);
+                sh = a.bn_beta.p[g] ? __ldg(a.bn_beta.p[g] + u) : 0.f;
+            }
+            reinterpret_cast<float*>(bn_m)[i] = m;
+            reinterpret_cast<float*>(bn_a)[i] = sc;
+            reinterpret_cast<float*>(bn_b)[i] = sh;
+        }
+    }
     {
         const uint4* s4 = reinterpret_cast<const uint4*>(a.wfrag + (size_t)rank * SPC * KS * 64);
         uint4* d4 = reinterpret_cast<uint4*>(wf_s);
@@ -436,6 +462,12 @@ __global__ void __launch_bounds__(TC_MAX_WARPS * 32, 1) lstm_tc_fwd_kernel(const
             const int sl = warp * SPW + i;
             if (sl >= SPC) continue;  // warp-uniform
             const int ul = sl * 4 + ui;
+            float4 bm = make_float4(0.f, 0.f, 0.f, 0.f), ba = make_float4(1.f, 1.f, 1.f, 1.f), bb = bm;
+            if (use_bn) {
+                bm = bn_m[ul];
+                ba = bn_a[ul];
+                bb = bn_b[ul];
+            }
 #pragma unroll
             for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
@@ -444,7 +476,13 @@ __global__ void __launch_bounds__(TC_MAX_WARPS * 32, 1) lstm_tc_fwd_kernel(const
                     float hval = 0.f;
                     if (ok[i][nt][hh]) {
                         float4* pz = reinterpret_cast<float4*>(stage + (size_t)bl * PRS + ul * 4);
-                        const float4 p = *pz;
+                        float4 p = *pz;
+                        if (use_bn) {
+                            p.x = (p.x - bm.x) * ba.x + bb.x;
+                            p.y = (p.y - bm.y) * ba.y + bb.y;
+                            p.z = (p.z - bm.z) * ba.z + bb.z;
+                            p.w = (p.w - bm.w) * ba.w + bb.w;
+                        }
                         const float zf = acc[i][0][nt][hh * 2 + 0] + p.x;
                         const float zi = acc[i][0][nt][hh * 2 + 1] + p.y;
                         const float zo = acc[i][1][nt][hh * 2 + 0] + p.z;
@@ -595,7 +633,7 @@ __global__ void __launch_bounds__(512, 1) lstm_tc_bwd_kernel(const TcBwdArgs a) 
                 const size_t row = (size_t)(a.T - 1) * a.B + b0 + it_b[j];
                 p_g[j] = __ldg(reinterpret_cast<const float4*>(a.gates + row * 4 * ldH + (size_t)u * 4));
                 p_c[j] = __ldg(a.c + row * ldH + u);
-                p_cm1[j] = (a.T > 1) ? __ldg(a.c + (row - a.B) * ldH + u) : 0.f;
+                p_cm1[j] = __ldg(a.c + (a.T > 1 ? row - a.B : row) * ldH + u);
                 p_dh[j] = __ldg(a.dh_out + row * H + u);
             }
         }
@@ -626,7 +664,7 @@ __global__ void __launch_bounds__(512, 1) lstm_tc_bwd_kernel(const TcBwdArgs a) 
                 const float dct = dh * og * act_grad_from_out(a.act, tc) + dc_carry[j];
                 const float dig = dct * gg * dr[j];
                 const float dgg = dct * ig * dr[j];
-                const float dfg = dct * p_cm1[j];
+                const float dfg = k > 0 ? dct * p_cm1[j] : 0.f;   // c_{-1} = 0
                 dc_carry[j] = dct * fg;
                 dp.x = dfg * fg * (1.f - fg);
                 dp.y = dig * ig * (1.f - ig);
@@ -638,13 +676,14 @@ __global__ void __launch_bounds__(512, 1) lstm_tc_bwd_kernel(const TcBwdArgs a) 
                 if (a.dpreb)
                     *reinterpret_cast<uint2*>(a.dpreb + row * 4 * ldH + (size_t)u * 4) =
                         make_uint2(pack_bf16x2(dp.x, dp.y), pack_bf16x2(dp.z, dp.w));
-                if (k > 0) {
-                    const size_t rowp = row - a.B;
-                    p_g[j] = __ldg(reinterpret_cast<const float4*>(a.gates + rowp * 4 * ldH + (size_t)u * 4));
-                    p_c[j] = p_cm1[j];
-                    p_cm1[j] = (k > 1) ? __ldg(a.c + (rowp - a.B) * ldH + u) : 0.f;
-                    p_dh[j] = __ldg(a.dh_out + rowp * H + u);
-                }
+                // prefetch step k-1 (consumed one step later).  The loads are unconditional on clamped
+                // rows: a select on a loaded value would make this thread wait for DRAM right here.
+                const size_t rowp = (size_t)(k > 0 ? k - 1 : 0) * a.B + b0 + b;
+                const size_t rowpp = (size_t)(k > 1 ? k - 2 : 0) * a.B + b0 + b;
+                p_c[j] = p_cm1[j];
+                p_g[j] = __ldg(reinterpret_cast<const float4*>(a.gates + rowp * 4 * ldH + (size_t)u * 4));
+                p_cm1[j] = __ldg(a.c + rowpp * ldH + u);
+                p_dh[j] = __ldg(a.dh_out + rowp * H + u);
             } else if (u0 + ul < ldH && b0 + b < a.B) {  // pad columns of the padded tensors stay zero
                 const size_t row = (size_t)k * a.B + b0 + b;
                 *reinterpret_cast<float4*>(a.dpre + row * 4 * ldH + (size_t)(u0 + ul) * 4) = dp;
@@ -940,8 +979,10 @@ static int tc_max_active_clusters(const TcPlan& t, int NB, int* fwd_clusters, in
 extern "C" int hcgs_lstm_tc_fwd(const hcgs_plan* plan, int cluster_size, int nb, const uint32_t* fwd_pack,
                                 const float* pre, int ld_h, const float* drop, float drop_scalar, int act,
                                 int t_len, int batch, float* h_out, void* hb_out, float* c_out, float* gates_out,
-                                hcgs_stream stream) {
+                                const float* bn_mean, const float* bn_invstd, const float* const* bn_gamma,
+                                const float* const* bn_beta, hcgs_stream stream) {
     HCGS_REQUIRE(plan && fwd_pack && pre, "hcgs_lstm_tc_fwd: NULL argument");
+    HCGS_REQUIRE((bn_mean == nullptr) == (bn_invstd == nullptr), "hcgs_lstm_tc_fwd: bn_mean and bn_invstd go together");
     HCGS_REQUIRE(h_out || hb_out, "hcgs_lstm_tc_fwd: no output requested");
     if (t_len <= 0 || batch <= 0) return 0;
     TcPlan* t = nullptr;
@@ -960,6 +1001,10 @@ extern "C" int hcgs_lstm_tc_fwd(const hcgs_plan* plan, int cluster_size, int nb,
     a.hb_out = reinterpret_cast<__nv_bfloat16*>(hb_out);
     a.c_out = c_out;
     a.gates_out = gates_out;
+    a.bn_mean = bn_mean;
+    a.bn_invstd = bn_invstd;
+    a.bn_gamma = make_pack<const float>(bn_mean ? bn_gamma : nullptr, 4);
+    a.bn_beta = make_pack<const float>(bn_mean ? bn_beta : nullptr, 4);
     a.T = t_len;
     a.B = batch;
     a.H = t->H;

@@ -51,6 +51,31 @@ def test_tc_gemm_nt(n_out, n_in, blocks, drops, n_w, M):
     ref = torch.stack([bf(x) @ bf(w).t() + (bias[g] if bias else 0) for g, w in enumerate(ws)], 2)  # [M, n_out, n_w]
     got = y.cpu().view(M, ldo, n_w)[:, :n_out, :]
     close(got, ref, 2e-5, 'nt')
+    if ldo > n_out and n_w == 4:
+        assert y.view(M, ldo, n_w)[:, n_out:, :].abs().max().item() == 0, 'pad columns of a padded output must be zero'
+    if n_w == 4:
+        # fused batch-norm statistics: per-tile partials from the epilogue, merged by bn_stats_il
+        part = torch.full(((M + 127) // 128, ldo * 4, 2), 7.0, device=d)
+        y2 = torch.empty_like(y)
+        native.tc_gemm_nt(plan, 4, wpack, xb, y2, None, part)
+        assert torch.equal(y2, y)
+        sm = torch.empty(ldo * 4, device=d)
+        si = torch.empty(ldo * 4, device=d)
+        rm = [torch.zeros(n_out, device=d) for _ in range(4)]
+        rv = [torch.ones(n_out, device=d) for _ in range(4)]
+        native.bn_stats_il(part, 128, M, 4, n_out, ldo, rm, rv, 1e-5, 0.05, True, sm, si)
+        torch.cuda.synchronize()
+        yy = y.cpu().view(M, ldo, 4)[:, :n_out, :].double()
+        mean, var = yy.mean(0), yy.var(0, unbiased=False)
+        close(sm.cpu().view(ldo, 4)[:n_out], mean, 1e-5, 'bn mean')
+        close(si.cpu().view(ldo, 4)[:n_out], 1.0 / torch.sqrt(var + 1e-5), 1e-5, 'bn invstd')
+        for g in range(4):
+            close(rm[g].cpu(), 0.05 * mean[:, g], 1e-5, 'running mean')
+            close(rv[g].cpu(), 0.95 + 0.05 * yy.var(0, unbiased=True)[:, g], 1e-5, 'running var')
+        # eval: the running statistics come back as mean / invstd
+        native.bn_stats_il(None, 128, M, 4, n_out, ldo, rm, rv, 1e-5, 0.05, False, sm, si)
+        close(sm.cpu().view(ldo, 4)[:n_out, 2], rm[2].cpu(), 1e-7, 'eval mean')
+        close(si.cpu().view(ldo, 4)[:n_out, 1], 1.0 / torch.sqrt(rv[1].cpu() + 1e-5), 1e-6, 'eval invstd')
     plan.destroy()
 
 

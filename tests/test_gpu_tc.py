@@ -121,6 +121,23 @@ def test_tc_recurrent_kernels(H, B, T, blocks, drops, act, cl, nb):
     assert torch.equal(dpb.float().cpu(), bf(dpre.cpu())), 'bf16 copy of dpre'
     if ldH > H:
         assert dpre.view(T * B, ldH, 4)[:, H:, :].abs().max().item() == 0, 'pad columns of dpre must be zero'
+    # fused batch norm: (pre - mean) * invstd * gamma + beta inside the kernel == normalising pre beforehand
+    mean = torch.randn(4 * ldH) * 0.3
+    invstd = torch.rand(4 * ldH) + 0.5
+    gam = [torch.rand(H) + 0.5 for _ in range(4)]
+    bet = [torch.randn(H) * 0.2 for _ in range(4)]
+    raw = torch.randn(T, B, 4 * H)
+    raw_i = to_inter(raw, T, B, H, ldH)
+    gi = to_inter(torch.cat(gam).view(1, 1, 4 * H), 1, 1, H, ldH).view(-1)
+    bi = to_inter(torch.cat(bet).view(1, 1, 4 * H), 1, 1, H, ldH).view(-1)
+    normed = ((raw_i - mean) * invstd * gi + bi) * (gi != 0)
+    h_a = torch.empty(T * B, H, device=d)
+    h_b = torch.empty(T * B, H, device=d)
+    native.lstm_tc_fwd(plan, cfg, fp, normed.to(d), drop.to(d), 1.0, code, T, B, h_a)
+    native.lstm_tc_fwd(plan, cfg, fp, raw_i.to(d), drop.to(d), 1.0, code, T, B, h_b,
+                       bn=(mean.to(d), invstd.to(d), [g.to(d) for g in gam], [b.to(d) for b in bet]))
+    torch.cuda.synchronize()
+    check(h_b, h_a, 3e-5, 1e-2, 'fused batch norm')
     # eval variant: scalar drop, only the bf16 output
     hb2 = torch.zeros(T * B, ldH, device=d, dtype=torch.bfloat16)
     native.lstm_tc_fwd(plan, cfg, fp, pre_d, None, 0.8, code, T, B, None, hb2)
