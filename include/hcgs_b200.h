@@ -164,7 +164,8 @@ int hcgs_lstm_bwd(const hcgs_plan* plan, const float* bwd_pack, const float* dh_
  * Layout of this build's tensors (ld_h = H rounded up to a multiple of 8, pad columns zero):
  *   pre / gates / dpre : [T*B, 4*ld_h] fp32, gate-INTERLEAVED: (row, unit u, gate g) at row*4*ld_h + u*4 + g
  *   c                  : [T*B, ld_h] fp32          hb (bf16 copy of h for the GEMMs): [T*B, ld_h]
- *   h_out, dh_out      : [T*B, H] fp32 (the reference's [T,B,H] tensors), drop: [B,H]
+ *   h_out              : [T*B, ld_h] fp32 (pad columns zero; the reference's [T,B,H] tensor is its [:, :H] view)
+ *   dh_out             : [T*B, H] fp32, drop: [B,H]
  * hcgs_lstm_tc_info: info[0]=cluster size [1]=nb [2]=fwd pack uint32s [3]=bwd pack uint32s
  *   [4]=fwd smem bytes [5]=bwd smem bytes [6]=fwd warps [7]=strips/CTA [8]=k-steps [9]=4x4 blocks
  *   [10]=strips/warp [11]=padded hidden size of the cluster.
@@ -182,6 +183,9 @@ int hcgs_lstm_tc_fwd(const hcgs_plan* plan, int cluster_size, int nb, const uint
                      int t_len, int batch, float* h_out, void* hb_out, float* c_out, float* gates_out,
                      const float* bn_mean, const float* bn_invstd, const float* const* bn_gamma,
                      const float* const* bn_beta, hcgs_stream stream);
+/* tuning aid: with HCGS_TC_DEBUG=64 in the environment the recurrent kernels accumulate clock64 deltas per
+ * phase (thread 0 of CTA 0); out16 receives the 16 counters of the last traced launch.              */
+int hcgs_tc_trace_read(int64_t* out16);
 int hcgs_lstm_tc_bwd(const hcgs_plan* plan, int cluster_size, int nb, const uint32_t* bwd_pack,
                      const float* dh_out, const float* gates, const float* c, int ld_h, const float* drop,
                      float drop_scalar, int act, int t_len, int batch, float* dpre, void* dpre_bf16,

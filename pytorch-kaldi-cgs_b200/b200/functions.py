@@ -282,13 +282,14 @@ class LSTMLayerTCFunction(torch.autograd.Function):
         fwd_pack = torch.empty(cfg.fwd_pack_u32, device=dev, dtype=torch.int32)
         bwd_pack = torch.empty(max(cfg.bwd_pack_u32, 1), device=dev, dtype=torch.int32) if need_grad else None
         native.lstm_tc_pack(ph, cfg, us, fwd_pack, bwd_pack)
-        h = torch.empty(T, B, H, device=dev, dtype=torch.float32)
+        h_pad = torch.empty(T, B, ldH, device=dev, dtype=torch.float32)   # rows 16-byte aligned for the bulk stores
+        h = h_pad[:, :, :H]
         hb = torch.empty(M, ldH, device=dev, dtype=torch.bfloat16)
         c = gates = None
         if need_grad:
             c = torch.empty(M, ldH, device=dev, dtype=torch.float32)
             gates = torch.empty(M, 4 * ldH, device=dev, dtype=torch.float32)
-        native.lstm_tc_fwd(ph, cfg, fwd_pack, pre_raw, rt.drop, rt.drop_scalar, rt.act, T, B, h.view(M, H), hb, c, gates,
+        native.lstm_tc_fwd(ph, cfg, fwd_pack, pre_raw, rt.drop, rt.drop_scalar, rt.act, T, B, h_pad.view(M, ldH), hb, c, gates,
                            bn)
         rt.hb_out = hb
         if need_grad:

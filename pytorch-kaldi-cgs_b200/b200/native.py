@@ -62,6 +62,7 @@ SIGNATURES = {
                                  _f, _f, _f, _pp, _pp, c_void_p]),
     'hcgs_lstm_tc_bwd': (c_int, [c_void_p, c_int, c_int, _f, _f, _f, _f, c_int, _f, c_float, c_int, c_int, c_int, _f,
                                  _f, c_void_p]),
+    'hcgs_tc_trace_read': (c_int, [POINTER(c_int64)]),
     'hcgs_tc_pack_nt': (c_int, [c_void_p, c_int, _pp, c_int, _f, c_void_p]),
     'hcgs_tc_gemm_nt': (c_int, [c_void_p, c_int, _f, _f, c_int64, c_int64, _pp, _f, c_int64, _f, c_void_p]),
     'hcgs_cast_bf16': (c_int, [_f, c_int64, c_int64, c_int, _f, c_int64, c_void_p]),
@@ -382,7 +383,7 @@ def pad8(n):
 def lstm_tc_fwd(plan, cfg, fwd_pack, pre, drop, drop_scalar, act, T, B, h_out=None, hb_out=None, c_out=None,
                 gates_out=None, bn=None):
     """pre / gates_out: [T*B, 4*ldH] fp32 gate-interleaved (column u*4+g), ldH = pad8(H);
-    c_out [T*B, ldH] fp32, hb_out [T*B, ldH] bf16, h_out [T*B, H] fp32 (all optional but one of h/hb).
+    c_out / h_out [T*B, ldH] fp32, hb_out [T*B, ldH] bf16, pad columns zero (all optional but one of h/hb).
     bn = (mean, invstd, gammas, betas): batch norm of `pre` fused into the kernel (bn_stats_il)."""
     _require_cuda(pre, drop, h_out, c_out, gates_out)
     bn_mean = bn_invstd = bn_g = bn_b = None
@@ -394,7 +395,7 @@ def lstm_tc_fwd(plan, cfg, fwd_pack, pre, drop, drop_scalar, act, T, B, h_out=No
     H = plan.n_out
     ldH = pre.shape[-1] // 4
     assert pre.is_contiguous() and pre.numel() == T * B * 4 * ldH and ldH % 8 == 0 and ldH >= H
-    for t, n in ((h_out, H), (hb_out, ldH), (c_out, ldH), (gates_out, 4 * ldH)):
+    for t, n in ((h_out, ldH), (hb_out, ldH), (c_out, ldH), (gates_out, 4 * ldH)):
         assert t is None or (t.is_contiguous() and t.numel() == T * B * n)
     _check(load().hcgs_lstm_tc_fwd(plan.handle, cfg.cluster_size, cfg.nb, _ptr(fwd_pack), _ptr(pre), ldH, _ptr(drop),
                                    float(drop_scalar), int(act), T, B, _ptr(h_out), _ptr(hb_out), _ptr(c_out),
@@ -414,6 +415,13 @@ def lstm_tc_bwd(plan, cfg, bwd_pack, dh_out, gates, c, drop, drop_scalar, act, T
     _check(load().hcgs_lstm_tc_bwd(plan.handle, cfg.cluster_size, cfg.nb, _ptr(bwd_pack), _ptr(dh_out), _ptr(gates),
                                    _ptr(c), ldH, _ptr(drop), float(drop_scalar), int(act), T, B, _ptr(dpre),
                                    _ptr(dpre_bf16), _stream()), 'hcgs_lstm_tc_bwd')
+
+
+def tc_trace_read():
+    """per-phase clock totals of the last recurrent launch made with HCGS_TC_DEBUG=64 (tuning aid)"""
+    out = (c_int64 * 16)()
+    _check(load().hcgs_tc_trace_read(out), 'hcgs_tc_trace_read')
+    return [int(v) for v in out]
 
 
 def tc_pack_nt(plan, weights, wpack):

@@ -70,7 +70,11 @@ struct RecurrentPlan {
     size_t smem_fwd = 0, smem_bwd = 0;
 };
 
-struct TcPlan;                 // tensor-core recurrent layouts of one cluster size (lstm_tc.cu)
+struct TcPlan;
+// gemm_tc.cu: CUtensorMap of a [d2][d1][d0] tensor with box {box0, box1, 1} (no swizzle)
+int make_tmap_3d(void* map, int elem_bytes, const void* base, uint64_t d0, uint64_t d1, uint64_t d2,
+                 uint64_t stride1_bytes, uint64_t stride2_bytes, uint32_t box0, uint32_t box1);
+// tensor-core recurrent layouts of one cluster size (lstm_tc.cu)
 void tc_plan_free(TcPlan* t);  // defined in lstm_tc.cu
 
 }  // namespace hcgs

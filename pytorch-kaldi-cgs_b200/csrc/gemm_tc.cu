@@ -171,6 +171,32 @@ static int make_tmap_bf16(CUtensorMap* map, const void* base, int64_t rows, int6
     return 0;
 }
 
+}  // namespace hcgs (reopened below)
+
+// [d2][d1][d0] tensor (d0 contiguous) of 2-byte (bf16) or 4-byte (fp32) elements, no swizzle; used by the
+// recurrent kernels for their per-step [1][16 sequences][slice] boxes.  `map` points to a CUtensorMap.
+int hcgs::make_tmap_3d(void* map, int elem_bytes, const void* base, uint64_t d0, uint64_t d1, uint64_t d2,
+                       uint64_t stride1_bytes, uint64_t stride2_bytes, uint32_t box0, uint32_t box1) {
+    EncodeTiledFn fn = get_encode_fn();
+    HCGS_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled is not available from this driver");
+    HCGS_REQUIRE(elem_bytes == 2 || elem_bytes == 4, "make_tmap_3d: element size %d", elem_bytes);
+    HCGS_REQUIRE(((uintptr_t)base & 15) == 0 && stride1_bytes % 16 == 0 && stride2_bytes % 16 == 0,
+                 "TMA operand must be 16-byte aligned with 16-byte multiple pitches");
+    HCGS_REQUIRE(box0 >= 1 && box0 <= 256 && box1 >= 1 && box1 <= 256 && (box0 * (uint32_t)elem_bytes) % 16 == 0,
+                 "make_tmap_3d: bad box %u x %u", box0, box1);
+    cuuint64_t gdim[3] = {d0, d1, d2};
+    cuuint64_t gstr[2] = {stride1_bytes, stride2_bytes};
+    cuuint32_t box[3] = {box0, box1, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = fn((CUtensorMap*)map, elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32,
+                    3, const_cast<void*>(base), gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    HCGS_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled (3d) failed (%d)", (int)r);
+    return 0;
+}
+
+namespace hcgs {
+
 // ---- weight packing: masked dense fp32 -> pre-swizzled bf16 tiles ------------------------------
 // nt tiles, CSR order (tile t = (r, c) from the plan's flat list): [32*NG rows n = u*NG+g][32 k],
 // 64-byte rows in the SWIZZLE_64B pattern (16-byte chunk index ^= (row >> 1) & 3).

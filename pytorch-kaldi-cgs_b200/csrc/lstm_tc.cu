@@ -25,6 +25,7 @@
 //             -> fp32 partial dh for ALL columns -> pushed to the owner of each column slice
 //             (reduce-scatter over DSMEM, summed by the owner in rank order => deterministic).
 #include <cooperative_groups.h>
+#include <cuda.h>
 #include <cuda_bf16.h>
 
 #include <stdlib.h>
@@ -39,6 +40,7 @@ namespace cg = cooperative_groups;
 namespace hcgs {
 
 constexpr int TC_MAX_WARPS = 16;
+constexpr int TC_MAX_WARPS2 = 20;  // forward kernels with <= 2 strips per warp (register budget 65536 / 640)
 constexpr int TC_HPAD = 8;  // bf16 elements of padding per h row (bank spread, keeps 16 B alignment)
 constexpr int TC_PPAD = 4;  // fp32 elements of padding per partial-dh row
 constexpr int TC_DPAD = 8;  // bf16 elements of padding per dpre row
@@ -99,7 +101,9 @@ static int tc_plan_get(const hcgs_plan* cplan, int CL, TcPlan** out) {
     if (t->SPC & 1) ++t->SPC;  // Hc multiple of 8 -> 16-byte chunks of bf16
     t->Hc = t->SPC * 4;
     t->HP = CL * t->Hc;
-    t->SPW = (t->SPC + TC_MAX_WARPS - 1) / TC_MAX_WARPS;
+    // forward warps: up to 20 warps of <= 2 strips (short per-warp dependency chains), else 16 warps of 3..4
+    t->SPW = (t->SPC + TC_MAX_WARPS2 - 1) / TC_MAX_WARPS2;
+    if (t->SPW > 2) t->SPW = (t->SPC + TC_MAX_WARPS - 1) / TC_MAX_WARPS;
     t->WARPS = (t->SPC + t->SPW - 1) / t->SPW;
     const uint8_t* occ = plan->h_blk44;
     // forward: per strip the kept column groups
@@ -171,6 +175,24 @@ static size_t tc_fwd_smem(const TcPlan& t, int NB) {
     b += 64;                                                          // mbarriers
     return b;
 }
+
+static size_t tc_fwd2_smem(const TcPlan& t, int NB) {
+    const int HcS = (t.Hc % 16 == 8) ? t.Hc : t.Hc + 8;
+    size_t b = 128;                                                   // alignment slack (TMA boxes: 128 B)
+    b += (size_t)2 * NB * t.Hc * 16;                                  // pre-activation / gate stages (dense boxes)
+    b += 2 * (((size_t)NB * t.Hc * 4 + 127) & ~(size_t)127);          // c and h output stages
+    b += ((size_t)NB * t.Hc * 2 + 127) & ~(size_t)127;                // dense bf16 copy of the slice
+    b += ((size_t)2 * t.CL * NB * HcS * 2 + 127) & ~(size_t)127;      // slice-major h double buffer (bf16)
+    b += tc_align16((size_t)t.SPC * t.KS * 2 * 32 * 8);               // B fragments
+    b += 3 * tc_align16((size_t)t.Hc * 16);                           // fused batch-norm coefficients
+    b += 64;                                                          // mbarriers
+    return b;
+}
+static int tc_fwd_version() {
+    const char* e = getenv("HCGS_TC_FWD");
+    return (e && atoi(e) == 1) ? 1 : 2;   // 1 = LSU build (kept for A/B timing), 2 = bulk-copy build
+}
+static size_t tc_fwd_smem_v(const TcPlan& t, int NB) { return tc_fwd_version() == 1 ? tc_fwd_smem(t, NB) : tc_fwd2_smem(t, NB); }
 
 static size_t tc_bwd_smem(const TcPlan& t, int NB) {
     size_t b = 0;
@@ -267,6 +289,28 @@ __device__ __forceinline__ void cp_async_wait() {
     asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
+// phase timing for kernel tuning (HCGS_TC_DEBUG bit 64): thread 0 of every CTA accumulates clock64 deltas per
+// phase in shared memory; CTA 0 publishes them (hcgs_tc_trace_read).  Costs two predicated branches per phase.
+__device__ long long g_tc_trace[16];
+#define TC_TRACE(p)                                   \
+    if (a.dbg & 64) {                                 \
+        if (threadIdx.x == 0) {                       \
+            const long long now_ = clock64();         \
+            trace_s[p] += now_ - trace_s[15];         \
+            trace_s[15] = now_;                       \
+        }                                             \
+    }
+#define TC_TRACE_INIT()                                        \
+    __shared__ long long trace_s[16];                          \
+    if (threadIdx.x == 0) {                                    \
+        for (int i_ = 0; i_ < 15; ++i_) trace_s[i_] = 0;       \
+        trace_s[15] = clock64();                               \
+    }
+#define TC_TRACE_FLUSH()                                                          \
+    if ((a.dbg & 64) && threadIdx.x == 0 && blockIdx.x == 0)                      \
+        for (int i_ = 0; i_ < 15; ++i_) g_tc_trace[i_] = trace_s[i_];
+
+__host__ __device__ inline size_t tc_align128(size_t b) { return (b + 127) & ~(size_t)127; }
 constexpr int TC_NSTG = 2;  // shared-memory stages of the pre-activation stream (refilled right after B1)
 
 struct TcFwdArgs {
@@ -276,7 +320,7 @@ struct TcFwdArgs {
     const float* pre;     // [T*B][4*ldH] gate-interleaved: (row, u, g) at pre[row*4*ldH + u*4 + g]
     const float* drop;    // [B,H] or NULL
     float drop_scalar;
-    float* h_out;           // [T*B][H] fp32 or NULL
+    float* h_out;           // [T*B][ldH] fp32 (pad columns zero) or NULL
     __nv_bfloat16* hb_out;  // [T*B][ldH] bf16 copy for the tensor-core GEMMs, or NULL
     float* c_out;           // [T*B][ldH] or NULL
     float* gates_out;       // [T*B][4*ldH] gate-interleaved, or NULL
@@ -286,6 +330,9 @@ struct TcFwdArgs {
     PtrPack<const float> bn_gamma, bn_beta;  // per gate [H] (NULL = 1 / 0)
     int T, B, H, ldH, CL, SPC, KS, HP, act;
     int dbg;  // timing experiments only (HCGS_TC_DEBUG): 1 = no global stores, 2 = no prefetch, 4 = no MMA
+    // TMA build: [T][B][cols] tensor maps with boxes {BW | Hc, 16, 1}; the pre / gates slice of a CTA is NBX boxes
+    int BW, NBX;
+    alignas(64) CUtensorMap tm_pre, tm_gates, tm_c, tm_h, tm_hb;
 };
 
 // NT m16 tiles of sequences per cluster, SPW strips per warp, KSM >= k-steps per strip (compile time
@@ -298,7 +345,8 @@ __device__ __forceinline__ float act_fwd_t(int act, float x) {
 
 // ACT = HCGS_ACT_TANH compiles the (default) tanh cell without the activation switch; -1 = generic
 template <int NT, int SPW, int KSM, int ACT>
-__global__ void __launch_bounds__(TC_MAX_WARPS * 32, 1) lstm_tc_fwd_kernel(const TcFwdArgs a) {
+__global__ void __launch_bounds__((SPW <= 2 ? TC_MAX_WARPS2 : TC_MAX_WARPS) * 32, 1)
+    lstm_tc_fwd_kernel(const TcFwdArgs a) {
     constexpr int NB = NT * 16;
     cg::cluster_group cluster = cg::this_cluster();
     const int rank = (int)cluster.block_rank();
@@ -334,6 +382,7 @@ __global__ void __launch_bounds__(TC_MAX_WARPS * 32, 1) lstm_tc_fwd_kernel(const
     uint64_t* mbar = reinterpret_cast<uint64_t*>(sp);
     const bool use_bn = a.bn_mean != nullptr;
 
+    TC_TRACE_INIT();
     // ---- one-time loads ------------------------------------------------------------------------
     if (use_bn) {
         for (int i = tid; i < Hc * 4; i += nthreads) {
@@ -423,8 +472,11 @@ __global__ void __launch_bounds__(TC_MAX_WARPS * 32, 1) lstm_tc_fwd_kernel(const
         const __nv_bfloat16* hc = hbuf + (size_t)cur * NB * HPs;
         __nv_bfloat16* hn = hbuf + (size_t)nxt * NB * HPs;
         float* stage = pre_s + (size_t)(k % TC_NSTG) * NB * PRS;
+        TC_TRACE(0);
         cp_async_wait<0>();  // this thread's chunks of step k have landed
+        TC_TRACE(1);
         if (k > 0) mbar_wait(mbar_addr + cur * 8, (uint32_t)(((k - 1) >> 1) & 1));
+        TC_TRACE(2);
         // ---- U h_{k-1}: gather A fragments from the h buffer, B fragments resident ---------------
         float acc[SPW][2][NT][4];
 #pragma unroll
@@ -454,8 +506,11 @@ __global__ void __launch_bounds__(TC_MAX_WARPS * 32, 1) lstm_tc_fwd_kernel(const
                 }
             }
         }
+        TC_TRACE(3);
         __syncthreads();  // B1: every thread's cp.async chunks of step k are visible
+        TC_TRACE(4);
         issue_pre(k + 1);  // the other stage was drained (stored out) before anybody reached B1
+        TC_TRACE(5);
         // ---- fused gates / cell / hidden; gates overwrite the staged pre-activations in place ---
 #pragma unroll
         for (int i = 0; i < SPW; ++i) {
@@ -499,7 +554,9 @@ __global__ void __launch_bounds__(TC_MAX_WARPS * 32, 1) lstm_tc_fwd_kernel(const
                     hn[(size_t)bl * HPs + u0 + ul] = __float2bfloat16_rn(hval);
                 }
         }
+        TC_TRACE(6);
         __syncthreads();  // B2: this CTA's slice of h_k (and the output stages) are complete
+        TC_TRACE(7);
         if (k + 1 < a.T) {
             // push the slice into every peer (coalesced 16-byte DSMEM stores)
             for (int b = warp; b < NB; b += nwarps)
@@ -510,11 +567,14 @@ __global__ void __launch_bounds__(TC_MAX_WARPS * 32, 1) lstm_tc_fwd_kernel(const
                     for (int d = 1; d < CL; ++d)
                         st_cluster_v4(mapa_u32(hbuf_addr + off, (uint32_t)((rank + d) % CL)), v);
                 }
+            TC_TRACE(8);
             __syncthreads();  // B3: all pushes of this CTA are issued
+            TC_TRACE(9);
             if (tid < CL) {   // one arrival per (source CTA, destination CTA)
                 fence_release_cluster();
                 mbar_arrive_cluster_relaxed(mapa_u32(mbar_addr + nxt * 8, (uint32_t)((rank + tid) % CL)));
             }
+            TC_TRACE(10);
         }
         // ---- coalesced global stores of step k (after the signal) and the prefetch of step k+2 --
         if (!(a.dbg & 1)) {
@@ -536,11 +596,349 @@ __global__ void __launch_bounds__(TC_MAX_WARPS * 32, 1) lstm_tc_fwd_kernel(const
                         *reinterpret_cast<uint4*>(a.hb_out + (row0 + b) * ldH + u0 + q * 8) =
                             *reinterpret_cast<const uint4*>(hn + (size_t)b * HPs + u0 + q * 8);
                 if (a.h_out)
-                    for (int q = lane; q < nh; q += 32) a.h_out[(row0 + b) * H + u0 + q] = h_s[b * CS + q];
+                    for (int q = lane; q < nv; q += 32) a.h_out[(row0 + b) * ldH + u0 + q] = h_s[b * CS + q];
             }
         }
+        TC_TRACE(11);
     }
     cp_async_wait<0>();
+    TC_TRACE_FLUSH();
+    cluster.sync();  // nobody exits while peers may still write into its shared memory
+}
+
+// ---- forward, bulk-copy build --------------------------------------------------------------------
+// Same math as lstm_tc_fwd_kernel; all data movement is done by the bulk-copy engine instead of the
+// LSU (measured with HCGS_TC_DEBUG=64: pushes, release fence + arrives, global stores and prefetch
+// issue were >55 % of a step in the LSU version):
+//   * h exchange   : every CTA owns slice `rank` of the slice-major h buffer [2][CL][NB][HcS]; after
+//                    the gate math ONE cp.async.bulk (shared::cta -> shared::cluster) per peer moves the
+//                    whole slice and completes transaction bytes on the peer's mbarrier -- no release
+//                    fence, no arrive messages, no third block barrier;
+//   * pre stream   : one cp.async.bulk global -> shared per sequence row and step (mbarrier tx);
+//   * outputs      : gates (in place in the pre stage), c, h (fp32) and the bf16 copy of h leave by
+//                    one cp.async.bulk shared -> global per row and tensor.
+__device__ __forceinline__ void mbar_expect_tx(uint32_t addr, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(addr), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t mbar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(src), "r"(bytes), "r"(mbar)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_s2g(void* dst, uint32_t src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_s2c(uint32_t dst_cluster, uint32_t src, uint32_t bytes, uint32_t mbar_cluster) {
+    asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     dst_cluster),
+                 "r"(src), "r"(bytes), "r"(mbar_cluster)
+                 : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* m, int c0, int c1, int c2, uint32_t mbar) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+        ::"r"(dst), "l"(m), "r"(c0), "r"(c1), "r"(c2), "r"(mbar)
+        : "memory");
+}
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* m, int c0, int c1, int c2, uint32_t src) {
+    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(m),
+                 "r"(src), "r"(c0), "r"(c1), "r"(c2)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() {
+    asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+template <int N>
+__device__ __forceinline__ void bulk_wait_all() {
+    asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ float rcp_approx(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ float clamp17(float x) { return fminf(fmaxf(x, -17.f), 17.f); }
+
+// bf16 elements per row of one h slice: a multiple of 8 (16-byte rows for the bulk copies) that is 8 mod 16,
+// so the eight rows of an A-fragment gather fall into different bank groups
+__host__ __device__ inline int tc_hcs(int Hc) { return (Hc % 16 == 8) ? Hc : Hc + 8; }
+
+template <int NT, int SPW, int KSM, int ACT>
+__global__ void __launch_bounds__((SPW <= 2 ? TC_MAX_WARPS2 : TC_MAX_WARPS) * 32, 1)
+    lstm_tc_fwd2_kernel(const __grid_constant__ TcFwdArgs a) {
+    constexpr int NB = NT * 16;
+    static_assert(NT == 1, "one m16 tile of sequences per cluster");
+    cg::cluster_group cluster = cg::this_cluster();
+    const int rank = (int)cluster.block_rank();
+    const int CL = a.CL, SPC = a.SPC, KS = a.KS, H = a.H, ldH = a.ldH;
+    const int b0 = (blockIdx.x / CL) * NB;
+    const int Hc = SPC * 4;
+    const int u0 = rank * Hc;
+    const int nv = max(0, min(Hc, ldH - u0));  // units of this CTA inside the padded tensors (multiple of 8)
+    const int HcS = tc_hcs(Hc);
+    const int BW = a.BW, NBX = a.NBX;  // pre / gate stage = NBX boxes of [16][BW] floats
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nthreads = blockDim.x, nwarps = nthreads >> 5;
+
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    unsigned char* sp = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);  // TMA boxes: 128-byte aligned
+    float* pre_s = reinterpret_cast<float*>(sp);  // [2][NBX][16][BW]
+    sp += (size_t)2 * NB * Hc * 16;
+    float* c_s = reinterpret_cast<float*>(sp);  // [16][Hc]
+    sp += tc_align128((size_t)NB * Hc * 4);
+    float* h_s = reinterpret_cast<float*>(sp);
+    sp += tc_align128((size_t)NB * Hc * 4);
+    __nv_bfloat16* hb_s = reinterpret_cast<__nv_bfloat16*>(sp);  // [16][Hc] dense bf16 copy for the store
+    sp += tc_align128((size_t)NB * Hc * 2);
+    __nv_bfloat16* hbuf = reinterpret_cast<__nv_bfloat16*>(sp);  // [2][CL][NB][HcS]
+    sp += tc_align128((size_t)2 * CL * NB * HcS * 2);
+    uint2* wf_s = reinterpret_cast<uint2*>(sp);
+    sp += tc_align16((size_t)SPC * KS * 2 * 32 * 8);
+    float4* bn_m = reinterpret_cast<float4*>(sp);
+    sp += tc_align16((size_t)Hc * 16);
+    float4* bn_a = reinterpret_cast<float4*>(sp);
+    sp += tc_align16((size_t)Hc * 16);
+    float4* bn_b = reinterpret_cast<float4*>(sp);
+    sp += tc_align16((size_t)Hc * 16);
+    uint64_t* mbar = reinterpret_cast<uint64_t*>(sp);  // [0..1] h exchange, [2..3] pre stages
+    const bool use_bn = a.bn_mean != nullptr;
+    const size_t slice = (size_t)NB * HcS;  // bf16 elements of one slice
+    const uint32_t slice_bytes = (uint32_t)(slice * 2);
+    const uint32_t mbar_addr = smem_u32(mbar);
+    const uint32_t hbuf_addr = smem_u32(hbuf);
+    const uint32_t stage_bytes = (uint32_t)NB * Hc * 16;
+    const int stage_floats = NB * Hc * 4;
+
+    TC_TRACE_INIT();
+    if (use_bn) {
+        for (int i = tid; i < Hc * 4; i += nthreads) {
+            const int ul = i >> 2, g = i & 3, u = u0 + ul;
+            float m = 0.f, sc = 0.f, sh = 0.f;
+            if (u < H) {
+                m = __ldg(a.bn_mean + (size_t)u * 4 + g);
+                sc = __ldg(a.bn_invstd + (size_t)u * 4 + g) * (a.bn_gamma.p[g] ? __ldg(a.bn_gamma.p[g] + u) : 1.f);
+                sh = a.bn_beta.p[g] ? __ldg(a.bn_beta.p[g] + u) : 0.f;
+            }
+            reinterpret_cast<float*>(bn_m)[i] = m;
+            reinterpret_cast<float*>(bn_a)[i] = sc;
+            reinterpret_cast<float*>(bn_b)[i] = sh;
+        }
+    }
+    {
+        const uint4* s4 = reinterpret_cast<const uint4*>(a.wfrag + (size_t)rank * SPC * KS * 64);
+        uint4* d4 = reinterpret_cast<uint4*>(wf_s);
+        for (int i = tid; i < SPC * KS * 32; i += nthreads) d4[i] = __ldg(s4 + i);
+        uint32_t* hz = reinterpret_cast<uint32_t*>(hbuf);
+        for (int i = tid; i < (int)(CL * slice); i += nthreads) hz[i] = 0u;  // both buffers (2*CL*slice bf16)
+        for (int i = tid; i < NB * Hc; i += nthreads) c_s[i] = h_s[i] = 0.f;
+        uint32_t* hbz = reinterpret_cast<uint32_t*>(hb_s);
+        for (int i = tid; i < NB * Hc / 2; i += nthreads) hbz[i] = 0u;
+        if (tid == 0) {
+            for (int i = 0; i < 4; ++i) mbar_init(mbar_addr + 8 * i, 1u);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+    }
+    fence_proxy_async();
+    __syncthreads();
+
+    // pre-activations of step `step` -> stage (step & 1): NBX boxes, issued by lane 0 of warps 0..NBX-1
+    auto load_pre = [&](int step) {
+        if (step >= a.T || nv == 0 || lane != 0) return;
+        const uint32_t bar = mbar_addr + 8 * (2 + (step & 1));
+        if (warp == 0) mbar_expect_tx(bar, stage_bytes);
+        for (int x = warp; x < NBX; x += nwarps)
+            tma_load_3d(smem_u32(pre_s + (size_t)(step & 1) * stage_floats + (size_t)x * NB * BW), &a.tm_pre,
+                        u0 * 4 + x * BW, b0, step, bar);
+    };
+    load_pre(0);
+    load_pre(1);
+
+    // ---- per-thread constants: gather offsets of this warp's strips, item state ----------------
+    const int ui = lane & 3;   // unit inside the strip
+    const int br = lane >> 2;  // batch row inside the m16 tile (and +8)
+    int off0[SPW][KSM], off2[SPW][KSM], pzo[SPW];
+    float c_reg[SPW][2], dr[SPW][2];
+    bool ok[SPW][2];
+#pragma unroll
+    for (int i = 0; i < SPW; ++i) {
+        const int sl = warp * SPW + i;
+#pragma unroll
+        for (int ks = 0; ks < KSM; ++ks) {
+            off0[i][ks] = off2[i][ks] = 0;
+            if (sl < SPC && ks < KS) {
+                const uint16_t* cgp = a.cg + ((size_t)(rank * SPC + sl) * KS + ks) * 4 + (ui >> 1);
+                const uint16_t c0 = cgp[0], c2 = cgp[2];
+                const int col0 = (c0 == 0xFFFF ? 0 : c0 * 4) + (lane & 1) * 2;  // padded blocks carry zero weights
+                const int col2 = (c2 == 0xFFFF ? 0 : c2 * 4) + (lane & 1) * 2;
+                off0[i][ks] = (col0 / Hc) * (int)slice + col0 % Hc;
+                off2[i][ks] = (col2 / Hc) * (int)slice + col2 % Hc;
+            }
+        }
+        const int ul = sl * 4 + ui;
+        const int u = u0 + ul;
+        pzo[i] = ((ul * 4) / BW) * (NB * BW) + (ul * 4) % BW;  // box, column inside the box (row term added later)
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+            const int b = b0 + br + 8 * hh;
+            ok[i][hh] = (sl < SPC) && (u < H) && (b < a.B);
+            c_reg[i][hh] = 0.f;
+            dr[i][hh] = a.drop_scalar;
+            if (ok[i][hh] && a.drop) dr[i][hh] = __ldg(a.drop + (size_t)b * H + u);
+        }
+    }
+    cluster.sync();  // every CTA's barriers are initialised and its buffers zeroed before any peer writes
+
+    for (int k = 0; k < a.T; ++k) {
+        const int cur = k & 1, nxt = cur ^ 1;
+        const __nv_bfloat16* hc = hbuf + (size_t)cur * CL * slice;
+        __nv_bfloat16* hn = hbuf + (size_t)nxt * CL * slice + (size_t)rank * slice;  // own slice of h_k
+        float* stage = pre_s + (size_t)cur * stage_floats;
+        TC_TRACE(0);
+        if (k > 0) mbar_wait(mbar_addr + cur * 8, (uint32_t)(((k - 1) >> 1) & 1));
+        TC_TRACE(2);
+        // ---- U h_{k-1}: gather A fragments from the h buffer, B fragments resident ---------------
+        float acc[SPW][2][4];
+#pragma unroll
+        for (int i = 0; i < SPW; ++i) {
+#pragma unroll
+            for (int gp = 0; gp < 2; ++gp)
+#pragma unroll
+                for (int q = 0; q < 4; ++q) acc[i][gp][q] = 0.f;
+        }
+        if (k > 0) {
+#pragma unroll
+            for (int ks = 0; ks < KSM; ++ks) {
+                if (ks < KS) {  // uniform
+#pragma unroll
+                    for (int i = 0; i < SPW; ++i) {
+                        const int sl = warp * SPW + i;
+                        if (sl < SPC) {  // warp-uniform
+                            const uint2 bA = wf_s[((size_t)(sl * KS + ks) * 2 + 0) * 32 + lane];
+                            const uint2 bB = wf_s[((size_t)(sl * KS + ks) * 2 + 1) * 32 + lane];
+                            const __nv_bfloat16* row = hc + (size_t)br * HcS;
+                            const uint32_t a0 = *reinterpret_cast<const uint32_t*>(row + off0[i][ks]);
+                            const uint32_t a1 = *reinterpret_cast<const uint32_t*>(row + 8 * HcS + off0[i][ks]);
+                            const uint32_t a2 = *reinterpret_cast<const uint32_t*>(row + off2[i][ks]);
+                            const uint32_t a3 = *reinterpret_cast<const uint32_t*>(row + 8 * HcS + off2[i][ks]);
+                            mma_bf16_16816(acc[i][0], a0, a1, a2, a3, bA.x, bA.y);
+                            mma_bf16_16816(acc[i][1], a0, a1, a2, a3, bB.x, bB.y);
+                        }
+                    }
+                }
+            }
+        }
+        TC_TRACE(3);
+        // the TMA stores of step k-1 have finished reading c_s / h_s / hb_s / the other pre stage
+        if (lane == 0) bulk_wait_read<0>();
+        if (nv > 0) mbar_wait(mbar_addr + 8 * (2 + cur), (uint32_t)((k >> 1) & 1));  // pre boxes of step k landed
+        TC_TRACE(1);
+        __syncthreads();  // B1
+        TC_TRACE(4);
+        if (k > 0) load_pre(k + 1);  // into the stage drained by the stores of step k-1
+        TC_TRACE(5);
+        // ---- fused gates / cell / hidden; gates overwrite the staged pre-activations in place ---
+#pragma unroll
+        for (int i = 0; i < SPW; ++i) {
+            const int sl = warp * SPW + i;
+            if (sl >= SPC) continue;  // warp-uniform
+            const int ul = sl * 4 + ui;
+            float4 bm = make_float4(0.f, 0.f, 0.f, 0.f), ba = make_float4(1.f, 1.f, 1.f, 1.f), bb = bm;
+            if (use_bn) {
+                bm = bn_m[ul];
+                ba = bn_a[ul];
+                bb = bn_b[ul];
+            }
+#pragma unroll
+            for (int hh = 0; hh < 2; ++hh) {
+                // branch free: absent sequences / pad units run on zeros and are masked at the end, so the
+                // two items and the strips of a thread overlap their MUFU / FMA chains
+                const int bl = br + 8 * hh;
+                const float okf = ok[i][hh] ? 1.f : 0.f;
+                float4* pz = reinterpret_cast<float4*>(stage + pzo[i] + bl * BW);
+                float4 p = *pz;
+                if (use_bn) {
+                    p.x = (p.x - bm.x) * ba.x + bb.x;
+                    p.y = (p.y - bm.y) * ba.y + bb.y;
+                    p.z = (p.z - bm.z) * ba.z + bb.z;
+                    p.w = (p.w - bm.w) * ba.w + bb.w;
+                }
+                const float zf = acc[i][0][hh * 2 + 0] + p.x;
+                const float zi = acc[i][0][hh * 2 + 1] + p.y;
+                const float zo = acc[i][1][hh * 2 + 0] + p.z;
+                const float zc = acc[i][1][hh * 2 + 1] + p.w;
+                float fg, ig, og, gg, cn, hval;
+                if (ACT == HCGS_ACT_TANH) {
+                    // four activations, one reciprocal: 1/(1+e_x) for x in {f, i, o} and 1 - 2/(1+e^{2 z_c});
+                    // arguments clamped to +-17 (sigmoid(-17) = 4e-8) so the product of the four denominators
+                    // stays far inside the fp32 range
+                    const float da = 1.f + __expf(-clamp17(zf)), db = 1.f + __expf(-clamp17(zi));
+                    const float dc = 1.f + __expf(-clamp17(zo)), dd = 1.f + __expf(clamp17(2.f * zc));
+                    const float ab = da * db, cd = dc * dd;
+                    const float r = rcp_approx(ab * cd);
+                    const float rab = r * cd, rcd = r * ab;
+                    fg = rab * db;
+                    ig = rab * da;
+                    og = rcd * dd;
+                    gg = 1.f - 2.f * (rcd * dc);
+                    cn = ig * gg * dr[i][hh] + fg * c_reg[i][hh];
+                    hval = og * (1.f - 2.f * rcp_approx(1.f + __expf(clamp17(2.f * cn))));
+                } else {
+                    fg = fast_sigmoid(zf), ig = fast_sigmoid(zi), og = fast_sigmoid(zo);
+                    gg = act_apply_fast(a.act, zc);
+                    cn = ig * gg * dr[i][hh] + fg * c_reg[i][hh];
+                    hval = og * act_apply_fast(a.act, cn);
+                }
+                cn *= okf;
+                hval *= okf;
+                c_reg[i][hh] = cn;
+                *pz = make_float4(fg * okf, ig * okf, og * okf, gg * okf);
+                c_s[bl * Hc + ul] = cn;
+                h_s[bl * Hc + ul] = hval;
+                const __nv_bfloat16 hbv = __float2bfloat16_rn(hval);
+                hn[(size_t)bl * HcS + ul] = hbv;
+                hb_s[bl * Hc + ul] = hbv;
+            }
+        }
+        fence_proxy_async();  // generic writes above -> visible to the bulk copies issued after the barrier
+        TC_TRACE(6);
+        __syncthreads();  // B2: this CTA's slice of h_k and the output stages are complete
+        TC_TRACE(7);
+        // ---- bulk operations of step k, one per warp (lane 0): slice -> peers, outputs -> HBM --------
+        if (lane == 0) {
+            const int n_push = (k + 1 < a.T) ? CL - 1 : 0;
+            const int n_ops = n_push + NBX + 3;
+            for (int op = warp; op < n_ops; op += nwarps) {
+                if (op < n_push) {  // own slice -> same place in the peer's buffer, completes on the peer's barrier
+                    const uint32_t peer = (uint32_t)((rank + 1 + op) % CL);
+                    const uint32_t off = (uint32_t)(((size_t)nxt * CL + rank) * slice * 2);
+                    bulk_s2c(mapa_u32(hbuf_addr + off, peer), hbuf_addr + off, slice_bytes,
+                             mapa_u32(mbar_addr + nxt * 8, peer));
+                    continue;
+                }
+                if (nv == 0) continue;
+                const int o = op - n_push;
+                if (o < NBX) {
+                    if (a.gates_out)
+                        tma_store_3d(&a.tm_gates, u0 * 4 + o * BW, b0, k, smem_u32(stage + (size_t)o * NB * BW));
+                } else if (o == NBX) {
+                    if (a.c_out) tma_store_3d(&a.tm_c, u0, b0, k, smem_u32(c_s));
+                } else if (o == NBX + 1) {
+                    if (a.hb_out) tma_store_3d(&a.tm_hb, u0, b0, k, smem_u32(hb_s));
+                } else {
+                    if (a.h_out) tma_store_3d(&a.tm_h, u0, b0, k, smem_u32(h_s));
+                }
+            }
+            bulk_commit();
+            // arm this CTA's barrier for the peers' slices of h_k
+            if (warp == nwarps - 1 && k + 1 < a.T) mbar_expect_tx(mbar_addr + nxt * 8, (uint32_t)(CL - 1) * slice_bytes);
+        }
+        TC_TRACE(11);
+    }
+    if (lane == 0) bulk_wait_all<0>();
+    TC_TRACE_FLUSH();
     cluster.sync();  // nobody exits while peers may still write into its shared memory
 }
 
@@ -558,6 +956,7 @@ struct TcBwdArgs {
     float* dpre;             // [T*B][4*ldH] gate-interleaved fp32
     __nv_bfloat16* dpreb;    // optional bf16 copy, same layout
     int T, B, H, ldH, CL, SPC, NS, HP, max_blocks, act;
+    int dbg;  // timing experiments only (HCGS_TC_DEBUG): 1 = no global stores, 2 = no prefetch, 4 = no MMA, 8 = no push
 };
 
 template <int NT, int IT>
@@ -591,6 +990,7 @@ __global__ void __launch_bounds__(512, 1) lstm_tc_bwd_kernel(const TcBwdArgs a) 
     sp += tc_align16((size_t)2 * CL * NB * Hc * 4);
     uint64_t* mbar = reinterpret_cast<uint64_t*>(sp);
 
+    TC_TRACE_INIT();
     {
         const uint4* s4 = reinterpret_cast<const uint4*>(a.wfrag + (size_t)blk0 * 16);
         uint4* d4 = reinterpret_cast<uint4*>(wf_s);
@@ -645,7 +1045,9 @@ __global__ void __launch_bounds__(512, 1) lstm_tc_bwd_kernel(const TcBwdArgs a) 
 
     for (int k = a.T - 1; k >= 0; --k) {
         const int wr = k & 1, rd = wr ^ 1;
+        TC_TRACE(0);
         if (k < a.T - 1) mbar_wait(mbar_addr + rd * 8, (uint32_t)(((a.T - 2 - k) >> 1) & 1));
+        TC_TRACE(1);
         // ---- fused gate derivatives ------------------------------------------------------------
 #pragma unroll
         for (int j = 0; j < IT; ++j) {
@@ -672,18 +1074,22 @@ __global__ void __launch_bounds__(512, 1) lstm_tc_bwd_kernel(const TcBwdArgs a) 
                 dp.w = dgg * act_grad_from_out(a.act, gg);
                 const size_t row = (size_t)k * a.B + b0 + b;
                 const int u = u0 + ul;
-                *reinterpret_cast<float4*>(a.dpre + row * 4 * ldH + (size_t)u * 4) = dp;
-                if (a.dpreb)
-                    *reinterpret_cast<uint2*>(a.dpreb + row * 4 * ldH + (size_t)u * 4) =
-                        make_uint2(pack_bf16x2(dp.x, dp.y), pack_bf16x2(dp.z, dp.w));
+                if (!(a.dbg & 1)) {
+                    *reinterpret_cast<float4*>(a.dpre + row * 4 * ldH + (size_t)u * 4) = dp;
+                    if (a.dpreb)
+                        *reinterpret_cast<uint2*>(a.dpreb + row * 4 * ldH + (size_t)u * 4) =
+                            make_uint2(pack_bf16x2(dp.x, dp.y), pack_bf16x2(dp.z, dp.w));
+                }
                 // prefetch step k-1 (consumed one step later).  The loads are unconditional on clamped
                 // rows: a select on a loaded value would make this thread wait for DRAM right here.
                 const size_t rowp = (size_t)(k > 0 ? k - 1 : 0) * a.B + b0 + b;
                 const size_t rowpp = (size_t)(k > 1 ? k - 2 : 0) * a.B + b0 + b;
                 p_c[j] = p_cm1[j];
-                p_g[j] = __ldg(reinterpret_cast<const float4*>(a.gates + rowp * 4 * ldH + (size_t)u * 4));
-                p_cm1[j] = __ldg(a.c + rowpp * ldH + u);
-                p_dh[j] = __ldg(a.dh_out + rowp * H + u);
+                if (!(a.dbg & 2)) {
+                    p_g[j] = __ldg(reinterpret_cast<const float4*>(a.gates + rowp * 4 * ldH + (size_t)u * 4));
+                    p_cm1[j] = __ldg(a.c + rowpp * ldH + u);
+                    p_dh[j] = __ldg(a.dh_out + rowp * H + u);
+                }
             } else if (u0 + ul < ldH && b0 + b < a.B) {  // pad columns of the padded tensors stay zero
                 const size_t row = (size_t)k * a.B + b0 + b;
                 *reinterpret_cast<float4*>(a.dpre + row * 4 * ldH + (size_t)(u0 + ul) * 4) = dp;
@@ -695,8 +1101,10 @@ __global__ void __launch_bounds__(512, 1) lstm_tc_bwd_kernel(const TcBwdArgs a) 
             d[8] = __float2bfloat16_rn(dp.z);
             d[12] = __float2bfloat16_rn(dp.w);
         }
+        TC_TRACE(2);
         if (k == 0) break;  // dh_{-1} is not needed
         __syncthreads();
+        TC_TRACE(3);
         // ---- partial dh for every column strip from this CTA's rows ---------------------------
         for (int cs = warp; cs < NS; cs += nwarps) {
             float acc[NT][4];
@@ -704,7 +1112,7 @@ __global__ void __launch_bounds__(512, 1) lstm_tc_bwd_kernel(const TcBwdArgs a) 
             for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
                 for (int q = 0; q < 4; ++q) acc[nt][q] = 0.f;
-            const int e1 = csp_s[cs + 1];
+            const int e1 = (a.dbg & 4) ? 0 : csp_s[cs + 1];
             const int koff = (lane & 3) * 2;  // k = gate*4 + row inside the block
             for (int e = csp_s[cs]; e < e1; ++e) {
                 const int rs = rs_s[e];
@@ -729,7 +1137,9 @@ __global__ void __launch_bounds__(512, 1) lstm_tc_bwd_kernel(const TcBwdArgs a) 
                 }
             }
         }
+        TC_TRACE(4);
         __syncthreads();
+        TC_TRACE(5);
         // ---- reduce-scatter: column slice d of the partial sums goes to CTA d -------------------
         for (int db = warp; db < CL * NB; db += nwarps) {  // one warp per (destination, sequence) row
             const int d = db / NB, b = db - d * NB;
@@ -738,15 +1148,19 @@ __global__ void __launch_bounds__(512, 1) lstm_tc_bwd_kernel(const TcBwdArgs a) 
                 uint4 v = make_uint4(0u, 0u, 0u, 0u);
                 if (col < NS * 4) v = *reinterpret_cast<const uint4*>(partial + (size_t)b * HPp + col);
                 const uint32_t off = (uint32_t)((((size_t)(wr * CL + rank) * NB + b) * Hc + q * 4) * 4);
-                st_cluster_v4(mapa_u32(slots_addr + off, (uint32_t)d), v);
+                if (!(a.dbg & 8)) st_cluster_v4(mapa_u32(slots_addr + off, (uint32_t)d), v);
             }
         }
+        TC_TRACE(6);
         __syncthreads();
+        TC_TRACE(7);
         if (tid < CL) {  // one arrival per (source CTA, destination CTA)
             fence_release_cluster();
             mbar_arrive_cluster_relaxed(mapa_u32(mbar_addr + wr * 8, (uint32_t)((rank + tid) % CL)));
         }
+        TC_TRACE(8);
     }
+    TC_TRACE_FLUSH();
     cluster.sync();
 }
 
@@ -834,7 +1248,7 @@ static int tc_resolve(const hcgs_plan* plan, int cluster_size, int nb, TcPlan** 
         if (cluster_size && cands[ci] != cluster_size) continue;
         TcPlan* t = nullptr;
         if (tc_plan_get(plan, cands[ci], &t)) return 1;
-        const bool fits = tc_fwd_smem(*t, NB) <= (size_t)limit && tc_bwd_smem(*t, NB) <= (size_t)limit &&
+        const bool fits = tc_fwd_smem_v(*t, NB) <= (size_t)limit && tc_bwd_smem(*t, NB) <= (size_t)limit &&
                           t->SPW <= 4 && t->KS <= 8 && (t->Hc * NB + 511) / 512 <= 8;
         if (fits) {
             *out = t;
@@ -864,7 +1278,7 @@ extern "C" int hcgs_lstm_tc_info(const hcgs_plan* plan, int cluster_size, int nb
     info[1] = NB;
     info[2] = t->fwd_pack_u32;
     info[3] = t->bwd_pack_u32;
-    info[4] = (int64_t)tc_fwd_smem(*t, NB);
+    info[4] = (int64_t)tc_fwd_smem_v(*t, NB);
     info[5] = (int64_t)tc_bwd_smem(*t, NB);
     info[6] = t->WARPS;
     info[7] = t->SPC;
@@ -910,8 +1324,13 @@ typedef void (*TcBwdKernel)(const TcBwdArgs);
 
 template <int SPW, int ACT>
 static TcFwdKernel tc_pick_fwd_ks(int KS) {
-    if (KS <= 4) return lstm_tc_fwd_kernel<1, SPW, 4, ACT>;
-    if (KS <= 8) return lstm_tc_fwd_kernel<1, SPW, 8, ACT>;
+    if (tc_fwd_version() == 1) {
+        if (KS <= 4) return lstm_tc_fwd_kernel<1, SPW, 4, ACT>;
+        if (KS <= 8) return lstm_tc_fwd_kernel<1, SPW, 8, ACT>;
+        return nullptr;
+    }
+    if (KS <= 4) return lstm_tc_fwd2_kernel<1, SPW, 4, ACT>;
+    if (KS <= 8) return lstm_tc_fwd2_kernel<1, SPW, 8, ACT>;
     return nullptr;
 }
 
@@ -945,7 +1364,7 @@ static int tc_max_active_clusters(const TcPlan& t, int NB, int* fwd_clusters, in
     *fwd_clusters = *bwd_clusters = 0;
     const void* ks[2] = {(const void*)tc_pick_fwd(NB / 16, t.SPW, t.KS, HCGS_ACT_TANH),
                          (const void*)tc_pick_bwd(NB / 16, (t.Hc * NB + 511) / 512)};
-    const size_t smem[2] = {tc_fwd_smem(t, NB), tc_bwd_smem(t, NB)};
+    const size_t smem[2] = {tc_fwd_smem_v(t, NB), tc_bwd_smem(t, NB)};
     const int threads[2] = {t.WARPS * 32, 512};
     int* outs[2] = {fwd_clusters, bwd_clusters};
     for (int i = 0; i < 2; ++i) {
@@ -1018,10 +1437,35 @@ extern "C" int hcgs_lstm_tc_fwd(const hcgs_plan* plan, int cluster_size, int nb,
         const char* e = getenv("HCGS_TC_DEBUG");
         a.dbg = e ? atoi(e) : 0;
     }
+    a.BW = a.NBX = 0;
+    if (tc_fwd_version() != 1) {
+        // boxes of the TMA build: the CTA's [16][Hc*4] fp32 slice as NBX boxes of BW floats; BW % 32 == 16 makes
+        // the float4 accesses of the gate math bank-conflict free
+        const int W = t->Hc * 4;
+        for (int nbx = 1; nbx <= t->Hc; ++nbx) {
+            if (W % nbx) continue;
+            const int bw = W / nbx;
+            if (bw > 256 || bw % 4) continue;
+            if (a.NBX == 0 || bw % 32 == 16) a.BW = bw, a.NBX = nbx;
+            if (bw % 32 == 16 || bw < 64) break;
+        }
+        HCGS_REQUIRE(a.NBX > 0 && t->Hc <= 256, "hcgs_lstm_tc_fwd: slice of %d units has no TMA box", t->Hc);
+        const uint64_t B64 = (uint64_t)batch, T64 = (uint64_t)t_len, ld = (uint64_t)ld_h;
+        if (int rc = make_tmap_3d(&a.tm_pre, 4, pre, 4 * ld, B64, T64, 16 * ld, B64 * 16 * ld, a.BW, 16)) return rc;
+        if (gates_out)
+            if (int rc = make_tmap_3d(&a.tm_gates, 4, gates_out, 4 * ld, B64, T64, 16 * ld, B64 * 16 * ld, a.BW, 16))
+                return rc;
+        if (c_out)
+            if (int rc = make_tmap_3d(&a.tm_c, 4, c_out, ld, B64, T64, 4 * ld, B64 * 4 * ld, t->Hc, 16)) return rc;
+        if (h_out)
+            if (int rc = make_tmap_3d(&a.tm_h, 4, h_out, ld, B64, T64, 4 * ld, B64 * 4 * ld, t->Hc, 16)) return rc;
+        if (hb_out)
+            if (int rc = make_tmap_3d(&a.tm_hb, 2, hb_out, ld, B64, T64, 2 * ld, B64 * 2 * ld, t->Hc, 16)) return rc;
+    }
     TcFwdKernel k = tc_pick_fwd(NB / 16, t->SPW, t->KS, act);
     HCGS_REQUIRE(k != nullptr, "hcgs_lstm_tc_fwd: no kernel for nb=%d strips/warp=%d k-steps=%d", NB, t->SPW, t->KS);
     const int n_clusters = (batch + NB - 1) / NB;
-    return tc_launch(k, a, n_clusters, t->CL, t->WARPS * 32, tc_fwd_smem(*t, NB), (cudaStream_t)stream);
+    return tc_launch(k, a, n_clusters, t->CL, t->WARPS * 32, tc_fwd_smem_v(*t, NB), (cudaStream_t)stream);
 }
 
 extern "C" int hcgs_lstm_tc_bwd(const hcgs_plan* plan, int cluster_size, int nb, const uint32_t* bwd_pack,
@@ -1040,6 +1484,10 @@ extern "C" int hcgs_lstm_tc_bwd(const hcgs_plan* plan, int cluster_size, int nb,
     a.blk_off = t->d_blk_off;
     a.cs_ptr = t->d_cs_ptr;
     a.blk_rs = t->d_blk_rs;
+    {
+        const char* e = getenv("HCGS_TC_DEBUG");
+        a.dbg = e ? atoi(e) : 0;
+    }
     a.dh_out = dh_out;
     a.gates = gates;
     a.c = c;
@@ -1062,4 +1510,13 @@ extern "C" int hcgs_lstm_tc_bwd(const hcgs_plan* plan, int cluster_size, int nb,
     HCGS_REQUIRE(k != nullptr, "hcgs_lstm_tc_bwd: no kernel for nb=%d items=%d", NB, items);
     const int n_clusters = (batch + NB - 1) / NB;
     return tc_launch(k, a, n_clusters, t->CL, 512, tc_bwd_smem(*t, NB), (cudaStream_t)stream);
+}
+
+// tuning aid: per-phase clock totals of CTA 0 / thread 0 of the last traced launch (HCGS_TC_DEBUG bit 64)
+extern "C" int hcgs_tc_trace_read(int64_t* out16) {
+    HCGS_REQUIRE(out16, "hcgs_tc_trace_read: NULL argument");
+    long long h[16];
+    HCGS_CHECK_CUDA(cudaMemcpyFromSymbol(h, hcgs::g_tc_trace, sizeof(h)));
+    for (int i = 0; i < 16; ++i) out16[i] = (int64_t)h[i];
+    return 0;
 }

@@ -101,16 +101,19 @@ def test_tc_recurrent_kernels(H, B, T, blocks, drops, act, cl, nb):
     bp = torch.empty(max(cfg.bwd_pack_u32, 1), device=d, dtype=torch.int32)
     native.lstm_tc_pack(plan, cfg, ud, fp, bp)
     pre_d = to_inter(pre.detach(), T, B, H, ldH).to(d)
-    h = torch.empty(T * B, H, device=d)
+    h_pad = torch.full((T * B, ldH), 5.0, device=d)
+    h = h_pad[:, :H]
     c = torch.zeros(T * B, ldH, device=d)
     gates = torch.zeros(T * B, 4 * ldH, device=d)
     hb = torch.full((T * B, ldH), 7.0, device=d, dtype=torch.bfloat16)
     code = native.ACT_CODES[act]
-    native.lstm_tc_fwd(plan, cfg, fp, pre_d, drop.to(d), 1.0, code, T, B, h, hb, c, gates)
+    native.lstm_tc_fwd(plan, cfg, fp, pre_d, drop.to(d), 1.0, code, T, B, h_pad, hb, c, gates)
     torch.cuda.synchronize()
     # fast transcendental forms (abs err ~1e-6) + occasional bf16 rounding flips of h
-    check(h.view(T, B, H), href, 3e-5, 1e-2, 'h')
+    check(h.reshape(T, B, H), href, 3e-5, 1e-2, 'h')
     assert torch.equal(hb[:, :H].float().cpu(), bf(h.cpu())), 'bf16 copy of h'
+    if ldH > H:
+        assert h_pad[:, H:].abs().max().item() == 0, 'pad columns of h must be zero'
     if ldH > H:
         assert hb[:, H:].float().abs().max().item() == 0, 'pad columns of hb must be zero'
     dpre = torch.full((T * B, 4 * ldH), 3.0, device=d)
@@ -131,8 +134,8 @@ def test_tc_recurrent_kernels(H, B, T, blocks, drops, act, cl, nb):
     gi = to_inter(torch.cat(gam).view(1, 1, 4 * H), 1, 1, H, ldH).view(-1)
     bi = to_inter(torch.cat(bet).view(1, 1, 4 * H), 1, 1, H, ldH).view(-1)
     normed = ((raw_i - mean) * invstd * gi + bi) * (gi != 0)
-    h_a = torch.empty(T * B, H, device=d)
-    h_b = torch.empty(T * B, H, device=d)
+    h_a = torch.empty(T * B, ldH, device=d)
+    h_b = torch.empty(T * B, ldH, device=d)
     native.lstm_tc_fwd(plan, cfg, fp, normed.to(d), drop.to(d), 1.0, code, T, B, h_a)
     native.lstm_tc_fwd(plan, cfg, fp, raw_i.to(d), drop.to(d), 1.0, code, T, B, h_b,
                        bn=(mean.to(d), invstd.to(d), [g.to(d) for g in gam], [b.to(d) for b in bet]))
@@ -159,7 +162,7 @@ def test_tc_matches_fp32_kernels_on_bf16_exact_inputs():
     pre = torch.randn(T, B, 4 * H, device=d)
     fp = torch.empty(cfg.fwd_pack_u32, device=d, dtype=torch.int32)
     native.lstm_tc_pack(plan, cfg, us, fp, None)
-    h = torch.empty(T * B, H, device=d)
+    h = torch.empty(T * B, H, device=d)   # H = 64: no padding
     native.lstm_tc_fwd(plan, cfg, fp, to_inter(pre.cpu(), T, B, H, H).to(d), None, 1.0, 2, T, B, h)
     fp32 = torch.empty(plan.fwd_pack_floats, device=d)
     native.lstm_pack(plan, us, fp32, None)

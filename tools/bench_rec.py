@@ -44,7 +44,7 @@ def main():
         print('   clusters co-resident: fwd %d bwd %d, smem fwd %d bwd %d' % (cfg.max_clusters_fwd, cfg.max_clusters_bwd, cfg.smem_fwd, cfg.smem_bwd))
         pre = torch.randn(T * B, 4 * ldH, device=d)
         drop = torch.bernoulli(torch.full((B, H), 0.8, device=d))
-        h = torch.empty(T * B, H, device=d)
+        h = torch.empty(T * B, native.pad8(H), device=d)
         hb = torch.empty(T * B, ldH, device=d, dtype=torch.bfloat16)
         c = torch.empty(T * B, ldH, device=d)
         gates = torch.empty(T * B, 4 * ldH, device=d)

@@ -1,4 +1,4 @@
-"""Timing experiments on the tensor-core forward recurrence (HCGS_TC_DEBUG bit flags)."""
+"""Timing experiments on the tensor-core recurrence (HCGS_TC_DEBUG bit flags: phases switched off one by one)."""
 import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, 'pytorch-kaldi-cgs_b200')); sys.path.insert(0, ROOT)
@@ -12,15 +12,28 @@ np.random.seed(3)
 mask = torch.from_numpy(hcgs_oracle.conn_mat(H, H, [32, 4], [75, 62.5]).astype(np.float32))
 plan = native.Plan(mask, recurrent=True)
 us = [(torch.randn(H, H) * 0.1 * mask).to(d) for _ in range(4)]
-for B, cl in [(16, 8), (128, 8)]:
+which = sys.argv[1] if len(sys.argv) > 1 else 'both'
+for B, cl in [(16, 8), (128, 8), (512, 4), (16, 4)]:
     cfg = native.TcConfig(plan, cl, 16)
     ldH = native.pad8(H)
     pre = torch.randn(T * B, 4 * ldH, device=d); drop = torch.bernoulli(torch.full((B, H), 0.8, device=d))
-    h = torch.empty(T * B, H, device=d); c = torch.empty(T * B, ldH, device=d); gates = torch.empty(T * B, 4 * ldH, device=d)
+    h = torch.empty(T * B, native.pad8(H), device=d); c = torch.empty(T * B, ldH, device=d); gates = torch.empty(T * B, 4 * ldH, device=d)
     hb = torch.empty(T * B, ldH, device=d, dtype=torch.bfloat16)
     fp = torch.empty(cfg.fwd_pack_u32, device=d, dtype=torch.int32)
-    native.lstm_tc_pack(plan, cfg, us, fp, None)
-    for flags in [0, 1, 2, 3, 4, 7]:
-        os.environ['HCGS_TC_DEBUG'] = str(flags)
-        t = timed(lambda: native.lstm_tc_fwd(plan, cfg, fp, pre, drop, 1.0, 2, T, B, h, hb, c, gates))
-        print('B=%d cl=%d flags=%d: %.3f ms  %.2f us/step' % (B, cl, flags, t, t * 1e3 / T), flush=True)
+    bp = torch.empty(cfg.bwd_pack_u32, device=d, dtype=torch.int32)
+    native.lstm_tc_pack(plan, cfg, us, fp, bp)
+    os.environ['HCGS_TC_DEBUG'] = '0'
+    native.lstm_tc_fwd(plan, cfg, fp, pre, drop, 1.0, 2, T, B, h, hb, c, gates)
+    dh = torch.randn(T * B, H, device=d); dpre = torch.empty(T * B, 4 * ldH, device=d)
+    dpb = torch.empty(T * B, 4 * ldH, device=d, dtype=torch.bfloat16)
+    if which in ('fwd', 'both'):
+        for flags in [0, 1, 2, 3, 4, 7]:
+            os.environ['HCGS_TC_DEBUG'] = str(flags)
+            t = timed(lambda: native.lstm_tc_fwd(plan, cfg, fp, pre, drop, 1.0, 2, T, B, h, hb, c, gates))
+            print('fwd B=%d cl=%d flags=%d: %.3f ms  %.2f us/step' % (B, cl, flags, t, t * 1e3 / T), flush=True)
+    if which in ('bwd', 'both'):
+        for flags in [0, 1, 2, 3, 4, 8, 12, 15]:
+            os.environ['HCGS_TC_DEBUG'] = str(flags)
+            t = timed(lambda: native.lstm_tc_bwd(plan, cfg, bp, dh, gates, c, drop, 1.0, 2, T, B, dpre, dpb))
+            print('bwd B=%d cl=%d flags=%d: %.3f ms  %.2f us/step' % (B, cl, flags, t, t * 1e3 / T), flush=True)
+os.environ['HCGS_TC_DEBUG'] = '0'

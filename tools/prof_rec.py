@@ -15,7 +15,7 @@ us = [(torch.randn(H, H) * 0.1 * mask).to(d) for _ in range(4)]
 cfg = native.TcConfig(plan, cl, 16)
 ldH = native.pad8(H)
 pre = torch.randn(T * B, 4 * ldH, device=d); drop = torch.bernoulli(torch.full((B, H), 0.8, device=d))
-h = torch.empty(T * B, H, device=d); c = torch.empty(T * B, ldH, device=d); gates = torch.empty(T * B, 4 * ldH, device=d)
+h = torch.empty(T * B, native.pad8(H), device=d); c = torch.empty(T * B, ldH, device=d); gates = torch.empty(T * B, 4 * ldH, device=d)
 hb = torch.empty(T * B, ldH, device=d, dtype=torch.bfloat16)
 dh = torch.randn(T * B, H, device=d); dpre = torch.empty(T * B, 4 * ldH, device=d)
 dpb = torch.empty(T * B, 4 * ldH, device=d, dtype=torch.bfloat16)
