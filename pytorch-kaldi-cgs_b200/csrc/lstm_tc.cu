@@ -101,9 +101,10 @@ static int tc_plan_get(const hcgs_plan* cplan, int CL, TcPlan** out) {
     if (t->SPC & 1) ++t->SPC;  // Hc multiple of 8 -> 16-byte chunks of bf16
     t->Hc = t->SPC * 4;
     t->HP = CL * t->Hc;
-    // forward warps: up to 20 warps of <= 2 strips (short per-warp dependency chains), else 16 warps of 3..4
-    t->SPW = (t->SPC + TC_MAX_WARPS2 - 1) / TC_MAX_WARPS2;
-    if (t->SPW > 2) t->SPW = (t->SPC + TC_MAX_WARPS - 1) / TC_MAX_WARPS;
+    // forward compute warps (two more warps drive the copy engine): up to 18 warps of <= 2 strips (short
+    // per-warp dependency chains, 640 threads x 102 registers), else up to 14 warps of 3..4 strips (512 x 128)
+    t->SPW = (t->SPC + (TC_MAX_WARPS2 - 2) - 1) / (TC_MAX_WARPS2 - 2);
+    if (t->SPW > 2) t->SPW = (t->SPC + (TC_MAX_WARPS - 2) - 1) / (TC_MAX_WARPS - 2);
     t->WARPS = (t->SPC + t->SPW - 1) / t->SPW;
     const uint8_t* occ = plan->h_blk44;
     // forward: per strip the kept column groups
@@ -646,6 +647,20 @@ __device__ __forceinline__ void tma_store_3d(const CUtensorMap* m, int c0, int c
                  "r"(src), "r"(c0), "r"(c1), "r"(c2)
                  : "memory");
 }
+__device__ __forceinline__ void st_async_v4(uint32_t cluster_addr, const uint4& v, uint32_t mbar_cluster) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.b32 [%0], {%1, %2, %3, %4}, [%5];" ::"r"(
+                     cluster_addr),
+                 "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "r"(mbar_cluster)
+                 : "memory");
+}
+__device__ __forceinline__ void st_async_b64(uint32_t cluster_addr, uint64_t v, uint32_t mbar_cluster) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b64 [%0], %1, [%2];" ::"r"(cluster_addr),
+                 "l"(v), "r"(mbar_cluster)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_local(uint32_t addr) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(addr) : "memory");
+}
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void bulk_wait_read() {
@@ -681,7 +696,12 @@ __global__ void __launch_bounds__((SPW <= 2 ? TC_MAX_WARPS2 : TC_MAX_WARPS) * 32
     const int nv = max(0, min(Hc, ldH - u0));  // units of this CTA inside the padded tensors (multiple of 8)
     const int HcS = tc_hcs(Hc);
     const int BW = a.BW, NBX = a.NBX;  // pre / gate stage = NBX boxes of [16][BW] floats
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nthreads = blockDim.x, nwarps = nthreads >> 5;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nthreads = blockDim.x;
+    // the last two warps only drive the copy engine (a TMA issue costs its thread 150..600 cycles): DMA warp 0
+    // loads the pre boxes and stores the gate boxes, DMA warp 1 stores c / h / bf16 h and arms the h barrier
+    const int CW = (nthreads >> 5) - 2;  // compute warps
+    const bool is_dma = warp >= CW;
+    const int cthreads = CW * 32;
 
     extern __shared__ __align__(16) unsigned char smem_raw[];
     unsigned char* sp = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);  // TMA boxes: 128-byte aligned
@@ -703,10 +723,10 @@ __global__ void __launch_bounds__((SPW <= 2 ? TC_MAX_WARPS2 : TC_MAX_WARPS) * 32
     sp += tc_align16((size_t)Hc * 16);
     float4* bn_b = reinterpret_cast<float4*>(sp);
     sp += tc_align16((size_t)Hc * 16);
-    uint64_t* mbar = reinterpret_cast<uint64_t*>(sp);  // [0..1] h exchange, [2..3] pre stages
+    uint64_t* mbar = reinterpret_cast<uint64_t*>(sp);
     const bool use_bn = a.bn_mean != nullptr;
     const size_t slice = (size_t)NB * HcS;  // bf16 elements of one slice
-    const uint32_t slice_bytes = (uint32_t)(slice * 2);
+    const uint32_t push_bytes = (uint32_t)NB * Hc * 2;  // bytes one peer receives from this CTA per step
     const uint32_t mbar_addr = smem_u32(mbar);
     const uint32_t hbuf_addr = smem_u32(hbuf);
     const uint32_t stage_bytes = (uint32_t)NB * Hc * 16;
@@ -737,19 +757,34 @@ __global__ void __launch_bounds__((SPW <= 2 ? TC_MAX_WARPS2 : TC_MAX_WARPS) * 32
         uint32_t* hbz = reinterpret_cast<uint32_t*>(hb_s);
         for (int i = tid; i < NB * Hc / 2; i += nthreads) hbz[i] = 0u;
         if (tid == 0) {
-            for (int i = 0; i < 4; ++i) mbar_init(mbar_addr + 8 * i, 1u);
+            // [0..1] h_k complete: CW compute-warp arrivals (own slice) + the arm + the peers' transaction bytes
+            // [2..3] pre boxes landed   [4..5] outputs of a step complete (CW arrivals)   [6] c/h/hb stages drained
+            mbar_init(mbar_addr + 0, (uint32_t)CW + 1u);
+            mbar_init(mbar_addr + 8, (uint32_t)CW + 1u);
+            mbar_init(mbar_addr + 16, 1u);
+            mbar_init(mbar_addr + 24, 1u);
+            mbar_init(mbar_addr + 32, (uint32_t)CW);
+            mbar_init(mbar_addr + 40, (uint32_t)CW);
+            mbar_init(mbar_addr + 48, 1u);
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         }
+    }
+    if (tid == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&a.tm_pre) : "memory");
+        if (a.gates_out) asm volatile("prefetch.tensormap [%0];" ::"l"(&a.tm_gates) : "memory");
+        if (a.c_out) asm volatile("prefetch.tensormap [%0];" ::"l"(&a.tm_c) : "memory");
+        if (a.h_out) asm volatile("prefetch.tensormap [%0];" ::"l"(&a.tm_h) : "memory");
+        if (a.hb_out) asm volatile("prefetch.tensormap [%0];" ::"l"(&a.tm_hb) : "memory");
     }
     fence_proxy_async();
     __syncthreads();
 
     // pre-activations of step `step` -> stage (step & 1): NBX boxes, issued by lane 0 of warps 0..NBX-1
-    auto load_pre = [&](int step) {
-        if (step >= a.T || nv == 0 || lane != 0) return;
+    auto load_pre = [&](int step) {  // DMA warp 0, lane 0
+        if (step >= a.T || nv == 0 || warp != CW || lane != 0) return;
         const uint32_t bar = mbar_addr + 8 * (2 + (step & 1));
-        if (warp == 0) mbar_expect_tx(bar, stage_bytes);
-        for (int x = warp; x < NBX; x += nwarps)
+        mbar_expect_tx(bar, stage_bytes);
+        for (int x = 0; x < NBX; ++x)
             tma_load_3d(smem_u32(pre_s + (size_t)(step & 1) * stage_floats + (size_t)x * NB * BW), &a.tm_pre,
                         u0 * 4 + x * BW, b0, step, bar);
     };
@@ -783,7 +818,7 @@ __global__ void __launch_bounds__((SPW <= 2 ? TC_MAX_WARPS2 : TC_MAX_WARPS) * 32
 #pragma unroll
         for (int hh = 0; hh < 2; ++hh) {
             const int b = b0 + br + 8 * hh;
-            ok[i][hh] = (sl < SPC) && (u < H) && (b < a.B);
+            ok[i][hh] = (sl < SPC) && !is_dma && (u < H) && (b < a.B);
             c_reg[i][hh] = 0.f;
             dr[i][hh] = a.drop_scalar;
             if (ok[i][hh] && a.drop) dr[i][hh] = __ldg(a.drop + (size_t)b * H + u);
@@ -791,153 +826,201 @@ __global__ void __launch_bounds__((SPW <= 2 ? TC_MAX_WARPS2 : TC_MAX_WARPS) * 32
     }
     cluster.sync();  // every CTA's barriers are initialised and its buffers zeroed before any peer writes
 
+    // strips of this warp and its share of the slice (consecutive units => one 8- or 16-byte chunk per row)
+    const int s0w = warp * SPW;
+    const int nstr = max(0, min(SPW, SPC - s0w));
+    const bool push16 = (nstr & 1) == 0 && (SPW & 1) == 0;
+    const int pch = push16 ? nstr / 2 : nstr;  // chunks per row
+    const bool coop_push = CL > 4;
+    const uint32_t mb_h = mbar_addr, mb_pre = mbar_addr + 16, mb_out = mbar_addr + 32, mb_free = mbar_addr + 48;
+
     for (int k = 0; k < a.T; ++k) {
         const int cur = k & 1, nxt = cur ^ 1;
         const __nv_bfloat16* hc = hbuf + (size_t)cur * CL * slice;
         __nv_bfloat16* hn = hbuf + (size_t)nxt * CL * slice + (size_t)rank * slice;  // own slice of h_k
         float* stage = pre_s + (size_t)cur * stage_floats;
-        TC_TRACE(0);
-        if (k > 0) mbar_wait(mbar_addr + cur * 8, (uint32_t)(((k - 1) >> 1) & 1));
-        TC_TRACE(2);
-        // ---- U h_{k-1}: gather A fragments from the h buffer, B fragments resident ---------------
-        float acc[SPW][2][4];
-#pragma unroll
-        for (int i = 0; i < SPW; ++i) {
-#pragma unroll
-            for (int gp = 0; gp < 2; ++gp)
-#pragma unroll
-                for (int q = 0; q < 4; ++q) acc[i][gp][q] = 0.f;
-        }
-        if (k > 0) {
-#pragma unroll
-            for (int ks = 0; ks < KSM; ++ks) {
-                if (ks < KS) {  // uniform
-#pragma unroll
-                    for (int i = 0; i < SPW; ++i) {
-                        const int sl = warp * SPW + i;
-                        if (sl < SPC) {  // warp-uniform
-                            const uint2 bA = wf_s[((size_t)(sl * KS + ks) * 2 + 0) * 32 + lane];
-                            const uint2 bB = wf_s[((size_t)(sl * KS + ks) * 2 + 1) * 32 + lane];
-                            const __nv_bfloat16* row = hc + (size_t)br * HcS;
-                            const uint32_t a0 = *reinterpret_cast<const uint32_t*>(row + off0[i][ks]);
-                            const uint32_t a1 = *reinterpret_cast<const uint32_t*>(row + 8 * HcS + off0[i][ks]);
-                            const uint32_t a2 = *reinterpret_cast<const uint32_t*>(row + off2[i][ks]);
-                            const uint32_t a3 = *reinterpret_cast<const uint32_t*>(row + 8 * HcS + off2[i][ks]);
-                            mma_bf16_16816(acc[i][0], a0, a1, a2, a3, bA.x, bA.y);
-                            mma_bf16_16816(acc[i][1], a0, a1, a2, a3, bB.x, bB.y);
+        if (!is_dma) {
+            // ================= compute warps: no block-wide barrier, only mbarrier waits ====================
+            TC_TRACE(0);
+            if (k > 0) mbar_wait(mb_h + cur * 8, (uint32_t)(((k - 1) >> 1) & 1));  // h_{k-1}: own warps + peers
+            TC_TRACE(2);
+            // ---- U h_{k-1}: gather A fragments from the h buffer, B fragments resident ---------------
+            float acc[SPW][2][4];
+    #pragma unroll
+            for (int i = 0; i < SPW; ++i) {
+    #pragma unroll
+                for (int gp = 0; gp < 2; ++gp)
+    #pragma unroll
+                    for (int q = 0; q < 4; ++q) acc[i][gp][q] = 0.f;
+            }
+            if (k > 0) {
+    #pragma unroll
+                for (int ks = 0; ks < KSM; ++ks) {
+                    if (ks < KS) {  // uniform
+    #pragma unroll
+                        for (int i = 0; i < SPW; ++i) {
+                            const int sl = warp * SPW + i;
+                            if (sl < SPC) {  // warp-uniform
+                                const uint2 bA = wf_s[((size_t)(sl * KS + ks) * 2 + 0) * 32 + lane];
+                                const uint2 bB = wf_s[((size_t)(sl * KS + ks) * 2 + 1) * 32 + lane];
+                                const __nv_bfloat16* row = hc + (size_t)br * HcS;
+                                const uint32_t a0 = *reinterpret_cast<const uint32_t*>(row + off0[i][ks]);
+                                const uint32_t a1 = *reinterpret_cast<const uint32_t*>(row + 8 * HcS + off0[i][ks]);
+                                const uint32_t a2 = *reinterpret_cast<const uint32_t*>(row + off2[i][ks]);
+                                const uint32_t a3 = *reinterpret_cast<const uint32_t*>(row + 8 * HcS + off2[i][ks]);
+                                if (a.dbg & 4) {  // timing experiment: operand loads without the tensor-core instructions
+                                    acc[i][0][0] += __uint_as_float((a0 ^ a1 ^ a2 ^ a3 ^ bA.x ^ bA.y ^ bB.x ^ bB.y) & 0x3f800000u);
+                                    continue;
+                                }
+                                mma_bf16_16816(acc[i][0], a0, a1, a2, a3, bA.x, bA.y);
+                                mma_bf16_16816(acc[i][1], a0, a1, a2, a3, bB.x, bB.y);
+                            }
                         }
                     }
                 }
             }
-        }
-        TC_TRACE(3);
-        // the TMA stores of step k-1 have finished reading c_s / h_s / hb_s / the other pre stage
-        if (lane == 0) bulk_wait_read<0>();
-        if (nv > 0) mbar_wait(mbar_addr + 8 * (2 + cur), (uint32_t)((k >> 1) & 1));  // pre boxes of step k landed
-        TC_TRACE(1);
-        __syncthreads();  // B1
-        TC_TRACE(4);
-        if (k > 0) load_pre(k + 1);  // into the stage drained by the stores of step k-1
-        TC_TRACE(5);
-        // ---- fused gates / cell / hidden; gates overwrite the staged pre-activations in place ---
-#pragma unroll
-        for (int i = 0; i < SPW; ++i) {
-            const int sl = warp * SPW + i;
-            if (sl >= SPC) continue;  // warp-uniform
-            const int ul = sl * 4 + ui;
-            float4 bm = make_float4(0.f, 0.f, 0.f, 0.f), ba = make_float4(1.f, 1.f, 1.f, 1.f), bb = bm;
-            if (use_bn) {
-                bm = bn_m[ul];
-                ba = bn_a[ul];
-                bb = bn_b[ul];
-            }
-#pragma unroll
-            for (int hh = 0; hh < 2; ++hh) {
-                // branch free: absent sequences / pad units run on zeros and are masked at the end, so the
-                // two items and the strips of a thread overlap their MUFU / FMA chains
-                const int bl = br + 8 * hh;
-                const float okf = ok[i][hh] ? 1.f : 0.f;
-                float4* pz = reinterpret_cast<float4*>(stage + pzo[i] + bl * BW);
-                float4 p = *pz;
+            TC_TRACE(3);
+            if (nv > 0) mbar_wait(mb_pre + cur * 8, (uint32_t)((k >> 1) & 1));  // pre boxes of step k landed
+            if (k > 0) mbar_wait(mb_free, (uint32_t)((k - 1) & 1));  // c / h / hb stages of step k-1 were stored out
+            TC_TRACE(1);
+            // ---- fused gates / cell / hidden; gates overwrite the staged pre-activations in place ---
+    #pragma unroll
+            for (int i = 0; i < SPW; ++i) {
+                const int sl = warp * SPW + i;
+                if (sl >= SPC) continue;  // warp-uniform
+                const int ul = sl * 4 + ui;
+                float4 bm = make_float4(0.f, 0.f, 0.f, 0.f), ba = make_float4(1.f, 1.f, 1.f, 1.f), bb = bm;
                 if (use_bn) {
-                    p.x = (p.x - bm.x) * ba.x + bb.x;
-                    p.y = (p.y - bm.y) * ba.y + bb.y;
-                    p.z = (p.z - bm.z) * ba.z + bb.z;
-                    p.w = (p.w - bm.w) * ba.w + bb.w;
+                    bm = bn_m[ul];
+                    ba = bn_a[ul];
+                    bb = bn_b[ul];
                 }
-                const float zf = acc[i][0][hh * 2 + 0] + p.x;
-                const float zi = acc[i][0][hh * 2 + 1] + p.y;
-                const float zo = acc[i][1][hh * 2 + 0] + p.z;
-                const float zc = acc[i][1][hh * 2 + 1] + p.w;
-                float fg, ig, og, gg, cn, hval;
-                if (ACT == HCGS_ACT_TANH) {
-                    // four activations, one reciprocal: 1/(1+e_x) for x in {f, i, o} and 1 - 2/(1+e^{2 z_c});
-                    // arguments clamped to +-17 (sigmoid(-17) = 4e-8) so the product of the four denominators
-                    // stays far inside the fp32 range
-                    const float da = 1.f + __expf(-clamp17(zf)), db = 1.f + __expf(-clamp17(zi));
-                    const float dc = 1.f + __expf(-clamp17(zo)), dd = 1.f + __expf(clamp17(2.f * zc));
-                    const float ab = da * db, cd = dc * dd;
-                    const float r = rcp_approx(ab * cd);
-                    const float rab = r * cd, rcd = r * ab;
-                    fg = rab * db;
-                    ig = rab * da;
-                    og = rcd * dd;
-                    gg = 1.f - 2.f * (rcd * dc);
-                    cn = ig * gg * dr[i][hh] + fg * c_reg[i][hh];
-                    hval = og * (1.f - 2.f * rcp_approx(1.f + __expf(clamp17(2.f * cn))));
-                } else {
-                    fg = fast_sigmoid(zf), ig = fast_sigmoid(zi), og = fast_sigmoid(zo);
-                    gg = act_apply_fast(a.act, zc);
-                    cn = ig * gg * dr[i][hh] + fg * c_reg[i][hh];
-                    hval = og * act_apply_fast(a.act, cn);
+    #pragma unroll
+                for (int hh = 0; hh < 2; ++hh) {
+                    // branch free: absent sequences / pad units run on zeros and are masked at the end, so the
+                    // two items and the strips of a thread overlap their MUFU / FMA chains
+                    const int bl = br + 8 * hh;
+                    const float okf = ok[i][hh] ? 1.f : 0.f;
+                    float4* pz = reinterpret_cast<float4*>(stage + pzo[i] + bl * BW);
+                    float4 p = *pz;
+                    if (use_bn) {
+                        p.x = (p.x - bm.x) * ba.x + bb.x;
+                        p.y = (p.y - bm.y) * ba.y + bb.y;
+                        p.z = (p.z - bm.z) * ba.z + bb.z;
+                        p.w = (p.w - bm.w) * ba.w + bb.w;
+                    }
+                    const float zf = acc[i][0][hh * 2 + 0] + p.x;
+                    const float zi = acc[i][0][hh * 2 + 1] + p.y;
+                    const float zo = acc[i][1][hh * 2 + 0] + p.z;
+                    const float zc = acc[i][1][hh * 2 + 1] + p.w;
+                    float fg, ig, og, gg, cn, hval;
+                    if (ACT == HCGS_ACT_TANH) {
+                        // four activations, one reciprocal: 1/(1+e_x) for x in {f, i, o} and 1 - 2/(1+e^{2 z_c});
+                        // arguments clamped to +-17 (sigmoid(-17) = 4e-8) so the product of the four denominators
+                        // stays far inside the fp32 range
+                        const float da = 1.f + __expf(-clamp17(zf)), db = 1.f + __expf(-clamp17(zi));
+                        const float dc = 1.f + __expf(-clamp17(zo)), dd = 1.f + __expf(clamp17(2.f * zc));
+                        const float ab = da * db, cd = dc * dd;
+                        const float r = rcp_approx(ab * cd);
+                        const float rab = r * cd, rcd = r * ab;
+                        fg = rab * db;
+                        ig = rab * da;
+                        og = rcd * dd;
+                        gg = 1.f - 2.f * (rcd * dc);
+                        cn = ig * gg * dr[i][hh] + fg * c_reg[i][hh];
+                        hval = og * (1.f - 2.f * rcp_approx(1.f + __expf(clamp17(2.f * cn))));
+                    } else {
+                        fg = fast_sigmoid(zf), ig = fast_sigmoid(zi), og = fast_sigmoid(zo);
+                        gg = act_apply_fast(a.act, zc);
+                        cn = ig * gg * dr[i][hh] + fg * c_reg[i][hh];
+                        hval = og * act_apply_fast(a.act, cn);
+                    }
+                    cn *= okf;
+                    hval *= okf;
+                    c_reg[i][hh] = cn;
+                    *pz = make_float4(fg * okf, ig * okf, og * okf, gg * okf);
+                    c_s[bl * Hc + ul] = cn;
+                    h_s[bl * Hc + ul] = hval;
+                    const __nv_bfloat16 hbv = __float2bfloat16_rn(hval);
+                    hn[(size_t)bl * HcS + ul] = hbv;
+                    hb_s[bl * Hc + ul] = hbv;
                 }
-                cn *= okf;
-                hval *= okf;
-                c_reg[i][hh] = cn;
-                *pz = make_float4(fg * okf, ig * okf, og * okf, gg * okf);
-                c_s[bl * Hc + ul] = cn;
-                h_s[bl * Hc + ul] = hval;
-                const __nv_bfloat16 hbv = __float2bfloat16_rn(hval);
-                hn[(size_t)bl * HcS + ul] = hbv;
-                hb_s[bl * Hc + ul] = hbv;
             }
-        }
-        fence_proxy_async();  // generic writes above -> visible to the bulk copies issued after the barrier
-        TC_TRACE(6);
-        __syncthreads();  // B2: this CTA's slice of h_k and the output stages are complete
-        TC_TRACE(7);
-        // ---- bulk operations of step k, one per warp (lane 0): slice -> peers, outputs -> HBM --------
-        if (lane == 0) {
-            const int n_push = (k + 1 < a.T) ? CL - 1 : 0;
-            const int n_ops = n_push + NBX + 3;
-            for (int op = warp; op < n_ops; op += nwarps) {
-                if (op < n_push) {  // own slice -> same place in the peer's buffer, completes on the peer's barrier
-                    const uint32_t peer = (uint32_t)((rank + 1 + op) % CL);
-                    const uint32_t off = (uint32_t)(((size_t)nxt * CL + rank) * slice * 2);
-                    bulk_s2c(mapa_u32(hbuf_addr + off, peer), hbuf_addr + off, slice_bytes,
-                             mapa_u32(mbar_addr + nxt * 8, peer));
-                    continue;
+            fence_proxy_async();  // generic writes above -> visible to the TMA stores of the DMA warps
+            __syncwarp();
+            TC_TRACE(6);
+            // (the DMA warps are released AFTER the per-warp push: their TMA stores compete with the remote stores
+            //  for the shared-memory port and the push is on the critical path -- measured 0.9 us/step)
+            if (lane == 0 && (coop_push || k + 1 >= a.T)) mbar_arrive_local(mb_out + cur * 8);
+            if (k + 1 < a.T) {
+                // h_k -> every peer with st.async: remote stores that complete transaction bytes on the peer's
+                // barrier (no release fence, no arrive message).
+                if (!coop_push) {
+                    // per warp, right after its own gate math, so that the DSMEM traffic overlaps the other warps
+                    const uint32_t base = (uint32_t)((((size_t)nxt * CL + rank) * slice + (size_t)s0w * 4) * 2);
+                    const int total = NB * pch * (CL - 1);
+                    for (int q = lane; q < total; q += 32) {
+                        const int row = q & 15, rest = q >> 4;
+                        const int d = rest % (CL - 1), ch = rest / (CL - 1);
+                        const uint32_t peer = (uint32_t)((rank + 1 + d) % CL);
+                        const uint32_t off = base + (uint32_t)(row * HcS * 2 + ch * (push16 ? 16 : 8));
+                        const unsigned char* src = reinterpret_cast<const unsigned char*>(hbuf) + off;
+                        if (push16)
+                            st_async_v4(mapa_u32(hbuf_addr + off, peer), *reinterpret_cast<const uint4*>(src),
+                                        mapa_u32(mb_h + nxt * 8, peer));
+                        else
+                            st_async_b64(mapa_u32(hbuf_addr + off, peer), *reinterpret_cast<const uint64_t*>(src),
+                                         mapa_u32(mb_h + nxt * 8, peer));
+                    }
+                } else {
+                    // large clusters: many small per-warp bursts cost more than one cooperative sweep over the
+                    // finished slice (measured at cluster 8), so wait for all compute warps first
+                    mbar_wait(mb_out + cur * 8, (uint32_t)((k >> 1) & 1));
+                    const uint32_t base = (uint32_t)(((size_t)nxt * CL + rank) * slice * 2);
+                    const int rchunks = Hc / 8;  // 16-byte chunks per row
+                    for (int q = tid; q < NB * rchunks * (CL - 1); q += cthreads) {
+                        const int d = q / (NB * rchunks), rc = q - d * (NB * rchunks);
+                        const int row = rc / rchunks, ch = rc - row * rchunks;
+                        const uint32_t peer = (uint32_t)((rank + 1 + d) % CL);
+                        const uint32_t off = base + (uint32_t)(row * HcS * 2 + ch * 16);
+                        const uint4 v = *reinterpret_cast<const uint4*>(reinterpret_cast<const unsigned char*>(hbuf) + off);
+                        st_async_v4(mapa_u32(hbuf_addr + off, peer), v, mapa_u32(mb_h + nxt * 8, peer));
+                    }
+                    __syncwarp();
                 }
-                if (nv == 0) continue;
-                const int o = op - n_push;
-                if (o < NBX) {
-                    if (a.gates_out)
-                        tma_store_3d(&a.tm_gates, u0 * 4 + o * BW, b0, k, smem_u32(stage + (size_t)o * NB * BW));
-                } else if (o == NBX) {
-                    if (a.c_out) tma_store_3d(&a.tm_c, u0, b0, k, smem_u32(c_s));
-                } else if (o == NBX + 1) {
+                if (lane == 0) {
+                    if (!coop_push) mbar_arrive_local(mb_out + cur * 8);
+                    mbar_arrive_local(mb_h + nxt * 8);
+                }
+            }
+            TC_TRACE(8);
+        } else if (lane == 0) {
+            // ================= DMA warps: drive the copy engine ==============================================
+            if (warp == CW) {
+                mbar_wait(mb_out + cur * 8, (uint32_t)((k >> 1) & 1));  // gate math of step k is complete
+                if (nv > 0 && a.gates_out) {
+                    for (int x = 0; x < NBX; ++x)
+                        tma_store_3d(&a.tm_gates, u0 * 4 + x * BW, b0, k, smem_u32(stage + (size_t)x * NB * BW));
+                    bulk_commit();
+                    bulk_wait_read<0>();
+                }
+                load_pre(k + 2);  // into the stage just drained
+            } else {
+                // arm this CTA's barrier for the peers' slices of h_k
+                if (k + 1 < a.T) mbar_expect_tx(mb_h + nxt * 8, (uint32_t)(CL - 1) * push_bytes);
+                mbar_wait(mb_out + cur * 8, (uint32_t)((k >> 1) & 1));
+                if (nv > 0) {
                     if (a.hb_out) tma_store_3d(&a.tm_hb, u0, b0, k, smem_u32(hb_s));
-                } else {
+                    if (a.c_out) tma_store_3d(&a.tm_c, u0, b0, k, smem_u32(c_s));
                     if (a.h_out) tma_store_3d(&a.tm_h, u0, b0, k, smem_u32(h_s));
+                    bulk_commit();
+                    bulk_wait_read<0>();
                 }
+                mbar_arrive_local(mb_free);
             }
-            bulk_commit();
-            // arm this CTA's barrier for the peers' slices of h_k
-            if (warp == nwarps - 1 && k + 1 < a.T) mbar_expect_tx(mbar_addr + nxt * 8, (uint32_t)(CL - 1) * slice_bytes);
         }
-        TC_TRACE(11);
     }
-    if (lane == 0) bulk_wait_all<0>();
+    if (is_dma && lane == 0) bulk_wait_all<0>();
     TC_TRACE_FLUSH();
     cluster.sync();  // nobody exits while peers may still write into its shared memory
 }
@@ -1365,7 +1448,7 @@ static int tc_max_active_clusters(const TcPlan& t, int NB, int* fwd_clusters, in
     const void* ks[2] = {(const void*)tc_pick_fwd(NB / 16, t.SPW, t.KS, HCGS_ACT_TANH),
                          (const void*)tc_pick_bwd(NB / 16, (t.Hc * NB + 511) / 512)};
     const size_t smem[2] = {tc_fwd_smem_v(t, NB), tc_bwd_smem(t, NB)};
-    const int threads[2] = {t.WARPS * 32, 512};
+    const int threads[2] = {(t.WARPS + (tc_fwd_version() == 1 ? 0 : 2)) * 32, 512};
     int* outs[2] = {fwd_clusters, bwd_clusters};
     for (int i = 0; i < 2; ++i) {
         if (!ks[i]) continue;
@@ -1465,7 +1548,8 @@ extern "C" int hcgs_lstm_tc_fwd(const hcgs_plan* plan, int cluster_size, int nb,
     TcFwdKernel k = tc_pick_fwd(NB / 16, t->SPW, t->KS, act);
     HCGS_REQUIRE(k != nullptr, "hcgs_lstm_tc_fwd: no kernel for nb=%d strips/warp=%d k-steps=%d", NB, t->SPW, t->KS);
     const int n_clusters = (batch + NB - 1) / NB;
-    return tc_launch(k, a, n_clusters, t->CL, t->WARPS * 32, tc_fwd_smem_v(*t, NB), (cudaStream_t)stream);
+    return tc_launch(k, a, n_clusters, t->CL, (t->WARPS + (tc_fwd_version() == 1 ? 0 : 2)) * 32, tc_fwd_smem_v(*t, NB),
+                     (cudaStream_t)stream);
 }
 
 extern "C" int hcgs_lstm_tc_bwd(const hcgs_plan* plan, int cluster_size, int nb, const uint32_t* bwd_pack,
