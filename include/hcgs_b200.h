@@ -165,7 +165,7 @@ int hcgs_lstm_bwd(const hcgs_plan* plan, const float* bwd_pack, const float* dh_
  *   pre / gates / dpre : [T*B, 4*ld_h] fp32, gate-INTERLEAVED: (row, unit u, gate g) at row*4*ld_h + u*4 + g
  *   c                  : [T*B, ld_h] fp32          hb (bf16 copy of h for the GEMMs): [T*B, ld_h]
  *   h_out              : [T*B, ld_h] fp32 (pad columns zero; the reference's [T,B,H] tensor is its [:, :H] view)
- *   dh_out             : [T*B, H] fp32, drop: [B,H]
+ *   dh_out             : [T*B, ld_h] fp32 (pad columns are ignored), drop: [B,H]
  * hcgs_lstm_tc_info: info[0]=cluster size [1]=nb [2]=fwd pack uint32s [3]=bwd pack uint32s
  *   [4]=fwd smem bytes [5]=bwd smem bytes [6]=fwd warps [7]=strips/CTA [8]=k-steps [9]=4x4 blocks
  *   [10]=strips/warp [11]=padded hidden size of the cluster.

@@ -232,6 +232,20 @@ def tc_config_for(plan, batch):
     return get(0)   # raises with the library's message if no cluster shape fits
 
 
+def _padded_rows(g, T, B, H, ldH):
+    """[T,B,H] gradient -> [T*B, ldH] fp32 with 16-byte aligned rows.  A gradient produced by the layer above is
+    already a [:, :, :H] view of such a buffer and is used in place; anything else is copied once."""
+    M = T * B
+    if ldH == H and g.is_contiguous():
+        return g.view(M, H)
+    if (g.dim() == 3 and g.stride() == (B * ldH, ldH, 1) and (g.storage_offset() * 4) % 16 == 0 and
+            g.untyped_storage().nbytes() >= (g.storage_offset() + M * ldH) * 4):
+        return g.as_strided((M, ldH), (ldH, 1))
+    out = torch.zeros(M, ldH, device=g.device, dtype=torch.float32)
+    out[:, :H].copy_(g.reshape(M, H))
+    return out
+
+
 def _bf16_rows(x2d, ld):
     out = torch.empty(x2d.shape[0], ld, device=x2d.device, dtype=torch.bfloat16)
     native.cast_bf16(x2d, out)
@@ -311,10 +325,10 @@ class LSTMLayerTCFunction(torch.autograd.Function):
         (xb, wf, wi, wo, wc, gf, gi, go, gc, pre_raw, save_mean, save_invstd, c, gates, bwd_pack,
          hb) = ctx.saved_tensors
         dev = dh.device
-        dh = dh.contiguous()
+        dh_pad = _padded_rows(dh, T, B, H, ldH)
         dpre = torch.empty(M, 4 * ldH, device=dev, dtype=torch.float32)
         dpre_b = torch.empty(M, 4 * ldH, device=dev, dtype=torch.bfloat16)
-        native.lstm_tc_bwd(rt.plan_h, ctx.cfg, bwd_pack, dh.view(M, H), gates, c, ctx.drop, ctx.drop_scalar, rt.act,
+        native.lstm_tc_bwd(rt.plan_h, ctx.cfg, bwd_pack, dh_pad, gates, c, ctx.drop, ctx.drop_scalar, rt.act,
                            T, B, dpre, dpre_b)
         dgam = [None] * 4
         dbet = [None] * 4
@@ -337,9 +351,10 @@ class LSTMLayerTCFunction(torch.autograd.Function):
             px = rt.plan_x
             wpack = torch.empty(px.nz_tiles * 32 * 4 * 32, device=dev, dtype=torch.bfloat16)
             native.tc_pack_nn(px, [wf, wi, wo, wc], wpack)
-            dx2d = torch.empty(M, D, device=dev, dtype=torch.float32)
-            native.tc_gemm_nn(px, 4, wpack, dproj_b, dx2d)
-            dx = dx2d.view(T, B, D)
+            # rows padded to 16 bytes: the layer below reads its dh through TMA boxes (no repacking pass)
+            dx_pad = torch.zeros(M, native.pad8(D), device=dev, dtype=torch.float32)
+            native.tc_gemm_nn(px, 4, wpack, dproj_b, dx_pad)
+            dx = dx_pad[:, :D].view(T, B, D)
         return (dx, dws[0], dws[1], dws[2], dws[3], dus[0], dus[1], dus[2], dus[3],
                 dgam[0], dbet[0], dgam[1], dbet[1], dgam[2], dbet[2], dgam[3], dbet[3], None)
 

@@ -404,13 +404,13 @@ def lstm_tc_fwd(plan, cfg, fwd_pack, pre, drop, drop_scalar, act, T, B, h_out=No
 
 
 def lstm_tc_bwd(plan, cfg, bwd_pack, dh_out, gates, c, drop, drop_scalar, act, T, B, dpre, dpre_bf16=None):
-    """gates / dpre / dpre_bf16: [T*B, 4*ldH] gate-interleaved; c [T*B, ldH]; dh_out [T*B, H]."""
+    """gates / dpre / dpre_bf16: [T*B, 4*ldH] gate-interleaved; c and dh_out [T*B, ldH] (pad columns ignored)."""
     _require_cuda(dh_out, gates, c, drop, dpre)
     _require_cuda_any(bwd_pack, dpre_bf16)
     H = plan.n_out
     ldH = gates.shape[-1] // 4
     assert dh_out.is_contiguous() and gates.is_contiguous() and c.is_contiguous() and dpre.is_contiguous()
-    assert dh_out.numel() == T * B * H and gates.numel() == T * B * 4 * ldH and c.numel() == T * B * ldH
+    assert dh_out.numel() == T * B * ldH and gates.numel() == T * B * 4 * ldH and c.numel() == T * B * ldH
     assert dpre.numel() == gates.numel() and (dpre_bf16 is None or dpre_bf16.numel() == gates.numel())
     _check(load().hcgs_lstm_tc_bwd(plan.handle, cfg.cluster_size, cfg.nb, _ptr(bwd_pack), _ptr(dh_out), _ptr(gates),
                                    _ptr(c), ldH, _ptr(drop), float(drop_scalar), int(act), T, B, _ptr(dpre),

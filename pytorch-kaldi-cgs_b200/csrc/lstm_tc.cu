@@ -195,6 +195,26 @@ static int tc_fwd_version() {
 }
 static size_t tc_fwd_smem_v(const TcPlan& t, int NB) { return tc_fwd_version() == 1 ? tc_fwd_smem(t, NB) : tc_fwd2_smem(t, NB); }
 
+static int tc_bwd_version() {
+    const char* e = getenv("HCGS_TC_BWD");
+    return (e && atoi(e) == 1) ? 1 : 2;   // 1 = LSU build (kept for A/B timing), 2 = asynchronous build
+}
+static size_t tc_bwd2_smem(const TcPlan& t, int NB) {
+    size_t b = 128;                                                   // alignment slack (TMA boxes: 128 B)
+    b += (size_t)2 * NB * t.Hc * 16;                                  // gate stages (dense boxes)
+    b += ((size_t)2 * NB * t.Hc * 4 + 127) & ~(size_t)127;            // c ring
+    b += ((size_t)NB * t.Hc * 4 + 127) & ~(size_t)127;                // dh
+    b += ((size_t)t.CL * NB * t.Hc * 4 + 127) & ~(size_t)127;         // partial-dh slots, one per source CTA
+    b += tc_align16((size_t)NB * (t.Hc * 4 + 8) * 2);                 // bf16 dpre tile (MMA A operand)
+    b += tc_align16((size_t)std::max(t.max_cta_blocks, 1) * 16 * 8);  // B fragments (16 lanes x 8 B)
+    b += tc_align16((size_t)std::max(t.max_cta_blocks, 1) * 2);       // row strip of each block
+    b += tc_align16((size_t)(t.NS + 1) * 4);                          // CSR over column strips
+    b += 64;
+    return b;
+}
+static size_t tc_bwd_smem(const TcPlan& t, int NB);
+static size_t tc_bwd_smem_v(const TcPlan& t, int NB) { return tc_bwd_version() == 1 ? tc_bwd_smem(t, NB) : tc_bwd2_smem(t, NB); }
+
 static size_t tc_bwd_smem(const TcPlan& t, int NB) {
     size_t b = 0;
     b += tc_align16((size_t)t.max_cta_blocks * 16 * 8);               // B fragments (16 lanes x 8 B)
@@ -247,6 +267,27 @@ __device__ __forceinline__ void mbar_wait(uint32_t addr, uint32_t parity) {
     for (int spin = 0; spin < (1 << 22); ++spin)
         if (mbar_try_wait(addr, parity)) return;
     __trap();
+}
+// Development variant (HCGS_TC_DEBUG bit 512): the first wait that times out records {tag, block, warp, parity,
+// step} and every later wait returns at once, so the kernel ends normally and hcgs_tc_trace_read shows who hung.
+__device__ int g_tc_fail[8];
+__device__ __forceinline__ void mbar_wait_dbg(uint32_t addr, uint32_t parity, int dbg, int tag, int step) {
+    if (!(dbg & 512)) {
+        mbar_wait(addr, parity);
+        return;
+    }
+    for (int spin = 0; spin < (1 << 18); ++spin) {
+        if (mbar_try_wait(addr, parity)) return;
+        if ((spin & 255) == 255 && *reinterpret_cast<volatile int*>(&g_tc_fail[0])) return;
+    }
+    if (atomicCAS(&g_tc_fail[0], 0, 1) == 0) {
+        g_tc_fail[1] = tag;
+        g_tc_fail[2] = (int)blockIdx.x;
+        g_tc_fail[3] = (int)(threadIdx.x >> 5);
+        g_tc_fail[4] = (int)parity;
+        g_tc_fail[5] = step;
+        __threadfence();
+    }
 }
 
 __device__ __forceinline__ void st_cluster_v4(uint32_t cluster_addr, const uint4& v) {
@@ -1040,6 +1081,9 @@ struct TcBwdArgs {
     __nv_bfloat16* dpreb;    // optional bf16 copy, same layout
     int T, B, H, ldH, CL, SPC, NS, HP, max_blocks, act;
     int dbg;  // timing experiments only (HCGS_TC_DEBUG): 1 = no global stores, 2 = no prefetch, 4 = no MMA, 8 = no push
+    // TMA build: dh_out is [T*B][ldH]; [T][B][cols] tensor maps with boxes {BW | Hc, 16, 1}
+    int BW, NBX;
+    alignas(64) CUtensorMap tm_gates, tm_c, tm_dh;
 };
 
 template <int NT, int IT>
@@ -1247,6 +1291,305 @@ __global__ void __launch_bounds__(512, 1) lstm_tc_bwd_kernel(const TcBwdArgs a) 
     cluster.sync();
 }
 
+// ---- backward, asynchronous build ----------------------------------------------------------------
+// Same recurrence as lstm_tc_bwd_kernel, re-organised like the forward kernel after the per-phase clock trace
+// (item phase 48 %, MMA 27 %, push + release fence 17 % of a step in the LSU version):
+//   * 16 compute warps + 2 DMA warps; no block-wide barrier inside the time loop, only mbarriers;
+//   * gates / c / dh of a step arrive by TMA boxes ([16 sequences][slice]) one step ahead, so the item phase is
+//     shared-memory loads + math + two coalesced global stores (dpre fp32, dpre bf16) with precomputed offsets;
+//   * the bf16 dpre tile is unit-major (k = row-in-block*4 + gate), i.e. exactly the global dpre layout;
+//   * partial dh sums leave the MMA accumulators directly as 8-byte st.async stores that complete transaction
+//     bytes on the owner's barrier: no staging buffer, no push phase, no release fence; the traffic overlaps the
+//     (shared-memory bound) MMA phase of the other warps;
+//   * the receive slots are single-buffered; a consumed-handshake (one remote arrive per peer and step, sent by
+//     a DMA warp) guards their reuse.
+// the m16 x k16 bf16 A tile of one mma in ONE shared-memory instruction (instead of four 4-byte gathers): lane i
+// passes the address of row (i & 15), k-half (i >> 4); registers come back in a0..a3 fragment order
+__device__ __forceinline__ void ldmatrix_x4(uint32_t (&r)[4], uint32_t addr) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+                 : "r"(addr));
+}
+__device__ __forceinline__ void st_async_v2(uint32_t cluster_addr, float x, float y, uint32_t mbar_cluster) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.b32 [%0], {%1, %2}, [%3];" ::"r"(
+                     cluster_addr),
+                 "r"(__float_as_uint(x)), "r"(__float_as_uint(y)), "r"(mbar_cluster)
+                 : "memory");
+}
+
+constexpr int TCB_CW = 16;  // compute warps of the backward kernel (+2 DMA warps)
+
+template <int NT, int IT, int ACT>
+__global__ void __launch_bounds__((TCB_CW + 2) * 32, 1) lstm_tc_bwd2_kernel(const __grid_constant__ TcBwdArgs a) {
+    constexpr int NB = NT * 16;
+    static_assert(NT == 1, "one m16 tile of sequences per cluster");
+    cg::cluster_group cluster = cg::this_cluster();
+    const int rank = (int)cluster.block_rank();
+    const int CL = a.CL, SPC = a.SPC, NS = a.NS, H = a.H, ldH = a.ldH;
+    const int b0 = (blockIdx.x / CL) * NB;
+    const int Hc = SPC * 4;
+    const int u0 = rank * Hc;
+    const int nv = max(0, min(Hc, ldH - u0));
+    const int DPS = Hc * 4 + 8;  // bf16 elements per dpre row: pitch = 16 mod 128 bytes (Hc multiple of 8)
+    const int BW = a.BW, NBX = a.NBX;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int CW = TCB_CW;
+    constexpr int cthreads = CW * 32;
+    const bool is_dma = warp >= CW;
+    const int blk0 = a.blk_off[rank];
+    const int nblk = a.blk_off[rank + 1] - blk0;
+
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    unsigned char* sp = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
+    float* gates_s = reinterpret_cast<float*>(sp);  // [2][NBX][16][BW]
+    sp += (size_t)2 * NB * Hc * 16;
+    float* c_s = reinterpret_cast<float*>(sp);  // [2][16][Hc]
+    sp += tc_align128((size_t)2 * NB * Hc * 4);
+    float* dh_s = reinterpret_cast<float*>(sp);  // [16][Hc]
+    sp += tc_align128((size_t)NB * Hc * 4);
+    float* slots = reinterpret_cast<float*>(sp);  // [CL][16][Hc]: partial dh of the next step, one slot per source
+    sp += tc_align128((size_t)CL * NB * Hc * 4);
+    __nv_bfloat16* dpre_s = reinterpret_cast<__nv_bfloat16*>(sp);  // [16][DPS], unit-major (u*4+g)
+    sp += tc_align16((size_t)NB * DPS * 2);
+    uint2* wf_s = reinterpret_cast<uint2*>(sp);
+    sp += tc_align16((size_t)a.max_blocks * 16 * 8);
+    uint16_t* rs_s = reinterpret_cast<uint16_t*>(sp);
+    sp += tc_align16((size_t)a.max_blocks * 2);
+    int* csp_s = reinterpret_cast<int*>(sp);
+    sp += tc_align16((size_t)(NS + 1) * 4);
+    uint64_t* mbar = reinterpret_cast<uint64_t*>(sp);
+    const uint32_t mbar_addr = smem_u32(mbar);
+    // [0..1] gate stage landed  [2] c / dh boxes landed  [3] slots full (CW own arrivals + arm + peers' bytes)
+    // [4] item phase done (CW arrivals)  [5] peers have consumed their slots (CL-1 remote arrivals)
+    const uint32_t mb_g = mbar_addr, mb_s = mbar_addr + 16, mb_full = mbar_addr + 24, mb_items = mbar_addr + 32,
+                   mb_free = mbar_addr + 40;
+    const uint32_t slots_addr = smem_u32(slots);
+    const int stage_floats = NB * Hc * 4;
+    const uint32_t stage_bytes = (uint32_t)stage_floats * 4, box_bytes = (uint32_t)NB * Hc * 4;
+
+    TC_TRACE_INIT();
+    {
+        const uint4* s4 = reinterpret_cast<const uint4*>(a.wfrag + (size_t)blk0 * 16);
+        uint4* d4 = reinterpret_cast<uint4*>(wf_s);
+        for (int i = tid; i < nblk * 8; i += blockDim.x) d4[i] = __ldg(s4 + i);
+        for (int i = tid; i < nblk; i += blockDim.x) rs_s[i] = a.blk_rs[blk0 + i];
+        for (int i = tid; i <= NS; i += blockDim.x) csp_s[i] = a.cs_ptr[(size_t)rank * (NS + 1) + i];
+        for (int i = tid; i < CL * NB * Hc; i += blockDim.x) slots[i] = 0.f;
+        uint32_t* dz = reinterpret_cast<uint32_t*>(dpre_s);
+        for (int i = tid; i < NB * DPS / 2; i += blockDim.x) dz[i] = 0u;
+        if (tid == 0) {
+            mbar_init(mb_g, 1u);
+            mbar_init(mb_g + 8, 1u);
+            mbar_init(mb_s, 1u);
+            mbar_init(mb_full, (uint32_t)CW + 1u);
+            mbar_init(mb_items, (uint32_t)CW);
+            mbar_init(mb_free, (uint32_t)(CL - 1));
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            asm volatile("prefetch.tensormap [%0];" ::"l"(&a.tm_gates) : "memory");
+            asm volatile("prefetch.tensormap [%0];" ::"l"(&a.tm_c) : "memory");
+            asm volatile("prefetch.tensormap [%0];" ::"l"(&a.tm_dh) : "memory");
+        }
+    }
+    fence_proxy_async();
+    __syncthreads();
+
+    // DMA warp 0, lane 0: inputs of time step kk.  Gate boxes go to stage kk&1 (own barrier, a full step ahead);
+    // c_{kk} goes to c buffer kk&1 and dh_{kk} to the single dh buffer (shared barrier, loaded late: small boxes)
+    auto load_gates = [&](int kk) {
+        if (kk < 0 || nv == 0) return;
+        const uint32_t bar = mb_g + 8 * (kk & 1);
+        mbar_expect_tx(bar, stage_bytes);
+        for (int x = 0; x < NBX; ++x)
+            tma_load_3d(smem_u32(gates_s + (size_t)(kk & 1) * stage_floats + (size_t)x * NB * BW), &a.tm_gates,
+                        u0 * 4 + x * BW, b0, kk, bar);
+    };
+    if (warp == CW && lane == 0 && nv > 0) {
+        load_gates(a.T - 1);
+        load_gates(a.T - 2);
+        mbar_expect_tx(mb_s, box_bytes * (a.T > 1 ? 3u : 2u));
+        tma_load_3d(smem_u32(dh_s), &a.tm_dh, u0, b0, a.T - 1, mb_s);
+        tma_load_3d(smem_u32(c_s + (size_t)((a.T - 1) & 1) * NB * Hc), &a.tm_c, u0, b0, a.T - 1, mb_s);
+        if (a.T > 1) tma_load_3d(smem_u32(c_s + (size_t)((a.T - 2) & 1) * NB * Hc), &a.tm_c, u0, b0, a.T - 2, mb_s);
+    }
+
+    // ---- pointwise items (unit fastest => conflict-free shared loads, coalesced 16-byte global stores) --------
+    int it_sm[IT];        // b*Hc + ul
+    int it_gs[IT];        // offset inside a gate stage (box, row, column)
+    uint32_t it_go[IT];   // element offset of the item inside one time step of dpre: (b0+b)*4*ldH + u*4
+    int it_ds[IT];        // offset inside the bf16 dpre tile
+    int it_flag[IT];      // bit0 = item exists, bit1 = real unit of a present sequence, bit2 = pad column to zero
+    float dc_carry[IT], dr[IT];
+#pragma unroll
+    for (int j = 0; j < IT; ++j) {
+        const int idx = tid + j * cthreads;
+        const bool in = !is_dma && idx < Hc * NB;
+        const int b = in ? idx / Hc : 0, ul = in ? idx % Hc : 0;
+        const int u = u0 + ul;
+        const bool ok = in && u < H && b0 + b < a.B;
+        const bool pad = in && !ok && u < ldH && b0 + b < a.B;
+        it_flag[j] = (in ? 1 : 0) | (ok ? 2 : 0) | (pad ? 4 : 0);
+        it_sm[j] = b * Hc + ul;
+        it_ds[j] = b * DPS + ul * 4;
+        it_gs[j] = ((ul * 4) / BW) * (NB * BW) + b * BW + (ul * 4) % BW;
+        it_go[j] = (uint32_t)((size_t)(b0 + b) * 4 * ldH + (size_t)u * 4);
+        dc_carry[j] = 0.f;
+        dr[j] = a.drop_scalar;
+        if (ok && a.drop) dr[j] = __ldg(a.drop + (size_t)(b0 + b) * H + u);
+    }
+    const int br = lane >> 2;
+    const int koff = (lane & 3) * 2;
+    cluster.sync();
+
+    for (int s = 0; s < a.T; ++s) {
+        const int k = a.T - 1 - s;
+        if (!is_dma) {
+            // ============================ compute warps ==========================================================
+            TC_TRACE(0);
+            if (nv > 0) {
+                mbar_wait_dbg(mb_g + 8 * (k & 1), (uint32_t)((s >> 1) & 1), a.dbg, 1, s);
+                mbar_wait_dbg(mb_s, (uint32_t)(s & 1), a.dbg, 2, s);
+            }
+            if (s > 0) mbar_wait_dbg(mb_full, (uint32_t)((s - 1) & 1), a.dbg, 3, s);  // partial dh_k from every CTA has landed
+            TC_TRACE(1);
+            const float* gst = gates_s + (size_t)(k & 1) * stage_floats;
+            const float* ck_s = c_s + (size_t)(k & 1) * NB * Hc;
+            const float* cm_s = c_s + (size_t)((k & 1) ^ 1) * NB * Hc;
+            float* dpre_k = a.dpre + (size_t)k * a.B * 4 * ldH;
+            __nv_bfloat16* dpreb_k = a.dpreb ? a.dpreb + (size_t)k * a.B * 4 * ldH : nullptr;
+#pragma unroll
+            for (int j = 0; j < IT; ++j) {
+                if (!(it_flag[j] & 1)) continue;
+                const bool ok = (it_flag[j] & 2) != 0;
+                const int sm = it_sm[j];
+                float dh = dh_s[sm];
+                if (s > 0) {
+                    for (int src = 0; src < CL; ++src) dh += slots[(size_t)src * NB * Hc + sm];
+                }
+                const float4 g4 = *reinterpret_cast<const float4*>(gst + it_gs[j]);
+                const float cval = ck_s[sm];
+                const float cm1 = (k > 0) ? cm_s[sm] : 0.f;  // c_{-1} = 0
+                const float fg = g4.x, ig = g4.y, og = g4.z, gg = g4.w;
+                const float tc = (ACT == HCGS_ACT_TANH) ? fast_tanh(cval) : act_apply_fast(a.act, cval);
+                const float dog = dh * tc;
+                const float dct = dh * og * ((ACT == HCGS_ACT_TANH) ? (1.f - tc * tc) : act_grad_from_out(a.act, tc)) +
+                                  dc_carry[j];
+                const float dig = dct * gg * dr[j];
+                const float dgg = dct * ig * dr[j];
+                const float dfg = dct * cm1;
+                float4 dp;
+                dp.x = dfg * fg * (1.f - fg);
+                dp.y = dig * ig * (1.f - ig);
+                dp.z = dog * og * (1.f - og);
+                dp.w = dgg * ((ACT == HCGS_ACT_TANH) ? (1.f - gg * gg) : act_grad_from_out(a.act, gg));
+                if (!ok) dp = make_float4(0.f, 0.f, 0.f, 0.f);
+                dc_carry[j] = ok ? dct * fg : 0.f;
+                const uint2 pb = make_uint2(pack_bf16x2(dp.x, dp.y), pack_bf16x2(dp.z, dp.w));
+                if ((it_flag[j] & 6) && !(a.dbg & 1)) {
+                    *reinterpret_cast<float4*>(dpre_k + it_go[j]) = dp;
+                    if (dpreb_k) *reinterpret_cast<uint2*>(dpreb_k + it_go[j]) = pb;
+                }
+                *reinterpret_cast<uint2*>(dpre_s + it_ds[j]) = pb;
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive_local(mb_items);
+            TC_TRACE(2);
+            if (k == 0) break;
+            mbar_wait_dbg(mb_items, (uint32_t)(s & 1), a.dbg, 4, s);  // every warp's share of the bf16 dpre tile is in place
+            TC_TRACE(3);
+            // ---- partial dh_{k-1} for every column strip from this CTA's rows; pushed as soon as a strip is done
+            bool freed = false;
+            const int q = lane & 3;
+            // every warp owns a run of adjacent column strips (so that the remote stores of a row are contiguous)
+            const int spw = (CL * SPC + CW - 1) / CW;
+            const int cs_end = min(CL * SPC, (warp + 1) * spw);
+            const uint32_t lm_base = smem_u32(dpre_s) + (uint32_t)(((lane & 15) * DPS + (lane >> 4) * 8) * 2);
+            constexpr int SB = 2;
+            for (int c0 = warp * spw; c0 < cs_end; c0 += SB) {
+                // two adjacent strips per trip; the kept blocks of a strip are loaded four at a time
+                float acc[SB][4];
+#pragma unroll
+                for (int t = 0; t < SB; ++t) {
+                    acc[t][0] = acc[t][1] = acc[t][2] = acc[t][3] = 0.f;
+                    const int cs = c0 + t;
+                    const bool live = cs < cs_end && cs < NS && !(a.dbg & 4);
+                    const int e0 = live ? csp_s[cs] : 0, e1 = live ? csp_s[cs + 1] : 0;
+                    for (int e = e0; e < e1; e += 4) {
+                        const int n = e1 - e;
+                        uint32_t af[4][4];
+                        uint2 bw[4];
+#pragma unroll
+                        for (int x = 0; x < 4; ++x) {
+                            if (x < n) {  // warp-uniform
+                                const int rs = rs_s[e + x];
+                                bw[x] = make_uint2(0u, 0u);
+                                if (lane < 16) bw[x] = wf_s[(size_t)(e + x) * 16 + lane];
+                                ldmatrix_x4(af[x], lm_base + (uint32_t)rs * 32u);
+                            }
+                        }
+#pragma unroll
+                        for (int x = 0; x < 4; ++x)
+                            if (x < n) mma_bf16_16816(acc[t], af[x][0], af[x][1], af[x][2], af[x][3], bw[x].x, bw[x].y);
+                    }
+                }
+                // ---- results leave straight from the accumulators: lanes q < 2 hold columns 2q, 2q+1 of rows br and
+                // br+8, i.e. 8 contiguous bytes each (no shuffles: the shared-memory / shuffle pipe is what bounds
+                // this phase, ~2.6 cycles per warp instruction)
+#pragma unroll
+                for (int t = 0; t < SB; ++t) {
+                    const int cs = c0 + t;
+                    if (cs >= cs_end) break;  // warp-uniform
+                    const int d = cs / SPC;
+                    if (d != rank && !freed) {  // the peers have consumed the slots of this step
+                        TC_TRACE(4);
+                        mbar_wait_dbg(mb_free, (uint32_t)(s & 1), a.dbg, 5, s);
+                        freed = true;
+                        TC_TRACE(5);
+                    }
+                    if (q < 2) {
+                        const uint32_t off = (uint32_t)((((size_t)rank * NB + br) * Hc + (cs - d * SPC) * 4 + koff) * 4);
+                        if (d == rank) {
+                            float* p = reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(slots) + off);
+                            *reinterpret_cast<float2*>(p) = make_float2(acc[t][0], acc[t][1]);
+                            *reinterpret_cast<float2*>(p + 8 * Hc) = make_float2(acc[t][2], acc[t][3]);
+                        } else if (!(a.dbg & 8)) {
+                            const uint32_t ra = mapa_u32(slots_addr + off, (uint32_t)d);
+                            const uint32_t rb = mapa_u32(mb_full, (uint32_t)d);
+                            st_async_v2(ra, acc[t][0], acc[t][1], rb);
+                            st_async_v2(ra + (uint32_t)(8 * Hc * 4), acc[t][2], acc[t][3], rb);
+                        }
+                    }
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive_local(mb_full);
+            TC_TRACE(4);
+        } else if (lane == 0) {
+            // ============================ DMA warps ==============================================================
+            if (warp == CW) {
+                mbar_wait_dbg(mb_items, (uint32_t)(s & 1), a.dbg, 6, s);  // item phase of step k is over: its input buffers are free
+                if (k >= 1 && nv > 0 && !(a.dbg & 2)) {
+                    if (!(a.dbg & 16)) load_gates(k - 2);
+                    mbar_expect_tx(mb_s, box_bytes * (k >= 2 ? 2u : 1u));
+                    tma_load_3d(smem_u32(dh_s), &a.tm_dh, u0, b0, k - 1, mb_s);
+                    if (k >= 2) tma_load_3d(smem_u32(c_s + (size_t)(k & 1) * NB * Hc), &a.tm_c, u0, b0, k - 2, mb_s);
+                }
+            } else {
+                // arm for the partial dh_{k-1} -- only once the previous phase of this barrier is complete, or the
+                // arm would be counted as an arrival of that phase
+                if (s > 0) mbar_wait_dbg(mb_full, (uint32_t)((s - 1) & 1), a.dbg, 8, s);
+                if (k > 0) mbar_expect_tx(mb_full, (uint32_t)(CL - 1) * box_bytes);
+                mbar_wait_dbg(mb_items, (uint32_t)(s & 1), a.dbg, 7, s);
+                if (k > 0)  // this CTA has consumed its slots: the peers may overwrite them
+                    // (relaxed: nothing is published, the slot reads are complete; a release per arrive costs ~1000 cycles)
+                    for (int d = 1; d < CL; ++d)
+                        mbar_arrive_cluster_relaxed(mapa_u32(mb_free, (uint32_t)((rank + d) % CL)));
+            }
+        }
+    }
+    TC_TRACE_FLUSH();
+    cluster.sync();
+}
+
 // ---- pack kernels: masked dense fp32 U_g -> bf16 mma B fragments ------------------------------
 __global__ void tc_pack_fwd_kernel(const uint16_t* __restrict__ cg, PtrPack<const float> U, int ldu, int H, int KS,
                                    int64_t total, uint32_t* __restrict__ out) {
@@ -1271,7 +1614,7 @@ __global__ void tc_pack_fwd_kernel(const uint16_t* __restrict__ cg, PtrPack<cons
 
 __global__ void tc_pack_bwd_kernel(const int* __restrict__ blk_off, const uint16_t* __restrict__ blk_rs,
                                    const uint16_t* __restrict__ blk_cs, PtrPack<const float> U, int ldu, int H,
-                                   int CL, int SPC, int64_t total, uint32_t* __restrict__ out) {
+                                   int CL, int SPC, int64_t total, int unit_major, uint32_t* __restrict__ out) {
     for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
          idx += (int64_t)gridDim.x * blockDim.x) {
         const int j = idx & 1, lane = (idx >> 1) & 15;
@@ -1279,13 +1622,23 @@ __global__ void tc_pack_bwd_kernel(const int* __restrict__ blk_off, const uint16
         int r = 0;
         while (r + 1 < CL && blk_off[r + 1] <= e) ++r;
         const int n = lane >> 2;
-        const int k0 = (lane & 3) * 2 + 8 * j, g = k0 >> 2, i = k0 & 3;
-        const int64_t row = (int64_t)(r * SPC + blk_rs[e]) * 4 + i;
+        const int k0 = (lane & 3) * 2 + 8 * j;
         const int col = blk_cs[e] * 4 + n;
         float lo = 0.f, hi = 0.f;
-        if (col < H) {
-            if (row < H) lo = __ldg(U.p[g] + row * ldu + col);
-            if (row + 1 < H) hi = __ldg(U.p[g] + (row + 1) * ldu + col);
+        if (unit_major) {  // k = row-in-block * 4 + gate: the pair (k0, k0+1) is two gates of one row
+            const int i = k0 >> 2, g = k0 & 3;
+            const int64_t row = (int64_t)(r * SPC + blk_rs[e]) * 4 + i;
+            if (col < H && row < H) {
+                lo = __ldg(U.p[g] + row * ldu + col);
+                hi = __ldg(U.p[g + 1] + row * ldu + col);
+            }
+        } else {  // k = gate * 4 + row-in-block: two rows of one gate
+            const int g = k0 >> 2, i = k0 & 3;
+            const int64_t row = (int64_t)(r * SPC + blk_rs[e]) * 4 + i;
+            if (col < H) {
+                if (row < H) lo = __ldg(U.p[g] + row * ldu + col);
+                if (row + 1 < H) hi = __ldg(U.p[g] + (row + 1) * ldu + col);
+            }
         }
         out[idx] = pack_bf16x2(lo, hi);
     }
@@ -1331,7 +1684,7 @@ static int tc_resolve(const hcgs_plan* plan, int cluster_size, int nb, TcPlan** 
         if (cluster_size && cands[ci] != cluster_size) continue;
         TcPlan* t = nullptr;
         if (tc_plan_get(plan, cands[ci], &t)) return 1;
-        const bool fits = tc_fwd_smem_v(*t, NB) <= (size_t)limit && tc_bwd_smem(*t, NB) <= (size_t)limit &&
+        const bool fits = tc_fwd_smem_v(*t, NB) <= (size_t)limit && tc_bwd_smem_v(*t, NB) <= (size_t)limit &&
                           t->SPW <= 4 && t->KS <= 8 && (t->Hc * NB + 511) / 512 <= 8;
         if (fits) {
             *out = t;
@@ -1362,7 +1715,7 @@ extern "C" int hcgs_lstm_tc_info(const hcgs_plan* plan, int cluster_size, int nb
     info[2] = t->fwd_pack_u32;
     info[3] = t->bwd_pack_u32;
     info[4] = (int64_t)tc_fwd_smem_v(*t, NB);
-    info[5] = (int64_t)tc_bwd_smem(*t, NB);
+    info[5] = (int64_t)tc_bwd_smem_v(*t, NB);
     info[6] = t->WARPS;
     info[7] = t->SPC;
     info[8] = t->KS;
@@ -1394,13 +1747,29 @@ extern "C" int hcgs_lstm_tc_pack(const hcgs_plan* plan, int cluster_size, const 
         const int64_t total = (int64_t)t->n_blocks * 32;
         const int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 8);
         tc_pack_bwd_kernel<<<blocks, 256, 0, st>>>(t->d_blk_off, t->d_blk_rs, t->d_blk_cs, U, ldu, t->H, t->CL,
-                                                  t->SPC, total, bwd_pack);
+                                                  t->SPC, total, tc_bwd_version() == 1 ? 0 : 1, bwd_pack);
         HCGS_LAUNCH_CHECK();
     }
     return 0;
 }
 
 namespace hcgs {
+
+// boxes of the TMA builds: a CTA's [16][Hc*4] fp32 slice as NBX boxes of BW floats; BW % 32 == 16 makes the
+// float4 accesses of the gate math bank-conflict free
+static int tc_pick_box(int Hc, int* BW, int* NBX) {
+    *BW = *NBX = 0;
+    const int W = Hc * 4;
+    for (int nbx = 1; nbx <= Hc; ++nbx) {
+        if (W % nbx) continue;
+        const int bw = W / nbx;
+        if (bw > 256 || bw % 4) continue;
+        if (*NBX == 0 || bw % 32 == 16) *BW = bw, *NBX = nbx;
+        if (bw % 32 == 16 || bw < 64) break;
+    }
+    HCGS_REQUIRE(*NBX > 0 && Hc <= 256, "tensor-core recurrence: a slice of %d units has no TMA box", Hc);
+    return 0;
+}
 
 typedef void (*TcFwdKernel)(const TcFwdArgs);
 typedef void (*TcBwdKernel)(const TcBwdArgs);
@@ -1433,8 +1802,17 @@ static TcFwdKernel tc_pick_fwd(int NT, int SPW, int KS, int act) {
     return act == HCGS_ACT_TANH ? tc_pick_fwd_act<HCGS_ACT_TANH>(SPW, KS) : tc_pick_fwd_act<-1>(SPW, KS);
 }
 
-static TcBwdKernel tc_pick_bwd(int NT, int items) {
+template <int ACT>
+static TcBwdKernel tc_pick_bwd2(int items) {
+    if (items <= 2) return lstm_tc_bwd2_kernel<1, 2, ACT>;
+    if (items <= 4) return lstm_tc_bwd2_kernel<1, 4, ACT>;
+    if (items <= 6) return lstm_tc_bwd2_kernel<1, 6, ACT>;
+    if (items <= 8) return lstm_tc_bwd2_kernel<1, 8, ACT>;
+    return nullptr;
+}
+static TcBwdKernel tc_pick_bwd(int NT, int items, int act = HCGS_ACT_TANH) {
     if (NT != 1) return nullptr;
+    if (tc_bwd_version() != 1) return act == HCGS_ACT_TANH ? tc_pick_bwd2<HCGS_ACT_TANH>(items) : tc_pick_bwd2<-1>(items);
     if (items <= 2) return lstm_tc_bwd_kernel<1, 2>;
     if (items <= 4) return lstm_tc_bwd_kernel<1, 4>;
     if (items <= 6) return lstm_tc_bwd_kernel<1, 6>;
@@ -1447,8 +1825,8 @@ static int tc_max_active_clusters(const TcPlan& t, int NB, int* fwd_clusters, in
     *fwd_clusters = *bwd_clusters = 0;
     const void* ks[2] = {(const void*)tc_pick_fwd(NB / 16, t.SPW, t.KS, HCGS_ACT_TANH),
                          (const void*)tc_pick_bwd(NB / 16, (t.Hc * NB + 511) / 512)};
-    const size_t smem[2] = {tc_fwd_smem_v(t, NB), tc_bwd_smem(t, NB)};
-    const int threads[2] = {(t.WARPS + (tc_fwd_version() == 1 ? 0 : 2)) * 32, 512};
+    const size_t smem[2] = {tc_fwd_smem_v(t, NB), tc_bwd_smem_v(t, NB)};
+    const int threads[2] = {(t.WARPS + (tc_fwd_version() == 1 ? 0 : 2)) * 32, tc_bwd_version() == 1 ? 512 : (TCB_CW + 2) * 32};
     int* outs[2] = {fwd_clusters, bwd_clusters};
     for (int i = 0; i < 2; ++i) {
         if (!ks[i]) continue;
@@ -1522,17 +1900,7 @@ extern "C" int hcgs_lstm_tc_fwd(const hcgs_plan* plan, int cluster_size, int nb,
     }
     a.BW = a.NBX = 0;
     if (tc_fwd_version() != 1) {
-        // boxes of the TMA build: the CTA's [16][Hc*4] fp32 slice as NBX boxes of BW floats; BW % 32 == 16 makes
-        // the float4 accesses of the gate math bank-conflict free
-        const int W = t->Hc * 4;
-        for (int nbx = 1; nbx <= t->Hc; ++nbx) {
-            if (W % nbx) continue;
-            const int bw = W / nbx;
-            if (bw > 256 || bw % 4) continue;
-            if (a.NBX == 0 || bw % 32 == 16) a.BW = bw, a.NBX = nbx;
-            if (bw % 32 == 16 || bw < 64) break;
-        }
-        HCGS_REQUIRE(a.NBX > 0 && t->Hc <= 256, "hcgs_lstm_tc_fwd: slice of %d units has no TMA box", t->Hc);
+        if (int rc = tc_pick_box(t->Hc, &a.BW, &a.NBX)) return rc;
         const uint64_t B64 = (uint64_t)batch, T64 = (uint64_t)t_len, ld = (uint64_t)ld_h;
         if (int rc = make_tmap_3d(&a.tm_pre, 4, pre, 4 * ld, B64, T64, 16 * ld, B64 * 16 * ld, a.BW, 16)) return rc;
         if (gates_out)
@@ -1590,10 +1958,19 @@ extern "C" int hcgs_lstm_tc_bwd(const hcgs_plan* plan, int cluster_size, int nb,
     a.max_blocks = std::max(t->max_cta_blocks, 1);
     a.act = act;
     const int items = (t->Hc * NB + 511) / 512;
-    TcBwdKernel k = tc_pick_bwd(NB / 16, items);
+    a.BW = a.NBX = 0;
+    if (tc_bwd_version() != 1) {
+        if (int rc = tc_pick_box(t->Hc, &a.BW, &a.NBX)) return rc;
+        const uint64_t B64 = (uint64_t)batch, T64 = (uint64_t)t_len, ld = (uint64_t)ld_h;
+        if (int rc = make_tmap_3d(&a.tm_gates, 4, gates, 4 * ld, B64, T64, 16 * ld, B64 * 16 * ld, a.BW, 16)) return rc;
+        if (int rc = make_tmap_3d(&a.tm_c, 4, c, ld, B64, T64, 4 * ld, B64 * 4 * ld, t->Hc, 16)) return rc;
+        if (int rc = make_tmap_3d(&a.tm_dh, 4, dh_out, ld, B64, T64, 4 * ld, B64 * 4 * ld, t->Hc, 16)) return rc;
+    }
+    TcBwdKernel k = tc_pick_bwd(NB / 16, items, act);
     HCGS_REQUIRE(k != nullptr, "hcgs_lstm_tc_bwd: no kernel for nb=%d items=%d", NB, items);
     const int n_clusters = (batch + NB - 1) / NB;
-    return tc_launch(k, a, n_clusters, t->CL, 512, tc_bwd_smem(*t, NB), (cudaStream_t)stream);
+    return tc_launch(k, a, n_clusters, t->CL, tc_bwd_version() == 1 ? 512 : (TCB_CW + 2) * 32, tc_bwd_smem_v(*t, NB),
+                     (cudaStream_t)stream);
 }
 
 // tuning aid: per-phase clock totals of CTA 0 / thread 0 of the last traced launch (HCGS_TC_DEBUG bit 64)
@@ -1602,5 +1979,12 @@ extern "C" int hcgs_tc_trace_read(int64_t* out16) {
     long long h[16];
     HCGS_CHECK_CUDA(cudaMemcpyFromSymbol(h, hcgs::g_tc_trace, sizeof(h)));
     for (int i = 0; i < 16; ++i) out16[i] = (int64_t)h[i];
+    int f[8];
+    HCGS_CHECK_CUDA(cudaMemcpyFromSymbol(f, hcgs::g_tc_fail, sizeof(f)));
+    if (f[0]) {  // a wait timed out in debug mode: {tag, block, warp, parity, step} packed into out16[15]
+        out16[15] = -((int64_t)f[1] * 100000000 + (int64_t)f[2] * 1000000 + (int64_t)f[3] * 10000 + (int64_t)f[4] * 1000 + f[5]);
+        int z[8] = {0};
+        HCGS_CHECK_CUDA(cudaMemcpyToSymbol(hcgs::g_tc_fail, z, sizeof(z)));
+    }
     return 0;
 }

@@ -118,7 +118,9 @@ def test_tc_recurrent_kernels(H, B, T, blocks, drops, act, cl, nb):
         assert hb[:, H:].float().abs().max().item() == 0, 'pad columns of hb must be zero'
     dpre = torch.full((T * B, 4 * ldH), 3.0, device=d)
     dpb = torch.full((T * B, 4 * ldH), 3.0, device=d, dtype=torch.bfloat16)
-    native.lstm_tc_bwd(plan, cfg, bp, dh.to(d).view(T * B, H), gates, c, drop.to(d), 1.0, code, T, B, dpre, dpb)
+    dh_pad = torch.full((T * B, ldH), float('nan'), device=d)   # pad columns must be ignored
+    dh_pad[:, :H] = dh.to(d).view(T * B, H)
+    native.lstm_tc_bwd(plan, cfg, bp, dh_pad, gates, c, drop.to(d), 1.0, code, T, B, dpre, dpb)
     torch.cuda.synchronize()
     check(from_inter(dpre.cpu(), T, B, H, ldH), pre.grad, 1e-4, 3e-2, 'dpre')
     assert torch.equal(dpb.float().cpu(), bf(dpre.cpu())), 'bf16 copy of dpre'

@@ -48,7 +48,7 @@ def main():
         hb = torch.empty(T * B, ldH, device=d, dtype=torch.bfloat16)
         c = torch.empty(T * B, ldH, device=d)
         gates = torch.empty(T * B, 4 * ldH, device=d)
-        dh = torch.randn(T * B, H, device=d)
+        dh = torch.randn(T * B, native.pad8(H), device=d)
         dpre = torch.empty(T * B, 4 * ldH, device=d)
         dpb = torch.empty(T * B, 4 * ldH, device=d, dtype=torch.bfloat16)
         fp = torch.empty(cfg.fwd_pack_u32, device=d, dtype=torch.int32)

@@ -13,7 +13,7 @@ mask = torch.from_numpy(hcgs_oracle.conn_mat(H, H, [32, 4], [75, 62.5]).astype(n
 plan = native.Plan(mask, recurrent=True)
 us = [(torch.randn(H, H) * 0.1 * mask).to(d) for _ in range(4)]
 which = sys.argv[1] if len(sys.argv) > 1 else 'both'
-for B, cl in [(16, 8), (128, 8), (512, 4), (16, 4)]:
+for B, cl in [(128, 8), (512, 4)]:
     cfg = native.TcConfig(plan, cl, 16)
     ldH = native.pad8(H)
     pre = torch.randn(T * B, 4 * ldH, device=d); drop = torch.bernoulli(torch.full((B, H), 0.8, device=d))
@@ -24,7 +24,7 @@ for B, cl in [(16, 8), (128, 8), (512, 4), (16, 4)]:
     native.lstm_tc_pack(plan, cfg, us, fp, bp)
     os.environ['HCGS_TC_DEBUG'] = '0'
     native.lstm_tc_fwd(plan, cfg, fp, pre, drop, 1.0, 2, T, B, h, hb, c, gates)
-    dh = torch.randn(T * B, H, device=d); dpre = torch.empty(T * B, 4 * ldH, device=d)
+    dh = torch.randn(T * B, native.pad8(H), device=d); dpre = torch.empty(T * B, 4 * ldH, device=d)
     dpb = torch.empty(T * B, 4 * ldH, device=d, dtype=torch.bfloat16)
     if which in ('fwd', 'both'):
         for flags in [0, 1, 2, 3, 4, 7]:
@@ -32,7 +32,7 @@ for B, cl in [(16, 8), (128, 8), (512, 4), (16, 4)]:
             t = timed(lambda: native.lstm_tc_fwd(plan, cfg, fp, pre, drop, 1.0, 2, T, B, h, hb, c, gates))
             print('fwd B=%d cl=%d flags=%d: %.3f ms  %.2f us/step' % (B, cl, flags, t, t * 1e3 / T), flush=True)
     if which in ('bwd', 'both'):
-        for flags in [0, 1, 2, 3, 4, 8, 12, 15]:
+        for flags in [0, 4]:
             os.environ['HCGS_TC_DEBUG'] = str(flags)
             t = timed(lambda: native.lstm_tc_bwd(plan, cfg, bp, dh, gates, c, drop, 1.0, 2, T, B, dpre, dpb))
             print('bwd B=%d cl=%d flags=%d: %.3f ms  %.2f us/step' % (B, cl, flags, t, t * 1e3 / T), flush=True)

@@ -17,7 +17,7 @@ ldH = native.pad8(H)
 pre = torch.randn(T * B, 4 * ldH, device=d); drop = torch.bernoulli(torch.full((B, H), 0.8, device=d))
 h = torch.empty(T * B, native.pad8(H), device=d); c = torch.empty(T * B, ldH, device=d); gates = torch.empty(T * B, 4 * ldH, device=d)
 hb = torch.empty(T * B, ldH, device=d, dtype=torch.bfloat16)
-dh = torch.randn(T * B, H, device=d); dpre = torch.empty(T * B, 4 * ldH, device=d)
+dh = torch.randn(T * B, native.pad8(H), device=d); dpre = torch.empty(T * B, 4 * ldH, device=d)
 dpb = torch.empty(T * B, 4 * ldH, device=d, dtype=torch.bfloat16)
 fp = torch.empty(cfg.fwd_pack_u32, device=d, dtype=torch.int32)
 bp = torch.empty(max(cfg.bwd_pack_u32, 1), device=d, dtype=torch.int32)

@@ -13,7 +13,7 @@ plan = native.Plan(mask, recurrent=True)
 us = [(torch.randn(H, H) * 0.1 * mask).to(d) for _ in range(4)]
 FWD = ['loop top', 'pre wait', 'mbar wait', 'mma', 'B1 sync', 'issue prefetch', 'gate math', 'B2 sync', 'push',
        'B3 sync', 'fence+arrive', 'global stores']
-BWD = ['loop top', 'mbar wait', 'item phase', 'sync1', 'mma', 'sync2', 'push', 'sync3', 'fence+arrive']
+BWD = ['loop top', 'input waits', 'item phase', 'items barrier', 'mma + push', 'slots-free wait', '-', '-', '-']
 for B, cl in [(512, 4), (128, 8)]:
     cfg = native.TcConfig(plan, cl, 16)
     ldH = native.pad8(H)
@@ -23,7 +23,7 @@ for B, cl in [(512, 4), (128, 8)]:
     fp = torch.empty(cfg.fwd_pack_u32, device=d, dtype=torch.int32)
     bp = torch.empty(cfg.bwd_pack_u32, device=d, dtype=torch.int32)
     native.lstm_tc_pack(plan, cfg, us, fp, bp)
-    dh = torch.randn(T * B, H, device=d); dpre = torch.empty(T * B, 4 * ldH, device=d)
+    dh = torch.randn(T * B, native.pad8(H), device=d); dpre = torch.empty(T * B, 4 * ldH, device=d)
     dpb = torch.empty(T * B, 4 * ldH, device=d, dtype=torch.bfloat16)
     os.environ['HCGS_TC_DEBUG'] = '64'
     for rep in range(2):
