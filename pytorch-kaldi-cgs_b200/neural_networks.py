@@ -582,6 +582,29 @@ class LSTM(nn.Module):
             if kind == 'u' and i == (self.N_lstm_lay - 1):
                 self.final_quant = False
 
+    def _upload_drop_mask(self, i, mask, device):
+        """CPU-drawn mask (reference semantics) -> device without draining the stream: a pageable `.to(device)`
+        is a synchronous copy that waits for all queued kernels (four stalls per step); staging through two
+        alternating pinned buffers keeps the host running ahead of the GPU."""
+        if device.type != 'cuda':
+            return mask.to(device)
+        slots = self.__dict__.setdefault('_drop_stage', {})
+        key = (i, tuple(mask.shape))
+        if key not in slots:
+            slots[key] = {'buf': [torch.empty(mask.shape, dtype=mask.dtype).pin_memory() for _ in range(2)],
+                          'ev': [None, None], 'n': 0}
+        st = slots[key]
+        j = st['n'] % 2
+        st['n'] += 1
+        if st['ev'][j] is not None:
+            st['ev'][j].synchronize()       # the upload that used this buffer two calls ago has finished
+        st['buf'][j].copy_(mask)
+        out = st['buf'][j].to(device, non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(device))
+        st['ev'][j] = ev
+        return out
+
     def _quant_weights(self, kind, i):
         """QuantizeLinear weight handling: eval quantises in place, train returns compute copies."""
         lins = [getattr(self, n)[i] for n in self._names(kind)]
@@ -610,7 +633,7 @@ class LSTM(nn.Module):
             # drop mask: same for all time steps, NOT rescaled; drawn on the CPU generator (:843-851)
             if self.test_flag == False:  # noqa: E712 (reference spelling)
                 drop_mask = torch.bernoulli(torch.Tensor(B, H).fill_(1 - self.lstm_drop[i]))
-                rt.drop = drop_mask.to(x.device)
+                rt.drop = self._upload_drop_mask(i, drop_mask, x.device)
                 rt.drop_scalar = 1.0
             else:
                 rt.drop = None
