@@ -45,6 +45,7 @@ static inline PtrPack<T> make_pack(T* const* src, int n) {
     return r;
 }
 
+constexpr int kSdMaxTiles = 12;  // kept tiles of one tile row handled by one sddmm work item (3 MMAs of M = 128)
 constexpr int kTile = 32;  // weight sparsity tile (rows x cols) used by the block-sparse GEMMs
 
 // ---- the opaque plan --------------------------------------------------------------------

@@ -19,6 +19,8 @@
 #include <cuda.h>
 #include <cuda_bf16.h>
 
+#include <stdlib.h>
+
 #include <algorithm>
 
 #include "common.cuh"
@@ -742,20 +744,23 @@ namespace hcgs {
 // ---- sddmm: dW = mask .* (dY^T X) on the kept tiles ------------------------------------------------
 // Work item = (tile row r, group of <= 4 kept tile columns, split of the m rows).  Both operands are
 // MN-major (the reduction index m is the slow dimension of the row-major activations):
-//   A = X^T  : M = 128 = 4 kept column blocks x 32, each block one TMA box [32 cols x RK rows] (SWIZZLE_64B atom)
+//   A = X^T  : M = 128 = 4 kept column blocks x 32, each block one TMA box [32 cols x RK rows] (SWIZZLE_64B atom);
+//              a work item takes up to kSdMaxTiles kept blocks of its tile row = up to 3 MMAs per k-step that
+//              share ONE dY^T operand (the kernel is bound by its operand traffic: dY is then read once per tile row)
 //   B = dY^T : N = 32*NG (unit, gate) columns of tile row r; NG = 4: two boxes [64 x RK] (SWIZZLE_128B atoms)
 //   D[kc, (u,g)] = dW_g[r*32+u, c*32+kc]  (transposed tile) -> fp32 atomics, re-masked on the way out.
 constexpr int SD_RK = 64;       // m rows per stage
-constexpr int SD_STAGES = 4;
+constexpr int SD_STAGES = 3;
 constexpr int SD_A_ATOM = SD_RK * 64;
+constexpr int SD_MM = kSdMaxTiles / 4;  // MMAs (accumulators) per k-step
 
 template <int NG>
 struct SdCfg {
     static constexpr int BN = 32 * NG;
     static constexpr int B_BYTES = SD_RK * BN * 2;
-    static constexpr int STAGE = 4 * SD_A_ATOM + B_BYTES;
+    static constexpr int STAGE = kSdMaxTiles * SD_A_ATOM + B_BYTES;
     static constexpr int SMEM = 1024 + SD_STAGES * STAGE + 256;
-    static constexpr int TCOLS = BN < 32 ? 32 : BN;
+    static constexpr int TCOLS = SD_MM * BN <= 128 ? 128 : (SD_MM * BN <= 256 ? 256 : 512);
 };
 
 struct TcSdArgs {
@@ -799,21 +804,26 @@ __global__ void __launch_bounds__(128) tc_sddmm_kernel(const __grid_constant__ C
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
 
-    if (warp == 0 && lane == 0) {
+    if (warp == 0) {
+        // producer warp: lane j issues the box of kept block j, lanes 12 / 13 the dY boxes (a TMA issue costs its
+        // thread a few hundred cycles, one thread issuing 6..14 boxes per stage was the bottleneck of the kernel)
         for (int i = 0; i < nk; ++i) {
             const int s = i % SD_STAGES;
             if (i >= SD_STAGES) g_mbar_wait(empty0 + 8 * s, (uint32_t)(((i / SD_STAGES) - 1) & 1));
-            g_mbar_expect_tx(full0 + 8 * s, cnt * SD_A_ATOM + C::B_BYTES);
+            if (lane == 0) g_mbar_expect_tx(full0 + 8 * s, cnt * SD_A_ATOM + C::B_BYTES);
+            __syncwarp();
             unsigned char* st = smem + s * C::STAGE;
             const int row = (int)(mbeg + (int64_t)i * SD_RK);
             // splits are multiples of SD_RK rows (host), so only the global tail is ragged: TMA zero-fills it
-            for (int j = 0; j < cnt; ++j)
-                tma_load_2d(g_smem_u32(st + j * SD_A_ATOM), &tmX, a.col_idx[t0 + j] * 32, row, full0 + 8 * s);
+            if (lane < cnt)
+                tma_load_2d(g_smem_u32(st + lane * SD_A_ATOM), &tmX, a.col_idx[t0 + lane] * 32, row, full0 + 8 * s);
             if (NG == 4) {
-                tma_load_2d(g_smem_u32(st + 4 * SD_A_ATOM), &tmDY, r * 128, row, full0 + 8 * s);
-                tma_load_2d(g_smem_u32(st + 4 * SD_A_ATOM + SD_RK * 128), &tmDY, r * 128 + 64, row, full0 + 8 * s);
+                if (lane == 12) tma_load_2d(g_smem_u32(st + kSdMaxTiles * SD_A_ATOM), &tmDY, r * 128, row, full0 + 8 * s);
+                if (lane == 13)
+                    tma_load_2d(g_smem_u32(st + kSdMaxTiles * SD_A_ATOM + SD_RK * 128), &tmDY, r * 128 + 64, row,
+                                full0 + 8 * s);
             } else {
-                tma_load_2d(g_smem_u32(st + 4 * SD_A_ATOM), &tmDY, r * 32, row, full0 + 8 * s);
+                if (lane == 12) tma_load_2d(g_smem_u32(st + kSdMaxTiles * SD_A_ATOM), &tmDY, r * 32, row, full0 + 8 * s);
             }
         }
     } else if (warp == 1 && lane == 0) {
@@ -821,27 +831,35 @@ __global__ void __launch_bounds__(128) tc_sddmm_kernel(const __grid_constant__ C
             const int s = i % SD_STAGES;
             g_mbar_wait(full0 + 8 * s, (uint32_t)((i / SD_STAGES) & 1));
             tc_fence_after();
-            const uint32_t abase = g_smem_u32(smem + s * C::STAGE), bbase = abase + 4 * SD_A_ATOM;
+            const uint32_t abase = g_smem_u32(smem + s * C::STAGE), bbase = abase + kSdMaxTiles * SD_A_ATOM;
+            const int nmm = (cnt + 3) / 4;  // groups of four kept blocks; a partly filled group multiplies stale
+                                            // shared memory into accumulator rows that are never read
 #pragma unroll
             for (int kk = 0; kk < SD_RK / 16; ++kk) {  // 16 m rows per MMA = two 8-row groups
-                const uint64_t ad = umma_smem_desc(abase + kk * 1024, SD_A_ATOM, 512, UMMA_SW64);
                 const uint64_t bd = (NG == 4) ? umma_smem_desc(bbase + kk * 2048, SD_RK * 128, 1024, UMMA_SW128)
                                               : umma_smem_desc(bbase + kk * 1024, SD_A_ATOM, 512, UMMA_SW64);
-                umma_bf16(tmem, ad, bd, IDESC, (i > 0 || kk > 0) ? 1u : 0u);
+                for (int j = 0; j < nmm; ++j) {
+                    const uint64_t ad = umma_smem_desc(abase + j * 4 * SD_A_ATOM + kk * 1024, SD_A_ATOM, 512, UMMA_SW64);
+                    umma_bf16(tmem + (uint32_t)(j * C::BN), ad, bd, IDESC, (i > 0 || kk > 0) ? 1u : 0u);
+                }
             }
             umma_commit(empty0 + 8 * s);
         }
         umma_commit(done);
     }
     __syncwarp();
-    if (nk > 0 && warp < cnt) {  // warp w owns kept column block w of the group; lane = column inside it
+    if (nk > 0 && warp < cnt) {
         g_mbar_wait(done, 0);
         tc_fence_after();
-        const int col = a.col_idx[t0 + warp] * 32 + lane;
+    }
+    // warp w owns the kept column blocks w, w+4, w+8 of the item (TMEM lanes 32w..32w+31 of accumulator j/4)
+#pragma unroll 1
+    for (int jt = warp; nk > 0 && jt < cnt; jt += 4) {
+        const int col = a.col_idx[t0 + jt] * 32 + lane;
 #pragma unroll 1
         for (int cb = 0; cb < C::BN / 32; ++cb) {
             float v[32];
-            tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + cb * 32, v);
+            tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)((jt >> 2) * C::BN) + cb * 32, v);
             if (col < a.n_in) {
 #pragma unroll
                 for (int i = 0; i < 32; ++i) {
@@ -874,8 +892,11 @@ extern "C" int hcgs_tc_sddmm(const hcgs_plan* plan, int n_w, const void* dy_bf16
     if (int rc = make_tmap_bf16(&tmdy, dy_bf16, m, lddy, lddy, n_w == 4 ? 64 : 32, SD_RK,
                                 n_w == 4 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B))
         return rc;
-    // enough CTAs for ~4 per SM; a split is a multiple of SD_RK rows
-    int splits = std::max(1, (148 * 4 + plan->n_sd_items - 1) / plan->n_sd_items);
+    // one CTA per SM (shared memory, all 512 TMEM columns) and ONE wave: every extra split of the rows costs a
+    // full set of fp32 atomics per kept weight (measured 2.70 / 3.06 / 3.62 / 4.77 ms per step for 1 / 2 / 4 / 8
+    // waves, HCGS_SD_WAVES); a split is a multiple of SD_RK rows
+    static const int waves = [] { const char* e = getenv("HCGS_SD_WAVES"); return e ? std::max(1, atoi(e)) : 1; }();
+    int splits = std::max(1, (148 * waves) / plan->n_sd_items);
     int64_t rows = (m + splits - 1) / splits;
     rows = std::max<int64_t>((rows + SD_RK - 1) / SD_RK * SD_RK, 4 * SD_RK);
     splits = (int)((m + rows - 1) / rows);

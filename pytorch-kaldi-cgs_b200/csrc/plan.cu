@@ -181,10 +181,10 @@ extern "C" int hcgs_plan_create(const float* mask, int n_out, int n_in, int recu
             csc_rc.push_back(j);
         }
     for (int i = 0; i < p->tr; ++i)
-        for (int t0 = row_ptr[i]; t0 < row_ptr[i + 1]; t0 += 4) {
+        for (int t0 = row_ptr[i]; t0 < row_ptr[i + 1]; t0 += kSdMaxTiles) {
             sd_items.push_back(i);
             sd_items.push_back(t0);
-            sd_items.push_back(std::min(4, row_ptr[i + 1] - t0));
+            sd_items.push_back(std::min(kSdMaxTiles, row_ptr[i + 1] - t0));
         }
     p->n_sd_items = (int)sd_items.size() / 3;
     int rc = 0;
