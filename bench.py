@@ -167,7 +167,8 @@ def algorithmic_work(name, a):
         if name == 'lstm_tc_bwd':        # (plan, cfg, pack, dh, gates, c, drop, scalar, act, T, B, dpre, dpre_b)
             plan, gates = a[0], a[4]
             ld, H, rows = gates.shape[-1] // 4, plan.n_out, a[9] * a[10]
-            byts = rows * (4 * H + 16 * ld + 4 * ld + 16 * ld + (8 * ld if len(a) > 12 and a[12] is not None else 0))
+            byts = rows * (4 * H + 16 * ld + 4 * ld + (16 * ld if a[11] is not None else 0) +
+                           (8 * ld if len(a) > 12 and a[12] is not None else 0))
             return byts, 2 * 4 * 16 * plan.n_blocks * rows
         if name in ('tc_gemm_nt', 'tc_gemm_nn'):   # (plan, n_w, wpack, x_bf16 | dy_bf16, y | dx)
             plan, n_w, src, dst = a[0], a[1], a[3], a[4]

@@ -116,13 +116,14 @@ int hcgs_bn_bwd(const float* dy, int lddy, const float* x, int ldx, int64_t m, i
                 float* const* dbeta, float* workspace, int64_t workspace_floats, hcgs_stream stream);
 
 /* gate-interleaved variants for the tensor-core build: x / y / dy / dx are [m, n_groups*ld_units] with
- * column u*n_groups+g (u < units real, pad units up to ld_units stay zero); hcgs_bn_bwd_il writes dx as
- * fp32 and/or bf16 (either pointer may be NULL).                                                        */
+ * column u*n_groups+g (u < units real, pad units up to ld_units stay zero); hcgs_bn_bwd_il reads dy as
+ * fp32 (dy) or bf16 (dy_bf16, the copy hcgs_lstm_tc_bwd writes for the GEMMs) - exactly one of the two
+ * is non-NULL - and writes dx as fp32 and/or bf16 (either pointer may be NULL).                          */
 int hcgs_bn_fwd_il(const float* x, float* y, int64_t m, int n_groups, int units, int ld_units,
                    const float* const* gamma, const float* const* beta, float* const* running_mean,
                    float* const* running_var, float eps, float momentum, int training, float* save_mean,
                    float* save_invstd, float* workspace, int64_t workspace_floats, hcgs_stream stream);
-int hcgs_bn_bwd_il(const float* dy, const float* x, int64_t m, int n_groups, int units, int ld_units,
+int hcgs_bn_bwd_il(const float* dy, const void* dy_bf16, const float* x, int64_t m, int n_groups, int units, int ld_units,
                    const float* const* gamma, const float* save_mean, const float* save_invstd, float* dx,
                    void* dx_bf16, float* const* dgamma, float* const* dbeta, float* workspace,
                    int64_t workspace_floats, hcgs_stream stream);

@@ -326,21 +326,21 @@ class LSTMLayerTCFunction(torch.autograd.Function):
          hb) = ctx.saved_tensors
         dev = dh.device
         dh_pad = _padded_rows(dh, T, B, H, ldH)
-        dpre = torch.empty(M, 4 * ldH, device=dev, dtype=torch.float32)
+        # only the bf16 dpre exists: it is the operand of the dU product and (rounded once more after the batch-norm
+        # backward) of the dW / dx products, so the fp32 copy would be written and read for nothing
         dpre_b = torch.empty(M, 4 * ldH, device=dev, dtype=torch.bfloat16)
         native.lstm_tc_bwd(rt.plan_h, ctx.cfg, bwd_pack, dh_pad, gates, c, ctx.drop, ctx.drop_scalar, rt.act,
-                           T, B, dpre, dpre_b)
+                           T, B, None, dpre_b)
         dgam = [None] * 4
         dbet = [None] * 4
         if rt.use_bn:
             dproj_b = torch.empty(M, 4 * ldH, device=dev, dtype=torch.bfloat16)
             dgam = [torch.empty(H, device=dev, dtype=torch.float32) for _ in range(4)]
             dbet = [torch.empty(H, device=dev, dtype=torch.float32) for _ in range(4)]
-            native.bn_bwd_il(dpre, pre_raw, 4, H, ldH, [gf, gi, go, gc], save_mean, save_invstd, None, dproj_b,
+            native.bn_bwd_il(dpre_b, pre_raw, 4, H, ldH, [gf, gi, go, gc], save_mean, save_invstd, None, dproj_b,
                              dgam, dbet, _ws(dev, 4 * ldH))
         else:
             dproj_b = dpre_b
-        del dpre
         dus = [torch.zeros(H, H, device=dev, dtype=torch.float32) for _ in range(4)]
         if T > 1:
             native.tc_sddmm(rt.plan_h, 4, dpre_b[B:], hb[:M - B], dus, rt.mask_h)

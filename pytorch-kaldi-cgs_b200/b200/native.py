@@ -49,7 +49,7 @@ SIGNATURES = {
                             c_int64, c_void_p]),
     'hcgs_bn_fwd_il': (c_int, [_f, _f, c_int64, c_int, c_int, c_int, _pp, _pp, _pp, _pp, c_float, c_float, c_int, _f,
                                _f, _f, c_int64, c_void_p]),
-    'hcgs_bn_bwd_il': (c_int, [_f, _f, c_int64, c_int, c_int, c_int, _pp, _f, _f, _f, _f, _pp, _pp, _f, c_int64,
+    'hcgs_bn_bwd_il': (c_int, [_f, _f, _f, c_int64, c_int, c_int, c_int, _pp, _f, _f, _f, _f, _pp, _pp, _f, c_int64,
                                c_void_p]),
     'hcgs_bn_stats_il': (c_int, [_f, c_int64, c_int64, c_int64, c_int, c_int, c_int, _pp, _pp, c_float, c_float, c_int,
                                  _f, _f, c_void_p]),
@@ -301,10 +301,13 @@ def bn_fwd_il(x2d, y2d, n_groups, units, ld_units, gammas, betas, rmeans, rvars,
 
 def bn_bwd_il(dy2d, x2d, n_groups, units, ld_units, gammas, save_mean, save_invstd, dx2d, dx_bf16, dgammas, dbetas,
               workspace):
-    _require_cuda(dy2d, x2d, dx2d, save_mean, save_invstd, workspace)
-    _require_cuda_any(dx_bf16)
+    """dy2d: fp32 or bf16 [m, n_groups*ld_units] (the bf16 form is what lstm_tc_bwd writes for the GEMMs)"""
+    _require_cuda(x2d, dx2d, save_mean, save_invstd, workspace)
+    _require_cuda_any(dx_bf16, dy2d)
     assert dy2d.is_contiguous() and x2d.is_contiguous() and dy2d.shape[1] == n_groups * ld_units
-    _check(load().hcgs_bn_bwd_il(_ptr(dy2d), _ptr(x2d), x2d.shape[0], n_groups, units, ld_units, _ptrs(gammas),
+    dy_f, dy_b = (dy2d, None) if dy2d.dtype == torch.float32 else (None, dy2d)
+    assert dy2d.dtype in (torch.float32, torch.bfloat16)
+    _check(load().hcgs_bn_bwd_il(_ptr(dy_f), _ptr(dy_b), _ptr(x2d), x2d.shape[0], n_groups, units, ld_units, _ptrs(gammas),
                                  _ptr(save_mean), _ptr(save_invstd), _ptr(dx2d), _ptr(dx_bf16), _ptrs(dgammas),
                                  _ptrs(dbetas), _ptr(workspace), workspace.numel(), _stream()), 'hcgs_bn_bwd_il')
 
@@ -404,14 +407,17 @@ def lstm_tc_fwd(plan, cfg, fwd_pack, pre, drop, drop_scalar, act, T, B, h_out=No
 
 
 def lstm_tc_bwd(plan, cfg, bwd_pack, dh_out, gates, c, drop, drop_scalar, act, T, B, dpre, dpre_bf16=None):
-    """gates / dpre / dpre_bf16: [T*B, 4*ldH] gate-interleaved; c and dh_out [T*B, ldH] (pad columns ignored)."""
+    """gates / dpre / dpre_bf16: [T*B, 4*ldH] gate-interleaved; c and dh_out [T*B, ldH] (pad columns ignored).
+    Either of dpre (fp32) / dpre_bf16 may be None, not both."""
     _require_cuda(dh_out, gates, c, drop, dpre)
     _require_cuda_any(bwd_pack, dpre_bf16)
+    assert dpre is not None or dpre_bf16 is not None
     H = plan.n_out
     ldH = gates.shape[-1] // 4
-    assert dh_out.is_contiguous() and gates.is_contiguous() and c.is_contiguous() and dpre.is_contiguous()
+    assert dh_out.is_contiguous() and gates.is_contiguous() and c.is_contiguous()
     assert dh_out.numel() == T * B * ldH and gates.numel() == T * B * 4 * ldH and c.numel() == T * B * ldH
-    assert dpre.numel() == gates.numel() and (dpre_bf16 is None or dpre_bf16.numel() == gates.numel())
+    for d in (dpre, dpre_bf16):
+        assert d is None or (d.is_contiguous() and d.numel() == gates.numel())
     _check(load().hcgs_lstm_tc_bwd(plan.handle, cfg.cluster_size, cfg.nb, _ptr(bwd_pack), _ptr(dh_out), _ptr(gates),
                                    _ptr(c), ldH, _ptr(drop), float(drop_scalar), int(act), T, B, _ptr(dpre),
                                    _ptr(dpre_bf16), _stream()), 'hcgs_lstm_tc_bwd')

@@ -323,6 +323,142 @@ static int pick_splits(int64_t M, int strips, int64_t ws_floats, int Ctot, int64
 
 using namespace hcgs;
 
+// ---- gate-interleaved backward, two adjacent columns per thread (8-byte x loads, 4- or 8-byte dy loads, 4-byte
+// bf16 stores: full 32-byte sectors on every access).  DY = float or __nv_bfloat16: the tensor-core build hands
+// over the bf16 dpre the recurrent backward writes for the GEMMs, so the fp32 copy never exists.
+template <typename DY>
+__device__ __forceinline__ float2 bn_ld2(const DY* p);
+template <>
+__device__ __forceinline__ float2 bn_ld2<float>(const float* p) {
+    return __ldg(reinterpret_cast<const float2*>(p));
+}
+template <>
+__device__ __forceinline__ float2 bn_ld2<__nv_bfloat16>(const __nv_bfloat16* p) {
+    const unsigned v = __ldg(reinterpret_cast<const unsigned*>(p));
+    return make_float2(__uint_as_float(v << 16), __uint_as_float(v & 0xffff0000u));
+}
+
+template <typename DY>
+__global__ void __launch_bounds__(256) bn_bwd_il_partial_kernel(const DY* __restrict__ dy, const float* __restrict__ x,
+                                                                int ld, int64_t M, int64_t rows_per_split,
+                                                                const float* __restrict__ save_mean,
+                                                                const float* __restrict__ save_invstd,
+                                                                float* __restrict__ partial) {
+    __shared__ float red[8][33];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int col = blockIdx.x * 64 + lane * 2;
+    const bool ok = col < ld;
+    const int64_t mbeg = (int64_t)blockIdx.y * rows_per_split;
+    const int64_t mend = (mbeg + rows_per_split < M) ? mbeg + rows_per_split : M;
+    float2 mean = make_float2(0.f, 0.f), invstd = mean;
+    if (ok) {
+        mean = *reinterpret_cast<const float2*>(save_mean + col);
+        invstd = *reinterpret_cast<const float2*>(save_invstd + col);
+    }
+    float s1a = 0.f, s1b = 0.f, s2a = 0.f, s2b = 0.f;
+    if (ok) {
+#pragma unroll 4
+        for (int64_t m = mbeg + warp; m < mend; m += 8) {
+            const float2 d = bn_ld2<DY>(dy + m * ld + col);
+            const float2 xv = __ldg(reinterpret_cast<const float2*>(x + m * ld + col));
+            s1a += d.x;
+            s1b += d.y;
+            s2a = fmaf(d.x, (xv.x - mean.x) * invstd.x, s2a);
+            s2b = fmaf(d.y, (xv.y - mean.y) * invstd.y, s2b);
+        }
+    }
+    const float t1a = block_col_reduce(s1a, red, warp, lane);
+    const float t1b = block_col_reduce(s1b, red, warp, lane);
+    const float t2a = block_col_reduce(s2a, red, warp, lane);
+    const float t2b = block_col_reduce(s2b, red, warp, lane);
+    if (warp == 0 && ok)
+        *reinterpret_cast<float4*>(partial + ((int64_t)blockIdx.y * ld + col) * 2) = make_float4(t1a, t2a, t1b, t2b);
+}
+
+template <typename DY>
+__global__ void __launch_bounds__(256) bn_bwd_il_apply_kernel(const DY* __restrict__ dy, const float* __restrict__ x,
+                                                              int ld, int64_t M, int C, int G,
+                                                              PtrPack<const float> gamma,
+                                                              const float* __restrict__ save_mean,
+                                                              const float* __restrict__ save_invstd,
+                                                              const float* __restrict__ partial, int splits,
+                                                              float* __restrict__ dx, __nv_bfloat16* __restrict__ dxb,
+                                                              PtrPack<float> dgamma, PtrPack<float> dbeta,
+                                                              int rows_per_block) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int col = blockIdx.x * 64 + lane * 2;
+    if (col >= ld) return;
+    const int g = col % G, c = col / G;  // G is even: both columns belong to unit c, gates g and g+1
+    const int64_t mbeg = (int64_t)blockIdx.y * rows_per_block;
+    const int64_t mend = (mbeg + rows_per_block < M) ? mbeg + rows_per_block : M;
+    if (c >= C) {  // pad units of the padded tensors stay zero
+        for (int64_t m = mbeg + warp; m < mend; m += 8) {
+            if (dx) *reinterpret_cast<float2*>(dx + m * ld + col) = make_float2(0.f, 0.f);
+            if (dxb) *reinterpret_cast<unsigned*>(dxb + m * ld + col) = 0u;
+        }
+        return;
+    }
+    float s1a = 0.f, s2a = 0.f, s1b = 0.f, s2b = 0.f;
+    for (int s = 0; s < splits; ++s) {
+        const float4 p = *reinterpret_cast<const float4*>(partial + ((int64_t)s * ld + col) * 2);
+        s1a += p.x;
+        s2a += p.y;
+        s1b += p.z;
+        s2b += p.w;
+    }
+    if (blockIdx.y == 0 && warp == 0) {
+        if (dgamma.p[g]) dgamma.p[g][c] = s2a;
+        if (dbeta.p[g]) dbeta.p[g][c] = s1a;
+        if (dgamma.p[g + 1]) dgamma.p[g + 1][c] = s2b;
+        if (dbeta.p[g + 1]) dbeta.p[g + 1][c] = s1b;
+    }
+    const float2 mean = *reinterpret_cast<const float2*>(save_mean + col);
+    const float2 invstd = *reinterpret_cast<const float2*>(save_invstd + col);
+    const float ga = gamma.p[g] ? __ldg(gamma.p[g] + c) : 1.f;
+    const float gb = gamma.p[g + 1] ? __ldg(gamma.p[g + 1] + c) : 1.f;
+    const float inv_m = 1.0f / (float)M;
+    const float k1a = s1a * inv_m, k2a = s2a * inv_m, aa = ga * invstd.x;
+    const float k1b = s1b * inv_m, k2b = s2b * inv_m, ab = gb * invstd.y;
+#pragma unroll 4
+    for (int64_t m = mbeg + warp; m < mend; m += 8) {
+        const float2 d = bn_ld2<DY>(dy + m * ld + col);
+        const float2 xv = __ldg(reinterpret_cast<const float2*>(x + m * ld + col));
+        const float oa = aa * (d.x - k1a - (xv.x - mean.x) * invstd.x * k2a);
+        const float ob = ab * (d.y - k1b - (xv.y - mean.y) * invstd.y * k2b);
+        if (dx) *reinterpret_cast<float2*>(dx + m * ld + col) = make_float2(oa, ob);
+        if (dxb) {
+            const __nv_bfloat162 o2 = __floats2bfloat162_rn(oa, ob);
+            *reinterpret_cast<__nv_bfloat162*>(dxb + m * ld + col) = o2;
+        }
+    }
+}
+
+template <typename DY>
+static int bn_bwd_il_launch(const DY* dy, const float* x, int64_t m, int n_groups, int units, int ld_units,
+                            const float* const* gamma, const float* save_mean, const float* save_invstd, float* dx,
+                            void* dx_bf16, float* const* dgamma, float* const* dbeta, float* workspace,
+                            int64_t workspace_floats, cudaStream_t st) {
+    const int ld = n_groups * ld_units;
+    const int strips = (ld + 63) / 64;
+    int64_t rows;
+    const int splits = pick_splits(m, strips, workspace_floats, ld, &rows);
+    bn_bwd_il_partial_kernel<DY><<<dim3(strips, splits), 256, 0, st>>>(dy, x, ld, m, rows, save_mean, save_invstd,
+                                                                       workspace);
+    HCGS_LAUNCH_CHECK();
+    int rows_per_block = 256;
+    int64_t yb = (m + rows_per_block - 1) / rows_per_block;
+    while (yb > 65535) {
+        rows_per_block *= 2;
+        yb = (m + rows_per_block - 1) / rows_per_block;
+    }
+    bn_bwd_il_apply_kernel<DY><<<dim3(strips, (unsigned)yb), 256, 0, st>>>(
+        dy, x, ld, m, units, n_groups, make_pack<const float>(gamma, n_groups), save_mean, save_invstd, workspace,
+        splits, dx, (__nv_bfloat16*)dx_bf16, make_pack<float>(dgamma, n_groups), make_pack<float>(dbeta, n_groups),
+        rows_per_block);
+    HCGS_LAUNCH_CHECK();
+    return 0;
+}
+
 static int bn_fwd_impl(const float* x, int ldx, float* y, int ldy, int64_t m, int n_groups, int group_cols,
                        int ld_units, int il, const float* const* gamma, const float* const* beta,
                        float* const* running_mean, float* const* running_var, float eps, float momentum,
@@ -422,13 +558,23 @@ extern "C" int hcgs_bn_bwd(const float* dy, int lddy, const float* x, int ldx, i
                        lddx, nullptr, 0, dgamma, dbeta, workspace, workspace_floats, stream);
 }
 
-extern "C" int hcgs_bn_bwd_il(const float* dy, const float* x, int64_t m, int n_groups, int units, int ld_units,
-                              const float* const* gamma, const float* save_mean, const float* save_invstd,
-                              float* dx, void* dx_bf16, float* const* dgamma, float* const* dbeta,
-                              float* workspace, int64_t workspace_floats, hcgs_stream stream) {
-    const int ld = n_groups * ld_units;
-    return bn_bwd_impl(dy, ld, x, ld, m, n_groups, units, ld_units, 1, gamma, save_mean, save_invstd, dx, ld, dx_bf16,
-                       ld, dgamma, dbeta, workspace, workspace_floats, stream);
+extern "C" int hcgs_bn_bwd_il(const float* dy, const void* dy_bf16, const float* x, int64_t m, int n_groups,
+                              int units, int ld_units, const float* const* gamma, const float* save_mean,
+                              const float* save_invstd, float* dx, void* dx_bf16, float* const* dgamma,
+                              float* const* dbeta, float* workspace, int64_t workspace_floats, hcgs_stream stream) {
+    HCGS_REQUIRE((dy != nullptr) != (dy_bf16 != nullptr), "hcgs_bn_bwd_il: exactly one of dy / dy_bf16");
+    HCGS_REQUIRE(x && (dx || dx_bf16) && save_mean && save_invstd && workspace, "hcgs_bn_bwd_il: NULL argument");
+    HCGS_REQUIRE(n_groups >= 2 && n_groups <= HCGS_MAX_GROUPS && n_groups % 2 == 0,
+                 "hcgs_bn_bwd_il: n_groups must be even and <= %d", HCGS_MAX_GROUPS);
+    HCGS_REQUIRE(units >= 1 && ld_units >= units, "hcgs_bn_bwd_il: ld_units < units");
+    if (m <= 0) return 0;
+    HCGS_REQUIRE(workspace_floats >= 2 * (int64_t)n_groups * ld_units, "hcgs_bn_bwd_il: workspace too small");
+    if (dy)
+        return bn_bwd_il_launch<float>(dy, x, m, n_groups, units, ld_units, gamma, save_mean, save_invstd, dx, dx_bf16,
+                                       dgamma, dbeta, workspace, workspace_floats, (cudaStream_t)stream);
+    return bn_bwd_il_launch<__nv_bfloat16>((const __nv_bfloat16*)dy_bf16, x, m, n_groups, units, ld_units, gamma,
+                                           save_mean, save_invstd, dx, dx_bf16, dgamma, dbeta, workspace,
+                                           workspace_floats, (cudaStream_t)stream);
 }
 
 // Batch-norm statistics for the tensor-core build, without an apply pass (the recurrent kernel

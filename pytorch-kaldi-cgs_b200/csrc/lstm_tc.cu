@@ -1223,7 +1223,7 @@ __global__ void __launch_bounds__(512, 1) lstm_tc_bwd_kernel(const TcBwdArgs a) 
                 const size_t row = (size_t)k * a.B + b0 + b;
                 const int u = u0 + ul;
                 if (!(a.dbg & 1)) {
-                    *reinterpret_cast<float4*>(a.dpre + row * 4 * ldH + (size_t)u * 4) = dp;
+                    if (a.dpre) *reinterpret_cast<float4*>(a.dpre + row * 4 * ldH + (size_t)u * 4) = dp;
                     if (a.dpreb)
                         *reinterpret_cast<uint2*>(a.dpreb + row * 4 * ldH + (size_t)u * 4) =
                             make_uint2(pack_bf16x2(dp.x, dp.y), pack_bf16x2(dp.z, dp.w));
@@ -1240,7 +1240,7 @@ __global__ void __launch_bounds__(512, 1) lstm_tc_bwd_kernel(const TcBwdArgs a) 
                 }
             } else if (u0 + ul < ldH && b0 + b < a.B) {  // pad columns of the padded tensors stay zero
                 const size_t row = (size_t)k * a.B + b0 + b;
-                *reinterpret_cast<float4*>(a.dpre + row * 4 * ldH + (size_t)(u0 + ul) * 4) = dp;
+                if (a.dpre) *reinterpret_cast<float4*>(a.dpre + row * 4 * ldH + (size_t)(u0 + ul) * 4) = dp;
                 if (a.dpreb) *reinterpret_cast<uint2*>(a.dpreb + row * 4 * ldH + (size_t)(u0 + ul) * 4) = make_uint2(0u, 0u);
             }
             __nv_bfloat16* d = dpre_s + (size_t)b * DPS + (ul >> 2) * 16 + (ul & 3);
@@ -1475,7 +1475,7 @@ __global__ void __launch_bounds__((TCB_CW + 2) * 32, 1) lstm_tc_bwd2_kernel(cons
             const float* gst = gates_s + (size_t)(k & 1) * stage_floats;
             const float* ck_s = c_s + (size_t)(k & 1) * NB * Hc;
             const float* cm_s = c_s + (size_t)((k & 1) ^ 1) * NB * Hc;
-            float* dpre_k = a.dpre + (size_t)k * a.B * 4 * ldH;
+            float* dpre_k = a.dpre ? a.dpre + (size_t)k * a.B * 4 * ldH : nullptr;
             __nv_bfloat16* dpreb_k = a.dpreb ? a.dpreb + (size_t)k * a.B * 4 * ldH : nullptr;
 #pragma unroll
             for (int j = 0; j < IT; ++j) {
@@ -1506,7 +1506,7 @@ __global__ void __launch_bounds__((TCB_CW + 2) * 32, 1) lstm_tc_bwd2_kernel(cons
                 dc_carry[j] = ok ? dct * fg : 0.f;
                 const uint2 pb = make_uint2(pack_bf16x2(dp.x, dp.y), pack_bf16x2(dp.z, dp.w));
                 if ((it_flag[j] & 6) && !(a.dbg & 1)) {
-                    *reinterpret_cast<float4*>(dpre_k + it_go[j]) = dp;
+                    if (dpre_k) *reinterpret_cast<float4*>(dpre_k + it_go[j]) = dp;
                     if (dpreb_k) *reinterpret_cast<uint2*>(dpreb_k + it_go[j]) = pb;
                 }
                 *reinterpret_cast<uint2*>(dpre_s + it_ds[j]) = pb;
@@ -1945,7 +1945,7 @@ extern "C" int hcgs_lstm_tc_bwd(const hcgs_plan* plan, int cluster_size, int nb,
                                 const float* dh_out, const float* gates, const float* c, int ld_h,
                                 const float* drop, float drop_scalar, int act, int t_len, int batch, float* dpre,
                                 void* dpre_bf16, hcgs_stream stream) {
-    HCGS_REQUIRE(plan && bwd_pack && dh_out && gates && c && dpre, "hcgs_lstm_tc_bwd: NULL argument");
+    HCGS_REQUIRE(plan && bwd_pack && dh_out && gates && c && (dpre || dpre_bf16), "hcgs_lstm_tc_bwd: NULL argument");
     if (t_len <= 0 || batch <= 0) return 0;
     TcPlan* t = nullptr;
     int NB = 0;

@@ -79,6 +79,16 @@ def test_batch_norm_interleaved(M, units, ld):
     if ld > units:
         assert y3[:, units:, :].abs().max().item() == 0 and dx3[:, units:, :].abs().max().item() == 0
     assert torch.equal(dxb.float().cpu(), dxf.cpu().to(torch.bfloat16).float())
+    # bf16 dy (what the recurrent backward hands over) == fp32 dy holding the same rounded values
+    dy_b = dy.reshape(M, 4 * ld).to(d).to(torch.bfloat16)
+    dxf1 = torch.empty_like(dxf)
+    dxf2 = torch.empty_like(dxf)
+    dg2 = [torch.empty(units, device=d) for _ in range(4)]
+    native.bn_bwd_il(dy_b.float(), xd, 4, units, ld, gd, sm, si, dxf1, None, dg, db, ws)
+    native.bn_bwd_il(dy_b, xd, 4, units, ld, gd, sm, si, dxf2, dxb, dg2, db, ws)
+    torch.cuda.synchronize()
+    assert torch.equal(dxf1, dxf2) and all(torch.equal(a, b) for a, b in zip(dg, dg2))
+    assert torch.equal(dxb.float(), dxf2.to(torch.bfloat16).float())
     # eval mode uses the running statistics
     y2 = torch.empty_like(y)
     native.bn_fwd_il(xd, y2, 4, units, ld, gd, bd, rm, rv, 1e-5, 0.05, False, sm, si, ws)
@@ -87,7 +97,8 @@ def test_batch_norm_interleaved(M, units, ld):
     assert mx <= 2e-5 * sc
 
 
-@pytest.mark.parametrize('H,layers,T,B,P', [(550, 4, 60, 8, 1944), (512, 2, 40, 21, 1944), (72, 2, 9, 3, 100)])
+@pytest.mark.parametrize('H,layers,T,B,P', [(550, 4, 60, 8, 1944), (512, 2, 40, 21, 1944), (72, 2, 9, 3, 100),
+                                             (1024, 2, 12, 16, 3480)])
 def test_bf16_train_step_matches_bf16_operand_oracle(H, layers, T, B, P):
     D = 40
     lay = ','.join([str(H)] * layers)

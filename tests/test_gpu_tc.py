@@ -78,6 +78,7 @@ def from_inter(x, T, B, H, ldH):
     (550, 20, 6, [32, 4], [75, 62.5], 'tanh', 0, 0),
     (550, 37, 5, [32, 4], [75, 62.5], 'relu', 16, 16),
     (512, 16, 8, [32, 4], [75, 62.5], 'tanh', 0, 0),
+    (1024, 20, 5, [32, 4], [75, 62.5], 'tanh', 0, 0),
     (70, 5, 8, [16, 2], [50, 50], 'sigmoid', 4, 16),
 ])
 def test_tc_recurrent_kernels(H, B, T, blocks, drops, act, cl, nb):
@@ -124,6 +125,10 @@ def test_tc_recurrent_kernels(H, B, T, blocks, drops, act, cl, nb):
     torch.cuda.synchronize()
     check(from_inter(dpre.cpu(), T, B, H, ldH), pre.grad, 1e-4, 3e-2, 'dpre')
     assert torch.equal(dpb.float().cpu(), bf(dpre.cpu())), 'bf16 copy of dpre'
+    dpb2 = torch.full((T * B, 4 * ldH), 3.0, device=d, dtype=torch.bfloat16)   # the product path: bf16 dpre only
+    native.lstm_tc_bwd(plan, cfg, bp, dh_pad, gates, c, drop.to(d), 1.0, code, T, B, None, dpb2)
+    torch.cuda.synchronize()
+    assert torch.equal(dpb2, dpb), 'bf16-only dpre'
     if ldH > H:
         assert dpre.view(T * B, ldH, 4)[:, H:, :].abs().max().item() == 0, 'pad columns of dpre must be zero'
     # fused batch norm: (pre - mean) * invstd * gamma + beta inside the kernel == normalising pre beforehand
