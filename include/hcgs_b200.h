@@ -247,6 +247,24 @@ int hcgs_logsoftmax_bwd(const float* dlogp, const float* logp, float* dz, int64_
 int hcgs_nll_fwd_bwd(const float* logp, int64_t m, int p, const float* labels, int ldlab, float scale,
                      float* dz, float* stats, hcgs_stream stream);
 
+/* ---- fused output layer (tensor-core build) -------------------------------------------------
+ * out[m, :] = log_softmax(x[m, :] W^T + bias) - (log_prior ? log_prior : 0): the MLP output layer
+ * (neural_networks.py:306-317 with act = LogSoftmax(dim=1), :73-74) and the prior normalisation of the
+ * forward pass (core.py:241-245) as ONE kernel.  The logits stay in TMEM: a cluster of CTAs owns a 128-row
+ * tile, each CTA accumulates a slice of the output columns over the kept 32-wide k tiles (tcgen05, bf16
+ * operands, fp32 accumulate), the row max / sum-of-exponentials partials are exchanged through
+ * distributed shared memory and the log-posteriors are written once.  HBM traffic per row: n_in*2 + n_out*4 B.
+ * hcgs_out_info: info[0]=cluster size (0: n_out > 4096, use hcgs_tc_gemm_nt + hcgs_logsoftmax_fwd)
+ *   [1]=strips of 64 columns per CTA [2]=packed tiles [3]=TMEM columns [4]=smem bytes [5]=k items
+ *   [6]=bytes of the packed weights.
+ * hcgs_out_pack: masked dense fp32 W [n_out, n_in] -> pre-swizzled bf16 tiles (info[6] bytes).
+ * x_bf16: [m, ldx] bf16 (pad columns zero, ldx*2 a multiple of 16); out: [m, ldo] fp32.            */
+int hcgs_out_info(const hcgs_plan* plan, int64_t* info);
+int hcgs_out_pack(const hcgs_plan* plan, const float* w, int ldw, void* wpack, hcgs_stream stream);
+int hcgs_out_logsoftmax_prior_fwd(const hcgs_plan* plan, const void* wpack, const void* x_bf16, int64_t ldx,
+                                  int64_t m, const float* bias, const float* log_prior, float* out,
+                                  int64_t ldo, hcgs_stream stream);
+
 /* ---- optimizers on flat (compressed or dense) buffers -------------------------------------
  * torch.optim semantics as configured by utils.optimizer_init (utils.py:1833-1881).
  * kind: 0 = SGD(momentum, weight_decay, dampening, nesterov), 1 = RMSprop(alpha, eps,

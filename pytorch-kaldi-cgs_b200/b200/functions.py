@@ -246,6 +246,9 @@ def _padded_rows(g, T, B, H, ldH):
     return out
 
 
+_out_info = native.out_info
+
+
 def _bf16_rows(x2d, ld):
     out = torch.empty(x2d.shape[0], ld, device=x2d.device, dtype=torch.bfloat16)
     native.cast_bf16(x2d, out)
@@ -372,6 +375,22 @@ class MLPLayerTCFunction(torch.autograd.Function):
             xb = _bf16_rows(x if x.stride(-1) == 1 else x.contiguous(), native.pad8(D))
         cw = rt.q_ws[0] if rt.q_ws is not None else w
         px = rt.plan_x
+        if rt.softmax and not rt.use_bn and _out_info(px)['cluster'] > 0:
+            # output layer: GEMM + log-softmax (+ prior) in one kernel, the logits never reach HBM
+            oi = _out_info(px)
+            opack = torch.empty(max(oi['pack_bytes'] // 2, 1), device=dev, dtype=torch.bfloat16)
+            native.out_pack(px, cw, opack)
+            out = torch.empty(N, O, device=dev, dtype=torch.float32)
+            native.out_logsoftmax_prior_fwd(px, opack, xb, b, rt.log_prior, out)
+            if any(ctx.needs_input_grad):
+                ctx.rt = rt
+                ctx.softmax = True
+                ctx.had_prior = rt.log_prior is not None
+                ctx.drop_mask = None
+                ctx.out_store = out.detach()
+                ctx.save_for_backward(xb, cw, gamma, None, None, None)
+                ctx.dims = (N, D, O)
+            return out
         wpack = torch.empty(px.nz_tiles * 32 * 32, device=dev, dtype=torch.bfloat16)
         native.tc_pack_nt(px, [cw], wpack)
         z = torch.empty(N, O, device=dev, dtype=torch.float32)

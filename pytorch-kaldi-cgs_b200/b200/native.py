@@ -69,6 +69,9 @@ SIGNATURES = {
     'hcgs_tc_pack_nn': (c_int, [c_void_p, c_int, _pp, c_int, _f, c_void_p]),
     'hcgs_tc_gemm_nn': (c_int, [c_void_p, c_int, _f, _f, c_int64, c_int64, _f, c_int64, c_void_p]),
     'hcgs_tc_sddmm': (c_int, [c_void_p, c_int, _f, c_int64, _f, c_int64, c_int64, _pp, c_int64, _f, c_void_p]),
+    'hcgs_out_info': (c_int, [c_void_p, POINTER(c_int64)]),
+    'hcgs_out_pack': (c_int, [c_void_p, _f, c_int, _f, c_void_p]),
+    'hcgs_out_logsoftmax_prior_fwd': (c_int, [c_void_p, _f, _f, c_int64, c_int64, _f, _f, _f, c_int64, c_void_p]),
     'hcgs_act_fwd': (c_int, [_f, _f, _f, c_int64, c_int, c_void_p]),
     'hcgs_act_bwd': (c_int, [_f, _f, _f, _f, c_int64, c_int, c_void_p]),
     'hcgs_logsoftmax_fwd': (c_int, [_f, c_int, _f, c_int, c_int64, c_int, _f, c_void_p]),
@@ -104,7 +107,8 @@ KERNELS_PER_CALL = {'hcgs_mask_apply': 1, 'hcgs_quantize_w': 1, 'hcgs_quantize_a
                     'hcgs_lstm_pack': 2, 'hcgs_lstm_fwd': 1, 'hcgs_lstm_bwd': 1,
                     'hcgs_lstm_tc_pack': 2, 'hcgs_lstm_tc_fwd': 1, 'hcgs_lstm_tc_bwd': 1,
                     'hcgs_tc_pack_nt': 1, 'hcgs_tc_gemm_nt': 1, 'hcgs_cast_bf16': 1,
-                    'hcgs_tc_pack_nn': 1, 'hcgs_tc_gemm_nn': 1, 'hcgs_tc_sddmm': 1, 'hcgs_act_fwd': 1, 'hcgs_act_bwd': 1,
+                    'hcgs_tc_pack_nn': 1, 'hcgs_tc_gemm_nn': 1, 'hcgs_tc_sddmm': 1, 'hcgs_out_pack': 1,
+                    'hcgs_out_logsoftmax_prior_fwd': 1, 'hcgs_act_fwd': 1, 'hcgs_act_bwd': 1,
                     'hcgs_logsoftmax_fwd': 1, 'hcgs_logsoftmax_bwd': 1, 'hcgs_nll_fwd_bwd': 1, 'hcgs_opt_step': 1}
 LAUNCHES = {'total': 0}
 
@@ -485,6 +489,37 @@ def cast_bf16(x2d, out):
     assert out.dtype == torch.bfloat16 and out.shape[0] == x2d.shape[0] and out.stride(1) == 1
     _check(load().hcgs_cast_bf16(_ptr(x2d), _row_major_2d(x2d, 'x'), x2d.shape[0], x2d.shape[1], _ptr(out),
                                  out.stride(0), _stream()), 'hcgs_cast_bf16')
+
+
+def out_info(plan):
+    """Shape of the fused output-layer kernel for this plan (cluster 0 = too wide, use gemm + logsoftmax)."""
+    if '_out_info' in plan.__dict__:
+        return plan.__dict__['_out_info']
+    info = (c_int64 * 8)()
+    _check(load().hcgs_out_info(plan.handle, info), 'hcgs_out_info')
+    plan.__dict__['_out_info'] = {'cluster': int(info[0]), 'strips': int(info[1]), 'tiles': int(info[2]), 'tmem_cols': int(info[3]),
+            'smem': int(info[4]), 'items': int(info[5]), 'pack_bytes': int(info[6])}
+    return plan.__dict__['_out_info']
+
+
+def out_pack(plan, w, wpack):
+    """wpack: bf16 CUDA tensor of out_info(plan)['pack_bytes'] / 2 elements."""
+    _require_cuda(w)
+    _require_cuda_any(wpack)
+    assert wpack.dtype == torch.bfloat16 and wpack.numel() * 2 >= out_info(plan)['pack_bytes']
+    _check(load().hcgs_out_pack(plan.handle, _ptr(w), _row_major_2d(w, 'w'), _ptr(wpack), _stream()), 'hcgs_out_pack')
+
+
+def out_logsoftmax_prior_fwd(plan, wpack, x_bf16, bias, log_prior, out):
+    """out = log_softmax(x W^T + bias) - log_prior, one kernel (logits stay in TMEM)."""
+    _require_cuda(bias, log_prior, out)
+    _require_cuda_any(wpack, x_bf16)
+    assert x_bf16.dtype == torch.bfloat16 and x_bf16.dim() == 2 and x_bf16.stride(1) == 1
+    assert out.shape[0] == x_bf16.shape[0] and out.shape[1] == plan.n_out
+    _check(load().hcgs_out_logsoftmax_prior_fwd(plan.handle, _ptr(wpack), _ptr(x_bf16), x_bf16.stride(0),
+                                                x_bf16.shape[0], _ptr(bias), _ptr(log_prior), _ptr(out),
+                                                _row_major_2d(out, 'out'), _stream()),
+           'hcgs_out_logsoftmax_prior_fwd')
 
 
 def act_fwd(x, y, drop_mask, act):

@@ -101,6 +101,16 @@ struct hcgs_plan {
     uint8_t* h_blk44 = nullptr;
     int ns44 = 0;
     hcgs::TcPlan* tcp[3] = {nullptr, nullptr, nullptr};  // cluster size 4, 8, 16
+    // fused output layer (gemm_tc.cu, out_lsm_kernel): the n_out columns are cut into strips of 64; a cluster of
+    // out_C CTAs owns a 128-row tile, CTA j the strips [j*out_S, (j+1)*out_S).  Per CTA the kept 32-wide k tiles
+    // (union over 32x32 tile rows of a strip) are listed as items (k tile, strip bit mask, first packed tile).
+    int out_C = 0, out_S = 0;   // 0 = n_out too wide for the fused kernel (> 4096 columns)
+    int out_tiles = 0;          // packed [64 n x 32 k] bf16 tiles
+    int out_items = 0;
+    uint32_t out_any[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // per CTA: strips with at least one kept tile
+    int* d_out_ptr = nullptr;    // [out_C+1] item offsets
+    int* d_out_items = nullptr;  // [out_items*3]
+    int* d_out_tile = nullptr;   // [out_tiles*2] (global strip, k tile), pack order
 };
 
 namespace hcgs {

@@ -925,3 +925,320 @@ extern "C" int hcgs_tc_sddmm(const hcgs_plan* plan, int n_w, const void* dy_bf16
     HCGS_LAUNCH_CHECK();
     return 0;
 }
+
+// ---- fused output layer: log-posteriors = log_softmax(x W^T + b) - log_prior ---------------------------
+// (reference: MLP.forward neural_networks.py:306-317 with act = LogSoftmax(dim=1) :73-74, followed by the prior
+//  normalisation of core.py:241-245.)  The logits never touch HBM: a cluster of C CTAs owns a 128-row tile, CTA j
+// accumulates the logits of its S strips of 64 output columns in TMEM (S*64 fp32 columns, kept 32-wide k tiles only),
+// reads them once for the row max / sum of exponentials, exchanges the per-row partial {max, sum} with its peers
+// through distributed shared memory, and reads them a second time to write z - logsumexp - log_prior.
+// HBM traffic per frame: the bf16 input row once (peers hit L2) and the fp32 posterior row once.
+namespace hcgs {
+
+constexpr int OUT_STAGES = 4;
+constexpr int OUT_A_BYTES = 128 * 64;  // 128 rows x 32 bf16, SWIZZLE_64B
+constexpr int OUT_B_TILE = 64 * 64;    // 64 output columns x 32 bf16, SWIZZLE_64B
+
+template <int TC>
+struct OutCfg {
+    static constexpr int SMAX = TC / 64;
+    static constexpr int STAGE = OUT_A_BYTES + SMAX * OUT_B_TILE;
+    static constexpr int EP_BYTES = 4 * 32 * 33 * 4;  // per-warp transposition tiles of the store epilogue
+    static constexpr int PIPE = OUT_STAGES * STAGE > EP_BYTES ? OUT_STAGES * STAGE : EP_BYTES;
+    static constexpr int BAR_OFF = PIPE;                       // 2*STAGES+1 barriers + TMEM slot
+    static constexpr int SUB_OFF = BAR_OFF + 128;              // [TC] bias, [TC] bias - log_prior
+    static constexpr int PART_OFF = SUB_OFF + 2 * TC * 4;      // [8][128] float2 partial {max, sum}
+    static constexpr int SMEM = 1024 + PART_OFF + 8 * 128 * 8;
+};
+
+__global__ void out_pack_kernel(const int* __restrict__ tile_sk, int n_tiles, const float* __restrict__ W, int ldw,
+                                int n_out, int n_in, unsigned char* __restrict__ out) {
+    const int64_t total = (int64_t)n_tiles * 64 * 4;  // 16-byte chunks
+    for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+         idx += (int64_t)gridDim.x * blockDim.x) {
+        const int c16 = (int)(idx & 3);
+        const int n = (int)((idx >> 2) & 63);
+        const int t = (int)(idx >> 8);
+        const int row = tile_sk[2 * t] * 64 + n, col0 = tile_sk[2 * t + 1] * 32 + c16 * 8;
+        uint32_t w[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            float lo = 0.f, hi = 0.f;
+            if (row < n_out) {
+                if (col0 + 2 * j < n_in) lo = __ldg(W + (int64_t)row * ldw + col0 + 2 * j);
+                if (col0 + 2 * j + 1 < n_in) hi = __ldg(W + (int64_t)row * ldw + col0 + 2 * j + 1);
+            }
+            const __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+            w[j] = *reinterpret_cast<const uint32_t*>(&v);
+        }
+        *reinterpret_cast<uint4*>(out + (size_t)t * OUT_B_TILE + n * 64 + ((c16 ^ ((n >> 1) & 3)) << 4)) =
+            make_uint4(w[0], w[1], w[2], w[3]);
+    }
+}
+
+struct OutArgs {
+    const unsigned char* wpack;
+    const int* slice_ptr;  // [C+1]
+    const int* items;      // [n][3] (k tile, strip mask, first packed tile)
+    const float* bias;     // [P] or NULL
+    const float* log_prior;  // [P] or NULL
+    float* out;            // [M, ldo]
+    int64_t ldo, M;
+    int P, S, C;
+    uint32_t any[8];
+};
+
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+template <int TC>
+__global__ void __launch_bounds__(128) out_lsm_kernel(const __grid_constant__ CUtensorMap tmX, const OutArgs a) {
+    using C = OutCfg<TC>;
+    constexpr uint32_t IDESC = umma_idesc_bf16(128, 64, 0, 0);
+    extern __shared__ unsigned char smem_dyn[];
+    unsigned char* smem = reinterpret_cast<unsigned char*>(((uintptr_t)smem_dyn + 1023) & ~(uintptr_t)1023);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::BAR_OFF);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * OUT_STAGES + 1);
+    float* s_bias = reinterpret_cast<float*>(smem + C::SUB_OFF);
+    float* s_sub = s_bias + TC;
+    float2* s_part = reinterpret_cast<float2*>(smem + C::PART_OFF);
+    const uint32_t full0 = g_smem_u32(bars), empty0 = g_smem_u32(bars + OUT_STAGES),
+                   done = g_smem_u32(bars + 2 * OUT_STAGES);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int j = blockIdx.x;  // slice of the output columns = rank in the cluster (grid.x == cluster.x == C)
+    const int64_t m0 = (int64_t)blockIdx.y * 128;
+    const int i0 = a.slice_ptr[j], ni = a.slice_ptr[j + 1] - i0;
+    const int NC = a.S * 64, col_base = j * NC;
+    const uint32_t any = a.any[j];
+
+    if (warp == 0 && lane == 0) {
+        for (int s = 0; s < OUT_STAGES; ++s) {
+            g_mbar_init(full0 + 8 * s, 1);
+            g_mbar_init(empty0 + 8 * s, 1);
+        }
+        g_mbar_init(done, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) tmem_alloc<TC>(g_smem_u32(tmem_slot));
+    for (int c = threadIdx.x; c < NC; c += 128) {
+        const int col = col_base + c;
+        const float b = (a.bias && col < a.P) ? __ldg(a.bias + col) : 0.f;
+        s_bias[c] = b;
+        s_sub[c] = b - ((a.log_prior && col < a.P) ? __ldg(a.log_prior + col) : 0.f);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp == 0 && lane == 0) {
+        for (int i = 0; i < ni; ++i) {
+            const int s = i % OUT_STAGES;
+            if (i >= OUT_STAGES) g_mbar_wait(empty0 + 8 * s, (uint32_t)(((i / OUT_STAGES) - 1) & 1));
+            const int kt = a.items[3 * (i0 + i)], nb = __popc((uint32_t)a.items[3 * (i0 + i) + 1]);
+            const int t0 = a.items[3 * (i0 + i) + 2];
+            g_mbar_expect_tx(full0 + 8 * s, OUT_A_BYTES + nb * OUT_B_TILE);
+            unsigned char* st = smem + s * C::STAGE;
+            tma_load_2d(g_smem_u32(st), &tmX, kt * 32, (int)m0, full0 + 8 * s);
+            bulk_load_1d(g_smem_u32(st + OUT_A_BYTES), a.wpack + (size_t)t0 * OUT_B_TILE, nb * OUT_B_TILE, full0 + 8 * s);
+        }
+    } else if (warp == 1 && lane == 0) {
+        uint32_t started = 0;
+        for (int i = 0; i < ni; ++i) {
+            const int s = i % OUT_STAGES;
+            uint32_t sm = (uint32_t)a.items[3 * (i0 + i) + 1];
+            g_mbar_wait(full0 + 8 * s, (uint32_t)((i / OUT_STAGES) & 1));
+            tc_fence_after();
+            const uint32_t aaddr = g_smem_u32(smem + s * C::STAGE);
+            uint32_t baddr = aaddr + OUT_A_BYTES;
+            while (sm) {
+                const int q = __ffs(sm) - 1;
+                sm &= sm - 1;
+#pragma unroll
+                for (int kk = 0; kk < 2; ++kk) {
+                    const uint64_t ad = umma_smem_desc(aaddr + kk * 32, 16, 512, UMMA_SW64);
+                    const uint64_t bd = umma_smem_desc(baddr + kk * 32, 16, 512, UMMA_SW64);
+                    umma_bf16(tmem + (uint32_t)(q * 64), ad, bd, IDESC, ((started >> q & 1) || kk > 0) ? 1u : 0u);
+                }
+                started |= 1u << q;
+                baddr += OUT_B_TILE;
+            }
+            umma_commit(empty0 + 8 * s);
+        }
+        umma_commit(done);
+    }
+    __syncwarp();
+    if (ni > 0) {
+        g_mbar_wait(done, 0);
+        tc_fence_after();
+    }
+    // ---- pass 1: row maximum and sum of exponentials over this CTA's columns (thread = row = TMEM lane) ----
+    const int row = warp * 32 + lane;
+    const uint32_t trow = tmem + ((uint32_t)(warp * 32) << 16);
+    float mx = -INFINITY, sum = 0.f;
+    const int ncb = a.S * 2;
+#pragma unroll 1
+    for (int cb = 0; cb < ncb; ++cb) {
+        const int c0 = cb * 32;
+        if (col_base + c0 >= a.P) break;
+        float v[32];
+        if (any >> (cb >> 1) & 1) {
+            tmem_ld32(trow + c0, v);
+        } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = 0.f;
+        }
+        const int nv = min(32, a.P - col_base - c0);
+        float cm = -INFINITY;
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+            v[i] += s_bias[c0 + i];
+            if (i < nv) cm = fmaxf(cm, v[i]);
+        }
+        const float mn = fmaxf(mx, cm);
+        float acc = 0.f;
+#pragma unroll
+        for (int i = 0; i < 32; ++i)
+            if (i < nv) acc += __expf(v[i] - mn);
+        sum = sum * __expf(mx - mn) + acc;
+        mx = mn;
+    }
+    float lse;
+    if (a.C > 1) {
+        // every CTA of the cluster receives every partial: part[source rank][row]
+        const uint32_t local = g_smem_u32(&s_part[j * 128 + row]);
+        cluster_sync_all();  // all peers have started (their shared memory exists) before the first remote store
+        for (int peer = 0; peer < a.C; ++peer) {
+            uint32_t remote;
+            asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local), "r"(peer));
+            asm volatile("st.shared::cluster.v2.f32 [%0], {%1, %2};" ::"r"(remote), "f"(mx), "f"(sum) : "memory");
+        }
+        cluster_sync_all();
+        float gm = -INFINITY;
+        for (int p = 0; p < a.C; ++p) gm = fmaxf(gm, s_part[p * 128 + row].x);
+        float gs = 0.f;
+        for (int p = 0; p < a.C; ++p) {
+            const float2 e = s_part[p * 128 + row];
+            gs += e.y * __expf(e.x - gm);
+        }
+        lse = gm + logf(gs);
+    } else {
+        lse = mx + logf(sum);
+    }
+    // ---- pass 2: z - logsumexp - log_prior, transposed per warp through shared memory, 128-byte row stores ----
+    float* st = reinterpret_cast<float*>(smem) + warp * (32 * 33);
+#pragma unroll 1
+    for (int cb = 0; cb < ncb; ++cb) {
+        const int c0 = cb * 32;
+        if (col_base + c0 >= a.P) break;
+        float v[32];
+        if (any >> (cb >> 1) & 1) {
+            tmem_ld32(trow + c0, v);
+        } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = 0.f;
+        }
+#pragma unroll
+        for (int i = 0; i < 32; ++i) st[lane * 33 + i] = v[i] + s_sub[c0 + i] - lse;
+        __syncwarp();
+        const int col = col_base + c0 + lane;
+        const int64_t r0 = m0 + warp * 32;
+        const int nr = (int)min((int64_t)32, a.M - r0);
+        if (col < a.P) {
+            float* dst = a.out + r0 * a.ldo + col;
+#pragma unroll 4
+            for (int rr = 0; rr < nr; ++rr) dst[(int64_t)rr * a.ldo] = st[rr * 33 + lane];
+        }
+        __syncwarp();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc<TC>(tmem);
+}
+
+template <int TC>
+static int out_launch(const CUtensorMap& tm, const OutArgs& a, int64_t mt, cudaStream_t st) {
+    using C = OutCfg<TC>;
+    HCGS_CHECK_CUDA(cudaFuncSetAttribute(out_lsm_kernel<TC>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM));
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3((unsigned)a.C, (unsigned)mt, 1);
+    cfg.blockDim = dim3(128, 1, 1);
+    cfg.dynamicSmemBytes = C::SMEM;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = (unsigned)a.C;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    HCGS_CHECK_CUDA(cudaLaunchKernelEx(&cfg, out_lsm_kernel<TC>, tm, a));
+    return 0;
+}
+
+static int out_tmem_cols(int S) { return S <= 1 ? 64 : (S <= 2 ? 128 : (S <= 4 ? 256 : 512)); }
+
+}  // namespace hcgs
+
+extern "C" int hcgs_out_info(const hcgs_plan* plan, int64_t* info) {
+    HCGS_REQUIRE(plan && info, "hcgs_out_info: NULL argument");
+    for (int i = 0; i < 8; ++i) info[i] = 0;
+    if (plan->out_C == 0) return 0;
+    const int tc = out_tmem_cols(plan->out_S);
+    info[0] = plan->out_C;
+    info[1] = plan->out_S;
+    info[2] = plan->out_tiles;
+    info[3] = tc;
+    info[4] = tc == 64 ? OutCfg<64>::SMEM : tc == 128 ? OutCfg<128>::SMEM : tc == 256 ? OutCfg<256>::SMEM : OutCfg<512>::SMEM;
+    info[5] = plan->out_items;
+    info[6] = (int64_t)plan->out_tiles * OUT_B_TILE;  // bytes of the packed weights
+    return 0;
+}
+
+extern "C" int hcgs_out_pack(const hcgs_plan* plan, const float* w, int ldw, void* wpack, hcgs_stream stream) {
+    HCGS_REQUIRE(plan && w && wpack, "hcgs_out_pack: NULL argument");
+    HCGS_REQUIRE(plan->out_C > 0, "hcgs_out_pack: %d output columns exceed the fused output kernel (max 4096)", plan->n_out);
+    if (plan->out_tiles == 0) return 0;
+    const int64_t total = (int64_t)plan->out_tiles * 256;
+    const int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 8);
+    out_pack_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(plan->d_out_tile, plan->out_tiles, w, ldw, plan->n_out,
+                                                              plan->n_in, (unsigned char*)wpack);
+    HCGS_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int hcgs_out_logsoftmax_prior_fwd(const hcgs_plan* plan, const void* wpack, const void* x_bf16, int64_t ldx,
+                                             int64_t m, const float* bias, const float* log_prior, float* out,
+                                             int64_t ldo, hcgs_stream stream) {
+    HCGS_REQUIRE(plan && wpack && x_bf16 && out, "hcgs_out_logsoftmax_prior_fwd: NULL argument");
+    HCGS_REQUIRE(plan->out_C > 0, "hcgs_out_logsoftmax_prior_fwd: %d output columns exceed the fused kernel (max 4096)",
+                 plan->n_out);
+    HCGS_REQUIRE(ldo >= plan->n_out, "hcgs_out_logsoftmax_prior_fwd: ldo too small");
+    if (m <= 0) return 0;
+    CUtensorMap tm;
+    if (int rc = make_tmap_bf16(&tm, x_bf16, m, plan->n_in, ldx, 32, 128, CU_TENSOR_MAP_SWIZZLE_64B)) return rc;
+    OutArgs a;
+    a.wpack = (const unsigned char*)wpack;
+    a.slice_ptr = plan->d_out_ptr;
+    a.items = plan->d_out_items;
+    a.bias = bias;
+    a.log_prior = log_prior;
+    a.out = out;
+    a.ldo = ldo;
+    a.M = m;
+    a.P = plan->n_out;
+    a.S = plan->out_S;
+    a.C = plan->out_C;
+    for (int i = 0; i < 8; ++i) a.any[i] = plan->out_any[i];
+    const int64_t mt = (m + 127) / 128;
+    HCGS_REQUIRE(mt <= 65535, "hcgs_out_logsoftmax_prior_fwd: too many rows (%lld)", (long long)m);
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (out_tmem_cols(plan->out_S)) {
+        case 64: return out_launch<64>(tm, a, mt, st);
+        case 128: return out_launch<128>(tm, a, mt, st);
+        case 256: return out_launch<256>(tm, a, mt, st);
+        default: return out_launch<512>(tm, a, mt, st);
+    }
+}

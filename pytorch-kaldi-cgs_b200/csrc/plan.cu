@@ -195,6 +195,47 @@ extern "C" int hcgs_plan_create(const float* mask, int n_out, int n_in, int recu
     rc |= upload(col_ptr, &p->d_col_ptr);
     rc |= upload(row_idx, &p->d_row_idx);
     rc |= upload(tile_rc, &p->d_tile_rc);
+    {
+        // fused output-layer index (strips of 64 output columns x 32-wide k tiles)
+        const int strips = (n_out + 63) / 64;
+        int C = 1;
+        while (C < 8 && C * 4 < strips) C *= 2;
+        const int S = (strips + C - 1) / C;
+        if (S <= 8) {
+            std::vector<int> optr(C + 1, 0), oitems, otile;
+            for (int j = 0; j < C; ++j) {
+                optr[j] = (int)oitems.size() / 3;
+                for (int kt = 0; kt < p->tc; ++kt) {
+                    uint32_t m = 0;
+                    for (int s = 0; s < S; ++s) {
+                        const int gs = j * S + s;
+                        for (int h = 0; h < 2; ++h) {
+                            const int trow = gs * 2 + h;
+                            if (trow < p->tr && nz[(size_t)trow * p->tc + kt]) m |= 1u << s;
+                        }
+                    }
+                    if (!m) continue;
+                    oitems.push_back(kt);
+                    oitems.push_back((int)m);
+                    oitems.push_back((int)otile.size() / 2);
+                    for (int s = 0; s < S; ++s)
+                        if (m >> s & 1) {
+                            otile.push_back(j * S + s);
+                            otile.push_back(kt);
+                        }
+                    p->out_any[j] |= m;
+                }
+            }
+            optr[C] = (int)oitems.size() / 3;
+            p->out_C = C;
+            p->out_S = S;
+            p->out_items = optr[C];
+            p->out_tiles = (int)otile.size() / 2;
+            rc |= upload(optr, &p->d_out_ptr);
+            rc |= upload(oitems, &p->d_out_items);
+            rc |= upload(otile, &p->d_out_tile);
+        }
+    }
     if (rc) {
         hcgs_plan_destroy(p);
         return 1;
@@ -275,6 +316,9 @@ extern "C" int hcgs_plan_destroy(hcgs_plan* p) {
     cudaFree(p->d_tile_rc);
     cudaFree(p->d_csc_rc);
     cudaFree(p->d_sd_items);
+    cudaFree(p->d_out_ptr);
+    cudaFree(p->d_out_items);
+    cudaFree(p->d_out_tile);
     cudaFree(p->rp.d_bidx);
     cudaFree(p->rp.d_cta_blk_off);
     cudaFree(p->rp.d_blk_a);

@@ -132,3 +132,67 @@ def test_tc_gemm_nn_and_sddmm(n_out, n_in, blocks, drops, n_w, M):
             refw = (bf(dys[g])[8:].t() @ bf(x)[:M - 8]) * keep
             close(dws2[g], refw, 3e-5, 'sddmm shifted gate %d' % g)
     plan.destroy()
+
+
+OUT_CASES = [
+    # n_out (pdfs), n_in, blocks, drops, M, prior, bias
+    (1944, 550, [64, 4], [50, 25], 517, True, True),     # TIMIT cd head: cluster 8 x 4 strips
+    (48, 550, None, None, 300, False, True),             # monophone head: one CTA, one strip
+    (3480, 1024, [64, 4], [50, 25], 260, True, True),    # LibriSpeech head: cluster 8 x 7 strips (448 TMEM columns)
+    (1000, 72, [32, 4], [75, 62.5], 129, True, False),   # ragged strips, rows of the mask with no kept tile
+    (130, 40, [64, 4], [50, 25], 7, False, False),       # in=40 < block 64: the reference's all-zero mask
+    (4096, 64, None, None, 128, True, True),             # widest supported: 8 x 8 strips, all 512 TMEM columns
+]
+
+
+@pytest.mark.parametrize('n_out,n_in,blocks,drops,M,prior,use_bias', OUT_CASES)
+def test_out_logsoftmax_prior_fused(n_out, n_in, blocks, drops, M, prior, use_bias):
+    """Fused output layer (hcgs_out_logsoftmax_prior_fwd) vs torch on the same bf16-rounded operands and vs the
+    unfused pair tc_gemm_nt + logsoftmax_fwd.  Tolerance: max-abs 1e-4 on the log-posteriors (north star)."""
+    from b200 import native
+    torch.manual_seed(n_out + n_in + M + 2)
+    mask = random_mask(n_out, n_in, blocks, drops, 11) if blocks else torch.ones(n_out, n_in)
+    plan = native.Plan(mask)
+    info = native.out_info(plan)
+    assert info['cluster'] in (1, 2, 4, 8) and 1 <= info['strips'] <= 8
+    assert info['cluster'] * info['strips'] * 64 >= n_out
+    d = dev()
+    w = torch.randn(n_out, n_in) * mask * (2.0 / n_in ** 0.5)
+    x = torch.randn(M, n_in)
+    bias = torch.randn(n_out) if use_bias else None
+    counts = torch.rand(n_out) + 0.01
+    log_prior = torch.log(counts / counts.sum()) if prior else None
+    xb = torch.empty(M, native.pad8(n_in), device=d, dtype=torch.bfloat16)
+    native.cast_bf16(x.to(d), xb)
+    opack = torch.empty(max(info['pack_bytes'] // 2, 1), device=d, dtype=torch.bfloat16)
+    native.out_pack(plan, w.to(d), opack)
+    out = torch.full((M, n_out), 9.0, device=d)
+    native.out_logsoftmax_prior_fwd(plan, opack, xb, bias.to(d) if use_bias else None,
+                                    log_prior.to(d) if prior else None, out)
+    torch.cuda.synchronize()
+    z = (bf(x).double() @ bf(w).double().t()) + (bias.double() if use_bias else 0)
+    ref = torch.log_softmax(z, 1) - (log_prior.double() if prior else 0)
+    err = (out.cpu().double() - ref).abs().max().item()
+    assert err <= 1e-4, 'fused output layer: max-abs %.3e' % err
+    # the unfused pair computes the same thing through HBM
+    wpack = torch.empty(max(plan.nz_tiles, 1) * 32 * 32, device=d, dtype=torch.bfloat16)
+    native.tc_pack_nt(plan, [w.to(d)], wpack)
+    z2 = torch.empty(M, n_out, device=d)
+    native.tc_gemm_nt(plan, 1, wpack, xb, z2, [bias.to(d)] if use_bias else None)
+    out2 = torch.empty_like(z2)
+    native.logsoftmax_fwd(z2, out2, log_prior.to(d) if prior else None)
+    torch.cuda.synchronize()
+    assert (out - out2).abs().max().item() <= 2e-5
+    # every row is a normalised distribution once the prior is added back
+    p = out.cpu().double() + (log_prior.double() if prior else 0)
+    assert (p.exp().sum(1) - 1).abs().max().item() <= 1e-5
+    plan.destroy()
+
+
+def test_out_fused_too_wide_reports():
+    from b200 import native
+    plan = native.Plan(torch.ones(4100, 32))
+    assert native.out_info(plan)['cluster'] == 0
+    with pytest.raises(native.NativeError):
+        native.out_pack(plan, torch.zeros(4100, 32, device=dev()), torch.empty(8, device=dev(), dtype=torch.bfloat16))
+    plan.destroy()
