@@ -256,7 +256,7 @@ int hcgs_nll_fwd_bwd(const float* logp, int64_t m, int p, const float* labels, i
  * distributed shared memory and the log-posteriors are written once.  HBM traffic per row: n_in*2 + n_out*4 B.
  * hcgs_out_info: info[0]=cluster size (0: n_out > 4096, use hcgs_tc_gemm_nt + hcgs_logsoftmax_fwd)
  *   [1]=strips of 64 columns per CTA [2]=packed tiles [3]=TMEM columns [4]=smem bytes [5]=k items
- *   [6]=bytes of the packed weights.
+ *   [6]=bytes of the packed weights [7]=ring stages.
  * hcgs_out_pack: masked dense fp32 W [n_out, n_in] -> pre-swizzled bf16 tiles (info[6] bytes).
  * x_bf16: [m, ldx] bf16 (pad columns zero, ldx*2 a multiple of 16); out: [m, ldo] fp32.            */
 int hcgs_out_info(const hcgs_plan* plan, int64_t* info);

@@ -498,7 +498,8 @@ def out_info(plan):
     info = (c_int64 * 8)()
     _check(load().hcgs_out_info(plan.handle, info), 'hcgs_out_info')
     plan.__dict__['_out_info'] = {'cluster': int(info[0]), 'strips': int(info[1]), 'tiles': int(info[2]), 'tmem_cols': int(info[3]),
-            'smem': int(info[4]), 'items': int(info[5]), 'pack_bytes': int(info[6])}
+            'smem': int(info[4]), 'items': int(info[5]), 'pack_bytes': int(info[6]),
+                                     'stages': int(info[7])}
     return plan.__dict__['_out_info']
 
 

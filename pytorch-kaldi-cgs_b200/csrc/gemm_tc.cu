@@ -928,27 +928,38 @@ extern "C" int hcgs_tc_sddmm(const hcgs_plan* plan, int n_w, const void* dy_bf16
 
 // ---- fused output layer: log-posteriors = log_softmax(x W^T + b) - log_prior ---------------------------
 // (reference: MLP.forward neural_networks.py:306-317 with act = LogSoftmax(dim=1) :73-74, followed by the prior
-//  normalisation of core.py:241-245.)  The logits never touch HBM: a cluster of C CTAs owns a 128-row tile, CTA j
-// accumulates the logits of its S strips of 64 output columns in TMEM (S*64 fp32 columns, kept 32-wide k tiles only),
-// reads them once for the row max / sum of exponentials, exchanges the per-row partial {max, sum} with its peers
-// through distributed shared memory, and reads them a second time to write z - logsumexp - log_prior.
+//  normalisation of core.py:241-245.)  The logits never touch HBM.  A cluster of C CTAs owns a 128-row tile; CTA j
+// accumulates the logits of its S strips of 64 output columns in TMEM (kept 32-wide k tiles only).  The kernel is
+// persistent and warp specialised:
+//   warp 0      TMA producer: x boxes + packed weight tiles into a ring of shared-memory stages
+//   warp 1      tcgen05.mma issuer; accumulators double buffered in TMEM (2 x S*64 columns) when S <= 4, so the
+//               products of row tile i+1 run under the epilogue of tile i
+//   warps 2..9  epilogue: pass 1 reads the accumulators once for the row max / sum of exponentials, pushes the
+//               partial {max, sum} to every CTA of the cluster with st.async (transaction-count mbarrier, no cluster
+//               barrier), pass 2 reads them again, subtracts logsumexp + log prior and stores 32x32 fp32 boxes
+//               with TMA (128-byte swizzled staging tiles, two per warp)
 // HBM traffic per frame: the bf16 input row once (peers hit L2) and the fp32 posterior row once.
 namespace hcgs {
 
-constexpr int OUT_STAGES = 4;
 constexpr int OUT_A_BYTES = 128 * 64;  // 128 rows x 32 bf16, SWIZZLE_64B
 constexpr int OUT_B_TILE = 64 * 64;    // 64 output columns x 32 bf16, SWIZZLE_64B
+constexpr int OUT_EPI_WARPS = 8;
+constexpr int OUT_THREADS = 32 * (2 + OUT_EPI_WARPS);
+constexpr float OUT_L2E = 1.4426950408889634f;
 
 template <int TC>
 struct OutCfg {
     static constexpr int SMAX = TC / 64;
+    static constexpr int NBUF = TC <= 256 ? 2 : 1;           // TMEM accumulator buffers
+    static constexpr int TALLOC = NBUF * TC < 32 ? 32 : NBUF * TC;
     static constexpr int STAGE = OUT_A_BYTES + SMAX * OUT_B_TILE;
-    static constexpr int EP_BYTES = 4 * 32 * 33 * 4;  // per-warp transposition tiles of the store epilogue
-    static constexpr int PIPE = OUT_STAGES * STAGE > EP_BYTES ? OUT_STAGES * STAGE : EP_BYTES;
-    static constexpr int BAR_OFF = PIPE;                       // 2*STAGES+1 barriers + TMEM slot
-    static constexpr int SUB_OFF = BAR_OFF + 128;              // [TC] bias, [TC] bias - log_prior
-    static constexpr int PART_OFF = SUB_OFF + 2 * TC * 4;      // [8][128] float2 partial {max, sum}
-    static constexpr int SMEM = 1024 + PART_OFF + 8 * 128 * 8;
+    static constexpr int STG_OFF = 0;                                   // 8 warps x 2 x 4 KB store staging tiles
+    static constexpr int PART_OFF = STG_OFF + OUT_EPI_WARPS * 2 * 4096;  // [2][16][128] float2 partials
+    static constexpr int SUB_OFF = PART_OFF + 2 * 16 * 128 * 8;          // [TC] bias, [TC] bias - log_prior
+    static constexpr int BAR_OFF = SUB_OFF + 2 * TC * 4;                 // barriers, TMEM slot, strip mask
+    static constexpr int RING_OFF = (BAR_OFF + 256 + 1023) & ~1023;
+    static constexpr int STAGES = (227 * 1024 - 1024 - RING_OFF) / STAGE < 8 ? (227 * 1024 - 1024 - RING_OFF) / STAGE : 8;
+    static constexpr int SMEM = 1024 + RING_OFF + STAGES * STAGE;
 };
 
 __global__ void out_pack_kernel(const int* __restrict__ tile_sk, int n_tiles, const float* __restrict__ W, int ldw,
@@ -978,193 +989,291 @@ __global__ void out_pack_kernel(const int* __restrict__ tile_sk, int n_tiles, co
 
 struct OutArgs {
     const unsigned char* wpack;
-    const int* slice_ptr;  // [C+1]
-    const int* items;      // [n][3] (k tile, strip mask, first packed tile)
-    const float* bias;     // [P] or NULL
+    const int* slice_ptr;    // [C+1]
+    const int* items;        // [n][3] (k tile, strip mask, first packed tile)
+    const float* bias;       // [P] or NULL
     const float* log_prior;  // [P] or NULL
-    float* out;            // [M, ldo]
+    float* out;              // [M, ldo]
     int64_t ldo, M;
     int P, S, C;
-    uint32_t any[8];
+    int n_mtiles;            // row tiles of 128
+    int use_tma_store;       // out is 16-byte aligned with ldo % 4 == 0
 };
 
-__device__ __forceinline__ void cluster_sync_all() {
+__device__ __forceinline__ float ex2_fast(float x) {
+    float r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ uint32_t out_mapa(uint32_t addr, int rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void out_mbar_arrive(uint32_t addr) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(addr) : "memory");
+}
+
+template <int TC>
+__global__ void __launch_bounds__(OUT_THREADS, 1)
+out_lsm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmOut, const OutArgs a) {
+    using C = OutCfg<TC>;
+    constexpr uint32_t IDESC = umma_idesc_bf16(128, 64, 0, 0);
+    constexpr int ST = C::STAGES, NBUF = C::NBUF;
+    extern __shared__ unsigned char smem_dyn[];
+    unsigned char* smem = reinterpret_cast<unsigned char*>(((uintptr_t)smem_dyn + 1023) & ~(uintptr_t)1023);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::BAR_OFF);
+    // barrier map: full[ST] | empty[ST] | tfull[2] | tempty[2] | pfull[2]
+    const uint32_t full0 = g_smem_u32(bars), empty0 = full0 + 8 * ST, tfull0 = empty0 + 8 * ST, tempty0 = tfull0 + 16,
+                   pfull0 = tempty0 + 16;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * ST + 6);
+    uint32_t* any_slot = tmem_slot + 1;
+    float* s_bias = reinterpret_cast<float*>(smem + C::SUB_OFF);
+    float* s_sub = s_bias + TC;
+    float2* s_part = reinterpret_cast<float2*>(smem + C::PART_OFF);
+    unsigned char* ring = smem + C::RING_OFF;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int j = blockIdx.x;  // slice of the output columns = rank in the cluster (grid.x == cluster.x == C)
+    const int i0 = a.slice_ptr[j], ni = a.slice_ptr[j + 1] - i0;
+    const int NC = a.S * 64, col_base = j * NC;
+    const int n_my = (a.n_mtiles - (int)blockIdx.y + (int)gridDim.y - 1) / (int)gridDim.y;  // row tiles of this cluster
+
+    if (warp == 0 && lane == 0) {
+        for (int s = 0; s < ST; ++s) {
+            g_mbar_init(full0 + 8 * s, 1);
+            g_mbar_init(empty0 + 8 * s, 1);
+        }
+        for (int b = 0; b < 2; ++b) {
+            g_mbar_init(tfull0 + 8 * b, 1);
+            g_mbar_init(tempty0 + 8 * b, OUT_EPI_WARPS);
+            g_mbar_init(pfull0 + 8 * b, 1);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) tmem_alloc<C::TALLOC>(g_smem_u32(tmem_slot));
+    if (warp == 2) {
+        uint32_t m = 0;
+        for (int i = lane; i < ni; i += 32) m |= (uint32_t)a.items[3 * (i0 + i) + 1];
+        m = __reduce_or_sync(0xffffffffu, m);
+        if (lane == 0) *any_slot = m;
+    }
+    if (warp >= 2)
+        for (int c = threadIdx.x - 64; c < NC; c += 32 * OUT_EPI_WARPS) {
+            const int col = col_base + c;
+            const float b = (a.bias && col < a.P) ? __ldg(a.bias + col) : 0.f;
+            s_bias[c] = b;
+            s_sub[c] = b - ((a.log_prior && col < a.P) ? __ldg(a.log_prior + col) : 0.f);
+        }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    // every CTA of the cluster has initialised its barriers before any peer pushes partials into it
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+    const uint32_t tmem = *tmem_slot;
+    const uint32_t any = *any_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int g = 0;  // running stage counter over all tiles
+            for (int it = 0; it < n_my; ++it) {
+                const int m0 = ((int)blockIdx.y + it * (int)gridDim.y) * 128;
+                for (int i = 0; i < ni; ++i, ++g) {
+                    const int s = g % ST;
+                    if (g >= ST) g_mbar_wait(empty0 + 8 * s, (uint32_t)(((g / ST) - 1) & 1));
+                    const int kt = a.items[3 * (i0 + i)], nb = __popc((uint32_t)a.items[3 * (i0 + i) + 1]);
+                    const int t0 = a.items[3 * (i0 + i) + 2];
+                    g_mbar_expect_tx(full0 + 8 * s, OUT_A_BYTES + nb * OUT_B_TILE);
+                    unsigned char* st = ring + s * C::STAGE;
+                    tma_load_2d(g_smem_u32(st), &tmX, kt * 32, m0, full0 + 8 * s);
+                    bulk_load_1d(g_smem_u32(st + OUT_A_BYTES), a.wpack + (size_t)t0 * OUT_B_TILE, nb * OUT_B_TILE,
+                                 full0 + 8 * s);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            int g = 0;
+            for (int it = 0; it < n_my; ++it) {
+                const int b = it % NBUF, k = it / NBUF;
+                if (k >= 1) {
+                    g_mbar_wait(tempty0 + 8 * b, (uint32_t)((k - 1) & 1));
+                    tc_fence_after();
+                }
+                const uint32_t acc = tmem + (uint32_t)(b * TC);
+                uint32_t started = 0;
+                for (int i = 0; i < ni; ++i, ++g) {
+                    const int s = g % ST;
+                    uint32_t sm = (uint32_t)a.items[3 * (i0 + i) + 1];
+                    g_mbar_wait(full0 + 8 * s, (uint32_t)((g / ST) & 1));
+                    tc_fence_after();
+                    const uint32_t aaddr = g_smem_u32(ring + s * C::STAGE);
+                    uint32_t baddr = aaddr + OUT_A_BYTES;
+                    while (sm) {
+                        const int q = __ffs(sm) - 1;
+                        sm &= sm - 1;
+#pragma unroll
+                        for (int kk = 0; kk < 2; ++kk) {
+                            const uint64_t ad = umma_smem_desc(aaddr + kk * 32, 16, 512, UMMA_SW64);
+                            const uint64_t bd = umma_smem_desc(baddr + kk * 32, 16, 512, UMMA_SW64);
+                            umma_bf16(acc + (uint32_t)(q * 64), ad, bd, IDESC, ((started >> q & 1) || kk > 0) ? 1u : 0u);
+                        }
+                        started |= 1u << q;
+                        baddr += OUT_B_TILE;
+                    }
+                    umma_commit(empty0 + 8 * s);
+                }
+                umma_commit(tfull0 + 8 * b);  // arrives once every product of this tile has completed
+            }
+        }
+    } else {
+        // ---- epilogue warps: TMEM lane quadrant q (hardware: warp id % 4), column half hh ----
+        const int ew = warp - 2;
+        const int q = warp & 3, hh = ew >> 2;
+        const int row = q * 32 + lane;
+        const int ncb = a.S * 2;                               // 32-column chunks of this CTA
+        const int cb_lo = hh ? (ncb + 1) / 2 : 0, cb_hi = hh ? ncb : (ncb + 1) / 2;
+        unsigned char* stg = smem + C::STG_OFF + ew * 8192;
+        const uint32_t my_part = g_smem_u32(&s_part[(j * 2 + hh) * 128 + row]);
+        int sbuf = 0;
+        for (int it = 0; it < n_my; ++it) {
+            const int b = it % NBUF, k = it / NBUF, par = it & 1;
+            const int m0 = ((int)blockIdx.y + it * (int)gridDim.y) * 128;
+            const uint32_t trow = tmem + (uint32_t)(b * TC) + ((uint32_t)(q * 32) << 16);
+            if (warp == 2 && lane == 0) g_mbar_expect_tx(pfull0 + 8 * par, (uint32_t)a.C * 2 * 128 * 8);
+            g_mbar_wait(tfull0 + 8 * b, (uint32_t)(k & 1));
+            tc_fence_after();
+            // ---- pass 1 ----
+            float mx = -INFINITY, sum = 0.f;
+#pragma unroll 1
+            for (int cb = cb_lo; cb < cb_hi; ++cb) {
+                const int c0 = cb * 32;
+                if (col_base + c0 >= a.P) break;
+                float v[32];
+                if (any >> (cb >> 1) & 1) {
+                    tmem_ld32(trow + c0, v);
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) v[i] = 0.f;
+                }
+                const int nv = a.P - col_base - c0;  // valid columns of this chunk (>= 32: all)
+                float cm = -INFINITY;
+#pragma unroll
+                for (int i = 0; i < 32; i += 4) {
+                    const float4 bb = *reinterpret_cast<const float4*>(s_bias + c0 + i);
+                    v[i] += bb.x; v[i + 1] += bb.y; v[i + 2] += bb.z; v[i + 3] += bb.w;
+                }
+                if (nv >= 32) {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) cm = fmaxf(cm, v[i]);
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) {
+                        if (i >= nv) v[i] = -INFINITY;
+                        cm = fmaxf(cm, v[i]);
+                    }
+                }
+                const float mn = fmaxf(mx, cm);
+                const float off = -mn * OUT_L2E;
+                float acc0 = 0.f, acc1 = 0.f;
+#pragma unroll
+                for (int i = 0; i < 32; i += 2) {
+                    acc0 += ex2_fast(fmaf(v[i], OUT_L2E, off));
+                    acc1 += ex2_fast(fmaf(v[i + 1], OUT_L2E, off));
+                }
+                sum = sum * ex2_fast((mx - mn) * OUT_L2E) + (acc0 + acc1);
+                mx = mn;
+            }
+            // ---- partial {max, sum} of this half row -> every CTA of the cluster ----
+            {
+                const uint32_t slot = my_part + (uint32_t)(par * 16 * 128 * 8);
+                const uint64_t pv = ((uint64_t)__float_as_uint(sum) << 32) | (uint64_t)__float_as_uint(mx);
+                for (int peer = 0; peer < a.C; ++peer)
+                    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b64 [%0], %1, [%2];" ::"r"(
+                                     out_mapa(slot, peer)),
+                                 "l"(pv), "r"(out_mapa(pfull0 + 8 * par, peer))
+                                 : "memory");
+            }
+            g_mbar_wait(pfull0 + 8 * par, (uint32_t)((it >> 1) & 1));
+            float lse;
+            {
+                const float2* pp = s_part + par * 16 * 128 + row;
+                float gm = -INFINITY;
+                for (int p = 0; p < 2 * a.C; ++p) gm = fmaxf(gm, pp[p * 128].x);
+                float gs = 0.f;
+                for (int p = 0; p < 2 * a.C; ++p) {
+                    const float2 e = pp[p * 128];
+                    gs += e.y * ex2_fast((e.x - gm) * OUT_L2E);
+                }
+                lse = gm + logf(gs);
+            }
+            // ---- pass 2 ----
+#pragma unroll 1
+            for (int cb = cb_lo; cb < cb_hi; ++cb) {
+                const int c0 = cb * 32;
+                if (col_base + c0 >= a.P) break;
+                float v[32];
+                if (any >> (cb >> 1) & 1) {
+                    tmem_ld32(trow + c0, v);
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) v[i] = 0.f;
+                }
+#pragma unroll
+                for (int i = 0; i < 32; i += 4) {
+                    const float4 sb = *reinterpret_cast<const float4*>(s_sub + c0 + i);
+                    v[i] += sb.x - lse; v[i + 1] += sb.y - lse; v[i + 2] += sb.z - lse; v[i + 3] += sb.w - lse;
+                }
+                if (a.use_tma_store) {
+                    unsigned char* tile = stg + sbuf * 4096;
+                    if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+                    __syncwarp();
+#pragma unroll
+                    for (int i = 0; i < 8; ++i)  // 128-byte swizzle: 16-byte chunk i of row `lane` at chunk i ^ (lane & 7)
+                        *reinterpret_cast<float4*>(tile + lane * 128 + ((i ^ (lane & 7)) << 4)) =
+                            make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    __syncwarp();
+                    if (lane == 0) {
+                        asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                                         &tmOut),
+                                     "r"(g_smem_u32(tile)), "r"(col_base + c0), "r"(m0 + q * 32)
+                                     : "memory");
+                        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                    }
+                    sbuf ^= 1;
+                } else {
+                    const int64_t r = (int64_t)m0 + row;
+                    if (r < a.M) {
+                        float* dst = a.out + r * a.ldo + col_base + c0;
+                        const int nv = a.P - col_base - c0;
+#pragma unroll
+                        for (int i = 0; i < 32; ++i)
+                            if (i < nv) dst[i] = v[i];
+                    }
+                }
+            }
+            // this warp has drained its part of accumulator buffer b
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) out_mbar_arrive(tempty0 + 8 * b);
+        }
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc<C::TALLOC>(tmem);
+    // a CTA must not exit while a peer may still push partials into its shared memory
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 
 template <int TC>
-__global__ void __launch_bounds__(128) out_lsm_kernel(const __grid_constant__ CUtensorMap tmX, const OutArgs a) {
+static int out_launch(const CUtensorMap& tm, const CUtensorMap& tmo, OutArgs& a, cudaStream_t st) {
     using C = OutCfg<TC>;
-    constexpr uint32_t IDESC = umma_idesc_bf16(128, 64, 0, 0);
-    extern __shared__ unsigned char smem_dyn[];
-    unsigned char* smem = reinterpret_cast<unsigned char*>(((uintptr_t)smem_dyn + 1023) & ~(uintptr_t)1023);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::BAR_OFF);
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * OUT_STAGES + 1);
-    float* s_bias = reinterpret_cast<float*>(smem + C::SUB_OFF);
-    float* s_sub = s_bias + TC;
-    float2* s_part = reinterpret_cast<float2*>(smem + C::PART_OFF);
-    const uint32_t full0 = g_smem_u32(bars), empty0 = g_smem_u32(bars + OUT_STAGES),
-                   done = g_smem_u32(bars + 2 * OUT_STAGES);
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int j = blockIdx.x;  // slice of the output columns = rank in the cluster (grid.x == cluster.x == C)
-    const int64_t m0 = (int64_t)blockIdx.y * 128;
-    const int i0 = a.slice_ptr[j], ni = a.slice_ptr[j + 1] - i0;
-    const int NC = a.S * 64, col_base = j * NC;
-    const uint32_t any = a.any[j];
-
-    if (warp == 0 && lane == 0) {
-        for (int s = 0; s < OUT_STAGES; ++s) {
-            g_mbar_init(full0 + 8 * s, 1);
-            g_mbar_init(empty0 + 8 * s, 1);
-        }
-        g_mbar_init(done, 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    if (warp == 1) tmem_alloc<TC>(g_smem_u32(tmem_slot));
-    for (int c = threadIdx.x; c < NC; c += 128) {
-        const int col = col_base + c;
-        const float b = (a.bias && col < a.P) ? __ldg(a.bias + col) : 0.f;
-        s_bias[c] = b;
-        s_sub[c] = b - ((a.log_prior && col < a.P) ? __ldg(a.log_prior + col) : 0.f);
-    }
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
-    const uint32_t tmem = *tmem_slot;
-
-    if (warp == 0 && lane == 0) {
-        for (int i = 0; i < ni; ++i) {
-            const int s = i % OUT_STAGES;
-            if (i >= OUT_STAGES) g_mbar_wait(empty0 + 8 * s, (uint32_t)(((i / OUT_STAGES) - 1) & 1));
-            const int kt = a.items[3 * (i0 + i)], nb = __popc((uint32_t)a.items[3 * (i0 + i) + 1]);
-            const int t0 = a.items[3 * (i0 + i) + 2];
-            g_mbar_expect_tx(full0 + 8 * s, OUT_A_BYTES + nb * OUT_B_TILE);
-            unsigned char* st = smem + s * C::STAGE;
-            tma_load_2d(g_smem_u32(st), &tmX, kt * 32, (int)m0, full0 + 8 * s);
-            bulk_load_1d(g_smem_u32(st + OUT_A_BYTES), a.wpack + (size_t)t0 * OUT_B_TILE, nb * OUT_B_TILE, full0 + 8 * s);
-        }
-    } else if (warp == 1 && lane == 0) {
-        uint32_t started = 0;
-        for (int i = 0; i < ni; ++i) {
-            const int s = i % OUT_STAGES;
-            uint32_t sm = (uint32_t)a.items[3 * (i0 + i) + 1];
-            g_mbar_wait(full0 + 8 * s, (uint32_t)((i / OUT_STAGES) & 1));
-            tc_fence_after();
-            const uint32_t aaddr = g_smem_u32(smem + s * C::STAGE);
-            uint32_t baddr = aaddr + OUT_A_BYTES;
-            while (sm) {
-                const int q = __ffs(sm) - 1;
-                sm &= sm - 1;
-#pragma unroll
-                for (int kk = 0; kk < 2; ++kk) {
-                    const uint64_t ad = umma_smem_desc(aaddr + kk * 32, 16, 512, UMMA_SW64);
-                    const uint64_t bd = umma_smem_desc(baddr + kk * 32, 16, 512, UMMA_SW64);
-                    umma_bf16(tmem + (uint32_t)(q * 64), ad, bd, IDESC, ((started >> q & 1) || kk > 0) ? 1u : 0u);
-                }
-                started |= 1u << q;
-                baddr += OUT_B_TILE;
-            }
-            umma_commit(empty0 + 8 * s);
-        }
-        umma_commit(done);
-    }
-    __syncwarp();
-    if (ni > 0) {
-        g_mbar_wait(done, 0);
-        tc_fence_after();
-    }
-    // ---- pass 1: row maximum and sum of exponentials over this CTA's columns (thread = row = TMEM lane) ----
-    const int row = warp * 32 + lane;
-    const uint32_t trow = tmem + ((uint32_t)(warp * 32) << 16);
-    float mx = -INFINITY, sum = 0.f;
-    const int ncb = a.S * 2;
-#pragma unroll 1
-    for (int cb = 0; cb < ncb; ++cb) {
-        const int c0 = cb * 32;
-        if (col_base + c0 >= a.P) break;
-        float v[32];
-        if (any >> (cb >> 1) & 1) {
-            tmem_ld32(trow + c0, v);
-        } else {
-#pragma unroll
-            for (int i = 0; i < 32; ++i) v[i] = 0.f;
-        }
-        const int nv = min(32, a.P - col_base - c0);
-        float cm = -INFINITY;
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-            v[i] += s_bias[c0 + i];
-            if (i < nv) cm = fmaxf(cm, v[i]);
-        }
-        const float mn = fmaxf(mx, cm);
-        float acc = 0.f;
-#pragma unroll
-        for (int i = 0; i < 32; ++i)
-            if (i < nv) acc += __expf(v[i] - mn);
-        sum = sum * __expf(mx - mn) + acc;
-        mx = mn;
-    }
-    float lse;
-    if (a.C > 1) {
-        // every CTA of the cluster receives every partial: part[source rank][row]
-        const uint32_t local = g_smem_u32(&s_part[j * 128 + row]);
-        cluster_sync_all();  // all peers have started (their shared memory exists) before the first remote store
-        for (int peer = 0; peer < a.C; ++peer) {
-            uint32_t remote;
-            asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local), "r"(peer));
-            asm volatile("st.shared::cluster.v2.f32 [%0], {%1, %2};" ::"r"(remote), "f"(mx), "f"(sum) : "memory");
-        }
-        cluster_sync_all();
-        float gm = -INFINITY;
-        for (int p = 0; p < a.C; ++p) gm = fmaxf(gm, s_part[p * 128 + row].x);
-        float gs = 0.f;
-        for (int p = 0; p < a.C; ++p) {
-            const float2 e = s_part[p * 128 + row];
-            gs += e.y * __expf(e.x - gm);
-        }
-        lse = gm + logf(gs);
-    } else {
-        lse = mx + logf(sum);
-    }
-    // ---- pass 2: z - logsumexp - log_prior, transposed per warp through shared memory, 128-byte row stores ----
-    float* st = reinterpret_cast<float*>(smem) + warp * (32 * 33);
-#pragma unroll 1
-    for (int cb = 0; cb < ncb; ++cb) {
-        const int c0 = cb * 32;
-        if (col_base + c0 >= a.P) break;
-        float v[32];
-        if (any >> (cb >> 1) & 1) {
-            tmem_ld32(trow + c0, v);
-        } else {
-#pragma unroll
-            for (int i = 0; i < 32; ++i) v[i] = 0.f;
-        }
-#pragma unroll
-        for (int i = 0; i < 32; ++i) st[lane * 33 + i] = v[i] + s_sub[c0 + i] - lse;
-        __syncwarp();
-        const int col = col_base + c0 + lane;
-        const int64_t r0 = m0 + warp * 32;
-        const int nr = (int)min((int64_t)32, a.M - r0);
-        if (col < a.P) {
-            float* dst = a.out + r0 * a.ldo + col;
-#pragma unroll 4
-            for (int rr = 0; rr < nr; ++rr) dst[(int64_t)rr * a.ldo] = st[rr * 33 + lane];
-        }
-        __syncwarp();
-    }
-    tc_fence_before();
-    __syncthreads();
-    if (warp == 1) tmem_dealloc<TC>(tmem);
-}
-
-template <int TC>
-static int out_launch(const CUtensorMap& tm, const OutArgs& a, int64_t mt, cudaStream_t st) {
-    using C = OutCfg<TC>;
+    static_assert(C::STAGES >= 2, "output kernel: ring too small");
     HCGS_CHECK_CUDA(cudaFuncSetAttribute(out_lsm_kernel<TC>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM));
     cudaLaunchConfig_t cfg;
     memset(&cfg, 0, sizeof(cfg));
-    cfg.gridDim = dim3((unsigned)a.C, (unsigned)mt, 1);
-    cfg.blockDim = dim3(128, 1, 1);
+    cfg.blockDim = dim3(OUT_THREADS, 1, 1);
     cfg.dynamicSmemBytes = C::SMEM;
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
@@ -1174,7 +1283,18 @@ static int out_launch(const CUtensorMap& tm, const OutArgs& a, int64_t mt, cudaS
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    HCGS_CHECK_CUDA(cudaLaunchKernelEx(&cfg, out_lsm_kernel<TC>, tm, a));
+    static int max_clusters[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};  // per cluster size (same footprint for every TC: 1 CTA / SM)
+    if (max_clusters[a.C] == 0) {
+        cfg.gridDim = dim3((unsigned)a.C, 1024, 1);
+        int n = 0;
+        if (cudaOccupancyMaxActiveClusters(&n, out_lsm_kernel<TC>, &cfg) != cudaSuccess || n <= 0) {
+            cudaGetLastError();
+            n = 148 / a.C / 2;
+        }
+        max_clusters[a.C] = n;
+    }
+    cfg.gridDim = dim3((unsigned)a.C, (unsigned)std::min(a.n_mtiles, max_clusters[a.C]), 1);
+    HCGS_CHECK_CUDA(cudaLaunchKernelEx(&cfg, out_lsm_kernel<TC>, tm, tmo, a));
     return 0;
 }
 
@@ -1194,6 +1314,7 @@ extern "C" int hcgs_out_info(const hcgs_plan* plan, int64_t* info) {
     info[4] = tc == 64 ? OutCfg<64>::SMEM : tc == 128 ? OutCfg<128>::SMEM : tc == 256 ? OutCfg<256>::SMEM : OutCfg<512>::SMEM;
     info[5] = plan->out_items;
     info[6] = (int64_t)plan->out_tiles * OUT_B_TILE;  // bytes of the packed weights
+    info[7] = tc == 64 ? OutCfg<64>::STAGES : tc == 128 ? OutCfg<128>::STAGES : tc == 256 ? OutCfg<256>::STAGES : OutCfg<512>::STAGES;
     return 0;
 }
 
@@ -1217,9 +1338,23 @@ extern "C" int hcgs_out_logsoftmax_prior_fwd(const hcgs_plan* plan, const void* 
                  plan->n_out);
     HCGS_REQUIRE(ldo >= plan->n_out, "hcgs_out_logsoftmax_prior_fwd: ldo too small");
     if (m <= 0) return 0;
-    CUtensorMap tm;
+    HCGS_REQUIRE(m <= (int64_t)16777216 * 128 / 2, "hcgs_out_logsoftmax_prior_fwd: too many rows (%lld)", (long long)m);
+    CUtensorMap tm, tmo;
     if (int rc = make_tmap_bf16(&tm, x_bf16, m, plan->n_in, ldx, 32, 128, CU_TENSOR_MAP_SWIZZLE_64B)) return rc;
     OutArgs a;
+    a.use_tma_store = (((uintptr_t)out & 15) == 0 && (ldo & 3) == 0) ? 1 : 0;
+    memset(&tmo, 0, sizeof(tmo));
+    if (a.use_tma_store) {
+        EncodeTiledFn fn = get_encode_fn();
+        HCGS_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled is not available from this driver");
+        cuuint64_t gdim[2] = {(cuuint64_t)plan->n_out, (cuuint64_t)m};
+        cuuint64_t gstr[1] = {(cuuint64_t)ldo * 4};
+        cuuint32_t box[2] = {32, 32};
+        cuuint32_t estr[2] = {1, 1};
+        CUresult r = fn(&tmo, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, out, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        HCGS_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled (posteriors) failed (%d)", (int)r);
+    }
     a.wpack = (const unsigned char*)wpack;
     a.slice_ptr = plan->d_out_ptr;
     a.items = plan->d_out_items;
@@ -1231,14 +1366,12 @@ extern "C" int hcgs_out_logsoftmax_prior_fwd(const hcgs_plan* plan, const void* 
     a.P = plan->n_out;
     a.S = plan->out_S;
     a.C = plan->out_C;
-    for (int i = 0; i < 8; ++i) a.any[i] = plan->out_any[i];
-    const int64_t mt = (m + 127) / 128;
-    HCGS_REQUIRE(mt <= 65535, "hcgs_out_logsoftmax_prior_fwd: too many rows (%lld)", (long long)m);
+    a.n_mtiles = (int)((m + 127) / 128);
     cudaStream_t st = (cudaStream_t)stream;
     switch (out_tmem_cols(plan->out_S)) {
-        case 64: return out_launch<64>(tm, a, mt, st);
-        case 128: return out_launch<128>(tm, a, mt, st);
-        case 256: return out_launch<256>(tm, a, mt, st);
-        default: return out_launch<512>(tm, a, mt, st);
+        case 64: return out_launch<64>(tm, tmo, a, st);
+        case 128: return out_launch<128>(tm, tmo, a, st);
+        case 256: return out_launch<256>(tm, tmo, a, st);
+        default: return out_launch<512>(tm, tmo, a, st);
     }
 }
