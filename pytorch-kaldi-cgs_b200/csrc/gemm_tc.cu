@@ -943,7 +943,8 @@ namespace hcgs {
 
 constexpr int OUT_A_BYTES = 128 * 64;  // 128 rows x 32 bf16, SWIZZLE_64B
 constexpr int OUT_B_TILE = 64 * 64;    // 64 output columns x 32 bf16, SWIZZLE_64B
-constexpr int OUT_EPI_WARPS = 8;
+constexpr int OUT_EPI_WARPS = 16;   // four per TMEM lane quadrant, each takes a quarter of the CTA's columns
+constexpr int OUT_MAX_ITEMS = 128;   // 32-wide k tiles of one CTA (n_in <= 4096)
 constexpr int OUT_THREADS = 32 * (2 + OUT_EPI_WARPS);
 constexpr float OUT_L2E = 1.4426950408889634f;
 
@@ -953,10 +954,12 @@ struct OutCfg {
     static constexpr int NBUF = TC <= 256 ? 2 : 1;           // TMEM accumulator buffers
     static constexpr int TALLOC = NBUF * TC < 32 ? 32 : NBUF * TC;
     static constexpr int STAGE = OUT_A_BYTES + SMAX * OUT_B_TILE;
-    static constexpr int STG_OFF = 0;                                   // 8 warps x 2 x 4 KB store staging tiles
-    static constexpr int PART_OFF = STG_OFF + OUT_EPI_WARPS * 2 * 4096;  // [2][16][128] float2 partials
-    static constexpr int SUB_OFF = PART_OFF + 2 * 16 * 128 * 8;          // [TC] bias, [TC] bias - log_prior
-    static constexpr int BAR_OFF = SUB_OFF + 2 * TC * 4;                 // barriers, TMEM slot, strip mask
+    static constexpr int STG_OFF = 0;                                // one 4 KB store staging tile per epilogue warp
+    static constexpr int PART_OFF = STG_OFF + OUT_EPI_WARPS * 4096;  // [2][8][128] float2 partials of the cluster
+    static constexpr int LP_OFF = PART_OFF + 2 * 8 * 128 * 8;        // [4][128] float2 partials of this CTA's warps
+    static constexpr int SUB_OFF = LP_OFF + 4 * 128 * 8;             // [TC] bias, [TC] bias - log_prior
+    static constexpr int ITEM_OFF = SUB_OFF + 2 * TC * 4;            // [OUT_MAX_ITEMS] int4 (k tile, mask, tile, n)
+    static constexpr int BAR_OFF = ITEM_OFF + OUT_MAX_ITEMS * 16;    // barriers, TMEM slot, strip mask
     static constexpr int RING_OFF = (BAR_OFF + 256 + 1023) & ~1023;
     static constexpr int STAGES = (227 * 1024 - 1024 - RING_OFF) / STAGE < 8 ? (227 * 1024 - 1024 - RING_OFF) / STAGE : 8;
     static constexpr int SMEM = 1024 + RING_OFF + STAGES * STAGE;
@@ -998,6 +1001,7 @@ struct OutArgs {
     int P, S, C;
     int n_mtiles;            // row tiles of 128
     int use_tma_store;       // out is 16-byte aligned with ldo % 4 == 0
+    long long* trace;        // tuning aid (HCGS_OUT_TRACE=1): per-phase clock totals of CTA (0,0), else NULL
 };
 
 __device__ __forceinline__ float ex2_fast(float x) {
@@ -1014,11 +1018,41 @@ __device__ __forceinline__ void out_mbar_arrive(uint32_t addr) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(addr) : "memory");
 }
 
+// one 32x32 fp32 box of posteriors (thread = row): 128-byte swizzled staging tile -> TMA store; rows / columns past
+// the tensor are clipped by the TMA.  Without a 16-byte aligned output the rows are written directly.
+__device__ __forceinline__ void out_store_chunk(const float (&v)[32], const OutArgs& a, const CUtensorMap& tmOut,
+                                                unsigned char* tile, int lane, int col0, int m0, int q) {
+    if (a.use_tma_store) {
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < 8; ++i)  // 128-byte swizzle: 16-byte chunk i of row `lane` lands at chunk i ^ (lane & 7)
+            *reinterpret_cast<float4*>(tile + lane * 128 + ((i ^ (lane & 7)) << 4)) =
+                make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) {
+            asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group [%0, {%2, %3}], [%1];" ::"l"(&tmOut),
+                         "r"(g_smem_u32(tile)), "r"(col0), "r"(m0 + q * 32)
+                         : "memory");
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+    } else {
+        const int64_t r = (int64_t)m0 + q * 32 + lane;
+        if (r < a.M) {
+            float* dst = a.out + r * a.ldo + col0;
+            const int nv = a.P - col0;
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+                if (i < nv) dst[i] = v[i];
+        }
+    }
+}
+
 template <int TC>
 __global__ void __launch_bounds__(OUT_THREADS, 1)
 out_lsm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmOut, const OutArgs a) {
     using C = OutCfg<TC>;
-    constexpr uint32_t IDESC = umma_idesc_bf16(128, 64, 0, 0);
     constexpr int ST = C::STAGES, NBUF = C::NBUF;
     extern __shared__ unsigned char smem_dyn[];
     unsigned char* smem = reinterpret_cast<unsigned char*>(((uintptr_t)smem_dyn + 1023) & ~(uintptr_t)1023);
@@ -1051,9 +1085,15 @@ out_lsm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) tmem_alloc<C::TALLOC>(g_smem_u32(tmem_slot));
+    int4* s_items = reinterpret_cast<int4*>(smem + C::ITEM_OFF);
+    float2* s_lp = reinterpret_cast<float2*>(smem + C::LP_OFF);
     if (warp == 2) {
         uint32_t m = 0;
-        for (int i = lane; i < ni; i += 32) m |= (uint32_t)a.items[3 * (i0 + i) + 1];
+        for (int i = lane; i < ni; i += 32) {
+            const int mk = a.items[3 * (i0 + i) + 1];
+            m |= (uint32_t)mk;
+            s_items[i] = make_int4(a.items[3 * (i0 + i)], mk, a.items[3 * (i0 + i) + 2], __popc((uint32_t)mk));
+        }
         m = __reduce_or_sync(0xffffffffu, m);
         if (lane == 0) *any_slot = m;
     }
@@ -1061,8 +1101,9 @@ out_lsm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         for (int c = threadIdx.x - 64; c < NC; c += 32 * OUT_EPI_WARPS) {
             const int col = col_base + c;
             const float b = (a.bias && col < a.P) ? __ldg(a.bias + col) : 0.f;
+            const float lp = (a.log_prior && col < a.P) ? __ldg(a.log_prior + col) : 0.f;
             s_bias[c] = b;
-            s_sub[c] = b - ((a.log_prior && col < a.P) ? __ldg(a.log_prior + col) : 0.f);
+            s_sub[c] = b - lp;
         }
     tc_fence_before();
     __syncthreads();
@@ -1071,6 +1112,9 @@ out_lsm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
     const uint32_t tmem = *tmem_slot;
     const uint32_t any = *any_slot;
+    long long* tr = (a.trace && blockIdx.x == 0 && blockIdx.y == 0) ? a.trace : nullptr;
+    const long long t_begin = tr ? clock64() : 0;
+    long long t_acc0 = 0, t_acc1 = 0, t_acc2 = 0, t_acc3 = 0;  // per-thread phase totals, written once at the end
 
     if (warp == 0) {
         if (lane == 0) {
@@ -1079,9 +1123,11 @@ out_lsm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
                 const int m0 = ((int)blockIdx.y + it * (int)gridDim.y) * 128;
                 for (int i = 0; i < ni; ++i, ++g) {
                     const int s = g % ST;
+                    const long long tq0 = tr ? clock64() : 0;
                     if (g >= ST) g_mbar_wait(empty0 + 8 * s, (uint32_t)(((g / ST) - 1) & 1));
-                    const int kt = a.items[3 * (i0 + i)], nb = __popc((uint32_t)a.items[3 * (i0 + i) + 1]);
-                    const int t0 = a.items[3 * (i0 + i) + 2];
+                    if (tr) t_acc0 += clock64() - tq0;
+                    const int4 item = s_items[i];
+                    const int kt = item.x, nb = item.w, t0 = item.z;
                     g_mbar_expect_tx(full0 + 8 * s, OUT_A_BYTES + nb * OUT_B_TILE);
                     unsigned char* st = ring + s * C::STAGE;
                     tma_load_2d(g_smem_u32(st), &tmX, kt * 32, m0, full0 + 8 * s);
@@ -1093,32 +1139,39 @@ out_lsm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
     } else if (warp == 1) {
         if (lane == 0) {
             int g = 0;
+            const uint64_t desc0 = umma_smem_desc(g_smem_u32(ring), 16, 512, UMMA_SW64);
+            const int nb = ni > 0 ? s_items[0].w : 0;  // strips per item (the same for every item of this CTA)
+            const uint32_t idesc_lo = umma_idesc_bf16(128, 64 * (nb < 4 ? nb : 4), 0, 0);
+            const uint32_t idesc_hi = umma_idesc_bf16(128, nb > 4 ? 64 * (nb - 4) : 64, 0, 0);
             for (int it = 0; it < n_my; ++it) {
                 const int b = it % NBUF, k = it / NBUF;
+                const long long tq0 = tr ? clock64() : 0;
                 if (k >= 1) {
                     g_mbar_wait(tempty0 + 8 * b, (uint32_t)((k - 1) & 1));
                     tc_fence_after();
                 }
+                if (tr) t_acc0 += clock64() - tq0;
                 const uint32_t acc = tmem + (uint32_t)(b * TC);
-                uint32_t started = 0;
                 for (int i = 0; i < ni; ++i, ++g) {
                     const int s = g % ST;
-                    uint32_t sm = (uint32_t)a.items[3 * (i0 + i) + 1];
+                    const long long tq1 = tr ? clock64() : 0;
                     g_mbar_wait(full0 + 8 * s, (uint32_t)((g / ST) & 1));
                     tc_fence_after();
-                    const uint32_t aaddr = g_smem_u32(ring + s * C::STAGE);
-                    uint32_t baddr = aaddr + OUT_A_BYTES;
-                    while (sm) {
-                        const int q = __ffs(sm) - 1;
-                        sm &= sm - 1;
-#pragma unroll
-                        for (int kk = 0; kk < 2; ++kk) {
-                            const uint64_t ad = umma_smem_desc(aaddr + kk * 32, 16, 512, UMMA_SW64);
-                            const uint64_t bd = umma_smem_desc(baddr + kk * 32, 16, 512, UMMA_SW64);
-                            umma_bf16(acc + (uint32_t)(q * 64), ad, bd, IDESC, ((started >> q & 1) || kk > 0) ? 1u : 0u);
-                        }
-                        started |= 1u << q;
-                        baddr += OUT_B_TILE;
+                    if (tr) t_acc1 += clock64() - tq1;
+                    // descriptors differ only in the start-address field (bits 0..13, address >> 4); one item
+                    // multiplies all nb strips of the CTA at once: N = 64 * nb (two instructions when nb > 4)
+                    const uint64_t ad = desc0 + (uint64_t)((s * C::STAGE) >> 4);
+                    const uint64_t bd = ad + (OUT_A_BYTES >> 4);
+                    const uint32_t accf = i > 0 ? 1u : 0u;
+                    if (nb <= 4) {
+                        umma_bf16(acc, ad, bd, idesc_lo, accf);
+                        umma_bf16(acc, ad + 2, bd + 2, idesc_lo, 1u);
+                    } else {
+                        constexpr uint64_t B4 = (4 * OUT_B_TILE) >> 4;
+                        umma_bf16(acc, ad, bd, idesc_lo, accf);
+                        umma_bf16(acc + 256, ad, bd + B4, idesc_hi, accf);
+                        umma_bf16(acc, ad + 2, bd + 2, idesc_lo, 1u);
+                        umma_bf16(acc + 256, ad + 2, bd + B4 + 2, idesc_hi, 1u);
                     }
                     umma_commit(empty0 + 8 * s);
                 }
@@ -1128,21 +1181,22 @@ out_lsm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
     } else {
         // ---- epilogue warps: TMEM lane quadrant q (hardware: warp id % 4), column half hh ----
         const int ew = warp - 2;
-        const int q = warp & 3, hh = ew >> 2;
+        const int q = warp & 3, hh = ew >> 2;                  // hh: which quarter of the chunks
         const int row = q * 32 + lane;
         const int ncb = a.S * 2;                               // 32-column chunks of this CTA
-        const int cb_lo = hh ? (ncb + 1) / 2 : 0, cb_hi = hh ? ncb : (ncb + 1) / 2;
-        unsigned char* stg = smem + C::STG_OFF + ew * 8192;
-        const uint32_t my_part = g_smem_u32(&s_part[(j * 2 + hh) * 128 + row]);
-        int sbuf = 0;
+        const int cb_lo = (ncb * hh) >> 2, cb_hi = (ncb * (hh + 1)) >> 2;
+        unsigned char* tile = smem + C::STG_OFF + ew * 4096;
+        const uint32_t my_part = g_smem_u32(&s_part[j * 128 + row]);
         for (int it = 0; it < n_my; ++it) {
             const int b = it % NBUF, k = it / NBUF, par = it & 1;
             const int m0 = ((int)blockIdx.y + it * (int)gridDim.y) * 128;
             const uint32_t trow = tmem + (uint32_t)(b * TC) + ((uint32_t)(q * 32) << 16);
-            if (warp == 2 && lane == 0) g_mbar_expect_tx(pfull0 + 8 * par, (uint32_t)a.C * 2 * 128 * 8);
+            if (warp == 2 && lane == 0) g_mbar_expect_tx(pfull0 + 8 * par, (uint32_t)a.C * 128 * 8);
+            long long tq = (tr && threadIdx.x == 64) ? clock64() : 0;
             g_mbar_wait(tfull0 + 8 * b, (uint32_t)(k & 1));
             tc_fence_after();
-            // ---- pass 1 ----
+            if (tr && threadIdx.x == 64) { const long long n = clock64(); t_acc0 += n - tq; tq = n; }
+            // ---- pass 1: row max and sum of exponentials over this warp's columns ----
             float mx = -INFINITY, sum = 0.f;
 #pragma unroll 1
             for (int cb = cb_lo; cb < cb_hi; ++cb) {
@@ -1183,81 +1237,76 @@ out_lsm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
                 sum = sum * ex2_fast((mx - mn) * OUT_L2E) + (acc0 + acc1);
                 mx = mn;
             }
-            // ---- partial {max, sum} of this half row -> every CTA of the cluster ----
+            // ---- the four warps of a lane quadrant merge their partial {max, sum}; the merged pair goes to every CTA
+            //      of the cluster (the four warps share the peers) ----
             {
-                const uint32_t slot = my_part + (uint32_t)(par * 16 * 128 * 8);
-                const uint64_t pv = ((uint64_t)__float_as_uint(sum) << 32) | (uint64_t)__float_as_uint(mx);
-                for (int peer = 0; peer < a.C; ++peer)
+                s_lp[hh * 128 + row] = make_float2(mx, sum);
+                asm volatile("bar.sync %0, 128;" ::"r"(q + 1) : "memory");
+                float gm = -INFINITY;
+#pragma unroll
+                for (int p = 0; p < 4; ++p) gm = fmaxf(gm, s_lp[p * 128 + row].x);
+                float gs = 0.f;
+#pragma unroll
+                for (int p = 0; p < 4; ++p) {
+                    const float2 e = s_lp[p * 128 + row];
+                    gs += e.y * ex2_fast((e.x - gm) * OUT_L2E);
+                }
+                const uint32_t slot = my_part + (uint32_t)(par * 8 * 128 * 8);
+                const uint64_t pv = ((uint64_t)__float_as_uint(gs) << 32) | (uint64_t)__float_as_uint(gm);
+                for (int peer = hh; peer < a.C; peer += 4)
                     asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b64 [%0], %1, [%2];" ::"r"(
                                      out_mapa(slot, peer)),
                                  "l"(pv), "r"(out_mapa(pfull0 + 8 * par, peer))
                                  : "memory");
             }
+            if (tr && threadIdx.x == 64) { const long long n = clock64(); t_acc1 += n - tq; tq = n; }
             g_mbar_wait(pfull0 + 8 * par, (uint32_t)((it >> 1) & 1));
+            if (tr && threadIdx.x == 64) { const long long n = clock64(); t_acc2 += n - tq; tq = n; }
             float lse;
             {
-                const float2* pp = s_part + par * 16 * 128 + row;
+                const float2* pp = s_part + par * 8 * 128 + row;
                 float gm = -INFINITY;
-                for (int p = 0; p < 2 * a.C; ++p) gm = fmaxf(gm, pp[p * 128].x);
+                for (int p = 0; p < a.C; ++p) gm = fmaxf(gm, pp[p * 128].x);
                 float gs = 0.f;
-                for (int p = 0; p < 2 * a.C; ++p) {
+                for (int p = 0; p < a.C; ++p) {
                     const float2 e = pp[p * 128];
                     gs += e.y * ex2_fast((e.x - gm) * OUT_L2E);
                 }
                 lse = gm + logf(gs);
             }
-            // ---- pass 2 ----
+            // ---- pass 2: z - logsumexp - log prior -> 32x32 boxes ----
+            {
 #pragma unroll 1
-            for (int cb = cb_lo; cb < cb_hi; ++cb) {
-                const int c0 = cb * 32;
-                if (col_base + c0 >= a.P) break;
-                float v[32];
-                if (any >> (cb >> 1) & 1) {
-                    tmem_ld32(trow + c0, v);
-                } else {
+                for (int cb = cb_lo; cb < cb_hi; ++cb) {
+                    const int c0 = cb * 32;
+                    if (col_base + c0 >= a.P) break;
+                    float v[32];
+                    if (any >> (cb >> 1) & 1) {
+                        tmem_ld32(trow + c0, v);
+                    } else {
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) v[i] = 0.f;
-                }
-#pragma unroll
-                for (int i = 0; i < 32; i += 4) {
-                    const float4 sb = *reinterpret_cast<const float4*>(s_sub + c0 + i);
-                    v[i] += sb.x - lse; v[i + 1] += sb.y - lse; v[i + 2] += sb.z - lse; v[i + 3] += sb.w - lse;
-                }
-                if (a.use_tma_store) {
-                    unsigned char* tile = stg + sbuf * 4096;
-                    if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
-                    __syncwarp();
-#pragma unroll
-                    for (int i = 0; i < 8; ++i)  // 128-byte swizzle: 16-byte chunk i of row `lane` at chunk i ^ (lane & 7)
-                        *reinterpret_cast<float4*>(tile + lane * 128 + ((i ^ (lane & 7)) << 4)) =
-                            make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                    __syncwarp();
-                    if (lane == 0) {
-                        asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
-                                         &tmOut),
-                                     "r"(g_smem_u32(tile)), "r"(col_base + c0), "r"(m0 + q * 32)
-                                     : "memory");
-                        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                        for (int i = 0; i < 32; ++i) v[i] = 0.f;
                     }
-                    sbuf ^= 1;
-                } else {
-                    const int64_t r = (int64_t)m0 + row;
-                    if (r < a.M) {
-                        float* dst = a.out + r * a.ldo + col_base + c0;
-                        const int nv = a.P - col_base - c0;
 #pragma unroll
-                        for (int i = 0; i < 32; ++i)
-                            if (i < nv) dst[i] = v[i];
+                    for (int i = 0; i < 32; i += 4) {
+                        const float4 sb = *reinterpret_cast<const float4*>(s_sub + c0 + i);
+                        v[i] += sb.x - lse; v[i + 1] += sb.y - lse; v[i + 2] += sb.z - lse; v[i + 3] += sb.w - lse;
                     }
+                    out_store_chunk(v, a, tmOut, tile, lane, col_base + c0, m0, q);
                 }
+                // this warp has drained its part of accumulator buffer b
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) out_mbar_arrive(tempty0 + 8 * b);
             }
-            // this warp has drained its part of accumulator buffer b
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) out_mbar_arrive(tempty0 + 8 * b);
+            if (tr && threadIdx.x == 64) { const long long n = clock64(); t_acc3 += n - tq; tq = n; }
         }
         if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+    }
+    if (tr && lane == 0) {
+        if (warp == 0) tr[0] = t_acc0;
+        if (warp == 1) { tr[1] = t_acc0; tr[2] = t_acc1; tr[9] = clock64() - t_begin; }
+        if (warp == 2) { tr[3] = t_acc0; tr[4] = t_acc1; tr[5] = t_acc2; tr[6] = t_acc3; tr[7] = clock64() - t_begin; tr[8] = n_my; }
     }
     tc_fence_before();
     __syncthreads();
@@ -1337,6 +1386,8 @@ extern "C" int hcgs_out_logsoftmax_prior_fwd(const hcgs_plan* plan, const void* 
     HCGS_REQUIRE(plan->out_C > 0, "hcgs_out_logsoftmax_prior_fwd: %d output columns exceed the fused kernel (max 4096)",
                  plan->n_out);
     HCGS_REQUIRE(ldo >= plan->n_out, "hcgs_out_logsoftmax_prior_fwd: ldo too small");
+    HCGS_REQUIRE(plan->tc <= OUT_MAX_ITEMS, "hcgs_out_logsoftmax_prior_fwd: n_in = %d exceeds %d", plan->n_in,
+                 OUT_MAX_ITEMS * 32);
     if (m <= 0) return 0;
     HCGS_REQUIRE(m <= (int64_t)16777216 * 128 / 2, "hcgs_out_logsoftmax_prior_fwd: too many rows (%lld)", (long long)m);
     CUtensorMap tm, tmo;
@@ -1368,10 +1419,29 @@ extern "C" int hcgs_out_logsoftmax_prior_fwd(const hcgs_plan* plan, const void* 
     a.C = plan->out_C;
     a.n_mtiles = (int)((m + 127) / 128);
     cudaStream_t st = (cudaStream_t)stream;
-    switch (out_tmem_cols(plan->out_S)) {
-        case 64: return out_launch<64>(tm, tmo, a, st);
-        case 128: return out_launch<128>(tm, tmo, a, st);
-        case 256: return out_launch<256>(tm, tmo, a, st);
-        default: return out_launch<512>(tm, tmo, a, st);
+    static const bool want_trace = getenv("HCGS_OUT_TRACE") != nullptr;
+    static long long* d_trace = nullptr;
+    a.trace = nullptr;
+    if (want_trace) {
+        if (!d_trace) HCGS_CHECK_CUDA(cudaMalloc((void**)&d_trace, 16 * sizeof(long long)));
+        HCGS_CHECK_CUDA(cudaMemsetAsync(d_trace, 0, 16 * sizeof(long long), st));
+        a.trace = d_trace;
     }
+    int rc;
+    switch (out_tmem_cols(plan->out_S)) {
+        case 64: rc = out_launch<64>(tm, tmo, a, st); break;
+        case 128: rc = out_launch<128>(tm, tmo, a, st); break;
+        case 256: rc = out_launch<256>(tm, tmo, a, st); break;
+        default: rc = out_launch<512>(tm, tmo, a, st); break;
+    }
+    if (want_trace && rc == 0) {
+        long long h[16];
+        HCGS_CHECK_CUDA(cudaStreamSynchronize(st));
+        HCGS_CHECK_CUDA(cudaMemcpy(h, d_trace, sizeof(h), cudaMemcpyDeviceToHost));
+        const double n = h[8] > 0 ? (double)h[8] : 1.0;
+        fprintf(stderr, "[out trace] tiles %lld, cycles/tile: total %.0f | producer wait-empty %.0f | mma wait-tempty %.0f "
+                        "wait-full %.0f (loop total %.0f) | epilogue wait-tfull %.0f pass1+push %.0f wait-pfull %.0f combine+pass2 %.0f\n",
+                h[8], h[7] / n, h[0] / n, h[1] / n, h[2] / n, h[9] / n, h[3] / n, h[4] / n, h[5] / n, h[6] / n);
+    }
+    return rc;
 }

@@ -205,26 +205,35 @@ extern "C" int hcgs_plan_create(const float* mask, int n_out, int n_in, int recu
             std::vector<int> optr(C + 1, 0), oitems, otile;
             for (int j = 0; j < C; ++j) {
                 optr[j] = (int)oitems.size() / 3;
+                // k tiles kept by any strip of this CTA, and the highest strip that keeps anything: every item
+                // multiplies ALL strips 0..hi at once (one wide MMA instead of one per kept strip; the masked
+                // weights inside are zeros) -- the issue rate of the single MMA thread, not the tensor pipe,
+                // bounds this kernel
+                std::vector<int> kts;
+                int hi = -1;
                 for (int kt = 0; kt < p->tc; ++kt) {
-                    uint32_t m = 0;
-                    for (int s = 0; s < S; ++s) {
-                        const int gs = j * S + s;
+                    bool keep = false;
+                    for (int s = 0; s < S; ++s)
                         for (int h = 0; h < 2; ++h) {
-                            const int trow = gs * 2 + h;
-                            if (trow < p->tr && nz[(size_t)trow * p->tc + kt]) m |= 1u << s;
+                            const int trow = (j * S + s) * 2 + h;
+                            if (trow < p->tr && nz[(size_t)trow * p->tc + kt]) {
+                                keep = true;
+                                hi = std::max(hi, s);
+                            }
                         }
-                    }
-                    if (!m) continue;
+                    if (keep) kts.push_back(kt);
+                }
+                const uint32_t m = hi < 0 ? 0u : (uint32_t)((1u << (hi + 1)) - 1u);
+                for (int kt : kts) {
                     oitems.push_back(kt);
                     oitems.push_back((int)m);
                     oitems.push_back((int)otile.size() / 2);
-                    for (int s = 0; s < S; ++s)
-                        if (m >> s & 1) {
-                            otile.push_back(j * S + s);
-                            otile.push_back(kt);
-                        }
-                    p->out_any[j] |= m;
+                    for (int s = 0; s <= hi; ++s) {
+                        otile.push_back(j * S + s);
+                        otile.push_back(kt);
+                    }
                 }
+                p->out_any[j] = m;
             }
             optr[C] = (int)oitems.size() / 3;
             p->out_C = C;
