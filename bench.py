@@ -178,6 +178,10 @@ def algorithmic_work(name, a):
             plan, n_w, dy, x = a[0], a[1], a[2], a[3]
             m = dy.shape[0]
             return m * (dy.shape[1] + x.shape[1]) * 2, 2 * m * plan.nz_tiles * 1024 * n_w
+        if name == 'out_logsoftmax_prior_fwd':   # (plan, wpack, x_bf16, bias, log_prior, out)
+            plan, x, out = a[0], a[2], a[5]
+            m = x.shape[0]
+            return m * (x.shape[1] * 2 + out.shape[1] * 4), 2 * m * plan.nz_tiles * 1024
         if name in ('lstm_fwd', 'lstm_bwd'):
             plan = a[0]
             t = a[2] if name == 'lstm_fwd' else a[3]
@@ -194,7 +198,8 @@ class KernelTimers:
     NAMES = ['mask_apply', 'bsgemm_nt', 'bsgemm_nn', 'bs_sddmm', 'colsum', 'bn_fwd', 'bn_bwd', 'lstm_pack',
              'lstm_fwd', 'lstm_bwd', 'logsoftmax_fwd', 'logsoftmax_bwd', 'act_fwd', 'act_bwd', 'quantize_w',
              'quantize_act', 'nll_fwd_bwd', 'bn_fwd_il', 'bn_bwd_il', 'lstm_tc_pack', 'lstm_tc_fwd', 'lstm_tc_bwd',
-             'tc_pack_nt', 'tc_gemm_nt', 'tc_pack_nn', 'tc_gemm_nn', 'tc_sddmm', 'cast_bf16']
+             'tc_pack_nt', 'tc_gemm_nt', 'tc_pack_nn', 'tc_gemm_nn', 'tc_sddmm', 'cast_bf16', 'out_pack',
+             'out_logsoftmax_prior_fwd', 'bn_stats_il', 'logsoftmax_bwd_fused']
 
     def __init__(self, names=None):
         from b200 import native
@@ -230,6 +235,136 @@ class KernelTimers:
     def restore(self):
         for n, f in self.orig.items():
             setattr(self.native, n, f)
+
+
+EXPORT_MODEL = ['out_dnn1=compute(LSTM_layers,fbank)', 'out_dnn2=compute(MLP_layers,out_dnn1)']
+
+
+def synthetic_utterances(n, T, seed):
+    """Evaluation set: n utterances of U[T/2, T] frames of N(0,1) features."""
+    g = torch.Generator().manual_seed(seed)
+    lens = torch.randint(max(1, T // 2), T + 1, (n,), generator=g).tolist()
+    return [torch.randn(l, D_FEA, generator=g) for l in lens]
+
+
+def run_export(dev, nets_train, args, T, B, rank, world, hbm_peak, peak_kind):
+    """Forward-only posterior export (BASELINE configs[4]; reference: core.run_nn to_do='forward', core.py:183-249):
+    the trained nets in eval mode, log prior fused into the output kernel, utterances batched right-padded."""
+    import tempfile
+    import neural_networks as nb
+    import posterior_io
+    from b200 import export as bexport
+    from b200 import native
+    from b200.graph import Graph
+    s_lstm, s_cd, _ = cfg_sections('forward', args.precision)
+    tmp = tempfile.mkdtemp(prefix='hcgs_export_')
+    s_lstm['out_folder'] = s_cd['out_folder'] = tmp
+    torch.manual_seed(2234)
+    np.random.seed(2234)
+    lstm = nb.LSTM(s_lstm, D_FEA)
+    cd = nb.MLP(s_cd, lstm.out_dim)
+    lstm.load_state_dict(nets_train['LSTM_layers'].state_dict())
+    cd.load_state_dict(nets_train['MLP_layers'].state_dict())
+    lstm.to(dev).eval()
+    cd.to(dev).eval()
+    counts = np.random.RandomState(7).rand(N_PDF).astype(np.float32) + 0.05
+    cd.log_prior = posterior_io.log_prior_tensor(counts, dev)
+    graph = Graph(EXPORT_MODEL, {'LSTM_layers': lstm, 'MLP_layers': cd}, {'LSTM_layers': True, 'MLP_layers': False},
+                  {'fbank': (0, D_FEA)}, {})
+
+    def fwd(x):
+        return graph.forward(x, x.shape[0], x.shape[1], 'forward', ['out_dnn2'])['out_dnn2']
+
+    n_groups = 3
+    feats = synthetic_utterances(n_groups * B, T, 4242 + rank)
+    lengths = [int(f.shape[0]) for f in feats]
+    groups = bexport.plan_groups(lengths, B)
+    resident = [bexport.pack_group(feats, g).to(dev) for g in groups]
+    real = [sum(lengths[i] for i in g) for g in groups]
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            torch.distributed.barrier()
+            torch.cuda.synchronize()
+
+    steps = max(args.steps, 3)
+    with torch.no_grad():
+        for s in range(3):
+            fwd(resident[s % len(resident)])
+        names = ['out_logsoftmax_prior_fwd', 'lstm_tc_fwd', 'tc_gemm_nt'] if args.precision == 'bf16' else ['lstm_fwd']
+        timers = KernelTimers(names)
+        sync_all()
+        native.reset_launch_count()
+        timers.on = True
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        frames = padded = 0
+        for s in range(steps):
+            post = fwd(resident[s % len(resident)])
+            frames += real[s % len(resident)]
+            padded += post.shape[0]
+        e1.record()
+        sync_all()
+        timers.on = False
+        launches = native.LAUNCHES['total']
+        ms = e0.elapsed_time(e1)
+        ktot, kcnt, kwork = timers.summary()
+        timers.restore()
+        # end to end through the exporter: host features -> pinned pack -> H2D -> forward -> D2H of the posteriors
+        ex = bexport.PosteriorExporter(fwd, dev, batch=B)
+        for _ in ex.run(feats):              # warm-up pass: the pinned staging buffers are allocated once
+            pass
+        ex.frames = ex.h2d_bytes = ex.d2h_bytes = 0
+        sync_all()
+        t0 = time.perf_counter()
+        checksum = 0.0
+        for _, m in ex.run(feats):
+            checksum += float(m[0, 0])
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+    assert np.isfinite(checksum)
+    t = torch.tensor([ms, dt * 1e3, float(frames), float(ex.frames), float(launches), float(ex.h2d_bytes),
+                      float(ex.d2h_bytes)], device=dev, dtype=torch.float64)
+    if world > 1:
+        tmax = t.clone()
+        torch.distributed.all_reduce(tmax, op=torch.distributed.ReduceOp.MAX)
+        tsum = t.clone()
+        torch.distributed.all_reduce(tsum, op=torch.distributed.ReduceOp.SUM)
+        t = torch.stack([tmax[0], tmax[1], tsum[2], tsum[3], tsum[4], tsum[5], tsum[6]])
+    ms, ms_e2e, frames, frames_e2e, launches, h2d, d2h = [v.item() for v in t]
+    res = {'metric': 'hcgs_lstm_posterior_frames_per_sec', 'value': frames / (ms * 1e-3), 'unit': 'frames/s',
+           'steps': steps, 'ms_per_step': ms / steps, 'gpu_launches': int(launches),
+           'workload': 'forward-only export of the same 4x550 HCGS LSTM + 1944-pdf head, eval batch norm, fused '
+                       'log-softmax - log-prior; %d utterances of U[%d,%d] frames per GPU, %d per right-padded group, '
+                       'utterances sharded over ranks without a collective' % (len(feats), T // 2, T, B),
+           'frames_counted': 'real (unpadded) frames; %.0f %% of the padded rows' % (100.0 * frames / max(padded * world, 1)),
+           'e2e': {'value': frames_e2e / (ms_e2e * 1e-3), 'unit': 'frames/s', 'h2d_bytes_per_step': h2d / len(groups),
+                   'd2h_bytes_per_step': d2h / len(groups), 'ms_per_step': ms_e2e / len(groups),
+                   'timed': 'wall clock around PosteriorExporter.run (host packing, H2D, forward, D2H of every '
+                            'posterior matrix into pinned memory, double buffered)'}}
+    k = 'out_logsoftmax_prior_fwd'
+    if k in ktot and k in kwork:
+        # the 1944-pdf head only (this export graph has no monophone head)
+        avg_ms = ktot[k] / kcnt[k]
+        byts = kwork[k][0] / kcnt[k]
+        traffic = None
+        tpath = os.path.join(ROOT, 'profiles', 'ncu_traffic.json')
+        if os.path.exists(tpath):
+            try:
+                traffic = json.load(open(tpath)).get('%s@T%d_B%d' % (k, T, B))
+            except Exception:
+                traffic = None
+        res['roofline'] = {'kernel': k, 'bound': 'hbm', 'achieved': byts / (avg_ms * 1e-3) / 1e9, 'peak': hbm_peak,
+                           'unit': 'GB/s', 'frac': byts / (avg_ms * 1e-3) / 1e9 / hbm_peak, 'traffic': traffic,
+                           'peak_source': peak_kind, 'avg_launch_ms': avg_ms, 'share_of_step': ktot[k] / ms,
+                           'algorithmic_bytes_per_launch': byts,
+                           'traffic_note': 'ncu capture of the same kernel on a full 131072-row group (T*B rows); '
+                                           'export groups are shorter on average',
+                           'effective_tflops': kwork[k][1] / kcnt[k] / (avg_ms * 1e-3) / 1e12}
+    res['kernels'] = {n: {'ms_per_step': round(ktot[n] / steps, 4), 'launches_per_step': kcnt[n] / steps}
+                      for n in sorted(ktot, key=lambda x: -ktot[x])}
+    return res
 
 
 def oracle_workload(seed=2234):
@@ -329,6 +464,7 @@ def main():
     ap.add_argument('--precision', default='bf16', choices=['bf16', 'fp32'],
                     help='bf16 = tensor-core build (BASELINE configs[1] "bf16 train"), fp32 = CUDA-core parity build')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-export', action='store_true', help='skip the posterior-export measurement')
     args = ap.parse_args()
 
     from b200 import dist as bdist
@@ -444,6 +580,11 @@ def main():
     ms_e2e = e2.elapsed_time(e3)
     assert len(losses) == args.steps and all(np.isfinite(losses)), losses
 
+    hbm_peak, tf_peak, peak_kind = measured_peaks()
+    export = None
+    if not args.no_export:
+        export = run_export(dev, nets, args, T, B, rank, world, hbm_peak, peak_kind)
+
     t = torch.tensor([ms_total, ms_e2e, float(frames), float(frames_e2e), float(launches)], device=dev,
                      dtype=torch.float64)
     if world > 1:
@@ -460,7 +601,6 @@ def main():
 
     value = frames / (ms_total * 1e-3)
     e2e = frames_e2e / (ms_e2e * 1e-3)
-    hbm_peak, tf_peak, peak_kind = measured_peaks()
     # dominant kernel = largest share of the timed region among our kernels
     dom = max(ktot, key=ktot.get)
     avg_ms = ktot[dom] / kcnt[dom]
@@ -489,7 +629,7 @@ def main():
             traffic = json.load(open(tpath)).get('%s@T%d_B%d' % (dom, T, B))
         except Exception:
             traffic = None
-    roof['traffic'] = traffic
+    roof['traffic'] = float(traffic) if isinstance(traffic, (int, float)) else None
     per_kernel = {}
     for k in sorted(ftot, key=lambda x: -ftot[x]):
         e = {'ms_per_step': round(ftot[k] / args.steps, 4), 'launches_per_step': fcnt[k] / args.steps}
@@ -506,6 +646,8 @@ def main():
                     'pipelining': 'next minibatch uploaded on a side stream; loss of step i read after step i+1 is queued'},
             'roofline': roof,
             'kernels_untimed_pass': per_kernel}
+    if export is not None:
+        line['export'] = export
     if not args.no_cpu_baseline and world == 1:
         threads = os.cpu_count() or 1
         fps, ms = time_oracle(100, 8, 3, 1, threads)

@@ -244,6 +244,11 @@ int hcgs_logsoftmax_fwd(const float* z, int ldz, float* out, int ldo, int64_t m,
                         const float* log_prior, hcgs_stream stream);
 int hcgs_logsoftmax_bwd(const float* dlogp, const float* logp, float* dz, int64_t m, int p,
                         hcgs_stream stream);
+/* tensor-core build: the same backward fused with what follows it in the output layer -- the bias gradient
+ * db[p] += sum_m dz[m,p] (fp32, caller zero-initialises; NULL = skip) and the bf16 copy of dz that the dW / dX
+ * products read ([m, ldo], pad columns zeroed).  The fp32 dz is never written.  p % 4 == 0, p <= 4096.   */
+int hcgs_logsoftmax_bwd_fused(const float* dlogp, const float* logp, int64_t m, int p, void* dz_bf16,
+                              int64_t ldo, float* db, hcgs_stream stream);
 int hcgs_nll_fwd_bwd(const float* logp, int64_t m, int p, const float* labels, int ldlab, float scale,
                      float* dz, float* stats, hcgs_stream stream);
 

@@ -426,27 +426,33 @@ class MLPLayerTCFunction(torch.autograd.Function):
         N, D, O = ctx.dims
         dev = dout.device
         dout = dout.contiguous()
-        dzb = torch.empty(N, O, device=dev, dtype=torch.float32)
-        if ctx.softmax:
-            if ctx.had_prior:
-                raise native.NativeError('backward through a prior-normalised posterior is not defined')
-            native.logsoftmax_bwd(dout, ctx.out_store, dzb)
+        dgamma = dbeta = db = None
+        if ctx.softmax and ctx.had_prior:
+            raise native.NativeError('backward through a prior-normalised posterior is not defined')
+        if ctx.softmax and not rt.use_bn and O % 4 == 0 and O <= 4096:
+            # log-softmax backward, bias gradient and the bf16 operand of the dW / dX products in one pass
+            dz_b = torch.empty(N, native.pad8(O), device=dev, dtype=torch.bfloat16)
+            if ctx.needs_input_grad[2]:
+                db = torch.zeros(O, device=dev, dtype=torch.float32)
+            native.logsoftmax_bwd_fused(dout, ctx.out_store, dz_b, db)
         else:
-            native.act_bwd(dout, ctx.out_store, ctx.drop_mask, dzb, rt.act)
-        dgamma = dbeta = None
-        if rt.use_bn:
-            dz = torch.empty_like(dzb)
-            dgamma = torch.empty(O, device=dev, dtype=torch.float32)
-            dbeta = torch.empty(O, device=dev, dtype=torch.float32)
-            native.bn_bwd(dzb, z, 1, O, [gamma], save_mean, save_invstd, dz, [dgamma], [dbeta], _ws(dev, O))
-        else:
-            dz = dzb
-        db = None
-        if ctx.needs_input_grad[2]:
-            db = torch.empty(O, device=dev, dtype=torch.float32)
-            native.colsum(dz, 1, O, [db])
-        dz_b = _bf16_rows(dz, native.pad8(O))
-        del dz, dzb
+            dzb = torch.empty(N, O, device=dev, dtype=torch.float32)
+            if ctx.softmax:
+                native.logsoftmax_bwd(dout, ctx.out_store, dzb)
+            else:
+                native.act_bwd(dout, ctx.out_store, ctx.drop_mask, dzb, rt.act)
+            if rt.use_bn:
+                dz = torch.empty_like(dzb)
+                dgamma = torch.empty(O, device=dev, dtype=torch.float32)
+                dbeta = torch.empty(O, device=dev, dtype=torch.float32)
+                native.bn_bwd(dzb, z, 1, O, [gamma], save_mean, save_invstd, dz, [dgamma], [dbeta], _ws(dev, O))
+            else:
+                dz = dzb
+            if ctx.needs_input_grad[2]:
+                db = torch.empty(O, device=dev, dtype=torch.float32)
+                native.colsum(dz, 1, O, [db])
+            dz_b = _bf16_rows(dz, native.pad8(O))
+            del dz, dzb
         dw = torch.zeros(O, D, device=dev, dtype=torch.float32)
         native.tc_sddmm(rt.plan_x, 1, dz_b, xb, [dw], rt.mask_x)
         dx = None

@@ -76,6 +76,7 @@ SIGNATURES = {
     'hcgs_act_bwd': (c_int, [_f, _f, _f, _f, c_int64, c_int, c_void_p]),
     'hcgs_logsoftmax_fwd': (c_int, [_f, c_int, _f, c_int, c_int64, c_int, _f, c_void_p]),
     'hcgs_logsoftmax_bwd': (c_int, [_f, _f, _f, c_int64, c_int, c_void_p]),
+    'hcgs_logsoftmax_bwd_fused': (c_int, [_f, _f, c_int64, c_int, _f, c_int64, _f, c_void_p]),
     'hcgs_nll_fwd_bwd': (c_int, [_f, c_int64, c_int, _f, c_int, c_float, _f, _f, c_void_p]),
     'hcgs_opt_step': (c_int, [c_int, _f, _f, _f, _f, c_int64, POINTER(c_float), c_float, c_void_p]),
 }
@@ -109,7 +110,7 @@ KERNELS_PER_CALL = {'hcgs_mask_apply': 1, 'hcgs_quantize_w': 1, 'hcgs_quantize_a
                     'hcgs_tc_pack_nt': 1, 'hcgs_tc_gemm_nt': 1, 'hcgs_cast_bf16': 1,
                     'hcgs_tc_pack_nn': 1, 'hcgs_tc_gemm_nn': 1, 'hcgs_tc_sddmm': 1, 'hcgs_out_pack': 1,
                     'hcgs_out_logsoftmax_prior_fwd': 1, 'hcgs_act_fwd': 1, 'hcgs_act_bwd': 1,
-                    'hcgs_logsoftmax_fwd': 1, 'hcgs_logsoftmax_bwd': 1, 'hcgs_nll_fwd_bwd': 1, 'hcgs_opt_step': 1}
+                    'hcgs_logsoftmax_fwd': 1, 'hcgs_logsoftmax_bwd': 1, 'hcgs_logsoftmax_bwd_fused': 1, 'hcgs_nll_fwd_bwd': 1, 'hcgs_opt_step': 1}
 LAUNCHES = {'total': 0}
 
 
@@ -547,6 +548,17 @@ def logsoftmax_bwd(dlogp, logp, dz):
     assert dlogp.is_contiguous() and logp.is_contiguous() and dz.is_contiguous()
     _check(load().hcgs_logsoftmax_bwd(_ptr(dlogp), _ptr(logp), _ptr(dz), logp.shape[0], logp.shape[1], _stream()),
            'hcgs_logsoftmax_bwd')
+
+
+def logsoftmax_bwd_fused(dlogp, logp, dz_bf16, db=None):
+    """dz = dlogp - exp(logp) * rowsum(dlogp) written as bf16 [m, ld] (pad columns zero) and, when db is given,
+    db += column sums of the fp32 dz (db zero-initialised by the caller).  Needs p % 4 == 0, p <= 4096."""
+    _require_cuda(dlogp, logp, db)
+    _require_cuda_any(dz_bf16)
+    assert dlogp.is_contiguous() and logp.is_contiguous() and dz_bf16.dtype == torch.bfloat16
+    assert dz_bf16.shape[0] == logp.shape[0] and dz_bf16.stride(1) == 1
+    _check(load().hcgs_logsoftmax_bwd_fused(_ptr(dlogp), _ptr(logp), logp.shape[0], logp.shape[1], _ptr(dz_bf16),
+                                            dz_bf16.stride(0), _ptr(db), _stream()), 'hcgs_logsoftmax_bwd_fused')
 
 
 def nll_fwd_bwd(logp, labels, ldlab, scale, dz, stats):

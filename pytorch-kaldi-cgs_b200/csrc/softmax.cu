@@ -2,6 +2,10 @@
 //
 // One warp per frame (row); a row of P = 1944 .. 3480 log-probabilities stays in L1 between the
 // passes, so HBM sees one read of the logits and one write of the result.
+#include <cuda_bf16.h>
+
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace hcgs {
@@ -98,9 +102,113 @@ __global__ void __launch_bounds__(256) nll_fwd_bwd_kernel(const float* __restric
     }
 }
 
+// Backward of the output layer's log-softmax for the tensor-core build, fused with what follows it:
+//   dz = dlogp - exp(logp) * rowsum(dlogp)   (autograd of nn.LogSoftmax, neural_networks.py:73-74)
+//   db[p] += sum_m dz[m, p]                  (bias gradient, fp32, before rounding)
+//   dz_bf16[m, :] = bf16(dz)                 (operand of the dW / dX tensor-core products; pad columns zero)
+// One warp per row, persistent over rows; a lane keeps its 4*NV4 columns of the row in registers between the
+// row sum and the write, and its running column sums in registers (NV4 <= 16) or in shared memory.
+template <int NV4>
+__global__ void __launch_bounds__(256) logsoftmax_bwd_fused_kernel(const float* __restrict__ dlogp,
+                                                                   const float* __restrict__ logp, int64_t M, int P,
+                                                                   __nv_bfloat16* __restrict__ dz, int64_t ldo,
+                                                                   float* __restrict__ db) {
+    constexpr bool COLREG = NV4 <= 16;
+    extern __shared__ float s_col[];  // [P] column sums of this CTA
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int p = threadIdx.x; p < P; p += 256) s_col[p] = 0.f;
+    __syncthreads();
+    const int nv = (P + 127) / 128;  // float4 per lane actually used (<= NV4)
+    float4 csum[COLREG ? NV4 : 1];
+    if (COLREG) {
+#pragma unroll
+        for (int i = 0; i < (COLREG ? NV4 : 1); ++i) csum[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    const int64_t wstride = (int64_t)gridDim.x * 8;
+    for (int64_t m = (int64_t)blockIdx.x * 8 + warp; m < M; m += wstride) {
+        const float4* dr = reinterpret_cast<const float4*>(dlogp + m * P);
+        const float4* lr = reinterpret_cast<const float4*>(logp + m * P);
+        float4 d[NV4];
+        float s = 0.f;
+#pragma unroll
+        for (int i = 0; i < NV4; ++i) {
+            const int c = (lane + 32 * i) * 4;
+            if (i < nv && c < P) {
+                d[i] = __ldcs(dr + lane + 32 * i);
+                s += (d[i].x + d[i].y) + (d[i].z + d[i].w);
+            } else {
+                d[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        }
+        s = warp_sum(s);
+        __nv_bfloat16* orow = dz + m * ldo;
+#pragma unroll
+        for (int i = 0; i < NV4; ++i) {
+            const int c = (lane + 32 * i) * 4;
+            if (i < nv && c < P) {
+                const float4 l = __ldcs(lr + lane + 32 * i);
+                float4 g;
+                g.x = d[i].x - __expf(l.x) * s;
+                g.y = d[i].y - __expf(l.y) * s;
+                g.z = d[i].z - __expf(l.z) * s;
+                g.w = d[i].w - __expf(l.w) * s;
+                if (COLREG) {
+                    csum[COLREG ? i : 0].x += g.x; csum[COLREG ? i : 0].y += g.y;
+                    csum[COLREG ? i : 0].z += g.z; csum[COLREG ? i : 0].w += g.w;
+                } else {
+                    atomicAdd(s_col + c, g.x); atomicAdd(s_col + c + 1, g.y);
+                    atomicAdd(s_col + c + 2, g.z); atomicAdd(s_col + c + 3, g.w);
+                }
+                const __nv_bfloat162 lo = __floats2bfloat162_rn(g.x, g.y), hi = __floats2bfloat162_rn(g.z, g.w);
+                uint2 pk;
+                pk.x = *reinterpret_cast<const uint32_t*>(&lo);
+                pk.y = *reinterpret_cast<const uint32_t*>(&hi);
+                *reinterpret_cast<uint2*>(orow + c) = pk;
+            }
+        }
+        for (int c = P + lane; c < ldo; c += 32) orow[c] = __float2bfloat16(0.f);
+    }
+    if (db == nullptr) return;
+    if (COLREG) {
+#pragma unroll
+        for (int i = 0; i < (COLREG ? NV4 : 1); ++i) {
+            const int c = (lane + 32 * i) * 4;
+            if (i < nv && c < P) {
+                atomicAdd(s_col + c, csum[i].x); atomicAdd(s_col + c + 1, csum[i].y);
+                atomicAdd(s_col + c + 2, csum[i].z); atomicAdd(s_col + c + 3, csum[i].w);
+            }
+        }
+    }
+    __syncthreads();
+    for (int p = threadIdx.x; p < P; p += 256) {
+        const float v = s_col[p];
+        if (v != 0.f) atomicAdd(db + p, v);
+    }
+}
+
 }  // namespace hcgs
 
 using namespace hcgs;
+
+extern "C" int hcgs_logsoftmax_bwd_fused(const float* dlogp, const float* logp, int64_t m, int p, void* dz_bf16,
+                                         int64_t ldo, float* db, hcgs_stream stream) {
+    HCGS_REQUIRE(dlogp && logp && dz_bf16, "hcgs_logsoftmax_bwd_fused: NULL argument");
+    HCGS_REQUIRE(p > 0 && p % 4 == 0 && p <= 4096, "hcgs_logsoftmax_bwd_fused: p = %d must be a multiple of 4, <= 4096", p);
+    HCGS_REQUIRE(ldo >= p && ldo % 4 == 0, "hcgs_logsoftmax_bwd_fused: ldo = %lld must be a multiple of 4, >= p",
+                 (long long)ldo);
+    HCGS_REQUIRE((((uintptr_t)dlogp | (uintptr_t)logp) & 15) == 0 && ((uintptr_t)dz_bf16 & 7) == 0,
+                 "hcgs_logsoftmax_bwd_fused: operands must be 16-byte aligned");
+    if (m <= 0) return 0;
+    const int blocks = (int)std::min<int64_t>((m + 7) / 8, 148 * 2);
+    const size_t smem = (size_t)p * sizeof(float);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (p <= 2048)
+        logsoftmax_bwd_fused_kernel<16><<<blocks, 256, smem, st>>>(dlogp, logp, m, p, (__nv_bfloat16*)dz_bf16, ldo, db);
+    else
+        logsoftmax_bwd_fused_kernel<32><<<blocks, 256, smem, st>>>(dlogp, logp, m, p, (__nv_bfloat16*)dz_bf16, ldo, db);
+    HCGS_LAUNCH_CHECK();
+    return 0;
+}
 
 extern "C" int hcgs_logsoftmax_fwd(const float* z, int ldz, float* out, int ldo, int64_t m, int p,
                                    const float* log_prior, hcgs_stream stream) {

@@ -324,3 +324,30 @@ def test_optimizer_steps_match_torch(kind):
         hp[7] = float(step)
         native.opt_step(k, pd, g.to(d), s1, s2, hp)
         close(pd, p.detach(), rtol=2e-6, what='%s step %d' % (kind, step))
+
+
+@pytest.mark.parametrize('M,P', [(517, 1944), (300, 48), (70, 3480), (9, 4)])
+def test_logsoftmax_bwd_fused(M, P):
+    """hcgs_logsoftmax_bwd_fused = logsoftmax_bwd + colsum + cast_bf16 of the unfused path (same arithmetic)."""
+    from b200 import native
+    d = torch.device('cuda', 0)
+    torch.manual_seed(M + P)
+    logp = torch.log_softmax(torch.randn(M, P) * 3, 1).to(d)
+    dlogp = (torch.randn(M, P) * (torch.rand(M, P) < 0.1)).to(d)      # mostly zeros, like the NLL gradient
+    ld = native.pad8(P)
+    dzb = torch.full((M, ld), 7.0, device=d, dtype=torch.bfloat16)
+    db = torch.zeros(P, device=d)
+    native.logsoftmax_bwd_fused(dlogp, logp, dzb, db)
+    dz = torch.empty(M, P, device=d)
+    native.logsoftmax_bwd(dlogp, logp, dz)
+    torch.cuda.synchronize()
+    ref = dlogp.double() - logp.double().exp() * dlogp.double().sum(1, keepdim=True)
+    assert (dz.double() - ref).abs().max().item() <= 1e-5 * max(ref.abs().max().item(), 1e-30)
+    want = dz.to(torch.bfloat16).float()
+    got = dzb[:, :P].float()
+    # same fp32 value rounded to bf16; __expf vs expf may flip a rounding of the last bf16 bit
+    assert (got - want).abs().max().item() <= 2 ** -7 * max(want.abs().max().item(), 1e-30)
+    assert (got - want).abs().mean().item() <= 1e-4 * max(want.abs().max().item(), 1e-30)
+    if ld > P:
+        assert dzb[:, P:].float().abs().max().item() == 0
+    assert (db.double() - ref.sum(0)).abs().max().item() <= 1e-4 * max(ref.sum(0).abs().max().item(), 1e-30)
