@@ -109,7 +109,7 @@ __global__ void __launch_bounds__(256) nll_fwd_bwd_kernel(const float* __restric
 // One warp per row, persistent over rows; a lane keeps its 4*NV4 columns of the row in registers between the
 // row sum and the write, and its running column sums in registers (NV4 <= 16) or in shared memory.
 template <int NV4>
-__global__ void __launch_bounds__(256) logsoftmax_bwd_fused_kernel(const float* __restrict__ dlogp,
+__global__ void __launch_bounds__(256, 2) logsoftmax_bwd_fused_kernel(const float* __restrict__ dlogp,
                                                                    const float* __restrict__ logp, int64_t M, int P,
                                                                    __nv_bfloat16* __restrict__ dz, int64_t ldo,
                                                                    float* __restrict__ db) {
@@ -128,16 +128,14 @@ __global__ void __launch_bounds__(256) logsoftmax_bwd_fused_kernel(const float* 
     for (int64_t m = (int64_t)blockIdx.x * 8 + warp; m < M; m += wstride) {
         const float4* dr = reinterpret_cast<const float4*>(dlogp + m * P);
         const float4* lr = reinterpret_cast<const float4*>(logp + m * P);
-        float4 d[NV4];
+        // the row sum first; the second read of dlogp below hits L1 (a row is 4*P bytes, the warp just read it)
         float s = 0.f;
 #pragma unroll
         for (int i = 0; i < NV4; ++i) {
             const int c = (lane + 32 * i) * 4;
             if (i < nv && c < P) {
-                d[i] = __ldcs(dr + lane + 32 * i);
-                s += (d[i].x + d[i].y) + (d[i].z + d[i].w);
-            } else {
-                d[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                const float4 d = __ldg(dr + lane + 32 * i);
+                s += (d.x + d.y) + (d.z + d.w);
             }
         }
         s = warp_sum(s);
@@ -147,11 +145,12 @@ __global__ void __launch_bounds__(256) logsoftmax_bwd_fused_kernel(const float* 
             const int c = (lane + 32 * i) * 4;
             if (i < nv && c < P) {
                 const float4 l = __ldcs(lr + lane + 32 * i);
+                const float4 d = __ldg(dr + lane + 32 * i);
                 float4 g;
-                g.x = d[i].x - __expf(l.x) * s;
-                g.y = d[i].y - __expf(l.y) * s;
-                g.z = d[i].z - __expf(l.z) * s;
-                g.w = d[i].w - __expf(l.w) * s;
+                g.x = d.x - __expf(l.x) * s;
+                g.y = d.y - __expf(l.y) * s;
+                g.z = d.z - __expf(l.z) * s;
+                g.w = d.w - __expf(l.w) * s;
                 if (COLREG) {
                     csum[COLREG ? i : 0].x += g.x; csum[COLREG ? i : 0].y += g.y;
                     csum[COLREG ? i : 0].z += g.z; csum[COLREG ? i : 0].w += g.w;
@@ -199,7 +198,7 @@ extern "C" int hcgs_logsoftmax_bwd_fused(const float* dlogp, const float* logp, 
     HCGS_REQUIRE((((uintptr_t)dlogp | (uintptr_t)logp) & 15) == 0 && ((uintptr_t)dz_bf16 & 7) == 0,
                  "hcgs_logsoftmax_bwd_fused: operands must be 16-byte aligned");
     if (m <= 0) return 0;
-    const int blocks = (int)std::min<int64_t>((m + 7) / 8, 148 * 2);
+    const int blocks = (int)std::min<int64_t>((m + 7) / 8, 148 * 2);  // two resident CTAs per SM, one wave
     const size_t smem = (size_t)p * sizeof(float);
     cudaStream_t st = (cudaStream_t)stream;
     if (p <= 2048)
