@@ -934,7 +934,8 @@ extern "C" int hcgs_tc_sddmm(const hcgs_plan* plan, int n_w, const void* dy_bf16
 //   warp 0      TMA producer: x boxes + packed weight tiles into a ring of shared-memory stages
 //   warp 1      tcgen05.mma issuer; accumulators double buffered in TMEM (2 x S*64 columns) when S <= 4, so the
 //               products of row tile i+1 run under the epilogue of tile i
-//   warps 2..9  epilogue: pass 1 reads the accumulators once for the row max / sum of exponentials, pushes the
+//   warps 2..17 epilogue (two groups of 8 on alternate row tiles when the accumulators are double buffered):
+//               pass 1 reads the accumulators once for the row max / sum of exponentials, pushes the
 //               partial {max, sum} to every CTA of the cluster with st.async (transaction-count mbarrier, no cluster
 //               barrier), pass 2 reads them again, subtracts logsumexp + log prior and stores 32x32 fp32 boxes
 //               with TMA (128-byte swizzled staging tiles, two per warp)
@@ -1079,7 +1080,7 @@ out_lsm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         }
         for (int b = 0; b < 2; ++b) {
             g_mbar_init(tfull0 + 8 * b, 1);
-            g_mbar_init(tempty0 + 8 * b, OUT_EPI_WARPS);
+            g_mbar_init(tempty0 + 8 * b, OUT_EPI_WARPS / NBUF);
             g_mbar_init(pfull0 + 8 * b, 1);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -1180,18 +1181,24 @@ out_lsm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         }
     } else {
         // ---- epilogue warps: TMEM lane quadrant q (hardware: warp id % 4), column half hh ----
+        // With two accumulator buffers the 16 warps form two groups of 8 that take alternate row tiles: their
+        // phases (TMEM read, exponentials, exchange, stores) then overlap instead of adding up.  Inside a group
+        // PARTS warps share a TMEM lane quadrant, each takes 1/PARTS of the CTA's columns.
+        constexpr int GROUPS = NBUF, PARTS = 4 / GROUPS;
         const int ew = warp - 2;
-        const int q = warp & 3, hh = ew >> 2;                  // hh: which quarter of the chunks
+        const int q = warp & 3, grp = (ew >> 2) / PARTS, hh = (ew >> 2) % PARTS;
+        const bool leader = (ew == grp * PARTS * 4) && lane == 0;
         const int row = q * 32 + lane;
         const int ncb = a.S * 2;                               // 32-column chunks of this CTA
-        const int cb_lo = (ncb * hh) >> 2, cb_hi = (ncb * (hh + 1)) >> 2;
+        const int cb_lo = (ncb * hh) / PARTS, cb_hi = (ncb * (hh + 1)) / PARTS;
         unsigned char* tile = smem + C::STG_OFF + ew * 4096;
         const uint32_t my_part = g_smem_u32(&s_part[j * 128 + row]);
-        for (int it = 0; it < n_my; ++it) {
+        float2* lp_grp = s_lp + grp * PARTS * 128;
+        for (int it = grp; it < n_my; it += GROUPS) {
             const int b = it % NBUF, k = it / NBUF, par = it & 1;
             const int m0 = ((int)blockIdx.y + it * (int)gridDim.y) * 128;
             const uint32_t trow = tmem + (uint32_t)(b * TC) + ((uint32_t)(q * 32) << 16);
-            if (warp == 2 && lane == 0) g_mbar_expect_tx(pfull0 + 8 * par, (uint32_t)a.C * 128 * 8);
+            if (leader) g_mbar_expect_tx(pfull0 + 8 * par, (uint32_t)a.C * 128 * 8);
             long long tq = (tr && threadIdx.x == 64) ? clock64() : 0;
             g_mbar_wait(tfull0 + 8 * b, (uint32_t)(k & 1));
             tc_fence_after();
@@ -1240,20 +1247,20 @@ out_lsm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
             // ---- the four warps of a lane quadrant merge their partial {max, sum}; the merged pair goes to every CTA
             //      of the cluster (the four warps share the peers) ----
             {
-                s_lp[hh * 128 + row] = make_float2(mx, sum);
-                asm volatile("bar.sync %0, 128;" ::"r"(q + 1) : "memory");
+                lp_grp[hh * 128 + row] = make_float2(mx, sum);
+                asm volatile("bar.sync %0, %1;" ::"r"(1 + grp * 4 + q), "n"(32 * PARTS) : "memory");
                 float gm = -INFINITY;
 #pragma unroll
-                for (int p = 0; p < 4; ++p) gm = fmaxf(gm, s_lp[p * 128 + row].x);
+                for (int p = 0; p < PARTS; ++p) gm = fmaxf(gm, lp_grp[p * 128 + row].x);
                 float gs = 0.f;
 #pragma unroll
-                for (int p = 0; p < 4; ++p) {
-                    const float2 e = s_lp[p * 128 + row];
+                for (int p = 0; p < PARTS; ++p) {
+                    const float2 e = lp_grp[p * 128 + row];
                     gs += e.y * ex2_fast((e.x - gm) * OUT_L2E);
                 }
                 const uint32_t slot = my_part + (uint32_t)(par * 8 * 128 * 8);
                 const uint64_t pv = ((uint64_t)__float_as_uint(gs) << 32) | (uint64_t)__float_as_uint(gm);
-                for (int peer = hh; peer < a.C; peer += 4)
+                for (int peer = hh; peer < a.C; peer += PARTS)
                     asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b64 [%0], %1, [%2];" ::"r"(
                                      out_mapa(slot, peer)),
                                  "l"(pv), "r"(out_mapa(pfull0 + 8 * par, peer))
@@ -1306,7 +1313,7 @@ out_lsm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
     if (tr && lane == 0) {
         if (warp == 0) tr[0] = t_acc0;
         if (warp == 1) { tr[1] = t_acc0; tr[2] = t_acc1; tr[9] = clock64() - t_begin; }
-        if (warp == 2) { tr[3] = t_acc0; tr[4] = t_acc1; tr[5] = t_acc2; tr[6] = t_acc3; tr[7] = clock64() - t_begin; tr[8] = n_my; }
+        if (warp == 2) { tr[3] = t_acc0; tr[4] = t_acc1; tr[5] = t_acc2; tr[6] = t_acc3; tr[7] = clock64() - t_begin; tr[8] = (n_my + NBUF - 1) / NBUF; }
     }
     tc_fence_before();
     __syncthreads();
