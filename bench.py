@@ -26,12 +26,24 @@ import torch  # noqa: E402
 
 D_FEA, N_PDF, N_MONO = 40, 1944, 48
 LAYERS, HID = 4, 550
+DROP, CONFIG = '0.2', 'timit'
+
+
+def select_config(name):
+    """timit = BASELINE configs[1] (the headline workload); libri = configs[3]: 5x1024 HCGS LSTM, 3480 pdfs, single
+    cd head, no dropout (cfg/LibriSpeech_CGS/libri_LSTM_fmllr_460.cfg:93-94, 157-160; BN on)."""
+    global N_PDF, N_MONO, LAYERS, HID, DROP, CONFIG, MODEL
+    CONFIG = name
+    if name == 'libri':
+        N_PDF, N_MONO, LAYERS, HID, DROP = 3480, 0, 5, 1024, '0.0'
+        MODEL = ['out_dnn1=compute(LSTM_layers,fbank)', 'out_dnn2=compute(MLP_layers,out_dnn1)',
+                 'loss_final=cost_nll(out_dnn2,lab_cd)', 'err_final=cost_err(out_dnn2,lab_cd)']
 
 
 def cfg_sections(to_do='train', precision='bf16'):
     lay = ','.join([str(HID)] * LAYERS)
     rep = lambda v: ','.join([v] * LAYERS)  # noqa: E731
-    lstm = dict(arch_name='LSTM_layers', lstm_lay=lay, lstm_drop=rep('0.2'), lstm_use_laynorm_inp='False',
+    lstm = dict(arch_name='LSTM_layers', lstm_lay=lay, lstm_drop=rep(DROP), lstm_use_laynorm_inp='False',
                 lstm_use_batchnorm_inp='False', lstm_use_laynorm=rep('False'), lstm_use_batchnorm=rep('True'),
                 lstm_bidir='False', lstm_act=rep('tanh'), if_hsigmoid='True', lstm_orthinit='True', arch_lr='0.0016',
                 arch_opt='rmsprop', opt_momentum='0.0', opt_alpha='0.95', opt_eps='1e-8', opt_centered='False',
@@ -47,7 +59,7 @@ def cfg_sections(to_do='train', precision='bf16'):
                apply_guided_hcgs='False', hcgs_block='64,4', hcgs_sparse='50,25', mlp_quant='False', param_quant='8',
                mlp_quant_inp='False', inp_quant='16', mlp_prune='False', mlp_prune_perc='70',
                skip_regularization='True', to_do=to_do, use_cuda='True', b200_precision=precision)
-    mono = dict(mlp, arch_name='MLP_layers2', dnn_lay=str(N_MONO), mlp_hcgs='False', arch_lr='0.0004')
+    mono = dict(mlp, arch_name='MLP_layers2', dnn_lay=str(max(N_MONO, 1)), mlp_hcgs='False', arch_lr='0.0004')
     return lstm, mlp, mono
 
 
@@ -69,7 +81,7 @@ def synthetic_minibatch(T, B, seed):
         left = int(torch.randint(0, T - n + 1, (1,), generator=g))
         inp[left:left + n, b, :D_FEA] = torch.randn(n, D_FEA, generator=g)
         inp[left:left + n, b, D_FEA] = torch.randint(0, N_PDF, (n,), generator=g).float()
-        inp[left:left + n, b, D_FEA + 1] = torch.randint(0, N_MONO, (n,), generator=g).float()
+        inp[left:left + n, b, D_FEA + 1] = torch.randint(0, max(N_MONO, 1), (n,), generator=g).float()
         frames += n
     return inp, frames
 
@@ -133,13 +145,15 @@ def build_workload(device, seed=2234, precision='bf16'):
     s_lstm, s_cd, s_mono = cfg_sections('train', precision)
     lstm = nb.LSTM(s_lstm, D_FEA)
     cd = nb.MLP(s_cd, lstm.out_dim)
-    mono = nb.MLP(s_mono, lstm.out_dim)
-    nets = {'LSTM_layers': lstm, 'MLP_layers': cd, 'MLP_layers2': mono}
+    nets = {'LSTM_layers': lstm, 'MLP_layers': cd}
+    if N_MONO:
+        nets['MLP_layers2'] = nb.MLP(s_mono, lstm.out_dim)
     for n in nets.values():
         n.to(device).train()
     graph = Graph(MODEL, nets, {'LSTM_layers': True, 'MLP_layers': False, 'MLP_layers2': False},
                   {'fbank': (0, D_FEA)}, {'lab_cd': D_FEA, 'lab_mono': D_FEA + 1})
-    opts = {k: make_optimizer(nets[k], s) for k, s in zip(nets, (s_lstm, s_cd, s_mono))}
+    opts = {k: make_optimizer(nets[k], s) for k, s in zip(('LSTM_layers', 'MLP_layers', 'MLP_layers2'),
+                                                          (s_lstm, s_cd, s_mono)) if k in nets}
     return nets, graph, opts
 
 
@@ -436,8 +450,12 @@ def run_reference_arm(args, rank):
 
 
 def workload_config(args, T, B):
-    return {'workload': 'TIMIT_CGS LSTM train step: 40-dim fbank -> 4x550 HCGS LSTM (32,4 / 75,62.5 masks, BN, tanh, '
-                        'drop 0.2) -> 1944-pdf (64,4 / 50,25) + 48-mono softmax heads, NLL, RMSprop',
+    wl = ('TIMIT_CGS LSTM train step: 40-dim fbank -> 4x550 HCGS LSTM (32,4 / 75,62.5 masks, BN, tanh, '
+          'drop 0.2) -> 1944-pdf (64,4 / 50,25) + 48-mono softmax heads, NLL, RMSprop')
+    if CONFIG == 'libri':
+        wl = ('LibriSpeech_CGS LSTM train step: 40-dim fbank -> 5x1024 HCGS LSTM (32,4 / 75,62.5 masks, BN, tanh, '
+              'no dropout) -> 3480-pdf head (64,4 / 50,25), NLL, RMSprop')
+    return {'workload': wl,
             'precision': getattr(args, 'precision', 'bf16') if getattr(args, 'impl', 'b200') == 'b200' else 'fp32',
             'seq_len': T, 'batch_per_gpu': B, 'frames_counted': 'real (unpadded) frames',
             'parallelism': 'dp%d' % args.gpus,
@@ -465,7 +483,12 @@ def main():
                     help='bf16 = tensor-core build (BASELINE configs[1] "bf16 train"), fp32 = CUDA-core parity build')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-export', action='store_true', help='skip the posterior-export measurement')
+    ap.add_argument('--config', default='timit', choices=['timit', 'libri'],
+                    help='timit = BASELINE configs[1] (headline); libri = configs[3], 5x1024 / 3480 pdfs (no CPU leg)')
     args = ap.parse_args()
+    select_config(args.config)
+    if args.config != 'timit':
+        args.no_cpu_baseline = True
 
     from b200 import dist as bdist
     if args.impl == 'reference':
