@@ -78,6 +78,16 @@ def quantize_w_t(w, bits):
     return _ste(w, q)
 
 
+def prune_t(w, perc):
+    """quantized_modules.prune (:15-28) on one weight matrix: threshold = np.percentile(|w|, perc) (float64, linear
+    interpolation), mask = |w| > threshold; the reference multiplies the mask into weight.data (the gradient
+    stays dense)."""
+    import numpy as np
+    thr = np.percentile(w.detach().abs().numpy().flatten(), perc)
+    mask = (w.detach().abs() > thr).float()
+    return _ste(w, w.detach() * mask) if w.requires_grad else w * mask, mask
+
+
 def quantize_inp_t(x, bits, repeat=1):
     """Quantize_inp (quantized_modules.py:99-119) applied `repeat` times; STE."""
     v = x.detach()
@@ -109,6 +119,9 @@ def lstm_forward(p, spec, x, drop_masks, training):
             if spec.get('hcgs', False):
                 w[g] = w[g] * p['hcgsx.%d.mask' % i]                      # :858-861
                 u[g] = u[g] * p['hcgsh.%d.mask' % i]                      # :980-983
+            if spec.get('prune', 0):                                      # :887-896, 997-1005
+                w[g] = w[g] * prune_t(w[g], spec['prune'])[1]
+                u[g] = u[g] * prune_t(u[g], spec['prune'])[1]
             if spec.get('quant', 0):
                 w[g] = quantize_w_t(w[g], spec['quant'])
                 u[g] = quantize_w_t(u[g], spec['quant'])
@@ -149,6 +162,8 @@ def mlp_forward(p, spec, x, training, drop_masks=None):
         b = p['wx.%d.bias' % i]
         if spec.get('hcgs', False):
             w = w * p['hcgs.%d.mask' % i]                                 # :258
+        if spec.get('prune', 0):                                          # :275-277
+            w = w * prune_t(w, spec['prune'])[1]
         if spec.get('quant', 0):
             w = quantize_w_t(w, spec['quant'])
         if spec.get('quant_inp', 0):

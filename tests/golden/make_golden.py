@@ -229,6 +229,16 @@ def gen_quant():
     print('quant.npz')
 
 
+def gen_quant_inp():
+    """The shipped QuantExp configuration (cfg/20200910_QuantExp/...whcgs.cfg:166-171, 202-207): 8-bit weights,
+    16-bit activations (Quantize_inp of the layer input AND of h_t at every time step), magnitude pruning 70."""
+    run_model('train_quant_inp', 'train', T=6, B=3, D=12,
+              lstm_over=dict(lstm_quant='True', lstm_quant_inp='True', lstm_prune='True', lstm_prune_perc='70,70',
+                             lstm_lay='24,24'),
+              mlp_over=dict(mlp_quant='True', mlp_quant_inp='True', mlp_prune='True', mlp_prune_perc='70'),
+              steps=1, seed=6)
+
+
 if __name__ == '__main__':
     gen_masks()
     run_model('train_small', 'train', steps=2)
@@ -239,3 +249,4 @@ if __name__ == '__main__':
     gen_quant()
     run_model('train_quant', 'train', lstm_over=dict(lstm_quant='True', lstm_lay='24,24'),
               mlp_over=dict(mlp_quant='True'), steps=1, seed=5)
+    gen_quant_inp()

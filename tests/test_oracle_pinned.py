@@ -124,12 +124,12 @@ def _params(g, stage, net):
     return {k[len(pre):]: torch.from_numpy(g[k].copy()) for k in g.files if k.startswith(pre)}
 
 
-def golden_specs(lstm_over=None, quant=False):
-    lstm = dict(lay=[24, 24], act=['tanh', 'tanh'], use_bn=[True, True], drop=[0.2, 0.2], hcgs=True,
-                quant=8 if quant else 0, quant_inp=0)
+def golden_specs(lstm_over=None, quant=False, quant_inp=0, prune=0):
+    q = dict(quant=8 if quant else 0, quant_inp=quant_inp, prune=prune)
+    lstm = dict(lay=[24, 24], act=['tanh', 'tanh'], use_bn=[True, True], drop=[0.2, 0.2], hcgs=True, **q)
     lstm.update(lstm_over or {})
-    cd = dict(lay=[10], act=['softmax'], use_bn=[False], drop=[0.0], hcgs=True, quant=8 if quant else 0, quant_inp=0)
-    mono = dict(lay=[5], act=['softmax'], use_bn=[False], drop=[0.0], hcgs=False, quant=8 if quant else 0, quant_inp=0)
+    cd = dict(lay=[10], act=['softmax'], use_bn=[False], drop=[0.0], hcgs=True, **q)
+    mono = dict(lay=[5], act=['softmax'], use_bn=[False], drop=[0.0], hcgs=False, **q)
     return {'lstm': lstm, 'cd': cd, 'mono': mono}
 
 
@@ -222,6 +222,31 @@ def test_oracle_quantised_train_matches_reference():
     for n in ('ufh.0.weight', 'wcx.1.weight'):
         mask = params['lstm'][('hcgsx.%s.mask' if n[0] == 'w' else 'hcgsh.%s.mask') % n.split('.')[1]].detach().numpy()
         np.testing.assert_allclose(grads['lstm'][n].numpy(), g['grad/LSTM_layers/' + n] * mask, rtol=3e-4, atol=1e-7)
+
+
+def test_oracle_quantised_activations_and_pruning_match_reference():
+    """The shipped QuantExp configuration: 8-bit weights, 16-bit Quantize_inp of every layer input and of h_t at
+    every time step (the stacked output holds the quantised h for all steps but the last), magnitude pruning 70."""
+    g = _load('train_quant_inp')
+    specs = golden_specs(quant=True, quant_inp=16, prune=70)
+    params, outs = _run_oracle_train(g, specs, 1)
+    out, grads = outs[0]
+    ref_loss = g['loss/0']
+    assert abs(out['loss_final'].item() - ref_loss[0]) <= 2e-6 * abs(ref_loss[0])
+    np.testing.assert_allclose(out['out_dnn2'].detach().numpy(), g['out_dnn2/0'], rtol=1e-5, atol=2e-6)
+    # the reference's gradients are dense; the oracle (like the product) carries the masks in the graph, so the
+    # comparison is on the kept entries: HCGS mask x pruning mask of the initial weights
+    def kept(net, n, hmask):
+        w0 = torch.from_numpy(g['init/%s/%s' % (net, n)]) * hmask
+        return (hmask * model_oracle.prune_t(w0, 70)[1]).numpy()
+    for n in ('ufh.0.weight', 'wcx.1.weight'):
+        hm = params['lstm'][('hcgsx.%s.mask' if n[0] == 'w' else 'hcgsh.%s.mask') % n.split('.')[1]].detach()
+        m = kept('LSTM_layers', n, hm)
+        assert 0 < m.sum() < m.size
+        np.testing.assert_allclose(grads['lstm'][n].numpy() * m, g['grad/LSTM_layers/' + n] * m, rtol=3e-4, atol=2e-6)
+    m = kept('MLP_layers', 'wx.0.weight', params['cd']['hcgs.0.mask'].detach())
+    np.testing.assert_allclose(grads['cd']['wx.0.weight'].numpy() * m, g['grad/MLP_layers/wx.0.weight'] * m,
+                               rtol=3e-4, atol=2e-4 * np.abs(g['grad/MLP_layers/wx.0.weight']).max())
 
 
 @pytest.mark.parametrize('name', ['valid_small', 'eval_forward'])
