@@ -34,6 +34,7 @@ class LayerRuntime:
         # quantised weights, the gradient lands on the fp32 master -- straight-through)
         self.q_ws = None
         self.q_us = None
+        self.act_bits = 0         # > 0: per-step Quantize_inp of h_t inside the recurrence (lstm_quant_inp)
         # tensor-core build: bf16 copy of the layer input handed over by the previous layer, and of
         # this layer's output for the next one (saves a cast pass per layer)
         self.xb_in = None
@@ -82,7 +83,8 @@ class LSTMLayerFunction(torch.autograd.Function):
         if need_grad:
             c = torch.empty(T, B, H, device=dev, dtype=torch.float32)
             gates = torch.empty(T, B, 4 * H, device=dev, dtype=torch.float32)
-        native.lstm_fwd(plan, fwd_pack, pre.view(T, B, 4 * H), rt.drop, rt.drop_scalar, rt.act, h, c, gates)
+        native.lstm_fwd(plan, fwd_pack, pre.view(T, B, 4 * H), rt.drop, rt.drop_scalar, rt.act, h, c, gates,
+                        act_bits=rt.act_bits)
         if need_grad:
             ctx.rt = rt
             ctx.dims = (T, B, D, H)

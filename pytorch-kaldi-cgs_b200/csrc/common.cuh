@@ -157,6 +157,16 @@ __device__ __forceinline__ float act_grad_from_out(int act, float y) {
     }
 }
 
+// one application of Quantize_inp to an element, given the tensor's max |x| (quantized_modules.py:109-118):
+// inp.div(var).abs().mul(2^(B-1)).ceil().div(2^(B-1)).mul(var) * sign
+__device__ __forceinline__ float quant_act_once(float v, float var, float scale, float inv_scale) {
+    const float sgn = (v > 0.f) ? 1.f : ((v < 0.f) ? -1.f : 0.f);
+    float t = v / var;
+    t = ceilf(fabsf(t) * scale) * inv_scale;
+    t = t * var;
+    return t * sgn;
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

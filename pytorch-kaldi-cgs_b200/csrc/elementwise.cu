@@ -39,15 +39,6 @@ __global__ void absmax_kernel(const float* __restrict__ x, int ldx, int64_t rows
     if ((threadIdx.x & 31) == 0) atomicMax(out_bits, __float_as_uint(m));  // non-negative floats order as uints
 }
 
-__device__ __forceinline__ float quant_act_once(float v, float var, float scale, float inv_scale) {
-    // inp.div(var).abs().mul(2^(B-1)).ceil().div(2^(B-1)).mul(var) * sign   (quantized_modules.py:109-118)
-    const float sgn = (v > 0.f) ? 1.f : ((v < 0.f) ? -1.f : 0.f);
-    float t = v / var;
-    t = ceilf(fabsf(t) * scale) * inv_scale;
-    t = t * var;
-    return t * sgn;
-}
-
 __global__ void quantize_act_kernel(const float* __restrict__ x, int ldx, float* __restrict__ y, int ldy,
                                     int64_t rows, int cols, float scale, float inv_scale, int repeat,
                                     const unsigned int* __restrict__ max_bits) {

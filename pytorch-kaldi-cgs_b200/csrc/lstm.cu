@@ -67,6 +67,7 @@ struct LstmFwdArgs {
     float* c_out;
     float* gates_out;
     int T, B, H, CL, Hc, HcP, RG, L, NCG, act, w_in_smem;
+    int act_bits;  // > 0: Quantize_inp of h_{k-1} before the four recurrent products of step k (whole batch in ONE cluster)
 };
 
 __global__ void __launch_bounds__(512) lstm_fwd_kernel(const LstmFwdArgs a) {
@@ -139,9 +140,37 @@ __global__ void __launch_bounds__(512) lstm_fwd_kernel(const LstmFwdArgs a) {
     }
     const int chunks = Hc * NB / 4;  // float4 chunks of one h slice
 
+    __shared__ float q_red[16];
+    const float q_scale = (float)(1 << (a.act_bits > 0 ? a.act_bits - 1 : 0)), q_inv = 1.0f / q_scale;
+
     for (int k = 0; k < a.T; ++k) {
         const int cur = k & 1, nxt = cur ^ 1;
         const float* hc = hbuf + (size_t)cur * H4 * NB;
+        if (a.act_bits > 0 && k > 0) {
+            // QuantizeLinear(if_inp_quant) on h_{k-1}: u{f,i,o,c}h each replace ht.data by Quantize_inp(ht.data)
+            // (quantized_modules.py:212-219, neural_networks.py:1077-1088): scale = max |h| over the WHOLE [B,H]
+            // tensor (this cluster holds the whole batch), four applications in a row.  The tensor object that was
+            // appended to the output list is the one that gets swapped, so h_out[k-1] becomes the quantised copy.
+            float* hq = hbuf + (size_t)cur * H4 * NB;
+            float m = 0.f;
+            for (int i = t; i < H4 * NB; i += nthreads) m = fmaxf(m, fabsf(hq[i]));
+            m = warp_max(m);
+            if ((t & 31) == 0) q_red[t >> 5] = m;
+            __syncthreads();
+            float var = 0.f;
+            for (int w = 0; w < (nthreads + 31) / 32; ++w) var = fmaxf(var, q_red[w]);
+            if (var != 0.f) {
+                for (int i = t; i < H4 * NB; i += nthreads) {
+                    float v = hq[i];
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) v = quant_act_once(v, var, q_scale, q_inv);
+                    hq[i] = v;
+                    const int u = i / NB, b = i - u * NB;
+                    if (u >= u0 && u < u0 + nu && b < nb) a.h_out[((size_t)(k - 1) * a.B + b0 + b) * H + u] = v;
+                }
+            }
+            __syncthreads();
+        }
         // ---- U h_{k-1} for my rows ---------------------------------------------------------
         if (mv) {
             float acc0[4] = {0.f, 0.f, 0.f, 0.f}, acc1[4] = {0.f, 0.f, 0.f, 0.f};
@@ -504,7 +533,10 @@ extern "C" int hcgs_lstm_fwd(const hcgs_plan* plan, const float* fwd_pack, const
                              float* gates_out, int act_bits, hcgs_stream stream) {
     HCGS_REQUIRE(plan && plan->recurrent, "hcgs_lstm_fwd: needs a recurrent plan");
     HCGS_REQUIRE(fwd_pack && pre && h_out, "hcgs_lstm_fwd: NULL argument");
-    HCGS_REQUIRE(act_bits == 0, "hcgs_lstm_fwd: activation quantisation inside the recurrence is not built yet");
+    HCGS_REQUIRE(act_bits >= 0 && act_bits <= 24, "hcgs_lstm_fwd: act_bits out of range");
+    HCGS_REQUIRE(act_bits == 0 || batch <= NB,
+                 "hcgs_lstm_fwd: Quantize_inp of h_t scales by the max over the WHOLE batch; that is built for a batch that "
+                 "fits one cluster (<= %d sequences, the cfg batch size), got %d", NB, batch);
     if (t_len <= 0 || batch <= 0) return 0;
     const RecurrentPlan& rp = plan->rp;
     HCGS_REQUIRE(rp.Hc * NB <= IPT * rp.threads, "hcgs_lstm_fwd: internal sizing error");
@@ -528,6 +560,7 @@ extern "C" int hcgs_lstm_fwd(const hcgs_plan* plan, const float* fwd_pack, const
     a.NCG = rp.NCG;
     a.act = act;
     a.w_in_smem = rp.w_in_smem ? 1 : 0;
+    a.act_bits = act_bits;
     const int n_clusters = (batch + NB - 1) / NB;
     return launch_cluster(lstm_fwd_kernel, a, n_clusters, rp.CL, rp.threads, rp.smem_fwd, (cudaStream_t)stream);
 }

@@ -667,8 +667,14 @@ class LSTM(nn.Module):
                     rt.q_ws = self._quant_weights('w', i)
                     rt.q_us = self._quant_weights('u', i)
                     if self.lstm_quant_inp:
-                        raise NotImplementedError(
-                            'lstm_quant_inp (per-step Quantize_inp of h_t inside the recurrence) is not built yet')
+                        if _precision(self) == 'bf16':
+                            raise NotImplementedError('lstm_quant_inp is built for b200_precision = fp32 only')
+                        # w{f,i,o,c}x(x): each QuantizeLinear swaps x.data for Quantize_inp(x.data) (four times in a
+                        # row, quantized_modules.py:212-219); u{f,i,o,c}h(ht) does the same to h_t at every time step,
+                        # which the recurrent kernel applies itself (LayerRuntime.act_bits)
+                        lin0 = self.wfx[i]
+                        x.data = Quantize_inp(x.data, lin0.inp_quant, lin0.if_forward, repeat=4)
+                        rt.act_bits = int(lin0.inp_quant)
             ws = [self.wfx[i].weight, self.wix[i].weight, self.wox[i].weight, self.wcx[i].weight]
             us = [self.ufh[i].weight, self.uih[i].weight, self.uoh[i].weight, self.uch[i].weight]
             if rt.use_bn and not rt.training and torch.is_grad_enabled() and ws[0].requires_grad:

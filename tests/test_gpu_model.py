@@ -268,3 +268,36 @@ def test_quantised_weights_train_step_matches_reference_fixture():
         i = int(k.split('.')[1])
         mask = (lstm.hcgsx if k[0] == 'w' else lstm.hcgsh)[i].mask.detach().cpu()
         close(dict(lstm.named_parameters())[k].grad, torch.from_numpy(g['grad/LSTM_layers/' + k]) * mask, 1e-4, k)
+
+
+def test_quantised_activations_and_pruning_train_step_matches_reference_fixture():
+    """BASELINE configs[2], the shipped QuantExp semantics (cfg/20200910_QuantExp/...whcgs.cfg:166-171, 202-207):
+    8-bit weights, 16-bit Quantize_inp of every layer input and of h_t at EVERY time step (inside the recurrent
+    kernel; the stacked output carries the quantised h for all steps but the last), magnitude pruning 70."""
+    from oracle import model_oracle
+    g = load_golden('train_quant_inp')
+    T, B, D, _ = [int(v) for v in g['dims']]
+    lo = dict(lstm_quant='True', lstm_quant_inp='True', lstm_prune='True', lstm_prune_perc='70,70')
+    mo = dict(mlp_quant='True', mlp_quant_inp='True', mlp_prune='True', mlp_prune_perc='70')
+    nets, _ = build_product_nets('train', seed=6, lstm_over=lo, mlp_over=mo, device='cuda')
+    for n, net in nets.items():
+        net.load_state_dict(golden_state(g, 'init', n))
+    graph = make_graph(nets, D)
+    drops = [torch.from_numpy(g['drop/%d' % i]) for i in range(2)]
+    with _ReplayBernoulli(drops):
+        out = graph.forward(torch.from_numpy(g['inp/0']).cuda(), T, B, 'train', ['out_dnn2'])
+    out['loss_final'].backward()
+    assert abs(out['loss_final'].item() - g['loss/0'][0]) <= 1e-5 * abs(g['loss/0'][0])
+    close(out['out_dnn2'], g['out_dnn2/0'], 1e-5, 'out_dnn2 (8-bit weights, 16-bit activations, prune 70)')
+    lstm = nets['LSTM_layers']
+    for k in ('ufh.0.weight', 'wcx.1.weight', 'uoh.1.weight'):
+        i = int(k.split('.')[1])
+        hm = (lstm.hcgsx if k[0] == 'w' else lstm.hcgsh)[i].mask.detach().cpu()
+        w0 = torch.from_numpy(g['init/LSTM_layers/' + k]) * hm
+        m = hm * model_oracle.prune_t(w0, 70)[1]
+        close(dict(lstm.named_parameters())[k].grad.cpu() * m, torch.from_numpy(g['grad/LSTM_layers/' + k]) * m, 2e-4, k)
+    # a batch that does not fit one cluster cannot take the whole-tensor scale of Quantize_inp: loud error
+    from b200 import native
+    big = torch.zeros(T, 9, D + 2).cuda()
+    with pytest.raises(native.NativeError):
+        graph.forward(big, T, 9, 'train', ['out_dnn2'])
