@@ -526,6 +526,18 @@ def main():
     # CUDA events -- 8 launches per step; the full per-kernel table comes from a second, untimed pass.
     for s in range(W):
         train_step(graph, opts, resident[s % n_batches], T, B, bucket)
+    # untimed pass with every native entry point bracketed: the per-kernel table of the report.  It runs BEFORE the
+    # timed region (it also lets the caching allocator reach its steady state: with 3 warm-up steps alone the first
+    # timed steps still paid cudaMalloc calls, 32.6 vs 30.4 ms per step)
+    full = KernelTimers()
+    full.on = True
+    for s in range(min(args.steps, 10)):
+        train_step(graph, opts, resident[s % n_batches], T, B, bucket)
+    sync_all()
+    full.on = False
+    ftot, fcnt, fwork = full.summary()
+    full_steps = min(args.steps, 10)
+    full.restore()
     rec = ['lstm_tc_fwd', 'lstm_tc_bwd'] if args.precision == 'bf16' else ['lstm_fwd', 'lstm_bwd']
     timers = KernelTimers(rec)
     sampler = ClockSampler(local)
@@ -547,15 +559,6 @@ def main():
     ms_total = e0.elapsed_time(e1)
     ktot, kcnt, kwork = timers.summary()
     timers.restore()
-    # untimed pass with every native entry point bracketed: the per-kernel table of the report
-    full = KernelTimers()
-    full.on = True
-    for s in range(args.steps):
-        train_step(graph, opts, resident[s % n_batches], T, B, bucket)
-    sync_all()
-    full.on = False
-    ftot, fcnt, fwork = full.summary()
-    full.restore()
 
     # ---- end to end through the public API: pinned host minibatch -> GPU -> loss on the host ------
     # Every step copies its minibatch from pinned host memory and its loss back to the host inside the timed
@@ -655,7 +658,7 @@ def main():
     roof['traffic'] = float(traffic) if isinstance(traffic, (int, float)) else None
     per_kernel = {}
     for k in sorted(ftot, key=lambda x: -ftot[x]):
-        e = {'ms_per_step': round(ftot[k] / args.steps, 4), 'launches_per_step': fcnt[k] / args.steps}
+        e = {'ms_per_step': round(ftot[k] / full_steps, 4), 'launches_per_step': fcnt[k] / full_steps}
         if k in fwork:
             e['GB_per_s'] = round(fwork[k][0] / (ftot[k] * 1e-3) / 1e9, 1)
             e['TFLOP_per_s'] = round(fwork[k][1] / (ftot[k] * 1e-3) / 1e12, 2)
