@@ -1050,6 +1050,12 @@ __device__ __forceinline__ void out_store_chunk(const float (&v)[32], const OutA
     }
 }
 
+__device__ __forceinline__ bool out_elect_one() {
+    uint32_t p;
+    asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(p));
+    return p != 0;
+}
+
 template <int TC>
 __global__ void __launch_bounds__(OUT_THREADS, 1)
 out_lsm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmOut, const OutArgs a) {
@@ -1068,6 +1074,7 @@ out_lsm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
     float2* s_part = reinterpret_cast<float2*>(smem + C::PART_OFF);
     unsigned char* ring = smem + C::RING_OFF;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp_u = __shfl_sync(0xffffffffu, warp, 0);  // the same value, provably warp-uniform for the compiler
     const int j = blockIdx.x;  // slice of the output columns = rank in the cluster (grid.x == cluster.x == C)
     const int i0 = a.slice_ptr[j], ni = a.slice_ptr[j + 1] - i0;
     const int NC = a.S * 64, col_base = j * NC;
@@ -1137,47 +1144,56 @@ out_lsm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
                 }
             }
         }
-    } else if (warp == 1) {
-        if (lane == 0) {
-            int g = 0;
-            const uint64_t desc0 = umma_smem_desc(g_smem_u32(ring), 16, 512, UMMA_SW64);
-            const int nb = ni > 0 ? s_items[0].w : 0;  // strips per item (the same for every item of this CTA)
-            const uint32_t idesc_lo = umma_idesc_bf16(128, 64 * (nb < 4 ? nb : 4), 0, 0);
-            const uint32_t idesc_hi = umma_idesc_bf16(128, nb > 4 ? 64 * (nb - 4) : 64, 0, 0);
-            for (int it = 0; it < n_my; ++it) {
-                const int b = it % NBUF, k = it / NBUF;
-                const long long tq0 = tr ? clock64() : 0;
-                if (k >= 1) {
-                    g_mbar_wait(tempty0 + 8 * b, (uint32_t)((k - 1) & 1));
-                    tc_fence_after();
-                }
-                if (tr) t_acc0 += clock64() - tq0;
-                const uint32_t acc = tmem + (uint32_t)(b * TC);
-                for (int i = 0; i < ni; ++i, ++g) {
-                    const int s = g % ST;
-                    const long long tq1 = tr ? clock64() : 0;
-                    g_mbar_wait(full0 + 8 * s, (uint32_t)((g / ST) & 1));
-                    tc_fence_after();
-                    if (tr) t_acc1 += clock64() - tq1;
-                    // descriptors differ only in the start-address field (bits 0..13, address >> 4); one item
-                    // multiplies all nb strips of the CTA at once: N = 64 * nb (two instructions when nb > 4)
-                    const uint64_t ad = desc0 + (uint64_t)((s * C::STAGE) >> 4);
-                    const uint64_t bd = ad + (OUT_A_BYTES >> 4);
-                    const uint32_t accf = i > 0 ? 1u : 0u;
-                    if (nb <= 4) {
-                        umma_bf16(acc, ad, bd, idesc_lo, accf);
-                        umma_bf16(acc, ad + 2, bd + 2, idesc_lo, 1u);
-                    } else {
-                        constexpr uint64_t B4 = (4 * OUT_B_TILE) >> 4;
-                        umma_bf16(acc, ad, bd, idesc_lo, accf);
-                        umma_bf16(acc + 256, ad, bd + B4, idesc_hi, accf);
-                        umma_bf16(acc, ad + 2, bd + 2, idesc_lo, 1u);
-                        umma_bf16(acc + 256, ad + 2, bd + B4 + 2, idesc_hi, 1u);
-                    }
-                    umma_commit(empty0 + 8 * s);
-                }
-                umma_commit(tfull0 + 8 * b);  // arrives once every product of this tile has completed
+    } else if (warp_u == 1) {
+        // The whole warp runs this loop convergently on warp-uniform values (warp_u and the TMEM base come from a
+        // shuffle, everything else from loop counters and constants) and ONE elected lane issues: the descriptors
+        // then live in uniform registers.  Issued from a `lane == 0` branch instead, every tcgen05.mma was wrapped in
+        // an ELECT / R2UR.BROADCAST loop by the compiler and cost ~180 cycles of the issuing thread.
+        int g = 0;
+        const uint64_t desc0 = umma_smem_desc(g_smem_u32(ring), 16, 512, UMMA_SW64);
+        const uint32_t idesc0 = umma_idesc_bf16(128, 0, 0, 0);
+        const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem, 0);
+        for (int it = 0; it < n_my; ++it) {
+            const int b = it % NBUF, k = it / NBUF;
+            const long long tq0 = tr ? clock64() : 0;
+            if (k >= 1) {
+                g_mbar_wait(tempty0 + 8 * b, (uint32_t)((k - 1) & 1));
+                tc_fence_after();
             }
+            if (tr) t_acc0 += clock64() - tq0;
+            const uint32_t acc = tmem_u + (uint32_t)(b * TC);
+            for (int i = 0; i < ni; ++i, ++g) {
+                const int s = g % ST;
+                const long long tq1 = tr ? clock64() : 0;
+                g_mbar_wait(full0 + 8 * s, (uint32_t)((g / ST) & 1));
+                tc_fence_after();
+                if (tr) t_acc1 += clock64() - tq1;
+                // descriptors differ only in the start-address field (bits 0..13, address >> 4).  Every run of
+                // adjacent kept strips is one instruction of N = 64 * run (<= 256); the first item of a tile
+                // covers all strips (it initialises the accumulators), so every later one accumulates
+                const uint64_t ad = desc0 + (uint64_t)((s * C::STAGE) >> 4);
+                uint64_t bd = ad + (OUT_A_BYTES >> 4);
+                const uint32_t accf = i > 0 ? 1u : 0u;
+                uint32_t m = __shfl_sync(0xffffffffu, (uint32_t)s_items[i].y, 0);
+                const bool issuer = out_elect_one();
+                while (m) {
+                    const int lo = __ffs(m) - 1;
+                    int len = __ffs(~(m >> lo)) - 1;
+                    len = len > 4 ? 4 : len;
+                    const uint32_t idesc = idesc0 | ((uint32_t)(len * 8) << 17);
+                    const uint32_t d = acc + (uint32_t)(lo * 64);
+                    if (issuer) {
+                        umma_bf16(d, ad, bd, idesc, accf);
+                        umma_bf16(d, ad + 2, bd + 2, idesc, 1u);
+                    }
+                    bd += (uint64_t)len * (OUT_B_TILE >> 4);
+                    m &= ~(((1u << len) - 1u) << lo);
+                }
+                if (issuer) umma_commit(empty0 + 8 * s);
+                __syncwarp();
+            }
+            if (out_elect_one()) umma_commit(tfull0 + 8 * b);  // arrives once every product of this tile has completed
+            __syncwarp();
         }
     } else {
         // ---- epilogue warps: TMEM lane quadrant q (hardware: warp id % 4), column half hh ----

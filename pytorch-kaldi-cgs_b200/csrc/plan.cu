@@ -205,33 +205,39 @@ extern "C" int hcgs_plan_create(const float* mask, int n_out, int n_in, int recu
             std::vector<int> optr(C + 1, 0), oitems, otile;
             for (int j = 0; j < C; ++j) {
                 optr[j] = (int)oitems.size() / 3;
-                // k tiles kept by any strip of this CTA, and the highest strip that keeps anything: every item
-                // multiplies ALL strips 0..hi at once (one wide MMA instead of one per kept strip; the masked
-                // weights inside are zeros) -- the issue rate of the single MMA thread, not the tensor pipe,
-                // bounds this kernel
+                // k tiles kept by any strip of this CTA.  The FIRST item multiplies all strips 0..hi (masked weights
+                // inside are zeros) so that every accumulator strip is initialised by it; the following items carry
+                // only their kept strips, and the kernel multiplies each run of adjacent kept strips with one wide MMA
+                // (the issue rate of the single MMA thread and the bytes streamed per row tile bound this kernel)
                 std::vector<int> kts;
+                std::vector<uint32_t> kms;
                 int hi = -1;
                 for (int kt = 0; kt < p->tc; ++kt) {
-                    bool keep = false;
+                    uint32_t km = 0;
                     for (int s = 0; s < S; ++s)
                         for (int h = 0; h < 2; ++h) {
                             const int trow = (j * S + s) * 2 + h;
                             if (trow < p->tr && nz[(size_t)trow * p->tc + kt]) {
-                                keep = true;
+                                km |= 1u << s;
                                 hi = std::max(hi, s);
                             }
                         }
-                    if (keep) kts.push_back(kt);
+                    if (km) {
+                        kts.push_back(kt);
+                        kms.push_back(km);
+                    }
                 }
                 const uint32_t m = hi < 0 ? 0u : (uint32_t)((1u << (hi + 1)) - 1u);
-                for (int kt : kts) {
-                    oitems.push_back(kt);
-                    oitems.push_back((int)m);
+                for (size_t q = 0; q < kts.size(); ++q) {
+                    const uint32_t im = q == 0 ? m : kms[q];
+                    oitems.push_back(kts[q]);
+                    oitems.push_back((int)im);
                     oitems.push_back((int)otile.size() / 2);
-                    for (int s = 0; s <= hi; ++s) {
-                        otile.push_back(j * S + s);
-                        otile.push_back(kt);
-                    }
+                    for (int s = 0; s <= hi; ++s)
+                        if (im >> s & 1) {
+                            otile.push_back(j * S + s);
+                            otile.push_back(kts[q]);
+                        }
                 }
                 p->out_any[j] = m;
             }
