@@ -66,6 +66,15 @@ __device__ __forceinline__ void bulk_load_1d(uint32_t smem_dst, const void* gsrc
                  : "memory");
 }
 
+// one lane of a CONVERGENT warp.  The MMA-issuing warps below run their loops on warp-uniform values (warp index and
+// loop bounds passed through a shuffle) and let the elected lane issue: the tcgen05 operands then sit in uniform
+// registers.  Issued from a `lane == 0` branch, every tcgen05.mma is wrapped in an ELECT / R2UR.BROADCAST loop.
+__device__ __forceinline__ bool out_elect_one() {
+    uint32_t p;
+    asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(p));
+    return p != 0;
+}
+
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
@@ -273,6 +282,7 @@ __global__ void __launch_bounds__(128) tc_gemm_nt_kernel(const __grid_constant__
     const uint32_t full0 = g_smem_u32(bars), empty0 = g_smem_u32(bars + NT_STAGES),
                    done = g_smem_u32(bars + 2 * NT_STAGES);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp_u = __shfl_sync(0xffffffffu, warp, 0);  // provably warp-uniform copy (see out_elect_one)
     const int r = blockIdx.x;
     const int64_t m0 = (int64_t)blockIdx.y * 128;
     const int k0 = a.row_ptr[r], nk = a.row_ptr[r + 1] - k0;
@@ -302,22 +312,28 @@ __global__ void __launch_bounds__(128) tc_gemm_nt_kernel(const __grid_constant__
                          reinterpret_cast<const unsigned char*>(a.wpack) + (size_t)(k0 + i) * B_BYTES, B_BYTES,
                          full0 + 8 * s);
         }
-    } else if (warp == 1 && lane == 0) {
-        // ---- MMA issuer ------------------------------------------------------------------------
-        for (int i = 0; i < nk; ++i) {
+    } else if (warp_u == 1) {
+        // ---- MMA issuer (convergent warp, elected lane) -----------------------------------------
+        const int nk_u = __shfl_sync(0xffffffffu, nk, 0);
+        const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem, 0);
+        for (int i = 0; i < nk_u; ++i) {
             const int s = i % NT_STAGES;
             g_mbar_wait(full0 + 8 * s, (uint32_t)((i / NT_STAGES) & 1));
             tc_fence_after();
             const uint32_t aaddr = g_smem_u32(sA + s * NT_A_BYTES), baddr = g_smem_u32(sB + s * B_BYTES);
+            if (out_elect_one()) {
 #pragma unroll
-            for (int kk = 0; kk < 2; ++kk) {  // 32 k per stage = 2 x (K = 16); +32 bytes inside the swizzle atom
-                const uint64_t ad = umma_smem_desc(aaddr + kk * 32, 16, 512, UMMA_SW64);
-                const uint64_t bd = umma_smem_desc(baddr + kk * 32, 16, 512, UMMA_SW64);
-                umma_bf16(tmem, ad, bd, IDESC, (i > 0 || kk > 0) ? 1u : 0u);
+                for (int kk = 0; kk < 2; ++kk) {  // 32 k per stage = 2 x (K = 16); +32 bytes inside the swizzle atom
+                    const uint64_t ad = umma_smem_desc(aaddr + kk * 32, 16, 512, UMMA_SW64);
+                    const uint64_t bd = umma_smem_desc(baddr + kk * 32, 16, 512, UMMA_SW64);
+                    umma_bf16(tmem_u, ad, bd, IDESC, (i > 0 || kk > 0) ? 1u : 0u);
+                }
+                umma_commit(empty0 + 8 * s);  // stage reusable once these MMAs have read it
             }
-            umma_commit(empty0 + 8 * s);  // stage reusable once these MMAs have read it
+            __syncwarp();
         }
-        umma_commit(done);
+        if (out_elect_one()) umma_commit(done);
+        __syncwarp();
     }
     // ---- epilogue: TMEM -> registers -> global ------------------------------------------------------
     __syncwarp();
@@ -603,6 +619,7 @@ __global__ void __launch_bounds__(128) tc_gemm_nn_kernel(const __grid_constant__
     const uint32_t full0 = g_smem_u32(bars), empty0 = g_smem_u32(bars + C::STAGES),
                    done = g_smem_u32(bars + 2 * C::STAGES);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp_u = __shfl_sync(0xffffffffu, warp, 0);  // provably warp-uniform copy (see out_elect_one)
     const int c = blockIdx.x;
     const int64_t m0 = (int64_t)blockIdx.y * 128;
     const int k0 = a.col_ptr[c], nk = a.col_ptr[c + 1] - k0;
@@ -635,24 +652,30 @@ __global__ void __launch_bounds__(128) tc_gemm_nn_kernel(const __grid_constant__
                          reinterpret_cast<const unsigned char*>(a.wpack) + (size_t)(k0 + i) * (C::NSUB * C::B_SUB),
                          C::NSUB * C::B_SUB, full0 + 8 * s);
         }
-    } else if (warp == 1 && lane == 0) {
-        for (int i = 0; i < nk; ++i) {
+    } else if (warp_u == 1) {
+        const int nk_u = __shfl_sync(0xffffffffu, nk, 0);
+        const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem, 0);
+        for (int i = 0; i < nk_u; ++i) {
             const int s = i % C::STAGES;
             g_mbar_wait(full0 + 8 * s, (uint32_t)((i / C::STAGES) & 1));
             tc_fence_after();
             const uint32_t base = g_smem_u32(smem + s * C::STAGE);
+            if (out_elect_one()) {
 #pragma unroll
-            for (int h = 0; h < C::NSUB; ++h)
+                for (int h = 0; h < C::NSUB; ++h)
 #pragma unroll
-                for (int kk = 0; kk < C::KCH / 16; ++kk) {
-                    const uint64_t ad = umma_smem_desc(base + h * C::A_SUB + kk * 32, 16, C::SBO, C::SW);
-                    const uint64_t bd =
-                        umma_smem_desc(base + C::NSUB * C::A_SUB + h * C::B_SUB + kk * 32, 16, C::SBO, C::SW);
-                    umma_bf16(tmem, ad, bd, IDESC, (i > 0 || h > 0 || kk > 0) ? 1u : 0u);
-                }
-            umma_commit(empty0 + 8 * s);
+                    for (int kk = 0; kk < C::KCH / 16; ++kk) {
+                        const uint64_t ad = umma_smem_desc(base + h * C::A_SUB + kk * 32, 16, C::SBO, C::SW);
+                        const uint64_t bd =
+                            umma_smem_desc(base + C::NSUB * C::A_SUB + h * C::B_SUB + kk * 32, 16, C::SBO, C::SW);
+                        umma_bf16(tmem_u, ad, bd, IDESC, (i > 0 || h > 0 || kk > 0) ? 1u : 0u);
+                    }
+                umma_commit(empty0 + 8 * s);
+            }
+            __syncwarp();
         }
-        umma_commit(done);
+        if (out_elect_one()) umma_commit(done);
+        __syncwarp();
     }
     __syncwarp();
     float v[32];
@@ -785,6 +808,7 @@ __global__ void __launch_bounds__(128) tc_sddmm_kernel(const __grid_constant__ C
     const uint32_t full0 = g_smem_u32(bars), empty0 = g_smem_u32(bars + SD_STAGES),
                    done = g_smem_u32(bars + 2 * SD_STAGES);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp_u = __shfl_sync(0xffffffffu, warp, 0);  // provably warp-uniform copy (see out_elect_one)
     const int r = a.items[3 * blockIdx.x], t0 = a.items[3 * blockIdx.x + 1], cnt = a.items[3 * blockIdx.x + 2];
     const int64_t mbeg = (int64_t)blockIdx.y * a.rows_per_split;
     const int64_t mend = (mbeg + a.rows_per_split < a.M) ? mbeg + a.rows_per_split : a.M;
@@ -826,26 +850,33 @@ __global__ void __launch_bounds__(128) tc_sddmm_kernel(const __grid_constant__ C
                 if (lane == 12) tma_load_2d(g_smem_u32(st + kSdMaxTiles * SD_A_ATOM), &tmDY, r * 32, row, full0 + 8 * s);
             }
         }
-    } else if (warp == 1 && lane == 0) {
-        for (int i = 0; i < nk; ++i) {
+    } else if (warp_u == 1) {
+        const int nk_u = __shfl_sync(0xffffffffu, nk, 0);
+        const int nmm = (__shfl_sync(0xffffffffu, cnt, 0) + 3) / 4;  // groups of four kept blocks; a partly filled group
+                                            // multiplies stale shared memory into accumulator rows that are never read
+        const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem, 0);
+        for (int i = 0; i < nk_u; ++i) {
             const int s = i % SD_STAGES;
             g_mbar_wait(full0 + 8 * s, (uint32_t)((i / SD_STAGES) & 1));
             tc_fence_after();
             const uint32_t abase = g_smem_u32(smem + s * C::STAGE), bbase = abase + kSdMaxTiles * SD_A_ATOM;
-            const int nmm = (cnt + 3) / 4;  // groups of four kept blocks; a partly filled group multiplies stale
-                                            // shared memory into accumulator rows that are never read
+            if (out_elect_one()) {
 #pragma unroll
-            for (int kk = 0; kk < SD_RK / 16; ++kk) {  // 16 m rows per MMA = two 8-row groups
-                const uint64_t bd = (NG == 4) ? umma_smem_desc(bbase + kk * 2048, SD_RK * 128, 1024, UMMA_SW128)
-                                              : umma_smem_desc(bbase + kk * 1024, SD_A_ATOM, 512, UMMA_SW64);
-                for (int j = 0; j < nmm; ++j) {
-                    const uint64_t ad = umma_smem_desc(abase + j * 4 * SD_A_ATOM + kk * 1024, SD_A_ATOM, 512, UMMA_SW64);
-                    umma_bf16(tmem + (uint32_t)(j * C::BN), ad, bd, IDESC, (i > 0 || kk > 0) ? 1u : 0u);
+                for (int kk = 0; kk < SD_RK / 16; ++kk) {  // 16 m rows per MMA = two 8-row groups
+                    const uint64_t bd = (NG == 4) ? umma_smem_desc(bbase + kk * 2048, SD_RK * 128, 1024, UMMA_SW128)
+                                                  : umma_smem_desc(bbase + kk * 1024, SD_A_ATOM, 512, UMMA_SW64);
+                    for (int j = 0; j < nmm; ++j) {
+                        const uint64_t ad =
+                            umma_smem_desc(abase + j * 4 * SD_A_ATOM + kk * 1024, SD_A_ATOM, 512, UMMA_SW64);
+                        umma_bf16(tmem_u + (uint32_t)(j * C::BN), ad, bd, IDESC, (i > 0 || kk > 0) ? 1u : 0u);
+                    }
                 }
+                umma_commit(empty0 + 8 * s);
             }
-            umma_commit(empty0 + 8 * s);
+            __syncwarp();
         }
-        umma_commit(done);
+        if (out_elect_one()) umma_commit(done);
+        __syncwarp();
     }
     __syncwarp();
     if (nk > 0 && warp < cnt) {
@@ -1048,12 +1079,6 @@ __device__ __forceinline__ void out_store_chunk(const float (&v)[32], const OutA
                 if (i < nv) dst[i] = v[i];
         }
     }
-}
-
-__device__ __forceinline__ bool out_elect_one() {
-    uint32_t p;
-    asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(p));
-    return p != 0;
 }
 
 template <int TC>
