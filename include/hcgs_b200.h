@@ -136,6 +136,18 @@ int hcgs_bn_stats_il(const float* partial, int64_t splits, int64_t rows_per_spli
                      int units, int ld_units, float* const* running_mean, float* const* running_var, float eps,
                      float momentum, int training, float* save_mean, float* save_invstd, hcgs_stream stream);
 
+/* ---- the reference's LayerNorm (neural_networks.py:40-51; NOT nn.LayerNorm) ---------------------
+ * y = gamma * (x - mean) / (std + eps) + beta over the last dimension, std unbiased (n-1).
+ * Used by *_use_laynorm_inp (:825-826, :248-249) and dnn_use_laynorm (:306-314).  save_mean / save_std
+ * ([m], optional, both or none) feed hcgs_layernorm_bwd, which writes dx (optional) and ADDS the column sums
+ * to dgamma / dbeta (caller zero-initialises; either may be NULL).                                       */
+int hcgs_layernorm_fwd(const float* x, int64_t ldx, float* y, int64_t ldy, int64_t m, int n,
+                       const float* gamma, const float* beta, float eps, float* save_mean, float* save_std,
+                       hcgs_stream stream);
+int hcgs_layernorm_bwd(const float* dy, int64_t lddy, const float* x, int64_t ldx, int64_t m, int n,
+                       const float* gamma, float eps, const float* save_mean, const float* save_std, float* dx,
+                       int64_t lddx, float* dgamma, float* dbeta, hcgs_stream stream);
+
 /* ---- persistent recurrent LSTM kernels ------------------------------------------------------
  * hcgs_lstm_pack: gather the four masked U_g [H,H] (ld = ldu) into the plan's compressed
  *   resident layouts (fwd_pack: info[8] floats, bwd_pack: info[9] floats; either may be NULL).

@@ -46,6 +46,102 @@ def _ws(device, n_cols):
     return torch.empty(2 * n_cols * 64, device=device, dtype=torch.float32)
 
 
+class LayerNormFunction(torch.autograd.Function):
+    """The reference's LayerNorm (neural_networks.py:40-51) over the last dimension of any-rank input."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, beta, eps):
+        F = x.shape[-1]
+        x2d = x.reshape(-1, F)
+        if x2d.stride(-1) != 1:
+            x2d = x2d.contiguous()
+        M = x2d.shape[0]
+        y = torch.empty(M, F, device=x.device, dtype=torch.float32)
+        need = any(ctx.needs_input_grad)
+        mean = torch.empty(M, device=x.device, dtype=torch.float32) if need else None
+        std = torch.empty(M, device=x.device, dtype=torch.float32) if need else None
+        native.layernorm_fwd(x2d, y, gamma, beta, eps, mean, std)
+        if need:
+            ctx.eps = eps
+            ctx.shape = x.shape
+            ctx.save_for_backward(x2d, gamma, mean, std)
+        return y.view(x.shape)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2d, gamma, mean, std = ctx.saved_tensors
+        M, F = x2d.shape
+        dy2d = dy.reshape(M, F)
+        if dy2d.stride(-1) != 1:
+            dy2d = dy2d.contiguous()
+        dx = torch.empty(M, F, device=dy.device, dtype=torch.float32) if ctx.needs_input_grad[0] else None
+        dg = torch.zeros(F, device=dy.device, dtype=torch.float32)
+        db = torch.zeros(F, device=dy.device, dtype=torch.float32)
+        native.layernorm_bwd(dy2d, x2d, gamma, ctx.eps, mean, std, dx, dg, db)
+        return (dx.view(ctx.shape) if dx is not None else None), dg, db, None
+
+
+class BatchNormInputFunction(torch.autograd.Function):
+    """nn.BatchNorm1d(momentum=0.05) on the layer input, all rows at once (*_use_batchnorm_inp,
+    neural_networks.py:828-830, 251-252)."""
+
+    @staticmethod
+    def forward(ctx, x2d, gamma, beta, running_mean, running_var, eps, momentum, training):
+        x2d = x2d if x2d.stride(-1) == 1 else x2d.contiguous()
+        M, F = x2d.shape
+        y = torch.empty(M, F, device=x2d.device, dtype=torch.float32)
+        sm = torch.empty(F, device=x2d.device, dtype=torch.float32)
+        si = torch.empty(F, device=x2d.device, dtype=torch.float32)
+        native.bn_fwd(x2d, y, 1, F, [gamma], [beta], [running_mean], [running_var], eps, momentum, training, sm, si,
+                      _ws(x2d.device, F))
+        if any(ctx.needs_input_grad):
+            if not training:
+                raise native.NativeError('backward through eval-mode batch norm is not built')
+            ctx.save_for_backward(x2d, gamma, sm, si)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2d, gamma, sm, si = ctx.saved_tensors
+        M, F = x2d.shape
+        dy = dy.contiguous()
+        dx = torch.empty(M, F, device=dy.device, dtype=torch.float32)
+        dg = torch.empty(F, device=dy.device, dtype=torch.float32)
+        db = torch.empty(F, device=dy.device, dtype=torch.float32)
+        native.bn_bwd(dy, x2d, 1, F, [gamma], sm, si, dx, [dg], [db], _ws(dy.device, F))
+        return dx, dg, db, None, None, None, None, None
+
+
+class ActDropFunction(torch.autograd.Function):
+    """y = drop_mask * act(x) (or LogSoftmax(dim=1) - log_prior) as a stand-alone step: used when a LayerNorm sits
+    between the linear and the activation of an MLP layer (neural_networks.py:306-307)."""
+
+    @staticmethod
+    def forward(ctx, x, act, drop_mask, softmax, log_prior):
+        x = x.contiguous()
+        y = torch.empty_like(x)
+        if softmax:
+            native.logsoftmax_fwd(x, y, log_prior)
+        else:
+            native.act_fwd(x, y, drop_mask, act)
+        ctx.act, ctx.softmax, ctx.had_prior, ctx.drop_mask = act, softmax, log_prior is not None, drop_mask
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        y, = ctx.saved_tensors
+        dy = dy.contiguous()
+        dx = torch.empty_like(y)
+        if ctx.softmax:
+            if ctx.had_prior:
+                raise native.NativeError('backward through a prior-normalised posterior is not defined')
+            native.logsoftmax_bwd(dy, y, dx)
+        else:
+            native.act_bwd(dy, y, ctx.drop_mask, dx, ctx.act)
+        return dx, None, None, None, None
+
+
 class LSTMLayerFunction(torch.autograd.Function):
     """One HCGS LSTM layer: projections -> BN -> persistent recurrence (neural_networks.py:950-1100)."""
 

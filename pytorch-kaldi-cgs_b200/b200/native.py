@@ -53,6 +53,9 @@ SIGNATURES = {
                                c_void_p]),
     'hcgs_bn_stats_il': (c_int, [_f, c_int64, c_int64, c_int64, c_int, c_int, c_int, _pp, _pp, c_float, c_float, c_int,
                                  _f, _f, c_void_p]),
+    'hcgs_layernorm_fwd': (c_int, [_f, c_int64, _f, c_int64, c_int64, c_int, _f, _f, c_float, _f, _f, c_void_p]),
+    'hcgs_layernorm_bwd': (c_int, [_f, c_int64, _f, c_int64, c_int64, c_int, _f, c_float, _f, _f, _f, c_int64, _f, _f,
+                                   c_void_p]),
     'hcgs_lstm_pack': (c_int, [c_void_p, _pp, c_int, _f, _f, c_void_p]),
     'hcgs_lstm_fwd': (c_int, [c_void_p, _f, _f, _f, c_float, c_int, c_int, c_int, _f, _f, _f, c_int, c_void_p]),
     'hcgs_lstm_bwd': (c_int, [c_void_p, _f, _f, _f, _f, _f, c_float, c_int, c_int, c_int, _f, c_void_p]),
@@ -110,7 +113,8 @@ KERNELS_PER_CALL = {'hcgs_mask_apply': 1, 'hcgs_quantize_w': 1, 'hcgs_quantize_a
                     'hcgs_tc_pack_nt': 1, 'hcgs_tc_gemm_nt': 1, 'hcgs_cast_bf16': 1,
                     'hcgs_tc_pack_nn': 1, 'hcgs_tc_gemm_nn': 1, 'hcgs_tc_sddmm': 1, 'hcgs_out_pack': 1,
                     'hcgs_out_logsoftmax_prior_fwd': 1, 'hcgs_act_fwd': 1, 'hcgs_act_bwd': 1,
-                    'hcgs_logsoftmax_fwd': 1, 'hcgs_logsoftmax_bwd': 1, 'hcgs_logsoftmax_bwd_fused': 1, 'hcgs_nll_fwd_bwd': 1, 'hcgs_opt_step': 1}
+                    'hcgs_logsoftmax_fwd': 1, 'hcgs_logsoftmax_bwd': 1, 'hcgs_logsoftmax_bwd_fused': 1,
+                    'hcgs_layernorm_fwd': 1, 'hcgs_layernorm_bwd': 1, 'hcgs_nll_fwd_bwd': 1, 'hcgs_opt_step': 1}
 LAUNCHES = {'total': 0}
 
 
@@ -326,6 +330,23 @@ def bn_stats_il(partial, rows_per_split, m, n_groups, units, ld_units, rmeans, r
     _check(load().hcgs_bn_stats_il(_ptr(partial), splits, int(rows_per_split), int(m), n_groups, units, ld_units,
                                    _ptrs(rmeans), _ptrs(rvars), float(eps), float(momentum), 1 if training else 0,
                                    _ptr(save_mean), _ptr(save_invstd), _stream()), 'hcgs_bn_stats_il')
+
+
+def layernorm_fwd(x2d, y2d, gamma, beta, eps, save_mean=None, save_std=None):
+    """reference LayerNorm over the last dimension (unbiased std, divide by std + eps)"""
+    _require_cuda(x2d, y2d, gamma, beta, save_mean, save_std)
+    _check(load().hcgs_layernorm_fwd(_ptr(x2d), _row_major_2d(x2d, 'x'), _ptr(y2d), _row_major_2d(y2d, 'y'),
+                                     x2d.shape[0], x2d.shape[1], _ptr(gamma), _ptr(beta), float(eps), _ptr(save_mean),
+                                     _ptr(save_std), _stream()), 'hcgs_layernorm_fwd')
+
+
+def layernorm_bwd(dy2d, x2d, gamma, eps, save_mean, save_std, dx2d, dgamma, dbeta):
+    """dx written (or skipped when None); dgamma / dbeta are ADDED to (zero-initialise them)"""
+    _require_cuda(dy2d, x2d, gamma, save_mean, save_std, dx2d, dgamma, dbeta)
+    _check(load().hcgs_layernorm_bwd(_ptr(dy2d), _row_major_2d(dy2d, 'dy'), _ptr(x2d), _row_major_2d(x2d, 'x'),
+                                     x2d.shape[0], x2d.shape[1], _ptr(gamma), float(eps), _ptr(save_mean),
+                                     _ptr(save_std), _ptr(dx2d), _row_major_2d(dx2d, 'dx') if dx2d is not None else 0,
+                                     _ptr(dgamma), _ptr(dbeta), _stream()), 'hcgs_layernorm_bwd')
 
 
 def lstm_pack(plan, us, fwd_pack=None, bwd_pack=None):

@@ -30,7 +30,7 @@ from HCGS import guidedHCGS as guidedHCGS
 from quantized_modules import QuantizeLinear, Quantize, Quantize_inp, prune
 from b200 import native
 from b200.functions import (LayerRuntime, LSTMLayerFunction, MLPLayerFunction, LSTMLayerTCFunction,
-                            MLPLayerTCFunction)
+                            MLPLayerTCFunction, LayerNormFunction, BatchNormInputFunction, ActDropFunction)
 
 
 def strtobool(val):
@@ -76,8 +76,15 @@ class LayerNorm(nn.Module):
         self.eps = eps
 
     def forward(self, x):
-        raise NotImplementedError('layer normalisation is not built into the B200 hot path yet '
-                                  '(no shipped CGS cfg enables *_use_laynorm)')
+        return LayerNormFunction.apply(x, self.gamma, self.beta, self.eps)
+
+
+def _input_batch_norm(bn, x2d):
+    """*_use_batchnorm_inp: nn.BatchNorm1d(momentum=0.05) over all rows of the layer input (:828-830, 251-252)."""
+    y = BatchNormInputFunction.apply(x2d, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.eps, bn.momentum,
+                                     bn.training)
+    _bump_bn_counter(bn)
+    return y
 
 
 def act_fun(act_type):
@@ -298,16 +305,17 @@ class MLP(nn.Module):
     def forward(self, x):
         if bool(self.dnn_use_laynorm_inp):
             x = self.ln0(x)
-        if bool(self.dnn_use_batchnorm_inp):
-            raise NotImplementedError('dnn_use_batchnorm_inp is not built into the B200 hot path yet')
         if x.dim() != 2:
             raise native.NativeError('MLP expects [N, in] input, got %s' % (tuple(x.shape),))
+        if bool(self.dnn_use_batchnorm_inp):
+            x = _input_batch_norm(self.bn0, x)
         for i in range(self.N_dnn_lay):
             with torch.no_grad():
                 self._apply_masks(i)
                 self._side_effects(i)
-            if self.dnn_use_laynorm[i]:
-                self.ln[i](x)  # raises: not built
+            ln_between = bool(self.dnn_use_laynorm[i])
+            if ln_between and self.dnn_use_batchnorm[i]:
+                raise NotImplementedError('dnn_use_laynorm together with dnn_use_batchnorm on one layer is not built')
             lin = self.wx[i]
             rt = LayerRuntime()
             factors = self._mask_factors(i)
@@ -340,7 +348,15 @@ class MLP(nn.Module):
             gamma = bn.weight if rt.use_bn else None
             beta = bn.bias if rt.use_bn else None
             fn = MLPLayerTCFunction if _precision(self) == 'bf16' else MLPLayerFunction
-            x = fn.apply(x, lin.weight, lin.bias, gamma, beta, rt)
+            if ln_between:
+                # drop(act(ln(wx(x)))) (:306-307): the linear alone, the reference's LayerNorm, then the activation
+                soft, act_code, dmask, prior = rt.softmax, rt.act, rt.mlp_drop_mask, rt.log_prior
+                rt.softmax, rt.act, rt.mlp_drop_mask, rt.log_prior = False, native.ACT_CODES['linear'], None, None
+                z = fn.apply(x, lin.weight, lin.bias, None, None, rt)
+                z = self.ln[i](z)
+                x = ActDropFunction.apply(z, act_code, dmask, soft, prior)
+            else:
+                x = fn.apply(x, lin.weight, lin.bias, gamma, beta, rt)
             if rt.use_bn:
                 _bump_bn_counter(bn)
         return x
@@ -617,10 +633,10 @@ class LSTM(nn.Module):
     def forward(self, x):
         if bool(self.lstm_use_laynorm_inp):
             x = self.ln0(x)
-        if bool(self.lstm_use_batchnorm_inp):
-            raise NotImplementedError('lstm_use_batchnorm_inp is not built into the B200 hot path yet')
         if x.dim() != 3:
             raise native.NativeError('LSTM expects [T, B, in] input, got %s' % (tuple(x.shape),))
+        if bool(self.lstm_use_batchnorm_inp):
+            x = _input_batch_norm(self.bn0, x.reshape(x.shape[0] * x.shape[1], x.shape[2])).view(x.shape)
         prev_hb = None
         for i in range(self.N_lstm_lay):
             self.bidir = 0           # as the reference (:835)
@@ -628,7 +644,8 @@ class LSTM(nn.Module):
             H = self.lstm_lay[i]
             T, B, D = x.shape
             if self.lstm_use_laynorm[i]:
-                self.ln[i](x)  # raises: not built
+                raise NotImplementedError('lstm_use_laynorm (LayerNorm of h_t inside the time loop, reference '
+                                          'neural_networks.py:1092-1093) is not built into the recurrent kernels')
             rt = LayerRuntime()
             # drop mask: same for all time steps, NOT rescaled; drawn on the CPU generator (:843-851)
             if self.test_flag == False:  # noqa: E712 (reference spelling)

@@ -239,6 +239,16 @@ def gen_quant_inp():
               steps=1, seed=6)
 
 
+def gen_norm_inp():
+    """Input normalisations and the reference's own LayerNorm: LSTM with lstm_use_laynorm_inp + lstm_use_batchnorm_inp
+    (neural_networks.py:825-830), MLP heads with dnn_use_laynorm_inp + dnn_use_batchnorm_inp (:248-252) and
+    dnn_use_laynorm between the linear and the activation (:306-307)."""
+    run_model('train_norm_inp', 'train', T=6, B=4, D=12,
+              lstm_over=dict(lstm_use_laynorm_inp='True', lstm_use_batchnorm_inp='True', lstm_lay='24,24'),
+              mlp_over=dict(dnn_use_laynorm_inp='True', dnn_use_batchnorm_inp='True', dnn_use_laynorm='True'),
+              steps=2, seed=8)
+
+
 if __name__ == '__main__':
     gen_masks()
     run_model('train_small', 'train', steps=2)
@@ -250,3 +260,4 @@ if __name__ == '__main__':
     run_model('train_quant', 'train', lstm_over=dict(lstm_quant='True', lstm_lay='24,24'),
               mlp_over=dict(mlp_quant='True'), steps=1, seed=5)
     gen_quant_inp()
+    gen_norm_inp()

@@ -351,3 +351,33 @@ def test_logsoftmax_bwd_fused(M, P):
     if ld > P:
         assert dzb[:, P:].float().abs().max().item() == 0
     assert (db.double() - ref.sum(0)).abs().max().item() <= 1e-4 * max(ref.sum(0).abs().max().item(), 1e-30)
+
+
+@pytest.mark.parametrize('shape', [(7, 3, 12), (300, 550), (65, 1)])
+def test_reference_layernorm_fwd_bwd(shape):
+    """hcgs_layernorm_fwd / _bwd = the reference's LayerNorm class (neural_networks.py:40-51: unbiased std, divide by
+    std + eps) and its autograd, against torch on the CPU in float64."""
+    from b200.functions import LayerNormFunction
+    if shape[-1] == 1:
+        pytest.skip('n = 1: the unbiased std is nan in the reference too')
+    torch.manual_seed(sum(shape))
+    d = torch.device('cuda', 0)
+    F = shape[-1]
+    x = torch.randn(*shape) * 2 + 0.3
+    gamma, beta = torch.rand(F) + 0.5, torch.randn(F)
+    w = torch.randn(*shape)
+    xr, gr, br = [t.double().requires_grad_(True) for t in (x, gamma, beta)]
+    yr = gr * (xr - xr.mean(-1, keepdim=True)) / (xr.std(-1, keepdim=True) + 1e-6) + br
+    (yr * w.double()).sum().backward()
+    xg, gg, bg = [t.to(d).requires_grad_(True) for t in (x, gamma, beta)]
+    y = LayerNormFunction.apply(xg, gg, bg, 1e-6)
+    (y * w.to(d)).sum().backward()
+    torch.cuda.synchronize()
+
+    def close_(a, b, what):
+        err = (a.detach().cpu().double() - b.detach()).abs().max().item()
+        assert err <= 1e-5 * max(b.detach().abs().max().item(), 1e-30), '%s: %.3e' % (what, err)
+    close_(y, yr, 'y')
+    close_(xg.grad, xr.grad, 'dx')
+    close_(gg.grad, gr.grad, 'dgamma')
+    close_(bg.grad, br.grad, 'dbeta')

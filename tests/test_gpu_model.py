@@ -301,3 +301,41 @@ def test_quantised_activations_and_pruning_train_step_matches_reference_fixture(
     big = torch.zeros(T, 9, D + 2).cuda()
     with pytest.raises(native.NativeError):
         graph.forward(big, T, 9, 'train', ['out_dnn2'])
+
+
+def test_input_norms_and_layernorm_train_steps_match_reference_fixture():
+    """lstm_use_laynorm_inp + lstm_use_batchnorm_inp (neural_networks.py:825-830), dnn_use_laynorm_inp +
+    dnn_use_batchnorm_inp (:248-252) and dnn_use_laynorm between linear and activation (:306-307): two reference
+    train steps (fixture train_norm_inp.npz, generated by running the reference)."""
+    g = load_golden('train_norm_inp')
+    T, B, D, steps = [int(v) for v in g['dims']]
+    lo = dict(lstm_use_laynorm_inp='True', lstm_use_batchnorm_inp='True')
+    mo = dict(dnn_use_laynorm_inp='True', dnn_use_batchnorm_inp='True', dnn_use_laynorm='True')
+    nets, sections = build_product_nets('train', seed=8, lstm_over=lo, mlp_over=mo, device='cuda')
+    for n, net in nets.items():
+        net.load_state_dict(golden_state(g, 'init', n))
+    from b200.graph import make_optimizer
+    opts = {k: make_optimizer(nets[k], s) for k, s in zip(nets, sections)}
+    graph = make_graph(nets, D)
+    drops = [torch.from_numpy(g['drop/%d' % i]) for i in range(2 * steps)]
+    with _ReplayBernoulli(drops):
+        for s in range(steps):
+            out = graph.forward(torch.from_numpy(g['inp/%d' % s]).cuda(), T, B, 'train', ['out_dnn2'])
+            for o in opts.values():
+                o.zero_grad()
+            out['loss_final'].backward()
+            assert abs(out['loss_final'].item() - g['loss/%d' % s][0]) <= 2e-5 * abs(g['loss/%d' % s][0]), s
+            close(out['out_dnn2'], g['out_dnn2/%d' % s], 2e-5, 'out_dnn2 step %d' % s)
+            if s == steps - 1:
+                lstm = nets['LSTM_layers']
+                close(lstm.ln0.gamma.grad, g['grad/LSTM_layers/ln0.gamma'], 2e-4, 'ln0.gamma grad')
+                close(lstm.bn0.weight.grad, g['grad/LSTM_layers/bn0.weight'], 2e-4, 'bn0.weight grad')
+                close(nets['MLP_layers'].ln[0].gamma.grad, g['grad/MLP_layers/ln.0.gamma'], 2e-4, 'ln.0.gamma grad')
+                mask = lstm.hcgsx[0].mask.detach().cpu()
+                close(lstm.wfx[0].weight.grad.cpu() * mask, torch.from_numpy(g['grad/LSTM_layers/wfx.0.weight']) * mask,
+                      2e-4, 'wfx.0 grad')
+            for o in opts.values():
+                o.step()
+    sd = nets['LSTM_layers'].state_dict()
+    close(sd['bn0.running_mean'], g['final/LSTM_layers/bn0.running_mean'], 1e-5, 'bn0 running mean')
+    close(sd['bn0.running_var'], g['final/LSTM_layers/bn0.running_var'], 1e-5, 'bn0 running var')
