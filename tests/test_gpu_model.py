@@ -334,8 +334,13 @@ def test_input_norms_and_layernorm_train_steps_match_reference_fixture():
                 mask = lstm.hcgsx[0].mask.detach().cpu()
                 close(lstm.wfx[0].weight.grad.cpu() * mask, torch.from_numpy(g['grad/LSTM_layers/wfx.0.weight']) * mask,
                       2e-4, 'wfx.0 grad')
+            if s == 0:
+                # running statistics of bn0 after ONE step against nn.BatchNorm1d's rule recomputed in float64.  (After
+                # the optimizer step they are not comparable any more: bn0 cancels ln0's gamma / beta, their gradients
+                # are rounding noise, and RMSprop turns the sign of that noise into a full-size first update.)
+                xr = torch.from_numpy(g['inp/0'])[:, :, :D].double()
+                ln = ((xr - xr.mean(-1, keepdim=True)) / (xr.std(-1, keepdim=True) + 1e-6)).reshape(T * B, D)
+                close(nets['LSTM_layers'].bn0.running_mean, 0.05 * ln.mean(0), 1e-5, 'bn0 running mean')
+                close(nets['LSTM_layers'].bn0.running_var, 0.95 + 0.05 * ln.var(0, unbiased=True), 1e-5, 'bn0 running var')
             for o in opts.values():
                 o.step()
-    sd = nets['LSTM_layers'].state_dict()
-    close(sd['bn0.running_mean'], g['final/LSTM_layers/bn0.running_mean'], 1e-5, 'bn0 running mean')
-    close(sd['bn0.running_var'], g['final/LSTM_layers/bn0.running_var'], 1e-5, 'bn0 running var')
