@@ -59,17 +59,40 @@ def Quantize_inp(inp, Bits, if_forward=False, repeat=1):
     return out.view(inp.shape)
 
 
+def percentile_threshold(values, perc):
+    """np.percentile(values, perc) of a 1-D float32 tensor WITHOUT leaving its device, as the installed numpy (2.x)
+    evaluates it for a float32 array and a Python-number percentile (method 'linear'): everything in float32 --
+    q = float32(perc) / float32(100), virtual index (n-1)*q, gamma = its fractional part, then
+    a + (b-a)*gamma, or b - (b-a)*(1-gamma) when gamma >= 0.5, on the two neighbouring order statistics.
+    Only the index arithmetic (scalars) runs on the host; returns a 0-dim float32 tensor."""
+    n = values.numel()
+    q = np.float32(perc) / np.float32(100)
+    vidx = np.float32(n - 1) * q
+    if vidx >= n - 1:
+        lo = hi = n - 1
+    elif vidx < 0:
+        lo = hi = 0
+    else:
+        lo = int(np.floor(vidx))
+        hi = lo + 1
+    gamma = np.float32(vidx - np.floor(vidx))
+    srt = torch.sort(values.reshape(-1))[0]
+    a, b = srt[lo], srt[hi]
+    diff = b - a
+    if gamma >= np.float32(0.5):
+        return b - diff * float(np.float32(1) - gamma)
+    return a + diff * float(gamma)
+
+
 def prune(model, pruning_perc):
-    """quantized_modules.py:15-28: magnitude mask per >=2-D parameter, one global percentile.
-    The percentile is taken on the host exactly like the reference (np.percentile, float64
-    linear interpolation); the mask itself is a device comparison."""
-    all_weights = [p.detach().abs().cpu().numpy().ravel() for p in model.parameters() if p.dim() != 1]
-    threshold = np.percentile(np.concatenate(all_weights), pruning_perc)
-    masks = []
-    for p in model.parameters():
-        if p.dim() != 1:
-            masks.append((p.data.abs() > threshold).float())
-    return masks
+    """quantized_modules.py:15-28: magnitude mask per >=2-D parameter, one global percentile.  The reference moves
+    every matrix to the host for np.percentile on every forward (8 round trips per LSTM layer); here the order
+    statistics, the interpolation and the comparison stay on the device (no synchronisation), bit-identical to the
+    host result (tests/test_host_cpu.py::test_percentile_threshold_matches_numpy)."""
+    mats = [p for p in model.parameters() if p.dim() != 1]
+    flat = torch.cat([p.detach().abs().reshape(-1) for p in mats]) if len(mats) != 1 else mats[0].detach().abs().reshape(-1)
+    threshold = percentile_threshold(flat, pruning_perc)
+    return [(p.data.abs() > threshold).float() for p in mats]
 
 
 class QuantizeLinear(nn.Module):

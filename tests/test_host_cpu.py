@@ -91,3 +91,23 @@ def test_c_abi_exports_every_declared_symbol():
         assert hasattr(lib, name), 'library does not export %s' % name
     assert declared == set(native.SIGNATURES), declared ^ set(native.SIGNATURES)
     assert native.load().hcgs_abi_version() == 1
+
+
+def test_percentile_threshold_matches_numpy():
+    """quantized_modules.percentile_threshold (device-side np.percentile of the pruning path, reference
+    quantized_modules.py:15-28) against numpy on the same float32 data, including the float32 cast the reference's
+    `tensor > threshold` comparison applies, ties, zeros (HCGS-masked weights) and both interpolation branches."""
+    import numpy as np
+    import torch
+    from quantized_modules import percentile_threshold
+    rng = np.random.RandomState(0)
+    for n, perc, zeros in [(1000, 70, 0.0), (577, 70, 0.9), (24 * 24, 70, 0.75), (10, 33.3, 0.0), (7, 50, 0.0),
+                           (302500, 70, 0.89), (5, 99.9, 0.0), (64, 0, 0.0), (64, 100, 0.0)]:
+        w = rng.randn(n).astype(np.float32)
+        w[rng.rand(n) < zeros] = 0.0
+        a = np.abs(w)
+        want = np.percentile(a, perc)
+        got = percentile_threshold(torch.from_numpy(a), perc)
+        assert got.dtype == torch.float32 and got.dim() == 0
+        assert got.item() == float(np.float32(want)), (n, perc, got.item(), want)
+        assert torch.equal(torch.from_numpy(a) > got, torch.from_numpy(a) > want)
