@@ -507,7 +507,9 @@ def main():
     nets, graph, opts = build_workload(dev, precision=args.precision)
     bucket = None
     if world > 1:
-        bucket = bdist.GradBucket(bdist.lstm_mlp_entries(list(nets.values())), dev)
+        # one compressed-gradient bucket per LSTM layer / head; each all-reduce starts from an autograd hook as soon as
+        # its gradients exist and overlaps the backward of the layers below
+        bucket = bdist.OverlappedGradBuckets(bdist.lstm_mlp_groups(list(nets.values())), dev)
     n_batches = 4
     host = []
     frames_per = []

@@ -105,6 +105,90 @@ def lstm_mlp_entries(nets):
     return out
 
 
+def lstm_mlp_groups(nets):
+    """The entries of lstm_mlp_entries cut into groups whose gradients become ready together during backward: one
+    group per LSTM layer (input-norm parameters ride with layer 0) and one per MLP net, in the order in which
+    backward completes them (heads first, then the LSTM layers from the top)."""
+    groups = []
+    for net in nets:
+        entries = lstm_mlp_entries([net])
+        names = [n for n, _ in net.named_parameters() if not n.endswith('mask')]
+        assert len(names) == len(entries)
+        if hasattr(net, 'N_lstm_lay'):
+            per = [[] for _ in range(net.N_lstm_lay)]
+            for n, e in zip(names, entries):
+                parts = n.split('.')
+                i = int(parts[1]) if len(parts) > 2 and parts[1].isdigit() and int(parts[1]) < net.N_lstm_lay else 0
+                per[i].append(e)
+            groups = [g for g in reversed(per) if g] + groups        # LSTM layers after whatever sits above them
+        else:
+            groups = [entries] + groups
+    return [g for g in groups if g]
+
+
+class OverlappedGradBuckets:
+    """Per-group GradBuckets whose all-reduce overlaps the rest of backward: an autograd hook counts the gradients
+    of a group as they are accumulated and launches the group's gather / all-reduce / scatter on a side stream when
+    the last one has arrived; ``all_reduce_mean()`` (called where the single-bucket version does its whole work,
+    after backward) only launches what has not fired and makes the main stream wait.  Same result as one GradBucket."""
+
+    def __init__(self, groups, device):
+        self.buckets = [GradBucket(g, device) for g in groups]
+        self.groups = [[p for p, _ in g if p.requires_grad] for g in groups]
+        self.calibrated = False
+        self.total = [len(g) for g in self.groups]
+        self.left = list(self.total)
+        self.fired = [False] * len(groups)
+        self.numel = sum(b.numel for b in self.buckets)
+        self.stream = torch.cuda.Stream(device=device) if device.type == 'cuda' else None
+        self.handles = []
+        for bi, g in enumerate(groups):
+            for p, _ in g:
+                if p.requires_grad:
+                    self.handles.append(p.register_post_accumulate_grad_hook(lambda _p, bi=bi: self._ready(bi)))
+
+    def mask_signature(self):
+        s = 0
+        for b in self.buckets:
+            s = (s * 1000003 + b.mask_signature()) % (2 ** 61 - 1)
+        return s
+
+    def _ready(self, bi):
+        self.left[bi] -= 1
+        if self.left[bi] == 0 and not self.fired[bi]:
+            self._launch(bi)
+
+    def _launch(self, bi):
+        self.fired[bi] = True
+        if not dist.is_initialized() or dist.get_world_size() == 1:
+            return
+        if self.stream is None:
+            self.buckets[bi].all_reduce_mean()
+            return
+        self.stream.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(self.stream):
+            self.buckets[bi].all_reduce_mean()
+
+    def all_reduce_mean(self):
+        for bi in range(len(self.buckets)):
+            if not self.fired[bi]:
+                self._launch(bi)
+        if self.stream is not None:
+            torch.cuda.current_stream().wait_stream(self.stream)
+        if not self.calibrated:
+            # parameters of unused options (e.g. the LayerNorm / BatchNorm modules the classes always create) never
+            # receive a gradient: count only those that did in the first step, or no group would ever fire early
+            self.total = [sum(1 for p in g if p.grad is not None) for g in self.groups]
+            self.calibrated = True
+        self.left = list(self.total)
+        self.fired = [False] * len(self.buckets)
+
+    def remove_hooks(self):
+        for h in self.handles:
+            h.remove()
+        self.handles = []
+
+
 def shard_utterances(lengths, world):
     """Length-balanced round robin: sort by length (descending), deal to the least-loaded rank."""
     order = sorted(range(len(lengths)), key=lambda i: -lengths[i])

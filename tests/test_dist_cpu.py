@@ -46,6 +46,23 @@ def _worker(rank, world, port, out_dir):
     bucket.all_reduce_mean()
     torch.save({'after': [p.grad.clone() for p in params], 'before': before, 'numel': bucket.numel},
                os.path.join(out_dir, 'rank%d.pt' % rank))
+    # overlapped per-group buckets: hooks fire during a real backward; same result as the single bucket
+    for p in params:
+        p.grad = None
+    ob = bdist.OverlappedGradBuckets(bdist.lstm_mlp_groups(list(nets.values())), torch.device('cpu'))
+    assert ob.numel == bucket.numel
+    trainable = [p for p in params if p.requires_grad]
+    fired_early = []
+    for step in range(2):
+        for p in trainable:
+            p.grad = None
+        loss = sum((p * float(rank + 1 + step)).sum() for p in trainable[::2])     # every other parameter gets a gradient
+        loss.backward()
+        fired_early.append(sum(ob.fired))
+        ob.all_reduce_mean()
+    torch.save({'grads': [None if p.grad is None else p.grad.clone() for p in trainable], 'fired_early': fired_early},
+               os.path.join(out_dir, 'overlap%d.pt' % rank))
+    ob.remove_hooks()
     # utterance sharding: every rank computes the same partition
     lengths = [int(v) for v in np.random.RandomState(3).randint(50, 900, size=37)]
     shards = bdist.shard_utterances(lengths, world)
@@ -78,6 +95,22 @@ def test_grad_bucket_allreduce_and_sharding_world2(tmp_path):
         total_kept += int((m.detach() != 0).sum()) if m is not None else p.numel()
         dense_total += p.numel()
     assert res[0]['numel'] == total_kept < dense_total      # only the kept weights travel
+    # overlapped buckets, second step: gradient (rank + 2) on each rank -> mean 2.5 on kept entries, own value elsewhere
+    ov = [torch.load(os.path.join(str(tmp_path), 'overlap%d.pt' % r)) for r in range(world)]
+    trainable = [(p, m) for p, m in entries if p.requires_grad]
+    for r in range(world):
+        assert ov[r]['fired_early'][0] <= ov[r]['fired_early'][1] and ov[r]['fired_early'][1] >= 1, ov[r]['fired_early']
+        for i, (p, m) in enumerate(trainable):
+            got = ov[r]['grads'][i]
+            if i % 2:
+                assert got is None
+                continue
+            if m is None:
+                assert torch.allclose(got, torch.full_like(got, 2.5))
+            else:
+                keep = m.detach() != 0
+                assert torch.allclose(got[keep], torch.full_like(got[keep], 2.5))
+                assert torch.allclose(got[~keep], torch.full_like(got[~keep], float(r + 2)))
     s0 = torch.load(os.path.join(str(tmp_path), 'shards0.pt'))
     s1 = torch.load(os.path.join(str(tmp_path), 'shards1.pt'))
     assert s0 == s1
