@@ -339,7 +339,7 @@ def _padded_rows(g, T, B, H, ldH):
     if (g.dim() == 3 and g.stride() == (B * ldH, ldH, 1) and (g.storage_offset() * 4) % 16 == 0 and
             g.untyped_storage().nbytes() >= (g.storage_offset() + M * ldH) * 4):
         return g.as_strided((M, ldH), (ldH, 1))
-    out = torch.zeros(M, ldH, device=g.device, dtype=torch.float32)
+    out = torch.empty(M, ldH, device=g.device, dtype=torch.float32)   # pad columns are ignored by the consumer
     out[:, :H].copy_(g.reshape(M, H))
     return out
 
@@ -453,7 +453,8 @@ class LSTMLayerTCFunction(torch.autograd.Function):
             wpack = torch.empty(px.nz_tiles * 32 * 4 * 32, device=dev, dtype=torch.bfloat16)
             native.tc_pack_nn(px, [wf, wi, wo, wc], wpack)
             # rows padded to 16 bytes: the layer below reads its dh through TMA boxes (no repacking pass)
-            dx_pad = torch.zeros(M, native.pad8(D), device=dev, dtype=torch.float32)
+            # (pad columns stay uninitialised: the recurrent backward of the layer below ignores them, include/hcgs_b200.h)
+            dx_pad = torch.empty(M, native.pad8(D), device=dev, dtype=torch.float32)
             native.tc_gemm_nn(px, 4, wpack, dproj_b, dx_pad)
             dx = dx_pad[:, :D].view(T, B, D)
         return (dx, dws[0], dws[1], dws[2], dws[3], dus[0], dus[1], dus[2], dus[3],
