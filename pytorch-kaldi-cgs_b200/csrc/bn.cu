@@ -433,12 +433,158 @@ __global__ void __launch_bounds__(256) bn_bwd_il_apply_kernel(const DY* __restri
     }
 }
 
+// ---- the same two passes for n_groups = 4 with ONE UNIT (its four gate columns) per thread: 16-byte x loads, 8- or
+// 16-byte dy loads, 8-byte bf16 stores, 512 contiguous bytes of x per warp and row (the two-column version moved 256)
+template <typename DY>
+__device__ __forceinline__ float4 bn_ld4(const DY* p);
+template <>
+__device__ __forceinline__ float4 bn_ld4<float>(const float* p) {
+    return __ldg(reinterpret_cast<const float4*>(p));
+}
+template <>
+__device__ __forceinline__ float4 bn_ld4<__nv_bfloat16>(const __nv_bfloat16* p) {
+    const uint2 v = __ldg(reinterpret_cast<const uint2*>(p));
+    return make_float4(__uint_as_float(v.x << 16), __uint_as_float(v.x & 0xffff0000u), __uint_as_float(v.y << 16),
+                       __uint_as_float(v.y & 0xffff0000u));
+}
+
+template <typename DY>
+__global__ void __launch_bounds__(256) bn_bwd_il4_partial_kernel(const DY* __restrict__ dy, const float* __restrict__ x,
+                                                                 int ld, int64_t M, int64_t rows_per_split,
+                                                                 const float* __restrict__ save_mean,
+                                                                 const float* __restrict__ save_invstd,
+                                                                 float* __restrict__ partial) {
+    __shared__ float red[8][33];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int col = blockIdx.x * 128 + lane * 4;
+    const bool ok = col < ld;
+    const int64_t mbeg = (int64_t)blockIdx.y * rows_per_split;
+    const int64_t mend = (mbeg + rows_per_split < M) ? mbeg + rows_per_split : M;
+    float4 mean = make_float4(0.f, 0.f, 0.f, 0.f), invstd = mean;
+    if (ok) {
+        mean = *reinterpret_cast<const float4*>(save_mean + col);
+        invstd = *reinterpret_cast<const float4*>(save_invstd + col);
+    }
+    float s1[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f};
+    if (ok) {
+#pragma unroll 4
+        for (int64_t m = mbeg + warp; m < mend; m += 8) {
+            const float4 d = bn_ld4<DY>(dy + m * ld + col);
+            const float4 xv = __ldg(reinterpret_cast<const float4*>(x + m * ld + col));
+            s1[0] += d.x; s1[1] += d.y; s1[2] += d.z; s1[3] += d.w;
+            s2[0] = fmaf(d.x, (xv.x - mean.x) * invstd.x, s2[0]);
+            s2[1] = fmaf(d.y, (xv.y - mean.y) * invstd.y, s2[1]);
+            s2[2] = fmaf(d.z, (xv.z - mean.z) * invstd.z, s2[2]);
+            s2[3] = fmaf(d.w, (xv.w - mean.w) * invstd.w, s2[3]);
+        }
+    }
+    float t1[4], t2[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        t1[q] = block_col_reduce(s1[q], red, warp, lane);
+        t2[q] = block_col_reduce(s2[q], red, warp, lane);
+    }
+    if (warp == 0 && ok) {
+        float4* dst = reinterpret_cast<float4*>(partial + ((int64_t)blockIdx.y * ld + col) * 2);
+        dst[0] = make_float4(t1[0], t2[0], t1[1], t2[1]);
+        dst[1] = make_float4(t1[2], t2[2], t1[3], t2[3]);
+    }
+}
+
+template <typename DY>
+__global__ void __launch_bounds__(256) bn_bwd_il4_apply_kernel(const DY* __restrict__ dy, const float* __restrict__ x,
+                                                               int ld, int64_t M, int C, PtrPack<const float> gamma,
+                                                               const float* __restrict__ save_mean,
+                                                               const float* __restrict__ save_invstd,
+                                                               const float* __restrict__ partial, int splits,
+                                                               float* __restrict__ dx, __nv_bfloat16* __restrict__ dxb,
+                                                               PtrPack<float> dgamma, PtrPack<float> dbeta,
+                                                               int rows_per_block) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int col = blockIdx.x * 128 + lane * 4;
+    if (col >= ld) return;
+    const int c = col >> 2;  // the unit; the four columns are its gates 0..3
+    const int64_t mbeg = (int64_t)blockIdx.y * rows_per_block;
+    const int64_t mend = (mbeg + rows_per_block < M) ? mbeg + rows_per_block : M;
+    if (c >= C) {  // pad units of the padded tensors stay zero
+        for (int64_t m = mbeg + warp; m < mend; m += 8) {
+            if (dx) *reinterpret_cast<float4*>(dx + m * ld + col) = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (dxb) *reinterpret_cast<uint2*>(dxb + m * ld + col) = make_uint2(0u, 0u);
+        }
+        return;
+    }
+    float s1[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int s = 0; s < splits; ++s) {
+        const float4* p = reinterpret_cast<const float4*>(partial + ((int64_t)s * ld + col) * 2);
+        const float4 p0 = p[0], p1 = p[1];
+        s1[0] += p0.x; s2[0] += p0.y; s1[1] += p0.z; s2[1] += p0.w;
+        s1[2] += p1.x; s2[2] += p1.y; s1[3] += p1.z; s2[3] += p1.w;
+    }
+    if (blockIdx.y == 0 && warp == 0) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            if (dgamma.p[q]) dgamma.p[q][c] = s2[q];
+            if (dbeta.p[q]) dbeta.p[q][c] = s1[q];
+        }
+    }
+    const float4 mean = *reinterpret_cast<const float4*>(save_mean + col);
+    const float4 invstd = *reinterpret_cast<const float4*>(save_invstd + col);
+    const float mu[4] = {mean.x, mean.y, mean.z, mean.w}, is[4] = {invstd.x, invstd.y, invstd.z, invstd.w};
+    const float inv_m = 1.0f / (float)M;
+    float k1[4], k2[4], aq[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        k1[q] = s1[q] * inv_m;
+        k2[q] = s2[q] * inv_m;
+        aq[q] = (gamma.p[q] ? __ldg(gamma.p[q] + c) : 1.f) * is[q];
+    }
+#pragma unroll 4
+    for (int64_t m = mbeg + warp; m < mend; m += 8) {
+        const float4 d = bn_ld4<DY>(dy + m * ld + col);
+        const float4 xv = __ldg(reinterpret_cast<const float4*>(x + m * ld + col));
+        const float dv[4] = {d.x, d.y, d.z, d.w}, xq[4] = {xv.x, xv.y, xv.z, xv.w};
+        float o[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) o[q] = aq[q] * (dv[q] - k1[q] - (xq[q] - mu[q]) * is[q] * k2[q]);
+        if (dx) *reinterpret_cast<float4*>(dx + m * ld + col) = make_float4(o[0], o[1], o[2], o[3]);
+        if (dxb) {
+            const __nv_bfloat162 lo = __floats2bfloat162_rn(o[0], o[1]), hi = __floats2bfloat162_rn(o[2], o[3]);
+            uint2 pk;
+            pk.x = *reinterpret_cast<const unsigned*>(&lo);
+            pk.y = *reinterpret_cast<const unsigned*>(&hi);
+            *reinterpret_cast<uint2*>(dxb + m * ld + col) = pk;
+        }
+    }
+}
+
 template <typename DY>
 static int bn_bwd_il_launch(const DY* dy, const float* x, int64_t m, int n_groups, int units, int ld_units,
                             const float* const* gamma, const float* save_mean, const float* save_invstd, float* dx,
                             void* dx_bf16, float* const* dgamma, float* const* dbeta, float* workspace,
                             int64_t workspace_floats, cudaStream_t st) {
     const int ld = n_groups * ld_units;
+    const bool aligned16 = (((uintptr_t)x | (uintptr_t)save_mean | (uintptr_t)save_invstd | (uintptr_t)workspace |
+                             (uintptr_t)dx) & 15) == 0 && ((uintptr_t)dy & (sizeof(DY) == 4 ? 15 : 7)) == 0 && ((uintptr_t)dx_bf16 & 7) == 0;
+    if (n_groups == 4 && aligned16) {  // one unit (four gate columns) per thread
+        const int strips = (ld + 127) / 128;
+        int64_t rows;
+        const int splits = pick_splits(m, strips, workspace_floats, ld, &rows);
+        bn_bwd_il4_partial_kernel<DY><<<dim3(strips, splits), 256, 0, st>>>(dy, x, ld, m, rows, save_mean, save_invstd,
+                                                                            workspace);
+        HCGS_LAUNCH_CHECK();
+        int rows_per_block = 256;
+        int64_t yb = (m + rows_per_block - 1) / rows_per_block;
+        while (yb > 65535) {
+            rows_per_block *= 2;
+            yb = (m + rows_per_block - 1) / rows_per_block;
+        }
+        bn_bwd_il4_apply_kernel<DY><<<dim3(strips, (unsigned)yb), 256, 0, st>>>(
+            dy, x, ld, m, units, make_pack<const float>(gamma, n_groups), save_mean, save_invstd, workspace, splits, dx,
+            (__nv_bfloat16*)dx_bf16, make_pack<float>(dgamma, n_groups), make_pack<float>(dbeta, n_groups),
+            rows_per_block);
+        HCGS_LAUNCH_CHECK();
+        return 0;
+    }
     const int strips = (ld + 63) / 64;
     int64_t rows;
     const int splits = pick_splits(m, strips, workspace_floats, ld, &rows);
