@@ -107,23 +107,25 @@ __global__ void __launch_bounds__(256) nll_fwd_bwd_kernel(const float* __restric
 //   db[p] += sum_m dz[m, p]                  (bias gradient, fp32, before rounding)
 //   dz_bf16[m, :] = bf16(dz)                 (operand of the dW / dX tensor-core products; pad columns zero)
 // One warp per row, persistent over rows; a lane keeps its 4*NV4 columns of the row in registers between the
-// row sum and the write, and its running column sums in registers (NV4 <= 16) or in shared memory.
+// row sum and the write.  Its running column sums live in a per-warp private slice of shared memory (NV4 <= 16: one
+// conflict-free 16-byte load + store per float4 of the row; in registers they cost 64 registers per thread and
+// held the kernel at 16 warps per SM, latency bound at 2.9 TB/s) or in shared-memory atomics (wider rows).
 template <int NV4>
-__global__ void __launch_bounds__(256, 2) logsoftmax_bwd_fused_kernel(const float* __restrict__ dlogp,
+__global__ void __launch_bounds__(256, NV4 <= 16 ? 3 : 2) logsoftmax_bwd_fused_kernel(const float* __restrict__ dlogp,
                                                                    const float* __restrict__ logp, int64_t M, int P,
                                                                    __nv_bfloat16* __restrict__ dz, int64_t ldo,
                                                                    float* __restrict__ db) {
     constexpr bool COLREG = NV4 <= 16;
-    extern __shared__ float s_col[];  // [P] column sums of this CTA
+    extern __shared__ float s_col[];  // [P] column sums of this CTA (+ [8][NV4*32] float4 private slices)
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int p = threadIdx.x; p < P; p += 256) s_col[p] = 0.f;
-    __syncthreads();
     const int nv = (P + 127) / 128;  // float4 per lane actually used (<= NV4)
-    float4 csum[COLREG ? NV4 : 1];
+    float4* csum = reinterpret_cast<float4*>(s_col + ((P + 3) & ~3)) + warp * (NV4 * 32) + lane;  // [i*32]
     if (COLREG) {
 #pragma unroll
-        for (int i = 0; i < (COLREG ? NV4 : 1); ++i) csum[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int i = 0; i < NV4; ++i) csum[i * 32] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
+    __syncthreads();
     const int64_t wstride = (int64_t)gridDim.x * 8;
     for (int64_t m = (int64_t)blockIdx.x * 8 + warp; m < M; m += wstride) {
         const float4* dr = reinterpret_cast<const float4*>(dlogp + m * P);
@@ -152,8 +154,9 @@ __global__ void __launch_bounds__(256, 2) logsoftmax_bwd_fused_kernel(const floa
                 g.z = d.z - __expf(l.z) * s;
                 g.w = d.w - __expf(l.w) * s;
                 if (COLREG) {
-                    csum[COLREG ? i : 0].x += g.x; csum[COLREG ? i : 0].y += g.y;
-                    csum[COLREG ? i : 0].z += g.z; csum[COLREG ? i : 0].w += g.w;
+                    float4 cs = csum[i * 32];
+                    cs.x += g.x; cs.y += g.y; cs.z += g.z; cs.w += g.w;
+                    csum[i * 32] = cs;
                 } else {
                     atomicAdd(s_col + c, g.x); atomicAdd(s_col + c + 1, g.y);
                     atomicAdd(s_col + c + 2, g.z); atomicAdd(s_col + c + 3, g.w);
@@ -170,11 +173,12 @@ __global__ void __launch_bounds__(256, 2) logsoftmax_bwd_fused_kernel(const floa
     if (db == nullptr) return;
     if (COLREG) {
 #pragma unroll
-        for (int i = 0; i < (COLREG ? NV4 : 1); ++i) {
+        for (int i = 0; i < NV4; ++i) {
             const int c = (lane + 32 * i) * 4;
             if (i < nv && c < P) {
-                atomicAdd(s_col + c, csum[i].x); atomicAdd(s_col + c + 1, csum[i].y);
-                atomicAdd(s_col + c + 2, csum[i].z); atomicAdd(s_col + c + 3, csum[i].w);
+                const float4 cs = csum[i * 32];
+                atomicAdd(s_col + c, cs.x); atomicAdd(s_col + c + 1, cs.y);
+                atomicAdd(s_col + c + 2, cs.z); atomicAdd(s_col + c + 3, cs.w);
             }
         }
     }
@@ -198,13 +202,18 @@ extern "C" int hcgs_logsoftmax_bwd_fused(const float* dlogp, const float* logp, 
     HCGS_REQUIRE((((uintptr_t)dlogp | (uintptr_t)logp) & 15) == 0 && ((uintptr_t)dz_bf16 & 7) == 0,
                  "hcgs_logsoftmax_bwd_fused: operands must be 16-byte aligned");
     if (m <= 0) return 0;
-    const int blocks = (int)std::min<int64_t>((m + 7) / 8, 148 * 2);  // two resident CTAs per SM, one wave
-    const size_t smem = (size_t)p * sizeof(float);
     cudaStream_t st = (cudaStream_t)stream;
-    if (p <= 2048)
+    if (p <= 2048) {
+        const int blocks = (int)std::min<int64_t>((m + 7) / 8, 148 * 3);  // three resident CTAs per SM, one wave
+        const size_t smem = (size_t)((p + 3) & ~3) * sizeof(float) + (size_t)8 * 16 * 32 * sizeof(float4);
+        HCGS_CHECK_CUDA(cudaFuncSetAttribute(logsoftmax_bwd_fused_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)smem));
         logsoftmax_bwd_fused_kernel<16><<<blocks, 256, smem, st>>>(dlogp, logp, m, p, (__nv_bfloat16*)dz_bf16, ldo, db);
-    else
+    } else {
+        const int blocks = (int)std::min<int64_t>((m + 7) / 8, 148 * 2);
+        const size_t smem = (size_t)p * sizeof(float);
         logsoftmax_bwd_fused_kernel<32><<<blocks, 256, smem, st>>>(dlogp, logp, m, p, (__nv_bfloat16*)dz_bf16, ldo, db);
+    }
     HCGS_LAUNCH_CHECK();
     return 0;
 }
