@@ -556,8 +556,9 @@ struct NnCfg {
     static constexpr int NSUB = NG == 4 ? 2 : 1;
     static constexpr int A_SUB = 128 * KCH * 2;
     static constexpr int B_SUB = 32 * KCH * 2;
-    static constexpr int STAGE = NSUB * (A_SUB + B_SUB);
-    static constexpr int STAGES = NG == 4 ? 2 : 4;
+    static constexpr int STAGE = A_SUB + B_SUB;     // one k sub-tile per stage: 20 KB (NG = 4) / 10 KB (NG = 1)
+    static constexpr int STAGES = NG == 4 ? 2 : 4;  // ~41 KB per CTA: five CTAs per SM (the CTAs are short and latency
+                                                    // bound; with both sub-tiles in one 40 KB stage only two fitted)
     static constexpr uint32_t SW = NG == 4 ? UMMA_SW128 : UMMA_SW64;
     static constexpr uint32_t SBO = 8 * KCH * 2;
     static constexpr int SMEM = 1024 + STAGES * STAGE + 256;
@@ -639,21 +640,20 @@ __global__ void __launch_bounds__(128) tc_gemm_nn_kernel(const __grid_constant__
     const uint32_t tmem = *tmem_slot;
 
     if (warp == 0 && lane == 0) {
-        for (int i = 0; i < nk; ++i) {
+        for (int i = 0; i < nk * C::NSUB; ++i) {
             const int s = i % C::STAGES;
             if (i >= C::STAGES) g_mbar_wait(empty0 + 8 * s, (uint32_t)(((i / C::STAGES) - 1) & 1));
             g_mbar_expect_tx(full0 + 8 * s, C::STAGE);
-            const int r = a.row_idx[k0 + i];
+            const int e = k0 + i / C::NSUB, h = i % C::NSUB;
+            const int r = a.row_idx[e];
             unsigned char* st = smem + s * C::STAGE;
-#pragma unroll
-            for (int h = 0; h < C::NSUB; ++h)
-                tma_load_2d(g_smem_u32(st + h * C::A_SUB), &tmDY, r * 32 * NG + h * C::KCH, (int)m0, full0 + 8 * s);
-            bulk_load_1d(g_smem_u32(st + C::NSUB * C::A_SUB),
-                         reinterpret_cast<const unsigned char*>(a.wpack) + (size_t)(k0 + i) * (C::NSUB * C::B_SUB),
-                         C::NSUB * C::B_SUB, full0 + 8 * s);
+            tma_load_2d(g_smem_u32(st), &tmDY, r * 32 * NG + h * C::KCH, (int)m0, full0 + 8 * s);
+            bulk_load_1d(g_smem_u32(st + C::A_SUB),
+                         reinterpret_cast<const unsigned char*>(a.wpack) + ((size_t)e * C::NSUB + h) * C::B_SUB, C::B_SUB,
+                         full0 + 8 * s);
         }
     } else if (warp_u == 1) {
-        const int nk_u = __shfl_sync(0xffffffffu, nk, 0);
+        const int nk_u = __shfl_sync(0xffffffffu, nk, 0) * C::NSUB;
         const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem, 0);
         for (int i = 0; i < nk_u; ++i) {
             const int s = i % C::STAGES;
@@ -662,14 +662,11 @@ __global__ void __launch_bounds__(128) tc_gemm_nn_kernel(const __grid_constant__
             const uint32_t base = g_smem_u32(smem + s * C::STAGE);
             if (out_elect_one()) {
 #pragma unroll
-                for (int h = 0; h < C::NSUB; ++h)
-#pragma unroll
-                    for (int kk = 0; kk < C::KCH / 16; ++kk) {
-                        const uint64_t ad = umma_smem_desc(base + h * C::A_SUB + kk * 32, 16, C::SBO, C::SW);
-                        const uint64_t bd =
-                            umma_smem_desc(base + C::NSUB * C::A_SUB + h * C::B_SUB + kk * 32, 16, C::SBO, C::SW);
-                        umma_bf16(tmem_u, ad, bd, IDESC, (i > 0 || h > 0 || kk > 0) ? 1u : 0u);
-                    }
+                for (int kk = 0; kk < C::KCH / 16; ++kk) {
+                    const uint64_t ad = umma_smem_desc(base + kk * 32, 16, C::SBO, C::SW);
+                    const uint64_t bd = umma_smem_desc(base + C::A_SUB + kk * 32, 16, C::SBO, C::SW);
+                    umma_bf16(tmem_u, ad, bd, IDESC, (i > 0 || kk > 0) ? 1u : 0u);
+                }
                 umma_commit(empty0 + 8 * s);
             }
             __syncwarp();
