@@ -347,6 +347,24 @@ def _padded_rows(g, T, B, H, ldH):
 _out_info = native.out_info
 
 
+# The bf16 copy of the most recent LSTM layer output (written by the recurrent kernel next to the fp32 h).  The MLP
+# heads that consume that output are separate modules; they recognise their input as an unmodified view of the cached
+# buffer (same storage, offset, strides and version counter) and reuse the copy instead of casting h again.
+_LAST_H = [None]
+
+
+def _cached_bf16_of(x, ld):
+    c = _LAST_H[0]
+    if c is None:
+        return None
+    h_pad, hb, version = c
+    if (x.dim() == 2 and x.stride() == (ld, 1) and hb.shape == (x.shape[0], ld) and x._version == version and
+            x.storage_offset() == h_pad.storage_offset() and
+            x.untyped_storage().data_ptr() == h_pad.untyped_storage().data_ptr()):
+        return hb
+    return None
+
+
 def _bf16_rows(x2d, ld):
     out = torch.empty(x2d.shape[0], ld, device=x2d.device, dtype=torch.bfloat16)
     native.cast_bf16(x2d, out)
@@ -407,6 +425,7 @@ class LSTMLayerTCFunction(torch.autograd.Function):
         native.lstm_tc_fwd(ph, cfg, fwd_pack, pre_raw, rt.drop, rt.drop_scalar, rt.act, T, B, h_pad.view(M, ldH), hb, c, gates,
                            bn)
         rt.hb_out = hb
+        _LAST_H[0] = (h_pad, hb, h_pad._version)
         if need_grad:
             ctx.rt = rt
             ctx.cfg = cfg
@@ -471,6 +490,8 @@ class MLPLayerTCFunction(torch.autograd.Function):
         dev = x.device
         xb = rt.xb_in
         if xb is None or xb.shape != (N, native.pad8(D)):
+            xb = _cached_bf16_of(x, native.pad8(D))
+        if xb is None:
             xb = _bf16_rows(x if x.stride(-1) == 1 else x.contiguous(), native.pad8(D))
         cw = rt.q_ws[0] if rt.q_ws is not None else w
         px = rt.plan_x
