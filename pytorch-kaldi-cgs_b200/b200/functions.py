@@ -461,10 +461,12 @@ class LSTMLayerTCFunction(torch.autograd.Function):
                              dgam, dbet, _ws(dev, 4 * ldH))
         else:
             dproj_b = dpre_b
-        dus = [torch.zeros(H, H, device=dev, dtype=torch.float32) for _ in range(4)]
+        # the eight weight gradients are views of ONE zero-filled buffer (one fill instead of eight)
+        wflat = torch.zeros(4 * H * H + 4 * H * D, device=dev, dtype=torch.float32)
+        dus = [wflat[g * H * H:(g + 1) * H * H].view(H, H) for g in range(4)]
+        dws = [wflat[4 * H * H + g * H * D:4 * H * H + (g + 1) * H * D].view(H, D) for g in range(4)]
         if T > 1:
             native.tc_sddmm(rt.plan_h, 4, dpre_b[B:], hb[:M - B], dus, rt.mask_h)
-        dws = [torch.zeros(H, D, device=dev, dtype=torch.float32) for _ in range(4)]
         native.tc_sddmm(rt.plan_x, 4, dproj_b, xb, dws, rt.mask_x)
         dx = None
         if ctx.needs_input_grad[0]:
