@@ -545,6 +545,11 @@ def main():
     rec = ['lstm_tc_fwd', 'lstm_tc_bwd'] if args.precision == 'bf16' else ['lstm_fwd', 'lstm_bwd']
     timers = KernelTimers(rec)
     sampler = ClockSampler(local)
+    # no cyclic-GC pass inside the timed regions: a generation-2 collection stalls the launching thread for tens of
+    # milliseconds (seen once as a 33 ms step among 30 ms ones)
+    import gc
+    gc.collect()
+    gc.disable()
     sync_all()
     sampler.start()
     native.reset_launch_count()
@@ -608,6 +613,7 @@ def main():
     e3.record()
     sync_all()
     ms_e2e = e2.elapsed_time(e3)
+    gc.enable()
     assert len(losses) == args.steps and all(np.isfinite(losses)), losses
 
     hbm_peak, tf_peak, peak_kind = measured_peaks()
