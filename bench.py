@@ -478,9 +478,9 @@ def main():
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
     ap.add_argument('--seq-len', type=int, default=256, help='padded minibatch length T (cfg max_seq_length_train <= 1000)')
-    ap.add_argument('--batch', type=int, default=528,
-                    help='sequences per GPU per optimizer step (528 = 33 clusters of 16 sequences: every co-resident '
-                         'cluster slot of the recurrent kernels is used)')
+    ap.add_argument('--batch', type=int, default=None,
+                    help='sequences per GPU per optimizer step (default 528 = 33 clusters of 16 sequences: every '
+                         'co-resident cluster slot of the recurrent kernels is used; libri: 224)')
     ap.add_argument('--precision', default='bf16', choices=['bf16', 'fp32'],
                     help='bf16 = tensor-core build (BASELINE configs[1] "bf16 train"), fp32 = CUDA-core parity build')
     ap.add_argument('--no-cpu-baseline', action='store_true')
@@ -491,6 +491,10 @@ def main():
     select_config(args.config)
     if args.config != 'timit':
         args.no_cpu_baseline = True
+    if args.batch is None:
+        # whole waves of co-resident clusters of the recurrent kernels: 33 clusters of 4 CTAs at H = 550 (16 sequences
+        # each), 7 clusters of 16 CTAs at H = 1024 -> 2 waves = 224 sequences
+        args.batch = 528 if args.config == 'timit' else 224
 
     from b200 import dist as bdist
     if args.impl == 'reference':
