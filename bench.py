@@ -188,6 +188,13 @@ def algorithmic_work(name, a):
             plan, n_w, src, dst = a[0], a[1], a[3], a[4]
             m = src.shape[0]
             return m * (src.shape[1] * 2 + dst.shape[1] * 4), 2 * m * plan.nz_tiles * 1024 * n_w
+        if name == 'tc_gemm_nt_split':   # (plan, n_w, wpack2, x_hi, x_lo, y): algorithmic FLOPs of ONE product (3 issued)
+            plan, n_w, xh, dst = a[0], a[1], a[3], a[5]
+            m = xh.shape[0]
+            return m * (2 * xh.shape[1] * 2 + dst.shape[1] * 4), 2 * m * plan.nz_tiles * 1024 * n_w
+        if name == 'split_bf16':         # (x2d, hi, lo)
+            x, hi, lo = a[0], a[1], a[2]
+            return x.shape[0] * (x.shape[1] * 4 + lo.shape[1] * 2 * (2 if hi is not None else 1)), 0
         if name == 'tc_sddmm':           # (plan, n_w, dy_bf16, x_bf16, dws, mask)
             plan, n_w, dy, x = a[0], a[1], a[2], a[3]
             m = dy.shape[0]
@@ -213,7 +220,8 @@ class KernelTimers:
              'lstm_fwd', 'lstm_bwd', 'logsoftmax_fwd', 'logsoftmax_bwd', 'act_fwd', 'act_bwd', 'quantize_w',
              'quantize_act', 'nll_fwd_bwd', 'bn_fwd_il', 'bn_bwd_il', 'lstm_tc_pack', 'lstm_tc_fwd', 'lstm_tc_bwd',
              'tc_pack_nt', 'tc_gemm_nt', 'tc_pack_nn', 'tc_gemm_nn', 'tc_sddmm', 'cast_bf16', 'out_pack',
-             'out_logsoftmax_prior_fwd', 'bn_stats_il', 'logsoftmax_bwd_fused']
+             'out_logsoftmax_prior_fwd', 'bn_stats_il', 'logsoftmax_bwd_fused', 'tc_pack_nt_split',
+             'tc_gemm_nt_split', 'split_bf16']
 
     def __init__(self, names=None):
         from b200 import native
@@ -306,7 +314,8 @@ def run_export(dev, nets_train, args, T, B, rank, world, hbm_peak, peak_kind):
     with torch.no_grad():
         for s in range(3):
             fwd(resident[s % len(resident)])
-        names = ['out_logsoftmax_prior_fwd', 'lstm_tc_fwd', 'tc_gemm_nt'] if args.precision == 'bf16' else ['lstm_fwd']
+        names = (['out_logsoftmax_prior_fwd', 'lstm_tc_fwd', 'tc_gemm_nt', 'tc_gemm_nt_split', 'split_bf16']
+                 if args.precision == 'bf16' else ['lstm_fwd'])
         timers = KernelTimers(names)
         sync_all()
         native.reset_launch_count()
@@ -651,7 +660,7 @@ def main():
         byts, flops = kwork[dom][0] / kcnt[dom], kwork[dom][1] / kcnt[dom]
         roof['algorithmic_bytes_per_launch'] = byts
         roof['algorithmic_flops_per_launch'] = flops
-        if dom in ('tc_gemm_nt', 'tc_gemm_nn', 'tc_sddmm'):
+        if dom in ('tc_gemm_nt', 'tc_gemm_nt_split', 'tc_gemm_nn', 'tc_sddmm'):
             ach = flops / (avg_ms * 1e-3) / 1e12
             roof.update(bound='tensor', achieved=ach, peak=tf_peak, unit='TFLOP/s', frac=ach / tf_peak)
         else:

@@ -214,7 +214,16 @@ int hcgs_lstm_tc_bwd(const hcgs_plan* plan, int cluster_size, int nb, const uint
  * hcgs_tc_gemm_nt stats (optional, n_w = 4 only): [ceil(m/128)][ldy][2] floats; the epilogue writes, per
  *   128-row tile and output column, {mean, M2} of that tile's rows -- the batch-norm statistics of the
  *   projections at no extra pass over them (merged by hcgs_bn_stats_il).
- * hcgs_cast_bf16 : fp32 [rows, cols] -> bf16 [rows, ldo], pad columns zeroed.                  */
+ * hcgs_cast_bf16 : fp32 [rows, cols] -> bf16 [rows, ldo], pad columns zeroed.
+ * Two-term ("split") forward products -- the projections W{f,i,o,c}x.x (neural_networks.py:951-954) and the
+ *   hidden MLP layers (:306) of the tensor-core build: each fp32 operand is carried as hi + lo with
+ *   hi = bf16(v), lo = bf16(v - hi) (16 mantissa bits) and the product is x_hi w_hi + x_lo w_hi + x_hi w_lo
+ *   (three tcgen05 products per kept k tile, fp32 accumulation; the lo*lo term, 2^-16 relative, is dropped).
+ *   This is what keeps the log-posteriors within 1e-4 of the reference's fp32 path (tools/bf16_attribution.py:
+ *   the single-term projections alone cost 1.8e-4).
+ *   hcgs_tc_pack_nt_split: wpack2 needs 2 * nz_tiles * 32*n_w * 32 bf16 ([hi tile | lo tile] per kept tile).
+ *   hcgs_tc_gemm_nt_split: x_hi / x_lo bf16 [m, ldx_hi] / [m, ldx_lo]; otherwise as hcgs_tc_gemm_nt.
+ *   hcgs_split_bf16: fp32 [rows, cols] -> hi (may be NULL) and lo, bf16 [rows, ldo], pad columns zeroed. */
 int hcgs_tc_pack_nt(const hcgs_plan* plan, int n_w, const float* const* w, int ldw, void* wpack,
                     hcgs_stream stream);
 int hcgs_tc_gemm_nt(const hcgs_plan* plan, int n_w, const void* wpack, const void* x_bf16, int64_t ldx,
@@ -222,6 +231,13 @@ int hcgs_tc_gemm_nt(const hcgs_plan* plan, int n_w, const void* wpack, const voi
                     hcgs_stream stream);
 int hcgs_cast_bf16(const float* x, int64_t ldx, int64_t rows, int cols, void* out, int64_t ldo,
                    hcgs_stream stream);
+int hcgs_tc_pack_nt_split(const hcgs_plan* plan, int n_w, const float* const* w, int ldw, void* wpack2,
+                          hcgs_stream stream);
+int hcgs_tc_gemm_nt_split(const hcgs_plan* plan, int n_w, const void* wpack2, const void* x_hi, int64_t ldx_hi,
+                          const void* x_lo, int64_t ldx_lo, int64_t m, const float* const* bias, float* y,
+                          int64_t ldy, float* stats, hcgs_stream stream);
+int hcgs_split_bf16(const float* x, int64_t ldx, int64_t rows, int cols, void* hi, void* lo, int64_t ldo,
+                    hcgs_stream stream);
 /* hcgs_tc_pack_nn / hcgs_tc_gemm_nn: dX[m,k] = sum_{u,g} dY[m,(u,g)] W_g[u,k]; wpack same size as for nt;
  *   dY bf16 [m, lddy] (lddy = padded n_out * n_w, pad columns zero); dX fp32 [m, lddx].
  * hcgs_tc_sddmm: dW_g[u,k] += mask[u,k] * sum_m dY[m,(u,g)] X[m,k] inside kept tiles only (fp32 atomics:

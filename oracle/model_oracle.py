@@ -60,13 +60,38 @@ class _RoundGrad(torch.autograd.Function):
         return _bf(g)
 
 
+class _SplitLinear(torch.autograd.Function):
+    """forward: x_hi w_hi^T + x_lo w_hi^T + x_hi w_lo^T (hi = bf16(v), lo = bf16(v - hi)), fp32 accumulate;
+    backward: the single-term bf16 products of the tensor-core build (dx = bf16(g) w_hi, dw = bf16(g)^T x_hi)."""
+
+    @staticmethod
+    def forward(ctx, x, w):
+        xh, wh = _bf(x), _bf(w)
+        xl, wl = _bf(x - xh), _bf(w - wh)
+        ctx.save_for_backward(xh, wh)
+        return F.linear(xh, wh) + F.linear(xl, wh) + F.linear(xh, wl)
+
+    @staticmethod
+    def backward(ctx, g):
+        xh, wh = ctx.saved_tensors
+        gb = _bf(g)
+        dx = gb @ wh
+        dw = gb.reshape(-1, gb.shape[-1]).t() @ xh.reshape(-1, xh.shape[-1])
+        return dx, dw
+
+
 def linear(x, w, b=None, bf16=False):
     """F.linear; with bf16=True the three matrix products of the layer (forward, dX, dW) take bf16-rounded
     operands (x, w, and the incoming gradient) and accumulate in fp32 -- the arithmetic of the tensor-core
-    build (spec key 'bf16_operands').  Bias and its gradient stay fp32."""
+    build (spec key 'bf16_operands').  bf16='split': the forward product takes two-term bf16 operands (the
+    projections and hidden MLP layers of the tensor-core build, hcgs_tc_gemm_nt_split), backward as bf16=True.
+    Bias and its gradient stay fp32."""
     if not bf16:
         return F.linear(x, w, b)
-    y = _RoundGrad.apply(F.linear(_ste(x, _bf(x.detach())), _ste(w, _bf(w.detach()))))
+    if bf16 == 'split':
+        y = _SplitLinear.apply(x, w)
+    else:
+        y = _RoundGrad.apply(F.linear(_ste(x, _bf(x.detach())), _ste(w, _bf(w.detach()))))
     return y if b is None else y + b
 
 
@@ -109,6 +134,7 @@ def lstm_forward(p, spec, x, drop_masks, training):
     with torch.bernoulli on the CPU generator (:843-845); in eval the scalar (1-p) is used (:847).
     BN running statistics in `p` are updated in place when training (momentum 0.05)."""
     bfo = bool(spec.get('bf16_operands', False))
+    bfp = ('split' if spec.get('proj_terms', 2) == 2 else True) if bfo else False   # projections: two-term operands
     for i, H in enumerate(spec['lay']):
         T, B, _ = x.shape
         drop = drop_masks[i] if training else torch.tensor([1 - spec['drop'][i]])
@@ -130,7 +156,7 @@ def lstm_forward(p, spec, x, drop_masks, training):
             xin = quantize_inp_t(x, spec['quant_inp'], 4)                 # four gate linears re-quantise x
         pre = {}
         for g in GATES:
-            out = linear(xin, w[g], None, bfo)                            # :951-954
+            out = linear(xin, w[g], None, bfp)                            # :951-954
             if spec['use_bn'][i]:
                 k = 'bn_w%sx.%d.' % (g, i)
                 out = F.batch_norm(out.view(T * B, H), p[k + 'running_mean'], p[k + 'running_var'], p[k + 'weight'],
@@ -168,7 +194,10 @@ def mlp_forward(p, spec, x, training, drop_masks=None):
             w = quantize_w_t(w, spec['quant'])
         if spec.get('quant_inp', 0):
             x = quantize_inp_t(x, spec['quant_inp'], 1)
-        z = linear(x, w, b, bool(spec.get('bf16_operands', False)))
+        bfo = bool(spec.get('bf16_operands', False))
+        if bfo and spec['act'][i] != 'softmax' and spec.get('proj_terms', 2) == 2:
+            bfo = 'split'                                                 # hidden layers: two-term operands
+        z = linear(x, w, b, bfo)
         if spec['use_bn'][i]:
             k = 'bn.%d.' % i
             z = F.batch_norm(z, p[k + 'running_mean'], p[k + 'running_var'], p[k + 'weight'], p[k + 'bias'],

@@ -39,6 +39,9 @@ class LayerRuntime:
         # this layer's output for the next one (saves a cast pass per layer)
         self.xb_in = None
         self.hb_out = None
+        # forward products of the projections / hidden MLP layers with two-term bf16 operands (hi + lo, three
+        # tcgen05 products per k tile): keeps the posteriors within 1e-4 of the fp32 reference
+        self.split_fwd = True
 
 
 def _ws(device, n_cols):
@@ -371,6 +374,36 @@ def _bf16_rows(x2d, ld):
     return out
 
 
+def _rows_2d(x, M, D):
+    x2d = x.reshape(M, D)     # a [:, :, :D] view of a padded buffer stays a view (row pitch = the padded width)
+    return x2d if x2d.stride(-1) == 1 else x2d.contiguous()
+
+
+def _split_rows(x2d, ld, hi=None):
+    """(hi, lo) bf16 [rows, ld] with hi = bf16(x), lo = bf16(x - hi); an existing hi copy is reused."""
+    lo = torch.empty(x2d.shape[0], ld, device=x2d.device, dtype=torch.bfloat16)
+    if hi is None:
+        hi = torch.empty_like(lo)
+        native.split_bf16(x2d, hi, lo)
+    else:
+        native.split_bf16(x2d, None, lo)
+    return hi, lo
+
+
+def _gemm_nt_fwd(plan, ws, xb, xl, y, biases=None, stats=None):
+    """forward product of one layer: two-term operands when xl is given, else the plain bf16 product"""
+    n_w = len(ws)
+    dev = y.device
+    if xl is not None:
+        wpack = torch.empty(2 * plan.nz_tiles * 32 * n_w * 32, device=dev, dtype=torch.bfloat16)
+        native.tc_pack_nt_split(plan, ws, wpack)
+        native.tc_gemm_nt_split(plan, n_w, wpack, xb, xl, y, biases, stats)
+    else:
+        wpack = torch.empty(plan.nz_tiles * 32 * n_w * 32, device=dev, dtype=torch.bfloat16)
+        native.tc_pack_nt(plan, ws, wpack)
+        native.tc_gemm_nt(plan, n_w, wpack, xb, y, biases, stats)
+
+
 class LSTMLayerTCFunction(torch.autograd.Function):
     """One HCGS LSTM layer on the tensor-core build (same math as LSTMLayerFunction)."""
 
@@ -386,21 +419,21 @@ class LSTMLayerTCFunction(torch.autograd.Function):
         us = rt.q_us if rt.q_us is not None else [uf, ui, uo, uc]
         need_grad = any(ctx.needs_input_grad)
         xb = rt.xb_in
-        if xb is None or xb.shape != (M, ldD):
-            x2d = x.reshape(M, D)
-            if x2d.stride(-1) != 1:
-                x2d = x2d.contiguous()
-            xb = _bf16_rows(x2d, ldD)
+        if xb is not None and xb.shape != (M, ldD):
+            xb = None
+        xl = None
+        if rt.split_fwd:
+            xb, xl = _split_rows(_rows_2d(x, M, D), ldD, xb)
+        elif xb is None:
+            xb = _bf16_rows(_rows_2d(x, M, D), ldD)
         px = rt.plan_x
-        wpack = torch.empty(px.nz_tiles * 32 * 4 * 32, device=dev, dtype=torch.bfloat16)
-        native.tc_pack_nt(px, ws, wpack)
         pre_raw = torch.empty(M, 4 * ldH, device=dev, dtype=torch.float32)
         save_mean = save_invstd = bn = None
         if rt.use_bn:
             # statistics come out of the GEMM epilogue (per 128-row tile), the normalisation itself is
             # applied inside the recurrent kernel: the projections are written once and read once
             part = torch.empty((M + 127) // 128, 4 * ldH, 2, device=dev, dtype=torch.float32) if rt.training else None
-            native.tc_gemm_nt(px, 4, wpack, xb, pre_raw, None, part)
+            _gemm_nt_fwd(px, ws, xb, xl, pre_raw, None, part)
             save_mean = torch.empty(4 * ldH, device=dev, dtype=torch.float32)
             save_invstd = torch.empty(4 * ldH, device=dev, dtype=torch.float32)
             rms = [r[0] for r in rt.bn_running]
@@ -409,7 +442,8 @@ class LSTMLayerTCFunction(torch.autograd.Function):
                                save_mean, save_invstd)
             bn = (save_mean, save_invstd, [gf, gi, go, gc], [bf, bi, bo, bc])
         else:
-            native.tc_gemm_nt(px, 4, wpack, xb, pre_raw)
+            _gemm_nt_fwd(px, ws, xb, xl, pre_raw)
+        del xl
         ph = rt.plan_h
         cfg = tc_config_for(ph, B)
         fwd_pack = torch.empty(cfg.fwd_pack_u32, device=dev, dtype=torch.int32)
@@ -513,10 +547,13 @@ class MLPLayerTCFunction(torch.autograd.Function):
                 ctx.save_for_backward(xb, cw, gamma, None, None, None)
                 ctx.dims = (N, D, O)
             return out
-        wpack = torch.empty(px.nz_tiles * 32 * 32, device=dev, dtype=torch.bfloat16)
-        native.tc_pack_nt(px, [cw], wpack)
         z = torch.empty(N, O, device=dev, dtype=torch.float32)
-        native.tc_gemm_nt(px, 1, wpack, xb, z, [b] if b is not None else None)
+        xl = None
+        if rt.split_fwd and not rt.softmax:
+            # hidden layers: two-term operands; output (softmax) layers stay single-term like the fused kernel
+            _, xl = _split_rows(x if x.stride(-1) == 1 else x.contiguous(), native.pad8(D), xb)
+        _gemm_nt_fwd(px, [cw], xb, xl, z, [b] if b is not None else None)
+        del xl
         save_mean = save_invstd = None
         if rt.use_bn:
             zb = torch.empty_like(z)

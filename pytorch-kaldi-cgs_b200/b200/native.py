@@ -69,6 +69,10 @@ SIGNATURES = {
     'hcgs_tc_pack_nt': (c_int, [c_void_p, c_int, _pp, c_int, _f, c_void_p]),
     'hcgs_tc_gemm_nt': (c_int, [c_void_p, c_int, _f, _f, c_int64, c_int64, _pp, _f, c_int64, _f, c_void_p]),
     'hcgs_cast_bf16': (c_int, [_f, c_int64, c_int64, c_int, _f, c_int64, c_void_p]),
+    'hcgs_tc_pack_nt_split': (c_int, [c_void_p, c_int, _pp, c_int, _f, c_void_p]),
+    'hcgs_tc_gemm_nt_split': (c_int, [c_void_p, c_int, _f, _f, c_int64, _f, c_int64, c_int64, _pp, _f, c_int64, _f,
+                                      c_void_p]),
+    'hcgs_split_bf16': (c_int, [_f, c_int64, c_int64, c_int, _f, _f, c_int64, c_void_p]),
     'hcgs_tc_pack_nn': (c_int, [c_void_p, c_int, _pp, c_int, _f, c_void_p]),
     'hcgs_tc_gemm_nn': (c_int, [c_void_p, c_int, _f, _f, c_int64, c_int64, _f, c_int64, c_void_p]),
     'hcgs_tc_sddmm': (c_int, [c_void_p, c_int, _f, c_int64, _f, c_int64, c_int64, _pp, c_int64, _f, c_void_p]),
@@ -111,6 +115,7 @@ KERNELS_PER_CALL = {'hcgs_mask_apply': 1, 'hcgs_quantize_w': 1, 'hcgs_quantize_a
                     'hcgs_lstm_pack': 2, 'hcgs_lstm_fwd': 1, 'hcgs_lstm_bwd': 1,
                     'hcgs_lstm_tc_pack': 2, 'hcgs_lstm_tc_fwd': 1, 'hcgs_lstm_tc_bwd': 1,
                     'hcgs_tc_pack_nt': 1, 'hcgs_tc_gemm_nt': 1, 'hcgs_cast_bf16': 1,
+                    'hcgs_tc_pack_nt_split': 1, 'hcgs_tc_gemm_nt_split': 1, 'hcgs_split_bf16': 1,
                     'hcgs_tc_pack_nn': 1, 'hcgs_tc_gemm_nn': 1, 'hcgs_tc_sddmm': 1, 'hcgs_out_pack': 1,
                     'hcgs_out_logsoftmax_prior_fwd': 1, 'hcgs_act_fwd': 1, 'hcgs_act_bwd': 1,
                     'hcgs_logsoftmax_fwd': 1, 'hcgs_logsoftmax_bwd': 1, 'hcgs_logsoftmax_bwd_fused': 1,
@@ -474,6 +479,38 @@ def tc_gemm_nt(plan, n_w, wpack, x_bf16, y, biases=None, stats=None):
     assert x_bf16.dtype == torch.bfloat16 and x_bf16.dim() == 2 and x_bf16.stride(1) == 1
     _check(load().hcgs_tc_gemm_nt(plan.handle, int(n_w), _ptr(wpack), _ptr(x_bf16), x_bf16.stride(0), x_bf16.shape[0],
                                   _ptrs(biases), _ptr(y), y.stride(0), _ptr(stats), _stream()), 'hcgs_tc_gemm_nt')
+
+
+def tc_pack_nt_split(plan, weights, wpack2):
+    """wpack2: bf16 CUDA tensor of 2 * plan.nz_tiles * 32*len(weights) * 32 elements ([hi | lo] per kept tile)."""
+    _require_cuda(*weights)
+    _require_cuda_any(wpack2)
+    assert wpack2.dtype == torch.bfloat16 and wpack2.numel() >= 2 * plan.nz_tiles * 32 * len(weights) * 32
+    _check(load().hcgs_tc_pack_nt_split(plan.handle, len(weights), _ptrs(weights), _row_major_2d(weights[0], 'w'),
+                                        _ptr(wpack2), _stream()), 'hcgs_tc_pack_nt_split')
+
+
+def tc_gemm_nt_split(plan, n_w, wpack2, x_hi, x_lo, y, biases=None, stats=None):
+    """tc_gemm_nt with two-term operands: y = x_hi w_hi^T + x_lo w_hi^T + x_hi w_lo^T (fp32 accumulate)."""
+    _require_cuda(y, stats)
+    assert stats is None or (stats.is_contiguous() and stats.numel() == (x_hi.shape[0] + 127) // 128 * y.stride(0) * 2)
+    _require_cuda_any(wpack2, x_hi, x_lo)
+    for t in (x_hi, x_lo):
+        assert t.dtype == torch.bfloat16 and t.dim() == 2 and t.stride(1) == 1
+    assert x_hi.shape[0] == x_lo.shape[0]
+    _check(load().hcgs_tc_gemm_nt_split(plan.handle, int(n_w), _ptr(wpack2), _ptr(x_hi), x_hi.stride(0), _ptr(x_lo),
+                                        x_lo.stride(0), x_hi.shape[0], _ptrs(biases), _ptr(y), y.stride(0),
+                                        _ptr(stats), _stream()), 'hcgs_tc_gemm_nt_split')
+
+
+def split_bf16(x2d, hi, lo):
+    """fp32 rows -> hi = bf16(x) (hi may be None: only the residual is wanted) and lo = bf16(x - hi)."""
+    _require_cuda(x2d)
+    _require_cuda_any(hi, lo)
+    assert lo.dtype == torch.bfloat16 and lo.shape[0] == x2d.shape[0] and lo.stride(1) == 1
+    assert hi is None or (hi.dtype == torch.bfloat16 and hi.shape == lo.shape and hi.stride(0) == lo.stride(0))
+    _check(load().hcgs_split_bf16(_ptr(x2d), _row_major_2d(x2d, 'x'), x2d.shape[0], x2d.shape[1], _ptr(hi), _ptr(lo),
+                                  lo.stride(0), _stream()), 'hcgs_split_bf16')
 
 
 def tc_pack_nn(plan, weights, wpack):

@@ -211,9 +211,11 @@ namespace hcgs {
 // ---- weight packing: masked dense fp32 -> pre-swizzled bf16 tiles ------------------------------
 // nt tiles, CSR order (tile t = (r, c) from the plan's flat list): [32*NG rows n = u*NG+g][32 k],
 // 64-byte rows in the SWIZZLE_64B pattern (16-byte chunk index ^= (row >> 1) & 3).
+// split = 1 (two-term operands, hcgs_tc_pack_nt_split): tile t becomes the pair [hi tile | lo tile] with
+// hi = bf16(w), lo = bf16(w - hi): hi + lo carries 16 mantissa bits of the fp32 master.
 template <int NG>
 __global__ void tc_pack_nt_kernel(const int* __restrict__ tile_rc, int nz, PtrPack<const float> W, int ldw,
-                                  int n_out, int n_in, __nv_bfloat16* __restrict__ out) {
+                                  int n_out, int n_in, __nv_bfloat16* __restrict__ out, int split) {
     const int64_t total = (int64_t)nz * 32 * NG * 4;  // 16-byte chunks
     for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
          idx += (int64_t)gridDim.x * blockDim.x) {
@@ -223,7 +225,7 @@ __global__ void tc_pack_nt_kernel(const int* __restrict__ tile_rc, int nz, PtrPa
         const int r = tile_rc[2 * t], c = tile_rc[2 * t + 1];
         const int u = n / NG, g = n % NG;
         const int row = r * 32 + u, col0 = c * 32 + c16 * 8;
-        uint32_t w[4];
+        uint32_t w[4], w2[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             float lo = 0.f, hi = 0.f;
@@ -233,10 +235,14 @@ __global__ void tc_pack_nt_kernel(const int* __restrict__ tile_rc, int nz, PtrPa
             }
             const __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
             w[j] = *reinterpret_cast<const uint32_t*>(&v);
+            const __nv_bfloat162 r2 = __floats2bfloat162_rn(lo - __low2float(v), hi - __high2float(v));
+            w2[j] = *reinterpret_cast<const uint32_t*>(&r2);
         }
-        unsigned char* dst = reinterpret_cast<unsigned char*>(out) + (size_t)t * (32 * NG * 64) + n * 64 +
+        const size_t tile_bytes = 32 * NG * 64;
+        unsigned char* dst = reinterpret_cast<unsigned char*>(out) + (size_t)t * tile_bytes * (split ? 2 : 1) + n * 64 +
                              ((c16 ^ ((n >> 1) & 3)) << 4);
         *reinterpret_cast<uint4*>(dst) = make_uint4(w[0], w[1], w[2], w[3]);
+        if (split) *reinterpret_cast<uint4*>(dst + tile_bytes) = make_uint4(w2[0], w2[1], w2[2], w2[3]);
     }
 }
 
@@ -251,6 +257,7 @@ struct TcNtArgs {
     int n_out;                   // output units (rows of one W_g)
     PtrPack<const float> bias;   // per gate [n_out] or NULL
     float* stats;                // optional [m-tiles][ldy][2]: per 128-row tile and column {mean, M2} (batch norm)
+    int split;                   // 1: two-term operands, three products per k tile (x_hi w_hi + x_lo w_hi + x_hi w_lo)
 };
 
 constexpr int NT_STAGES = 4;
@@ -266,7 +273,8 @@ __host__ __device__ constexpr int nt_smem_bytes() {
 }
 
 template <int NG>
-__global__ void __launch_bounds__(128) tc_gemm_nt_kernel(const __grid_constant__ CUtensorMap tmX, const TcNtArgs a) {
+__global__ void __launch_bounds__(128) tc_gemm_nt_kernel(const __grid_constant__ CUtensorMap tmX,
+                                                         const __grid_constant__ CUtensorMap tmXlo, const TcNtArgs a) {
     constexpr int BN = 32 * NG;
     constexpr int B_BYTES = BN * 64;
     constexpr int TCOLS = BN < 32 ? 32 : BN;
@@ -285,7 +293,9 @@ __global__ void __launch_bounds__(128) tc_gemm_nt_kernel(const __grid_constant__
     const int warp_u = __shfl_sync(0xffffffffu, warp, 0);  // provably warp-uniform copy (see out_elect_one)
     const int r = blockIdx.x;
     const int64_t m0 = (int64_t)blockIdx.y * 128;
-    const int k0 = a.row_ptr[r], nk = a.row_ptr[r + 1] - k0;
+    const int k0 = a.row_ptr[r];
+    // pipeline items: one per kept k tile, or three in split mode (the lo x lo term, 2^-16 relative, is dropped)
+    const int nk = (a.row_ptr[r + 1] - k0) * (a.split ? 3 : 1);
 
     if (warp == 0 && lane == 0) {
         for (int s = 0; s < NT_STAGES; ++s) {
@@ -307,10 +317,16 @@ __global__ void __launch_bounds__(128) tc_gemm_nt_kernel(const __grid_constant__
             const int s = i % NT_STAGES;
             if (i >= NT_STAGES) g_mbar_wait(empty0 + 8 * s, (uint32_t)(((i / NT_STAGES) - 1) & 1));
             g_mbar_expect_tx(full0 + 8 * s, NT_A_BYTES + B_BYTES);
-            tma_load_2d(g_smem_u32(sA + s * NT_A_BYTES), &tmX, a.col_idx[k0 + i] * 32, (int)m0, full0 + 8 * s);
-            bulk_load_1d(g_smem_u32(sB + s * B_BYTES),
-                         reinterpret_cast<const unsigned char*>(a.wpack) + (size_t)(k0 + i) * B_BYTES, B_BYTES,
-                         full0 + 8 * s);
+            int kt = i, piece = 0;
+            if (a.split) {
+                kt = i / 3;
+                piece = i - 3 * kt;
+            }
+            tma_load_2d(g_smem_u32(sA + s * NT_A_BYTES), piece == 1 ? &tmXlo : &tmX, a.col_idx[k0 + kt] * 32, (int)m0,
+                        full0 + 8 * s);
+            const size_t wtile = a.split ? (size_t)(k0 + kt) * 2 + (piece == 2 ? 1 : 0) : (size_t)(k0 + kt);
+            bulk_load_1d(g_smem_u32(sB + s * B_BYTES), reinterpret_cast<const unsigned char*>(a.wpack) + wtile * B_BYTES,
+                         B_BYTES, full0 + 8 * s);
         }
     } else if (warp_u == 1) {
         // ---- MMA issuer (convergent warp, elected lane) -----------------------------------------
@@ -459,8 +475,8 @@ __global__ void __launch_bounds__(128) tc_gemm_nt_kernel(const __grid_constant__
 
 using namespace hcgs;
 
-extern "C" int hcgs_tc_pack_nt(const hcgs_plan* plan, int n_w, const float* const* w, int ldw, void* wpack,
-                               hcgs_stream stream) {
+static int tc_pack_nt_impl(const hcgs_plan* plan, int n_w, const float* const* w, int ldw, void* wpack, int split,
+                           hcgs_stream stream) {
     HCGS_REQUIRE(plan && w && wpack, "hcgs_tc_pack_nt: NULL argument");
     HCGS_REQUIRE(n_w == 1 || n_w == 4, "hcgs_tc_pack_nt: n_w must be 1 or 4");
     if (plan->nz_tiles == 0) return 0;
@@ -469,26 +485,42 @@ extern "C" int hcgs_tc_pack_nt(const hcgs_plan* plan, int n_w, const float* cons
     cudaStream_t st = (cudaStream_t)stream;
     if (n_w == 4)
         tc_pack_nt_kernel<4><<<blocks, 256, 0, st>>>(plan->d_tile_rc, plan->nz_tiles, make_pack<const float>(w, 4), ldw,
-                                                     plan->n_out, plan->n_in, (__nv_bfloat16*)wpack);
+                                                     plan->n_out, plan->n_in, (__nv_bfloat16*)wpack, split);
     else
         tc_pack_nt_kernel<1><<<blocks, 256, 0, st>>>(plan->d_tile_rc, plan->nz_tiles, make_pack<const float>(w, 1), ldw,
-                                                     plan->n_out, plan->n_in, (__nv_bfloat16*)wpack);
+                                                     plan->n_out, plan->n_in, (__nv_bfloat16*)wpack, split);
     HCGS_LAUNCH_CHECK();
     return 0;
 }
 
-extern "C" int hcgs_tc_gemm_nt(const hcgs_plan* plan, int n_w, const void* wpack, const void* x_bf16, int64_t ldx,
-                               int64_t m, const float* const* bias, float* y, int64_t ldy, float* stats,
+extern "C" int hcgs_tc_pack_nt(const hcgs_plan* plan, int n_w, const float* const* w, int ldw, void* wpack,
                                hcgs_stream stream) {
+    return tc_pack_nt_impl(plan, n_w, w, ldw, wpack, 0, stream);
+}
+
+extern "C" int hcgs_tc_pack_nt_split(const hcgs_plan* plan, int n_w, const float* const* w, int ldw, void* wpack2,
+                                     hcgs_stream stream) {
+    return tc_pack_nt_impl(plan, n_w, w, ldw, wpack2, 1, stream);
+}
+
+static int tc_gemm_nt_impl(const hcgs_plan* plan, int n_w, const void* wpack, const void* x_bf16, int64_t ldx,
+                           const void* x_lo, int64_t ldx_lo, int64_t m, const float* const* bias, float* y,
+                           int64_t ldy, float* stats, hcgs_stream stream) {
     HCGS_REQUIRE(plan && wpack && x_bf16 && y, "hcgs_tc_gemm_nt: NULL argument");
     HCGS_REQUIRE(stats == nullptr || n_w == 4, "hcgs_tc_gemm_nt: fused column statistics need n_w = 4");
     HCGS_REQUIRE(n_w == 1 || n_w == 4, "hcgs_tc_gemm_nt: n_w must be 1 or 4");
     if (m <= 0) return 0;
     HCGS_REQUIRE(ldy >= (int64_t)plan->tr * 32 * n_w || ldy >= (int64_t)plan->n_out * n_w,
                  "hcgs_tc_gemm_nt: ldy too small");
-    CUtensorMap tm;
+    CUtensorMap tm, tml;
     if (int rc = make_tmap_bf16(&tm, x_bf16, m, plan->n_in, ldx, 32, 128, CU_TENSOR_MAP_SWIZZLE_64B)) return rc;
+    if (x_lo) {
+        if (int rc = make_tmap_bf16(&tml, x_lo, m, plan->n_in, ldx_lo, 32, 128, CU_TENSOR_MAP_SWIZZLE_64B)) return rc;
+    } else {
+        tml = tm;
+    }
     TcNtArgs a;
+    a.split = x_lo ? 1 : 0;
     a.wpack = (const __nv_bfloat16*)wpack;
     a.row_ptr = plan->d_row_ptr;
     a.col_idx = plan->d_col_idx;
@@ -505,14 +537,28 @@ extern "C" int hcgs_tc_gemm_nt(const hcgs_plan* plan, int n_w, const void* wpack
     if (n_w == 4) {
         HCGS_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm_nt_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              nt_smem_bytes<4>()));
-        tc_gemm_nt_kernel<4><<<grid, 128, nt_smem_bytes<4>(), st>>>(tm, a);
+        tc_gemm_nt_kernel<4><<<grid, 128, nt_smem_bytes<4>(), st>>>(tm, tml, a);
     } else {
         HCGS_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm_nt_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              nt_smem_bytes<1>()));
-        tc_gemm_nt_kernel<1><<<grid, 128, nt_smem_bytes<1>(), st>>>(tm, a);
+        tc_gemm_nt_kernel<1><<<grid, 128, nt_smem_bytes<1>(), st>>>(tm, tml, a);
     }
     HCGS_LAUNCH_CHECK();
     return 0;
+}
+
+extern "C" int hcgs_tc_gemm_nt(const hcgs_plan* plan, int n_w, const void* wpack, const void* x_bf16, int64_t ldx,
+                               int64_t m, const float* const* bias, float* y, int64_t ldy, float* stats,
+                               hcgs_stream stream) {
+    return tc_gemm_nt_impl(plan, n_w, wpack, x_bf16, ldx, nullptr, 0, m, bias, y, ldy, stats, stream);
+}
+
+extern "C" int hcgs_tc_gemm_nt_split(const hcgs_plan* plan, int n_w, const void* wpack2, const void* x_hi,
+                                     int64_t ldx_hi, const void* x_lo, int64_t ldx_lo, int64_t m,
+                                     const float* const* bias, float* y, int64_t ldy, float* stats,
+                                     hcgs_stream stream) {
+    HCGS_REQUIRE(x_lo != nullptr, "hcgs_tc_gemm_nt_split: x_lo is NULL");
+    return tc_gemm_nt_impl(plan, n_w, wpack2, x_hi, ldx_hi, x_lo, ldx_lo, m, bias, y, ldy, stats, stream);
 }
 
 // fp32 [rows, cols] (ld = ldx) -> bf16 [rows, ldo] with zero pad columns (cols <= ldo)
@@ -530,6 +576,38 @@ __global__ void cast_bf16_kernel(const float* __restrict__ x, int64_t ldx, int64
     }
 }
 }  // namespace hcgs
+
+namespace hcgs {
+// two-term split of fp32 rows: hi = bf16(x) (optional output), lo = bf16(x - hi); pad columns zero
+__global__ void split_bf16_kernel(const float* __restrict__ x, int64_t ldx, int64_t rows, int cols,
+                                  __nv_bfloat16* __restrict__ hi, __nv_bfloat16* __restrict__ lo, int64_t ldo) {
+    const int64_t total = rows * (ldo / 2);
+    for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+         idx += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = idx / (ldo / 2);
+        const int c = (int)(idx - r * (ldo / 2)) * 2;
+        const float a = c < cols ? __ldg(x + r * ldx + c) : 0.f;
+        const float b = c + 1 < cols ? __ldg(x + r * ldx + c + 1) : 0.f;
+        const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+        if (hi) *reinterpret_cast<__nv_bfloat162*>(hi + r * ldo + c) = h;
+        *reinterpret_cast<__nv_bfloat162*>(lo + r * ldo + c) =
+            __floats2bfloat162_rn(a - __low2float(h), b - __high2float(h));
+    }
+}
+}  // namespace hcgs
+
+extern "C" int hcgs_split_bf16(const float* x, int64_t ldx, int64_t rows, int cols, void* hi, void* lo, int64_t ldo,
+                               hcgs_stream stream) {
+    HCGS_REQUIRE(x && lo, "hcgs_split_bf16: NULL argument");
+    HCGS_REQUIRE(ldo >= cols && (ldo & 1) == 0, "hcgs_split_bf16: ldo must be even and >= cols");
+    if (rows <= 0) return 0;
+    const int64_t total = rows * (ldo / 2);
+    const int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 16);
+    split_bf16_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(x, ldx, rows, cols, (__nv_bfloat16*)hi,
+                                                                (__nv_bfloat16*)lo, ldo);
+    HCGS_LAUNCH_CHECK();
+    return 0;
+}
 
 extern "C" int hcgs_cast_bf16(const float* x, int64_t ldx, int64_t rows, int cols, void* out, int64_t ldo,
                               hcgs_stream stream) {

@@ -121,8 +121,15 @@ class _PlanCache:
     def __init__(self):
         self._store = {}
 
+    def clear(self):
+        for hit in self._store.values():
+            hit[1].destroy()
+        self._store = {}
+
     def get(self, key, sources, build_mask, shape, recurrent):
-        """sources: the mask tensors the structural mask is derived from (may be empty = dense);
+        """sources: the mask Parameters / tensors the structural mask is derived from (may be empty = dense) --
+        the objects themselves, NOT their `.data` (a `.data` alias carries its own version counter that never
+        moves, so an in-place change such as load_state_dict's copy_ would go unnoticed);
         build_mask(): returns the structural 0/1 mask (only called on a miss)."""
         sig = tuple((m.data_ptr(), m._version, tuple(m.shape)) for m in sources)
         hit = self._store.get(key)
@@ -189,6 +196,9 @@ class MLP(nn.Module):
         _parse_pattern_options(self, options, 'mlp')
         self.arch_name = _opt(options, 'arch_name', 'MLP')
         self.b200_precision = _opt(options, 'b200_precision', 'fp32')
+        # bf16 build only: 2 (default) = two-term bf16 operands in the forward projections (posteriors within 1e-4 of
+        # the fp32 reference), 1 = single bf16 term (faster, ~2e-4)
+        self.b200_proj_terms = int(_opt(options, 'b200_proj_terms', '2'))
 
         self.test_flag = self.to_do != 'train'
         first_eval = self.to_do in ('forward', 'valid')
@@ -253,17 +263,18 @@ class MLP(nn.Module):
             current_input = self.dnn_lay[i]
         self.out_dim = current_input
         self._plans = _PlanCache()
+        self.register_load_state_dict_post_hook(lambda module, incompatible: module._plans.clear())
         self.log_prior = None   # set by the export path to fuse `- log(counts/sum)` (core.py:244-245)
 
     # -- mask bookkeeping ------------------------------------------------------------------------
     def _mask_factors(self, i):
         f = []
         if self.mlp_hcgs:
-            f.append(self.hcgs[i].mask.data)
+            f.append(self.hcgs[i].mask)
         if self.guided_hcgs and self.apply_guided_hcgs:
-            f.append(self.ghcgs[i].mask.data)
+            f.append(self.ghcgs[i].mask)
         if self.if_pattern and len(self.pattern_mask) > i:
-            f.append(self.pattern_mask[i].data)
+            f.append(self.pattern_mask[i])
         return f
 
     def _apply_masks(self, i):
@@ -318,6 +329,7 @@ class MLP(nn.Module):
                 raise NotImplementedError('dnn_use_laynorm together with dnn_use_batchnorm on one layer is not built')
             lin = self.wx[i]
             rt = LayerRuntime()
+            rt.split_fwd = self.b200_proj_terms == 2
             factors = self._mask_factors(i)
             rt.plan_x, rt.mask_x = self._plans.get(
                 i, factors, lambda f=factors: _structural_mask([f]), (self.dnn_lay[i], lin.weight.shape[1]), False)
@@ -446,6 +458,9 @@ class LSTM(nn.Module):
         _parse_pattern_options(self, options, 'lstm')
         self.arch_name = _opt(options, 'arch_name', 'LSTM')
         self.b200_precision = _opt(options, 'b200_precision', 'fp32')
+        # bf16 build only: 2 (default) = two-term bf16 operands in the forward projections (posteriors within 1e-4 of
+        # the fp32 reference), 1 = single bf16 term (faster, ~2e-4)
+        self.b200_proj_terms = int(_opt(options, 'b200_proj_terms', '2'))
 
         self.test_flag = self.to_do != 'train'
         first_eval = self.to_do in ('forward', 'valid')
@@ -533,6 +548,7 @@ class LSTM(nn.Module):
             current_input = 2 * H if self.bidir else H
         self.out_dim = self.lstm_lay[-1] + self.bidir * self.lstm_lay[-1]
         self._plans = _PlanCache()
+        self.register_load_state_dict_post_hook(lambda module, incompatible: module._plans.clear())
 
     # -- helpers ---------------------------------------------------------------------------------
     def _lin(self, kind, gate, i):
@@ -548,11 +564,11 @@ class LSTM(nn.Module):
         for n in self._names(kind):
             f = []
             if self.lstm_hcgs:
-                f.append((self.hcgsx if kind == 'w' else self.hcgsh)[i].mask.data)
+                f.append((self.hcgsx if kind == 'w' else self.hcgsh)[i].mask)
             if self.guided_hcgs and self.apply_guided_hcgs:
-                f.append(getattr(self, 'ghcgs_' + n)[i].mask.data)
+                f.append(getattr(self, 'ghcgs_' + n)[i].mask)
             if self.if_pattern and len(self.pattern_mask['pattern_mask_' + n]) > i:
-                f.append(self.pattern_mask['pattern_mask_' + n][i].data)
+                f.append(self.pattern_mask['pattern_mask_' + n][i])
             lists.append(f)
         return lists
 
@@ -647,6 +663,7 @@ class LSTM(nn.Module):
                 raise NotImplementedError('lstm_use_laynorm (LayerNorm of h_t inside the time loop, reference '
                                           'neural_networks.py:1092-1093) is not built into the recurrent kernels')
             rt = LayerRuntime()
+            rt.split_fwd = self.b200_proj_terms == 2
             # drop mask: same for all time steps, NOT rescaled; drawn on the CPU generator (:843-851)
             if self.test_flag == False:  # noqa: E712 (reference spelling)
                 drop_mask = torch.bernoulli(torch.Tensor(B, H).fill_(1 - self.lstm_drop[i]))

@@ -79,6 +79,61 @@ def test_tc_gemm_nt(n_out, n_in, blocks, drops, n_w, M):
     plan.destroy()
 
 
+@pytest.mark.parametrize('n_out,n_in,blocks,drops,n_w,M', CASES)
+def test_tc_gemm_nt_split(n_out, n_in, blocks, drops, n_w, M):
+    """two-term operands: x_hi w_hi + x_lo w_hi + x_hi w_lo against float64 on the same split operands (2e-5) and
+    against the un-rounded fp32 product (the point of the split: 2^-15 instead of 2^-8 per operand)."""
+    from b200 import native
+    torch.manual_seed(n_out + n_in + M + 2)
+    mask = random_mask(n_out, n_in, blocks, drops, 7) if blocks else torch.ones(n_out, n_in)
+    plan = native.Plan(mask)
+    d = dev()
+    ws = [torch.randn(n_out, n_in) * mask for _ in range(n_w)]
+    x = torch.randn(M, n_in)
+    bias = [torch.randn(n_out) for _ in range(n_w)] if n_w == 1 else None
+    ldx = native.pad8(n_in)
+    xh = torch.full((M, ldx), 5.0, device=d, dtype=torch.bfloat16)
+    xl = torch.full((M, ldx), 5.0, device=d, dtype=torch.bfloat16)
+    native.split_bf16(x.to(d), xh, xl)
+    xh_ref = bf(x)
+    xl_ref = bf(x - xh_ref)
+    assert torch.equal(xh[:, :n_in].float().cpu(), xh_ref) and torch.equal(xl[:, :n_in].float().cpu(), xl_ref)
+    assert ldx == n_in or (xh[:, n_in:].float().abs().max() == 0 and xl[:, n_in:].float().abs().max() == 0)
+    # lo only (the hi copy already exists: the recurrent kernel's bf16 h)
+    xl2 = torch.empty_like(xl)
+    native.split_bf16(x.to(d), None, xl2)
+    assert torch.equal(xl2, xl)
+    wpack = torch.empty(2 * max(plan.nz_tiles, 1) * 32 * n_w * 32, device=d, dtype=torch.bfloat16)
+    native.tc_pack_nt_split(plan, [w.to(d) for w in ws], wpack)
+    ldo = native.pad8(n_out) if n_w == 4 else n_out
+    y = torch.full((M, ldo * n_w), 9.0, device=d)
+    part = torch.full(((M + 127) // 128, ldo * 4, 2), 7.0, device=d) if n_w == 4 else None
+    native.tc_gemm_nt_split(plan, n_w, wpack, xh, xl, y, [b.to(d) for b in bias] if bias else None, part)
+    torch.cuda.synchronize()
+    refs, exact = [], []
+    for g, w in enumerate(ws):
+        wh = bf(w)
+        wl = bf(w - wh)
+        b = bias[g].double() if bias else 0
+        refs.append(xh_ref.double() @ wh.double().t() + xl_ref.double() @ wh.double().t() +
+                    xh_ref.double() @ wl.double().t() + b)
+        exact.append(x.double() @ w.double().t() + b)
+    got = y.cpu().view(M, ldo, n_w)[:, :n_out, :]
+    close(got, torch.stack(refs, 2), 2e-5, 'nt split vs split operands')
+    close(got, torch.stack(exact, 2), 6e-5, 'nt split vs exact product')
+    if ldo > n_out and n_w == 4:
+        assert y.view(M, ldo, n_w)[:, n_out:, :].abs().max().item() == 0
+    if n_w == 4:
+        sm = torch.empty(ldo * 4, device=d)
+        si = torch.empty(ldo * 4, device=d)
+        rm = [torch.zeros(n_out, device=d) for _ in range(4)]
+        rv = [torch.ones(n_out, device=d) for _ in range(4)]
+        native.bn_stats_il(part, 128, M, 4, n_out, ldo, rm, rv, 1e-5, 0.05, True, sm, si)
+        yy = y.cpu().view(M, ldo, 4)[:, :n_out, :].double()
+        close(sm.cpu().view(ldo, 4)[:n_out], yy.mean(0), 1e-5, 'bn mean (split)')
+    plan.destroy()
+
+
 def _dy_layout(dy_list, M, n_out, n_w, ld_units):
     """list of per-gate [M, n_out] -> bf16-able fp32 [M, ld_units*n_w], column u*n_w+g, pad columns zero"""
     out = torch.zeros(M, ld_units, n_w)

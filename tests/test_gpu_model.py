@@ -344,3 +344,29 @@ def test_input_norms_and_layernorm_train_steps_match_reference_fixture():
                 close(nets['LSTM_layers'].bn0.running_var, 0.95 + 0.05 * ln.var(0, unbiased=True), 1e-5, 'bn0 running var')
             for o in opts.values():
                 o.step()
+
+
+def test_plan_follows_masks_replaced_by_load_state_dict():
+    """a mask changed in place after the first forward (load_state_dict copies into the same storage)
+    must rebuild the block index -- the packing IS the masking in the recurrent and GEMM kernels."""
+    T, B, D = 7, 4, 12
+    x = torch.randn(T, B, D, generator=torch.Generator().manual_seed(0)).cuda()
+    for prec in ('fp32', 'bf16'):
+        over = dict(b200_precision=prec)
+        nets_a, _ = build_product_nets('valid', seed=1, device='cuda', lstm_over=over, mlp_over=over)
+        nets_b, _ = build_product_nets('valid', seed=2, device='cuda', lstm_over=over, mlp_over=over)
+        for n in list(nets_a.values()) + list(nets_b.values()):
+            n.save_mat = False
+        a, b = nets_a['LSTM_layers'], nets_b['LSTM_layers']
+        assert not torch.equal(a.hcgsh[0].mask, b.hcgsh[0].mask)
+        with torch.no_grad():
+            a(x)                                   # builds plans for a's own masks
+            want = b(x).clone()
+            a.load_state_dict(b.state_dict())      # in-place copy: same storage, new mask values
+            got = a(x)
+            ha, hb = nets_a['MLP_layers'], nets_b['MLP_layers']
+            ha(got.reshape(T * B, -1))
+            ha.load_state_dict(hb.state_dict())
+            pa, pb = ha(got.reshape(T * B, -1)), hb(want.reshape(T * B, -1))
+        assert torch.equal(got, want), prec
+        assert torch.equal(pa, pb), prec

@@ -1,16 +1,19 @@
 """Tensor-core build (b200_precision = bf16) at model level.
 
-Oracle: oracle/model_oracle.py with spec['bf16_operands'] = True, i.e. the reference's operator sequence in
-which every matrix product (forward, dX, dW) takes bf16-rounded operands and accumulates in fp32 -- exactly
-what the tcgen05 / mma.sync kernels compute.  What is left is summation order, the fast exp forms of the
-recurrent kernel (abs 1e-6) and the occasional flip of a bf16 rounding of h, hence the tolerances below:
+Two oracles, both oracle/model_oracle.py:
+  (1) the fp32 operator sequence -- the one PINNED to the reference by tests/test_oracle_pinned.py.  The north
+      star's bound "posteriors max-abs <= 1e-4 for bf16-accumulate modes" is asserted against THIS oracle, at
+      the benchmarked shape in time (T = 256) -- test_bf16_posteriors_within_1e4_of_fp32_reference_path.
+      (Forward projections and hidden MLP layers run with two-term bf16 operands for that purpose; the
+      recurrent product and the output layer with single bf16 operands: tools/bf16_attribution.py.)
+  (2) the same sequence with spec['bf16_operands'] = True, i.e. exactly the roundings the kernels apply
+      (two-term forward projections, bf16 recurrent / output / backward products, fp32 accumulation).  What is
+      left is summation order, the fast exp forms of the recurrent kernel (abs 1e-6) and the occasional flip of
+      a bf16 rounding of h:
 
-    log-posteriors      max-abs <= 1e-4 (the north star's bf16 bound; measured 4e-5 at 4x550/1944)
-    loss                rel <= 1e-4
-    gradients           mean-abs <= 2e-3 of the tensor max, max-abs <= 5e-2 of the tensor max
-
-Against the fp32 oracle the same run differs by the bf16 operand rounding itself; that gap is measured and
-bounded too (loss rel <= 2e-2) so a gross error in the rounding points cannot hide."""
+    log-posteriors      max-abs <= 1e-4 vs (2) AND vs (1)
+    loss                rel <= 1e-4 vs (2)
+    gradients           mean-abs <= 2e-3 of the tensor max, max-abs <= 5e-2 of the tensor max vs (2)"""
 import json
 import os
 
@@ -136,7 +139,7 @@ def test_bf16_train_step_matches_bf16_operand_oracle(H, layers, T, B, P):
         out = graph.forward(inp.cuda(), T, B, 'train', ['out_dnn2'])
     out['loss_final'].backward()
     torch.cuda.synchronize()
-    assert native.LAUNCHES.get('hcgs_lstm_tc_fwd', 0) == layers and native.LAUNCHES.get('hcgs_tc_gemm_nt', 0) > 0
+    assert native.LAUNCHES.get('hcgs_lstm_tc_fwd', 0) == layers and native.LAUNCHES.get('hcgs_tc_gemm_nt_split', 0) == layers
     assert 'hcgs_lstm_fwd' not in native.LAUNCHES and 'hcgs_bsgemm_nt' not in native.LAUNCHES
     rep = {}
     rep['loss'] = (out['loss_final'].item(), ref['loss_final'].item())
@@ -172,7 +175,124 @@ def test_bf16_train_step_matches_bf16_operand_oracle(H, layers, T, B, P):
     assert rep['logp'][0] <= 1e-4, 'log-posteriors max-abs %.3e (mean %.3e)' % rep['logp'][:2]
     # h: a bf16 rounding flip of one h element is 2^-9 relative, hence the loose max and the tight mean
     assert rep['h'][1] <= 2e-4 and rep['h'][0] <= 2e-2, 'lstm output max-abs %.3e mean-abs %.3e' % rep['h'][:2]
-    assert abs(rep['loss'][0] - rep['loss_fp32']) <= 2e-2 * abs(rep['loss_fp32'])
+    assert abs(rep['loss'][0] - rep['loss_fp32']) <= 1e-4 * abs(rep['loss_fp32'])
+    # the reference-pinned fp32 path: the north-star bound itself
+    assert rep['logp_vs_fp32'][0] <= 1e-4, 'log-posteriors vs fp32 oracle max-abs %.3e' % rep['logp_vs_fp32'][0]
+
+
+def _big_nets(H, layers, P, to_do, seed=2234, terms='2'):
+    D = 40
+    lay = ','.join([str(H)] * layers)
+    lstm_over = dict(lstm_lay=lay, lstm_drop=','.join(['0.2'] * layers), lstm_use_laynorm=','.join(['False'] * layers),
+                     lstm_use_batchnorm=','.join(['True'] * layers), lstm_act=','.join(['tanh'] * layers),
+                     hcgsx_block='32,4', hcgsx_sparse='75,62.5', hcgsh_block='32,4', hcgsh_sparse='75,62.5',
+                     b200_precision='bf16', b200_proj_terms=terms)
+    mlp_over = dict(dnn_lay=str(P), hcgs_block='64,4', hcgs_sparse='50,25', b200_precision='bf16',
+                    b200_proj_terms=terms)
+    nets, sections = build_product_nets(to_do, D=D, seed=seed, lstm_over=lstm_over, mlp_over=mlp_over, device='cuda')
+    specs = golden_specs(dict(lay=[H] * layers, act=['tanh'] * layers, use_bn=[True] * layers, drop=[0.2] * layers))
+    specs['cd']['lay'] = [P]
+    return nets, sections, specs, D
+
+
+@pytest.mark.parametrize('H,layers,T,B,P', [(550, 4, 256, 32, 1944), (1024, 2, 256, 16, 3480)])
+def test_bf16_posteriors_within_1e4_of_fp32_reference_path(H, layers, T, B, P):
+    """The benchmarked shape in time (T = 256): train-mode forward of the tensor-core build against the fp32
+    oracle (pinned to the reference), north-star bound max-abs <= 1e-4 on the log-posteriors."""
+    nets, _, specs, D = _big_nets(H, layers, P, 'train')
+    params = _state_to_cpu(nets)
+    gen = torch.Generator().manual_seed(3)
+    inp = torch.zeros(T, B, D + 2)
+    inp[:, :, :D] = torch.randn(T, B, D, generator=gen)
+    inp[:, :, D] = torch.randint(0, P, (T, B), generator=gen).float()
+    inp[:, :, D + 1] = torch.randint(0, 5, (T, B), generator=gen).float()
+    inp[T - 40:, B - 2:, :] = 0       # right-padded short sequences
+    drops = [torch.bernoulli(torch.full((B, H), 0.8), generator=gen) for _ in range(layers)]
+    with torch.no_grad():
+        ref32 = model_oracle.model_forward(params, specs, inp, D, True, drops)
+        with _ReplayBernoulli(drops):
+            out = make_graph(nets, D).forward(inp.cuda(), T, B, 'train', ['out_dnn2'])
+    torch.cuda.synchronize()
+    mx, mean, _ = _err(out['out_dnn2'], ref32['out_dnn2'])
+    rep = {'logp_vs_fp32': (mx, mean), 'loss': (out['loss_final'].item(), ref32['loss_final'].item())}
+    try:
+        os.makedirs(REPORT, exist_ok=True)
+        with open(os.path.join(REPORT, 'bf16_vs_fp32_T%d_H%d_L%d.json' % (T, H, layers)), 'w') as f:
+            json.dump(rep, f, indent=1)
+    except OSError:
+        pass
+    assert mx <= 1e-4, 'log-posteriors vs fp32 oracle at T=%d: max-abs %.3e (mean %.3e)' % (T, mx, mean)
+    assert abs(rep['loss'][0] - rep['loss'][1]) <= 1e-4 * abs(rep['loss'][1]), rep['loss']
+
+
+def test_bf16_single_term_option_is_the_old_arithmetic():
+    """b200_proj_terms = 1 keeps the single-term projections (faster, ~2e-4 from fp32): still within 1e-4 of ITS
+    bf16-operand restatement."""
+    H, layers, T, B, P = 550, 2, 40, 8, 1944
+    nets, _, specs, D = _big_nets(H, layers, P, 'train', terms='1')
+    params = _state_to_cpu(nets)
+    gen = torch.Generator().manual_seed(4)
+    inp = torch.zeros(T, B, D + 2)
+    inp[:, :, :D] = torch.randn(T, B, D, generator=gen)
+    drops = [torch.bernoulli(torch.full((B, H), 0.8), generator=gen) for _ in range(layers)]
+    for sp in specs.values():
+        sp['bf16_operands'] = True
+        sp['proj_terms'] = 1
+    from b200 import native
+    native.reset_launch_count()
+    with torch.no_grad():
+        ref = model_oracle.model_forward(params, specs, inp, D, True, drops)
+        with _ReplayBernoulli(drops):
+            out = make_graph(nets, D).forward(inp.cuda(), T, B, 'train', ['out_dnn2'])
+    assert 'hcgs_tc_gemm_nt_split' not in native.LAUNCHES and native.LAUNCHES.get('hcgs_tc_gemm_nt', 0) >= layers
+    mx, mean, _ = _err(out['out_dnn2'], ref['out_dnn2'])
+    assert mx <= 1e-4, (mx, mean)
+
+
+def test_bf16_three_train_steps_do_not_drift():
+    """three optimizer steps on the tensor-core build against the bf16-operand oracle driven by torch RMSprop on
+    the CPU: loss rel <= 1e-3 and posteriors max-abs <= 5e-4 at every step (the updates feed the rounding points)."""
+    H, layers, T, B, P = 550, 2, 30, 8, 1944
+    nets, sections, specs, D = _big_nets(H, layers, P, 'train')
+    for sp in specs.values():
+        sp['bf16_operands'] = True
+    params = _state_to_cpu(nets)
+    leafs = {}
+    for k, d in params.items():
+        for n, v in d.items():
+            if v.dtype == torch.float32 and not n.endswith(('running_mean', 'running_var', 'mask')):
+                v.requires_grad_(True)
+                leafs[(k, n)] = v
+    from b200.graph import make_optimizer
+    opts = {n: make_optimizer(nets[n], sec) for n, sec in zip(nets, sections)}
+    lr = {'lstm': 0.0016, 'cd': 0.0016, 'mono': 0.0004}
+    ref_opts = {k: torch.optim.RMSprop([v for (kk, _), v in leafs.items() if kk == k], lr=lr[k], alpha=0.95, eps=1e-8)
+                for k in params}
+    gen = torch.Generator().manual_seed(5)
+    graph = make_graph(nets, D)
+    for step in range(3):
+        inp = torch.zeros(T, B, D + 2)
+        inp[:, :, :D] = torch.randn(T, B, D, generator=gen)
+        inp[:, :, D] = torch.randint(0, P, (T, B), generator=gen).float()
+        inp[:, :, D + 1] = torch.randint(0, 5, (T, B), generator=gen).float()
+        drops = [torch.bernoulli(torch.full((B, H), 0.8), generator=gen) for _ in range(layers)]
+        ref = model_oracle.model_forward(params, specs, inp, D, True, drops)
+        for o in ref_opts.values():
+            o.zero_grad()
+        ref['loss_final'].backward()
+        with _ReplayBernoulli(drops):
+            out = graph.forward(inp.cuda(), T, B, 'train', ['out_dnn2'])
+        for o in opts.values():
+            o.zero_grad()
+        out['loss_final'].backward()
+        a, b = out['loss_final'].item(), ref['loss_final'].item()
+        mx, mean, _ = _err(out['out_dnn2'], ref['out_dnn2'])
+        assert abs(a - b) <= 1e-3 * abs(b), (step, a, b)
+        assert mx <= 5e-4, (step, mx, mean)
+        for o in opts.values():
+            o.step()
+        for o in ref_opts.values():
+            o.step()
 
 
 def test_bf16_eval_forward_with_prior():
@@ -208,4 +328,13 @@ def test_bf16_eval_forward_with_prior():
         hh = nets['LSTM_layers'](x.cuda())
         got = nets['MLP_layers'](hh.view(T * B, -1))
     mx, mean, sc = _err(got, ref)
-    assert mean <= 2e-5 and mx <= 2e-4, 'posterior max-abs %.3e mean-abs %.3e' % (mx, mean)
+    assert mean <= 2e-5 and mx <= 1e-4, 'posterior max-abs %.3e mean-abs %.3e' % (mx, mean)
+    # ... and against the fp32 (reference-pinned) path: the north-star bound on exported posteriors
+    for sp in specs.values():
+        sp['bf16_operands'] = False
+    with torch.no_grad():
+        h32 = model_oracle.lstm_forward(params['lstm'], specs['lstm'], x, None, False)
+        ref32 = model_oracle.mlp_forward(params['cd'], specs['cd'], h32.view(T * B, -1), False)
+    ref32 = model_oracle.posterior(ref32.numpy(), counts.numpy())
+    mx32, mean32, _ = _err(got, ref32)
+    assert mx32 <= 1e-4, 'posterior vs fp32 oracle max-abs %.3e mean-abs %.3e' % (mx32, mean32)
