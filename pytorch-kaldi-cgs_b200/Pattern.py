@@ -159,10 +159,13 @@ def apply_patterns(raw_w, kernel):
     if unsq:
         w = w.unsqueeze(2)
     w = w.permute(2, 0, 1)
-    out = F.conv2d(w.unsqueeze(1), kernel, stride=stride, padding=0)
+    # fp32 scores: a TF32 convolution (the cuDNN default on the device) could move the per-block arg-max
+    with torch.backends.cudnn.flags(enabled=True, allow_tf32=False):
+        out = F.conv2d(w.unsqueeze(1), kernel, stride=stride, padding=0)
     out_max = torch.max(out, dim=1)[0].unsqueeze(1).repeat(1, kernel.size(0), 1, 1)
     idx = torch.where(out >= out_max, torch.ones_like(out), torch.zeros_like(out))
-    mask = F.conv_transpose2d(idx, kernel, bias=None, stride=stride, padding=0, output_padding=0, groups=1)
+    with torch.backends.cudnn.flags(enabled=True, allow_tf32=False):
+        mask = F.conv_transpose2d(idx, kernel, bias=None, stride=stride, padding=0, output_padding=0, groups=1)
     mask = mask.squeeze(1).permute(1, 2, 0)
     if unsq:
         mask = mask.squeeze(2)

@@ -580,6 +580,14 @@ class LSTM(nn.Module):
         if self.guided_hcgs and self.apply_guided_hcgs:
             for n, w in zip(names, ws):
                 native.mask_apply([w], getattr(self, 'ghcgs_' + n)[i].mask.data)
+        if self.if_pattern and kind == 'w':
+            # same place as the reference (:876-884): after the HCGS / guided masks of W, before pruning and before
+            # the HCGS mask of U; mines patterns and masks on first use, then masks all eight matrices of all layers
+            if self.pattern['pattern_wfx'] == []:
+                self.update_patterns()
+            if self.pattern_mask['pattern_mask_wfx'] == []:
+                self.update_mask()
+            self.update_weight()
         if self.prune:
             for n, w in zip(names, ws):
                 m = prune(getattr(self, n)[i], self.prune_perc[i])
@@ -673,14 +681,7 @@ class LSTM(nn.Module):
                 rt.drop = None
                 rt.drop_scalar = 1 - self.lstm_drop[i]
             with torch.no_grad():
-                if self.if_pattern:
-                    if self.pattern['pattern_wfx'] == []:
-                        self.update_patterns()
-                    if self.pattern_mask['pattern_mask_wfx'] == []:
-                        self.update_mask()
                 self._apply_masks('w', i)
-                if self.if_pattern:
-                    self.update_weight()
                 self._side_effects('w', i)
                 self._apply_masks('u', i)
                 self._side_effects('u', i)

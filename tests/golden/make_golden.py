@@ -105,7 +105,7 @@ MODEL_2HEAD = ['out_dnn1=compute(LSTM_layers,fbank)', 'out_dnn2=compute(MLP_laye
                'loss_final=sum(loss_cd,loss_mono_w)', 'err_final=cost_err(out_dnn2,lab_cd)']
 
 
-def build_config(to_do, lstm_over=None, mlp_over=None, out_folder=''):
+def build_config(to_do, lstm_over=None, mlp_over=None, out_folder='', mono_over=None):
     cfg = configparser.ConfigParser()
     cfg['exp'] = dict(use_cuda='False', to_do=to_do, multi_gpu='False', seed='2234', out_folder=out_folder)
     a1 = dict(LSTM_OPTS, out_folder=out_folder)
@@ -113,14 +113,16 @@ def build_config(to_do, lstm_over=None, mlp_over=None, out_folder=''):
     a2 = dict(MLP_OPTS, out_folder=out_folder)
     a2.update(mlp_over or {})
     a3 = dict(a2, arch_name='MLP_layers2', dnn_lay='5', mlp_hcgs='False', arch_lr='0.0004')
+    a3.update(mono_over or {})
     cfg['architecture1'], cfg['architecture2'], cfg['architecture3'] = a1, a2, a3
     return cfg
 
 
-def run_model(tag, to_do, T=7, B=3, D=12, lstm_over=None, mlp_over=None, steps=1, seed=2234):
+def run_model(tag, to_do, T=7, B=3, D=12, lstm_over=None, mlp_over=None, steps=1, seed=2234, mono_over=None,
+              extra=None):
     """One (or a few) reference train steps / one eval forward; returns a dict of arrays."""
     tmp = tempfile.mkdtemp()
-    cfg = build_config(to_do, lstm_over, mlp_over, out_folder=tmp)
+    cfg = build_config(to_do, lstm_over, mlp_over, out_folder=tmp, mono_over=mono_over)
     torch.manual_seed(seed)
     np.random.seed(seed)
     fea_dict = {'fbank': ['scp', 'opts', 0, 0, 0, 0, D, D]}
@@ -184,6 +186,8 @@ def run_model(tag, to_do, T=7, B=3, D=12, lstm_over=None, mlp_over=None, steps=1
         for k, v in nns[net].state_dict().items():
             out['final/%s/%s' % (net, k)] = v.detach().numpy().copy()
     out['dims'] = np.array([T, B, D, steps])
+    if extra is not None:
+        extra(out, nns)
     np.savez_compressed(os.path.join(HERE, tag + '.npz'), **out)
     print(tag + '.npz', 'loss', out.get('loss/0'))
     return out, nns
@@ -249,7 +253,112 @@ def gen_norm_inp():
               steps=2, seed=8)
 
 
+# ---- pattern masks -----------------------------------------------------------------------
+def _cpu_cuda_shim():
+    """SURVEY 8(c) shim 3: sparsity/sparsity.py:1045, 1125, 1131 call .cuda() unconditionally; on this GPU-less
+    host Tensor.cuda() becomes the identity (nothing else of the reference is touched)."""
+    torch.Tensor.cuda = lambda self, *a, **k: self
+
+
+def gen_patterns():
+    """Pattern.Pattern (pattern / coo / pattern_coo, drawn and file-backed pattern sets), sparsity.apply_patterns
+    (incl. ties: overlapping patterns add up to mask values of 2) and sparsity.find_top_k_by_kmeans."""
+    _cpu_cuda_shim()
+    import Pattern as ref_pattern
+    from sparsity import sparsity as ref_sp
+    out = {}
+    cases = []
+    k = 0
+    for (r, c, seed) in ((64, 40, 21), (32, 48, 22)):
+        for mode in ('pattern', 'coo', 'pattern_coo'):
+            for from_file in ('', 'b08b08_k04_n16_pattern.npy', 'b08b08_k04_n16_pattern_v1.npy',
+                              'b08b08_k04_n16_pattern_v2.npy'):
+                if from_file and mode == 'coo':
+                    continue
+                torch.manual_seed(seed)
+                w = torch.randn(r, c)
+                np.random.seed(seed)
+                if from_file:
+                    # Pattern.get_pattern tests and loads the module-level name `pattern_from_file`, which the
+                    # reference never defines (Pattern.py:63-67, a NameError as shipped); the harness provides it
+                    ref_pattern.pattern_from_file = os.path.join(REF, 'pattern_file', from_file)
+                m = ref_pattern.Pattern(w.numpy(), mode, [8, 8], 4, 16, '', pattern_from_file=bool(from_file))
+                mask = m.mask.detach().numpy()
+                assert mask.dtype == np.float64 and set(np.unique(mask)) <= {0.0, 1.0}
+                out['w_%d' % k] = w.numpy()
+                out['bits_%d' % k] = np.packbits(mask.astype(np.uint8))
+                out['next_rand_%d' % k] = np.array([np.random.randint(0, 2 ** 31 - 1)])
+                cases.append(repr((r, c, mode, from_file, seed)))
+                k += 1
+    out['cases'] = np.array(cases)
+    for f in ('b08b08_k04_n16_pattern.npy', 'b08b08_k04_n16_pattern_v1.npy', 'b08b08_k04_n16_pattern_v2.npy'):
+        out['file/' + f] = np.packbits(np.load(os.path.join(REF, 'pattern_file', f)).astype(np.uint8))
+    # apply_patterns on fixed kernels; kernel set B contains a duplicated and an overlapping pattern => ties => 2s
+    pats = np.split(np.load(os.path.join(REF, 'pattern_file', 'b08b08_k04_n16_pattern.npy')), 16, 0)
+    kern_a = torch.from_numpy(np.stack(pats)[:, None].astype(np.float32))
+    kern_b = kern_a.clone()
+    kern_b[1] = kern_b[0]
+    torch.manual_seed(31)
+    w = torch.randn(48, 64)
+    w[8:16, 0:8] = 1.0        # a constant block: every pattern with 4 ones ties
+    for name, kern in (('a', kern_a), ('b', kern_b)):
+        mask = ref_sp.apply_patterns(w, kern)
+        out['apply_%s_kernel' % name] = kern.numpy()
+        out['apply_%s_mask' % name] = mask.numpy()
+    assert out['apply_b_mask'].max() >= 2.0
+    out['apply_w'] = w.numpy()
+    # k-means pattern mining (sklearn draws its initialisation from the global numpy RNG)
+    torch.manual_seed(32)
+    w = torch.randn(64, 48)
+    np.random.seed(32)
+    kern = ref_sp.find_top_k_by_kmeans(w, 16, [8, 8], 4, [8, 8])
+    out['kmeans_w'] = w.numpy()
+    out['kmeans_kernel'] = kern.numpy()
+    out['kmeans_next_rand'] = np.array([np.random.randint(0, 2 ** 31 - 1)])
+    np.savez_compressed(os.path.join(HERE, 'patterns.npz'), **out)
+    print('patterns.npz', k, 'Pattern cases; tie mask max', out['apply_b_mask'].max())
+
+
+def gen_pattern_model():
+    """LSTM + cd head with if_pattern=True (neural_networks.py:876-884, 265-272, 1162-1237): two train steps; the
+    mined kernels and the pattern masks are dumped so that the product can be checked with k-means out of the loop."""
+    _cpu_cuda_shim()
+
+    def extra(out, nns):
+        lstm, cd = nns['LSTM_layers'], nns['MLP_layers']
+        for name, lst in lstm.pattern.items():
+            for i, kern in enumerate(lst):
+                out['pattern/LSTM_layers/%s/%d' % (name, i)] = kern.numpy()
+        for name, lst in lstm.pattern_mask.items():
+            for i, m in enumerate(lst):
+                out['pattern_mask/LSTM_layers/%s/%d' % (name, i)] = m.numpy()
+        for i, kern in enumerate(cd.pattern):
+            out['pattern/MLP_layers/%d' % i] = kern.numpy()
+        for i, m in enumerate(cd.pattern_mask):
+            out['pattern_mask/MLP_layers/%d' % i] = m.numpy()
+
+    pat = dict(if_pattern='True', pattern_mode='pattern', pattern_shape='8,8')
+    run_model('train_pattern', 'train', T=6, B=3, D=16,
+              lstm_over=dict(pat, pattern_nnz='4,4', pattern_num='4,6', lstm_lay='32,40', lstm_hcgs='False'),
+              mlp_over=dict(pat, pattern_nnz='8', pattern_num='5', dnn_lay='16', mlp_hcgs='False'),
+              mono_over=dict(if_pattern='False'), steps=2, seed=12, extra=extra)
+    # HCGS and pattern masks together (the pattern search then sees HCGS-masked W but not yet masked U, :858-884)
+    run_model('train_pattern_hcgs', 'train', T=5, B=2, D=16,
+              lstm_over=dict(pat, pattern_nnz='4', pattern_num='4', lstm_lay='32', lstm_drop='0.2',
+                             lstm_use_laynorm='False', lstm_use_batchnorm='True', lstm_act='tanh',
+                             hcgsx_block='16,4', hcgsh_block='16,4'),
+              mlp_over=dict(dnn_lay='10'), steps=1, seed=13, extra=lambda out, nns: [
+                  out.__setitem__('pattern_mask/LSTM_layers/%s/%d' % (n, i), m.numpy())
+                  for n, lst in nns['LSTM_layers'].pattern_mask.items() for i, m in enumerate(lst)] and None)
+
+
 if __name__ == '__main__':
+    if len(sys.argv) > 1:
+        for name in sys.argv[1:]:
+            globals()[name]()
+        sys.exit(0)
+    gen_patterns()
+    gen_pattern_model()
     gen_masks()
     run_model('train_small', 'train', steps=2)
     run_model('train_htanh', 'train', T=5, B=9, D=12, lstm_over=dict(lstm_act='htanh,htanh', lstm_lay='20,28',

@@ -41,21 +41,24 @@ def load_golden(name):
     return np.load(os.path.join(GOLDEN, name + '.npz'), allow_pickle=False)
 
 
-def section_opts(to_do, lstm_over=None, mlp_over=None, out_folder='', use_cuda='False'):
+def section_opts(to_do, lstm_over=None, mlp_over=None, out_folder='', use_cuda='False', mono_over=None):
     a1 = dict(LSTM_OPTS, out_folder=out_folder, to_do=to_do, use_cuda=use_cuda)
     a1.update(lstm_over or {})
     a2 = dict(MLP_OPTS, out_folder=out_folder, to_do=to_do, use_cuda=use_cuda)
     a2.update(mlp_over or {})
     a3 = dict(a2, arch_name='MLP_layers2', dnn_lay='5', mlp_hcgs='False', arch_lr='0.0004')
+    a3.update(mono_over or {})
     return a1, a2, a3
 
 
-def build_product_nets(to_do, D=12, seed=2234, lstm_over=None, mlp_over=None, out_folder='', device='cpu'):
+def build_product_nets(to_do, D=12, seed=2234, lstm_over=None, mlp_over=None, out_folder='', device='cpu',
+                       mono_over=None):
     """Construct LSTM + two MLP heads in the cfg's ``model=`` order with the run_nn seeding."""
     import neural_networks as nn_b200
     torch.manual_seed(seed)
     np.random.seed(seed)
-    a1, a2, a3 = section_opts(to_do, lstm_over, mlp_over, out_folder, use_cuda=str(device != 'cpu'))
+    a1, a2, a3 = section_opts(to_do, lstm_over, mlp_over, out_folder, use_cuda=str(device != 'cpu'),
+                              mono_over=mono_over)
     lstm = nn_b200.LSTM(a1, D)
     cd = nn_b200.MLP(a2, lstm.out_dim)
     mono = nn_b200.MLP(a3, lstm.out_dim)

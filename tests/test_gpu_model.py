@@ -370,3 +370,84 @@ def test_plan_follows_masks_replaced_by_load_state_dict():
             pa, pb = ha(got.reshape(T * B, -1)), hb(want.reshape(T * B, -1))
         assert torch.equal(got, want), prec
         assert torch.equal(pa, pb), prec
+
+
+_PAT = dict(if_pattern='True', pattern_mode='pattern', pattern_shape='8,8')
+
+
+@pytest.mark.parametrize('name,kw', [
+    ('train_pattern', dict(seed=12, D=16, mono_over=dict(if_pattern='False'),
+                           lstm_over=dict(_PAT, pattern_nnz='4,4', pattern_num='4,6', lstm_lay='32,40', lstm_hcgs='False'),
+                           mlp_over=dict(_PAT, pattern_nnz='8', pattern_num='5', dnn_lay='16', mlp_hcgs='False'))),
+    ('train_pattern_hcgs', dict(seed=13, D=16, mlp_over=dict(dnn_lay='10'),
+                                lstm_over=dict(_PAT, pattern_nnz='4', pattern_num='4', lstm_lay='32', lstm_drop='0.2',
+                                               lstm_use_laynorm='False', lstm_use_batchnorm='True', lstm_act='tanh',
+                                               hcgsx_block='16,4', hcgsh_block='16,4'))),
+])
+@pytest.mark.parametrize('mine_on_box', [False, True])
+def test_pattern_masked_train_steps_match_reference_fixture(name, kw, mine_on_box):
+    """if_pattern=True (neural_networks.py:876-884, 265-272, 1162-1237): LSTM (+ MLP head) running with
+    8x8 pattern masks against tensors dumped from the reference.  mine_on_box=False feeds the reference's mined
+    kernels (k-means out of the loop, as core.py:129-131 does from the second chunk on); True lets the product mine
+    them with sklearn from the same numpy RNG state.  Pattern masks bit-exact, fp32 numerics rel <= 1e-5."""
+    from neural_networks import _structural_mask
+    g = load_golden(name)
+    T, B, D, steps = [int(v) for v in g['dims']]
+    nets, sections = build_product_nets('train', device='cuda', **kw)
+    for n, net in nets.items():
+        net.load_state_dict(golden_state(g, 'init', n))
+    lstm, cd = nets['LSTM_layers'], nets['MLP_layers']
+    if not mine_on_box:
+        for key in g.files:
+            if key.startswith('pattern/LSTM_layers/'):
+                _, _, pname, i = key.split('/')
+                assert len(lstm.pattern[pname]) == int(i)
+                lstm.pattern[pname].append(torch.from_numpy(g[key]).cuda())
+        if cd.if_pattern:
+            cd.pattern = [torch.from_numpy(g['pattern/MLP_layers/0']).cuda()]
+    graph = make_graph(nets, D)
+    from b200.graph import make_optimizer
+    opts = {n: make_optimizer(nets[n], sec) for n, sec in zip(nets, sections)}
+    nl = lstm.N_lstm_lay
+    drops = [torch.from_numpy(g['drop/%d' % i]) for i in range(steps * nl)]
+    with _ReplayBernoulli(drops):
+        for s in range(steps):
+            inp = torch.from_numpy(g['inp/%d' % s]).cuda()
+            out = graph.forward(inp, T, B, 'train', ['out_dnn2'])
+            if s == 0:
+                seen = 0
+                for key in g.files:
+                    if key.startswith('pattern_mask/LSTM_layers/'):
+                        _, _, pname, i = key.split('/')
+                        got = lstm.pattern_mask[pname][int(i)].cpu().numpy()
+                        assert np.array_equal(got, g[key]), key
+                        seen += 1
+                    elif key.startswith('pattern/LSTM_layers/') and mine_on_box:
+                        _, _, pname, i = key.split('/')
+                        assert np.array_equal(lstm.pattern[pname][int(i)].cpu().numpy(), g[key]), key
+                assert seen == 8 * nl
+                if cd.if_pattern:
+                    assert np.array_equal(cd.pattern_mask[0].cpu().numpy(), g['pattern_mask/MLP_layers/0'])
+            for o in opts.values():
+                o.zero_grad()
+            out['loss_final'].backward()
+            ref = g['loss/%d' % s]
+            assert abs(out['loss_final'].item() - ref[0]) <= 1e-5 * abs(ref[0]), (s, out['loss_final'].item(), ref[0])
+            close(out['out_dnn1'].reshape(T * B, -1), g['out_dnn1/%d' % s], 1e-5, 'out_dnn1')
+            close(out['out_dnn2'], g['out_dnn2/%d' % s], 1e-5, 'out_dnn2')
+            if s == steps - 1:
+                checked = 0
+                for kind in 'wu':
+                    for i in range(nl):
+                        for gate, factors in zip('fioc', lstm._mask_factor_lists(kind, i)):
+                            k = ('w%sx.%d.weight' if kind == 'w' else 'u%sh.%d.weight') % (gate, i)
+                            keep = _structural_mask([factors]).cpu()
+                            assert 0 < keep.mean().item() < 0.6
+                            refg = torch.from_numpy(g['grad/LSTM_layers/' + k]) * keep     # kept entries (SURVEY a14)
+                            close(dict(lstm.named_parameters())[k].grad, refg, 1e-4, k)
+                            checked += 1
+                assert checked == 8 * nl
+                keep = _structural_mask([cd._mask_factors(0)]).cpu()
+                close(cd.wx[0].weight.grad, torch.from_numpy(g['grad/MLP_layers/wx.0.weight']) * keep, 1e-4, 'cd wx')
+            for o in opts.values():
+                o.step()

@@ -251,7 +251,10 @@ def test_bf16_single_term_option_is_the_old_arithmetic():
 
 def test_bf16_three_train_steps_do_not_drift():
     """three optimizer steps on the tensor-core build against the bf16-operand oracle driven by torch RMSprop on
-    the CPU: loss rel <= 1e-3 and posteriors max-abs <= 5e-4 at every step (the updates feed the rounding points)."""
+    the CPU.  Step 0 must meet the single-step bounds; afterwards the comparison is necessarily loose: the first
+    RMSprop update is lr * g / sqrt((1 - alpha) g^2) = +-4.5 lr for EVERY weight whatever |g|, so a near-zero
+    gradient whose sign differs by rounding moves that weight by 9 lr = 1.4e-2.  Bounds: loss rel <= 1e-3,
+    posteriors mean-abs <= 1e-3 / max-abs <= 1e-2 at every step, and no growth from step 1 to step 2 beyond 2x."""
     H, layers, T, B, P = 550, 2, 30, 8, 1944
     nets, sections, specs, D = _big_nets(H, layers, P, 'train')
     for sp in specs.values():
@@ -288,7 +291,13 @@ def test_bf16_three_train_steps_do_not_drift():
         a, b = out['loss_final'].item(), ref['loss_final'].item()
         mx, mean, _ = _err(out['out_dnn2'], ref['out_dnn2'])
         assert abs(a - b) <= 1e-3 * abs(b), (step, a, b)
-        assert mx <= 5e-4, (step, mx, mean)
+        if step == 0:
+            assert mx <= 1e-4, (step, mx, mean)
+        else:
+            assert mx <= 1e-2 and mean <= 1e-3, (step, mx, mean)
+            if step == 2:
+                assert mean <= 2 * prev_mean + 1e-5, (step, mean, prev_mean)
+            prev_mean = mean
         for o in opts.values():
             o.step()
         for o in ref_opts.values():
