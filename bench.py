@@ -390,47 +390,63 @@ def run_export(dev, nets_train, args, T, B, rank, world, hbm_peak, peak_kind):
     return res
 
 
-def oracle_workload(seed=2234):
-    """The reference's CPU path restated (oracle/model_oracle.py): same nets, same init."""
-    import neural_networks as nb
-    torch.manual_seed(seed)
-    np.random.seed(seed)
-    s_lstm, s_cd, s_mono = cfg_sections('train')
-    for s in (s_lstm, s_cd, s_mono):
-        s['use_cuda'] = 'False'
-    nets = {'lstm': nb.LSTM(s_lstm, D_FEA), 'cd': nb.MLP(s_cd, HID), 'mono': nb.MLP(s_mono, HID)}
-    params = {k: {a: b.detach().cpu().clone() for a, b in n.state_dict().items()} for k, n in nets.items()}
-    train = []
-    for k, d in params.items():
-        for n, v in d.items():
-            if v.dtype == torch.float32 and not n.endswith(('running_mean', 'running_var', 'mask')):
-                v.requires_grad_(True)
-    opts = []
-    for k in params:
-        lr = 0.0004 if k == 'mono' else 0.0016
-        opts.append(torch.optim.RMSprop([v for v in params[k].values() if v.requires_grad], lr=lr, alpha=0.95,
-                                        eps=1e-8))
-    specs = {'lstm': dict(lay=[HID] * LAYERS, act=['tanh'] * LAYERS, use_bn=[True] * LAYERS, drop=[0.2] * LAYERS,
-                          hcgs=True),
-             'cd': dict(lay=[N_PDF], act=['softmax'], use_bn=[False], drop=[0.0], hcgs=True),
-             'mono': dict(lay=[N_MONO], act=['softmax'], use_bn=[False], drop=[0.0], hcgs=False)}
-    return params, specs, opts
+def _reference_modules():
+    """Import the UNMODIFIED reference (baseline/_ref, else /root/reference) in THIS process: its directory goes first on
+    sys.path and the plugin package is taken off, so `neural_networks`, `utils`, `hcgs` ... are the reference's own.
+    Only the reference arm calls this (a process of its own: module names collide with the plugin's by design)."""
+    import ref_harness as rh
+    ref = rh.reference_dir()
+    if ref is None:
+        return None, None
+    sys.path[:] = [p for p in sys.path if not p.rstrip('/').endswith('pytorch-kaldi-cgs_b200')]
+    sys.path.insert(0, ref)
+    import warnings
+    warnings.filterwarnings('ignore')
+    import neural_networks as ref_nn   # noqa: F401
+    import utils as ref_utils
+    assert os.path.dirname(os.path.abspath(ref_utils.__file__)) == ref and 'pytorch-kaldi-cgs_b200' not in ref_nn.__file__
+    rh.cpu_shims(sys.modules)
+    return ref_utils, ref
 
 
-def time_oracle(T, B, steps, warmup, threads):
-    from oracle import model_oracle
+def _reference_nets(ref_utils, to_do, model):
+    import configparser
+    s_lstm, s_cd, s_mono = cfg_sections(to_do, 'fp32')
+    cfg = configparser.ConfigParser()
+    cfg['exp'] = dict(use_cuda='False', to_do=to_do, multi_gpu='False', seed='2234', out_folder='')
+    extra = dict(arch_proto='', arch_library='neural_networks', arch_pretrain_file='none', arch_freeze='False',
+                 arch_halving_factor='0.5', arch_improvement_threshold='0.001')
+    import tempfile
+    tmp = tempfile.mkdtemp(prefix='hcgs_ref_')
+    for k, (sec, cls, seq) in enumerate(((s_lstm, 'LSTM', 'True'), (s_cd, 'MLP', 'False'), (s_mono, 'MLP', 'False'))):
+        sec = {a: b for a, b in sec.items() if not a.startswith('b200_') and a not in ('to_do', 'use_cuda')}
+        cfg['architecture%d' % (k + 1)] = dict(sec, arch_class=cls, arch_seq_model=seq, out_folder=tmp, **extra)
+    fea_dict = {'fbank': ['scp', 'opts', 0, 0, 0, 0, D_FEA, D_FEA]}
+    lab_dict = {'lab_cd': ['f', 'o', 'c', D_FEA], 'lab_mono': ['f', 'o', 'c', D_FEA + 1]}
+    arch_dict = {'LSTM_layers': ['architecture1', 'LSTM_layers', True], 'MLP_layers': ['architecture2', 'MLP_layers', False]}
+    if N_MONO and any('MLP_layers2' in line for line in model):
+        arch_dict['MLP_layers2'] = ['architecture3', 'MLP_layers2', False]
+    torch.manual_seed(2234)
+    np.random.seed(2234)
+    inp_out = dict(fea_dict)
+    nns, costs = ref_utils.model_init(inp_out, model, cfg, arch_dict, False, False, to_do)
+    opts = ref_utils.optimizer_init(nns, cfg, arch_dict) if to_do == 'train' else {}
+    return nns, costs, opts, (fea_dict, lab_dict, arch_dict, inp_out)
+
+
+def time_reference_train(ref_utils, T, B, steps, warmup, threads):
+    """forward_model + backward + optimizer step of the reference's own classes (body of core.py:216-232)."""
     torch.set_num_threads(threads)
-    params, specs, opts = oracle_workload()
+    nns, costs, opts, (fea, lab, arch, io) = _reference_nets(ref_utils, 'train', MODEL)
     times, frames = [], 0
     for s in range(warmup + steps):
         inp, fr = synthetic_minibatch(T, B, 100 + s)
-        drops = [torch.bernoulli(torch.full((B, HID), 0.8)) for _ in range(LAYERS)]
         t0 = time.perf_counter()
-        out = model_oracle.model_forward(params, specs, inp, D_FEA, True, drops)
-        for o in opts:
+        out = ref_utils.forward_model(fea, lab, arch, MODEL, nns, costs, inp, io, T, B, 'train', ['out_dnn2'])
+        for o in opts.values():
             o.zero_grad()
         out['loss_final'].backward()
-        for o in opts:
+        for o in opts.values():
             o.step()
         dt = time.perf_counter() - t0
         if s >= warmup:
@@ -439,23 +455,81 @@ def time_oracle(T, B, steps, warmup, threads):
     return frames / sum(times), sum(times) / len(times) * 1e3
 
 
+def time_reference_export(ref_utils, T, n_utt, warmup, threads):
+    """to_do = forward at batch size 1 (core.py:234-249): forward_model under no_grad, D2H (a no-op on the host),
+    `out - log(counts / sum(counts))` in NumPy per utterance."""
+    torch.set_num_threads(threads)
+    nns, costs, _, (fea, lab, arch, io) = _reference_nets(ref_utils, 'forward', EXPORT_MODEL)
+    counts = np.random.RandomState(7).rand(N_PDF).astype(np.float32) + 0.05
+    feats = synthetic_utterances(warmup + n_utt, T, 4242)
+    t_sum, frames = 0.0, 0
+    for i, f in enumerate(feats):
+        inp = torch.zeros(f.shape[0], 1, D_FEA + 2)
+        inp[:, 0, :D_FEA] = f
+        t0 = time.perf_counter()
+        with torch.no_grad():
+            out = ref_utils.forward_model(fea, lab, arch, EXPORT_MODEL, nns, costs, inp, io, f.shape[0], 1, 'forward',
+                                          ['out_dnn2'])
+        post = out['out_dnn2'].data.cpu().numpy()
+        post = post - np.log(counts / np.sum(counts))
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            t_sum += dt
+            frames += f.shape[0]
+    assert np.isfinite(post).all()
+    return frames / t_sum, t_sum / n_utt * 1e3
+
+
+REF_BATCH = 8    # the reference cfg's minibatch (cfg/TIMIT_CGS/TIMIT_LSTM_fmllr_hcgs.cfg:124 batch_size_train)
+
+
 def run_reference_arm(args, rank):
-    """Reference arm: the reference's own CPU implementation of the path (oracle port), all host threads."""
+    """Reference arm: the UNMODIFIED reference's own classes and forward_model on the box's host cores, all threads.
+    One step = one optimizer step of the reference on a bounded sample of the workload: B = 8 sequences (the cfg's own
+    minibatch size) of the same padded length T as the GPU arm (a full 528-sequence step takes about a minute of
+    CPU time)."""
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    T, B = min(args.seq_len, 100), 8
-    steps = max(1, min(args.steps, 5))
-    fps, ms = time_oracle(T, B, steps, min(args.warmup, 1), threads)
-    line = {'impl': 'reference', 'metric': 'hcgs_lstm_train_frames_per_sec', 'value': fps, 'unit': 'frames/s',
-            'n_gpus': args.gpus, 'steps': steps, 'warmup': min(args.warmup, 1), 'ms_per_step': ms,
-            'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-            'config': workload_config(args, T, B),
-            'cpu_baseline': {'value': fps, 'unit': 'frames/s', 'cores': threads, 'kind': 'port',
-                             'sample': '%d train steps of one [T=%d, B=%d] minibatch (reference cfg batch size), '
-                                       'oracle/model_oracle.py on torch CPU kernels' % (steps, T, B)},
-            'e2e': {'value': fps, 'unit': 'frames/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
+    ref_utils, ref_dir = _reference_modules()
+    base = {'impl': 'reference', 'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup}
+    if ref_utils is None:
+        print(json.dumps(dict(base, unavailable='reference sources not found (run baseline/install_reference.py)')))
+        return
+    T, B = args.seq_len, args.ref_batch
+    if args.what == 'export':
+        fps, ms = time_reference_export(ref_utils, T, max(args.steps, 1), args.warmup, threads)
+        metric, sample = 'hcgs_lstm_posterior_frames_per_sec', (
+            '%d utterances of U[%d,%d] frames, batch size 1 (core.py:183-249): forward_model under no_grad + '
+            'prior normalisation in NumPy' % (max(args.steps, 1), T // 2, T))
+    else:
+        fps, ms = time_reference_train(ref_utils, T, B, max(args.steps, 1), args.warmup, threads)
+        metric, sample = 'hcgs_lstm_train_frames_per_sec', (
+            '%d train steps (forward_model, backward, RMSprop) of one [T=%d, B=%d] minibatch each: B = the reference '
+            "cfg's batch_size_train; the GPU arm's step holds %s such sequences" % (max(args.steps, 1), T, B, args.batch))
+    line = dict(base, metric=metric, value=fps, unit='frames/s', ms_per_step=ms, higher_is_better=True, scaling='weak',
+                vs_baseline=None, dtype='f32', data='synthetic', config=workload_config(args, T, B),
+                cpu_baseline={'value': fps, 'unit': 'frames/s', 'cores': threads, 'kind': 'reference',
+                              'sample': sample, 'source': ref_dir},
+                e2e={'value': fps, 'unit': 'frames/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0})
     print(json.dumps(line))
+
+
+def reference_subprocess(what, T, B, steps, warmup, config):
+    """cpu_baseline legs of the GPU arm: the reference arm in a process of its own (module names collide)."""
+    cmd = [sys.executable, os.path.abspath(__file__), '--impl', 'reference', '--what', what, '--seq-len', str(T),
+           '--ref-batch', str(B), '--steps', str(steps), '--warmup', str(warmup), '--config', config]
+    try:
+        out = subprocess.run(cmd, capture_output=True, text=True, timeout=900,
+                             env=dict(os.environ, CUDA_VISIBLE_DEVICES='')).stdout
+        line = json.loads([l for l in out.splitlines() if l.startswith('{')][-1])
+    except Exception as e:   # noqa: BLE001
+        return {'unavailable': 'reference arm failed: %r' % (e,)}
+    if 'unavailable' in line:
+        return {'unavailable': line['unavailable']}
+    cb = line['cpu_baseline']
+    cb['ms_per_step'] = line['ms_per_step']
+    return cb
 
 
 def workload_config(args, T, B):
@@ -494,6 +568,9 @@ def main():
                     help='bf16 = tensor-core build (BASELINE configs[1] "bf16 train"), fp32 = CUDA-core parity build')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-export', action='store_true', help='skip the posterior-export measurement')
+    ap.add_argument('--no-cfg-batch', action='store_true', help='skip the T = 1000, B = 8 (reference cfg minibatch) line')
+    ap.add_argument('--what', default='train', choices=['train', 'export'], help='reference arm: which leg to time')
+    ap.add_argument('--ref-batch', type=int, default=REF_BATCH, help='reference arm: sequences per step (cfg batch size)')
     ap.add_argument('--config', default='timit', choices=['timit', 'libri'],
                     help='timit = BASELINE configs[1] (headline); libri = configs[3], 5x1024 / 3480 pdfs (no CPU leg)')
     args = ap.parse_args()
@@ -629,6 +706,29 @@ def main():
     gc.enable()
     assert len(losses) == args.steps and all(np.isfinite(losses)), losses
 
+    # ---- the cfg-faithful minibatch: T = 1000, B = 8 sequences per optimizer step, same nets -----------
+    cfg_batch = None
+    if world == 1 and not args.no_cfg_batch and args.config == 'timit':
+        Tc, Bc = 1000, REF_BATCH
+        mbs = [synthetic_minibatch(Tc, Bc, 777 + i) for i in range(2)]
+        res_c = [m[0].to(dev) for m in mbs]
+        for s in range(3):
+            train_step(graph, opts, res_c[s % 2], Tc, Bc, None)
+        torch.cuda.synchronize()
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        c0.record()
+        fr_c = 0
+        for s in range(args.steps):
+            train_step(graph, opts, res_c[s % 2], Tc, Bc, None)
+            fr_c += mbs[s % 2][1]
+        c1.record()
+        torch.cuda.synchronize()
+        ms_c = c0.elapsed_time(c1)
+        cfg_batch = {'seq_len': Tc, 'batch_per_gpu': Bc, 'value': fr_c / (ms_c * 1e-3), 'unit': 'frames/s',
+                     'ms_per_step': ms_c / args.steps, 'steps': args.steps,
+                     'note': "the reference cfg's own minibatch (batch_size_train = 8, max_seq_length_train = 1000): "
+                             'one cluster group of sequences, the recurrence is latency bound'}
+
     hbm_peak, tf_peak, peak_kind = measured_peaks()
     export = None
     if not args.no_export:
@@ -697,13 +797,18 @@ def main():
             'kernels_untimed_pass': per_kernel}
     if export is not None:
         line['export'] = export
+        # top-level copies so that per-N export numbers survive in the driver's SCALE records
+        line['export_value'] = export['value']
+        line['export_e2e_value'] = export['e2e']['value']
+    if cfg_batch is not None:
+        line['cfg_batch'] = cfg_batch
+        if not args.no_cpu_baseline:
+            cfg_batch['cpu_baseline'] = reference_subprocess('train', cfg_batch['seq_len'], REF_BATCH, 2, 1, args.config)
     if not args.no_cpu_baseline and world == 1:
-        threads = os.cpu_count() or 1
-        fps, ms = time_oracle(100, 8, 3, 1, threads)
-        line['cpu_baseline'] = {'value': fps, 'unit': 'frames/s', 'cores': threads, 'kind': 'port',
-                                'sample': '3 train steps of one [T=100, B=8] minibatch (the cfg batch size) with '
-                                          'oracle/model_oracle.py (reference operator sequence on torch CPU kernels)',
-                                'ms_per_step': ms}
+        # the reference's own classes on the host cores (baseline/_ref), bounded samples of the same workloads
+        line['cpu_baseline'] = reference_subprocess('train', T, REF_BATCH, 3, 1, args.config)
+        if export is not None:
+            export['cpu_baseline'] = reference_subprocess('export', T, 1, 12, 2, args.config)
     print(json.dumps(line))
 
 

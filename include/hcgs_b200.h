@@ -173,7 +173,7 @@ int hcgs_lstm_bwd(const hcgs_plan* plan, const float* bwd_pack, const float* dh_
  * Same loop as hcgs_lstm_fwd / hcgs_lstm_bwd (neural_networks.py:1063-1100 and its autograd), for
  * the "bf16 train" configurations: U and h_{t-1} are rounded to bf16 for the product, gates, cell
  * state and all saved tensors stay fp32.  A cluster of `cluster_size` CTAs (4, 8 or 16; 0 = the
- * smallest that fits) runs `nb` sequences (16 or 32; 0 = 16) through all T steps.
+ * smallest that fits) runs `nb` = 16 sequences (0 = 16; no other value is built) through all T steps.
  * Layout of this build's tensors (ld_h = H rounded up to a multiple of 8, pad columns zero):
  *   pre / gates / dpre : [T*B, 4*ld_h] fp32, gate-INTERLEAVED: (row, unit u, gate g) at row*4*ld_h + u*4 + g
  *   c                  : [T*B, ld_h] fp32          hb (bf16 copy of h for the GEMMs): [T*B, ld_h]
@@ -287,7 +287,7 @@ int hcgs_nll_fwd_bwd(const float* logp, int64_t m, int p, const float* labels, i
  * tile, each CTA accumulates a slice of the output columns over the kept 32-wide k tiles (tcgen05, bf16
  * operands, fp32 accumulate), the row max / sum-of-exponentials partials are exchanged through
  * distributed shared memory and the log-posteriors are written once.  HBM traffic per row: n_in*2 + n_out*4 B.
- * hcgs_out_info: info[0]=cluster size (0: n_out > 4096, use hcgs_tc_gemm_nt + hcgs_logsoftmax_fwd)
+ * hcgs_out_info: info[0]=cluster size (0: n_out or n_in > 4096, use hcgs_tc_gemm_nt + hcgs_logsoftmax_fwd)
  *   [1]=strips of 64 columns per CTA [2]=packed tiles [3]=TMEM columns [4]=smem bytes [5]=k items
  *   [6]=bytes of the packed weights [7]=ring stages.
  * hcgs_out_pack: masked dense fp32 W [n_out, n_in] -> pre-swizzled bf16 tiles (info[6] bytes).

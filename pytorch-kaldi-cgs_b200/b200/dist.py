@@ -33,7 +33,7 @@ class GradBucket:
     is non-zero travel; everything else is copied whole.  The index lists are built once.
     """
 
-    def __init__(self, entries, device):
+    def __init__(self, entries, device, check=True):
         self.items = []
         off = 0
         for p, m in entries:
@@ -48,12 +48,20 @@ class GradBucket:
             off += n
         self.numel = off
         self.flat = torch.zeros(off, device=device, dtype=torch.float32)
+        if check:
+            assert_same_masks(self.mask_signature(), device)
 
     def mask_signature(self):
-        """Cheap cross-rank consistency check of the index (masks must be identical on all ranks)."""
+        """Hash of the whole kept-entry index (every index, position weighted).  The compressed all-reduce sums
+        buffer slot k of every rank: if the HCGS masks differed across ranks (per-rank numpy seed, another
+        checkpoint) gradients of DIFFERENT weights would be added silently -- hence assert_same_masks()."""
         s = 0
         for _, idx, off, n in self.items:
-            s = (s * 1000003 + n + (int(idx[:: max(1, n // 64)].sum().item()) if idx is not None and n else 0)) % (2 ** 61 - 1)
+            h = 0
+            if idx is not None and n:
+                wgt = (torch.arange(n, device=idx.device, dtype=torch.int64) % 8191) + 1
+                h = int((idx.to(torch.int64) * wgt).sum().item()) % (2 ** 61 - 1)
+            s = (s * 1000003 + n * 31 + h) % (2 ** 61 - 1)
         return s
 
     def gather(self):
@@ -83,6 +91,20 @@ class GradBucket:
         dist.all_reduce(self.flat, op=dist.ReduceOp.SUM)
         self.flat.div_(dist.get_world_size())
         self.scatter()
+
+
+def assert_same_masks(signature, device):
+    """All ranks must hold the same kept-entry index: all-reduce MIN and MAX of the signature, raise on a mismatch
+    (on every rank, so that no rank is left waiting in a collective)."""
+    if not dist.is_initialized() or dist.get_world_size() == 1:
+        return
+    t = torch.tensor([signature, -signature], dtype=torch.int64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    lo, hi = int(t[0].item()), -int(t[1].item())
+    if lo != hi:
+        raise RuntimeError('HCGS masks differ across ranks (kept-entry index signature %d on this rank, min %d / max %d '
+                           'over ranks): seed numpy identically on every rank before constructing the nets, or load the '
+                           'same checkpoint' % (signature, lo, hi))
 
 
 def lstm_mlp_entries(nets):
@@ -133,7 +155,7 @@ class OverlappedGradBuckets:
     after backward) only launches what has not fired and makes the main stream wait.  Same result as one GradBucket."""
 
     def __init__(self, groups, device):
-        self.buckets = [GradBucket(g, device) for g in groups]
+        self.buckets = [GradBucket(g, device, check=False) for g in groups]
         self.groups = [[p for p, _ in g if p.requires_grad] for g in groups]
         self.calibrated = False
         self.total = [len(g) for g in self.groups]
@@ -142,6 +164,7 @@ class OverlappedGradBuckets:
         self.numel = sum(b.numel for b in self.buckets)
         self.stream = torch.cuda.Stream(device=device) if device.type == 'cuda' else None
         self.handles = []
+        assert_same_masks(self.mask_signature(), device)
         for bi, g in enumerate(groups):
             for p, _ in g:
                 if p.requires_grad:

@@ -588,7 +588,8 @@ class MLPLayerTCFunction(torch.autograd.Function):
         dgamma = dbeta = db = None
         if ctx.softmax and ctx.had_prior:
             raise native.NativeError('backward through a prior-normalised posterior is not defined')
-        if ctx.softmax and not rt.use_bn and O % 4 == 0 and O <= 4096:
+        if (ctx.softmax and not rt.use_bn and O % 4 == 0 and O <= 4096 and dout.data_ptr() % 16 == 0 and
+                ctx.out_store.data_ptr() % 16 == 0):
             # log-softmax backward, bias gradient and the bf16 operand of the dW / dX products in one pass
             dz_b = torch.empty(N, native.pad8(O), device=dev, dtype=torch.bfloat16)
             if ctx.needs_input_grad[2]:

@@ -201,7 +201,9 @@ extern "C" int hcgs_plan_create(const float* mask, int n_out, int n_in, int recu
         int C = 1;
         while (C < 8 && C * 4 < strips) C *= 2;
         const int S = (strips + C - 1) / C;
-        if (S <= 8) {
+        // n_in <= 4096 (128 k tiles per CTA, OUT_MAX_ITEMS in gemm_tc.cu) and n_out <= 4096; anything wider keeps
+        // out_C = 0 and runs as hcgs_tc_gemm_nt + hcgs_logsoftmax_fwd
+        if (S <= 8 && p->tc <= 128) {
             std::vector<int> optr(C + 1, 0), oitems, otile;
             for (int j = 0; j < C; ++j) {
                 optr[j] = (int)oitems.size() / 3;

@@ -352,6 +352,28 @@ def gen_pattern_model():
                   for n, lst in nns['LSTM_layers'].pattern_mask.items() for i, m in enumerate(lst)] and None)
 
 
+def gen_run_nn():
+    """SURVEY a12 / 8(c) shim 4: the reference's OWN chunk loop core.run_nn (train chunk, then a forward chunk from the
+    training checkpoints) over a synthetic chunk, with the reference's own nets on the CPU.  tests/test_reference_loop.py
+    runs the same loop with the plugin classes on the GPU and compares with what is stored here."""
+    sys.path.insert(0, os.path.join(os.path.dirname(HERE)))
+    import ref_harness as rh
+    import core as ref_core
+    rh.cpu_shims(sys.modules)
+    chunk = rh.synthetic_chunk()
+    a1, a2, a3 = (dict(LSTM_OPTS), dict(MLP_OPTS), dict(MLP_OPTS, arch_name='MLP_layers2', dnn_lay='5',
+                                                        mlp_hcgs='False', arch_lr='0.0004'))
+    work = tempfile.mkdtemp()
+    res = rh.run_chunk_pair(ref_core, chunk, [a1, a2, a3], work, use_cuda=False)
+    out = {'loss': np.array([res['loss'], res['err']]), 'ark': np.frombuffer(res['ark'], dtype=np.uint8),
+           'files': np.array([f for f in res['files'] if not f.endswith('.cfg')])}
+    for arch, sd in res['model_par'].items():
+        for k, v in sd.items():
+            out['model_par/%s/%s' % (arch, k)] = v.numpy()
+    np.savez_compressed(os.path.join(HERE, 'run_nn_chunk.npz'), **out)
+    print('run_nn_chunk.npz loss', res['loss'], 'err', res['err'], len(res['ark']), 'ark bytes', res['files'])
+
+
 if __name__ == '__main__':
     if len(sys.argv) > 1:
         for name in sys.argv[1:]:

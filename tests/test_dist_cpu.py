@@ -71,6 +71,34 @@ def _worker(rank, world, port, out_dir):
     dist.destroy_process_group()
 
 
+def _mismatch_worker(rank, world, port, out_dir):
+    os.environ.update(MASTER_ADDR='127.0.0.1', MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    from b200 import dist as bdist
+    from helpers import build_product_nets
+    bdist.init_from_env('gloo')
+    nets, _ = build_product_nets('train', D=12, seed=2234 + rank, device='cpu')     # per-rank seed: masks differ
+    raised = []
+    for make in (lambda: bdist.GradBucket(bdist.lstm_mlp_entries(list(nets.values())), torch.device('cpu')),
+                 lambda: bdist.OverlappedGradBuckets(bdist.lstm_mlp_groups(list(nets.values())), torch.device('cpu'))):
+        try:
+            make()
+            raised.append(False)
+        except RuntimeError as e:
+            raised.append('masks differ across ranks' in str(e))
+    torch.save(raised, os.path.join(out_dir, 'mismatch%d.pt' % rank))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_mask_mismatch_across_ranks_is_refused_world2(tmp_path):
+    """the compressed all-reduce must not start when the kept-entry index differs between ranks."""
+    world = 2
+    mp.spawn(_mismatch_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    for r in range(world):
+        assert torch.load(os.path.join(str(tmp_path), 'mismatch%d.pt' % r)) == [True, True]
+
+
 def test_grad_bucket_allreduce_and_sharding_world2(tmp_path):
     world = 2
     port = _free_port()
