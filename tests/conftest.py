@@ -13,6 +13,9 @@ GOLDEN = os.path.join(ROOT, 'tests', 'golden')
 
 def pytest_configure(config):
     config.addinivalue_line('markers', 'gpu: needs a CUDA device (run on the B200 box)')
+    # the reference's own modules (tests/test_reference_loop.py) carry old-style regex literals
+    config.addinivalue_line('filterwarnings', 'ignore::SyntaxWarning')
+    config.addinivalue_line('filterwarnings', 'ignore::DeprecationWarning')
 
 
 @pytest.fixture(scope='session')
