@@ -110,6 +110,21 @@ int hcgs_bn_fwd(const float* x, int ldx, float* y, int ldy, int64_t m, int n_gro
                 float* const* running_var, float eps, float momentum, int training,
                 float* save_mean, float* save_invstd, float* workspace, int64_t workspace_floats,
                 hcgs_stream stream);
+/* hcgs_bn_fwd_static: hcgs_bn_fwd WITHOUT a caller workspace and without any allocation.  It has NO counterpart in
+ * the reference: it was added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it).  The statistics scratch is a file-scope
+ * device array of the library (2 * HCGS_BN_STATIC_MAX_COLS * 64 floats = 2 MiB per GPU that loads the library, held
+ * until exit).  Limit: n_groups * group_cols <= HCGS_BN_STATIC_MAX_COLS, anything wider is rejected with an error
+ * (use hcgs_bn_fwd).  Calls no cudaMalloc / cudaFree / allocating library routine; the first call on a device
+ * resolves the array's address (cudaGetSymbolAddress) -- make that call outside a capture.  Every call shares the
+ * array (nothing in it has to be cleared: each call writes what it reads), so calls that OVERLAP on the GPU race;
+ * serialise them on one stream or with events.  Same arithmetic and results as hcgs_bn_fwd with a workspace of
+ * 2 * C * 64 floats.                                                                                           */
+#define HCGS_BN_STATIC_MAX_COLS 4096
+int hcgs_bn_fwd_static(const float* x, int ldx, float* y, int ldy, int64_t m, int n_groups, int group_cols,
+                       const float* const* gamma, const float* const* beta, float* const* running_mean,
+                       float* const* running_var, float eps, float momentum, int training,
+                       float* save_mean, float* save_invstd, hcgs_stream stream);
 int hcgs_bn_bwd(const float* dy, int lddy, const float* x, int ldx, int64_t m, int n_groups,
                 int group_cols, const float* const* gamma, const float* save_mean,
                 const float* save_invstd, float* dx, int lddx, float* const* dgamma,

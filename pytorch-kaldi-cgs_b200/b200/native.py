@@ -45,6 +45,8 @@ SIGNATURES = {
     'hcgs_colsum': (c_int, [_f, c_int, c_int64, c_int, c_int, _pp, c_void_p]),
     'hcgs_bn_fwd': (c_int, [_f, c_int, _f, c_int, c_int64, c_int, c_int, _pp, _pp, _pp, _pp, c_float, c_float,
                             c_int, _f, _f, _f, c_int64, c_void_p]),
+    'hcgs_bn_fwd_static': (c_int, [_f, c_int, _f, c_int, c_int64, c_int, c_int, _pp, _pp, _pp, _pp, c_float, c_float,
+                                   c_int, _f, _f, c_void_p]),
     'hcgs_bn_bwd': (c_int, [_f, c_int, _f, c_int, c_int64, c_int, c_int, _pp, _f, _f, _f, c_int, _pp, _pp, _f,
                             c_int64, c_void_p]),
     'hcgs_bn_fwd_il': (c_int, [_f, _f, c_int64, c_int, c_int, c_int, _pp, _pp, _pp, _pp, c_float, c_float, c_int, _f,
@@ -111,7 +113,7 @@ def load():
 
 # kernels launched by each entry point (our own kernels only; memsets are not counted)
 KERNELS_PER_CALL = {'hcgs_mask_apply': 1, 'hcgs_quantize_w': 1, 'hcgs_quantize_act': 2, 'hcgs_bsgemm_nt': 1,
-                    'hcgs_bsgemm_nn': 1, 'hcgs_bs_sddmm': 1, 'hcgs_colsum': 1, 'hcgs_bn_fwd': 3, 'hcgs_bn_bwd': 2, 'hcgs_bn_fwd_il': 3, 'hcgs_bn_bwd_il': 2, 'hcgs_bn_stats_il': 1,
+                    'hcgs_bsgemm_nn': 1, 'hcgs_bs_sddmm': 1, 'hcgs_colsum': 1, 'hcgs_bn_fwd': 3, 'hcgs_bn_fwd_static': 3, 'hcgs_bn_bwd': 2, 'hcgs_bn_fwd_il': 3, 'hcgs_bn_bwd_il': 2, 'hcgs_bn_stats_il': 1,
                     'hcgs_lstm_pack': 2, 'hcgs_lstm_fwd': 1, 'hcgs_lstm_bwd': 1,
                     'hcgs_lstm_tc_pack': 2, 'hcgs_lstm_tc_fwd': 1, 'hcgs_lstm_tc_bwd': 1,
                     'hcgs_tc_pack_nt': 1, 'hcgs_tc_gemm_nt': 1, 'hcgs_cast_bf16': 1,
@@ -292,6 +294,20 @@ def bn_fwd(x2d, y2d, n_groups, group_cols, gammas, betas, rmeans, rvars, eps, mo
                               float(eps), float(momentum), 1 if training else 0, _ptr(save_mean),
                               _ptr(save_invstd), _ptr(workspace),
                               0 if workspace is None else workspace.numel(), _stream()), 'hcgs_bn_fwd')
+
+
+BN_STATIC_MAX_COLS = 4096   # HCGS_BN_STATIC_MAX_COLS of include/hcgs_b200.h
+
+
+def bn_fwd_static(x2d, y2d, n_groups, group_cols, gammas, betas, rmeans, rvars, eps, momentum, training, save_mean,
+                  save_invstd):
+    """hcgs_bn_fwd without a workspace: the scratch is a static device array of the library (no allocation here or
+    in the library; n_groups * group_cols <= BN_STATIC_MAX_COLS; overlapping calls race on the shared scratch)."""
+    _require_cuda(x2d, y2d, save_mean, save_invstd)
+    _check(load().hcgs_bn_fwd_static(_ptr(x2d), _row_major_2d(x2d, 'x'), _ptr(y2d), _row_major_2d(y2d, 'y'),
+                                     x2d.shape[0], n_groups, group_cols, _ptrs(gammas), _ptrs(betas), _ptrs(rmeans),
+                                     _ptrs(rvars), float(eps), float(momentum), 1 if training else 0,
+                                     _ptr(save_mean), _ptr(save_invstd), _stream()), 'hcgs_bn_fwd_static')
 
 
 def bn_bwd(dy2d, x2d, n_groups, group_cols, gammas, save_mean, save_invstd, dx2d, dgammas, dbetas, workspace):

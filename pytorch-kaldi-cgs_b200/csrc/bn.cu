@@ -7,6 +7,7 @@
 // Statistics: rows are split over S CTAs per 32-column strip; every split computes a local
 // (mean, M2) pair with a two-pass scan of its rows and the splits are merged in a fixed order with
 // Chan's formula, so the result is deterministic and free of E[x^2]-E[x]^2 cancellation.
+#include <mutex>
 #include <cuda_bf16.h>
 
 #include "common.cuh"
@@ -652,6 +653,56 @@ extern "C" int hcgs_bn_fwd(const float* x, int ldx, float* y, int ldy, int64_t m
     return bn_fwd_impl(x, ldx, y, ldy, m, n_groups, group_cols, group_cols, 0, gamma, beta, running_mean,
                        running_var, eps, momentum, training, save_mean, save_invstd, workspace, workspace_floats,
                        stream);
+}
+
+// ---- allocation-free variant of hcgs_bn_fwd ------------------------------------------------------------------
+// No counterpart in the reference; added for callers that cannot call
+// cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  The statistics scratch of
+// hcgs_bn_fwd (per row split and column {mean, M2}) lives in a file-scope device array instead of a caller buffer:
+// HCGS_BN_STATIC_MAX_COLS columns x 64 row splits x 2 floats = 2 MiB, held by every GPU that loads the library until
+// the process exits.  Every slot the finalize kernel reads is written by the partial kernel of the SAME call, so
+// nothing has to start at zero and the previous call's contents are never read; but all calls share the array:
+// two calls that overlap on the GPU (different streams, no dependency) race on it.
+static __device__ __align__(256) float g_bn_static_ws[2 * HCGS_BN_STATIC_MAX_COLS * 64];
+
+namespace {
+constexpr int kBnStaticMaxDevices = 64;
+std::mutex g_bn_static_mu;
+float* g_bn_static_ptr[kBnStaticMaxDevices] = {};   // device address of g_bn_static_ws, per device ordinal
+}  // namespace
+
+// In host code `g_bn_static_ws` is only a stand-in for the symbol, not a device address: resolve it once per device,
+// with that device current, and hand the resolved pointer to the kernels.
+static int bn_static_scratch(float** out) {
+    int dev = -1;
+    HCGS_CHECK_CUDA(cudaGetDevice(&dev));
+    HCGS_REQUIRE(dev >= 0 && dev < kBnStaticMaxDevices, "hcgs_bn_fwd_static: device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lock(g_bn_static_mu);
+    if (g_bn_static_ptr[dev] == nullptr) {
+        float* p = nullptr;
+        HCGS_CHECK_CUDA(cudaGetSymbolAddress((void**)&p, g_bn_static_ws));
+        HCGS_REQUIRE(p != nullptr, "hcgs_bn_fwd_static: cudaGetSymbolAddress returned NULL");
+        g_bn_static_ptr[dev] = p;
+    }
+    *out = g_bn_static_ptr[dev];
+    return 0;
+}
+
+extern "C" int hcgs_bn_fwd_static(const float* x, int ldx, float* y, int ldy, int64_t m, int n_groups, int group_cols,
+                                  const float* const* gamma, const float* const* beta, float* const* running_mean,
+                                  float* const* running_var, float eps, float momentum, int training,
+                                  float* save_mean, float* save_invstd, hcgs_stream stream) {
+    HCGS_REQUIRE(n_groups >= 1 && n_groups <= HCGS_MAX_GROUPS, "hcgs_bn_fwd_static: n_groups out of range");
+    HCGS_REQUIRE(group_cols >= 1, "hcgs_bn_fwd_static: group_cols must be positive");
+    const int64_t Ctot = (int64_t)n_groups * group_cols;
+    HCGS_REQUIRE(Ctot <= HCGS_BN_STATIC_MAX_COLS,
+                 "hcgs_bn_fwd_static: %lld columns exceed the static scratch (HCGS_BN_STATIC_MAX_COLS = %d); use "
+                 "hcgs_bn_fwd with a caller workspace", (long long)Ctot, HCGS_BN_STATIC_MAX_COLS);
+    float* ws = nullptr;
+    if (int rc = bn_static_scratch(&ws)) return rc;
+    // the same 64 row splits per column that the plugin's own workspace (2 * C * 64 floats) allows
+    return bn_fwd_impl(x, ldx, y, ldy, m, n_groups, group_cols, group_cols, 0, gamma, beta, running_mean,
+                       running_var, eps, momentum, training, save_mean, save_invstd, ws, 2 * Ctot * 64, stream);
 }
 
 extern "C" int hcgs_bn_fwd_il(const float* x, float* y, int64_t m, int n_groups, int units, int ld_units,
