@@ -41,9 +41,6 @@ namespace hcgs {
 
 constexpr int TC_MAX_WARPS = 16;
 constexpr int TC_MAX_WARPS2 = 20;  // forward kernels with <= 2 strips per warp (register budget 65536 / 640)
-constexpr int TC_HPAD = 8;  // bf16 elements of padding per h row (bank spread, keeps 16 B alignment)
-constexpr int TC_PPAD = 4;  // fp32 elements of padding per partial-dh row
-constexpr int TC_DPAD = 8;  // bf16 elements of padding per dpre row
 
 struct TcPlan {
     int CL = 0, H = 0, NS = 0;  // cluster size, hidden size, 4-row strips in total
@@ -166,17 +163,6 @@ static int tc_plan_get(const hcgs_plan* cplan, int CL, TcPlan** out) {
 
 __host__ __device__ static inline size_t tc_align16(size_t x) { return (x + 15) & ~(size_t)15; }
 
-static size_t tc_fwd_smem(const TcPlan& t, int NB) {
-    size_t b = 0;
-    b += tc_align16((size_t)t.SPC * t.KS * 2 * 32 * 8);               // B fragments
-    b += tc_align16((size_t)2 * NB * (t.HP + TC_HPAD) * 2);           // h double buffer (bf16)
-    b += tc_align16((size_t)2 * NB * (t.Hc * 4 + 16) * 4);            // pre-activation / gate stages (TC_NSTG)
-    b += 2 * tc_align16((size_t)NB * (t.Hc + 4) * 4);                 // c and h output stages
-    b += 3 * tc_align16((size_t)t.Hc * 16);                           // fused batch-norm coefficients
-    b += 64;                                                          // mbarriers
-    return b;
-}
-
 static size_t tc_fwd2_smem(const TcPlan& t, int NB) {
     const int HcS = (t.Hc % 16 == 8) ? t.Hc : t.Hc + 8;
     size_t b = 128;                                                   // alignment slack (TMA boxes: 128 B)
@@ -189,16 +175,8 @@ static size_t tc_fwd2_smem(const TcPlan& t, int NB) {
     b += 64;                                                          // mbarriers
     return b;
 }
-static int tc_fwd_version() {
-    const char* e = getenv("HCGS_TC_FWD");
-    return (e && atoi(e) == 1) ? 1 : 2;   // 1 = LSU build (kept for A/B timing), 2 = bulk-copy build
-}
-static size_t tc_fwd_smem_v(const TcPlan& t, int NB) { return tc_fwd_version() == 1 ? tc_fwd_smem(t, NB) : tc_fwd2_smem(t, NB); }
+static size_t tc_fwd_smem_v(const TcPlan& t, int NB) { return tc_fwd2_smem(t, NB); }
 
-static int tc_bwd_version() {
-    const char* e = getenv("HCGS_TC_BWD");
-    return (e && atoi(e) == 1) ? 1 : 2;   // 1 = LSU build (kept for A/B timing), 2 = asynchronous build
-}
 static size_t tc_bwd2_smem(const TcPlan& t, int NB) {
     size_t b = 128;                                                   // alignment slack (TMA boxes: 128 B)
     b += (size_t)2 * NB * t.Hc * 16;                                  // gate stages (dense boxes)
@@ -212,20 +190,7 @@ static size_t tc_bwd2_smem(const TcPlan& t, int NB) {
     b += 64;
     return b;
 }
-static size_t tc_bwd_smem(const TcPlan& t, int NB);
-static size_t tc_bwd_smem_v(const TcPlan& t, int NB) { return tc_bwd_version() == 1 ? tc_bwd_smem(t, NB) : tc_bwd2_smem(t, NB); }
-
-static size_t tc_bwd_smem(const TcPlan& t, int NB) {
-    size_t b = 0;
-    b += tc_align16((size_t)t.max_cta_blocks * 16 * 8);               // B fragments (16 lanes x 8 B)
-    b += tc_align16((size_t)t.max_cta_blocks * 2);                    // row strip of each block
-    b += tc_align16((size_t)(t.NS + 1) * 4);                          // CSR over column strips
-    b += tc_align16((size_t)NB * (t.SPC * 16 + TC_DPAD) * 2);         // dpre (bf16) [b][strip][g][i]
-    b += tc_align16((size_t)NB * (t.HP + TC_PPAD) * 4);               // partial dh (fp32) [b][col]
-    b += tc_align16((size_t)2 * t.CL * NB * t.Hc * 4);                // slots [2][src][b][ul]
-    b += 64;
-    return b;
-}
+static size_t tc_bwd_smem_v(const TcPlan& t, int NB) { return tc_bwd2_smem(t, NB); }
 
 // ---- PTX helpers -----------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -240,12 +205,6 @@ __device__ __forceinline__ void mbar_init(uint32_t addr, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(addr), "r"(count) : "memory");
 }
 
-__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
-}
-
-// one release fence for a burst of relaxed arrives (a release per arrive serialises CL fences)
-__device__ __forceinline__ void fence_release_cluster() { asm volatile("fence.acq_rel.cluster;" ::: "memory"); }
 __device__ __forceinline__ void mbar_arrive_cluster_relaxed(uint32_t cluster_addr) {
     asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
@@ -311,12 +270,6 @@ __device__ __forceinline__ void mbar_wait_dbg(uint32_t addr, uint32_t parity, in
     }
 }
 
-__device__ __forceinline__ void st_cluster_v4(uint32_t cluster_addr, const uint4& v) {
-    asm volatile("st.shared::cluster.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(cluster_addr), "r"(v.x), "r"(v.y),
-                 "r"(v.z), "r"(v.w)
-                 : "memory");
-}
-
 __device__ __forceinline__ void mma_bf16_16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
                                                uint32_t b0, uint32_t b1) {
     asm volatile(
@@ -343,15 +296,6 @@ __device__ __forceinline__ float act_apply_fast(int act, float x) {
     return act_apply(act, x);
 }
 
-__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(gmem_src) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() {
-    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
-}
-
 // phase timing for kernel tuning (HCGS_TC_DEBUG bit 64): thread 0 of every CTA accumulates clock64 deltas per
 // phase in shared memory; CTA 0 publishes them (hcgs_tc_trace_read).  Costs two predicated branches per phase.
 __device__ long long g_tc_trace[16];
@@ -374,7 +318,6 @@ __device__ long long g_tc_trace[16];
         for (int i_ = 0; i_ < 15; ++i_) g_tc_trace[i_] = trace_s[i_];
 
 __host__ __device__ inline size_t tc_align128(size_t b) { return (b + 127) & ~(size_t)127; }
-constexpr int TC_NSTG = 2;  // shared-memory stages of the pre-activation stream (refilled right after B1)
 
 struct TcFwdArgs {
     const uint2* wfrag;   // [CL][SPC][KS][2][32]
@@ -406,273 +349,9 @@ __device__ __forceinline__ float act_fwd_t(int act, float x) {
     return act_apply_fast(act, x);
 }
 
-// ACT = HCGS_ACT_TANH compiles the (default) tanh cell without the activation switch; -1 = generic
-template <int NT, int SPW, int KSM, int ACT>
-__global__ void __launch_bounds__((SPW <= 2 ? TC_MAX_WARPS2 : TC_MAX_WARPS) * 32, 1)
-    lstm_tc_fwd_kernel(const TcFwdArgs a) {
-    constexpr int NB = NT * 16;
-    cg::cluster_group cluster = cg::this_cluster();
-    const int rank = (int)cluster.block_rank();
-    const int CL = a.CL, SPC = a.SPC, KS = a.KS, H = a.H, ldH = a.ldH;
-    const int b0 = (blockIdx.x / CL) * NB;
-    const int Hc = SPC * 4;
-    const int u0 = rank * Hc;
-    const int nv = max(0, min(Hc, ldH - u0));  // units of this CTA inside the padded tensors (multiple of 8)
-    const int nh = max(0, min(Hc, H - u0));    // real units
-    const int HPs = a.HP + TC_HPAD;
-    const int PRS = Hc * 4 + 16;  // floats per staged row: 64 B of padding keep float4 reads conflict free
-    const int CS = Hc + 4;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nthreads = blockDim.x;
-
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    unsigned char* sp = smem_raw;
-    uint2* wf_s = reinterpret_cast<uint2*>(sp);
-    sp += tc_align16((size_t)SPC * KS * 2 * 32 * 8);
-    __nv_bfloat16* hbuf = reinterpret_cast<__nv_bfloat16*>(sp);
-    sp += tc_align16((size_t)2 * NB * HPs * 2);
-    float* pre_s = reinterpret_cast<float*>(sp);
-    sp += tc_align16((size_t)TC_NSTG * NB * PRS * 4);
-    float* c_s = reinterpret_cast<float*>(sp);
-    sp += tc_align16((size_t)NB * CS * 4);
-    float* h_s = reinterpret_cast<float*>(sp);
-    sp += tc_align16((size_t)NB * CS * 4);
-    float4* bn_m = reinterpret_cast<float4*>(sp);  // per local unit: the four gates' mean / scale / shift
-    sp += tc_align16((size_t)Hc * 16);
-    float4* bn_a = reinterpret_cast<float4*>(sp);
-    sp += tc_align16((size_t)Hc * 16);
-    float4* bn_b = reinterpret_cast<float4*>(sp);
-    sp += tc_align16((size_t)Hc * 16);
-    uint64_t* mbar = reinterpret_cast<uint64_t*>(sp);
-    const bool use_bn = a.bn_mean != nullptr;
-
-    TC_TRACE_INIT();
-    // ---- one-time loads ------------------------------------------------------------------------
-    if (use_bn) {
-        for (int i = tid; i < Hc * 4; i += nthreads) {
-            const int ul = i >> 2, g = i & 3, u = u0 + ul;
-            float m = 0.f, sc = 0.f, sh = 0.f;
-            if (u < H) {
-                m = __ldg(a.bn_mean + (size_t)u * 4 + g);
-                sc = __ldg(a.bn_invstd + (size_t)u * 4 + g) * (a.bn_gamma.p[g] ? __ldg(a.bn_gamma.p[g] + u) : 1.f);
-                sh = a.bn_beta.p[g] ? __ldg(a.bn_beta.p[g] + u) : 0.f;
-            }
-            reinterpret_cast<float*>(bn_m)[i] = m;
-            reinterpret_cast<float*>(bn_a)[i] = sc;
-            reinterpret_cast<float*>(bn_b)[i] = sh;
-        }
-    }
-    {
-        const uint4* s4 = reinterpret_cast<const uint4*>(a.wfrag + (size_t)rank * SPC * KS * 64);
-        uint4* d4 = reinterpret_cast<uint4*>(wf_s);
-        for (int i = tid; i < SPC * KS * 32; i += nthreads) d4[i] = __ldg(s4 + i);
-        uint32_t* hz = reinterpret_cast<uint32_t*>(hbuf);
-        for (int i = tid; i < NB * HPs; i += nthreads) hz[i] = 0u;  // both buffers (2*NB*HPs bf16)
-        for (int i = tid; i < NB * CS; i += nthreads) c_s[i] = h_s[i] = 0.f;
-        if (tid == 0) {
-            mbar_init(smem_u32(&mbar[0]), (uint32_t)CL);
-            mbar_init(smem_u32(&mbar[1]), (uint32_t)CL);
-            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        }
-    }
-
-    // staged, coalesced stream of the pre-activations: 16-byte cp.async chunks, one commit per step
-    const int pchunks = NB * nv;  // one chunk = the four gates of one (sequence, unit) item
-    const int nwarps = nthreads >> 5;
-    auto issue_pre = [&](int step) {
-        if (step < a.T && !(a.dbg & 2)) {
-            float* dst = pre_s + (size_t)(step % TC_NSTG) * NB * PRS;
-            for (int b = warp; b < NB; b += nwarps) {  // one warp per staged row: no index division
-                if (b0 + b >= a.B) continue;
-                const float* src = a.pre + ((size_t)step * a.B + b0 + b) * 4 * ldH + (size_t)u0 * 4;
-                for (int q = lane; q < nv; q += 32) cp_async16(dst + (size_t)b * PRS + q * 4, src + q * 4);
-            }
-        }
-        cp_async_commit();
-    };
-    issue_pre(0);
-
-    // ---- per-thread constants: gather offsets of this warp's strips, item state ----------------
-    const int ui = lane & 3;   // unit inside the strip
-    const int br = lane >> 2;  // batch row inside the m16 tile (and +8)
-    int off0[SPW][KSM], off2[SPW][KSM], nk[SPW];
-    float c_reg[SPW][NT][2], dr[SPW][NT][2];
-    bool ok[SPW][NT][2];
-#pragma unroll
-    for (int i = 0; i < SPW; ++i) {
-        const int sl = warp * SPW + i;
-        nk[i] = (sl < SPC && !(a.dbg & 4)) ? a.nks[(size_t)rank * SPC + sl] : 0;
-#pragma unroll
-        for (int ks = 0; ks < KSM; ++ks) {
-            off0[i][ks] = off2[i][ks] = 0;
-            if (sl < SPC && ks < KS) {
-                const uint16_t* cgp = a.cg + ((size_t)(rank * SPC + sl) * KS + ks) * 4 + (ui >> 1);
-                const uint16_t c0 = cgp[0], c2 = cgp[2];
-                off0[i][ks] = (c0 == 0xFFFF ? 0 : c0 * 4) + (lane & 1) * 2;  // padded blocks carry zero weights
-                off2[i][ks] = (c2 == 0xFFFF ? 0 : c2 * 4) + (lane & 1) * 2;
-            }
-        }
-        const int u = u0 + sl * 4 + ui;
-#pragma unroll
-        for (int nt = 0; nt < NT; ++nt)
-#pragma unroll
-            for (int hh = 0; hh < 2; ++hh) {
-                const int b = b0 + nt * 16 + br + 8 * hh;
-                ok[i][nt][hh] = (sl < SPC) && (u < H) && (b < a.B);
-                c_reg[i][nt][hh] = 0.f;
-                dr[i][nt][hh] = a.drop_scalar;
-                if (ok[i][nt][hh] && a.drop) dr[i][nt][hh] = __ldg(a.drop + (size_t)b * H + u);
-            }
-    }
-    __syncthreads();
-    cluster.sync();
-
-    const uint32_t hbuf_addr = smem_u32(hbuf);
-    const uint32_t mbar_addr = smem_u32(mbar);
-    const int hchunks = Hc / 8;  // 16-byte chunks of one bf16 slice row
-
-    for (int k = 0; k < a.T; ++k) {
-        const int cur = k & 1, nxt = cur ^ 1;
-        const __nv_bfloat16* hc = hbuf + (size_t)cur * NB * HPs;
-        __nv_bfloat16* hn = hbuf + (size_t)nxt * NB * HPs;
-        float* stage = pre_s + (size_t)(k % TC_NSTG) * NB * PRS;
-        TC_TRACE(0);
-        cp_async_wait<0>();  // this thread's chunks of step k have landed
-        TC_TRACE(1);
-        if (k > 0) mbar_wait(mbar_addr + cur * 8, (uint32_t)(((k - 1) >> 1) & 1));
-        TC_TRACE(2);
-        // ---- U h_{k-1}: gather A fragments from the h buffer, B fragments resident ---------------
-        float acc[SPW][2][NT][4];
-#pragma unroll
-        for (int i = 0; i < SPW; ++i) {
-#pragma unroll
-            for (int gp = 0; gp < 2; ++gp)
-#pragma unroll
-                for (int nt = 0; nt < NT; ++nt)
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) acc[i][gp][nt][q] = 0.f;
-            const int sl = warp * SPW + i;
-#pragma unroll
-            for (int ks = 0; ks < KSM; ++ks) {
-                if (ks < nk[i]) {  // warp-uniform
-                    const uint2 bA = wf_s[((size_t)(sl * KS + ks) * 2 + 0) * 32 + lane];
-                    const uint2 bB = wf_s[((size_t)(sl * KS + ks) * 2 + 1) * 32 + lane];
-#pragma unroll
-                    for (int nt = 0; nt < NT; ++nt) {
-                        const __nv_bfloat16* row = hc + (size_t)(nt * 16 + br) * HPs;
-                        const uint32_t a0 = *reinterpret_cast<const uint32_t*>(row + off0[i][ks]);
-                        const uint32_t a1 = *reinterpret_cast<const uint32_t*>(row + 8 * HPs + off0[i][ks]);
-                        const uint32_t a2 = *reinterpret_cast<const uint32_t*>(row + off2[i][ks]);
-                        const uint32_t a3 = *reinterpret_cast<const uint32_t*>(row + 8 * HPs + off2[i][ks]);
-                        mma_bf16_16816(acc[i][0][nt], a0, a1, a2, a3, bA.x, bA.y);
-                        mma_bf16_16816(acc[i][1][nt], a0, a1, a2, a3, bB.x, bB.y);
-                    }
-                }
-            }
-        }
-        TC_TRACE(3);
-        __syncthreads();  // B1: every thread's cp.async chunks of step k are visible
-        TC_TRACE(4);
-        issue_pre(k + 1);  // the other stage was drained (stored out) before anybody reached B1
-        TC_TRACE(5);
-        // ---- fused gates / cell / hidden; gates overwrite the staged pre-activations in place ---
-#pragma unroll
-        for (int i = 0; i < SPW; ++i) {
-            const int sl = warp * SPW + i;
-            if (sl >= SPC) continue;  // warp-uniform
-            const int ul = sl * 4 + ui;
-            float4 bm = make_float4(0.f, 0.f, 0.f, 0.f), ba = make_float4(1.f, 1.f, 1.f, 1.f), bb = bm;
-            if (use_bn) {
-                bm = bn_m[ul];
-                ba = bn_a[ul];
-                bb = bn_b[ul];
-            }
-#pragma unroll
-            for (int nt = 0; nt < NT; ++nt)
-#pragma unroll
-                for (int hh = 0; hh < 2; ++hh) {
-                    const int bl = nt * 16 + br + 8 * hh;
-                    float hval = 0.f;
-                    if (ok[i][nt][hh]) {
-                        float4* pz = reinterpret_cast<float4*>(stage + (size_t)bl * PRS + ul * 4);
-                        float4 p = *pz;
-                        if (use_bn) {
-                            p.x = (p.x - bm.x) * ba.x + bb.x;
-                            p.y = (p.y - bm.y) * ba.y + bb.y;
-                            p.z = (p.z - bm.z) * ba.z + bb.z;
-                            p.w = (p.w - bm.w) * ba.w + bb.w;
-                        }
-                        const float zf = acc[i][0][nt][hh * 2 + 0] + p.x;
-                        const float zi = acc[i][0][nt][hh * 2 + 1] + p.y;
-                        const float zo = acc[i][1][nt][hh * 2 + 0] + p.z;
-                        const float zc = acc[i][1][nt][hh * 2 + 1] + p.w;
-                        const float fg = fast_sigmoid(zf), ig = fast_sigmoid(zi), og = fast_sigmoid(zo);
-                        const float gg = act_fwd_t<ACT>(a.act, zc);
-                        const float cn = ig * gg * dr[i][nt][hh] + fg * c_reg[i][nt][hh];
-                        c_reg[i][nt][hh] = cn;
-                        hval = og * act_fwd_t<ACT>(a.act, cn);
-                        *pz = make_float4(fg, ig, og, gg);
-                        c_s[bl * CS + ul] = cn;
-                        h_s[bl * CS + ul] = hval;
-                    }
-                    hn[(size_t)bl * HPs + u0 + ul] = __float2bfloat16_rn(hval);
-                }
-        }
-        TC_TRACE(6);
-        __syncthreads();  // B2: this CTA's slice of h_k (and the output stages) are complete
-        TC_TRACE(7);
-        if (k + 1 < a.T) {
-            // push the slice into every peer (coalesced 16-byte DSMEM stores)
-            for (int b = warp; b < NB; b += nwarps)
-                for (int q = lane; q < hchunks; q += 32) {
-                    const uint32_t off = (uint32_t)(((size_t)nxt * NB * HPs + (size_t)b * HPs + u0 + q * 8) * 2);
-                    const uint4 v =
-                        *reinterpret_cast<const uint4*>(reinterpret_cast<const unsigned char*>(hbuf) + off);
-                    for (int d = 1; d < CL; ++d)
-                        st_cluster_v4(mapa_u32(hbuf_addr + off, (uint32_t)((rank + d) % CL)), v);
-                }
-            TC_TRACE(8);
-            __syncthreads();  // B3: all pushes of this CTA are issued
-            TC_TRACE(9);
-            if (tid < CL) {   // one arrival per (source CTA, destination CTA)
-                fence_release_cluster();
-                mbar_arrive_cluster_relaxed(mapa_u32(mbar_addr + nxt * 8, (uint32_t)((rank + tid) % CL)));
-            }
-            TC_TRACE(10);
-        }
-        // ---- coalesced global stores of step k (after the signal) and the prefetch of step k+2 --
-        if (!(a.dbg & 1)) {
-            const size_t row0 = (size_t)k * a.B + b0;
-            for (int b = warp; b < NB; b += nwarps) {
-                if (b0 + b >= a.B) continue;
-                if (a.gates_out) {
-                    float* dst = a.gates_out + (row0 + b) * 4 * ldH + (size_t)u0 * 4;
-                    for (int q = lane; q < nv; q += 32)
-                        *reinterpret_cast<float4*>(dst + q * 4) =
-                            *reinterpret_cast<const float4*>(stage + (size_t)b * PRS + q * 4);
-                }
-                if (a.c_out)
-                    for (int q = lane; q < nv / 4; q += 32)
-                        *reinterpret_cast<float4*>(a.c_out + (row0 + b) * ldH + u0 + q * 4) =
-                            *reinterpret_cast<const float4*>(c_s + b * CS + q * 4);
-                if (a.hb_out)
-                    for (int q = lane; q < nv / 8; q += 32)
-                        *reinterpret_cast<uint4*>(a.hb_out + (row0 + b) * ldH + u0 + q * 8) =
-                            *reinterpret_cast<const uint4*>(hn + (size_t)b * HPs + u0 + q * 8);
-                if (a.h_out)
-                    for (int q = lane; q < nv; q += 32) a.h_out[(row0 + b) * ldH + u0 + q] = h_s[b * CS + q];
-            }
-        }
-        TC_TRACE(11);
-    }
-    cp_async_wait<0>();
-    TC_TRACE_FLUSH();
-    cluster.sync();  // nobody exits while peers may still write into its shared memory
-}
-
 // ---- forward, bulk-copy build --------------------------------------------------------------------
-// Same math as lstm_tc_fwd_kernel; all data movement is done by the bulk-copy engine instead of the
-// LSU (measured with HCGS_TC_DEBUG=64: pushes, release fence + arrives, global stores and prefetch
-// issue were >55 % of a step in the LSU version):
+// All data movement is done by the bulk-copy engine instead of the LSU (measured with HCGS_TC_DEBUG=64 on a first
+// LSU-based version: pushes, release fence + arrives, global stores and prefetch issue were >55 % of a step):
 //   * h exchange   : every CTA owns slice `rank` of the slice-major h buffer [2][CL][NB][HcS]; after
 //                    the gate math ONE cp.async.bulk (shared::cta -> shared::cluster) per peer moves the
 //                    whole slice and completes transaction bytes on the peer's mbarrier -- no release
@@ -1107,214 +786,9 @@ struct TcBwdArgs {
     alignas(64) CUtensorMap tm_gates, tm_c, tm_dh;
 };
 
-template <int NT, int IT>
-__global__ void __launch_bounds__(512, 1) lstm_tc_bwd_kernel(const TcBwdArgs a) {
-    constexpr int NB = NT * 16;
-    cg::cluster_group cluster = cg::this_cluster();
-    const int rank = (int)cluster.block_rank();
-    const int CL = a.CL, SPC = a.SPC, NS = a.NS, H = a.H, ldH = a.ldH;
-    const int b0 = (blockIdx.x / CL) * NB;
-    const int Hc = SPC * 4;
-    const int u0 = rank * Hc;
-    const int HPp = a.HP + TC_PPAD;
-    const int DPS = SPC * 16 + TC_DPAD;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nthreads = blockDim.x, nwarps = nthreads >> 5;
-    const int blk0 = a.blk_off[rank];
-    const int nblk = a.blk_off[rank + 1] - blk0;
-
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    unsigned char* sp = smem_raw;
-    uint2* wf_s = reinterpret_cast<uint2*>(sp);
-    sp += tc_align16((size_t)a.max_blocks * 16 * 8);
-    uint16_t* rs_s = reinterpret_cast<uint16_t*>(sp);
-    sp += tc_align16((size_t)a.max_blocks * 2);
-    int* csp_s = reinterpret_cast<int*>(sp);
-    sp += tc_align16((size_t)(NS + 1) * 4);
-    __nv_bfloat16* dpre_s = reinterpret_cast<__nv_bfloat16*>(sp);
-    sp += tc_align16((size_t)NB * DPS * 2);
-    float* partial = reinterpret_cast<float*>(sp);
-    sp += tc_align16((size_t)NB * HPp * 4);
-    float* slots = reinterpret_cast<float*>(sp);  // [2][CL][NB][Hc]
-    sp += tc_align16((size_t)2 * CL * NB * Hc * 4);
-    uint64_t* mbar = reinterpret_cast<uint64_t*>(sp);
-
-    TC_TRACE_INIT();
-    {
-        const uint4* s4 = reinterpret_cast<const uint4*>(a.wfrag + (size_t)blk0 * 16);
-        uint4* d4 = reinterpret_cast<uint4*>(wf_s);
-        for (int i = tid; i < nblk * 8; i += nthreads) d4[i] = __ldg(s4 + i);
-        for (int i = tid; i < nblk; i += nthreads) rs_s[i] = a.blk_rs[blk0 + i];
-        for (int i = tid; i <= NS; i += nthreads) csp_s[i] = a.cs_ptr[(size_t)rank * (NS + 1) + i];
-        for (int i = tid; i < 2 * CL * NB * Hc; i += nthreads) slots[i] = 0.f;
-        uint32_t* dz = reinterpret_cast<uint32_t*>(dpre_s);
-        for (int i = tid; i < NB * DPS / 2; i += nthreads) dz[i] = 0u;
-        if (tid == 0) {
-            mbar_init(smem_u32(&mbar[0]), (uint32_t)CL);
-            mbar_init(smem_u32(&mbar[1]), (uint32_t)CL);
-            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        }
-    }
-    __syncthreads();
-    cluster.sync();
-
-    // ---- pointwise items (unit fastest => coalesced 16-byte global traffic) --------------------
-    int it_b[IT], it_ul[IT];
-    bool it_in[IT], it_ok[IT];
-    float dc_carry[IT], dr[IT];
-    float4 p_g[IT];
-    float p_c[IT], p_cm1[IT], p_dh[IT];
-#pragma unroll
-    for (int j = 0; j < IT; ++j) {
-        const int idx = tid + j * nthreads;
-        it_in[j] = idx < Hc * NB;
-        it_b[j] = it_in[j] ? idx / Hc : 0;
-        it_ul[j] = it_in[j] ? idx % Hc : 0;
-        it_ok[j] = it_in[j] && (u0 + it_ul[j] < H) && (b0 + it_b[j] < a.B);
-        dc_carry[j] = 0.f;
-        dr[j] = a.drop_scalar;
-        p_c[j] = p_cm1[j] = p_dh[j] = 0.f;
-        p_g[j] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (it_ok[j]) {
-            const int u = u0 + it_ul[j];
-            if (a.drop) dr[j] = __ldg(a.drop + (size_t)(b0 + it_b[j]) * H + u);
-            if (a.T > 0) {
-                const size_t row = (size_t)(a.T - 1) * a.B + b0 + it_b[j];
-                p_g[j] = __ldg(reinterpret_cast<const float4*>(a.gates + row * 4 * ldH + (size_t)u * 4));
-                p_c[j] = __ldg(a.c + row * ldH + u);
-                p_cm1[j] = __ldg(a.c + (a.T > 1 ? row - a.B : row) * ldH + u);
-                p_dh[j] = __ldg(a.dh_out + row * H + u);
-            }
-        }
-    }
-    const uint32_t slots_addr = smem_u32(slots);
-    const uint32_t mbar_addr = smem_u32(mbar);
-    const int br = lane >> 2;
-    const int chunks = Hc / 4;  // 16-byte chunks of one fp32 slice row
-
-    for (int k = a.T - 1; k >= 0; --k) {
-        const int wr = k & 1, rd = wr ^ 1;
-        TC_TRACE(0);
-        if (k < a.T - 1) mbar_wait(mbar_addr + rd * 8, (uint32_t)(((a.T - 2 - k) >> 1) & 1));
-        TC_TRACE(1);
-        // ---- fused gate derivatives ------------------------------------------------------------
-#pragma unroll
-        for (int j = 0; j < IT; ++j) {
-            if (!it_in[j]) continue;
-            const int b = it_b[j], ul = it_ul[j];
-            float4 dp = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (it_ok[j]) {
-                float dh = p_dh[j];
-                if (k < a.T - 1) {
-                    const float* sl = slots + ((size_t)rd * CL * NB + b) * Hc + ul;
-                    for (int src = 0; src < CL; ++src) dh += sl[(size_t)src * NB * Hc];
-                }
-                const float fg = p_g[j].x, ig = p_g[j].y, og = p_g[j].z, gg = p_g[j].w;
-                const float tc = act_apply_fast(a.act, p_c[j]);
-                const float dog = dh * tc;
-                const float dct = dh * og * act_grad_from_out(a.act, tc) + dc_carry[j];
-                const float dig = dct * gg * dr[j];
-                const float dgg = dct * ig * dr[j];
-                const float dfg = k > 0 ? dct * p_cm1[j] : 0.f;   // c_{-1} = 0
-                dc_carry[j] = dct * fg;
-                dp.x = dfg * fg * (1.f - fg);
-                dp.y = dig * ig * (1.f - ig);
-                dp.z = dog * og * (1.f - og);
-                dp.w = dgg * act_grad_from_out(a.act, gg);
-                const size_t row = (size_t)k * a.B + b0 + b;
-                const int u = u0 + ul;
-                if (!(a.dbg & 1)) {
-                    if (a.dpre) *reinterpret_cast<float4*>(a.dpre + row * 4 * ldH + (size_t)u * 4) = dp;
-                    if (a.dpreb)
-                        *reinterpret_cast<uint2*>(a.dpreb + row * 4 * ldH + (size_t)u * 4) =
-                            make_uint2(pack_bf16x2(dp.x, dp.y), pack_bf16x2(dp.z, dp.w));
-                }
-                // prefetch step k-1 (consumed one step later).  The loads are unconditional on clamped
-                // rows: a select on a loaded value would make this thread wait for DRAM right here.
-                const size_t rowp = (size_t)(k > 0 ? k - 1 : 0) * a.B + b0 + b;
-                const size_t rowpp = (size_t)(k > 1 ? k - 2 : 0) * a.B + b0 + b;
-                p_c[j] = p_cm1[j];
-                if (!(a.dbg & 2)) {
-                    p_g[j] = __ldg(reinterpret_cast<const float4*>(a.gates + rowp * 4 * ldH + (size_t)u * 4));
-                    p_cm1[j] = __ldg(a.c + rowpp * ldH + u);
-                    p_dh[j] = __ldg(a.dh_out + rowp * H + u);
-                }
-            } else if (u0 + ul < ldH && b0 + b < a.B) {  // pad columns of the padded tensors stay zero
-                const size_t row = (size_t)k * a.B + b0 + b;
-                if (a.dpre) *reinterpret_cast<float4*>(a.dpre + row * 4 * ldH + (size_t)(u0 + ul) * 4) = dp;
-                if (a.dpreb) *reinterpret_cast<uint2*>(a.dpreb + row * 4 * ldH + (size_t)(u0 + ul) * 4) = make_uint2(0u, 0u);
-            }
-            __nv_bfloat16* d = dpre_s + (size_t)b * DPS + (ul >> 2) * 16 + (ul & 3);
-            d[0] = __float2bfloat16_rn(dp.x);
-            d[4] = __float2bfloat16_rn(dp.y);
-            d[8] = __float2bfloat16_rn(dp.z);
-            d[12] = __float2bfloat16_rn(dp.w);
-        }
-        TC_TRACE(2);
-        if (k == 0) break;  // dh_{-1} is not needed
-        __syncthreads();
-        TC_TRACE(3);
-        // ---- partial dh for every column strip from this CTA's rows ---------------------------
-        for (int cs = warp; cs < NS; cs += nwarps) {
-            float acc[NT][4];
-#pragma unroll
-            for (int nt = 0; nt < NT; ++nt)
-#pragma unroll
-                for (int q = 0; q < 4; ++q) acc[nt][q] = 0.f;
-            const int e1 = (a.dbg & 4) ? 0 : csp_s[cs + 1];
-            const int koff = (lane & 3) * 2;  // k = gate*4 + row inside the block
-            for (int e = csp_s[cs]; e < e1; ++e) {
-                const int rs = rs_s[e];
-                uint2 bw = make_uint2(0u, 0u);
-                if (lane < 16) bw = wf_s[(size_t)e * 16 + lane];
-#pragma unroll
-                for (int nt = 0; nt < NT; ++nt) {
-                    const __nv_bfloat16* base = dpre_s + (size_t)(nt * 16 + br) * DPS + rs * 16 + koff;
-                    const uint32_t a0 = *reinterpret_cast<const uint32_t*>(base);
-                    const uint32_t a1 = *reinterpret_cast<const uint32_t*>(base + 8 * DPS);
-                    const uint32_t a2 = *reinterpret_cast<const uint32_t*>(base + 8);
-                    const uint32_t a3 = *reinterpret_cast<const uint32_t*>(base + 8 * DPS + 8);
-                    mma_bf16_16816(acc[nt], a0, a1, a2, a3, bw.x, bw.y);
-                }
-            }
-            if ((lane & 3) < 2) {
-#pragma unroll
-                for (int nt = 0; nt < NT; ++nt) {
-                    float* p = partial + (size_t)(nt * 16 + br) * HPp + cs * 4 + (lane & 3) * 2;
-                    *reinterpret_cast<float2*>(p) = make_float2(acc[nt][0], acc[nt][1]);
-                    *reinterpret_cast<float2*>(p + 8 * HPp) = make_float2(acc[nt][2], acc[nt][3]);
-                }
-            }
-        }
-        TC_TRACE(4);
-        __syncthreads();
-        TC_TRACE(5);
-        // ---- reduce-scatter: column slice d of the partial sums goes to CTA d -------------------
-        for (int db = warp; db < CL * NB; db += nwarps) {  // one warp per (destination, sequence) row
-            const int d = db / NB, b = db - d * NB;
-            for (int q = lane; q < chunks; q += 32) {
-                const int col = d * Hc + q * 4;
-                uint4 v = make_uint4(0u, 0u, 0u, 0u);
-                if (col < NS * 4) v = *reinterpret_cast<const uint4*>(partial + (size_t)b * HPp + col);
-                const uint32_t off = (uint32_t)((((size_t)(wr * CL + rank) * NB + b) * Hc + q * 4) * 4);
-                if (!(a.dbg & 8)) st_cluster_v4(mapa_u32(slots_addr + off, (uint32_t)d), v);
-            }
-        }
-        TC_TRACE(6);
-        __syncthreads();
-        TC_TRACE(7);
-        if (tid < CL) {  // one arrival per (source CTA, destination CTA)
-            fence_release_cluster();
-            mbar_arrive_cluster_relaxed(mapa_u32(mbar_addr + wr * 8, (uint32_t)((rank + tid) % CL)));
-        }
-        TC_TRACE(8);
-    }
-    TC_TRACE_FLUSH();
-    cluster.sync();
-}
-
 // ---- backward, asynchronous build ----------------------------------------------------------------
-// Same recurrence as lstm_tc_bwd_kernel, re-organised like the forward kernel after the per-phase clock trace
-// (item phase 48 %, MMA 27 %, push + release fence 17 % of a step in the LSU version):
+// Organised like the forward kernel after the per-phase clock trace of a first LSU-based version (item phase 48 %,
+// MMA 27 %, push + release fence 17 % of a step there):
 //   * 16 compute warps + 2 DMA warps; no block-wide barrier inside the time loop, only mbarriers;
 //   * gates / c / dh of a step arrive by TMA boxes ([16 sequences][slice]) one step ahead, so the item phase is
 //     shared-memory loads + math + two coalesced global stores (dpre fp32, dpre bf16) with precomputed offsets;
@@ -1768,7 +1242,7 @@ extern "C" int hcgs_lstm_tc_pack(const hcgs_plan* plan, int cluster_size, const 
         const int64_t total = (int64_t)t->n_blocks * 32;
         const int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 8);
         tc_pack_bwd_kernel<<<blocks, 256, 0, st>>>(t->d_blk_off, t->d_blk_rs, t->d_blk_cs, U, ldu, t->H, t->CL,
-                                                  t->SPC, total, tc_bwd_version() == 1 ? 0 : 1, bwd_pack);
+                                                  t->SPC, total, 1, bwd_pack);
         HCGS_LAUNCH_CHECK();
     }
     return 0;
@@ -1797,11 +1271,6 @@ typedef void (*TcBwdKernel)(const TcBwdArgs);
 
 template <int SPW, int ACT>
 static TcFwdKernel tc_pick_fwd_ks(int KS) {
-    if (tc_fwd_version() == 1) {
-        if (KS <= 4) return lstm_tc_fwd_kernel<1, SPW, 4, ACT>;
-        if (KS <= 8) return lstm_tc_fwd_kernel<1, SPW, 8, ACT>;
-        return nullptr;
-    }
     if (KS <= 4) return lstm_tc_fwd2_kernel<1, SPW, 4, ACT>;
     if (KS <= 8) return lstm_tc_fwd2_kernel<1, SPW, 8, ACT>;
     return nullptr;
@@ -1833,12 +1302,7 @@ static TcBwdKernel tc_pick_bwd2(int items) {
 }
 static TcBwdKernel tc_pick_bwd(int NT, int items, int act = HCGS_ACT_TANH) {
     if (NT != 1) return nullptr;
-    if (tc_bwd_version() != 1) return act == HCGS_ACT_TANH ? tc_pick_bwd2<HCGS_ACT_TANH>(items) : tc_pick_bwd2<-1>(items);
-    if (items <= 2) return lstm_tc_bwd_kernel<1, 2>;
-    if (items <= 4) return lstm_tc_bwd_kernel<1, 4>;
-    if (items <= 6) return lstm_tc_bwd_kernel<1, 6>;
-    if (items <= 8) return lstm_tc_bwd_kernel<1, 8>;
-    return nullptr;
+    return act == HCGS_ACT_TANH ? tc_pick_bwd2<HCGS_ACT_TANH>(items) : tc_pick_bwd2<-1>(items);
 }
 
 // co-resident clusters of the two kernels on the current device (0 when the query is unavailable)
@@ -1847,7 +1311,7 @@ static int tc_max_active_clusters(const TcPlan& t, int NB, int* fwd_clusters, in
     const void* ks[2] = {(const void*)tc_pick_fwd(NB / 16, t.SPW, t.KS, HCGS_ACT_TANH),
                          (const void*)tc_pick_bwd(NB / 16, (t.Hc * NB + 511) / 512)};
     const size_t smem[2] = {tc_fwd_smem_v(t, NB), tc_bwd_smem_v(t, NB)};
-    const int threads[2] = {(t.WARPS + (tc_fwd_version() == 1 ? 0 : 2)) * 32, tc_bwd_version() == 1 ? 512 : (TCB_CW + 2) * 32};
+    const int threads[2] = {(t.WARPS + 2) * 32, (TCB_CW + 2) * 32};
     int* outs[2] = {fwd_clusters, bwd_clusters};
     for (int i = 0; i < 2; ++i) {
         if (!ks[i]) continue;
@@ -1920,7 +1384,7 @@ extern "C" int hcgs_lstm_tc_fwd(const hcgs_plan* plan, int cluster_size, int nb,
         a.dbg = e ? atoi(e) : 0;
     }
     a.BW = a.NBX = 0;
-    if (tc_fwd_version() != 1) {
+    {
         if (int rc = tc_pick_box(t->Hc, &a.BW, &a.NBX)) return rc;
         const uint64_t B64 = (uint64_t)batch, T64 = (uint64_t)t_len, ld = (uint64_t)ld_h;
         if (int rc = make_tmap_3d(&a.tm_pre, 4, pre, 4 * ld, B64, T64, 16 * ld, B64 * 16 * ld, a.BW, 16)) return rc;
@@ -1937,7 +1401,7 @@ extern "C" int hcgs_lstm_tc_fwd(const hcgs_plan* plan, int cluster_size, int nb,
     TcFwdKernel k = tc_pick_fwd(NB / 16, t->SPW, t->KS, act);
     HCGS_REQUIRE(k != nullptr, "hcgs_lstm_tc_fwd: no kernel for nb=%d strips/warp=%d k-steps=%d", NB, t->SPW, t->KS);
     const int n_clusters = (batch + NB - 1) / NB;
-    return tc_launch(k, a, n_clusters, t->CL, (t->WARPS + (tc_fwd_version() == 1 ? 0 : 2)) * 32, tc_fwd_smem_v(*t, NB),
+    return tc_launch(k, a, n_clusters, t->CL, (t->WARPS + 2) * 32, tc_fwd_smem_v(*t, NB),
                      (cudaStream_t)stream);
 }
 
@@ -1980,7 +1444,7 @@ extern "C" int hcgs_lstm_tc_bwd(const hcgs_plan* plan, int cluster_size, int nb,
     a.act = act;
     const int items = (t->Hc * NB + 511) / 512;
     a.BW = a.NBX = 0;
-    if (tc_bwd_version() != 1) {
+    {
         if (int rc = tc_pick_box(t->Hc, &a.BW, &a.NBX)) return rc;
         const uint64_t B64 = (uint64_t)batch, T64 = (uint64_t)t_len, ld = (uint64_t)ld_h;
         if (int rc = make_tmap_3d(&a.tm_gates, 4, gates, 4 * ld, B64, T64, 16 * ld, B64 * 16 * ld, a.BW, 16)) return rc;
@@ -1990,7 +1454,7 @@ extern "C" int hcgs_lstm_tc_bwd(const hcgs_plan* plan, int cluster_size, int nb,
     TcBwdKernel k = tc_pick_bwd(NB / 16, items, act);
     HCGS_REQUIRE(k != nullptr, "hcgs_lstm_tc_bwd: no kernel for nb=%d items=%d", NB, items);
     const int n_clusters = (batch + NB - 1) / NB;
-    return tc_launch(k, a, n_clusters, t->CL, tc_bwd_version() == 1 ? 512 : (TCB_CW + 2) * 32, tc_bwd_smem_v(*t, NB),
+    return tc_launch(k, a, n_clusters, t->CL, (TCB_CW + 2) * 32, tc_bwd_smem_v(*t, NB),
                      (cudaStream_t)stream);
 }
 

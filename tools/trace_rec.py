@@ -14,7 +14,7 @@ us = [(torch.randn(H, H) * 0.1 * mask).to(d) for _ in range(4)]
 FWD = ['loop top', 'pre wait', 'mbar wait', 'mma', 'B1 sync', 'issue prefetch', 'gate math', 'B2 sync', 'push',
        'B3 sync', 'fence+arrive', 'global stores']
 BWD = ['loop top', 'input waits', 'item phase', 'items barrier', 'mma + push', 'slots-free wait', '-', '-', '-']
-for B, cl in [(512, 4), (128, 8)]:
+for B, cl in [(528, 4), (128, 8)]:
     cfg = native.TcConfig(plan, cl, 16)
     ldH = native.pad8(H)
     pre = torch.randn(T * B, 4 * ldH, device=d); drop = torch.bernoulli(torch.full((B, H), 0.8, device=d))
