@@ -135,7 +135,10 @@ def lstm_forward(p, spec, x, drop_masks, training):
     BN running statistics in `p` are updated in place when training (momentum 0.05)."""
     bfo = bool(spec.get('bf16_operands', False))
     bfp = ('split' if spec.get('proj_terms', 2) == 2 else True) if bfo else False   # projections: two-term operands
+    bidir = bool(spec.get('bidir', False))      # the reference's dormant branch (:836-838, 1104-1107), override :835 lifted
     for i, H in enumerate(spec['lay']):
+        if bidir:
+            x = torch.cat([x, torch.flip(x, [0])], 1)
         T, B, _ = x.shape
         drop = drop_masks[i] if training else torch.tensor([1 - spec['drop'][i]])
         w, u = {}, {}
@@ -178,6 +181,8 @@ def lstm_forward(p, spec, x, drop_masks, training):
             ht = ot * act(a, ct)
             hs.append(ht)
         x = torch.stack(hs)                                               # :1100
+        if bidir:
+            x = torch.cat([x[:, :B // 2], torch.flip(x[:, B // 2:], [0])], 2)
     return x
 
 

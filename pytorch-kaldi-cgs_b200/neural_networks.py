@@ -14,7 +14,10 @@ native library or without a CUDA device raises.
 Deviations from the reference that are deliberate (all documented in DESIGN.md):
   * cfg keys the reference indexes unconditionally but baseline cfgs lack default to "off";
     ``hcgs*_drop`` is accepted as a spelling of ``hcgs*_sparse`` (LibriSpeech_CGS cfg).
-  * ``lstm_bidir`` is forced off exactly like the reference does in forward (:835).
+  * ``lstm_bidir = True`` runs the bidirectional recurrence the reference's code describes (:836-838, 1104-1107:
+    x and its time-flip side by side along the batch through ONE set of weights, outputs concatenated along the
+    features).  The reference itself overrides the flag in forward (:835) AFTER sizing the layers for 2H (:816-821)
+    and therefore crashes on every ``lstm_bidir = True`` cfg; SURVEY f4 asks for the override to be lifted.
   * the other model classes of the upstream toolkit (GRU, liGRU, CNN, SincNet, ...) carry no
     HCGS/quantisation hook in the reference and are out of scope.
 """
@@ -663,9 +666,12 @@ class LSTM(nn.Module):
             x = _input_batch_norm(self.bn0, x.reshape(x.shape[0] * x.shape[1], x.shape[2])).view(x.shape)
         prev_hb = None
         for i in range(self.N_lstm_lay):
-            self.bidir = 0           # as the reference (:835)
             self.if_hsigmoid = 0     # as the reference (:1080)
             H = self.lstm_lay[i]
+            if self.bidir:
+                # :836-838 -- the reversed copy rides along as B more sequences (shared weights, one BN, one drop mask)
+                x = torch.cat([x, torch.flip(x, [0])], 1)
+                prev_hb = None
             T, B, D = x.shape
             if self.lstm_use_laynorm[i]:
                 raise NotImplementedError('lstm_use_laynorm (LayerNorm of h_t inside the time loop, reference '
@@ -729,6 +735,11 @@ class LSTM(nn.Module):
             if rt.use_bn:
                 for b in bns:
                     _bump_bn_counter(b)
+            if self.bidir:
+                # :1104-1107 -- forward half, time-restored backward half, side by side along the features
+                half = B // 2
+                x = torch.cat([x[:, :half], torch.flip(x[:, half:], [0])], 2)
+                prev_hb = None
         return x
 
     def prune_parameters(self):

@@ -352,6 +352,25 @@ def gen_pattern_model():
                   for n, lst in nns['LSTM_layers'].pattern_mask.items() for i, m in enumerate(lst)] and None)
 
 
+def gen_bidir():
+    """bidirectional LSTM.  The reference's LSTM carries the whole bidirectional branch (:836-838, 1104-1107)
+    but switches it off with `self.bidir = 0` at :835 -- after __init__ has sized the layers for 2H -- so every
+    lstm_bidir = True cfg crashes as shipped.  The fixture comes from the reference source with exactly that ONE line
+    removed (in memory; nothing is written), driven through the reference's own model_init / forward_model."""
+    src = open(os.path.join(REF, 'neural_networks.py')).read()
+    marker = ('            self.bidir = 0\n            if self.bidir:\n'
+              '                h_init = torch.zeros(2 * x.shape[1], self.lstm_lay[i])')
+    assert src.count(marker) == 1
+    src = src.replace(marker, marker.replace('            self.bidir = 0\n', ''))
+    mod = types.ModuleType('neural_networks_bidir')
+    mod.__file__ = os.path.join(REF, 'neural_networks.py')
+    exec(compile(src, mod.__file__ + ' [line 835 removed]', 'exec'), mod.__dict__)
+    sys.modules['neural_networks_bidir'] = mod
+    run_model('train_bidir', 'train', T=7, B=3, D=12,
+              lstm_over=dict(lstm_bidir='True', arch_library='neural_networks_bidir', lstm_lay='24,16'),
+              steps=2, seed=21)
+
+
 def gen_run_nn():
     """SURVEY a12 / 8(c) shim 4: the reference's OWN chunk loop core.run_nn (train chunk, then a forward chunk from the
     training checkpoints) over a synthetic chunk, with the reference's own nets on the CPU.  tests/test_reference_loop.py

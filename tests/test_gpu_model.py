@@ -54,6 +54,8 @@ def _mask_of(net, name):
 @pytest.mark.parametrize('name,kw', [
     ('train_small', {}),
     ('train_htanh', dict(seed=11, lstm_over=dict(lstm_act='htanh,htanh', lstm_lay='20,28', lstm_drop='0.0,0.1'))),
+    # bidirectional: fixture from the reference with its `self.bidir = 0` override (:835) lifted
+    ('train_bidir', dict(seed=21, lstm_over=dict(lstm_bidir='True', lstm_lay='24,16'))),
 ])
 def test_train_steps_match_reference_fixture(name, kw):
     g = load_golden(name)

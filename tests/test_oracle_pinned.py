@@ -166,7 +166,9 @@ def _run_oracle_train(g, specs, steps):
 
 
 @pytest.mark.parametrize('name,over', [('train_small', None),
-                                       ('train_htanh', dict(lay=[20, 28], act=['htanh', 'htanh'], drop=[0.0, 0.1]))])
+                                       ('train_htanh', dict(lay=[20, 28], act=['htanh', 'htanh'], drop=[0.0, 0.1])),
+                                       # reference with the `self.bidir = 0` override (:835) lifted, SURVEY f4
+                                       ('train_bidir', dict(lay=[24, 16], bidir=True))])
 def test_oracle_train_matches_reference(name, over):
     g = _load(name)
     steps = int(g['dims'][3])
