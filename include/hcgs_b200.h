@@ -184,6 +184,33 @@ int hcgs_lstm_bwd(const hcgs_plan* plan, const float* bwd_pack, const float* dh_
                   const float* gates, const float* c, const float* drop, float drop_scalar, int act,
                   int t_len, int batch, float* dpre, hcgs_stream stream);
 
+/* ---- persistent recurrent kernels of the GRU family (fp32 build) ----------------------------
+ * One kernel pair for the four gated / plain cells of the toolkit.  The reference has them dense only
+ * (neural_networks.py GRU :1240-1426, liGRU :1429-1599, minimalGRU :1602-1777, RNN :1780-1931); here the
+ * recurrent matrices take an HCGS mask like the LSTM's, and the dense reference is the all-ones mask.
+ *   GRU        z = s(wz + Uz h)  r = s(wr + Ur h)  a = wh + Uh (r*h)      (:1395-1408)
+ *   minimalGRU z = s(wz + Uz h)                    a = wh + Uh (z*h)      (:1752-1763)
+ *   liGRU      z = s(wz + Uz h)                    a = wh + Uh h          (:1574-1585)
+ *   RNN                                            a = wh + Uh h          (:1907-1916)
+ *   hcand = act(a) * drop ; h = z*h + (1-z)*hcand (RNN: h = hcand); drop [B,H] or NULL (then drop_scalar, eval).
+ * Time-batched buffers hold NG = 3 / 2 / 2 / 1 groups of H columns, gate-major, in the order z, r, candidate
+ * (absent gates left out): pre / gates_out / dpre are [T, B, NG*H].
+ * Weights: hcgs_lstm_pack with u = {Uz, Ur, Uh, any} -- slot 0 = update, 1 = reset, 2 = candidate; a cell without
+ *   a gate passes any valid matrix in that slot (never read).
+ * hcgs_gru_fwd: h_out [T,B,H]; saved for the backward when non-NULL: gates_out (post-activation z, r, act(a)) and,
+ *   for GRU / minimalGRU, m_out [T,B,H] = the gated copy r*h_{t-1} (z*h_{t-1}) that Uh multiplied (operand of dUh).
+ * hcgs_gru_bwd: BPTT; dh_out [T,B,H] gradient from above, h = the forward's h_out; dpre [T,B,NG*H].          */
+#define HCGS_CELL_GRU 0
+#define HCGS_CELL_MINGRU 1
+#define HCGS_CELL_LIGRU 2
+#define HCGS_CELL_RNN 3
+int hcgs_gru_fwd(const hcgs_plan* plan, int cell, const float* fwd_pack, const float* pre, const float* drop,
+                 float drop_scalar, int act, int t_len, int batch, float* h_out, float* m_out, float* gates_out,
+                 hcgs_stream stream);
+int hcgs_gru_bwd(const hcgs_plan* plan, int cell, const float* bwd_pack, const float* dh_out, const float* gates,
+                 const float* h, const float* drop, float drop_scalar, int act, int t_len, int batch, float* dpre,
+                 hcgs_stream stream);
+
 /* ---- tensor-core recurrent kernels (bf16 operands, fp32 accumulate and state) ---------------
  * Same loop as hcgs_lstm_fwd / hcgs_lstm_bwd (neural_networks.py:1063-1100 and its autograd), for
  * the "bf16 train" configurations: U and h_{t-1} are rounded to bf16 for the product, gates, cell

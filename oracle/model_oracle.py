@@ -186,6 +186,58 @@ def lstm_forward(p, spec, x, drop_masks, training):
     return x
 
 
+CELL_GATES = {'gru': ('h', 'z', 'r'), 'ligru': ('h', 'z'), 'minimalgru': ('h', 'z'), 'rnn': ('h',)}
+
+
+def gated_rnn_forward(p, spec, x, drop_masks, training):
+    """GRU.forward (neural_networks.py:1343-1426), liGRU (:1523-1599), minimalGRU (:1701-1777), RNN (:1863-1931).
+    spec keys: cell ('gru' | 'ligru' | 'minimalgru' | 'rnn'), lay, act, use_bn, drop, bidir, hcgs (masks hcgsx.N.mask /
+    hcgsh.N.mask shared by the gates -- not in the reference, which has these cells dense)."""
+    cell = spec['cell']
+    gates = CELL_GATES[cell]
+    bidir = bool(spec.get('bidir', False))
+    for i, H in enumerate(spec['lay']):
+        if bidir:
+            x = torch.cat([x, torch.flip(x, [0])], 1)
+        T, B, _ = x.shape
+        drop = drop_masks[i] if training else torch.tensor([1 - spec['drop'][i]])
+        w, u, b, pre = {}, {}, {}, {}
+        for g in gates:
+            w[g], u[g] = p['w%s.%d.weight' % (g, i)], p['u%s.%d.weight' % (g, i)]
+            b[g] = p.get('w%s.%d.bias' % (g, i))
+            if spec.get('hcgs', False):
+                w[g] = w[g] * p['hcgsx.%d.mask' % i]
+                u[g] = u[g] * p['hcgsh.%d.mask' % i]
+            out = F.linear(x, w[g], b[g])
+            if spec['use_bn'][i]:
+                k = 'bn_w%s.%d.' % (g, i)
+                out = F.batch_norm(out.view(T * B, H), p[k + 'running_mean'], p[k + 'running_var'], p[k + 'weight'],
+                                   p[k + 'bias'], training, 0.05, 1e-5).view(T, B, H)
+            pre[g] = out
+        ht = torch.zeros(B, H)
+        hs = []
+        a = spec['act'][i]
+        for k in range(T):
+            if cell == 'rnn':
+                ht = act(a, pre['h'][k] + F.linear(ht, u['h'])) * drop
+            else:
+                zt = torch.sigmoid(pre['z'][k] + F.linear(ht, u['z']))
+                if cell == 'gru':
+                    rt = torch.sigmoid(pre['r'][k] + F.linear(ht, u['r']))
+                    at = pre['h'][k] + F.linear(rt * ht, u['h'])
+                elif cell == 'minimalgru':
+                    at = pre['h'][k] + F.linear(zt * ht, u['h'])
+                else:
+                    at = pre['h'][k] + F.linear(ht, u['h'])
+                hcand = act(a, at) * drop
+                ht = zt * ht + (1 - zt) * hcand
+            hs.append(ht)
+        x = torch.stack(hs)
+        if bidir:
+            x = torch.cat([x[:, :B // 2], torch.flip(x[:, B // 2:], [0])], 2)
+    return x
+
+
 def mlp_forward(p, spec, x, training, drop_masks=None):
     """MLP.forward (:245-319).  spec keys: lay, act, use_bn, drop, hcgs, quant, quant_inp."""
     for i, O in enumerate(spec['lay']):
@@ -232,7 +284,8 @@ def model_forward(params, specs, inp, n_fea, training, drop_masks, mono_weight=1
     inp: [T, B, n_fea + n_labels] with the labels as trailing float columns (core.py:183-200).
     params/specs: dicts keyed 'lstm', 'cd', optionally 'mono'."""
     T, B, _ = inp.shape
-    h = lstm_forward(params['lstm'], specs['lstm'], inp[:, :, :n_fea], drop_masks, training)
+    recurrent = gated_rnn_forward if specs['lstm'].get('cell') else lstm_forward
+    h = recurrent(params['lstm'], specs['lstm'], inp[:, :, :n_fea], drop_masks, training)
     flat = h.view(T * B, -1)
     out = {'out_dnn1': h}
     out['out_dnn2'] = mlp_forward(params['cd'], specs['cd'], flat, training)

@@ -35,6 +35,7 @@ class LayerRuntime:
         self.q_ws = None
         self.q_us = None
         self.act_bits = 0         # > 0: per-step Quantize_inp of h_t inside the recurrence (lstm_quant_inp)
+        self.cell = None          # GRU family: 'gru' | 'minimalgru' | 'ligru' | 'rnn'
         # tensor-core build: bf16 copy of the layer input handed over by the previous layer, and of
         # this layer's output for the next one (saves a cast pass per layer)
         self.xb_in = None
@@ -229,6 +230,108 @@ class LSTMLayerFunction(torch.autograd.Function):
             dx = dx2d.view(T, B, D)
         return (dx, dws[0], dws[1], dws[2], dws[3], dus[0], dus[1], dus[2], dus[3],
                 dgam[0], dbet[0], dgam[1], dbet[1], dgam[2], dbet[2], dgam[3], dbet[3], None)
+
+
+class GatedRNNLayerFunction(torch.autograd.Function):
+    """One layer of the GRU family on the fp32 build: projections -> BN -> persistent recurrence
+    (neural_networks.py GRU :1376-1410, liGRU :1553-1587, minimalGRU :1731-1765, RNN :1890-1918).
+    Gates in cell order (native.CELL_GATES): ws / us / gammas / betas / biases are lists of that length."""
+
+    @staticmethod
+    def forward(ctx, x, rt, n_g, *params):
+        ws, us = list(params[:n_g]), list(params[n_g:2 * n_g])
+        gammas, betas = list(params[2 * n_g:3 * n_g]), list(params[3 * n_g:4 * n_g])
+        biases = list(params[4 * n_g:5 * n_g])
+        cell = rt.cell
+        gates = native.CELL_GATES[cell]
+        T, B, D = x.shape
+        H = ws[0].shape[0]
+        M = T * B
+        dev = x.device
+        x2d = x.reshape(M, D)
+        if x2d.stride(-1) != 1:
+            x2d = x2d.contiguous()
+        need_grad = any(ctx.needs_input_grad)
+        pre_raw = torch.empty(M, n_g * H, device=dev, dtype=torch.float32)
+        native.bsgemm_nt(rt.plan_x, ws, x2d, pre_raw, biases if biases[0] is not None else None)
+        save_mean = save_invstd = None
+        if rt.use_bn:
+            pre = torch.empty_like(pre_raw)
+            save_mean = torch.empty(n_g * H, device=dev, dtype=torch.float32)
+            save_invstd = torch.empty(n_g * H, device=dev, dtype=torch.float32)
+            native.bn_fwd(pre_raw, pre, n_g, H, gammas, betas, [r[0] for r in rt.bn_running],
+                          [r[1] for r in rt.bn_running], rt.bn_eps, rt.bn_momentum, rt.training, save_mean, save_invstd,
+                          _ws(dev, n_g * H))
+        else:
+            pre = pre_raw
+        plan = rt.plan_h
+        fwd_pack = torch.empty(plan.fwd_pack_floats, device=dev, dtype=torch.float32)
+        bwd_pack = torch.empty(max(plan.bwd_pack_floats, 1), device=dev, dtype=torch.float32) if need_grad else None
+        native.gru_pack(plan, cell, dict(zip(gates, us)), fwd_pack, bwd_pack)
+        h = torch.empty(T, B, H, device=dev, dtype=torch.float32)
+        two_phase = cell in ('gru', 'minimalgru')
+        m = torch.empty(T, B, H, device=dev, dtype=torch.float32) if (need_grad and two_phase) else None
+        g_out = torch.empty(T, B, n_g * H, device=dev, dtype=torch.float32) if need_grad else None
+        native.gru_fwd(plan, cell, fwd_pack, pre.view(T, B, n_g * H), rt.drop, rt.drop_scalar, rt.act, h, m, g_out)
+        if need_grad:
+            ctx.rt, ctx.n_g, ctx.dims = rt, n_g, (T, B, D, H)
+            ctx.drop, ctx.drop_scalar = rt.drop, rt.drop_scalar
+            ctx.has_bias = biases[0] is not None
+            ctx.h_store = h.detach()
+            ctx.save_for_backward(x2d, pre_raw if rt.use_bn else None, save_mean, save_invstd, g_out, bwd_pack, m,
+                                  *ws, *[g for g in gammas if g is not None])
+        return h
+
+    @staticmethod
+    def backward(ctx, dh):
+        rt, n_g = ctx.rt, ctx.n_g
+        T, B, D, H = ctx.dims
+        M = T * B
+        cell = rt.cell
+        gates = native.CELL_GATES[cell]
+        saved = ctx.saved_tensors
+        x2d, pre_raw, save_mean, save_invstd, g_out, bwd_pack, m = saved[:7]
+        ws = list(saved[7:7 + n_g])
+        gammas = list(saved[7 + n_g:])
+        dev = dh.device
+        dh = dh.contiguous()
+        h = ctx.h_store
+        dpre = torch.empty(T, B, n_g * H, device=dev, dtype=torch.float32)
+        native.gru_bwd(rt.plan_h, cell, bwd_pack, dh, g_out, h, ctx.drop, ctx.drop_scalar, rt.act, dpre)
+        dpre2d = dpre.view(M, n_g * H)
+        dgam = [None] * n_g
+        dbet = [None] * n_g
+        if rt.use_bn:
+            dproj = torch.empty_like(dpre2d)
+            dgam = [torch.empty(H, device=dev, dtype=torch.float32) for _ in range(n_g)]
+            dbet = [torch.empty(H, device=dev, dtype=torch.float32) for _ in range(n_g)]
+            native.bn_bwd(dpre2d, pre_raw, n_g, H, gammas, save_mean, save_invstd, dproj, dgam, dbet, _ws(dev, n_g * H))
+        else:
+            dproj = dpre2d
+        # recurrent weight gradients: dU_g = sum_{t>=1} dpre_g[t]^T (operand of U_g at step t); the candidate's operand
+        # is the gated copy m[t] for the two-phase cells, h[t-1] otherwise (and for the update / reset gates)
+        dus = [torch.zeros(H, H, device=dev, dtype=torch.float32) for _ in range(n_g)]
+        if T > 1:
+            h2d = h.view(M, H)
+            hi = gates.index('h')
+            if m is not None:
+                if hi > 0:
+                    native.bs_sddmm(rt.plan_h, dpre2d[B:, :hi * H], h2d[:M - B], dus[:hi], rt.mask_h)
+                native.bs_sddmm(rt.plan_h, dpre2d[B:, hi * H:(hi + 1) * H], m.view(M, H)[B:], [dus[hi]], rt.mask_h)
+            else:
+                native.bs_sddmm(rt.plan_h, dpre2d[B:], h2d[:M - B], dus, rt.mask_h)
+        dws = [torch.zeros(H, D, device=dev, dtype=torch.float32) for _ in range(n_g)]
+        native.bs_sddmm(rt.plan_x, dproj, x2d, dws, rt.mask_x)
+        dbias = [None] * n_g
+        if ctx.has_bias:
+            dbias = [torch.empty(H, device=dev, dtype=torch.float32) for _ in range(n_g)]
+            native.colsum(dproj, n_g, H, dbias)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx2d = torch.empty(M, D, device=dev, dtype=torch.float32)
+            native.bsgemm_nn(rt.plan_x, ws, dproj, dx2d)
+            dx = dx2d.view(T, B, D)
+        return (dx, None, None, *dws, *dus, *dgam, *dbet, *dbias)
 
 
 class MLPLayerFunction(torch.autograd.Function):

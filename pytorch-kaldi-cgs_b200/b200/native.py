@@ -61,6 +61,8 @@ SIGNATURES = {
     'hcgs_lstm_pack': (c_int, [c_void_p, _pp, c_int, _f, _f, c_void_p]),
     'hcgs_lstm_fwd': (c_int, [c_void_p, _f, _f, _f, c_float, c_int, c_int, c_int, _f, _f, _f, c_int, c_void_p]),
     'hcgs_lstm_bwd': (c_int, [c_void_p, _f, _f, _f, _f, _f, c_float, c_int, c_int, c_int, _f, c_void_p]),
+    'hcgs_gru_fwd': (c_int, [c_void_p, c_int, _f, _f, _f, c_float, c_int, c_int, c_int, _f, _f, _f, c_void_p]),
+    'hcgs_gru_bwd': (c_int, [c_void_p, c_int, _f, _f, _f, _f, _f, c_float, c_int, c_int, c_int, _f, c_void_p]),
     'hcgs_lstm_tc_info': (c_int, [c_void_p, c_int, c_int, POINTER(c_int64)]),
     'hcgs_lstm_tc_pack': (c_int, [c_void_p, c_int, _pp, c_int, _f, _f, c_void_p]),
     'hcgs_lstm_tc_fwd': (c_int, [c_void_p, c_int, c_int, _f, _f, c_int, _f, c_float, c_int, c_int, c_int, _f, _f, _f,
@@ -114,7 +116,7 @@ def load():
 # kernels launched by each entry point (our own kernels only; memsets are not counted)
 KERNELS_PER_CALL = {'hcgs_mask_apply': 1, 'hcgs_quantize_w': 1, 'hcgs_quantize_act': 2, 'hcgs_bsgemm_nt': 1,
                     'hcgs_bsgemm_nn': 1, 'hcgs_bs_sddmm': 1, 'hcgs_colsum': 1, 'hcgs_bn_fwd': 3, 'hcgs_bn_fwd_static': 3, 'hcgs_bn_bwd': 2, 'hcgs_bn_fwd_il': 3, 'hcgs_bn_bwd_il': 2, 'hcgs_bn_stats_il': 1,
-                    'hcgs_lstm_pack': 2, 'hcgs_lstm_fwd': 1, 'hcgs_lstm_bwd': 1,
+                    'hcgs_lstm_pack': 2, 'hcgs_lstm_fwd': 1, 'hcgs_lstm_bwd': 1, 'hcgs_gru_fwd': 1, 'hcgs_gru_bwd': 1,
                     'hcgs_lstm_tc_pack': 2, 'hcgs_lstm_tc_fwd': 1, 'hcgs_lstm_tc_bwd': 1,
                     'hcgs_tc_pack_nt': 1, 'hcgs_tc_gemm_nt': 1, 'hcgs_cast_bf16': 1,
                     'hcgs_tc_pack_nt_split': 1, 'hcgs_tc_gemm_nt_split': 1, 'hcgs_split_bf16': 1,
@@ -393,6 +395,38 @@ def lstm_bwd(plan, bwd_pack, dh_out, gates, c, drop, drop_scalar, act, dpre):
     assert dh_out.is_contiguous() and gates.is_contiguous() and c.is_contiguous() and dpre.is_contiguous()
     _check(load().hcgs_lstm_bwd(plan.handle, _ptr(bwd_pack), _ptr(dh_out), _ptr(gates), _ptr(c), _ptr(drop),
                                 float(drop_scalar), int(act), T, B, _ptr(dpre), _stream()), 'hcgs_lstm_bwd')
+
+
+CELL_CODES = {'gru': 0, 'minimalgru': 1, 'ligru': 2, 'rnn': 3}
+CELL_GATES = {'gru': ('z', 'r', 'h'), 'minimalgru': ('z', 'h'), 'ligru': ('z', 'h'), 'rnn': ('h',)}
+
+
+def gru_pack(plan, cell, us, fwd_pack=None, bwd_pack=None):
+    """us: dict gate letter -> U [H,H] for the gates of `cell`; packed into the LSTM's four-slot layout
+    (slot 0 = update, 1 = reset, 2 = candidate; absent gates get a placeholder that is never read)."""
+    uh = us['h']
+    lstm_pack(plan, [us.get('z', uh), us.get('r', uh), uh, uh], fwd_pack, bwd_pack)
+
+
+def gru_fwd(plan, cell, fwd_pack, pre, drop, drop_scalar, act, h_out, m_out=None, gates_out=None):
+    """pre / gates_out [T,B,NG*H] (gate-major: z, r, candidate as far as the cell has them), h_out / m_out [T,B,H]"""
+    _require_cuda(fwd_pack, pre, drop, h_out, m_out, gates_out)
+    T, B = pre.shape[0], pre.shape[1]
+    ng = len(CELL_GATES[cell])
+    assert pre.is_contiguous() and h_out.is_contiguous() and pre.shape[2] == ng * plan.n_out
+    for t in (m_out, gates_out):
+        assert t is None or t.is_contiguous()
+    _check(load().hcgs_gru_fwd(plan.handle, CELL_CODES[cell], _ptr(fwd_pack), _ptr(pre), _ptr(drop), float(drop_scalar),
+                               int(act), T, B, _ptr(h_out), _ptr(m_out), _ptr(gates_out), _stream()), 'hcgs_gru_fwd')
+
+
+def gru_bwd(plan, cell, bwd_pack, dh_out, gates, h, drop, drop_scalar, act, dpre):
+    _require_cuda(bwd_pack, dh_out, gates, h, drop, dpre)
+    T, B = dh_out.shape[0], dh_out.shape[1]
+    assert dh_out.is_contiguous() and gates.is_contiguous() and h.is_contiguous() and dpre.is_contiguous()
+    assert dpre.shape == gates.shape and gates.shape[2] == len(CELL_GATES[cell]) * plan.n_out
+    _check(load().hcgs_gru_bwd(plan.handle, CELL_CODES[cell], _ptr(bwd_pack), _ptr(dh_out), _ptr(gates), _ptr(h),
+                               _ptr(drop), float(drop_scalar), int(act), T, B, _ptr(dpre), _stream()), 'hcgs_gru_bwd')
 
 
 def _require_cuda_any(*tensors):

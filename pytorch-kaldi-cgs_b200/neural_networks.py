@@ -18,8 +18,9 @@ Deviations from the reference that are deliberate (all documented in DESIGN.md):
     x and its time-flip side by side along the batch through ONE set of weights, outputs concatenated along the
     features).  The reference itself overrides the flag in forward (:835) AFTER sizing the layers for 2H (:816-821)
     and therefore crashes on every ``lstm_bidir = True`` cfg; SURVEY f4 asks for the override to be lifted.
-  * the other model classes of the upstream toolkit (GRU, liGRU, CNN, SincNet, ...) carry no
-    HCGS/quantisation hook in the reference and are out of scope.
+  * ``GRU`` / ``liGRU`` / ``minimalGRU`` / ``RNN`` (dense in the reference) run on the same kind of persistent
+    recurrent kernels and additionally take HCGS masks (``<prefix>_hcgs`` + the LSTM's hcgs* keys); the
+    remaining upstream classes (CNN, SincNet, ...) carry no HCGS/quantisation hook and are out of scope.
 """
 import torch
 import torch.nn as nn
@@ -33,6 +34,7 @@ from HCGS import guidedHCGS as guidedHCGS
 from quantized_modules import QuantizeLinear, Quantize, Quantize_inp, prune
 from b200 import native
 from b200.functions import (LayerRuntime, LSTMLayerFunction, MLPLayerFunction, LSTMLayerTCFunction,
+                            GatedRNNLayerFunction,
                             MLPLayerTCFunction, LayerNormFunction, BatchNormInputFunction, ActDropFunction)
 
 
@@ -802,3 +804,174 @@ class LSTM(nn.Module):
                     native.mask_apply([getattr(self, n)[i].weight.data],
                                       self.pattern_mask['pattern_mask_' + n][i].data.contiguous())
         return 1
+
+
+class _GatedRNN(nn.Module):
+    """Common body of GRU / liGRU / minimalGRU / RNN (reference: neural_networks.py:1240-1931).
+
+    The reference has these four classes dense.  Here they keep the reference's option names (``<p>_lay``,
+    ``<p>_drop``, ``<p>_use_batchnorm`` ... with p = gru / ligru / minimalgru / rnn), module names, registration and
+    RNG order (identical seeds give bit-identical initial parameters), and additionally accept the LSTM's HCGS keys
+    with the class prefix -- ``<p>_hcgs``, ``hcgsx_block``, ``hcgsx_sparse``, ``hcgsh_block``, ``hcgsh_sparse`` -- one
+    x-mask and one h-mask per layer shared by the gates.  Without ``<p>_hcgs`` the masks are all ones and
+    the result is the dense reference's.  Arithmetic: the fp32 kernels (csrc/gru.cu); ``b200_precision`` is accepted
+    and ignored (there is no tensor-core recurrence for these cells yet)."""
+
+    prefix = None      # option prefix == native cell name
+    gates = None       # gate letters in the REFERENCE's creation order (RNG order of the nn.Linear inits)
+
+    def __init__(self, options, inp_dim):
+        super(_GatedRNN, self).__init__()
+        p = self.prefix
+        self.input_dim = inp_dim
+        self.lay = list(map(int, options[p + '_lay'].split(',')))
+        self.drop = list(map(float, options[p + '_drop'].split(',')))
+        self.use_batchnorm = list(map(strtobool, options[p + '_use_batchnorm'].split(',')))
+        self.use_laynorm = list(map(strtobool, options[p + '_use_laynorm'].split(',')))
+        self.use_laynorm_inp = strtobool(options[p + '_use_laynorm_inp'])
+        self.use_batchnorm_inp = strtobool(options[p + '_use_batchnorm_inp'])
+        self.orthinit = strtobool(options[p + '_orthinit'])
+        self.act_names = options[p + '_act'].split(',')
+        self.bidir = strtobool(options[p + '_bidir'])
+        self.use_cuda = strtobool(_opt(options, 'use_cuda', 'True'))
+        self.to_do = _opt(options, 'to_do', 'train')
+        self.test_flag = self.to_do != 'train'
+        for k in ('lay', 'drop', 'use_batchnorm', 'use_laynorm', 'use_laynorm_inp', 'use_batchnorm_inp', 'orthinit'):
+            setattr(self, p + '_' + k, getattr(self, k))      # the reference's attribute names
+        setattr(self, p + '_act', self.act_names)
+
+        self.rnn_hcgs = strtobool(_opt(options, p + '_hcgs', 'False'))
+        self.hcgsx_block = list(map(int, _opt(options, 'hcgsx_block', '32,4').split(',')))
+        self.hcgsh_block = list(map(int, _opt(options, 'hcgsh_block', '32,4').split(',')))
+        self.hcgsx_sparse = list(map(float, _opt(options, 'hcgsx_sparse', '75,62.5', 'hcgsx_drop').split(',')))
+        self.hcgsh_sparse = list(map(float, _opt(options, 'hcgsh_sparse', '75,62.5', 'hcgsh_drop').split(',')))
+        self.arch_name = _opt(options, 'arch_name', p.upper())
+        self.b200_precision = _opt(options, 'b200_precision', 'fp32')
+        # attributes core.run_nn reads on every net (core.py:123-131, 292-306)
+        self.prune = False
+        self.guided_hcgs = False
+        self.apply_guided_hcgs = False
+        self.if_pattern = False
+        self.skip_regularization = strtobool(_opt(options, 'skip_regularization', 'True'))
+
+        # registration order == reference (e.g. GRU :1268-1283): wh, uh, wz, uz, wr, ur, ln, bn_w*, act
+        for g in self.gates:
+            setattr(self, 'w' + g, nn.ModuleList([]))
+            setattr(self, 'u' + g, nn.ModuleList([]))
+        self.ln = nn.ModuleList([])
+        for g in self.gates:
+            setattr(self, 'bn_w' + g, nn.ModuleList([]))
+        self.act = nn.ModuleList([])
+        if self.use_laynorm_inp:
+            self.ln0 = LayerNorm(self.input_dim)
+        if self.use_batchnorm_inp:
+            self.bn0 = nn.BatchNorm1d(self.input_dim, momentum=0.05)
+        if self.rnn_hcgs:
+            self.hcgsx = nn.ModuleList([])
+            self.hcgsh = nn.ModuleList([])
+
+        self.N_lay = len(self.lay)
+        setattr(self, 'N_%s_lay' % p, self.N_lay)
+        current_input = self.input_dim
+        for i in range(self.N_lay):
+            H = self.lay[i]
+            self.act.append(act_fun(self.act_names[i]))
+            add_bias = not (self.use_laynorm[i] or self.use_batchnorm[i])
+            for g in self.gates:                                   # feed-forward connections
+                getattr(self, 'w' + g).append(nn.Linear(current_input, H, bias=add_bias))
+            for g in self.gates:                                   # recurrent connections
+                getattr(self, 'u' + g).append(nn.Linear(H, H, bias=False))
+            if self.orthinit:
+                for g in self.gates:
+                    nn.init.orthogonal_(getattr(self, 'u' + g)[i].weight)
+            for g in self.gates:
+                getattr(self, 'bn_w' + g).append(nn.BatchNorm1d(H, momentum=0.05))
+            self.ln.append(LayerNorm(H))
+            if self.rnn_hcgs:      # after everything the reference creates: its torch RNG stream is not disturbed
+                self.hcgsx.append(HCGS(current_input, H, self.hcgsx_block, self.hcgsx_sparse,
+                                       str(i) + '_x_' + self.arch_name))
+                self.hcgsh.append(HCGS(H, H, self.hcgsh_block, self.hcgsh_sparse, str(i) + '_h_' + self.arch_name))
+            current_input = 2 * H if self.bidir else H
+        self.out_dim = self.lay[-1] + self.bidir * self.lay[-1]
+        self._plans = _PlanCache()
+        self.register_load_state_dict_post_hook(lambda module, incompatible: module._plans.clear())
+
+    def prune_parameters(self):
+        return 1
+
+    def forward(self, x):
+        cell = self.prefix
+        order = native.CELL_GATES[cell]                            # kernel order: z, r, h
+        if bool(self.use_laynorm_inp):
+            x = self.ln0(x)
+        if x.dim() != 3:
+            raise native.NativeError('%s expects [T, B, in] input, got %s' % (type(self).__name__, tuple(x.shape)))
+        if bool(self.use_batchnorm_inp):
+            x = _input_batch_norm(self.bn0, x.reshape(x.shape[0] * x.shape[1], x.shape[2])).view(x.shape)
+        for i in range(self.N_lay):
+            H = self.lay[i]
+            if self.use_laynorm[i]:
+                raise NotImplementedError('%s_use_laynorm (LayerNorm of h_t inside the time loop) is not built into the '
+                                          'recurrent kernels' % cell)
+            if self.bidir:
+                x = torch.cat([x, torch.flip(x, [0])], 1)
+            T, B, D = x.shape
+            rt = LayerRuntime()
+            rt.cell = cell
+            if self.test_flag == False:  # noqa: E712 (reference spelling)
+                drop_mask = torch.bernoulli(torch.Tensor(B, H).fill_(1 - self.drop[i]))
+                rt.drop = drop_mask.to(x.device)
+                rt.drop_scalar = 1.0
+            else:
+                rt.drop = None
+                rt.drop_scalar = 1 - self.drop[i]
+            ws = [getattr(self, 'w' + g)[i] for g in order]
+            us = [getattr(self, 'u' + g)[i] for g in order]
+            bns = [getattr(self, 'bn_w' + g)[i] for g in order]
+            src_x, src_h = [], []
+            if self.rnn_hcgs:
+                with torch.no_grad():
+                    native.mask_apply([l.weight.data for l in ws], self.hcgsx[i].mask.data)
+                    native.mask_apply([l.weight.data for l in us], self.hcgsh[i].mask.data)
+                src_x, src_h = [self.hcgsx[i].mask], [self.hcgsh[i].mask]
+            rt.plan_x, rt.mask_x = self._plans.get(('x', i), src_x, lambda: _structural_mask([src_x]), (H, D), False)
+            rt.plan_h, rt.mask_h = self._plans.get(('h', i), src_h, lambda: _structural_mask([src_h]), (H, H), True)
+            rt.use_bn = bool(self.use_batchnorm[i])
+            rt.training = bns[0].training
+            rt.bn_running = [(b.running_mean, b.running_var) for b in bns]
+            rt.bn_eps, rt.bn_momentum = bns[0].eps, bns[0].momentum
+            rt.act = native.ACT_CODES[self.act_names[i]]
+            if rt.use_bn and not rt.training and torch.is_grad_enabled() and ws[0].weight.requires_grad:
+                raise NotImplementedError('backward through eval-mode batch norm (arch_freeze) is not built yet')
+            n_g = len(order)
+            gam = [b.weight if rt.use_bn else None for b in bns]
+            bet = [b.bias if rt.use_bn else None for b in bns]
+            x = GatedRNNLayerFunction.apply(x, rt, n_g, *[l.weight for l in ws], *[l.weight for l in us], *gam, *bet,
+                                            *[l.bias for l in ws])
+            if rt.use_bn:
+                for b in bns:
+                    _bump_bn_counter(b)
+            if self.bidir:
+                half = B // 2
+                x = torch.cat([x[:, :half], torch.flip(x[:, half:], [0])], 2)
+        return x
+
+
+class GRU(_GatedRNN):
+    """reference: neural_networks.py:1240-1426"""
+    prefix, gates = 'gru', ('h', 'z', 'r')
+
+
+class liGRU(_GatedRNN):
+    """reference: neural_networks.py:1429-1599"""
+    prefix, gates = 'ligru', ('h', 'z')
+
+
+class minimalGRU(_GatedRNN):
+    """reference: neural_networks.py:1602-1777"""
+    prefix, gates = 'minimalgru', ('h', 'z')
+
+
+class RNN(_GatedRNN):
+    """reference: neural_networks.py:1780-1931"""
+    prefix, gates = 'rnn', ('h',)

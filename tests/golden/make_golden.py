@@ -105,10 +105,10 @@ MODEL_2HEAD = ['out_dnn1=compute(LSTM_layers,fbank)', 'out_dnn2=compute(MLP_laye
                'loss_final=sum(loss_cd,loss_mono_w)', 'err_final=cost_err(out_dnn2,lab_cd)']
 
 
-def build_config(to_do, lstm_over=None, mlp_over=None, out_folder='', mono_over=None):
+def build_config(to_do, lstm_over=None, mlp_over=None, out_folder='', mono_over=None, arch1=None):
     cfg = configparser.ConfigParser()
     cfg['exp'] = dict(use_cuda='False', to_do=to_do, multi_gpu='False', seed='2234', out_folder=out_folder)
-    a1 = dict(LSTM_OPTS, out_folder=out_folder)
+    a1 = dict(arch1 if arch1 is not None else LSTM_OPTS, out_folder=out_folder)
     a1.update(lstm_over or {})
     a2 = dict(MLP_OPTS, out_folder=out_folder)
     a2.update(mlp_over or {})
@@ -119,10 +119,10 @@ def build_config(to_do, lstm_over=None, mlp_over=None, out_folder='', mono_over=
 
 
 def run_model(tag, to_do, T=7, B=3, D=12, lstm_over=None, mlp_over=None, steps=1, seed=2234, mono_over=None,
-              extra=None):
+              extra=None, arch1=None):
     """One (or a few) reference train steps / one eval forward; returns a dict of arrays."""
     tmp = tempfile.mkdtemp()
-    cfg = build_config(to_do, lstm_over, mlp_over, out_folder=tmp, mono_over=mono_over)
+    cfg = build_config(to_do, lstm_over, mlp_over, out_folder=tmp, mono_over=mono_over, arch1=arch1)
     torch.manual_seed(seed)
     np.random.seed(seed)
     fea_dict = {'fbank': ['scp', 'opts', 0, 0, 0, 0, D, D]}
@@ -369,6 +369,37 @@ def gen_bidir():
     run_model('train_bidir', 'train', T=7, B=3, D=12,
               lstm_over=dict(lstm_bidir='True', arch_library='neural_networks_bidir', lstm_lay='24,16'),
               steps=2, seed=21)
+
+
+def rnn_family_opts(prefix, cls, **over):
+    """cfg section of one of the reference's dense recurrent classes (cfg/TIMIT_baselines/TIMIT_{GRU,liGRU,RNN}_*.cfg)."""
+    p = prefix
+    o = {'arch_name': 'LSTM_layers', 'arch_proto': 'proto/%s.proto' % cls, 'arch_library': 'neural_networks',
+         'arch_class': cls, 'arch_pretrain_file': 'none', 'arch_freeze': 'False', 'arch_seq_model': 'True',
+         p + '_lay': '24,16', p + '_drop': '0.2,0.2', p + '_use_laynorm_inp': 'False', p + '_use_batchnorm_inp': 'False',
+         p + '_use_laynorm': 'False,False', p + '_use_batchnorm': 'True,True', p + '_bidir': 'False',
+         p + '_act': 'tanh,tanh', p + '_orthinit': 'True', 'arch_lr': '0.0016', 'arch_halving_factor': '0.5',
+         'arch_improvement_threshold': '0.001', 'arch_opt': 'rmsprop', 'opt_momentum': '0.0', 'opt_alpha': '0.95',
+         'opt_eps': '1e-8', 'opt_centered': 'False', 'opt_weight_decay': '0.0', 'out_folder': ''}
+    o.update(over)
+    return o
+
+
+RNN_FAMILY = [   # (fixture, option prefix, class, overrides)
+    ('train_gru', 'gru', 'GRU', {}),
+    ('train_gru_bidir_nobn', 'gru', 'GRU', {'gru_bidir': 'True', 'gru_use_batchnorm': 'False,False', 'gru_drop': '0.0,0.1'}),
+    ('train_ligru', 'ligru', 'liGRU', {'ligru_act': 'relu,relu'}),
+    ('train_minimalgru', 'minimalgru', 'minimalGRU', {}),
+    ('train_rnn', 'rnn', 'RNN', {'rnn_act': 'relu,relu'}),
+]
+
+
+def gen_gru_family():
+    """the reference's own GRU / liGRU / minimalGRU / RNN (dense; neural_networks.py:1240-1931) through
+    model_init / forward_model: two train steps each.  The plugin's block-sparse versions must reproduce them with
+    all-ones masks."""
+    for k, (tag, prefix, cls, over) in enumerate(RNN_FAMILY):
+        run_model(tag, 'train', T=6, B=3, D=12, arch1=rnn_family_opts(prefix, cls, **over), steps=2, seed=30 + k)
 
 
 def gen_run_nn():
