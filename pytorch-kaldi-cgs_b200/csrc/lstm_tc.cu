@@ -41,6 +41,7 @@ namespace hcgs {
 
 constexpr int TC_MAX_WARPS = 16;
 constexpr int TC_MAX_WARPS2 = 20;  // forward kernels with <= 2 strips per warp (register budget 65536 / 640)
+constexpr int TCB_CW = 18;         // compute warps of the backward kernel (+2 DMA warps)
 
 struct TcPlan {
     int CL = 0, H = 0, NS = 0;  // cluster size, hidden size, 4-row strips in total
@@ -50,11 +51,18 @@ struct TcPlan {
     // forward tables
     uint16_t* d_cg = nullptr;  // [CL][SPC][KS*4] column group of block j of the strip (0xFFFF = padding)
     uint8_t* d_nks = nullptr;  // [CL][SPC] k-steps actually used by the strip
-    // backward tables (blocks of CTA r in column-strip-major order)
-    int* d_blk_off = nullptr;     // [CL+1]
-    int* d_cs_ptr = nullptr;      // [CL][NS+1] CSR over column strips into the CTA's block list
-    uint16_t* d_blk_rs = nullptr;  // [n_blocks] local row strip of block e
-    uint16_t* d_blk_cs = nullptr;  // [n_blocks] column strip of block e
+    // backward tables: the kept blocks of CTA r in task order (warp, task, row-strip group, column strip)
+    int* d_blk_off = nullptr;      // [CL+1]
+    uint16_t* d_blk_rs = nullptr;  // [n_blocks] local row strip of block e (pack kernel)
+    uint16_t* d_blk_cs = nullptr;  // [n_blocks] column strip of block e (pack kernel)
+    int* d_grp_off = nullptr;      // [CL+1] row-strip groups per CTA
+    uint32_t* d_grp = nullptr;     // [n_groups] (local row strip * 32) | (kept column strips of the task's 8) << 16
+    int* d_task_off = nullptr;     // [CL+1]
+    int* d_task = nullptr;         // [n_tasks][8] {g0, g1, blk0, jlo, nst, dest, sl0, 0} (CTA-relative indices)
+    int* d_wtp = nullptr;          // [CL][TCB_CW+1] tasks of each compute warp
+    int* d_rx = nullptr;           // [CL][3] {bytes of partial dh the CTA receives from its peers per time step,
+                                   //          peers that send it nothing, bit mask of the peers it sends nothing to}
+    int max_cta_groups = 0, max_cta_tasks = 0;
     int64_t fwd_pack_u32 = 0, bwd_pack_u32 = 0;
 };
 
@@ -63,7 +71,12 @@ void tc_plan_free(TcPlan* t) {
     cudaFree(t->d_cg);
     cudaFree(t->d_nks);
     cudaFree(t->d_blk_off);
-    cudaFree(t->d_cs_ptr);
+    cudaFree(t->d_grp_off);
+    cudaFree(t->d_grp);
+    cudaFree(t->d_task_off);
+    cudaFree(t->d_task);
+    cudaFree(t->d_wtp);
+    cudaFree(t->d_rx);
     cudaFree(t->d_blk_rs);
     cudaFree(t->d_blk_cs);
     delete t;
@@ -121,27 +134,119 @@ static int tc_plan_get(const hcgs_plan* cplan, int CL, TcPlan** out) {
         for (size_t j = 0; j < l.size(); ++j) cgt[(size_t)s * t->KS * 4 + j] = l[j];
         nks[s] = (uint8_t)((l.size() + 3) / 4);
     }
-    // backward: per CTA, blocks grouped by column strip
-    std::vector<int> blk_off(CL + 1, 0), cs_ptr((size_t)CL * (NS + 1), 0);
+    // backward: the 8-strip (32-column) column blocks of U are the tasks of the compute warps.  A task keeps the
+    // partial dh of its <= 8 column strips in accumulators and walks the CTA's row strips: one A tile (the bf16 dpre
+    // of a row strip, 16 sequences x 4 rows x 4 gates) serves every kept block of that row strip inside the column
+    // block ("group").  Tasks are cut at destination-CTA boundaries, heavy ones are halved, and the result is spread
+    // over the warps longest-first.  Column blocks without a kept block in the CTA's rows have no task: their
+    // partial sums are zero and the owner's receive slots keep the zeros they were initialised with.
+    struct HTask {
+        int base, jlo, nst, ngroups, nblocks, cost;
+    };
+    const int CS = CL * t->SPC;
+    auto measure = [&](int r, HTask& k) {
+        k.ngroups = k.nblocks = 0;
+        for (int sl = 0; sl < t->SPC; ++sl) {
+            const int s = r * t->SPC + sl;
+            if (s >= NS) break;
+            int n = 0;
+            for (int j = k.jlo; j < k.jlo + k.nst; ++j)
+                if (k.base + j < NS && occ[(size_t)s * NS + k.base + j]) ++n;
+            if (n) ++k.ngroups, k.nblocks += n;
+        }
+        k.cost = k.ngroups ? 12 + 5 * k.ngroups + 2 * k.nblocks : 0;
+    };
+    std::vector<int> blk_off(CL + 1, 0), grp_off(CL + 1, 0), task_off(CL + 1, 0), wtp((size_t)CL * (TCB_CW + 1), 0),
+        rx((size_t)CL * 3, 0), pair((size_t)CL * CL, 0), tasks;
     std::vector<uint16_t> blk_rs, blk_cs;
+    std::vector<uint32_t> grp;
     for (int r = 0; r < CL; ++r) {
-        blk_off[r] = (int)blk_rs.size();
-        int run = 0;
-        for (int c = 0; c < NS; ++c) {
-            cs_ptr[(size_t)r * (NS + 1) + c] = run;
-            for (int sl = 0; sl < t->SPC; ++sl) {
-                const int s = r * t->SPC + sl;
-                if (s < NS && occ[(size_t)s * NS + c]) {
-                    blk_rs.push_back((uint16_t)sl);
-                    blk_cs.push_back((uint16_t)c);
-                    ++run;
-                }
+        std::vector<HTask> work;
+        for (int base = 0; base < NS; base += 8) {
+            int j = 0;
+            while (j < 8 && base + j < NS) {
+                const int d = (base + j) / t->SPC;
+                int je = j;
+                while (je < 8 && base + je < NS && (base + je) / t->SPC == d) ++je;
+                HTask k{base, j, je - j, 0, 0, 0};
+                measure(r, k);
+                if (k.cost) work.push_back(k);
+                j = je;
             }
         }
-        cs_ptr[(size_t)r * (NS + 1) + NS] = run;
-        t->max_cta_blocks = std::max(t->max_cta_blocks, run);
+        int64_t total = 0;
+        for (const HTask& k : work) total += k.cost;
+        const int64_t limit = std::max<int64_t>(40, (total * 5 / 4 + TCB_CW - 1) / TCB_CW);
+        for (size_t i = 0; i < work.size();) {
+            if (work[i].cost > limit && work[i].nst > 1) {
+                HTask lo = work[i], hi = work[i];
+                lo.nst = work[i].nst / 2;
+                hi.jlo = lo.jlo + lo.nst;
+                hi.nst = work[i].nst - lo.nst;
+                measure(r, lo);
+                measure(r, hi);
+                work.erase(work.begin() + i);
+                if (hi.cost) work.insert(work.begin() + i, hi);
+                if (lo.cost) work.insert(work.begin() + i, lo);
+                continue;  // the halves are looked at again
+            }
+            ++i;
+        }
+        std::stable_sort(work.begin(), work.end(), [](const HTask& x, const HTask& y) { return x.cost > y.cost; });
+        std::vector<std::vector<int>> per_warp(TCB_CW);
+        std::vector<int64_t> load(TCB_CW, 0);
+        for (size_t i = 0; i < work.size(); ++i) {
+            int w = 0;
+            for (int x = 1; x < TCB_CW; ++x)
+                if (load[x] < load[w]) w = x;
+            per_warp[w].push_back((int)i);
+            load[w] += work[i].cost;
+        }
+        blk_off[r] = (int)blk_rs.size();
+        grp_off[r] = (int)grp.size();
+        task_off[r] = (int)tasks.size() / 8;
+        int nt = 0;
+        for (int w = 0; w < TCB_CW; ++w) {
+            wtp[(size_t)r * (TCB_CW + 1) + w] = nt;
+            for (int i : per_warp[w]) {
+                const HTask& k = work[i];
+                const int g0 = (int)grp.size() - grp_off[r], b0 = (int)blk_rs.size() - blk_off[r];
+                for (int sl = 0; sl < t->SPC; ++sl) {
+                    const int s = r * t->SPC + sl;
+                    if (s >= NS) break;
+                    uint32_t m = 0;
+                    for (int j = k.jlo; j < k.jlo + k.nst; ++j)
+                        if (k.base + j < NS && occ[(size_t)s * NS + k.base + j]) {
+                            m |= 1u << j;
+                            blk_rs.push_back((uint16_t)sl);
+                            blk_cs.push_back((uint16_t)(k.base + j));
+                        }
+                    if (m) grp.push_back((uint32_t)(sl * 32) | (m << 16));
+                }
+                const int first = k.base + k.jlo, dest = first / t->SPC;
+                const int rec[8] = {g0, (int)grp.size() - grp_off[r], b0, k.jlo, k.nst, dest, first - dest * t->SPC, 0};
+                tasks.insert(tasks.end(), rec, rec + 8);
+                if (dest != r) rx[(size_t)dest * 3] += k.nst * 256, pair[(size_t)r * CL + dest] += k.nst * 256;
+                ++nt;
+            }
+        }
+        wtp[(size_t)r * (TCB_CW + 1) + TCB_CW] = nt;
+        t->max_cta_blocks = std::max(t->max_cta_blocks, (int)blk_rs.size() - blk_off[r]);
+        t->max_cta_groups = std::max(t->max_cta_groups, (int)grp.size() - grp_off[r]);
+        t->max_cta_tasks = std::max(t->max_cta_tasks, nt);
+        (void)CS;
     }
+    // a pair of CTAs without traffic still exchanges one empty arrival per step: the reduce-scatter is what keeps the
+    // cluster in lock step (nobody runs more than one step ahead), and the handshake barriers count on that
+    for (int src = 0; src < CL; ++src)
+        for (int dst = 0; dst < CL; ++dst)
+            if (src != dst && pair[(size_t)src * CL + dst] == 0) {
+                ++rx[(size_t)dst * 3 + 1];
+                rx[(size_t)src * 3 + 2] |= 1 << dst;
+            }
     blk_off[CL] = (int)blk_rs.size();
+    grp_off[CL] = (int)grp.size();
+    task_off[CL] = (int)tasks.size() / 8;
     t->n_blocks = (int)blk_rs.size();
     t->fwd_pack_u32 = (int64_t)CL * t->SPC * t->KS * 2 * 32 * 2;
     t->bwd_pack_u32 = (int64_t)std::max(t->n_blocks, 1) * 16 * 2;
@@ -149,7 +254,12 @@ static int tc_plan_get(const hcgs_plan* cplan, int CL, TcPlan** out) {
     rc |= tc_upload(cgt, &t->d_cg);
     rc |= tc_upload(nks, &t->d_nks);
     rc |= tc_upload(blk_off, &t->d_blk_off);
-    rc |= tc_upload(cs_ptr, &t->d_cs_ptr);
+    rc |= tc_upload(grp_off, &t->d_grp_off);
+    rc |= tc_upload(grp, &t->d_grp);
+    rc |= tc_upload(task_off, &t->d_task_off);
+    rc |= tc_upload(tasks, &t->d_task);
+    rc |= tc_upload(wtp, &t->d_wtp);
+    rc |= tc_upload(rx, &t->d_rx);
     rc |= tc_upload(blk_rs, &t->d_blk_rs);
     rc |= tc_upload(blk_cs, &t->d_blk_cs);
     if (rc) {
@@ -177,20 +287,21 @@ static size_t tc_fwd2_smem(const TcPlan& t, int NB) {
 }
 static size_t tc_fwd_smem_v(const TcPlan& t, int NB) { return tc_fwd2_smem(t, NB); }
 
-static size_t tc_bwd2_smem(const TcPlan& t, int NB) {
+static size_t tc_bwd3_smem(const TcPlan& t, int NB) {
     size_t b = 128;                                                   // alignment slack (TMA boxes: 128 B)
     b += (size_t)2 * NB * t.Hc * 16;                                  // gate stages (dense boxes)
     b += ((size_t)2 * NB * t.Hc * 4 + 127) & ~(size_t)127;            // c ring
     b += ((size_t)NB * t.Hc * 4 + 127) & ~(size_t)127;                // dh
-    b += ((size_t)t.CL * NB * t.Hc * 4 + 127) & ~(size_t)127;         // partial-dh slots, one per source CTA
+    b += ((size_t)t.CL * t.SPC * 256 + 127) & ~(size_t)127;           // partial-dh slots [source][strip][16 x 4]
     b += tc_align16((size_t)NB * (t.Hc * 4 + 8) * 2);                 // bf16 dpre tile (MMA A operand)
     b += tc_align16((size_t)std::max(t.max_cta_blocks, 1) * 16 * 8);  // B fragments (16 lanes x 8 B)
-    b += tc_align16((size_t)std::max(t.max_cta_blocks, 1) * 2);       // row strip of each block
-    b += tc_align16((size_t)(t.NS + 1) * 4);                          // CSR over column strips
+    b += tc_align16((size_t)std::max(t.max_cta_groups, 1) * 4);       // row-strip groups
+    b += tc_align16((size_t)std::max(t.max_cta_tasks, 1) * 32);       // tasks
+    b += tc_align16((size_t)(TCB_CW + 1) * 4);                        // tasks of each warp
     b += 64;
     return b;
 }
-static size_t tc_bwd_smem_v(const TcPlan& t, int NB) { return tc_bwd2_smem(t, NB); }
+static size_t tc_bwd_smem_v(const TcPlan& t, int NB) { return tc_bwd3_smem(t, NB); }
 
 // ---- PTX helpers -----------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -768,71 +879,91 @@ __global__ void __launch_bounds__((SPW <= 2 ? TC_MAX_WARPS2 : TC_MAX_WARPS) * 32
 
 // ---- backward ----------------------------------------------------------------------------------
 struct TcBwdArgs {
-    const uint2* wfrag;      // [n_blocks][16]  (lanes 0..15 of the B fragment; lanes 16..31 are zero)
-    const int* blk_off;      // [CL+1]
-    const int* cs_ptr;       // [CL][NS+1]
-    const uint16_t* blk_rs;  // [n_blocks]
-    const float* dh_out;     // [T*B][H]
-    const float* gates;      // [T*B][4*ldH] gate-interleaved
-    const float* c;          // [T*B][ldH]
+    const uint2* wfrag;       // [n_blocks][16]  (lanes 0..15 of the B fragment; n columns 4..7 are not used)
+    const int* blk_off;       // [CL+1]
+    const int* grp_off;       // [CL+1]
+    const uint32_t* grp;      // [n_groups]
+    const int* task_off;      // [CL+1]
+    const int* task;          // [n_tasks][8]
+    const int* wtp;           // [CL][TCB_CW+1]
+    const int* rx;            // [CL][3] {bytes received per step, silent sources, mask of silent destinations}
+    const float* dh_out;      // [T*B][ldH]
+    const float* gates;       // [T*B][4*ldH] gate-interleaved
+    const float* c;           // [T*B][ldH]
     const float* drop;
     float drop_scalar;
     float* dpre;             // [T*B][4*ldH] gate-interleaved fp32
     __nv_bfloat16* dpreb;    // optional bf16 copy, same layout
-    int T, B, H, ldH, CL, SPC, NS, HP, max_blocks, act;
-    int dbg;  // timing experiments only (HCGS_TC_DEBUG): 1 = no global stores, 2 = no prefetch, 4 = no MMA, 8 = no push
-    // TMA build: dh_out is [T*B][ldH]; [T][B][cols] tensor maps with boxes {BW | Hc, 16, 1}
+    int T, B, H, ldH, CL, SPC, NS, HP, max_blocks, max_groups, max_tasks, act;
+    int dbg;  // timing experiments only (HCGS_TC_DEBUG): 1 = no global stores, 4 = no MMA
+    // [T][B][cols] tensor maps with boxes {BW | Hc, 16, 1}
     int BW, NBX;
     alignas(64) CUtensorMap tm_gates, tm_c, tm_dh;
 };
 
-// ---- backward, asynchronous build ----------------------------------------------------------------
-// Organised like the forward kernel after the per-phase clock trace of a first LSU-based version (item phase 48 %,
-// MMA 27 %, push + release fence 17 % of a step there):
-//   * 16 compute warps + 2 DMA warps; no block-wide barrier inside the time loop, only mbarriers;
-//   * gates / c / dh of a step arrive by TMA boxes ([16 sequences][slice]) one step ahead, so the item phase is
-//     shared-memory loads + math + two coalesced global stores (dpre fp32, dpre bf16) with precomputed offsets;
-//   * the bf16 dpre tile is unit-major (k = row-in-block*4 + gate), i.e. exactly the global dpre layout;
-//   * partial dh sums leave the MMA accumulators directly as 8-byte st.async stores that complete transaction
-//     bytes on the owner's barrier: no staging buffer, no push phase, no release fence; the traffic overlaps the
-//     (shared-memory bound) MMA phase of the other warps;
-//   * the receive slots are single-buffered; a consumed-handshake (one remote arrive per peer and step, sent by
-//     a DMA warp) guards their reuse.
-// the m16 x k16 bf16 A tile of one mma in ONE shared-memory instruction (instead of four 4-byte gathers): lane i
-// passes the address of row (i & 15), k-half (i >> 4); registers come back in a0..a3 fragment order
+// the m16 x k16 bf16 A tile of one mma in ONE shared-memory instruction: lane i passes the address of row (i & 15),
+// k-half (i >> 4); registers come back in a0..a3 fragment order
 __device__ __forceinline__ void ldmatrix_x4(uint32_t (&r)[4], uint32_t addr) {
     asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];"
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
                  : "r"(addr));
 }
-__device__ __forceinline__ void st_async_v2(uint32_t cluster_addr, float x, float y, uint32_t mbar_cluster) {
-    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.b32 [%0], {%1, %2}, [%3];" ::"r"(
-                     cluster_addr),
-                 "r"(__float_as_uint(x)), "r"(__float_as_uint(y)), "r"(mbar_cluster)
-                 : "memory");
+// register-only form the compiler may schedule freely
+__device__ __forceinline__ void mma_bf16_16816_s(float (&d)[4], const uint32_t (&af)[4], uint32_t b0, uint32_t b1) {
+    asm("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, "
+        "{%0, %1, %2, %3};"
+        : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+        : "r"(af[0]), "r"(af[1]), "r"(af[2]), "r"(af[3]), "r"(b0), "r"(b1));
+}
+// B fragments are written once before the time loop: a plain (schedulable) shared load
+__device__ __forceinline__ uint2 lds_u2(uint32_t addr) {
+    uint2 v;
+    asm("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
+    return v;
 }
 
-constexpr int TCB_CW = 16;  // compute warps of the backward kernel (+2 DMA warps)
-
-template <int NT, int IT, int ACT>
-__global__ void __launch_bounds__((TCB_CW + 2) * 32, 1) lstm_tc_bwd2_kernel(const __grid_constant__ TcBwdArgs a) {
-    constexpr int NB = NT * 16;
-    static_assert(NT == 1, "one m16 tile of sequences per cluster");
+// ---- backward, third build ----------------------------------------------------------------------
+// 18 compute warps + 2 DMA warps; no block-wide barrier inside the time loop, only mbarriers.  Per time step k
+// (descending):
+//   item phase : every compute thread owns one unit of the CTA's slice and up to IT sequences: dh_k = dh_out[k] +
+//                the partial sums the CLUSTER pushed into this CTA's slots during step k+1; gate derivatives from
+//                the TMA-staged gates / c; dpre leaves as fp32 + bf16 global stores and as the bf16 A tile
+//                (unit-major, k = row-in-strip * 4 + gate) in shared memory;
+//   MMA phase  : a warp walks its tasks (plan: column block of <= 8 strips x this CTA's rows).  Per row-strip
+//                group ONE ldmatrix.x4 brings the 16 x 16 A tile, then one mma per kept 4x4 block of the group
+//                into the accumulator of its column strip (warp-uniform predicates from the group's bit mask);
+//                round 1 loaded the A tile once per block and that shared-memory traffic bounded the phase;
+//   push       : a finished task leaves straight from the accumulators: two shuffles turn a strip's accumulator
+//                layout into 16-byte row pieces and ONE st.async.v4 (16 lanes, 256 contiguous bytes) per strip
+//                writes them into the owner's slot [source][strip][16 rows x 4 columns] and completes transaction
+//                bytes on its barrier (tools/probe/dsmem_push.cu: 2.4 k cycles per exchange against 3.9 k for the
+//                8-byte form of round 1; staged bulk copies are slower than either);
+//   the rows of a strip's slot are XOR-swizzled with the strip index so that the item phase reads them without
+//   bank conflicts; the slots are single-buffered, a consumed-handshake (one remote arrive per peer and step)
+//   guards their reuse; the owner sums the sources in rank order (deterministic).
+template <int IT, int ACT>
+__global__ void __launch_bounds__((TCB_CW + 2) * 32, 1) lstm_tc_bwd3_kernel(const __grid_constant__ TcBwdArgs a) {
+    constexpr int NB = 16;
+    constexpr int CW = TCB_CW;
+    constexpr int cthreads = CW * 32;
     cg::cluster_group cluster = cg::this_cluster();
     const int rank = (int)cluster.block_rank();
-    const int CL = a.CL, SPC = a.SPC, NS = a.NS, H = a.H, ldH = a.ldH;
+    const int CL = a.CL, SPC = a.SPC, H = a.H, ldH = a.ldH;
     const int b0 = (blockIdx.x / CL) * NB;
     const int Hc = SPC * 4;
     const int u0 = rank * Hc;
     const int nv = max(0, min(Hc, ldH - u0));
     const int DPS = Hc * 4 + 8;  // bf16 elements per dpre row: pitch = 16 mod 128 bytes (Hc multiple of 8)
     const int BW = a.BW, NBX = a.NBX;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    constexpr int CW = TCB_CW;
-    constexpr int cthreads = CW * 32;
+    const int tid = threadIdx.x, lane = tid & 31;
+    // broadcast form: the compiler then treats the warp index (and the task / group tables read through it) as
+    // warp-uniform and keeps the predicated mma free of re-convergence instructions
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
     const bool is_dma = warp >= CW;
     const int blk0 = a.blk_off[rank];
     const int nblk = a.blk_off[rank + 1] - blk0;
+    const int grp0 = a.grp_off[rank], ngrp = a.grp_off[rank + 1] - grp0;
+    const int task0 = a.task_off[rank], ntask = a.task_off[rank + 1] - task0;
 
     extern __shared__ __align__(16) unsigned char smem_raw[];
     unsigned char* sp = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
@@ -842,16 +973,18 @@ __global__ void __launch_bounds__((TCB_CW + 2) * 32, 1) lstm_tc_bwd2_kernel(cons
     sp += tc_align128((size_t)2 * NB * Hc * 4);
     float* dh_s = reinterpret_cast<float*>(sp);  // [16][Hc]
     sp += tc_align128((size_t)NB * Hc * 4);
-    float* slots = reinterpret_cast<float*>(sp);  // [CL][16][Hc]: partial dh of the next step, one slot per source
-    sp += tc_align128((size_t)CL * NB * Hc * 4);
+    float* slots = reinterpret_cast<float*>(sp);  // [CL][SPC][16 x 4]: partial dh of the next step, one slot per source
+    sp += tc_align128((size_t)CL * SPC * 256);
     __nv_bfloat16* dpre_s = reinterpret_cast<__nv_bfloat16*>(sp);  // [16][DPS], unit-major (u*4+g)
     sp += tc_align16((size_t)NB * DPS * 2);
     uint2* wf_s = reinterpret_cast<uint2*>(sp);
     sp += tc_align16((size_t)a.max_blocks * 16 * 8);
-    uint16_t* rs_s = reinterpret_cast<uint16_t*>(sp);
-    sp += tc_align16((size_t)a.max_blocks * 2);
-    int* csp_s = reinterpret_cast<int*>(sp);
-    sp += tc_align16((size_t)(NS + 1) * 4);
+    uint32_t* grp_s = reinterpret_cast<uint32_t*>(sp);
+    sp += tc_align16((size_t)a.max_groups * 4);
+    int4* task_s = reinterpret_cast<int4*>(sp);
+    sp += tc_align16((size_t)a.max_tasks * 32);
+    int* wtp_s = reinterpret_cast<int*>(sp);
+    sp += tc_align16((size_t)(CW + 1) * 4);
     uint64_t* mbar = reinterpret_cast<uint64_t*>(sp);
     const uint32_t mbar_addr = smem_u32(mbar);
     // [0..1] gate stage landed  [2] c / dh boxes landed  [3] slots full (CW own arrivals + arm + peers' bytes)
@@ -861,22 +994,26 @@ __global__ void __launch_bounds__((TCB_CW + 2) * 32, 1) lstm_tc_bwd2_kernel(cons
     const uint32_t slots_addr = smem_u32(slots);
     const int stage_floats = NB * Hc * 4;
     const uint32_t stage_bytes = (uint32_t)stage_floats * 4, box_bytes = (uint32_t)NB * Hc * 4;
+    const uint32_t rx_bytes = (uint32_t)a.rx[rank * 3];
+    const int silent_in = a.rx[rank * 3 + 1], silent_out = a.rx[rank * 3 + 2];
 
     TC_TRACE_INIT();
     {
         const uint4* s4 = reinterpret_cast<const uint4*>(a.wfrag + (size_t)blk0 * 16);
         uint4* d4 = reinterpret_cast<uint4*>(wf_s);
         for (int i = tid; i < nblk * 8; i += blockDim.x) d4[i] = __ldg(s4 + i);
-        for (int i = tid; i < nblk; i += blockDim.x) rs_s[i] = a.blk_rs[blk0 + i];
-        for (int i = tid; i <= NS; i += blockDim.x) csp_s[i] = a.cs_ptr[(size_t)rank * (NS + 1) + i];
-        for (int i = tid; i < CL * NB * Hc; i += blockDim.x) slots[i] = 0.f;
+        for (int i = tid; i < ngrp; i += blockDim.x) grp_s[i] = a.grp[grp0 + i];
+        const int4* t4 = reinterpret_cast<const int4*>(a.task) + (size_t)task0 * 2;
+        for (int i = tid; i < ntask * 2; i += blockDim.x) task_s[i] = __ldg(t4 + i);
+        for (int i = tid; i <= CW; i += blockDim.x) wtp_s[i] = a.wtp[(size_t)rank * (CW + 1) + i];
+        for (int i = tid; i < CL * SPC * 64; i += blockDim.x) slots[i] = 0.f;
         uint32_t* dz = reinterpret_cast<uint32_t*>(dpre_s);
         for (int i = tid; i < NB * DPS / 2; i += blockDim.x) dz[i] = 0u;
         if (tid == 0) {
             mbar_init(mb_g, 1u);
             mbar_init(mb_g + 8, 1u);
             mbar_init(mb_s, 1u);
-            mbar_init(mb_full, (uint32_t)CW + 1u);
+            mbar_init(mb_full, (uint32_t)(CW + 1 + silent_in));
             mbar_init(mb_items, (uint32_t)CW);
             mbar_init(mb_free, (uint32_t)(CL - 1));
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -907,32 +1044,31 @@ __global__ void __launch_bounds__((TCB_CW + 2) * 32, 1) lstm_tc_bwd2_kernel(cons
         if (a.T > 1) tma_load_3d(smem_u32(c_s + (size_t)((a.T - 2) & 1) * NB * Hc), &a.tm_c, u0, b0, a.T - 2, mb_s);
     }
 
-    // ---- pointwise items (unit fastest => conflict-free shared loads, coalesced 16-byte global stores) --------
-    int it_sm[IT];        // b*Hc + ul
-    int it_gs[IT];        // offset inside a gate stage (box, row, column)
-    uint32_t it_go[IT];   // element offset of the item inside one time step of dpre: (b0+b)*4*ldH + u*4
-    int it_ds[IT];        // offset inside the bf16 dpre tile
-    int it_flag[IT];      // bit0 = item exists, bit1 = real unit of a present sequence, bit2 = pad column to zero
+    // ---- pointwise items: thread -> unit `ul` of the slice (fastest over the lanes => conflict-free shared loads,
+    // coalesced 16-byte global stores) and the sequences bq, bq + BPP, ...; every offset is affine in the slot j
+    const int BPP = min(NB, cthreads / Hc);  // sequences per pass
+    const bool active = !is_dma && tid < BPP * Hc;
+    const int bq = active ? tid / Hc : 0, ul = active ? tid - (tid / Hc) * Hc : 0;
+    const int u = u0 + ul;
+    const bool unit_ok = active && u < H, unit_pad = active && u >= H && u < ldH;
+    const int swz = (ul >> 2) & 7;
+    const int sm0 = bq * Hc + ul;                                                          // dh_s / c_s
+    const int gs0 = ((ul * 4) / BW) * (NB * BW) + bq * BW + (ul * 4) % BW;                 // inside a gate stage
+    const int ds0 = bq * DPS + ul * 4;                                                     // bf16 dpre tile
+    const int so0 = (ul >> 2) * 64 + (ul & 3);                                             // inside one source's slots
+    const uint32_t go0 = (uint32_t)((size_t)(b0 + bq) * 4 * ldH + (size_t)u * 4);          // inside one step of dpre
     float dc_carry[IT], dr[IT];
 #pragma unroll
     for (int j = 0; j < IT; ++j) {
-        const int idx = tid + j * cthreads;
-        const bool in = !is_dma && idx < Hc * NB;
-        const int b = in ? idx / Hc : 0, ul = in ? idx % Hc : 0;
-        const int u = u0 + ul;
-        const bool ok = in && u < H && b0 + b < a.B;
-        const bool pad = in && !ok && u < ldH && b0 + b < a.B;
-        it_flag[j] = (in ? 1 : 0) | (ok ? 2 : 0) | (pad ? 4 : 0);
-        it_sm[j] = b * Hc + ul;
-        it_ds[j] = b * DPS + ul * 4;
-        it_gs[j] = ((ul * 4) / BW) * (NB * BW) + b * BW + (ul * 4) % BW;
-        it_go[j] = (uint32_t)((size_t)(b0 + b) * 4 * ldH + (size_t)u * 4);
+        const int b = bq + j * BPP;
         dc_carry[j] = 0.f;
         dr[j] = a.drop_scalar;
-        if (ok && a.drop) dr[j] = __ldg(a.drop + (size_t)(b0 + b) * H + u);
+        if (unit_ok && b < NB && b0 + b < a.B && a.drop) dr[j] = __ldg(a.drop + (size_t)(b0 + b) * H + u);
     }
-    const int br = lane >> 2;
-    const int koff = (lane & 3) * 2;
+    const int br = lane >> 2, q = lane & 3;
+    const int wt0 = is_dma ? 0 : wtp_s[warp], wt1 = is_dma ? 0 : wtp_s[warp + 1];
+    const uint32_t lm_base = smem_u32(dpre_s) + (uint32_t)(((lane & 15) * DPS + (lane >> 4) * 8) * 2);
+    const uint32_t wf_lane = smem_u32(wf_s) + (uint32_t)(lane & 15) * 8u;
     cluster.sync();
 
     for (int s = 0; s < a.T; ++s) {
@@ -946,44 +1082,49 @@ __global__ void __launch_bounds__((TCB_CW + 2) * 32, 1) lstm_tc_bwd2_kernel(cons
             }
             if (s > 0) mbar_wait_dbg(mb_full, (uint32_t)((s - 1) & 1), a.dbg, 3, s);  // partial dh_k from every CTA has landed
             TC_TRACE(1);
-            const float* gst = gates_s + (size_t)(k & 1) * stage_floats;
-            const float* ck_s = c_s + (size_t)(k & 1) * NB * Hc;
-            const float* cm_s = c_s + (size_t)((k & 1) ^ 1) * NB * Hc;
-            float* dpre_k = a.dpre ? a.dpre + (size_t)k * a.B * 4 * ldH : nullptr;
-            __nv_bfloat16* dpreb_k = a.dpreb ? a.dpreb + (size_t)k * a.B * 4 * ldH : nullptr;
+            if (active) {
+                const float* gst = gates_s + (size_t)(k & 1) * stage_floats;
+                const float* ck_s = c_s + (size_t)(k & 1) * NB * Hc;
+                const float* cm_s = c_s + (size_t)((k & 1) ^ 1) * NB * Hc;
+                float* dpre_k = a.dpre ? a.dpre + (size_t)k * a.B * 4 * ldH : nullptr;
+                __nv_bfloat16* dpreb_k = a.dpreb ? a.dpreb + (size_t)k * a.B * 4 * ldH : nullptr;
 #pragma unroll
-            for (int j = 0; j < IT; ++j) {
-                if (!(it_flag[j] & 1)) continue;
-                const bool ok = (it_flag[j] & 2) != 0;
-                const int sm = it_sm[j];
-                float dh = dh_s[sm];
-                if (s > 0) {
-                    for (int src = 0; src < CL; ++src) dh += slots[(size_t)src * NB * Hc + sm];
+                for (int j = 0; j < IT; ++j) {
+                    const int b = bq + j * BPP;
+                    if (b >= NB) break;
+                    const bool ok = unit_ok && b0 + b < a.B;
+                    const int sm = sm0 + j * BPP * Hc;
+                    float dh = dh_s[sm];
+                    if (s > 0) {
+                        const float* sl_p = slots + so0 + ((b ^ swz) << 2);
+                        for (int src = 0; src < CL; ++src) dh += sl_p[(size_t)src * SPC * 64];
+                    }
+                    const float4 g4 = *reinterpret_cast<const float4*>(gst + gs0 + j * BPP * BW);
+                    const float cval = ck_s[sm];
+                    const float cm1 = (k > 0) ? cm_s[sm] : 0.f;  // c_{-1} = 0
+                    const float fg = g4.x, ig = g4.y, og = g4.z, gg = g4.w;
+                    const float tc = (ACT == HCGS_ACT_TANH) ? fast_tanh(cval) : act_apply_fast(a.act, cval);
+                    const float dog = dh * tc;
+                    const float dct = dh * og * ((ACT == HCGS_ACT_TANH) ? (1.f - tc * tc) : act_grad_from_out(a.act, tc)) +
+                                      dc_carry[j];
+                    const float dig = dct * gg * dr[j];
+                    const float dgg = dct * ig * dr[j];
+                    const float dfg = dct * cm1;
+                    float4 dp;
+                    dp.x = dfg * fg * (1.f - fg);
+                    dp.y = dig * ig * (1.f - ig);
+                    dp.z = dog * og * (1.f - og);
+                    dp.w = dgg * ((ACT == HCGS_ACT_TANH) ? (1.f - gg * gg) : act_grad_from_out(a.act, gg));
+                    if (!ok) dp = make_float4(0.f, 0.f, 0.f, 0.f);
+                    dc_carry[j] = ok ? dct * fg : 0.f;
+                    const uint2 pb = make_uint2(pack_bf16x2(dp.x, dp.y), pack_bf16x2(dp.z, dp.w));
+                    if ((ok || (unit_pad && b0 + b < a.B)) && !(a.dbg & 1)) {
+                        const uint32_t go = go0 + (uint32_t)(j * BPP) * 4u * (uint32_t)ldH;
+                        if (dpre_k) *reinterpret_cast<float4*>(dpre_k + go) = dp;
+                        if (dpreb_k) *reinterpret_cast<uint2*>(dpreb_k + go) = pb;
+                    }
+                    *reinterpret_cast<uint2*>(dpre_s + ds0 + j * BPP * DPS) = pb;
                 }
-                const float4 g4 = *reinterpret_cast<const float4*>(gst + it_gs[j]);
-                const float cval = ck_s[sm];
-                const float cm1 = (k > 0) ? cm_s[sm] : 0.f;  // c_{-1} = 0
-                const float fg = g4.x, ig = g4.y, og = g4.z, gg = g4.w;
-                const float tc = (ACT == HCGS_ACT_TANH) ? fast_tanh(cval) : act_apply_fast(a.act, cval);
-                const float dog = dh * tc;
-                const float dct = dh * og * ((ACT == HCGS_ACT_TANH) ? (1.f - tc * tc) : act_grad_from_out(a.act, tc)) +
-                                  dc_carry[j];
-                const float dig = dct * gg * dr[j];
-                const float dgg = dct * ig * dr[j];
-                const float dfg = dct * cm1;
-                float4 dp;
-                dp.x = dfg * fg * (1.f - fg);
-                dp.y = dig * ig * (1.f - ig);
-                dp.z = dog * og * (1.f - og);
-                dp.w = dgg * ((ACT == HCGS_ACT_TANH) ? (1.f - gg * gg) : act_grad_from_out(a.act, gg));
-                if (!ok) dp = make_float4(0.f, 0.f, 0.f, 0.f);
-                dc_carry[j] = ok ? dct * fg : 0.f;
-                const uint2 pb = make_uint2(pack_bf16x2(dp.x, dp.y), pack_bf16x2(dp.z, dp.w));
-                if ((it_flag[j] & 6) && !(a.dbg & 1)) {
-                    if (dpre_k) *reinterpret_cast<float4*>(dpre_k + it_go[j]) = dp;
-                    if (dpreb_k) *reinterpret_cast<uint2*>(dpreb_k + it_go[j]) = pb;
-                }
-                *reinterpret_cast<uint2*>(dpre_s + it_ds[j]) = pb;
             }
             __syncwarp();
             if (lane == 0) mbar_arrive_local(mb_items);
@@ -991,66 +1132,62 @@ __global__ void __launch_bounds__((TCB_CW + 2) * 32, 1) lstm_tc_bwd2_kernel(cons
             if (k == 0) break;
             mbar_wait_dbg(mb_items, (uint32_t)(s & 1), a.dbg, 4, s);  // every warp's share of the bf16 dpre tile is in place
             TC_TRACE(3);
-            // ---- partial dh_{k-1} for every column strip from this CTA's rows; pushed as soon as a strip is done
+            // ---- partial dh_{k-1}: this warp's tasks
             bool freed = false;
-            const int q = lane & 3;
-            // every warp owns a run of adjacent column strips (so that the remote stores of a row are contiguous)
-            const int spw = (CL * SPC + CW - 1) / CW;
-            const int cs_end = min(CL * SPC, (warp + 1) * spw);
-            const uint32_t lm_base = smem_u32(dpre_s) + (uint32_t)(((lane & 15) * DPS + (lane >> 4) * 8) * 2);
-            constexpr int SB = 2;
-            for (int c0 = warp * spw; c0 < cs_end; c0 += SB) {
-                // two adjacent strips per trip; the kept blocks of a strip are loaded four at a time
-                float acc[SB][4];
+            for (int ti = wt0; ti < wt1; ++ti) {
+                const int4 ta = task_s[2 * ti], tb = task_s[2 * ti + 1];  // {g0, g1, blk0, jlo}, {nst, dest, sl0, -}
+                float acc[8][4];
 #pragma unroll
-                for (int t = 0; t < SB; ++t) {
-                    acc[t][0] = acc[t][1] = acc[t][2] = acc[t][3] = 0.f;
-                    const int cs = c0 + t;
-                    const bool live = cs < cs_end && cs < NS && !(a.dbg & 4);
-                    const int e0 = live ? csp_s[cs] : 0, e1 = live ? csp_s[cs + 1] : 0;
-                    for (int e = e0; e < e1; e += 4) {
-                        const int n = e1 - e;
-                        uint32_t af[4][4];
-                        uint2 bw[4];
+                for (int j = 0; j < 8; ++j) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.f;
+                uint32_t bp = wf_lane + (uint32_t)ta.z * 128u;
+                const int g1 = (a.dbg & 4) ? ta.x : ta.y;
+                for (int g = ta.x; g < g1; ++g) {
+                    const uint32_t meta = grp_s[g];
+                    uint32_t af[4];
+                    ldmatrix_x4(af, lm_base + (meta & 0xFFFFu));
 #pragma unroll
-                        for (int x = 0; x < 4; ++x) {
-                            if (x < n) {  // warp-uniform
-                                const int rs = rs_s[e + x];
-                                bw[x] = make_uint2(0u, 0u);
-                                if (lane < 16) bw[x] = wf_s[(size_t)(e + x) * 16 + lane];
-                                ldmatrix_x4(af[x], lm_base + (uint32_t)rs * 32u);
-                            }
+                    for (int j = 0; j < 8; ++j)
+                        if (meta & (0x10000u << j)) {  // warp-uniform
+                            const uint2 bw = lds_u2(bp);
+                            bp += 128u;
+                            mma_bf16_16816_s(acc[j], af, bw.x, bw.y);
                         }
-#pragma unroll
-                        for (int x = 0; x < 4; ++x)
-                            if (x < n) mma_bf16_16816(acc[t], af[x][0], af[x][1], af[x][2], af[x][3], bw[x].x, bw[x].y);
-                    }
                 }
-                // ---- results leave straight from the accumulators: lanes q < 2 hold columns 2q, 2q+1 of rows br and
-                // br+8, i.e. 8 contiguous bytes each (no shuffles: the shared-memory / shuffle pipe is what bounds
-                // this phase, ~2.6 cycles per warp instruction)
+                // ---- the task's strips leave from the accumulators.  Lane (br, q) holds columns 2q, 2q+1 of rows br
+                // and br+8 (q < 2; n columns 4..7 are unused): after one exchange with the neighbour lane q = 0 owns
+                // the 16 bytes of row br and q = 1 those of row br + 8
+                const int d = tb.y;
+                const bool remote = d != rank;
+                if (remote && !freed) {  // the peers have consumed the slots of this step
+                    TC_TRACE(4);
+                    mbar_wait_dbg(mb_free, (uint32_t)(s & 1), a.dbg, 5, s);
+                    freed = true;
+                    TC_TRACE(5);
+                }
+                const uint32_t obase = slots_addr + (uint32_t)((rank * SPC + tb.z) * 256);
+                const uint32_t rbase = remote ? mapa_u32(obase, (uint32_t)d) : obase;
+                const uint32_t rbar = remote ? mapa_u32(mb_full, (uint32_t)d) : 0u;
+                const int row = br + 8 * (q & 1);
 #pragma unroll
-                for (int t = 0; t < SB; ++t) {
-                    const int cs = c0 + t;
-                    if (cs >= cs_end) break;  // warp-uniform
-                    const int d = cs / SPC;
-                    if (d != rank && !freed) {  // the peers have consumed the slots of this step
-                        TC_TRACE(4);
-                        mbar_wait_dbg(mb_free, (uint32_t)(s & 1), a.dbg, 5, s);
-                        freed = true;
-                        TC_TRACE(5);
-                    }
-                    if (q < 2) {
-                        const uint32_t off = (uint32_t)((((size_t)rank * NB + br) * Hc + (cs - d * SPC) * 4 + koff) * 4);
-                        if (d == rank) {
-                            float* p = reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(slots) + off);
-                            *reinterpret_cast<float2*>(p) = make_float2(acc[t][0], acc[t][1]);
-                            *reinterpret_cast<float2*>(p + 8 * Hc) = make_float2(acc[t][2], acc[t][3]);
-                        } else if (!(a.dbg & 8)) {
-                            const uint32_t ra = mapa_u32(slots_addr + off, (uint32_t)d);
-                            const uint32_t rb = mapa_u32(mb_full, (uint32_t)d);
-                            st_async_v2(ra, acc[t][0], acc[t][1], rb);
-                            st_async_v2(ra + (uint32_t)(8 * Hc * 4), acc[t][2], acc[t][3], rb);
+                for (int j = 0; j < 8; ++j) {
+                    const int tj = j - ta.w;
+                    if (tj >= 0 && tj < tb.x) {  // warp-uniform
+                        const float sx = (q & 1) ? acc[j][0] : acc[j][2];
+                        const float sy = (q & 1) ? acc[j][1] : acc[j][3];
+                        const float rx = __shfl_xor_sync(0xffffffffu, sx, 1);
+                        const float ry = __shfl_xor_sync(0xffffffffu, sy, 1);
+                        uint4 v;
+                        v.x = __float_as_uint((q & 1) ? rx : acc[j][0]);
+                        v.y = __float_as_uint((q & 1) ? ry : acc[j][1]);
+                        v.z = __float_as_uint((q & 1) ? acc[j][2] : rx);
+                        v.w = __float_as_uint((q & 1) ? acc[j][3] : ry);
+                        const uint32_t off = (uint32_t)(tj * 256 + ((row ^ ((tb.z + tj) & 7)) << 4));
+                        if (q < 2 && !(a.dbg & 8)) {
+                            if (remote) st_async_v4(rbase + off, v, rbar);
+                            else
+                                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(rbase + off), "r"(v.x),
+                                             "r"(v.y), "r"(v.z), "r"(v.w)
+                                             : "memory");
                         }
                     }
                 }
@@ -1062,8 +1199,8 @@ __global__ void __launch_bounds__((TCB_CW + 2) * 32, 1) lstm_tc_bwd2_kernel(cons
             // ============================ DMA warps ==============================================================
             if (warp == CW) {
                 mbar_wait_dbg(mb_items, (uint32_t)(s & 1), a.dbg, 6, s);  // item phase of step k is over: its input buffers are free
-                if (k >= 1 && nv > 0 && !(a.dbg & 2)) {
-                    if (!(a.dbg & 16)) load_gates(k - 2);
+                if (k >= 1 && nv > 0) {
+                    load_gates(k - 2);
                     mbar_expect_tx(mb_s, box_bytes * (k >= 2 ? 2u : 1u));
                     tma_load_3d(smem_u32(dh_s), &a.tm_dh, u0, b0, k - 1, mb_s);
                     if (k >= 2) tma_load_3d(smem_u32(c_s + (size_t)(k & 1) * NB * Hc), &a.tm_c, u0, b0, k - 2, mb_s);
@@ -1072,12 +1209,17 @@ __global__ void __launch_bounds__((TCB_CW + 2) * 32, 1) lstm_tc_bwd2_kernel(cons
                 // arm for the partial dh_{k-1} -- only once the previous phase of this barrier is complete, or the
                 // arm would be counted as an arrival of that phase
                 if (s > 0) mbar_wait_dbg(mb_full, (uint32_t)((s - 1) & 1), a.dbg, 8, s);
-                if (k > 0) mbar_expect_tx(mb_full, (uint32_t)(CL - 1) * box_bytes);
+                if (k > 0) mbar_expect_tx(mb_full, rx_bytes);
                 mbar_wait_dbg(mb_items, (uint32_t)(s & 1), a.dbg, 7, s);
                 if (k > 0)  // this CTA has consumed its slots: the peers may overwrite them
                     // (relaxed: nothing is published, the slot reads are complete; a release per arrive costs ~1000 cycles)
                     for (int d = 1; d < CL; ++d)
                         mbar_arrive_cluster_relaxed(mapa_u32(mb_free, (uint32_t)((rank + d) % CL)));
+                if (k > 0 && silent_out) {  // peers this CTA has no partial sums for: an empty arrival keeps them in step
+                    mbar_wait_dbg(mb_free, (uint32_t)(s & 1), a.dbg, 9, s);
+                    for (int d = 0; d < CL; ++d)
+                        if (silent_out & (1 << d)) mbar_arrive_cluster_relaxed(mapa_u32(mb_full, (uint32_t)d));
+                }
             }
         }
     }
@@ -1180,7 +1322,7 @@ static int tc_resolve(const hcgs_plan* plan, int cluster_size, int nb, TcPlan** 
         TcPlan* t = nullptr;
         if (tc_plan_get(plan, cands[ci], &t)) return 1;
         const bool fits = tc_fwd_smem_v(*t, NB) <= (size_t)limit && tc_bwd_smem_v(*t, NB) <= (size_t)limit &&
-                          t->SPW <= 4 && t->KS <= 8 && (t->Hc * NB + 511) / 512 <= 8;
+                          t->SPW <= 4 && t->KS <= 8 && t->Hc <= 256;
         if (fits) {
             *out = t;
             *nb_out = NB;
@@ -1292,24 +1434,29 @@ static TcFwdKernel tc_pick_fwd(int NT, int SPW, int KS, int act) {
     return act == HCGS_ACT_TANH ? tc_pick_fwd_act<HCGS_ACT_TANH>(SPW, KS) : tc_pick_fwd_act<-1>(SPW, KS);
 }
 
+// slots of sequences per compute thread of the backward item phase: 16 sequences / (576 threads / Hc units)
+static int tc_bwd_items(int Hc) {
+    const int bpp = std::min(16, (TCB_CW * 32) / std::max(Hc, 1));
+    return bpp > 0 ? (16 + bpp - 1) / bpp : 99;
+}
 template <int ACT>
-static TcBwdKernel tc_pick_bwd2(int items) {
-    if (items <= 2) return lstm_tc_bwd2_kernel<1, 2, ACT>;
-    if (items <= 4) return lstm_tc_bwd2_kernel<1, 4, ACT>;
-    if (items <= 6) return lstm_tc_bwd2_kernel<1, 6, ACT>;
-    if (items <= 8) return lstm_tc_bwd2_kernel<1, 8, ACT>;
+static TcBwdKernel tc_pick_bwd3(int items) {
+    if (items <= 1) return lstm_tc_bwd3_kernel<1, ACT>;
+    if (items <= 2) return lstm_tc_bwd3_kernel<2, ACT>;
+    if (items <= 4) return lstm_tc_bwd3_kernel<4, ACT>;
+    if (items <= 8) return lstm_tc_bwd3_kernel<8, ACT>;
     return nullptr;
 }
 static TcBwdKernel tc_pick_bwd(int NT, int items, int act = HCGS_ACT_TANH) {
     if (NT != 1) return nullptr;
-    return act == HCGS_ACT_TANH ? tc_pick_bwd2<HCGS_ACT_TANH>(items) : tc_pick_bwd2<-1>(items);
+    return act == HCGS_ACT_TANH ? tc_pick_bwd3<HCGS_ACT_TANH>(items) : tc_pick_bwd3<-1>(items);
 }
 
 // co-resident clusters of the two kernels on the current device (0 when the query is unavailable)
 static int tc_max_active_clusters(const TcPlan& t, int NB, int* fwd_clusters, int* bwd_clusters) {
     *fwd_clusters = *bwd_clusters = 0;
     const void* ks[2] = {(const void*)tc_pick_fwd(NB / 16, t.SPW, t.KS, HCGS_ACT_TANH),
-                         (const void*)tc_pick_bwd(NB / 16, (t.Hc * NB + 511) / 512)};
+                         (const void*)tc_pick_bwd(NB / 16, tc_bwd_items(t.Hc))};
     const size_t smem[2] = {tc_fwd_smem_v(t, NB), tc_bwd_smem_v(t, NB)};
     const int threads[2] = {(t.WARPS + 2) * 32, (TCB_CW + 2) * 32};
     int* outs[2] = {fwd_clusters, bwd_clusters};
@@ -1419,8 +1566,12 @@ extern "C" int hcgs_lstm_tc_bwd(const hcgs_plan* plan, int cluster_size, int nb,
     TcBwdArgs a;
     a.wfrag = reinterpret_cast<const uint2*>(bwd_pack);
     a.blk_off = t->d_blk_off;
-    a.cs_ptr = t->d_cs_ptr;
-    a.blk_rs = t->d_blk_rs;
+    a.grp_off = t->d_grp_off;
+    a.grp = t->d_grp;
+    a.task_off = t->d_task_off;
+    a.task = t->d_task;
+    a.wtp = t->d_wtp;
+    a.rx = t->d_rx;
     {
         const char* e = getenv("HCGS_TC_DEBUG");
         a.dbg = e ? atoi(e) : 0;
@@ -1441,8 +1592,10 @@ extern "C" int hcgs_lstm_tc_bwd(const hcgs_plan* plan, int cluster_size, int nb,
     a.NS = t->NS;
     a.HP = t->HP;
     a.max_blocks = std::max(t->max_cta_blocks, 1);
+    a.max_groups = std::max(t->max_cta_groups, 1);
+    a.max_tasks = std::max(t->max_cta_tasks, 1);
     a.act = act;
-    const int items = (t->Hc * NB + 511) / 512;
+    const int items = tc_bwd_items(t->Hc);
     a.BW = a.NBX = 0;
     {
         if (int rc = tc_pick_box(t->Hc, &a.BW, &a.NBX)) return rc;
