@@ -241,6 +241,9 @@ int hcgs_lstm_tc_fwd(const hcgs_plan* plan, int cluster_size, int nb, const uint
 /* tuning aid: with HCGS_TC_DEBUG=64 in the environment the recurrent kernels accumulate clock64 deltas per
  * phase (thread 0 of CTA 0); out16 receives the 16 counters of the last traced launch.              */
 int hcgs_tc_trace_read(int64_t* out16);
+/* tuning aid: with HCGS_TC_DEBUG=128 hcgs_lstm_tc_bwd records clock64 stamps of the warps of CTA 0 at the middle
+ * time step (20 warps x 16 stamps; no counterpart in the reference).                                   */
+int hcgs_tc_timeline_read(int64_t* out320);
 int hcgs_lstm_tc_bwd(const hcgs_plan* plan, int cluster_size, int nb, const uint32_t* bwd_pack,
                      const float* dh_out, const float* gates, const float* c, int ld_h, const float* drop,
                      float drop_scalar, int act, int t_len, int batch, float* dpre, void* dpre_bf16,

@@ -70,6 +70,7 @@ SIGNATURES = {
     'hcgs_lstm_tc_bwd': (c_int, [c_void_p, c_int, c_int, _f, _f, _f, _f, c_int, _f, c_float, c_int, c_int, c_int, _f,
                                  _f, c_void_p]),
     'hcgs_tc_trace_read': (c_int, [POINTER(c_int64)]),
+    'hcgs_tc_timeline_read': (c_int, [POINTER(c_int64)]),
     'hcgs_tc_pack_nt': (c_int, [c_void_p, c_int, _pp, c_int, _f, c_void_p]),
     'hcgs_tc_gemm_nt': (c_int, [c_void_p, c_int, _f, _f, c_int64, c_int64, _pp, _f, c_int64, _f, c_void_p]),
     'hcgs_cast_bf16': (c_int, [_f, c_int64, c_int64, c_int, _f, c_int64, c_void_p]),
@@ -509,6 +510,13 @@ def tc_trace_read():
     out = (c_int64 * 16)()
     _check(load().hcgs_tc_trace_read(out), 'hcgs_tc_trace_read')
     return [int(v) for v in out]
+
+
+def tc_timeline_read():
+    """clock stamps [warp][16] of CTA 0 at the middle time step of the last hcgs_lstm_tc_bwd made with HCGS_TC_DEBUG=128"""
+    out = (c_int64 * 320)()
+    _check(load().hcgs_tc_timeline_read(out), 'hcgs_tc_timeline_read')
+    return [[int(out[w * 16 + i]) for i in range(16)] for w in range(20)]
 
 
 def tc_pack_nt(plan, weights, wpack):

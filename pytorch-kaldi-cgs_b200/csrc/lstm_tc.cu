@@ -41,7 +41,7 @@ namespace hcgs {
 
 constexpr int TC_MAX_WARPS = 16;
 constexpr int TC_MAX_WARPS2 = 20;  // forward kernels with <= 2 strips per warp (register budget 65536 / 640)
-constexpr int TCB_CW = 18;         // compute warps of the backward kernel (+2 DMA warps)
+constexpr int TCB_CW = 18;         // warps of the backward kernel
 
 struct TcPlan {
     int CL = 0, H = 0, NS = 0;  // cluster size, hidden size, 4-row strips in total
@@ -134,16 +134,18 @@ static int tc_plan_get(const hcgs_plan* cplan, int CL, TcPlan** out) {
         for (size_t j = 0; j < l.size(); ++j) cgt[(size_t)s * t->KS * 4 + j] = l[j];
         nks[s] = (uint8_t)((l.size() + 3) / 4);
     }
-    // backward: the 8-strip (32-column) column blocks of U are the tasks of the compute warps.  A task keeps the
-    // partial dh of its <= 8 column strips in accumulators and walks the CTA's row strips: one A tile (the bf16 dpre
-    // of a row strip, 16 sequences x 4 rows x 4 gates) serves every kept block of that row strip inside the column
-    // block ("group").  Tasks are cut at destination-CTA boundaries, heavy ones are halved, and the result is spread
-    // over the warps longest-first.  Column blocks without a kept block in the CTA's rows have no task: their
-    // partial sums are zero and the owner's receive slots keep the zeros they were initialised with.
+    // backward: the 8-strip (32-column) column blocks of U are the tasks of the warps.  A task keeps the partial dh of
+    // its <= 8 column strips in accumulators and walks the CTA's row strips: one A tile (the bf16 dpre of a row strip,
+    // 16 sequences x 4 rows x 4 gates) serves every kept block of that row strip inside the column block ("group").
+    // Tasks are cut at destination-CTA boundaries, heavy ones at the middle of the column block, and spread over the
+    // warps longest-first.  Column blocks without a kept block in the CTA's rows have no task: their partial sums are
+    // zero and the owner's receive slots keep the zeros they were initialised with.
     struct HTask {
         int base, jlo, nst, ngroups, nblocks, cost;
     };
     const int CS = CL * t->SPC;
+    // issue slots of a task (the group loop is issue bound: profiles/r02_ncu_lstm_tc_bwd3.md): ~20 per group plus 3 per
+    // column strip the loop variant tests (8, or 4 for tasks inside one half of the column block), ~30 per pushed strip
     auto measure = [&](int r, HTask& k) {
         k.ngroups = k.nblocks = 0;
         for (int sl = 0; sl < t->SPC; ++sl) {
@@ -154,12 +156,16 @@ static int tc_plan_get(const hcgs_plan* cplan, int CL, TcPlan** out) {
                 if (k.base + j < NS && occ[(size_t)s * NS + k.base + j]) ++n;
             if (n) ++k.ngroups, k.nblocks += n;
         }
-        k.cost = k.ngroups ? 12 + 5 * k.ngroups + 2 * k.nblocks : 0;
+        const bool half = k.jlo + k.nst <= 4 || k.jlo >= 4;
+        k.cost = k.ngroups ? 150 + k.ngroups * (20 + 3 * (half ? 4 : 8)) + 30 * k.nst : 0;
     };
     std::vector<int> blk_off(CL + 1, 0), grp_off(CL + 1, 0), task_off(CL + 1, 0), wtp((size_t)CL * (TCB_CW + 1), 0),
         rx((size_t)CL * 3, 0), pair((size_t)CL * CL, 0), tasks;
     std::vector<uint16_t> blk_rs, blk_cs;
     std::vector<uint32_t> grp;
+    // warp 0 leads (mbarrier waits, TMA, handshake: ~3 k cycles of a step) and takes no tasks unless there are more
+    // tasks than the other warps can hold
+    const int TW = TCB_CW - 1;
     for (int r = 0; r < CL; ++r) {
         std::vector<HTask> work;
         for (int base = 0; base < NS; base += 8) {
@@ -174,27 +180,31 @@ static int tc_plan_get(const hcgs_plan* cplan, int CL, TcPlan** out) {
                 j = je;
             }
         }
+        // a task that spans both halves of its column block and is heavier than a warp's fair share is cut at strip 4:
+        // both halves still walk nearly every row strip, but their loop tests 4 strips per group instead of 8
         int64_t total = 0;
         for (const HTask& k : work) total += k.cost;
-        const int64_t limit = std::max<int64_t>(40, (total * 5 / 4 + TCB_CW - 1) / TCB_CW);
-        for (size_t i = 0; i < work.size();) {
-            if (work[i].cost > limit && work[i].nst > 1) {
-                HTask lo = work[i], hi = work[i];
-                lo.nst = work[i].nst / 2;
-                hi.jlo = lo.jlo + lo.nst;
-                hi.nst = work[i].nst - lo.nst;
-                measure(r, lo);
-                measure(r, hi);
-                work.erase(work.begin() + i);
-                if (hi.cost) work.insert(work.begin() + i, hi);
-                if (lo.cost) work.insert(work.begin() + i, lo);
-                continue;  // the halves are looked at again
-            }
+        static const int split_pct = getenv("HCGS_TC_SPLIT") ? atoi(getenv("HCGS_TC_SPLIT")) : 150;  // tuning only
+        static const int lead_cost = getenv("HCGS_TC_LEAD") ? atoi(getenv("HCGS_TC_LEAD")) : 600;     // tuning only
+        const int64_t fair = std::max<int64_t>(300, (total * split_pct / 100 + TW - 1) / TW);
+        for (size_t i = 0; i < work.size(); ++i) {
+            const HTask w = work[i];
+            if (w.cost <= fair || w.jlo >= 4 || w.jlo + w.nst <= 4) continue;
+            HTask lo = w, hi = w;
+            lo.nst = 4 - w.jlo;
+            hi.jlo = 4;
+            hi.nst = w.jlo + w.nst - 4;
+            measure(r, lo);
+            measure(r, hi);
+            if (!lo.cost || !hi.cost) continue;
+            work[i] = lo;
+            work.insert(work.begin() + i + 1, hi);
             ++i;
         }
         std::stable_sort(work.begin(), work.end(), [](const HTask& x, const HTask& y) { return x.cost > y.cost; });
         std::vector<std::vector<int>> per_warp(TCB_CW);
         std::vector<int64_t> load(TCB_CW, 0);
+        load[0] = lead_cost;
         for (size_t i = 0; i < work.size(); ++i) {
             int w = 0;
             for (int x = 1; x < TCB_CW; ++x)
@@ -295,7 +305,7 @@ static size_t tc_bwd3_smem(const TcPlan& t, int NB) {
     b += ((size_t)t.CL * t.SPC * 256 + 127) & ~(size_t)127;           // partial-dh slots [source][strip][16 x 4]
     b += tc_align16((size_t)NB * (t.Hc * 4 + 8) * 2);                 // bf16 dpre tile (MMA A operand)
     b += tc_align16((size_t)std::max(t.max_cta_blocks, 1) * 16 * 8);  // B fragments (16 lanes x 8 B)
-    b += tc_align16((size_t)std::max(t.max_cta_groups, 1) * 4);       // row-strip groups
+    b += tc_align16((size_t)(std::max(t.max_cta_groups, 1) + 2) * 4); // row-strip groups (+2 spare)
     b += tc_align16((size_t)std::max(t.max_cta_tasks, 1) * 32);       // tasks
     b += tc_align16((size_t)(TCB_CW + 1) * 4);                        // tasks of each warp
     b += 64;
@@ -410,6 +420,9 @@ __device__ __forceinline__ float act_apply_fast(int act, float x) {
 // phase timing for kernel tuning (HCGS_TC_DEBUG bit 64): thread 0 of every CTA accumulates clock64 deltas per
 // phase in shared memory; CTA 0 publishes them (hcgs_tc_trace_read).  Costs two predicated branches per phase.
 __device__ long long g_tc_trace[16];
+__device__ long long g_tc_tl[20 * 16];  // HCGS_TC_DEBUG bit 128: clock stamps of every warp of CTA 0 at one time step
+#define TC_TL(i)                                                             \
+    if ((a.dbg & 128) && lane == 0 && blockIdx.x == 0 && s == a.T / 2) g_tc_tl[warp * 16 + (i)] = clock64();
 #define TC_TRACE(p)                                   \
     if (a.dbg & 64) {                                 \
         if (threadIdx.x == 0) {                       \
@@ -922,27 +935,66 @@ __device__ __forceinline__ uint2 lds_u2(uint32_t addr) {
     return v;
 }
 
+// The row-strip groups [g0, g1) of one task: per group one A tile (ldmatrix.x4) and one mma per kept block into the
+// accumulator of its column strip J0 <= j < J0 + JN (the loop is issue bound, so tasks inside one half of a column block
+// use the variant that tests four strips).  Lane L votes bit (L & 7) of the group's mask: the ballot is the mask again,
+// but in a form the compiler knows to be warp-uniform -- uniform predicates, no re-convergence instructions around the
+// predicated mma (redux.sync would do the same and is far slower: one per ~30 cycles per SM).  The word and the A tile
+// of group g + 1 are fetched before the mma of group g (the table has one spare entry behind the last group).
+template <int J0, int JN>
+__device__ __forceinline__ void tc_run_groups(float (&acc)[8][4], const uint32_t* grp_s, int g0, int g1,
+                                              uint32_t lm_base, uint32_t bp, uint32_t lane_bit) {
+    uint32_t meta = grp_s[g0];
+    uint32_t af[4];
+    ldmatrix_x4(af, lm_base + (meta & 0xFFFFu));
+    for (int g = g0; g < g1; ++g) {
+        const uint32_t meta_n = grp_s[g + 1];
+        uint32_t an[4];
+        ldmatrix_x4(an, lm_base + (meta_n & 0xFFFFu));
+        const uint32_t kept = __ballot_sync(0xffffffffu, (meta & lane_bit) != 0u);
+#pragma unroll
+        for (int j = J0; j < J0 + JN; ++j)
+            if (kept & (1u << j)) {
+                const uint2 bw = lds_u2(bp);
+                bp += 128u;
+                mma_bf16_16816_s(acc[j], af, bw.x, bw.y);
+            }
+        meta = meta_n;
+#pragma unroll
+        for (int x = 0; x < 4; ++x) af[x] = an[x];
+    }
+}
+
 // ---- backward, third build ----------------------------------------------------------------------
-// 18 compute warps + 2 DMA warps; no block-wide barrier inside the time loop, only mbarriers.  Per time step k
-// (descending):
-//   item phase : every compute thread owns one unit of the CTA's slice and up to IT sequences: dh_k = dh_out[k] +
-//                the partial sums the CLUSTER pushed into this CTA's slots during step k+1; gate derivatives from
-//                the TMA-staged gates / c; dpre leaves as fp32 + bf16 global stores and as the bf16 A tile
-//                (unit-major, k = row-in-strip * 4 + gate) in shared memory;
-//   MMA phase  : a warp walks its tasks (plan: column block of <= 8 strips x this CTA's rows).  Per row-strip
-//                group ONE ldmatrix.x4 brings the 16 x 16 A tile, then one mma per kept 4x4 block of the group
-//                into the accumulator of its column strip (warp-uniform predicates from the group's bit mask);
-//                round 1 loaded the A tile once per block and that shared-memory traffic bounded the phase;
+// 18 warps, all of them compute.  Per time step k (descending):
+//   item phase : every thread owns one unit of the CTA's slice and up to IT sequences: dh_k = dh_out[k] + the partial
+//                sums the CLUSTER pushed into this CTA's slots during step k+1; gate derivatives from the TMA-staged
+//                gates / c; dpre leaves as fp32 + bf16 global stores and as the bf16 A tile (unit-major,
+//                k = row-in-strip * 4 + gate) in shared memory;
+//   MMA phase  : a warp walks its tasks (plan: column block of <= 8 strips x this CTA's rows).  Per row-strip group
+//                ONE ldmatrix.x4 brings the 16 x 16 A tile, then one mma per kept 4x4 block of the group into the
+//                accumulator of its column strip (uniform predicates from the group's bit mask); round 1 loaded the
+//                A tile once per block and that shared-memory traffic bounded the phase;
 //   push       : a finished task leaves straight from the accumulators: two shuffles turn a strip's accumulator
-//                layout into 16-byte row pieces and ONE st.async.v4 (16 lanes, 256 contiguous bytes) per strip
-//                writes them into the owner's slot [source][strip][16 rows x 4 columns] and completes transaction
-//                bytes on its barrier (tools/probe/dsmem_push.cu: 2.4 k cycles per exchange against 3.9 k for the
-//                8-byte form of round 1; staged bulk copies are slower than either);
-//   the rows of a strip's slot are XOR-swizzled with the strip index so that the item phase reads them without
-//   bank conflicts; the slots are single-buffered, a consumed-handshake (one remote arrive per peer and step)
-//   guards their reuse; the owner sums the sources in rank order (deterministic).
+//                layout into 16-byte row pieces and ONE st.async.v4 (16 lanes, 256 contiguous bytes) per strip writes
+//                them into the owner's slot [source][strip][16 rows x 4 columns] and completes transaction bytes on
+//                its barrier (tools/probe/dsmem_push.cu: 2.4 k cycles per exchange against 3.9 k for the 8-byte form
+//                of round 1; staged bulk copies are slower than either).
+// Synchronisation: inside the CTA two NAMED barriers per step (inputs ready / A tile complete); only thread 0 waits on
+// mbarriers (TMA inputs, partial sums of the peers) and issues the TMA prefetches, the arm of the receive barrier and
+// the consumed-handshake.  Round 1 and the first version of this build let all 18 warps + 2 DMA warps wait on
+// mbarriers: every transaction byte that lands wakes every sleeping waiter, and the wake-up / re-check loop was 54 % of
+// all executed warp instructions (ncu, profiles/r02_ncu_lstm_tc_bwd3.md) -- issue slots taken from the working warps.
+// The rows of a strip's slot are XOR-swizzled with the strip index so that the item phase reads them without bank
+// conflicts; the slots are single-buffered, the consumed-handshake (one remote arrive per peer and step) guards
+// their reuse; the owner sums the sources in rank order (deterministic).
+template <int ID, int THREADS>
+__device__ __forceinline__ void named_bar_sync() {
+    asm volatile("bar.sync %0, %1;" ::"n"(ID), "n"(THREADS) : "memory");
+}
+
 template <int IT, int ACT>
-__global__ void __launch_bounds__((TCB_CW + 2) * 32, 1) lstm_tc_bwd3_kernel(const __grid_constant__ TcBwdArgs a) {
+__global__ void __launch_bounds__(TCB_CW * 32, 1) lstm_tc_bwd3_kernel(const __grid_constant__ TcBwdArgs a) {
     constexpr int NB = 16;
     constexpr int CW = TCB_CW;
     constexpr int cthreads = CW * 32;
@@ -956,10 +1008,7 @@ __global__ void __launch_bounds__((TCB_CW + 2) * 32, 1) lstm_tc_bwd3_kernel(cons
     const int DPS = Hc * 4 + 8;  // bf16 elements per dpre row: pitch = 16 mod 128 bytes (Hc multiple of 8)
     const int BW = a.BW, NBX = a.NBX;
     const int tid = threadIdx.x, lane = tid & 31;
-    // broadcast form: the compiler then treats the warp index (and the task / group tables read through it) as
-    // warp-uniform and keeps the predicated mma free of re-convergence instructions
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
-    const bool is_dma = warp >= CW;
     const int blk0 = a.blk_off[rank];
     const int nblk = a.blk_off[rank + 1] - blk0;
     const int grp0 = a.grp_off[rank], ngrp = a.grp_off[rank + 1] - grp0;
@@ -980,21 +1029,22 @@ __global__ void __launch_bounds__((TCB_CW + 2) * 32, 1) lstm_tc_bwd3_kernel(cons
     uint2* wf_s = reinterpret_cast<uint2*>(sp);
     sp += tc_align16((size_t)a.max_blocks * 16 * 8);
     uint32_t* grp_s = reinterpret_cast<uint32_t*>(sp);
-    sp += tc_align16((size_t)a.max_groups * 4);
+    sp += tc_align16((size_t)(a.max_groups + 2) * 4);
     int4* task_s = reinterpret_cast<int4*>(sp);
     sp += tc_align16((size_t)a.max_tasks * 32);
     int* wtp_s = reinterpret_cast<int*>(sp);
     sp += tc_align16((size_t)(CW + 1) * 4);
     uint64_t* mbar = reinterpret_cast<uint64_t*>(sp);
     const uint32_t mbar_addr = smem_u32(mbar);
-    // [0..1] gate stage landed  [2] c / dh boxes landed  [3] slots full (CW own arrivals + arm + peers' bytes)
-    // [4] item phase done (CW arrivals)  [5] peers have consumed their slots (CL-1 remote arrivals)
-    const uint32_t mb_g = mbar_addr, mb_s = mbar_addr + 16, mb_full = mbar_addr + 24, mb_items = mbar_addr + 32,
-                   mb_free = mbar_addr + 40;
+    // [0..1] inputs of a step landed (two arms: gates two steps ahead, c / dh one step ahead)
+    // [2] slots full (arm + silent peers' arrivals + peers' bytes)  [3] peers have consumed their slots (CL-1 arrivals)
+    const uint32_t mb_in = mbar_addr, mb_full = mbar_addr + 16, mb_free = mbar_addr + 24;
     const uint32_t slots_addr = smem_u32(slots);
     const int stage_floats = NB * Hc * 4;
     const uint32_t stage_bytes = (uint32_t)stage_floats * 4, box_bytes = (uint32_t)NB * Hc * 4;
     const uint32_t rx_bytes = (uint32_t)a.rx[rank * 3];
+    const bool staged = (CL - 1) * 256 <= 1024;  // the foreign strips fit a gate stage (SPC * 1024 bytes): CL <= 5
+    const uint32_t stage_addr0 = smem_u32(gates_s);
     const int silent_in = a.rx[rank * 3 + 1], silent_out = a.rx[rank * 3 + 2];
 
     TC_TRACE_INIT();
@@ -1002,7 +1052,7 @@ __global__ void __launch_bounds__((TCB_CW + 2) * 32, 1) lstm_tc_bwd3_kernel(cons
         const uint4* s4 = reinterpret_cast<const uint4*>(a.wfrag + (size_t)blk0 * 16);
         uint4* d4 = reinterpret_cast<uint4*>(wf_s);
         for (int i = tid; i < nblk * 8; i += blockDim.x) d4[i] = __ldg(s4 + i);
-        for (int i = tid; i < ngrp; i += blockDim.x) grp_s[i] = a.grp[grp0 + i];
+        for (int i = tid; i < ngrp + 2; i += blockDim.x) grp_s[i] = i < ngrp ? a.grp[grp0 + i] : 0u;
         const int4* t4 = reinterpret_cast<const int4*>(a.task) + (size_t)task0 * 2;
         for (int i = tid; i < ntask * 2; i += blockDim.x) task_s[i] = __ldg(t4 + i);
         for (int i = tid; i <= CW; i += blockDim.x) wtp_s[i] = a.wtp[(size_t)rank * (CW + 1) + i];
@@ -1010,11 +1060,9 @@ __global__ void __launch_bounds__((TCB_CW + 2) * 32, 1) lstm_tc_bwd3_kernel(cons
         uint32_t* dz = reinterpret_cast<uint32_t*>(dpre_s);
         for (int i = tid; i < NB * DPS / 2; i += blockDim.x) dz[i] = 0u;
         if (tid == 0) {
-            mbar_init(mb_g, 1u);
-            mbar_init(mb_g + 8, 1u);
-            mbar_init(mb_s, 1u);
-            mbar_init(mb_full, (uint32_t)(CW + 1 + silent_in));
-            mbar_init(mb_items, (uint32_t)CW);
+            mbar_init(mb_in, 2u);
+            mbar_init(mb_in + 8, 2u);
+            mbar_init(mb_full, (uint32_t)(1 + silent_in));
             mbar_init(mb_free, (uint32_t)(CL - 1));
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
             asm volatile("prefetch.tensormap [%0];" ::"l"(&a.tm_gates) : "memory");
@@ -1025,29 +1073,32 @@ __global__ void __launch_bounds__((TCB_CW + 2) * 32, 1) lstm_tc_bwd3_kernel(cons
     fence_proxy_async();
     __syncthreads();
 
-    // DMA warp 0, lane 0: inputs of time step kk.  Gate boxes go to stage kk&1 (own barrier, a full step ahead);
-    // c_{kk} goes to c buffer kk&1 and dh_{kk} to the single dh buffer (shared barrier, loaded late: small boxes)
+    // thread 0: inputs of time step kk.  Gate boxes go to stage kk&1 two steps ahead (first arm of barrier kk&1);
+    // dh_{kk} (single buffer) and c_{kk-1} (c buffer (kk-1)&1) one step ahead (second arm)
     auto load_gates = [&](int kk) {
-        if (kk < 0 || nv == 0) return;
-        const uint32_t bar = mb_g + 8 * (kk & 1);
+        const uint32_t bar = mb_in + 8 * (kk & 1);
         mbar_expect_tx(bar, stage_bytes);
         for (int x = 0; x < NBX; ++x)
             tma_load_3d(smem_u32(gates_s + (size_t)(kk & 1) * stage_floats + (size_t)x * NB * BW), &a.tm_gates,
                         u0 * 4 + x * BW, b0, kk, bar);
     };
-    if (warp == CW && lane == 0 && nv > 0) {
+    auto load_small = [&](int kk, bool with_c_kk) {
+        const uint32_t bar = mb_in + 8 * (kk & 1);
+        mbar_expect_tx(bar, box_bytes * (1u + (kk >= 1 ? 1u : 0u) + (with_c_kk ? 1u : 0u)));
+        tma_load_3d(smem_u32(dh_s), &a.tm_dh, u0, b0, kk, bar);
+        if (kk >= 1) tma_load_3d(smem_u32(c_s + (size_t)((kk - 1) & 1) * NB * Hc), &a.tm_c, u0, b0, kk - 1, bar);
+        if (with_c_kk) tma_load_3d(smem_u32(c_s + (size_t)(kk & 1) * NB * Hc), &a.tm_c, u0, b0, kk, bar);
+    };
+    if (tid == 0 && nv > 0) {
         load_gates(a.T - 1);
-        load_gates(a.T - 2);
-        mbar_expect_tx(mb_s, box_bytes * (a.T > 1 ? 3u : 2u));
-        tma_load_3d(smem_u32(dh_s), &a.tm_dh, u0, b0, a.T - 1, mb_s);
-        tma_load_3d(smem_u32(c_s + (size_t)((a.T - 1) & 1) * NB * Hc), &a.tm_c, u0, b0, a.T - 1, mb_s);
-        if (a.T > 1) tma_load_3d(smem_u32(c_s + (size_t)((a.T - 2) & 1) * NB * Hc), &a.tm_c, u0, b0, a.T - 2, mb_s);
+        load_small(a.T - 1, true);
+        if (a.T > 1) load_gates(a.T - 2);
     }
 
     // ---- pointwise items: thread -> unit `ul` of the slice (fastest over the lanes => conflict-free shared loads,
     // coalesced 16-byte global stores) and the sequences bq, bq + BPP, ...; every offset is affine in the slot j
     const int BPP = min(NB, cthreads / Hc);  // sequences per pass
-    const bool active = !is_dma && tid < BPP * Hc;
+    const bool active = tid < BPP * Hc;
     const int bq = active ? tid / Hc : 0, ul = active ? tid - (tid / Hc) * Hc : 0;
     const int u = u0 + ul;
     const bool unit_ok = active && u < H, unit_pad = active && u >= H && u < ldH;
@@ -1066,107 +1117,143 @@ __global__ void __launch_bounds__((TCB_CW + 2) * 32, 1) lstm_tc_bwd3_kernel(cons
         if (unit_ok && b < NB && b0 + b < a.B && a.drop) dr[j] = __ldg(a.drop + (size_t)(b0 + b) * H + u);
     }
     const int br = lane >> 2, q = lane & 3;
-    const int wt0 = is_dma ? 0 : wtp_s[warp], wt1 = is_dma ? 0 : wtp_s[warp + 1];
+    const int wt0 = wtp_s[warp], wt1 = wtp_s[warp + 1];
     const uint32_t lm_base = smem_u32(dpre_s) + (uint32_t)(((lane & 15) * DPS + (lane >> 4) * 8) * 2);
     const uint32_t wf_lane = smem_u32(wf_s) + (uint32_t)(lane & 15) * 8u;
+    const uint32_t lane_bit = 0x10000u << (lane & 7);
     cluster.sync();
 
     for (int s = 0; s < a.T; ++s) {
         const int k = a.T - 1 - s;
-        if (!is_dma) {
-            // ============================ compute warps ==========================================================
-            TC_TRACE(0);
-            if (nv > 0) {
-                mbar_wait_dbg(mb_g + 8 * (k & 1), (uint32_t)((s >> 1) & 1), a.dbg, 1, s);
-                mbar_wait_dbg(mb_s, (uint32_t)(s & 1), a.dbg, 2, s);
-            }
+        TC_TRACE(0);
+        if (tid == 0) {
+            if (nv > 0) mbar_wait_dbg(mb_in + 8 * (k & 1), (uint32_t)((s >> 1) & 1), a.dbg, 1, s);
             if (s > 0) mbar_wait_dbg(mb_full, (uint32_t)((s - 1) & 1), a.dbg, 3, s);  // partial dh_k from every CTA has landed
-            TC_TRACE(1);
-            if (active) {
-                const float* gst = gates_s + (size_t)(k & 1) * stage_floats;
-                const float* ck_s = c_s + (size_t)(k & 1) * NB * Hc;
-                const float* cm_s = c_s + (size_t)((k & 1) ^ 1) * NB * Hc;
-                float* dpre_k = a.dpre ? a.dpre + (size_t)k * a.B * 4 * ldH : nullptr;
-                __nv_bfloat16* dpreb_k = a.dpreb ? a.dpreb + (size_t)k * a.B * 4 * ldH : nullptr;
+        }
+        TC_TL(0);
+        named_bar_sync<1, cthreads>();  // inputs and partial sums are in place; everybody's local slot writes are done
+        TC_TRACE(1);
+        TC_TL(1);
+        if (active) {
+            const float* gst = gates_s + (size_t)(k & 1) * stage_floats;
+            const float* ck_s = c_s + (size_t)(k & 1) * NB * Hc;
+            const float* cm_s = c_s + (size_t)((k & 1) ^ 1) * NB * Hc;
+            float* dpre_k = a.dpre ? a.dpre + (size_t)k * a.B * 4 * ldH : nullptr;
+            __nv_bfloat16* dpreb_k = a.dpreb ? a.dpreb + (size_t)k * a.B * 4 * ldH : nullptr;
 #pragma unroll
-                for (int j = 0; j < IT; ++j) {
-                    const int b = bq + j * BPP;
-                    if (b >= NB) break;
-                    const bool ok = unit_ok && b0 + b < a.B;
-                    const int sm = sm0 + j * BPP * Hc;
-                    float dh = dh_s[sm];
-                    if (s > 0) {
-                        const float* sl_p = slots + so0 + ((b ^ swz) << 2);
-                        for (int src = 0; src < CL; ++src) dh += sl_p[(size_t)src * SPC * 64];
-                    }
-                    const float4 g4 = *reinterpret_cast<const float4*>(gst + gs0 + j * BPP * BW);
-                    const float cval = ck_s[sm];
-                    const float cm1 = (k > 0) ? cm_s[sm] : 0.f;  // c_{-1} = 0
-                    const float fg = g4.x, ig = g4.y, og = g4.z, gg = g4.w;
-                    const float tc = (ACT == HCGS_ACT_TANH) ? fast_tanh(cval) : act_apply_fast(a.act, cval);
-                    const float dog = dh * tc;
-                    const float dct = dh * og * ((ACT == HCGS_ACT_TANH) ? (1.f - tc * tc) : act_grad_from_out(a.act, tc)) +
-                                      dc_carry[j];
-                    const float dig = dct * gg * dr[j];
-                    const float dgg = dct * ig * dr[j];
-                    const float dfg = dct * cm1;
-                    float4 dp;
-                    dp.x = dfg * fg * (1.f - fg);
-                    dp.y = dig * ig * (1.f - ig);
-                    dp.z = dog * og * (1.f - og);
-                    dp.w = dgg * ((ACT == HCGS_ACT_TANH) ? (1.f - gg * gg) : act_grad_from_out(a.act, gg));
-                    if (!ok) dp = make_float4(0.f, 0.f, 0.f, 0.f);
-                    dc_carry[j] = ok ? dct * fg : 0.f;
-                    const uint2 pb = make_uint2(pack_bf16x2(dp.x, dp.y), pack_bf16x2(dp.z, dp.w));
-                    if ((ok || (unit_pad && b0 + b < a.B)) && !(a.dbg & 1)) {
-                        const uint32_t go = go0 + (uint32_t)(j * BPP) * 4u * (uint32_t)ldH;
-                        if (dpre_k) *reinterpret_cast<float4*>(dpre_k + go) = dp;
-                        if (dpreb_k) *reinterpret_cast<uint2*>(dpreb_k + go) = pb;
-                    }
-                    *reinterpret_cast<uint2*>(dpre_s + ds0 + j * BPP * DPS) = pb;
+            for (int j = 0; j < IT; ++j) {
+                const int b = bq + j * BPP;
+                if (b >= NB) break;
+                const bool ok = unit_ok && b0 + b < a.B;
+                const int sm = sm0 + j * BPP * Hc;
+                float dh = dh_s[sm];
+                if (s > 0) {
+                    const float* sl_p = slots + so0 + ((b ^ swz) << 2);
+                    for (int src = 0; src < CL; ++src) dh += sl_p[(size_t)src * SPC * 64];
                 }
+                const float4 g4 = *reinterpret_cast<const float4*>(gst + gs0 + j * BPP * BW);
+                const float cval = ck_s[sm];
+                const float cm1 = (k > 0) ? cm_s[sm] : 0.f;  // c_{-1} = 0
+                const float fg = g4.x, ig = g4.y, og = g4.z, gg = g4.w;
+                const float tc = (ACT == HCGS_ACT_TANH) ? fast_tanh(cval) : act_apply_fast(a.act, cval);
+                const float dog = dh * tc;
+                const float dct = dh * og * ((ACT == HCGS_ACT_TANH) ? (1.f - tc * tc) : act_grad_from_out(a.act, tc)) +
+                                  dc_carry[j];
+                const float dig = dct * gg * dr[j];
+                const float dgg = dct * ig * dr[j];
+                const float dfg = dct * cm1;
+                float4 dp;
+                dp.x = dfg * fg * (1.f - fg);
+                dp.y = dig * ig * (1.f - ig);
+                dp.z = dog * og * (1.f - og);
+                dp.w = dgg * ((ACT == HCGS_ACT_TANH) ? (1.f - gg * gg) : act_grad_from_out(a.act, gg));
+                if (!ok) dp = make_float4(0.f, 0.f, 0.f, 0.f);
+                dc_carry[j] = ok ? dct * fg : 0.f;
+                const uint2 pb = make_uint2(pack_bf16x2(dp.x, dp.y), pack_bf16x2(dp.z, dp.w));
+                if ((ok || (unit_pad && b0 + b < a.B)) && !(a.dbg & 1)) {
+                    const uint32_t go = go0 + (uint32_t)(j * BPP) * 4u * (uint32_t)ldH;
+                    if (dpre_k) *reinterpret_cast<float4*>(dpre_k + go) = dp;
+                    if (dpreb_k) *reinterpret_cast<uint2*>(dpreb_k + go) = pb;
+                }
+                *reinterpret_cast<uint2*>(dpre_s + ds0 + j * BPP * DPS) = pb;
             }
-            __syncwarp();
-            if (lane == 0) mbar_arrive_local(mb_items);
-            TC_TRACE(2);
-            if (k == 0) break;
-            mbar_wait_dbg(mb_items, (uint32_t)(s & 1), a.dbg, 4, s);  // every warp's share of the bf16 dpre tile is in place
-            TC_TRACE(3);
-            // ---- partial dh_{k-1}: this warp's tasks
-            bool freed = false;
-            for (int ti = wt0; ti < wt1; ++ti) {
-                const int4 ta = task_s[2 * ti], tb = task_s[2 * ti + 1];  // {g0, g1, blk0, jlo}, {nst, dest, sl0, -}
-                float acc[8][4];
+        }
+        TC_TRACE(2);
+        TC_TL(2);
+        if (k == 0) break;
+        named_bar_sync<2, cthreads>();  // the bf16 dpre tile is complete; gates / c / dh / slots of step k are consumed
+        TC_TRACE(3);
+        TC_TL(3);
+        bool freed = false;
+        if (tid == 0) {
+            // arm for the partial dh_{k-1} (the previous phase of this barrier is complete: waited for above), tell the
+            // peers that this CTA's slots may be overwritten (relaxed: nothing is published, the slot reads are
+            // complete; a release per arrive costs ~1000 cycles), prefetch the inputs of the next steps
+            mbar_expect_tx(mb_full, rx_bytes);
+            for (int d = 1; d < CL; ++d) mbar_arrive_cluster_relaxed(mapa_u32(mb_free, (uint32_t)((rank + d) % CL)));
+            if (nv > 0) {
+                if (!staged && k >= 2) load_gates(k - 2);
+                load_small(k - 1, false);
+            }
+            if (staged) {
+                // the gate stage consumed at step s-1 was the staging area of that step's pushes.  Once every peer has
+                // consumed ITS slots of this step, those copies have landed (they were part of what the peers waited
+                // for): only now may the TMA overwrite the stage with the gates of step k-1
+                mbar_wait_dbg(mb_free, (uint32_t)(s & 1), a.dbg, 6, s);
+                freed = true;
+                if (nv > 0 && s > 0) load_gates(k - 1);
+            }
+        }
+        TC_TL(4);
+        // ---- partial dh_{k-1}: this warp's tasks
+        for (int ti = wt0; ti < wt1; ++ti) {
+            const int4 ta = task_s[2 * ti], tb = task_s[2 * ti + 1];  // {g0, g1, blk0, jlo}, {nst, dest, sl0, -}
+            float acc[8][4];
 #pragma unroll
-                for (int j = 0; j < 8; ++j) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.f;
-                uint32_t bp = wf_lane + (uint32_t)ta.z * 128u;
-                const int g1 = (a.dbg & 4) ? ta.x : ta.y;
-                for (int g = ta.x; g < g1; ++g) {
-                    const uint32_t meta = grp_s[g];
-                    uint32_t af[4];
-                    ldmatrix_x4(af, lm_base + (meta & 0xFFFFu));
+            for (int j = 0; j < 8; ++j) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.f;
+            const uint32_t bp = wf_lane + (uint32_t)ta.z * 128u;
+            const int g1 = (a.dbg & 4) ? ta.x : ta.y;
+            if (ta.w + tb.x <= 4) tc_run_groups<0, 4>(acc, grp_s, ta.x, g1, lm_base, bp, lane_bit);
+            else if (ta.w >= 4) tc_run_groups<4, 4>(acc, grp_s, ta.x, g1, lm_base, bp, lane_bit);
+            else tc_run_groups<0, 8>(acc, grp_s, ta.x, g1, lm_base, bp, lane_bit);
+            if (ti == wt0) { TC_TL(5); }
+            // ---- the task's strips leave from the accumulators (lane (br, q) holds columns 2q, 2q+1 of rows br and
+            // br+8 for q < 2; n columns 4..7 are unused)
+            const int d = tb.y;
+            const bool remote = d != rank;
+            if (remote && !freed) {  // the peers have consumed the slots of this step
+                TC_TRACE(4);
+                mbar_wait_dbg(mb_free, (uint32_t)(s & 1), a.dbg, 5, s);
+                freed = true;
+                TC_TRACE(5);
+            }
+            if (ti == wt0) { TC_TL(6); }
+            const uint32_t obase = slots_addr + (uint32_t)((rank * SPC + tb.z) * 256);
+            // staged: remote strips are written to the gate stage consumed by this step's item phase (compact index over
+            // the CL-1 foreign slices) and ONE bulk copy per task moves them: the copy engine does the DSMEM transfer,
+            // the LSU queue stays free for the other warps' mma operands (direct st.async pushes back-pressure it)
+            const uint32_t sbase = stage_addr0 + (uint32_t)(k & 1) * stage_bytes +
+                                   (uint32_t)((((d - rank - 1 + CL) % CL) * SPC + tb.z) * 256);
+            const bool direct = remote && !staged;
+            const uint32_t rbase = direct ? mapa_u32(obase, (uint32_t)d) : (remote ? sbase : obase);
+            const uint32_t rbar = remote ? mapa_u32(mb_full, (uint32_t)d) : 0u;
+            if (!direct) {
+                // local slots or staging: the accumulator layout goes out as it is, two 8-byte stores per strip
+                // (lanes q < 2 hold columns 2q, 2q+1 of rows br and br + 8; row r of a strip sits at (r ^ swizzle) * 16)
 #pragma unroll
-                    for (int j = 0; j < 8; ++j)
-                        if (meta & (0x10000u << j)) {  // warp-uniform
-                            const uint2 bw = lds_u2(bp);
-                            bp += 128u;
-                            mma_bf16_16816_s(acc[j], af, bw.x, bw.y);
-                        }
+                for (int j = 0; j < 8; ++j) {
+                    const int tj = j - ta.w;
+                    if (tj >= 0 && tj < tb.x && q < 2) {
+                        const uint32_t ad = rbase + (uint32_t)(tj * 256 + ((br ^ ((tb.z + tj) & 7)) << 4) + q * 8);
+                        asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(ad), "f"(acc[j][0]), "f"(acc[j][1]) : "memory");
+                        asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(ad + 128u), "f"(acc[j][2]), "f"(acc[j][3])
+                                     : "memory");
+                    }
                 }
-                // ---- the task's strips leave from the accumulators.  Lane (br, q) holds columns 2q, 2q+1 of rows br
-                // and br+8 (q < 2; n columns 4..7 are unused): after one exchange with the neighbour lane q = 0 owns
-                // the 16 bytes of row br and q = 1 those of row br + 8
-                const int d = tb.y;
-                const bool remote = d != rank;
-                if (remote && !freed) {  // the peers have consumed the slots of this step
-                    TC_TRACE(4);
-                    mbar_wait_dbg(mb_free, (uint32_t)(s & 1), a.dbg, 5, s);
-                    freed = true;
-                    TC_TRACE(5);
-                }
-                const uint32_t obase = slots_addr + (uint32_t)((rank * SPC + tb.z) * 256);
-                const uint32_t rbase = remote ? mapa_u32(obase, (uint32_t)d) : obase;
-                const uint32_t rbar = remote ? mapa_u32(mb_full, (uint32_t)d) : 0u;
+            } else {
+                // direct push (clusters of 8 and 16: the foreign strips do not fit a gate stage): after one exchange with
+                // the neighbour lane q = 0 owns the 16 bytes of row br and q = 1 those of row br + 8; one st.async.v4 per
+                // strip = 256 contiguous bytes
                 const int row = br + 8 * (q & 1);
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
@@ -1182,46 +1269,23 @@ __global__ void __launch_bounds__((TCB_CW + 2) * 32, 1) lstm_tc_bwd3_kernel(cons
                         v.z = __float_as_uint((q & 1) ? acc[j][2] : rx);
                         v.w = __float_as_uint((q & 1) ? acc[j][3] : ry);
                         const uint32_t off = (uint32_t)(tj * 256 + ((row ^ ((tb.z + tj) & 7)) << 4));
-                        if (q < 2 && !(a.dbg & 8)) {
-                            if (remote) st_async_v4(rbase + off, v, rbar);
-                            else
-                                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(rbase + off), "r"(v.x),
-                                             "r"(v.y), "r"(v.z), "r"(v.w)
-                                             : "memory");
-                        }
+                        if (q < 2) st_async_v4(rbase + off, v, rbar);
                     }
                 }
             }
-            __syncwarp();
-            if (lane == 0) mbar_arrive_local(mb_full);
-            TC_TRACE(4);
-        } else if (lane == 0) {
-            // ============================ DMA warps ==============================================================
-            if (warp == CW) {
-                mbar_wait_dbg(mb_items, (uint32_t)(s & 1), a.dbg, 6, s);  // item phase of step k is over: its input buffers are free
-                if (k >= 1 && nv > 0) {
-                    load_gates(k - 2);
-                    mbar_expect_tx(mb_s, box_bytes * (k >= 2 ? 2u : 1u));
-                    tma_load_3d(smem_u32(dh_s), &a.tm_dh, u0, b0, k - 1, mb_s);
-                    if (k >= 2) tma_load_3d(smem_u32(c_s + (size_t)(k & 1) * NB * Hc), &a.tm_c, u0, b0, k - 2, mb_s);
-                }
-            } else {
-                // arm for the partial dh_{k-1} -- only once the previous phase of this barrier is complete, or the
-                // arm would be counted as an arrival of that phase
-                if (s > 0) mbar_wait_dbg(mb_full, (uint32_t)((s - 1) & 1), a.dbg, 8, s);
-                if (k > 0) mbar_expect_tx(mb_full, rx_bytes);
-                mbar_wait_dbg(mb_items, (uint32_t)(s & 1), a.dbg, 7, s);
-                if (k > 0)  // this CTA has consumed its slots: the peers may overwrite them
-                    // (relaxed: nothing is published, the slot reads are complete; a release per arrive costs ~1000 cycles)
-                    for (int d = 1; d < CL; ++d)
-                        mbar_arrive_cluster_relaxed(mapa_u32(mb_free, (uint32_t)((rank + d) % CL)));
-                if (k > 0 && silent_out) {  // peers this CTA has no partial sums for: an empty arrival keeps them in step
-                    mbar_wait_dbg(mb_free, (uint32_t)(s & 1), a.dbg, 9, s);
-                    for (int d = 0; d < CL; ++d)
-                        if (silent_out & (1 << d)) mbar_arrive_cluster_relaxed(mapa_u32(mb_full, (uint32_t)d));
-                }
+            if (remote && staged) {
+                fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) bulk_s2c(mapa_u32(obase, (uint32_t)d), sbase, (uint32_t)tb.x * 256u, rbar);
             }
         }
+        TC_TL(7);
+        if (tid == 0 && silent_out) {  // peers this CTA has no partial sums for: an empty arrival keeps them in step
+            if (!freed) mbar_wait_dbg(mb_free, (uint32_t)(s & 1), a.dbg, 9, s);
+            for (int d = 0; d < CL; ++d)
+                if (silent_out & (1 << d)) mbar_arrive_cluster_relaxed(mapa_u32(mb_full, (uint32_t)d));
+        }
+        TC_TRACE(4);
     }
     TC_TRACE_FLUSH();
     cluster.sync();
@@ -1458,7 +1522,7 @@ static int tc_max_active_clusters(const TcPlan& t, int NB, int* fwd_clusters, in
     const void* ks[2] = {(const void*)tc_pick_fwd(NB / 16, t.SPW, t.KS, HCGS_ACT_TANH),
                          (const void*)tc_pick_bwd(NB / 16, tc_bwd_items(t.Hc))};
     const size_t smem[2] = {tc_fwd_smem_v(t, NB), tc_bwd_smem_v(t, NB)};
-    const int threads[2] = {(t.WARPS + 2) * 32, (TCB_CW + 2) * 32};
+    const int threads[2] = {(t.WARPS + 2) * 32, TCB_CW * 32};
     int* outs[2] = {fwd_clusters, bwd_clusters};
     for (int i = 0; i < 2; ++i) {
         if (!ks[i]) continue;
@@ -1607,8 +1671,17 @@ extern "C" int hcgs_lstm_tc_bwd(const hcgs_plan* plan, int cluster_size, int nb,
     TcBwdKernel k = tc_pick_bwd(NB / 16, items, act);
     HCGS_REQUIRE(k != nullptr, "hcgs_lstm_tc_bwd: no kernel for nb=%d items=%d", NB, items);
     const int n_clusters = (batch + NB - 1) / NB;
-    return tc_launch(k, a, n_clusters, t->CL, (TCB_CW + 2) * 32, tc_bwd_smem_v(*t, NB),
+    return tc_launch(k, a, n_clusters, t->CL, TCB_CW * 32, tc_bwd_smem_v(*t, NB),
                      (cudaStream_t)stream);
+}
+
+// tuning aid (HCGS_TC_DEBUG bit 128): clock stamps of the warps of CTA 0 at the middle time step, 20 x 16 values
+extern "C" int hcgs_tc_timeline_read(int64_t* out320) {
+    HCGS_REQUIRE(out320, "hcgs_tc_timeline_read: NULL argument");
+    long long h[320];
+    HCGS_CHECK_CUDA(cudaMemcpyFromSymbol(h, hcgs::g_tc_tl, sizeof(h)));
+    for (int i = 0; i < 320; ++i) out320[i] = (int64_t)h[i];
+    return 0;
 }
 
 // tuning aid: per-phase clock totals of CTA 0 / thread 0 of the last traced launch (HCGS_TC_DEBUG bit 64)
