@@ -32,7 +32,7 @@ import save_cgs_mat
 from HCGS import HCGS as HCGS
 from HCGS import guidedHCGS as guidedHCGS
 from quantized_modules import QuantizeLinear, Quantize, Quantize_inp, prune
-from b200 import native
+from b200 import native, rng
 from b200.functions import (LayerRuntime, LSTMLayerFunction, MLPLayerFunction, LSTMLayerTCFunction,
                             GatedRNNLayerFunction,
                             MLPLayerTCFunction, LayerNormFunction, BatchNormInputFunction, ActDropFunction)
@@ -667,6 +667,16 @@ class LSTM(nn.Module):
         if bool(self.lstm_use_batchnorm_inp):
             x = _input_batch_norm(self.bn0, x.reshape(x.shape[0] * x.shape[1], x.shape[2])).view(x.shape)
         prev_hb = None
+        drop_masks = None
+        if self.test_flag == False:  # noqa: E712 (reference spelling)
+            # the per-layer CPU draws of the reference (:843-851), in its order; taken from the one-forward-ahead
+            # prefetch when the default generator has not been touched since (b200/rng.py), else drawn here
+            Bm = x.shape[1] * (2 if self.bidir else 1)   # the reversed copy rides along as B more sequences
+            spec = [(Bm, self.lstm_lay[i], 1 - self.lstm_drop[i]) for i in range(self.N_lstm_lay)]
+            pf = self.__dict__.setdefault('_drop_prefetch', rng.DropMaskPrefetcher())
+            drop_masks = pf.take(spec)
+            if x.is_cuda and torch.is_grad_enabled():
+                pf.prefetch(spec)
         for i in range(self.N_lstm_lay):
             self.if_hsigmoid = 0     # as the reference (:1080)
             H = self.lstm_lay[i]
@@ -682,7 +692,8 @@ class LSTM(nn.Module):
             rt.split_fwd = self.b200_proj_terms == 2
             # drop mask: same for all time steps, NOT rescaled; drawn on the CPU generator (:843-851)
             if self.test_flag == False:  # noqa: E712 (reference spelling)
-                drop_mask = torch.bernoulli(torch.Tensor(B, H).fill_(1 - self.lstm_drop[i]))
+                drop_mask = drop_masks[i]
+                assert tuple(drop_mask.shape) == (B, H)
                 rt.drop = self._upload_drop_mask(i, drop_mask, x.device)
                 rt.drop_scalar = 1.0
             else:

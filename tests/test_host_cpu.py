@@ -111,3 +111,44 @@ def test_percentile_threshold_matches_numpy():
         assert got.dtype == torch.float32 and got.dim() == 0
         assert got.item() == float(np.float32(want)), (n, perc, got.item(), want)
         assert torch.equal(torch.from_numpy(a) > got, torch.from_numpy(a) > want)
+
+
+def test_drop_mask_prefetch_is_bit_identical_to_drawing_on_demand():
+    """b200/rng.py: masks drawn one forward ahead on a copy of the generator state == the reference's on-demand draws
+    (neural_networks.py:843-851), also when somebody seeds or uses the default generator in between."""
+    import torch
+    from b200 import rng
+    spec = [(7, 5, 0.8), (7, 3, 0.6)]
+
+    def on_demand():
+        return [torch.bernoulli(torch.Tensor(b, h).fill_(p)) for (b, h, p) in spec]
+
+    # reference stream: forward, forward, foreign draw, forward, re-seed, forward
+    torch.manual_seed(11)
+    ref = [on_demand(), on_demand()]
+    foreign_ref = torch.rand(3)
+    ref.append(on_demand())
+    torch.manual_seed(5)
+    ref.append(on_demand())
+    tail_ref = torch.rand(2)
+
+    torch.manual_seed(11)
+    pf = rng.DropMaskPrefetcher()
+    got = []
+    got.append(pf.take(spec)); pf.prefetch(spec)
+    got.append(pf.take(spec)); pf.prefetch(spec)          # served from the prefetch
+    foreign = torch.rand(3)                                  # somebody else draws: the prefetch must be dropped
+    got.append(pf.take(spec)); pf.prefetch(spec)
+    torch.manual_seed(5)                                     # re-seeded: dropped again
+    got.append(pf.take(spec)); pf.prefetch(spec)
+    tail = torch.rand(2)                                     # a pending prefetch never advances the default generator
+    assert torch.equal(foreign, foreign_ref) and torch.equal(tail, tail_ref)
+    for a, b in zip(ref, got):
+        for x, y in zip(a, b):
+            assert torch.equal(x, y)
+    # a different shape request drops the prefetch as well
+    torch.manual_seed(3)
+    want = [torch.bernoulli(torch.Tensor(2, 2).fill_(0.5))]
+    torch.manual_seed(3)
+    pf.prefetch(spec)
+    assert torch.equal(pf.take([(2, 2, 0.5)])[0], want[0])

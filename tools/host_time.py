@@ -21,3 +21,7 @@ t1 = time.perf_counter()
 torch.cuda.synchronize()
 t2 = time.perf_counter()
 print('host enqueue %.2f ms per step, until drained %.2f ms per step' % ((t1 - t0) / K * 1e3, (t2 - t0) / K * 1e3))
+for n in nets.values():
+    pf = n.__dict__.get('_drop_prefetch')
+    if pf is not None:
+        print('drop-mask prefetch: %d hits, %d misses' % (pf.hits, pf.misses))
