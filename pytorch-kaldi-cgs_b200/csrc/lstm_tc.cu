@@ -823,11 +823,11 @@ __global__ void __launch_bounds__((SPW <= 2 ? TC_MAX_WARPS2 : TC_MAX_WARPS) * 32
                 if (!coop_push) {
                     // per warp, right after its own gate math, so that the DSMEM traffic overlaps the other warps
                     const uint32_t base = (uint32_t)((((size_t)nxt * CL + rank) * slice + (size_t)s0w * 4) * 2);
-                    const int total = NB * pch * (CL - 1);
+                    const int total = NB * pch * 3;  // this path is the cluster of 4 (coop_push = CL > 4)
                     for (int q = lane; q < total; q += 32) {
                         const int row = q & 15, rest = q >> 4;
-                        const int d = rest % (CL - 1), ch = rest / (CL - 1);
-                        const uint32_t peer = (uint32_t)((rank + 1 + d) % CL);
+                        const int d = rest % 3, ch = rest / 3;  // constants: no integer division in the time loop
+                        const uint32_t peer = (uint32_t)((rank + 1 + d) & 3);
                         const uint32_t off = base + (uint32_t)(row * HcS * 2 + ch * (push16 ? 16 : 8));
                         const unsigned char* src = reinterpret_cast<const unsigned char*>(hbuf) + off;
                         if (push16)
