@@ -185,7 +185,7 @@ static int tc_plan_get(const hcgs_plan* cplan, int CL, TcPlan** out) {
         int64_t total = 0;
         for (const HTask& k : work) total += k.cost;
         static const int split_pct = getenv("HCGS_TC_SPLIT") ? atoi(getenv("HCGS_TC_SPLIT")) : 150;  // tuning only
-        static const int lead_cost = getenv("HCGS_TC_LEAD") ? atoi(getenv("HCGS_TC_LEAD")) : 600;     // tuning only
+        static const int lead_cost = getenv("HCGS_TC_LEAD") ? atoi(getenv("HCGS_TC_LEAD")) : 300;     // tuning only
         const int64_t fair = std::max<int64_t>(300, (total * split_pct / 100 + TW - 1) / TW);
         for (size_t i = 0; i < work.size(); ++i) {
             const HTask w = work[i];
