@@ -1149,7 +1149,13 @@ __global__ void __launch_bounds__(TCB_CW * 32, 1) lstm_tc_bwd3_kernel(const __gr
                 float dh = dh_s[sm];
                 if (s > 0) {
                     const float* sl_p = slots + so0 + ((b ^ swz) << 2);
-                    for (int src = 0; src < CL; ++src) dh += sl_p[(size_t)src * SPC * 64];
+                    if (CL == 4) {  // the common cluster: four independent loads, same summation order
+                        const float p0 = sl_p[0], p1 = sl_p[(size_t)SPC * 64], p2 = sl_p[(size_t)2 * SPC * 64],
+                                    p3 = sl_p[(size_t)3 * SPC * 64];
+                        dh = (((dh + p0) + p1) + p2) + p3;
+                    } else {
+                        for (int src = 0; src < CL; ++src) dh += sl_p[(size_t)src * SPC * 64];
+                    }
                 }
                 const float4 g4 = *reinterpret_cast<const float4*>(gst + gs0 + j * BPP * BW);
                 const float cval = ck_s[sm];
@@ -1232,8 +1238,8 @@ __global__ void __launch_bounds__(TCB_CW * 32, 1) lstm_tc_bwd3_kernel(const __gr
             // staged: remote strips are written to the gate stage consumed by this step's item phase (compact index over
             // the CL-1 foreign slices) and ONE bulk copy per task moves them: the copy engine does the DSMEM transfer,
             // the LSU queue stays free for the other warps' mma operands (direct st.async pushes back-pressure it)
-            const uint32_t sbase = stage_addr0 + (uint32_t)(k & 1) * stage_bytes +
-                                   (uint32_t)((((d - rank - 1 + CL) % CL) * SPC + tb.z) * 256);
+            const int rel = d - rank - 1 + (d <= rank ? CL : 0);  // compact index of the destination among the peers
+            const uint32_t sbase = stage_addr0 + (uint32_t)(k & 1) * stage_bytes + (uint32_t)((rel * SPC + tb.z) * 256);
             const bool direct = remote && !staged;
             const uint32_t rbase = direct ? mapa_u32(obase, (uint32_t)d) : (remote ? sbase : obase);
             const uint32_t rbar = remote ? mapa_u32(mb_full, (uint32_t)d) : 0u;
