@@ -1138,8 +1138,10 @@ __global__ void __launch_bounds__(TCB_CW * 32, 1) lstm_tc_bwd3_kernel(const __gr
             const float* gst = gates_s + (size_t)(k & 1) * stage_floats;
             const float* ck_s = c_s + (size_t)(k & 1) * NB * Hc;
             const float* cm_s = c_s + (size_t)((k & 1) ^ 1) * NB * Hc;
-            float* dpre_k = a.dpre ? a.dpre + (size_t)k * a.B * 4 * ldH : nullptr;
-            __nv_bfloat16* dpreb_k = a.dpreb ? a.dpreb + (size_t)k * a.B * 4 * ldH : nullptr;
+            float* dpre_k = a.dpre + (size_t)k * a.B * 4 * ldH;
+            __nv_bfloat16* dpreb_k = a.dpreb + (size_t)k * a.B * 4 * ldH;
+            const bool st32 = a.dpre != nullptr && !(a.dbg & 1), st16 = a.dpreb != nullptr && !(a.dbg & 1);
+            const bool has_prev = k > 0;  // c_{-1} = 0 (the other c buffer then holds an older step or nothing)
 #pragma unroll
             for (int j = 0; j < IT; ++j) {
                 const int b = bq + j * BPP;
@@ -1159,7 +1161,8 @@ __global__ void __launch_bounds__(TCB_CW * 32, 1) lstm_tc_bwd3_kernel(const __gr
                 }
                 const float4 g4 = *reinterpret_cast<const float4*>(gst + gs0 + j * BPP * BW);
                 const float cval = ck_s[sm];
-                const float cm1 = (k > 0) ? cm_s[sm] : 0.f;  // c_{-1} = 0
+                const float cmv = cm_s[sm];
+                const float cm1 = has_prev ? cmv : 0.f;
                 const float fg = g4.x, ig = g4.y, og = g4.z, gg = g4.w;
                 const float tc = (ACT == HCGS_ACT_TANH) ? fast_tanh(cval) : act_apply_fast(a.act, cval);
                 const float dog = dh * tc;
@@ -1176,10 +1179,10 @@ __global__ void __launch_bounds__(TCB_CW * 32, 1) lstm_tc_bwd3_kernel(const __gr
                 if (!ok) dp = make_float4(0.f, 0.f, 0.f, 0.f);
                 dc_carry[j] = ok ? dct * fg : 0.f;
                 const uint2 pb = make_uint2(pack_bf16x2(dp.x, dp.y), pack_bf16x2(dp.z, dp.w));
-                if ((ok || (unit_pad && b0 + b < a.B)) && !(a.dbg & 1)) {
+                if (ok || (unit_pad && b0 + b < a.B)) {
                     const uint32_t go = go0 + (uint32_t)(j * BPP) * 4u * (uint32_t)ldH;
-                    if (dpre_k) *reinterpret_cast<float4*>(dpre_k + go) = dp;
-                    if (dpreb_k) *reinterpret_cast<uint2*>(dpreb_k + go) = pb;
+                    if (st32) *reinterpret_cast<float4*>(dpre_k + go) = dp;
+                    if (st16) *reinterpret_cast<uint2*>(dpreb_k + go) = pb;
                 }
                 *reinterpret_cast<uint2*>(dpre_s + ds0 + j * BPP * DPS) = pb;
             }

@@ -73,6 +73,8 @@ def from_inter(x, T, B, H, ldH):
 
 @pytest.mark.parametrize('H,B,T,blocks,drops,act,cl,nb', [
     (24, 3, 7, [8, 4], [50, 50], 'tanh', 4, 16),
+    (24, 3, 1, [8, 4], [50, 50], 'tanh', 4, 16),     # T = 1: c_{-1} and the second c buffer are never loaded
+    (550, 35, 3, [32, 4], [75, 62.5], 'tanh', 4, 16),  # three clusters, the last one with 3 of 16 sequences
     (40, 19, 9, [8, 4], [50, 50], 'htanh', 4, 16),
     (550, 8, 12, [32, 4], [75, 62.5], 'tanh', 8, 16),
     (550, 20, 6, [32, 4], [75, 62.5], 'tanh', 0, 0),
