@@ -34,6 +34,9 @@ def select_config(name):
     cd head, no dropout (cfg/LibriSpeech_CGS/libri_LSTM_fmllr_460.cfg:93-94, 157-160; BN on)."""
     global N_PDF, N_MONO, LAYERS, HID, DROP, CONFIG, MODEL
     CONFIG = name
+    if name == 'timit':
+        N_PDF, N_MONO, LAYERS, HID, DROP = 1944, 48, 4, 550, '0.2'
+        MODEL = list(MODEL_TIMIT)
     if name == 'libri':
         N_PDF, N_MONO, LAYERS, HID, DROP = 3480, 0, 5, 1024, '0.0'
         MODEL = ['out_dnn1=compute(LSTM_layers,fbank)', 'out_dnn2=compute(MLP_layers,out_dnn1)',
@@ -63,10 +66,11 @@ def cfg_sections(to_do='train', precision='bf16'):
     return lstm, mlp, mono
 
 
-MODEL = ['out_dnn1=compute(LSTM_layers,fbank)', 'out_dnn2=compute(MLP_layers,out_dnn1)',
+MODEL_TIMIT = ['out_dnn1=compute(LSTM_layers,fbank)', 'out_dnn2=compute(MLP_layers,out_dnn1)',
          'out_dnn3=compute(MLP_layers2,out_dnn1)', 'loss_mono=cost_nll(out_dnn3,lab_mono)',
          'loss_mono_w=mult_constant(loss_mono,1.0)', 'loss_cd=cost_nll(out_dnn2,lab_cd)',
          'loss_final=sum(loss_cd,loss_mono_w)', 'err_final=cost_err(out_dnn2,lab_cd)']
+MODEL = list(MODEL_TIMIT)
 
 
 def synthetic_minibatch(T, B, seed):
@@ -568,6 +572,7 @@ def main():
                     help='bf16 = tensor-core build (BASELINE configs[1] "bf16 train"), fp32 = CUDA-core parity build')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-export', action='store_true', help='skip the posterior-export measurement')
+    ap.add_argument('--no-libri', action='store_true', help='skip the LibriSpeech-shape (configs[3]) object of the line')
     ap.add_argument('--no-cfg-batch', action='store_true', help='skip the T = 1000, B = 8 (reference cfg minibatch) line')
     ap.add_argument('--what', default='train', choices=['train', 'export'], help='reference arm: which leg to time')
     ap.add_argument('--ref-batch', type=int, default=REF_BATCH, help='reference arm: sequences per step (cfg batch size)')
@@ -734,8 +739,15 @@ def main():
     if not args.no_export:
         export = run_export(dev, nets, args, T, B, rank, world, hbm_peak, peak_kind)
 
-    t = torch.tensor([ms_total, ms_e2e, float(frames), float(frames_e2e), float(launches)], device=dev,
-                     dtype=torch.float64)
+    libri = None
+    if args.config == 'timit' and not args.no_libri and args.precision == 'bf16':
+        del resident, stage_in
+        torch.cuda.empty_cache()
+        libri = run_libri_leg(dev, args, rank, world,
+                              lambda n: bdist.OverlappedGradBuckets(bdist.lstm_mlp_groups(list(n.values())), dev))
+    lib_ms, lib_frames = (libri[0], float(libri[1])) if libri else (0.0, 0.0)
+    t = torch.tensor([ms_total, ms_e2e, float(frames), float(frames_e2e), float(launches), lib_ms, lib_frames],
+                     device=dev, dtype=torch.float64)
     if world > 1:
         tmax = t.clone()
         torch.distributed.all_reduce(tmax, op=torch.distributed.ReduceOp.MAX)
@@ -743,6 +755,7 @@ def main():
         torch.distributed.all_reduce(tsum, op=torch.distributed.ReduceOp.SUM)
         ms_total, ms_e2e = tmax[0].item(), tmax[1].item()
         frames, frames_e2e, launches = tsum[2].item(), tsum[3].item(), int(tsum[4].item())
+        lib_ms, lib_frames = tmax[5].item(), tsum[6].item()
         torch.distributed.barrier()
         torch.distributed.destroy_process_group()
     if rank != 0:
@@ -800,6 +813,15 @@ def main():
         # top-level copies so that per-N export numbers survive in the driver's SCALE records
         line['export_value'] = export['value']
         line['export_e2e_value'] = export['e2e']['value']
+    if libri is not None:
+        line['libri'] = {'workload': 'LibriSpeech_CGS LSTM train step (BASELINE configs[3]): 40-dim fbank -> 5x1024 HCGS LSTM '
+                                     '(32,4 / 75,62.5 masks, BN, tanh, no dropout) -> 3480-pdf (64,4 / 50,25) softmax head, '
+                                     'NLL, RMSprop', 'value': lib_frames / (lib_ms * 1e-3), 'unit': 'frames/s',
+                         'ms_per_step': lib_ms / args.steps, 'steps': args.steps, 'seq_len': libri[2],
+                         'batch_per_gpu': libri[3], 'n_gpus': world, 'data': 'synthetic',
+                         'note': 'H = 1024 needs clusters of 16 CTAs for the recurrent kernels (7 co-resident = 112 '
+                                 'sequences per wave, two waves per step)'}
+        line['libri_value'] = line['libri']['value']   # top-level copy for the driver's SCALE records
     if cfg_batch is not None:
         line['cfg_batch'] = cfg_batch
         if not args.no_cpu_baseline:
@@ -810,6 +832,42 @@ def main():
         if export is not None:
             export['cpu_baseline'] = reference_subprocess('export', T, 1, 12, 2, args.config)
     print(json.dumps(line))
+
+
+def run_libri_leg(dev, args, rank, world, bucket_factory):
+    """BASELINE configs[3] as a second object of the default line: 5x1024 HCGS LSTM, 3480 pdfs, B = 224 sequences per GPU
+    (two waves of the 7 co-resident clusters of 16 CTAs), same T, device-resident minibatches, the same train step.
+    Every rank runs it (data parallel like the headline); returns (ms_total, frames) of this rank."""
+    select_config('libri')
+    try:
+        T, B = args.seq_len, 224
+        nets, graph, opts = build_workload(dev, precision=args.precision)
+        bucket = bucket_factory(nets) if world > 1 else None
+        mbs = [synthetic_minibatch(T, B, 5000 * (rank + 1) + i) for i in range(2)]
+        res = [m[0].to(dev) for m in mbs]
+        for s in range(6):   # warm-up + allocator steady state
+            train_step(graph, opts, res[s % 2], T, B, bucket)
+        torch.cuda.synchronize()
+        if world > 1:
+            torch.distributed.barrier()
+            torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        frames = 0
+        for s in range(args.steps):
+            train_step(graph, opts, res[s % 2], T, B, bucket)
+            frames += mbs[s % 2][1]
+        e1.record()
+        torch.cuda.synchronize()
+        if world > 1:
+            torch.distributed.barrier()
+            torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        del nets, graph, opts, res, bucket
+        torch.cuda.empty_cache()
+        return ms, frames, T, B
+    finally:
+        select_config('timit')
 
 
 if __name__ == '__main__':
