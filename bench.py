@@ -798,6 +798,11 @@ def main():
         if k in fwork:
             e['GB_per_s'] = round(fwork[k][0] / (ftot[k] * 1e-3) / 1e9, 1)
             e['TFLOP_per_s'] = round(fwork[k][1] / (ftot[k] * 1e-3) / 1e12, 2)
+            # fractions of the measured peaks (MEASURED_PEAKS.json: HBM copy bandwidth, sustained dense bf16): algorithmic
+            # bytes / FLOPs of the entry point over its event-timed duration inside a step
+            e['hbm_frac'] = round(e['GB_per_s'] / hbm_peak, 3)
+            if e['TFLOP_per_s'] > 0:
+                e['tensor_frac'] = round(e['TFLOP_per_s'] / tf_peak, 3)
         per_kernel[k] = e
     line = {'metric': 'hcgs_lstm_train_frames_per_sec', 'value': value, 'unit': 'frames/s', 'n_gpus': world,
             'steps': args.steps, 'warmup': W, 'ms_per_step': ms_total / args.steps, 'higher_is_better': True,
