@@ -350,6 +350,14 @@ int hcgs_out_logsoftmax_prior_fwd(const hcgs_plan* plan, const void* wpack, cons
  * hp = 8 floats: {lr, a, b, eps, weight_decay, c, d, step}; see optimizer.cu.                */
 int hcgs_opt_step(int kind, float* param, const float* grad, float* state1, float* state2,
                   int64_t numel, const float* hp, float grad_scale, hcgs_stream stream);
+/* hcgs_opt_step_multi: the same update for a whole parameter group in one launch per 48 tensors (torch.optim walks
+ * the group tensor by tensor, utils.py:1833-1881 hands it every parameter of a net): HOST arrays of n_tensors device
+ * pointers / element counts; state1 / state2 may be NULL when the optimizer kind does not use them.  hp: the same eight
+ * values in DOUBLE precision (1 - beta, the bias corrections and lr / bias_correction1 are formed in double and rounded
+ * once, as torch.optim does with its Python floats).                                                               */
+int hcgs_opt_step_multi(int kind, int n_tensors, float* const* params, const float* const* grads,
+                        float* const* state1, float* const* state2, const int64_t* numels, const double* hp,
+                        float grad_scale, hcgs_stream stream);
 
 #ifdef __cplusplus
 }

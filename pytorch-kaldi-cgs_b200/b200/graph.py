@@ -90,11 +90,32 @@ class Graph:
         return outs
 
 
-def make_optimizer(net, opts):
-    """utils.optimizer_init for one net; ``opts`` is the cfg section (string values)."""
+def make_optimizer(net, opts, fused=None):
+    """utils.optimizer_init for one net; ``opts`` is the cfg section (string values).  For CUDA nets the update runs
+    as one fused launch per net (b200/optim.py, same arithmetic and state names as torch.optim); ``fused=False`` or the
+    cfg key ``b200_fused_opt = False`` builds the torch.optim instance the reference would build."""
     from neural_networks import strtobool
     lr = float(opts['arch_lr'])
     kind = opts['arch_opt']
+    params = list(net.parameters())
+    if fused is None:
+        fused = bool(strtobool(opts.get('b200_fused_opt', 'True')))
+    fused = fused and bool(params) and all(p.is_cuda and p.dtype == torch.float32 for p in params)
+    if fused and kind == 'rmsprop' and bool(strtobool(opts['opt_centered'])):
+        fused = False
+    if fused and kind == 'adam' and bool(strtobool(opts['opt_amsgrad'])):
+        fused = False
+    if fused and kind in ('sgd', 'adam', 'rmsprop'):
+        from .optim import FusedOptimizer
+        if kind == 'sgd':
+            return FusedOptimizer(params, 'sgd', lr, momentum=float(opts['opt_momentum']),
+                                  weight_decay=float(opts['opt_weight_decay']), dampening=float(opts['opt_dampening']),
+                                  nesterov=bool(strtobool(opts['opt_nesterov'])))
+        if kind == 'adam':
+            return FusedOptimizer(params, 'adam', lr, betas=list(map(float, opts['opt_betas'].split(','))),
+                                  eps=float(opts['opt_eps']), weight_decay=float(opts['opt_weight_decay']))
+        return FusedOptimizer(params, 'rmsprop', lr, momentum=float(opts['opt_momentum']), alpha=float(opts['opt_alpha']),
+                              eps=float(opts['opt_eps']), weight_decay=float(opts['opt_weight_decay']))
     if kind == 'sgd':
         return optim.SGD(net.parameters(), lr=lr, momentum=float(opts['opt_momentum']),
                          weight_decay=float(opts['opt_weight_decay']), dampening=float(opts['opt_dampening']),

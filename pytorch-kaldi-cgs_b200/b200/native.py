@@ -91,6 +91,8 @@ SIGNATURES = {
     'hcgs_logsoftmax_bwd_fused': (c_int, [_f, _f, c_int64, c_int, _f, c_int64, _f, c_void_p]),
     'hcgs_nll_fwd_bwd': (c_int, [_f, c_int64, c_int, _f, c_int, c_float, _f, _f, c_void_p]),
     'hcgs_opt_step': (c_int, [c_int, _f, _f, _f, _f, c_int64, POINTER(c_float), c_float, c_void_p]),
+    'hcgs_opt_step_multi': (c_int, [c_int, c_int, POINTER(c_void_p), POINTER(c_void_p), POINTER(c_void_p),
+                                    POINTER(c_void_p), POINTER(c_int64), POINTER(ctypes.c_double), c_float, c_void_p]),
 }
 
 
@@ -124,7 +126,8 @@ KERNELS_PER_CALL = {'hcgs_mask_apply': 1, 'hcgs_quantize_w': 1, 'hcgs_quantize_a
                     'hcgs_tc_pack_nn': 1, 'hcgs_tc_gemm_nn': 1, 'hcgs_tc_sddmm': 1, 'hcgs_out_pack': 1,
                     'hcgs_out_logsoftmax_prior_fwd': 1, 'hcgs_act_fwd': 1, 'hcgs_act_bwd': 1,
                     'hcgs_logsoftmax_fwd': 1, 'hcgs_logsoftmax_bwd': 1, 'hcgs_logsoftmax_bwd_fused': 1,
-                    'hcgs_layernorm_fwd': 1, 'hcgs_layernorm_bwd': 1, 'hcgs_nll_fwd_bwd': 1, 'hcgs_opt_step': 1}
+                    'hcgs_layernorm_fwd': 1, 'hcgs_layernorm_bwd': 1, 'hcgs_nll_fwd_bwd': 1, 'hcgs_opt_step': 1,
+                    'hcgs_opt_step_multi': 1}
 LAUNCHES = {'total': 0}
 
 
@@ -693,3 +696,18 @@ def opt_step(kind, param, grad, state1, state2, hp, grad_scale=1.0):
     arr = (c_float * 8)(*[float(v) for v in hp])
     _check(load().hcgs_opt_step(OPT_KINDS[kind], _ptr(param), _ptr(grad), _ptr(state1), _ptr(state2), param.numel(),
                                 arr, float(grad_scale), _stream()), 'hcgs_opt_step')
+
+
+def opt_step_multi(kind, params, grads, state1, state2, hp, grad_scale=1.0):
+    """One fused optimizer update for a list of fp32 CUDA tensors (one launch per 48 tensors).  state1 / state2: lists of
+    tensors or None (kinds that do not use them)."""
+    _require_cuda(*params, *grads, *(state1 or ()), *(state2 or ()))
+    n = len(params)
+    assert len(grads) == n and len(hp) == 8 and all(t.is_contiguous() for t in list(params) + list(grads))
+
+    def table(ts):
+        return (c_void_p * n)(*[t.data_ptr() for t in ts]) if ts else None
+    arr = (ctypes.c_double * 8)(*[float(v) for v in hp])
+    numels = (c_int64 * n)(*[int(p.numel()) for p in params])
+    _check(load().hcgs_opt_step_multi(OPT_KINDS[kind], n, table(params), table(grads), table(state1), table(state2),
+                                      numels, arr, float(grad_scale), _stream()), 'hcgs_opt_step_multi')

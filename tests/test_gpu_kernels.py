@@ -326,6 +326,41 @@ def test_optimizer_steps_match_torch(kind):
         close(pd, p.detach(), rtol=2e-6, what='%s step %d' % (kind, step))
 
 
+@pytest.mark.parametrize('kind,kw', [
+    ('sgd', dict(lr=0.08)),
+    ('sgd', dict(lr=0.05, momentum=0.9, weight_decay=1e-3, nesterov=True)),
+    ('rmsprop', dict(lr=0.0016, alpha=0.95, eps=1e-8)),
+    ('rmsprop', dict(lr=0.001, alpha=0.9, eps=1e-8, momentum=0.5, weight_decay=1e-4)),
+    ('adam', dict(lr=0.002, betas=(0.9, 0.999), eps=1e-8)),
+])
+def test_fused_optimizer_matches_torch_optim(kind, kw):
+    """b200/optim.py (hcgs_opt_step_multi, one launch per 48 tensors) == torch.optim on the same parameters, incl. the
+    per-parameter state names, over three steps and more tensors than one launch holds."""
+    from b200.optim import FusedOptimizer
+    torch.manual_seed(5)
+    d = dev()
+    shapes = [(7, 5), (1,), (33,), (4, 1944)] * 13 + [(550, 64)]     # 53 tensors: two launches
+    ref = [torch.nn.Parameter(torch.randn(*s, device=d)) for s in shapes]
+    ours = [torch.nn.Parameter(r.detach().clone()) for r in ref]
+    cls = {'sgd': torch.optim.SGD, 'rmsprop': torch.optim.RMSprop, 'adam': torch.optim.Adam}[kind]
+    o_ref, o_our = cls(ref, **kw), FusedOptimizer(ours, kind, **kw)
+    for step in range(3):
+        for r, o in zip(ref, ours):
+            g = torch.randn_like(r)
+            r.grad, o.grad = g.clone(), g.clone()
+        if step == 1:
+            ours[3].grad = None      # a parameter without a gradient is skipped, like torch.optim does
+            ref[3].grad = None
+        o_ref.step()
+        o_our.step()
+        for i, (r, o) in enumerate(zip(ref, ours)):
+            close(o.detach(), r.detach(), rtol=3e-6, what='%s tensor %d step %d' % (kind, i, step))
+    names = {'sgd': ['momentum_buffer'] if kw.get('momentum') else [], 'rmsprop': ['square_avg'],
+             'adam': ['exp_avg', 'exp_avg_sq']}[kind]
+    for n in names:
+        close(o_our.state[ours[0]][n], o_ref.state[ref[0]][n], rtol=3e-6, what='state ' + n)
+
+
 @pytest.mark.parametrize('M,P', [(517, 1944), (300, 48), (70, 3480), (9, 4)])
 def test_logsoftmax_bwd_fused(M, P):
     """hcgs_logsoftmax_bwd_fused = logsoftmax_bwd + colsum + cast_bf16 of the unfused path (same arithmetic)."""
