@@ -90,6 +90,48 @@ def synthetic_minibatch(T, B, seed):
     return inp, frames
 
 
+def synthetic_chunk(n_snt, T, seed):
+    """One chunk as data_io.read_lab_fea hands it to core.run_nn (data_io.py:276-282): sentences of U[T/2, T] frames
+    sorted by length, [rows, D_FEA + 2] fp32 (features, then the pdf / monophone labels as float columns)."""
+    g = np.random.RandomState(seed)
+    lens = np.sort(g.randint(max(1, T // 2), T + 1, n_snt))
+    rows = int(lens.sum())
+    data = np.empty((rows, D_FEA + 2), dtype=np.float32)
+    data[:, :D_FEA] = g.standard_normal((rows, D_FEA)).astype(np.float32)
+    data[:, D_FEA] = g.randint(0, N_PDF, rows)
+    data[:, D_FEA + 1] = g.randint(0, max(N_MONO, 1), rows)
+    return data, np.cumsum(lens)
+
+
+def run_chunk_leg(graph, opts, dev, steps, T, B):
+    """one training chunk of `steps` minibatches through b200.chunk.run_chunk -- the chunk uploaded from
+    pinned host memory once, every minibatch assembled on the device (hcgs_assemble_batch), loss / error read once."""
+    import random
+    from b200 import chunk as bchunk
+    data, end = synthetic_chunk(steps * B, T, 4321)
+    host = torch.from_numpy(data).pin_memory()
+    random.seed(2234)
+    bchunk.run_chunk(graph, opts, host[:int(end[2 * B - 1])], end[:2 * B], B)       # warm-up: two minibatches
+    torch.cuda.synchronize()
+    random.seed(2234)
+    c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    c0.record()
+    loss, err = bchunk.run_chunk(graph, opts, host, end, B)
+    c1.record()
+    torch.cuda.synchronize()
+    wall = (time.perf_counter() - t0) * 1e3
+    ms = c0.elapsed_time(c1)
+    assert np.isfinite(loss) and 0.0 <= err <= 1.0, (loss, err)
+    plan = bchunk.ChunkPlan(end, B, random.Random(0))
+    return {'workload': 'one training chunk (core.py:156-273) of %d minibatches x %d sentences of U[%d, %d] frames sorted by '
+                        'length: chunk uploaded once, minibatches assembled on the device with the random left padding of '
+                        'core.py:183-200, loss / error read once per chunk' % (steps, B, max(1, T // 2), T),
+            'value': int(end[-1]) / (ms * 1e-3), 'unit': 'frames/s', 'ms_per_minibatch': ms / steps, 'ms_wall': wall,
+            'minibatches': steps, 'frames': int(end[-1]), 'padded_rows': int(plan.max_len.sum()) * B,
+            'h2d_bytes_per_chunk': int(data.nbytes), 'd2h_bytes_per_chunk': 8, 'loss': loss}
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
 
@@ -573,6 +615,7 @@ def main():
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-export', action='store_true', help='skip the posterior-export measurement')
     ap.add_argument('--no-libri', action='store_true', help='skip the LibriSpeech-shape (configs[3]) object of the line')
+    ap.add_argument('--no-chunk', action='store_true', help='skip the chunk-pipeline (device minibatch assembly) object')
     ap.add_argument('--no-cfg-batch', action='store_true', help='skip the T = 1000, B = 8 (reference cfg minibatch) line')
     ap.add_argument('--what', default='train', choices=['train', 'export'], help='reference arm: which leg to time')
     ap.add_argument('--ref-batch', type=int, default=REF_BATCH, help='reference arm: sequences per step (cfg batch size)')
@@ -734,6 +777,10 @@ def main():
                      'note': "the reference cfg's own minibatch (batch_size_train = 8, max_seq_length_train = 1000): "
                              'one cluster group of sequences, the recurrence is latency bound'}
 
+    chunk_leg = None
+    if world == 1 and not args.no_chunk and args.config == 'timit':
+        chunk_leg = run_chunk_leg(graph, opts, dev, args.steps, T, B)
+
     hbm_peak, tf_peak, peak_kind = measured_peaks()
     export = None
     if not args.no_export:
@@ -827,6 +874,8 @@ def main():
                          'note': 'H = 1024 needs clusters of 16 CTAs for the recurrent kernels (7 co-resident = 112 '
                                  'sequences per wave, two waves per step)'}
         line['libri_value'] = line['libri']['value']   # top-level copy for the driver's SCALE records
+    if chunk_leg is not None:
+        line['chunk'] = chunk_leg
     if cfg_batch is not None:
         line['cfg_batch'] = cfg_batch
         if not args.no_cpu_baseline:

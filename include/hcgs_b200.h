@@ -359,6 +359,18 @@ int hcgs_opt_step_multi(int kind, int n_tensors, float* const* params, const flo
                         float* const* state1, float* const* state2, const int64_t* numels, const double* hp,
                         float grad_scale, hcgs_stream stream);
 
+/* ---- minibatch assembly from a chunk resident in HBM ---------------------------------------
+ * Replaces the per-minibatch host loop of core.py:183-200 (torch.zeros(max_len, batch, dim) + one slice copy per
+ * sentence behind `random.randint(0, max_len - snt_len)` leading zero rows, then `.cuda()`): the chunk's
+ * [chunk_rows, dim] fp32 matrix (features and label columns, as read_lab_fea packs them) is uploaded once, the host
+ * draws the offsets in the reference's order and this entry point writes the whole [max_len, batch, dim] tensor,
+ * padding included, in one launch:
+ *   out[t][k][:] = chunk[beg[k] + t - left[k]][:]  for left[k] <= t < left[k] + len[k], else 0.
+ * beg / len / left: DEVICE arrays of `batch` entries (first chunk row, length and leading zero rows of sentence k).
+ * Rows that would fall outside the chunk are written as zeros (the host wrapper checks the tables before upload).  */
+int hcgs_assemble_batch(const float* chunk, int64_t chunk_rows, int dim, const int64_t* beg, const int32_t* len,
+                        const int32_t* left, int batch, int max_len, float* out, hcgs_stream stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -6,10 +6,13 @@ a CUDA device, an exception is raised -- the product path never silently runs on
 PyTorch is used for device memory and streams only (``tensor.data_ptr()``,
 ``torch.cuda.current_stream()``).
 """
+import collections
 import ctypes
+import hashlib
 import os
 from ctypes import POINTER, c_char_p, c_float, c_int, c_int64, c_void_p
 
+import numpy as np
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
@@ -93,6 +96,7 @@ SIGNATURES = {
     'hcgs_opt_step': (c_int, [c_int, _f, _f, _f, _f, c_int64, POINTER(c_float), c_float, c_void_p]),
     'hcgs_opt_step_multi': (c_int, [c_int, c_int, POINTER(c_void_p), POINTER(c_void_p), POINTER(c_void_p),
                                     POINTER(c_void_p), POINTER(c_int64), POINTER(ctypes.c_double), c_float, c_void_p]),
+    'hcgs_assemble_batch': (c_int, [_f, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, _f, c_void_p]),
 }
 
 
@@ -127,7 +131,7 @@ KERNELS_PER_CALL = {'hcgs_mask_apply': 1, 'hcgs_quantize_w': 1, 'hcgs_quantize_a
                     'hcgs_out_logsoftmax_prior_fwd': 1, 'hcgs_act_fwd': 1, 'hcgs_act_bwd': 1,
                     'hcgs_logsoftmax_fwd': 1, 'hcgs_logsoftmax_bwd': 1, 'hcgs_logsoftmax_bwd_fused': 1,
                     'hcgs_layernorm_fwd': 1, 'hcgs_layernorm_bwd': 1, 'hcgs_nll_fwd_bwd': 1, 'hcgs_opt_step': 1,
-                    'hcgs_opt_step_multi': 1}
+                    'hcgs_opt_step_multi': 1, 'hcgs_assemble_batch': 1}
 LAUNCHES = {'total': 0}
 
 
@@ -228,6 +232,34 @@ class Plan:
             self.destroy()
         except Exception:
             pass
+
+
+# Plans shared across model instances: core.run_nn rebuilds every net (and with it every mask-derived plan) for each
+# chunk (core.py:107-121).  The masks of a run come from one seeded generator or from the checkpoint, so chunk after
+# chunk they are the same bits: the plan -- block index, cluster layout, task tables -- is looked up by a digest of the
+# structural mask instead of being rebuilt.  Entries are only referenced, never destroyed, here: a plan
+# is freed by Plan.__del__ once the store and every net have dropped it.
+_PLAN_STORE = collections.OrderedDict()
+PLAN_STORE_LIMIT = 256
+PLAN_STORE_STATS = {'hits': 0, 'misses': 0}
+
+
+def shared_plan(mask, recurrent=False):
+    m = mask.detach().to('cpu', torch.float32).contiguous()
+    nz = (m != 0).numpy()
+    key = (tuple(m.shape), bool(recurrent), torch.cuda.current_device() if torch.cuda.is_available() else -1,
+           hashlib.blake2b(np.packbits(nz).tobytes(), digest_size=16).digest())
+    plan = _PLAN_STORE.get(key)
+    if plan is not None and plan._h is not None:
+        _PLAN_STORE.move_to_end(key)
+        PLAN_STORE_STATS['hits'] += 1
+        return plan
+    PLAN_STORE_STATS['misses'] += 1
+    plan = Plan(m, recurrent=recurrent)
+    _PLAN_STORE[key] = plan
+    while len(_PLAN_STORE) > PLAN_STORE_LIMIT:
+        _PLAN_STORE.popitem(last=False)
+    return plan
 
 
 # ---------------------------------------------------------------------------------------------
@@ -711,3 +743,22 @@ def opt_step_multi(kind, params, grads, state1, state2, hp, grad_scale=1.0):
     numels = (c_int64 * n)(*[int(p.numel()) for p in params])
     _check(load().hcgs_opt_step_multi(OPT_KINDS[kind], n, table(params), table(grads), table(state1), table(state2),
                                       numels, arr, float(grad_scale), _stream()), 'hcgs_opt_step_multi')
+
+
+def assemble_batch(chunk, beg, length, left, max_len, out=None):
+    """out[t, k, :] = chunk[beg[k] + t - left[k], :] inside sentence k, zeros elsewhere (core.py:183-200 in one launch).
+    chunk: [rows, dim] fp32 CUDA; beg int64, length / left int32 CUDA vectors of `batch` entries."""
+    _require_cuda(chunk)
+    _require_cuda_any(beg, length, left)
+    assert chunk.dim() == 2 and chunk.is_contiguous() and chunk.dtype == torch.float32
+    assert beg.dtype == torch.int64 and length.dtype == torch.int32 and left.dtype == torch.int32
+    batch = beg.numel()
+    assert length.numel() == batch and left.numel() == batch and batch >= 1
+    assert beg.is_contiguous() and length.is_contiguous() and left.is_contiguous()
+    dim = chunk.shape[1]
+    if out is None:
+        out = torch.empty(int(max_len), batch, dim, device=chunk.device, dtype=torch.float32)
+    assert out.is_contiguous() and tuple(out.shape) == (int(max_len), batch, dim)
+    _check(load().hcgs_assemble_batch(_ptr(chunk), chunk.shape[0], dim, _ptr(beg), _ptr(length), _ptr(left), batch,
+                                      int(max_len), _ptr(out), _stream()), 'hcgs_assemble_batch')
+    return out

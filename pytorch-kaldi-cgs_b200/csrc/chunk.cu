@@ -1,0 +1,60 @@
+// Minibatch assembly from a chunk that is resident in HBM (the loop at core.py:183-200 of the reference:
+// every sentence of the minibatch is copied into a zeroed [max_len, batch, dim] tensor behind a random number of leading
+// zero rows).  The random offsets are host decisions (Python's `random`, drawn by the caller in the reference's order);
+// the device does the byte movement: one pass that writes every output element once, zero padding included, so the
+// separate torch.zeros fill and the per-sentence slice copies of the reference are one launch.
+#include "common.cuh"
+
+namespace hcgs {
+
+// out[t][k][c] = chunk[beg[k] + t - left[k]][c] for left[k] <= t < left[k] + len[k], else 0.  One thread per four
+// consecutive floats of the flat output when dim % 4 == 0 (16-byte accesses), else one float per thread.
+template <int V>
+__global__ void __launch_bounds__(256) assemble_batch_kernel(const float* __restrict__ chunk, int64_t chunk_rows, int dim,
+                                                             const int64_t* __restrict__ beg,
+                                                             const int32_t* __restrict__ len,
+                                                             const int32_t* __restrict__ left, int batch,
+                                                             int64_t n_vec, float* __restrict__ out) {
+    const int dv = dim / V;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_vec; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t row = i / dv;
+        const int c = (int)(i - row * dv) * V;
+        const int k = (int)(row % batch);
+        const int64_t off = row / batch - (int64_t)__ldg(left + k);
+        const int64_t src = __ldg(beg + k) + off;
+        const bool in = off >= 0 && off < (int64_t)__ldg(len + k) && src >= 0 && src < chunk_rows;
+        if (V == 4) {
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (in) v = __ldg(reinterpret_cast<const float4*>(chunk + src * dim + c));
+            reinterpret_cast<float4*>(out)[i] = v;
+        } else {
+            out[i] = in ? __ldg(chunk + src * dim + c) : 0.f;
+        }
+    }
+}
+
+}  // namespace hcgs
+
+using namespace hcgs;
+
+extern "C" int hcgs_assemble_batch(const float* chunk, int64_t chunk_rows, int dim, const int64_t* beg,
+                                   const int32_t* len, const int32_t* left, int batch, int max_len, float* out,
+                                   hcgs_stream stream) {
+    HCGS_REQUIRE(chunk && beg && len && left && out, "hcgs_assemble_batch: NULL argument");
+    HCGS_REQUIRE(chunk_rows >= 0 && dim >= 1 && batch >= 1 && max_len >= 0,
+                 "hcgs_assemble_batch: bad shape (chunk_rows=%lld dim=%d batch=%d max_len=%d)", (long long)chunk_rows,
+                 dim, batch, max_len);
+    const int64_t total = (int64_t)max_len * batch * dim;
+    if (total == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    const bool vec = dim % 4 == 0 && ((uintptr_t)chunk & 15) == 0 && ((uintptr_t)out & 15) == 0;
+    const int64_t n_vec = vec ? total / 4 : total;
+    int64_t blocks = (n_vec + 255) / 256;
+    if (blocks > 148 * 8) blocks = 148 * 8;   // eight resident CTAs of 256 threads per SM, grid-stride beyond
+    if (vec)
+        assemble_batch_kernel<4><<<(unsigned)blocks, 256, 0, st>>>(chunk, chunk_rows, dim, beg, len, left, batch, n_vec, out);
+    else
+        assemble_batch_kernel<1><<<(unsigned)blocks, 256, 0, st>>>(chunk, chunk_rows, dim, beg, len, left, batch, n_vec, out);
+    HCGS_LAUNCH_CHECK();
+    return 0;
+}

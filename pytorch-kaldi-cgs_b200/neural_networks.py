@@ -121,14 +121,14 @@ def _parse_pattern_options(self, options, prefix):
 
 
 class _PlanCache:
-    """key -> native.Plan, rebuilt when the signature of the source masks changes."""
+    """key -> native.Plan, looked up again when the signature of the source masks changes.  The plans themselves live
+    in the process-wide store of b200/native.py (shared_plan), so a net rebuilt for the next chunk with the same masks
+    (core.py:107-121) finds its plans instead of rebuilding them."""
 
     def __init__(self):
         self._store = {}
 
     def clear(self):
-        for hit in self._store.values():
-            hit[1].destroy()
         self._store = {}
 
     def get(self, key, sources, build_mask, shape, recurrent):
@@ -140,10 +140,8 @@ class _PlanCache:
         hit = self._store.get(key)
         if hit is not None and hit[0] == sig:
             return hit[1], hit[2]
-        if hit is not None:
-            hit[1].destroy()
         mask = build_mask() if sources else None
-        plan = native.Plan(mask if mask is not None else torch.ones(shape), recurrent=recurrent)
+        plan = native.shared_plan(mask if mask is not None else torch.ones(shape), recurrent=recurrent)
         if mask is not None:
             mask = mask.detach().to(device=sources[0].device, dtype=torch.float32).contiguous()
         self._store[key] = (sig, plan, mask)

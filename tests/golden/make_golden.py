@@ -424,6 +424,45 @@ def gen_run_nn():
     print('run_nn_chunk.npz loss', res['loss'], 'err', res['err'], len(res['ark']), 'ark bytes', res['files'])
 
 
+def gen_chunk_batches():
+    """the minibatch tensors the reference's OWN loop (core.py:183-200) hands to forward_model for a
+    synthetic chunk -- random left padding drawn from Python's `random` after core.run_nn's random.seed(seed) -- and the
+    next random.random() after the chunk (position of the stream).  oracle/chunk_oracle.py and the device assembly
+    (b200/chunk.py, hcgs_assemble_batch) are compared with these."""
+    import random
+    sys.path.insert(0, os.path.join(os.path.dirname(HERE)))
+    import ref_harness as rh
+    import core as ref_core
+    rh.cpu_shims(sys.modules)
+    a = [dict(LSTM_OPTS), dict(MLP_OPTS), dict(MLP_OPTS, arch_name='MLP_layers2', dnn_lay='5', mlp_hcgs='False',
+                                                arch_lr='0.0004')]
+    out = {}
+    for tag, n_snt, bs in (('a', 7, 2), ('b', 9, 4), ('c', 5, 1)):
+        chunk = rh.synthetic_chunk(n_snt=n_snt, seed=20 + n_snt)
+        seen = []
+        orig = ref_core.forward_model
+
+        def rec(fea_dict, lab_dict, arch_dict, model, nns, costs, inp, *rest):
+            seen.append(inp.detach().clone().numpy())
+            return orig(fea_dict, lab_dict, arch_dict, model, nns, costs, inp, *rest)
+        ref_core.forward_model = rec
+        try:
+            work = tempfile.mkdtemp()
+            rh.patch_read_lab_fea(ref_core, chunk)
+            cfg = os.path.join(work, 'train_chunk.cfg')
+            rh.write_chunk_cfg(cfg, 'train', work, a, False, seed=2234, batch_size=bs)
+            ref_core.run_nn(None, None, None, None, None, None, cfg, True, cfg)
+            nxt = random.random()
+        finally:
+            ref_core.forward_model = orig
+        out['%s/n_snt' % tag] = np.array([n_snt, bs, 20 + n_snt])
+        out['%s/next_random' % tag] = np.array([nxt])
+        for i, x in enumerate(seen):
+            out['%s/inp%d' % (tag, i)] = x
+        print('chunk_batches', tag, [x.shape for x in seen], nxt)
+    np.savez_compressed(os.path.join(HERE, 'chunk_batches.npz'), **out)
+
+
 if __name__ == '__main__':
     if len(sys.argv) > 1:
         for name in sys.argv[1:]:
