@@ -172,7 +172,11 @@ int hcgs_layernorm_bwd(const float* dy, int64_t lddy, const float* x, int64_t ld
  *   pre [T,B,4H] (column g*H+u), drop [B,H] or NULL (then drop_scalar is used, eval mode),
  *   h_out [T,B,H]; c_out [T,B,H] and gates_out [T,B,4H] (post-activation f,i,o,g) are saved for
  *   the backward when non-NULL.  act_bits>0 enables the per-step Quantize_inp of h
- *   (quantized_modules.py:212/219 through QuantizeLinear on h_t, 4 applications per step).
+ *   (quantized_modules.py:212/219 through QuantizeLinear on h_t, 4 applications per step).  Its scale is the
+ *   max |h_t| over the WHOLE batch (quantized_modules.py:104-108): with more than 8 sequences the clusters exchange
+ *   their maxima once per time step through a static device scratch, so every cluster must be resident at the same
+ *   time -- the call fails with the limit in hcgs_last_error() when batch exceeds 8 x the co-resident clusters -- and
+ *   only one such launch may run on a device at a time.
  * hcgs_lstm_bwd: BPTT of the same loop; dh_out [T,B,H] is the gradient arriving from above,
  *   dpre [T,B,4H] the gradient w.r.t. the gate pre-activations.                  */
 int hcgs_lstm_pack(const hcgs_plan* plan, const float* const* u, int ldu, float* fwd_pack,

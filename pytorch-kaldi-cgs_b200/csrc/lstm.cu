@@ -67,8 +67,23 @@ struct LstmFwdArgs {
     float* c_out;
     float* gates_out;
     int T, B, H, CL, Hc, HcP, RG, L, NCG, act, w_in_smem;
-    int act_bits;  // > 0: Quantize_inp of h_{k-1} before the four recurrent products of step k (whole batch in ONE cluster)
+    int act_bits;  // > 0: Quantize_inp of h_{k-1} before the four recurrent products of step k
+    // act_bits > 0 with more than one cluster: the scale is the max |h| over the WHOLE batch, so the clusters exchange
+    // their maxima once per time step through q_sync = {slot[3], arrivals} in global memory (all clusters co-resident,
+    // checked by the launcher)
+    unsigned int* q_sync;
+    int n_groups;
 };
+
+__device__ __forceinline__ unsigned int ld_acquire_gpu(const unsigned int* p) {
+    unsigned int v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// static scratch of the grid-wide scale exchange: one quantised recurrence runs on a device at a time (it needs every
+// cluster co-resident, so two could not overlap anyway)
+__device__ unsigned int g_q_sync[4];
 
 __global__ void __launch_bounds__(512) lstm_fwd_kernel(const LstmFwdArgs a) {
     cg::cluster_group cluster = cg::this_cluster();
@@ -141,6 +156,7 @@ __global__ void __launch_bounds__(512) lstm_fwd_kernel(const LstmFwdArgs a) {
     const int chunks = Hc * NB / 4;  // float4 chunks of one h slice
 
     __shared__ float q_red[16];
+    __shared__ float q_glob;
     const float q_scale = (float)(1 << (a.act_bits > 0 ? a.act_bits - 1 : 0)), q_inv = 1.0f / q_scale;
 
     for (int k = 0; k < a.T; ++k) {
@@ -159,6 +175,29 @@ __global__ void __launch_bounds__(512) lstm_fwd_kernel(const LstmFwdArgs a) {
             __syncthreads();
             float var = 0.f;
             for (int w = 0; w < (nthreads + 31) / 32; ++w) var = fmaxf(var, q_red[w]);
+            if (a.n_groups > 1) {
+                // max over all clusters.  Step k uses slot k % 3; cluster 0 clears the slot of step k + 1 before it
+                // arrives (every cluster read that slot at step k - 2, i.e. before it arrived at step k - 1, and
+                // nobody writes it before this step's arrivals are complete).  |h| >= 0: the float bits order like
+                // unsigned integers.
+                if (t == 0) {
+                    if (rank == 0) {
+                        if (group == 0) *reinterpret_cast<volatile unsigned int*>(a.q_sync + (k + 1) % 3) = 0u;
+                        atomicMax(a.q_sync + k % 3, __float_as_uint(var));
+                        __threadfence();
+                        atomicAdd(a.q_sync + 3, 1u);
+                    }
+                    const unsigned int target = (unsigned int)k * (unsigned int)a.n_groups;
+                    unsigned int spins = 0;
+                    while (ld_acquire_gpu(a.q_sync + 3) < target) {
+                        if (++spins > (1u << 24)) __trap();   // a cluster that is not resident: fail, do not hang
+                        __nanosleep(32);
+                    }
+                    q_glob = __uint_as_float(ld_acquire_gpu(a.q_sync + k % 3));
+                }
+                __syncthreads();
+                var = q_glob;
+            }
             if (var != 0.f) {
                 for (int i = t; i < H4 * NB; i += nthreads) {
                     float v = hq[i];
@@ -502,6 +541,27 @@ static int launch_cluster(void (*kernel)(const Args), const Args& args, int n_cl
     return 0;
 }
 
+template <typename Args>
+static int max_resident_clusters(void (*kernel)(const Args), int CL, int threads, size_t smem, int* out) {
+    HCGS_CHECK_CUDA(cudaFuncSetAttribute((const void*)kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (CL > 8)
+        HCGS_CHECK_CUDA(cudaFuncSetAttribute((const void*)kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3((unsigned)CL, 1, 1);
+    cfg.blockDim = dim3((unsigned)threads, 1, 1);
+    cfg.dynamicSmemBytes = smem;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = (unsigned)CL;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    HCGS_CHECK_CUDA(cudaOccupancyMaxActiveClusters(out, kernel, &cfg));
+    return 0;
+}
+
 }  // namespace hcgs
 
 using namespace hcgs;
@@ -534,9 +594,6 @@ extern "C" int hcgs_lstm_fwd(const hcgs_plan* plan, const float* fwd_pack, const
     HCGS_REQUIRE(plan && plan->recurrent, "hcgs_lstm_fwd: needs a recurrent plan");
     HCGS_REQUIRE(fwd_pack && pre && h_out, "hcgs_lstm_fwd: NULL argument");
     HCGS_REQUIRE(act_bits >= 0 && act_bits <= 24, "hcgs_lstm_fwd: act_bits out of range");
-    HCGS_REQUIRE(act_bits == 0 || batch <= NB,
-                 "hcgs_lstm_fwd: Quantize_inp of h_t scales by the max over the WHOLE batch; that is built for a batch that "
-                 "fits one cluster (<= %d sequences, the cfg batch size), got %d", NB, batch);
     if (t_len <= 0 || batch <= 0) return 0;
     const RecurrentPlan& rp = plan->rp;
     HCGS_REQUIRE(rp.Hc * NB <= IPT * rp.threads, "hcgs_lstm_fwd: internal sizing error");
@@ -562,6 +619,21 @@ extern "C" int hcgs_lstm_fwd(const hcgs_plan* plan, const float* fwd_pack, const
     a.w_in_smem = rp.w_in_smem ? 1 : 0;
     a.act_bits = act_bits;
     const int n_clusters = (batch + NB - 1) / NB;
+    a.n_groups = n_clusters;
+    a.q_sync = nullptr;
+    if (act_bits > 0 && n_clusters > 1) {
+        // Quantize_inp of h_t scales by the max over the WHOLE batch (quantized_modules.py:104-108): the clusters meet
+        // once per time step, which needs all of them on the GPU at the same time
+        int resident = 0;
+        if (int rc = max_resident_clusters(lstm_fwd_kernel, rp.CL, rp.threads, rp.smem_fwd, &resident)) return rc;
+        HCGS_REQUIRE(n_clusters <= resident,
+                     "hcgs_lstm_fwd: Quantize_inp of h_t needs the whole batch co-resident: %d sequences = %d clusters of %d "
+                     "CTAs, this GPU holds %d clusters (<= %d sequences)", batch, n_clusters, rp.CL, resident, resident * NB);
+        void* sym = nullptr;
+        HCGS_CHECK_CUDA(cudaGetSymbolAddress(&sym, g_q_sync));
+        a.q_sync = static_cast<unsigned int*>(sym);
+        HCGS_CHECK_CUDA(cudaMemsetAsync(sym, 0, 4 * sizeof(unsigned int), (cudaStream_t)stream));
+    }
     return launch_cluster(lstm_fwd_kernel, a, n_clusters, rp.CL, rp.threads, rp.smem_fwd, (cudaStream_t)stream);
 }
 

@@ -201,6 +201,49 @@ def test_recurrent_kernels(H, B, T, blocks, drops, act, cl):
     plan.destroy()
 
 
+@pytest.mark.parametrize('H,B,T,blocks,drops', [(24, 75, 9, [8, 4], [50, 50]), (550, 100, 6, [32, 4], [75, 62.5]),
+                                                 (550, 8, 6, [32, 4], [75, 62.5])])
+def test_recurrent_quantised_h_scale_spans_clusters(H, B, T, blocks, drops):
+    """act_bits: Quantize_inp of h_t scales by max |h_t| over the WHOLE [B, H] tensor (quantized_modules.py:104-108).
+    A cluster of the kernel holds 8 sequences, so for B > 8 the clusters exchange their maxima at every step.  With 4
+    bits the stored h_t (t < T - 1: the reference's `.data` swap) must lie on the grid j * var_t / 8 of the GLOBAL
+    var_t = max over all sequences, and that maximum is itself a grid point; the sequences are scaled so that the
+    per-cluster maxima differ by up to 20x (a per-cluster scale would put the quiet clusters off the global grid)."""
+    from b200 import native
+    torch.manual_seed(B)
+    mask = random_mask(H, H, blocks, drops, 3)
+    plan = native.Plan(mask, recurrent=True)
+    d = dev()
+    us = [(torch.randn(H, H) * (1.5 / np.sqrt(max(mask.sum(1).mean().item(), 1.0))) * mask).to(d) for _ in range(4)]
+    pre = torch.randn(T, B, 4 * H) * torch.linspace(0.05, 1.0, B).view(1, B, 1)
+    fp = torch.empty(plan.fwd_pack_floats, device=d)
+    native.lstm_pack(plan, us, fp, None)
+    h = torch.empty(T, B, H, device=d)
+    native.lstm_fwd(plan, fp, pre.to(d), None, 1.0, native.ACT_CODES['tanh'], h, None, None, act_bits=4)
+    torch.cuda.synchronize()
+    h = h.cpu()
+    assert torch.isfinite(h).all()
+    for t in range(T - 1):
+        var = h[t].abs().max()
+        assert var > 0
+        r = h[t].abs().double() * 8 / var.double()
+        off = (r - r.round()).abs().max().item()
+        assert off <= 1e-4, 'step %d: stored h is not on the grid of the whole-batch scale (off by %.3e levels)' % (t, off)
+        if B > 8:
+            quiet = h[t, :8].abs().max()
+            assert quiet < 0.7 * var                    # the first cluster alone would have chosen another scale
+    # the last step is never re-quantised (nothing consumes it inside the loop)
+    r = h[T - 1].abs().double() * 8 / h[T - 1].abs().max().double()
+    assert (r - r.round()).abs().max().item() > 1e-2
+    if H == 550:
+        big = 8 * 19                                     # 19 clusters of 8 CTAs do not fit 148 SMs
+        pre2 = torch.zeros(2, big, 4 * H, device=d)
+        with pytest.raises(native.NativeError, match='co-resident'):
+            native.lstm_fwd(plan, fp, pre2, None, 1.0, native.ACT_CODES['tanh'], torch.empty(2, big, H, device=d), None,
+                            None, act_bits=4)
+    plan.destroy()
+
+
 def test_recurrent_dense_masks():
     """No HCGS (lstm_hcgs=False): the all-ones mask is just a very wide block list.  It runs while the
     compressed state fits the cluster's shared memory and is refused loudly (no silent fallback) beyond."""

@@ -298,11 +298,45 @@ def test_quantised_activations_and_pruning_train_step_matches_reference_fixture(
         w0 = torch.from_numpy(g['init/LSTM_layers/' + k]) * hm
         m = hm * model_oracle.prune_t(w0, 70)[1]
         close(dict(lstm.named_parameters())[k].grad.cpu() * m, torch.from_numpy(g['grad/LSTM_layers/' + k]) * m, 2e-4, k)
-    # a batch that does not fit one cluster cannot take the whole-tensor scale of Quantize_inp: loud error
+    # a batch whose clusters cannot all be resident cannot take the whole-tensor scale of Quantize_inp: loud error
     from b200 import native
-    big = torch.zeros(T, 9, D + 2).cuda()
-    with pytest.raises(native.NativeError):
-        graph.forward(big, T, 9, 'train', ['out_dnn2'])
+    big = torch.zeros(2, 8 * 1000, D + 2).cuda()
+    with pytest.raises(native.NativeError, match='co-resident'):
+        graph.forward(big, 2, 8 * 1000, 'train', ['out_dnn2'])
+
+
+@pytest.mark.parametrize('T,B', [(12, 20), (40, 75)])
+def test_quantised_model_runs_with_a_batch_spanning_clusters(T, B):
+    """The QuantExp options (8-bit weights, 16-bit Quantize_inp of layer inputs and of h_t per step) with more than 8
+    sequences: the per-step scale of h_t is the max over the whole batch, exchanged between the clusters of the recurrent
+    kernel (kernel-level proof: test_recurrent_quantised_h_scale_spans_clusters).  Against the oracle the comparison is
+    in quantisation levels, not in fp32 ulps: Quantize_inp rounds with `ceil` and is applied four times in a row, so an
+    input on a level boundary moves a full level (max|x| / 2^15) with the last bit of the scale -- CPU and GPU sums differ
+    in that bit.  Tolerance: 20 levels on the LSTM output, 1e-3 on loss and log-posteriors."""
+    from oracle import model_oracle
+    D = 12
+    lo = dict(lstm_quant='True', lstm_quant_inp='True')
+    mo = dict(mlp_quant='True', mlp_quant_inp='True')
+    nets, _ = build_product_nets('train', D=D, seed=6, lstm_over=lo, mlp_over=mo, device='cuda')
+    params = _state_to_cpu(nets)
+    gen = torch.Generator().manual_seed(T)
+    inp = torch.zeros(T, B, D + 2)
+    inp[:, :, :D] = torch.randn(T, B, D, generator=gen)
+    inp[:, :, D] = torch.randint(0, 10, (T, B), generator=gen).float()
+    inp[:, :, D + 1] = torch.randint(0, 5, (T, B), generator=gen).float()
+    drops = [torch.bernoulli(torch.full((B, 24), 0.8), generator=gen) for _ in range(2)]
+    specs = golden_specs(quant=True, quant_inp=16)
+    with torch.no_grad():
+        ref = model_oracle.model_forward(params, specs, inp, D, True, drops)
+    graph = make_graph(nets, D)
+    with _ReplayBernoulli(drops):
+        out = graph.forward(inp.cuda(), T, B, 'train', ['out_dnn2'])
+    out['loss_final'].backward()
+    assert abs(out['loss_final'].item() - ref['loss_final'].item()) <= 1e-3 * abs(ref['loss_final'].item())
+    err = (out['out_dnn1'].reshape(T, B, -1).detach().cpu() - ref['out_dnn1']).abs().max().item()
+    assert err <= 20 * ref['out_dnn1'].abs().max().item() / 2 ** 15, err
+    close(out['out_dnn2'], ref['out_dnn2'], 1e-3, 'log-posteriors')
+    assert all(torch.isfinite(p.grad).all() for n in nets.values() for p in n.parameters() if p.grad is not None)
 
 
 def test_input_norms_and_layernorm_train_steps_match_reference_fixture():
