@@ -187,6 +187,23 @@ int hcgs_lstm_fwd(const hcgs_plan* plan, const float* fwd_pack, const float* pre
 int hcgs_lstm_bwd(const hcgs_plan* plan, const float* bwd_pack, const float* dh_out,
                   const float* gates, const float* c, const float* drop, float drop_scalar, int act,
                   int t_len, int batch, float* dpre, hcgs_stream stream);
+/* LayerNorm of h_t INSIDE the time loop (lstm_use_laynorm: neural_networks.py:1092-1095 with the reference's own class at
+ * :40-51 -- gamma * (h - mean) / (std + eps) + beta over the H units of a sequence, UNBIASED std).  The normalised h_t is
+ * what the next step's U h product, Quantize_inp (act_bits) and the layer output see.  Each cluster normalises its 8
+ * sequences on the gathered h_t; the backward takes dh through the LayerNorm backward at every step (two cluster-wide sums
+ * per sequence) before the gate derivatives.
+ * hcgs_lstm_fwd_ln: hcgs_lstm_fwd + ln_gamma / ln_beta [H], ln_eps; ln_stats [T,B,2] = {mean, std + eps} (NULL when no
+ *   backward follows).
+ * hcgs_lstm_bwd_ln: hcgs_lstm_bwd + the same gamma / stats / eps; ln_dgamma / ln_dbeta: [ceil(B/8)][H] partial parameter
+ *   gradients, one row per cluster (deterministic; the caller sums the rows).                                        */
+int hcgs_lstm_fwd_ln(const hcgs_plan* plan, const float* fwd_pack, const float* pre, const float* drop,
+                     float drop_scalar, int act, int t_len, int batch, float* h_out, float* c_out, float* gates_out,
+                     int act_bits, const float* ln_gamma, const float* ln_beta, float ln_eps, float* ln_stats,
+                     hcgs_stream stream);
+int hcgs_lstm_bwd_ln(const hcgs_plan* plan, const float* bwd_pack, const float* dh_out, const float* gates,
+                     const float* c, const float* drop, float drop_scalar, int act, int t_len, int batch, float* dpre,
+                     const float* ln_gamma, const float* ln_stats, float ln_eps, float* ln_dgamma, float* ln_dbeta,
+                     hcgs_stream stream);
 
 /* ---- persistent recurrent kernels of the GRU family (fp32 build) ----------------------------
  * One kernel pair for the four gated / plain cells of the toolkit.  The reference has them dense only

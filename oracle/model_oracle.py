@@ -179,6 +179,10 @@ def lstm_forward(p, spec, x, drop_masks, training):
             ot = torch.sigmoid(pre['o'][k] + linear(hq, u['o'], None, bfo))
             ct = it * act(a, pre['c'][k] + linear(hq, u['c'], None, bfo)) * drop + ft * ct
             ht = ot * act(a, ct)
+            if spec.get('use_ln', None) and spec['use_ln'][i]:            # :1092-1095 with the reference's class :40-51
+                mean = ht.mean(-1, keepdim=True)
+                std = ht.std(-1, keepdim=True)                            # unbiased
+                ht = p['ln.%d.gamma' % i] * (ht - mean) / (std + 1e-6) + p['ln.%d.beta' % i]
             hs.append(ht)
         x = torch.stack(hs)                                               # :1100
         if bidir:

@@ -34,6 +34,7 @@ class LayerRuntime:
         # quantised weights, the gradient lands on the fp32 master -- straight-through)
         self.q_ws = None
         self.q_us = None
+        self.ln_eps = 1e-6        # eps of the in-loop LayerNorm (lstm_use_laynorm)
         self.act_bits = 0         # > 0: per-step Quantize_inp of h_t inside the recurrence (lstm_quant_inp)
         self.cell = None          # GRU family: 'gru' | 'minimalgru' | 'ligru' | 'rnn'
         # tensor-core build: bf16 copy of the layer input handed over by the previous layer, and of
@@ -150,7 +151,7 @@ class LSTMLayerFunction(torch.autograd.Function):
     """One HCGS LSTM layer: projections -> BN -> persistent recurrence (neural_networks.py:950-1100)."""
 
     @staticmethod
-    def forward(ctx, x, wf, wi, wo, wc, uf, ui, uo, uc, gf, bf, gi, bi, go, bo, gc, bc, rt):
+    def forward(ctx, x, wf, wi, wo, wc, uf, ui, uo, uc, gf, bf, gi, bi, go, bo, gc, bc, rt, lng, lnb):
         T, B, D = x.shape
         H = wf.shape[0]
         M = T * B
@@ -183,16 +184,24 @@ class LSTMLayerFunction(torch.autograd.Function):
         if need_grad:
             c = torch.empty(T, B, H, device=dev, dtype=torch.float32)
             gates = torch.empty(T, B, 4 * H, device=dev, dtype=torch.float32)
-        native.lstm_fwd(plan, fwd_pack, pre.view(T, B, 4 * H), rt.drop, rt.drop_scalar, rt.act, h, c, gates,
-                        act_bits=rt.act_bits)
+        ln_stats = None
+        if lng is not None:
+            # LayerNorm of h_t inside the time loop (lstm_use_laynorm, neural_networks.py:1092-1095)
+            ln_stats = torch.empty(T, B, 2, device=dev, dtype=torch.float32) if need_grad else None
+            native.lstm_fwd_ln(plan, fwd_pack, pre.view(T, B, 4 * H), rt.drop, rt.drop_scalar, rt.act, h, c, gates,
+                               rt.act_bits, lng.detach().contiguous(), lnb.detach().contiguous(), rt.ln_eps, ln_stats)
+        else:
+            native.lstm_fwd(plan, fwd_pack, pre.view(T, B, 4 * H), rt.drop, rt.drop_scalar, rt.act, h, c, gates,
+                            act_bits=rt.act_bits)
         if need_grad:
             ctx.rt = rt
             ctx.dims = (T, B, D, H)
             ctx.drop = rt.drop
             ctx.drop_scalar = rt.drop_scalar
             ctx.h_store = h.detach()   # private alias: survives a later `.data =` swap on the output
+            ctx.ln = lng is not None
             ctx.save_for_backward(x2d, ws[0], ws[1], ws[2], ws[3], gf, gi, go, gc, pre_raw, save_mean,
-                                  save_invstd, c, gates, bwd_pack)
+                                  save_invstd, c, gates, bwd_pack, lng, ln_stats)
         return h
 
     @staticmethod
@@ -200,11 +209,17 @@ class LSTMLayerFunction(torch.autograd.Function):
         rt = ctx.rt
         T, B, D, H = ctx.dims
         M = T * B
-        (x2d, wf, wi, wo, wc, gf, gi, go, gc, pre_raw, save_mean, save_invstd, c, gates, bwd_pack) = ctx.saved_tensors
+        (x2d, wf, wi, wo, wc, gf, gi, go, gc, pre_raw, save_mean, save_invstd, c, gates, bwd_pack, lng,
+         ln_stats) = ctx.saved_tensors
         dev = dh.device
         dh = dh.contiguous()
         dpre = torch.empty(T, B, 4 * H, device=dev, dtype=torch.float32)
-        native.lstm_bwd(rt.plan_h, bwd_pack, dh, gates, c, ctx.drop, ctx.drop_scalar, rt.act, dpre)
+        dlng = dlnb = None
+        if ctx.ln:
+            dlng, dlnb = native.lstm_bwd_ln(rt.plan_h, bwd_pack, dh, gates, c, ctx.drop, ctx.drop_scalar, rt.act, dpre,
+                                            lng.detach().contiguous(), ln_stats, rt.ln_eps)
+        else:
+            native.lstm_bwd(rt.plan_h, bwd_pack, dh, gates, c, ctx.drop, ctx.drop_scalar, rt.act, dpre)
         dpre2d = dpre.view(M, 4 * H)
         dgam = [None] * 4
         dbet = [None] * 4
@@ -229,7 +244,7 @@ class LSTMLayerFunction(torch.autograd.Function):
             native.bsgemm_nn(rt.plan_x, [wf, wi, wo, wc], dproj, dx2d)
             dx = dx2d.view(T, B, D)
         return (dx, dws[0], dws[1], dws[2], dws[3], dus[0], dus[1], dus[2], dus[3],
-                dgam[0], dbet[0], dgam[1], dbet[1], dgam[2], dbet[2], dgam[3], dbet[3], None)
+                dgam[0], dbet[0], dgam[1], dbet[1], dgam[2], dbet[2], dgam[3], dbet[3], None, dlng, dlnb)
 
 
 class GatedRNNLayerFunction(torch.autograd.Function):

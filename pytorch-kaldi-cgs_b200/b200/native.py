@@ -64,6 +64,10 @@ SIGNATURES = {
     'hcgs_lstm_pack': (c_int, [c_void_p, _pp, c_int, _f, _f, c_void_p]),
     'hcgs_lstm_fwd': (c_int, [c_void_p, _f, _f, _f, c_float, c_int, c_int, c_int, _f, _f, _f, c_int, c_void_p]),
     'hcgs_lstm_bwd': (c_int, [c_void_p, _f, _f, _f, _f, _f, c_float, c_int, c_int, c_int, _f, c_void_p]),
+    'hcgs_lstm_fwd_ln': (c_int, [c_void_p, _f, _f, _f, c_float, c_int, c_int, c_int, _f, _f, _f, c_int, _f, _f, c_float,
+                                 _f, c_void_p]),
+    'hcgs_lstm_bwd_ln': (c_int, [c_void_p, _f, _f, _f, _f, _f, c_float, c_int, c_int, c_int, _f, _f, _f, c_float, _f, _f,
+                                 c_void_p]),
     'hcgs_gru_fwd': (c_int, [c_void_p, c_int, _f, _f, _f, c_float, c_int, c_int, c_int, _f, _f, _f, c_void_p]),
     'hcgs_gru_bwd': (c_int, [c_void_p, c_int, _f, _f, _f, _f, _f, c_float, c_int, c_int, c_int, _f, c_void_p]),
     'hcgs_lstm_tc_info': (c_int, [c_void_p, c_int, c_int, POINTER(c_int64)]),
@@ -123,7 +127,7 @@ def load():
 # kernels launched by each entry point (our own kernels only; memsets are not counted)
 KERNELS_PER_CALL = {'hcgs_mask_apply': 1, 'hcgs_quantize_w': 1, 'hcgs_quantize_act': 2, 'hcgs_bsgemm_nt': 1,
                     'hcgs_bsgemm_nn': 1, 'hcgs_bs_sddmm': 1, 'hcgs_colsum': 1, 'hcgs_bn_fwd': 3, 'hcgs_bn_fwd_static': 3, 'hcgs_bn_bwd': 2, 'hcgs_bn_fwd_il': 3, 'hcgs_bn_bwd_il': 2, 'hcgs_bn_stats_il': 1,
-                    'hcgs_lstm_pack': 2, 'hcgs_lstm_fwd': 1, 'hcgs_lstm_bwd': 1, 'hcgs_gru_fwd': 1, 'hcgs_gru_bwd': 1,
+                    'hcgs_lstm_pack': 2, 'hcgs_lstm_fwd': 1, 'hcgs_lstm_bwd': 1, 'hcgs_lstm_fwd_ln': 1, 'hcgs_lstm_bwd_ln': 1, 'hcgs_gru_fwd': 1, 'hcgs_gru_bwd': 1,
                     'hcgs_lstm_tc_pack': 2, 'hcgs_lstm_tc_fwd': 1, 'hcgs_lstm_tc_bwd': 1,
                     'hcgs_tc_pack_nt': 1, 'hcgs_tc_gemm_nt': 1, 'hcgs_cast_bf16': 1,
                     'hcgs_tc_pack_nt_split': 1, 'hcgs_tc_gemm_nt_split': 1, 'hcgs_split_bf16': 1,
@@ -431,6 +435,37 @@ def lstm_bwd(plan, bwd_pack, dh_out, gates, c, drop, drop_scalar, act, dpre):
     assert dh_out.is_contiguous() and gates.is_contiguous() and c.is_contiguous() and dpre.is_contiguous()
     _check(load().hcgs_lstm_bwd(plan.handle, _ptr(bwd_pack), _ptr(dh_out), _ptr(gates), _ptr(c), _ptr(drop),
                                 float(drop_scalar), int(act), T, B, _ptr(dpre), _stream()), 'hcgs_lstm_bwd')
+
+
+def lstm_fwd_ln(plan, fwd_pack, pre, drop, drop_scalar, act, h_out, c_out, gates_out, act_bits, gamma, beta, eps,
+                stats=None):
+    """lstm_fwd with the reference's LayerNorm of h_t inside the time loop; stats [T,B,2] = {mean, std + eps}."""
+    _require_cuda(fwd_pack, pre, drop, h_out, c_out, gates_out, gamma, beta, stats)
+    T, B = pre.shape[0], pre.shape[1]
+    H = plan.n_out
+    assert pre.is_contiguous() and h_out.is_contiguous() and pre.shape[2] == 4 * H
+    assert gamma.is_contiguous() and beta.is_contiguous() and gamma.numel() == H and beta.numel() == H
+    for t, shape in ((c_out, (T, B, H)), (gates_out, (T, B, 4 * H)), (stats, (T, B, 2))):
+        assert t is None or (t.is_contiguous() and tuple(t.shape) == shape)
+    _check(load().hcgs_lstm_fwd_ln(plan.handle, _ptr(fwd_pack), _ptr(pre), _ptr(drop), float(drop_scalar), int(act), T, B,
+                                   _ptr(h_out), _ptr(c_out), _ptr(gates_out), int(act_bits), _ptr(gamma), _ptr(beta),
+                                   float(eps), _ptr(stats), _stream()), 'hcgs_lstm_fwd_ln')
+
+
+def lstm_bwd_ln(plan, bwd_pack, dh_out, gates, c, drop, drop_scalar, act, dpre, gamma, stats, eps):
+    """lstm_bwd through the in-loop LayerNorm; returns (dgamma, dbeta) [H]."""
+    _require_cuda(bwd_pack, dh_out, gates, c, drop, dpre, gamma, stats)
+    T, B = dh_out.shape[0], dh_out.shape[1]
+    H = plan.n_out
+    assert dh_out.is_contiguous() and gates.is_contiguous() and c.is_contiguous() and dpre.is_contiguous()
+    assert stats.is_contiguous() and tuple(stats.shape) == (T, B, 2) and gamma.is_contiguous() and gamma.numel() == H
+    groups = (B + 7) // 8
+    dg = torch.empty(groups, H, device=dpre.device, dtype=torch.float32)
+    db = torch.empty(groups, H, device=dpre.device, dtype=torch.float32)
+    _check(load().hcgs_lstm_bwd_ln(plan.handle, _ptr(bwd_pack), _ptr(dh_out), _ptr(gates), _ptr(c), _ptr(drop),
+                                   float(drop_scalar), int(act), T, B, _ptr(dpre), _ptr(gamma), _ptr(stats), float(eps),
+                                   _ptr(dg), _ptr(db), _stream()), 'hcgs_lstm_bwd_ln')
+    return dg.sum(0), db.sum(0)
 
 
 CELL_CODES = {'gru': 0, 'minimalgru': 1, 'ligru': 2, 'rnn': 3}

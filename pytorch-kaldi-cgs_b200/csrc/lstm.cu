@@ -28,6 +28,7 @@ namespace hcgs {
 
 constexpr int NB = 8;   // sequences per cluster
 constexpr int IPT = 2;  // pointwise items (unit, sequence) per thread
+constexpr size_t kLnScratchBytes = 2048;   // 2 x NB floats + 16 x NB x 2 floats (clusters of up to 16 CTAs)
 
 __host__ __device__ static inline size_t align16(size_t x) { return (x + 15) & ~(size_t)15; }
 
@@ -40,6 +41,7 @@ size_t lstm_fwd_smem_bytes(int H, int CL, int Hc, int HcP, int L, bool w_in_smem
     b += align16((size_t)2 * H4 * NB * 4);
     b += align16((size_t)4 * NB * HcP * 4);
     b += align16((size_t)Hc * NB * 4);
+    b += kLnScratchBytes;   // LayerNorm of h_t: per-sequence mean / denominator
     (void)CL;
     return b;
 }
@@ -53,6 +55,7 @@ size_t lstm_bwd_smem_bytes(int H, int CL, int Hc, int max_blocks, int n_colgroup
     b += align16((size_t)4 * Hc * NB * 4);          // dpre_s
     b += align16((size_t)max_blocks * 32 * 4);      // contrib
     b += align16((size_t)2 * CL * Hc * NB * 4);     // slots
+    b += kLnScratchBytes;                           // LayerNorm backward: statistics + cluster-wide sums [CL][NB][2]
     (void)H;
     return b;
 }
@@ -73,6 +76,14 @@ struct LstmFwdArgs {
     // checked by the launcher)
     unsigned int* q_sync;
     int n_groups;
+    // LayerNorm of h_t inside the time loop (lstm_use_laynorm, neural_networks.py:1092-1095 with the class at :40-51):
+    // h_t <- gamma * (h_t - mean) / (std + eps) + beta over the H units of every sequence, unbiased std; the normalised
+    // h_t is what the next step's U h product and the layer output see.  ln_stats [T,B,2] = {mean, std + eps} for the
+    // backward (may be NULL).
+    const float* ln_gamma;
+    const float* ln_beta;
+    float ln_eps;
+    float* ln_stats;
 };
 
 __device__ __forceinline__ unsigned int ld_acquire_gpu(const unsigned int* p) {
@@ -111,6 +122,9 @@ __global__ void __launch_bounds__(512) lstm_fwd_kernel(const LstmFwdArgs a) {
     float* gbuf = reinterpret_cast<float*>(sp);
     sp += align16((size_t)4 * NB * HcP * 4);
     float* stage = reinterpret_cast<float*>(sp);
+    sp += align16((size_t)Hc * NB * 4);
+    float* ln_mu = reinterpret_cast<float*>(sp);   // [NB] mean, [NB] std + eps
+    float* ln_den = ln_mu + NB;
 
     // ---- one-time load of the resident weights and index -----------------------------------
     const float* wsrc = a.wpack + (size_t)rank * L * RG * 64;
@@ -159,9 +173,48 @@ __global__ void __launch_bounds__(512) lstm_fwd_kernel(const LstmFwdArgs a) {
     __shared__ float q_glob;
     const float q_scale = (float)(1 << (a.act_bits > 0 ? a.act_bits - 1 : 0)), q_inv = 1.0f / q_scale;
 
+    // LayerNorm of the gathered h of time step `step`, in place on this CTA's copy hq [H4][NB]; every CTA of the cluster
+    // normalises its own copy (same arithmetic, same result) and stores the rows of the units it owns.
+    auto layer_norm_h = [&](float* hq, int step) {
+        const int w = t >> 5, lane = t & 31;
+        for (int b = w; b < NB; b += nthreads >> 5) {
+            float mu = 0.f, den = 1.f;
+            if (b < nb) {
+                float sum = 0.f;
+                for (int u = lane; u < H; u += 32) sum += hq[u * NB + b];
+                mu = warp_sum(sum) / (float)H;
+                float q = 0.f;
+                for (int u = lane; u < H; u += 32) {
+                    const float d = hq[u * NB + b] - mu;
+                    q = fmaf(d, d, q);
+                }
+                den = sqrtf(warp_sum(q) / (float)(H - 1)) + a.ln_eps;
+            }
+            if (lane == 0) {
+                ln_mu[b] = mu;
+                ln_den[b] = den;
+                if (rank == 0 && b < nb && a.ln_stats) {
+                    float* st = a.ln_stats + ((size_t)step * a.B + b0 + b) * 2;
+                    st[0] = mu;
+                    st[1] = den;
+                }
+            }
+        }
+        __syncthreads();
+        for (int i = t; i < H * NB; i += nthreads) {
+            const int u = i / NB, b = i - u * NB;
+            if (b >= nb) continue;
+            const float v = __ldg(a.ln_gamma + u) * (hq[i] - ln_mu[b]) / ln_den[b] + __ldg(a.ln_beta + u);
+            hq[i] = v;
+            if (u >= u0 && u < u0 + nu) a.h_out[((size_t)step * a.B + b0 + b) * H + u] = v;
+        }
+        __syncthreads();
+    };
+
     for (int k = 0; k < a.T; ++k) {
         const int cur = k & 1, nxt = cur ^ 1;
         const float* hc = hbuf + (size_t)cur * H4 * NB;
+        if (a.ln_gamma && k > 0) layer_norm_h(hbuf + (size_t)cur * H4 * NB, k - 1);
         if (a.act_bits > 0 && k > 0) {
             // QuantizeLinear(if_inp_quant) on h_{k-1}: u{f,i,o,c}h each replace ht.data by Quantize_inp(ht.data)
             // (quantized_modules.py:212-219, neural_networks.py:1077-1088): scale = max |h| over the WHOLE [B,H]
@@ -261,7 +314,7 @@ __global__ void __launch_bounds__(512) lstm_fwd_kernel(const LstmFwdArgs a) {
                 hval = og * act_apply(a.act, cn);
                 const size_t row = (size_t)k * a.B + b0 + b;
                 const int u = u0 + ul;
-                a.h_out[row * H + u] = hval;
+                if (!a.ln_gamma) a.h_out[row * H + u] = hval;   // with LayerNorm the normalised row is stored later
                 if (a.c_out) a.c_out[row * H + u] = cn;
                 if (a.gates_out) {
                     float* go = a.gates_out + row * 4 * H + u;
@@ -291,6 +344,8 @@ __global__ void __launch_bounds__(512) lstm_fwd_kernel(const LstmFwdArgs a) {
         }
         cluster.sync();
     }
+    // the last step's h is normalised too (it is only an output: nothing inside the loop consumes it)
+    if (a.ln_gamma && a.T > 0) layer_norm_h(hbuf + (size_t)(a.T & 1) * H4 * NB, a.T - 1);
 }
 
 struct LstmBwdArgs {
@@ -306,6 +361,15 @@ struct LstmBwdArgs {
     float drop_scalar;
     float* dpre;                // [T,B,4H]
     int T, B, H, CL, Hc, RG, NCG, max_blocks, act, w_in_smem;
+    // LayerNorm of h_t inside the loop (forward: LstmFwdArgs::ln_*).  dh arriving at step k -- from above and from step
+    // k + 1 -- is the gradient w.r.t. the NORMALISED h_k; it is taken through the LayerNorm backward (two sums over the H
+    // units of a sequence, i.e. over the whole cluster) before the gate derivatives.  ln_stats: {mean, std + eps} of the
+    // forward; ln_dgamma / ln_dbeta: [n_groups][H] partial parameter gradients (one row per cluster, summed by the caller).
+    const float* ln_gamma;
+    const float* ln_stats;
+    float ln_eps;
+    float* ln_dgamma;
+    float* ln_dbeta;
 };
 
 __global__ void __launch_bounds__(512) lstm_bwd_kernel(const LstmBwdArgs a) {
@@ -340,6 +404,10 @@ __global__ void __launch_bounds__(512) lstm_bwd_kernel(const LstmBwdArgs a) {
     float* contrib = reinterpret_cast<float*>(sp);
     sp += align16((size_t)a.max_blocks * 32 * 4);
     float* slots = reinterpret_cast<float*>(sp);  // [2][CL][Hc][NB]
+    sp += align16((size_t)2 * CL * Hc * NB * 4);
+    float* ln_mu = reinterpret_cast<float*>(sp);   // [NB] mean, [NB] std + eps of the step being processed
+    float* ln_den = ln_mu + NB;
+    float* ln_red = ln_den + NB;                   // [CL][NB][2] per-CTA sums of g and g * (h - mean), pushed by every CTA
 
     const float* wsrc = a.wT + (size_t)blk0 * 64;
     if (a.w_in_smem) {
@@ -388,8 +456,72 @@ __global__ void __launch_bounds__(512) lstm_bwd_kernel(const LstmBwdArgs a) {
         }
     }
 
+    const bool ln = a.ln_gamma != nullptr;
+    float ln_g[IPT], acc_dg[IPT], acc_db[IPT], dh_eff[IPT];
+#pragma unroll
+    for (int it = 0; it < IPT; ++it) {
+        ln_g[it] = (ln && it_ok[it]) ? __ldg(a.ln_gamma + u0 + it_ul[it]) : 0.f;
+        acc_dg[it] = acc_db[it] = dh_eff[it] = 0.f;
+    }
+
     for (int k = a.T - 1; k >= 0; --k) {
         const int wr = k & 1, rd = wr ^ 1;
+        if (ln) {
+            // ---- LayerNorm backward of step k (y = gamma * xc / den + beta, xc = x - mean, den = std + eps, unbiased
+            // std over N = H units):  dx_i = (g_i - S1 / N) / den - xc_i * S2 / ((N - 1) * std * den^2),
+            // g = dy * gamma, S1 = sum g, S2 = sum g * xc over ALL units of the sequence (cluster-wide) ----
+            if (t < NB) {
+                const bool ok = t < nb;
+                const float* st = a.ln_stats + ((size_t)k * a.B + b0 + (ok ? t : 0)) * 2;
+                ln_mu[t] = ok ? __ldg(st) : 0.f;
+                ln_den[t] = ok ? __ldg(st + 1) : 1.f;
+            }
+            __syncthreads();
+            float xc_r[IPT], g_r[IPT];
+#pragma unroll
+            for (int it = 0; it < IPT; ++it) {
+                if (!it_in[it]) continue;
+                const int b = it_b[it], ul = it_ul[it];
+                float g = 0.f, xc = 0.f;
+                if (it_ok[it]) {
+                    float dh = p_dh[it];
+                    const float* sl = slots + ((size_t)rd * CL * Hc + ul) * NB + b;
+                    for (int src = 0; src < CL; ++src) dh += sl[(size_t)src * Hc * NB];
+                    xc = p_o[it] * act_apply(a.act, p_c[it]) - ln_mu[b];
+                    g = dh * ln_g[it];
+                    acc_db[it] += dh;
+                    acc_dg[it] = fmaf(dh, xc / ln_den[b], acc_dg[it]);
+                }
+                xc_r[it] = xc;
+                g_r[it] = g;
+                dpre_s[((size_t)0 * Hc + ul) * NB + b] = g;        // planes 0 / 1 of the dpre tile are free until the
+                dpre_s[((size_t)1 * Hc + ul) * NB + b] = g * xc;   // gate derivatives below
+            }
+            __syncthreads();
+            for (int p = t >> 5; p < NB * 2; p += nthreads >> 5) {
+                const int b = p >> 1, which = p & 1;
+                float sum = 0.f;
+                for (int ul = t & 31; ul < Hc; ul += 32) sum += dpre_s[((size_t)which * Hc + ul) * NB + b];
+                sum = warp_sum(sum);
+                if ((t & 31) == 0)
+                    for (int dst = 0; dst < CL; ++dst) cluster.map_shared_rank(ln_red, dst)[(rank * NB + b) * 2 + which] = sum;
+            }
+            cluster.sync();
+            const float n = (float)H;
+#pragma unroll
+            for (int it = 0; it < IPT; ++it) {
+                if (!it_ok[it]) continue;
+                const int b = it_b[it];
+                float s1 = 0.f, s2 = 0.f;
+                for (int src = 0; src < CL; ++src) {
+                    s1 += ln_red[(src * NB + b) * 2];
+                    s2 += ln_red[(src * NB + b) * 2 + 1];
+                }
+                const float den = ln_den[b], sd = den - a.ln_eps;
+                dh_eff[it] = (g_r[it] - s1 / n) / den - xc_r[it] * s2 / ((n - 1.f) * sd * den * den);
+            }
+            __syncthreads();   // every thread is done with planes 0 / 1 and the statistics of this step
+        }
         // ---- fused gate derivatives -------------------------------------------------------------
 #pragma unroll
         for (int it = 0; it < IPT; ++it) {
@@ -397,9 +529,12 @@ __global__ void __launch_bounds__(512) lstm_bwd_kernel(const LstmBwdArgs a) {
             const int b = it_b[it], ul = it_ul[it];
             float dpf = 0.f, dpi = 0.f, dpo = 0.f, dpg = 0.f;
             if (it_ok[it]) {
-                float dh = p_dh[it];
-                const float* sl = slots + ((size_t)rd * CL * Hc + ul) * NB + b;
-                for (int src = 0; src < CL; ++src) dh += sl[(size_t)src * Hc * NB];
+                float dh = dh_eff[it];
+                if (!ln) {
+                    dh = p_dh[it];
+                    const float* sl = slots + ((size_t)rd * CL * Hc + ul) * NB + b;
+                    for (int src = 0; src < CL; ++src) dh += sl[(size_t)src * Hc * NB];
+                }
                 const float fg = p_f[it], ig = p_i[it], og = p_o[it], gg = p_g[it];
                 const float tc = act_apply(a.act, p_c[it]);
                 const float dog = dh * tc;
@@ -478,6 +613,23 @@ __global__ void __launch_bounds__(512) lstm_bwd_kernel(const LstmBwdArgs a) {
             *reinterpret_cast<float4*>(remote + (((size_t)wr * CL + rank) * Hc + ul) * NB + bq * 4) = s4;
         }
         cluster.sync();
+    }
+    if (ln) {
+        // parameter gradients of the LayerNorm: sums over time sit in registers, the sequences of this cluster are added
+        // in a fixed order; one row per cluster, the caller adds the rows
+#pragma unroll
+        for (int it = 0; it < IPT; ++it) {
+            if (!it_in[it]) continue;
+            dpre_s[((size_t)0 * Hc + it_ul[it]) * NB + it_b[it]] = acc_dg[it];
+            dpre_s[((size_t)1 * Hc + it_ul[it]) * NB + it_b[it]] = acc_db[it];
+        }
+        __syncthreads();
+        for (int i = t; i < 2 * nu; i += nthreads) {
+            const int which = i / nu, ul = i - which * nu;
+            float sum = 0.f;
+            for (int b = 0; b < nb; ++b) sum += dpre_s[((size_t)which * Hc + ul) * NB + b];
+            (which ? a.ln_dbeta : a.ln_dgamma)[(size_t)group * H + u0 + ul] = sum;
+        }
     }
 }
 
@@ -588,9 +740,10 @@ extern "C" int hcgs_lstm_pack(const hcgs_plan* plan, const float* const* u, int 
     return 0;
 }
 
-extern "C" int hcgs_lstm_fwd(const hcgs_plan* plan, const float* fwd_pack, const float* pre, const float* drop,
-                             float drop_scalar, int act, int t_len, int batch, float* h_out, float* c_out,
-                             float* gates_out, int act_bits, hcgs_stream stream) {
+static int lstm_fwd_impl(const hcgs_plan* plan, const float* fwd_pack, const float* pre, const float* drop,
+                         float drop_scalar, int act, int t_len, int batch, float* h_out, float* c_out, float* gates_out,
+                         int act_bits, const float* ln_gamma, const float* ln_beta, float ln_eps, float* ln_stats,
+                         hcgs_stream stream) {
     HCGS_REQUIRE(plan && plan->recurrent, "hcgs_lstm_fwd: needs a recurrent plan");
     HCGS_REQUIRE(fwd_pack && pre && h_out, "hcgs_lstm_fwd: NULL argument");
     HCGS_REQUIRE(act_bits >= 0 && act_bits <= 24, "hcgs_lstm_fwd: act_bits out of range");
@@ -618,6 +771,10 @@ extern "C" int hcgs_lstm_fwd(const hcgs_plan* plan, const float* fwd_pack, const
     a.act = act;
     a.w_in_smem = rp.w_in_smem ? 1 : 0;
     a.act_bits = act_bits;
+    a.ln_gamma = ln_gamma;
+    a.ln_beta = ln_beta;
+    a.ln_eps = ln_eps;
+    a.ln_stats = ln_stats;
     const int n_clusters = (batch + NB - 1) / NB;
     a.n_groups = n_clusters;
     a.q_sync = nullptr;
@@ -637,9 +794,27 @@ extern "C" int hcgs_lstm_fwd(const hcgs_plan* plan, const float* fwd_pack, const
     return launch_cluster(lstm_fwd_kernel, a, n_clusters, rp.CL, rp.threads, rp.smem_fwd, (cudaStream_t)stream);
 }
 
-extern "C" int hcgs_lstm_bwd(const hcgs_plan* plan, const float* bwd_pack, const float* dh_out, const float* gates,
-                             const float* c, const float* drop, float drop_scalar, int act, int t_len, int batch,
-                             float* dpre, hcgs_stream stream) {
+extern "C" int hcgs_lstm_fwd(const hcgs_plan* plan, const float* fwd_pack, const float* pre, const float* drop,
+                             float drop_scalar, int act, int t_len, int batch, float* h_out, float* c_out,
+                             float* gates_out, int act_bits, hcgs_stream stream) {
+    return lstm_fwd_impl(plan, fwd_pack, pre, drop, drop_scalar, act, t_len, batch, h_out, c_out, gates_out, act_bits,
+                         nullptr, nullptr, 0.f, nullptr, stream);
+}
+
+extern "C" int hcgs_lstm_fwd_ln(const hcgs_plan* plan, const float* fwd_pack, const float* pre, const float* drop,
+                                float drop_scalar, int act, int t_len, int batch, float* h_out, float* c_out,
+                                float* gates_out, int act_bits, const float* ln_gamma, const float* ln_beta,
+                                float ln_eps, float* ln_stats, hcgs_stream stream) {
+    HCGS_REQUIRE(ln_gamma && ln_beta, "hcgs_lstm_fwd_ln: NULL LayerNorm parameters");
+    HCGS_REQUIRE(plan && plan->n_out >= 2, "hcgs_lstm_fwd_ln: the unbiased std needs at least two hidden units");
+    return lstm_fwd_impl(plan, fwd_pack, pre, drop, drop_scalar, act, t_len, batch, h_out, c_out, gates_out, act_bits,
+                         ln_gamma, ln_beta, ln_eps, ln_stats, stream);
+}
+
+static int lstm_bwd_impl(const hcgs_plan* plan, const float* bwd_pack, const float* dh_out, const float* gates,
+                         const float* c, const float* drop, float drop_scalar, int act, int t_len, int batch, float* dpre,
+                         const float* ln_gamma, const float* ln_stats, float ln_eps, float* ln_dgamma, float* ln_dbeta,
+                         hcgs_stream stream) {
     HCGS_REQUIRE(plan && plan->recurrent, "hcgs_lstm_bwd: needs a recurrent plan");
     HCGS_REQUIRE(bwd_pack && dh_out && gates && c && dpre, "hcgs_lstm_bwd: NULL argument");
     if (t_len <= 0 || batch <= 0) return 0;
@@ -666,6 +841,27 @@ extern "C" int hcgs_lstm_bwd(const hcgs_plan* plan, const float* bwd_pack, const
     a.max_blocks = rp.max_cta_blocks;
     a.act = act;
     a.w_in_smem = rp.w_in_smem ? 1 : 0;
+    a.ln_gamma = ln_gamma;
+    a.ln_stats = ln_stats;
+    a.ln_eps = ln_eps;
+    a.ln_dgamma = ln_dgamma;
+    a.ln_dbeta = ln_dbeta;
     const int n_clusters = (batch + NB - 1) / NB;
     return launch_cluster(lstm_bwd_kernel, a, n_clusters, rp.CL, rp.threads, rp.smem_bwd, (cudaStream_t)stream);
+}
+
+extern "C" int hcgs_lstm_bwd(const hcgs_plan* plan, const float* bwd_pack, const float* dh_out, const float* gates,
+                             const float* c, const float* drop, float drop_scalar, int act, int t_len, int batch,
+                             float* dpre, hcgs_stream stream) {
+    return lstm_bwd_impl(plan, bwd_pack, dh_out, gates, c, drop, drop_scalar, act, t_len, batch, dpre, nullptr, nullptr,
+                         0.f, nullptr, nullptr, stream);
+}
+
+extern "C" int hcgs_lstm_bwd_ln(const hcgs_plan* plan, const float* bwd_pack, const float* dh_out, const float* gates,
+                                const float* c, const float* drop, float drop_scalar, int act, int t_len, int batch,
+                                float* dpre, const float* ln_gamma, const float* ln_stats, float ln_eps,
+                                float* ln_dgamma, float* ln_dbeta, hcgs_stream stream) {
+    HCGS_REQUIRE(ln_gamma && ln_stats && ln_dgamma && ln_dbeta, "hcgs_lstm_bwd_ln: NULL LayerNorm argument");
+    return lstm_bwd_impl(plan, bwd_pack, dh_out, gates, c, drop, drop_scalar, act, t_len, batch, dpre, ln_gamma, ln_stats,
+                         ln_eps, ln_dgamma, ln_dbeta, stream);
 }

@@ -683,9 +683,9 @@ class LSTM(nn.Module):
                 x = torch.cat([x, torch.flip(x, [0])], 1)
                 prev_hb = None
             T, B, D = x.shape
-            if self.lstm_use_laynorm[i]:
+            if self.lstm_use_laynorm[i] and _precision(self) == 'bf16':
                 raise NotImplementedError('lstm_use_laynorm (LayerNorm of h_t inside the time loop, reference '
-                                          'neural_networks.py:1092-1093) is not built into the recurrent kernels')
+                                          'neural_networks.py:1092-1093) is built for b200_precision = fp32 only')
             rt = LayerRuntime()
             rt.split_fwd = self.b200_proj_terms == 2
             # drop mask: same for all time steps, NOT rescaled; drawn on the CPU generator (:843-851)
@@ -742,7 +742,11 @@ class LSTM(nn.Module):
                 x = LSTMLayerTCFunction.apply(x, *ws, *us, *gb, rt)
                 prev_hb = rt.hb_out
             else:
-                x = LSTMLayerFunction.apply(x, *ws, *us, *gb, rt)
+                if self.lstm_use_laynorm[i]:
+                    rt.ln_eps = self.ln[i].eps
+                    x = LSTMLayerFunction.apply(x, *ws, *us, *gb, rt, self.ln[i].gamma, self.ln[i].beta)
+                else:
+                    x = LSTMLayerFunction.apply(x, *ws, *us, *gb, rt, None, None)
             if rt.use_bn:
                 for b in bns:
                     _bump_bn_counter(b)

@@ -254,6 +254,15 @@ def gen_norm_inp():
 
 
 # ---- pattern masks -----------------------------------------------------------------------
+def gen_laynorm_loop():
+    """lstm_use_laynorm: the reference's LayerNorm class (:40-51) applied to h_t INSIDE the time loop (:1092-1095);
+    two train steps, so the second runs with gamma / beta that the optimizer has moved."""
+    run_model('train_laynorm', 'train', T=6, B=3, D=12, steps=2, seed=17,
+              lstm_over=dict(lstm_use_laynorm='True,True', lstm_lay='24,20'))
+    run_model('train_laynorm_nobn', 'train', T=9, B=11, D=12, steps=2, seed=18,
+              lstm_over=dict(lstm_use_laynorm='True,False', lstm_use_batchnorm='False,True', lstm_act='tanh,relu',
+                             lstm_drop='0.0,0.2'))
+
 def _cpu_cuda_shim():
     """SURVEY 8(c) shim 3: sparsity/sparsity.py:1045, 1125, 1131 call .cuda() unconditionally; on this GPU-less
     host Tensor.cuda() becomes the identity (nothing else of the reference is touched)."""

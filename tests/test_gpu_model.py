@@ -56,6 +56,10 @@ def _mask_of(net, name):
     ('train_htanh', dict(seed=11, lstm_over=dict(lstm_act='htanh,htanh', lstm_lay='20,28', lstm_drop='0.0,0.1'))),
     # bidirectional: fixture from the reference with its `self.bidir = 0` override (:835) lifted
     ('train_bidir', dict(seed=21, lstm_over=dict(lstm_bidir='True', lstm_lay='24,16'))),
+    # LayerNorm of h_t inside the time loop (neural_networks.py:1092-1095), fused into the recurrent kernels
+    ('train_laynorm', dict(seed=17, lstm_over=dict(lstm_use_laynorm='True,True', lstm_lay='24,20'))),
+    ('train_laynorm_nobn', dict(seed=18, lstm_over=dict(lstm_use_laynorm='True,False', lstm_use_batchnorm='False,True',
+                                                        lstm_act='tanh,relu', lstm_drop='0.0,0.2'))),
 ])
 def test_train_steps_match_reference_fixture(name, kw):
     g = load_golden(name)
@@ -117,7 +121,18 @@ def test_train_steps_match_reference_fixture(name, kw):
                 mk = sd['hcgs.0.mask'].cpu()
             if mk is not None:
                 mine, ref = mine * mk, ref * mk
-            close(mine, ref, 1e-4, 'final %s/%s' % (n, k))
+            if k.startswith('ln.') and 'grad/%s/%s' % (n, k) in g.files:
+                # RMSprop turns a gradient of ANY size into a step of about lr / sqrt(1 - alpha): entries whose gradient
+                # is at the noise level of the fp32 sums (below 1e-3 of the largest) move by an amount that depends on
+                # the last bits of that gradient.  They are bounded by the step size, the others compared as usual.
+                gl = torch.from_numpy(g['grad/%s/%s' % (n, k)]).abs()
+                sel = gl > 1e-3 * gl.max()
+                assert sel.float().mean() > 0.5
+                if (~sel).any():
+                    assert (mine - ref)[~sel].abs().max().item() <= 2 * 0.0016 / (1 - 0.95) ** 0.5
+                mine, ref = mine[sel], ref[sel]
+            # with the in-loop LayerNorm the noise-level entries above feed step 2: 3e-4 on the state after two steps
+            close(mine, ref, 3e-4 if 'laynorm' in name else 1e-4, 'final %s/%s' % (n, k))
 
 
 @pytest.mark.parametrize('name,to_do,seed', [('valid_small', 'valid', 2234), ('eval_forward', 'forward', 77)])
@@ -169,12 +184,13 @@ def _state_to_cpu(nets):
     return params
 
 
-@pytest.mark.parametrize('H,layers,T,B,P', [(550, 4, 60, 8, 1944), (512, 2, 40, 5, 1944)])
-def test_cfg_shape_train_step_matches_oracle(H, layers, T, B, P):
+@pytest.mark.parametrize('H,layers,T,B,P,ln', [(550, 4, 60, 8, 1944, False), (512, 2, 40, 5, 1944, False),
+                                               (550, 2, 30, 21, 1944, True)])
+def test_cfg_shape_train_step_matches_oracle(H, layers, T, B, P, ln):
     """TIMIT_CGS shape: 40-dim input, HCGS 32,4/75,62.5 LSTM, 64,4/50,25 output layer, two heads."""
     D = 40
     lay = ','.join([str(H)] * layers)
-    lstm_over = dict(lstm_lay=lay, lstm_drop=','.join(['0.2'] * layers), lstm_use_laynorm=','.join(['False'] * layers),
+    lstm_over = dict(lstm_lay=lay, lstm_drop=','.join(['0.2'] * layers), lstm_use_laynorm=','.join([str(ln)] * layers),
                      lstm_use_batchnorm=','.join(['True'] * layers), lstm_act=','.join(['tanh'] * layers),
                      hcgsx_block='32,4', hcgsx_sparse='75,62.5', hcgsh_block='32,4', hcgsh_sparse='75,62.5')
     mlp_over = dict(dnn_lay=str(P), hcgs_block='64,4', hcgs_sparse='50,25')
@@ -193,7 +209,8 @@ def test_cfg_shape_train_step_matches_oracle(H, layers, T, B, P):
         for k, v in d.items():
             if v.dtype == torch.float32 and not k.endswith(('running_mean', 'running_var', 'mask')):
                 v.requires_grad_(True)
-    specs = golden_specs(dict(lay=[H] * layers, act=['tanh'] * layers, use_bn=[True] * layers, drop=[0.2] * layers))
+    specs = golden_specs(dict(lay=[H] * layers, act=['tanh'] * layers, use_bn=[True] * layers, drop=[0.2] * layers,
+                              use_ln=[ln] * layers))
     specs['cd']['lay'] = [P]
     ref = model_oracle.model_forward(params, specs, inp, D, True, drops)
     ref['loss_final'].backward()

@@ -168,7 +168,11 @@ def _run_oracle_train(g, specs, steps):
 @pytest.mark.parametrize('name,over', [('train_small', None),
                                        ('train_htanh', dict(lay=[20, 28], act=['htanh', 'htanh'], drop=[0.0, 0.1])),
                                        # reference with the `self.bidir = 0` override (:835) lifted, SURVEY f4
-                                       ('train_bidir', dict(lay=[24, 16], bidir=True))])
+                                       ('train_bidir', dict(lay=[24, 16], bidir=True)),
+                                       # LayerNorm of h_t inside the time loop (:1092-1095)
+                                       ('train_laynorm', dict(lay=[24, 20], use_ln=[True, True])),
+                                       ('train_laynorm_nobn', dict(use_ln=[True, False], use_bn=[False, True],
+                                                                   act=['tanh', 'relu'], drop=[0.0, 0.2]))])
 def test_oracle_train_matches_reference(name, over):
     g = _load(name)
     steps = int(g['dims'][3])
