@@ -392,6 +392,13 @@ int hcgs_opt_step_multi(int kind, int n_tensors, float* const* params, const flo
 int hcgs_assemble_batch(const float* chunk, int64_t chunk_rows, int dim, const int64_t* beg, const int32_t* len,
                         const int32_t* left, int batch, int max_len, float* out, hcgs_stream stream);
 
+/* hcgs_unpad_rows: the opposite movement after a batched forward (b200/export.py): rows t * batch + k, t < len[k], of
+ * src [t_max * batch, ld_src] go to rows row_off[k] + t of dst [sum(len), cols] -- every utterance one contiguous
+ * [len, cols] matrix, i.e. what core.py:238-249 hands to data_io.write_mat one utterance at a time; padding rows are
+ * not copied.  row_off (int64) / len (int32): DEVICE arrays of `batch` entries.                                      */
+int hcgs_unpad_rows(const float* src, int64_t ld_src, int cols, const int64_t* row_off, const int32_t* len, int batch,
+                    int t_max, float* dst, hcgs_stream stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -8,7 +8,8 @@ Here many utterances share one launch: they are sorted by length, cut into group
 and RIGHT-padded with zero frames to the group's longest utterance.  In forward mode the nets
 are causal and stateless across sequences (eval batch norm = running statistics, dropout = the
 scalar (1-p)), so frames ``t < len`` of every sequence are exactly what the batch_size=1 pass
-computes; the padded tail is simply not written.  The prior is subtracted inside the fused
+computes; the padded tail is dropped on the device (``hcgs_unpad_rows`` packs every utterance's rows into one
+contiguous block), so the host copy moves only what is written.  The prior is subtracted inside the fused
 output kernel (``hcgs_out_logsoftmax_prior_fwd``); device->host copies go through two pinned
 buffers on a side stream so that the copy of group i overlaps the compute of group i+1.
 Multi-GPU: ``dist.shard_utterances`` deals the utterances to the ranks, no collective; every rank
@@ -20,6 +21,7 @@ import torch
 import posterior_io
 
 from . import dist as bdist
+from . import native
 
 
 def plan_groups(lengths, batch, max_frames=None):
@@ -80,6 +82,16 @@ class PosteriorExporter:
         main = torch.cuda.current_stream(self.device)
         host = self.host_out
         done = [torch.cuda.Event(), torch.cuda.Event()]
+        # per-group tables for hcgs_unpad_rows (first packed row and length of every utterance), one upload for the run
+        offs, lens_g = [], []
+        for idx in groups:
+            ln = np.asarray([lengths[i] for i in idx], dtype=np.int64)
+            offs.append(np.concatenate([[0], np.cumsum(ln)[:-1]]) if len(idx) else ln)
+            lens_g.append(ln.astype(np.int32))
+        if groups:
+            d_off = torch.from_numpy(np.concatenate(offs).astype(np.int64)).to(self.device)
+            d_len = torch.from_numpy(np.concatenate(lens_g)).to(self.device)
+        first = 0
         pending = None
         for g, idx in enumerate(groups):
             slot = g % 2
@@ -93,29 +105,34 @@ class PosteriorExporter:
             with torch.no_grad():
                 post = self.forward_fn(x)
             t_max, b = x.shape[0], x.shape[1]
-            # utterance-major on the device, so that every utterance is one contiguous block of the host buffer
-            post = post.view(t_max, b, -1).transpose(0, 1).contiguous()
-            host[slot] = _pinned(host[slot], post.numel())
-            dst = host[slot][:post.numel()].view(post.shape)
+            rows = int(lens_g[g].sum())
+            # every utterance one contiguous [len, P] block, padding rows dropped, in ONE pass on the device: the host copy
+            # then moves exactly the matrices that get written
+            post2d = post.view(t_max * b, -1)
+            packed = torch.empty(rows, post2d.shape[1], device=self.device, dtype=torch.float32)
+            native.unpad_rows(post2d, d_off[first:first + b], d_len[first:first + b], t_max, packed)
+            first += b
+            host[slot] = _pinned(host[slot], packed.numel())
+            dst = host[slot][:packed.numel()].view(packed.shape)
             self.copy_stream.wait_stream(main)
             with torch.cuda.stream(self.copy_stream):
-                dst.copy_(post, non_blocking=True)
+                dst.copy_(packed, non_blocking=True)
                 done[slot].record(self.copy_stream)
-            post.record_stream(self.copy_stream)
-            self.d2h_bytes += post.numel() * 4
+            packed.record_stream(self.copy_stream)
+            self.d2h_bytes += packed.numel() * 4
             self.h2d_bytes += x.numel() * 4
             if pending is not None:
                 yield from self._drain(*pending)
-            pending = (dst, done[slot], idx, lengths)
+            pending = (dst, done[slot], idx, lengths, offs[g])
         if pending is not None:
             yield from self._drain(*pending)
 
-    def _drain(self, buf, ev, idx, lengths):
+    def _drain(self, buf, ev, idx, lengths, off):
         ev.synchronize()
         arr = buf.numpy()
         for b, i in enumerate(idx):
             self.frames += lengths[i]
-            yield i, arr[b, :lengths[i]]
+            yield i, arr[int(off[b]):int(off[b]) + lengths[i]]
 
 
 def export_ark(forward_fn, feats, keys, ark_path, device, batch=512, rank=0, world=1):

@@ -101,6 +101,7 @@ SIGNATURES = {
     'hcgs_opt_step_multi': (c_int, [c_int, c_int, POINTER(c_void_p), POINTER(c_void_p), POINTER(c_void_p),
                                     POINTER(c_void_p), POINTER(c_int64), POINTER(ctypes.c_double), c_float, c_void_p]),
     'hcgs_assemble_batch': (c_int, [_f, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, _f, c_void_p]),
+    'hcgs_unpad_rows': (c_int, [_f, c_int64, c_int, c_void_p, c_void_p, c_int, c_int, _f, c_void_p]),
 }
 
 
@@ -135,7 +136,7 @@ KERNELS_PER_CALL = {'hcgs_mask_apply': 1, 'hcgs_quantize_w': 1, 'hcgs_quantize_a
                     'hcgs_out_logsoftmax_prior_fwd': 1, 'hcgs_act_fwd': 1, 'hcgs_act_bwd': 1,
                     'hcgs_logsoftmax_fwd': 1, 'hcgs_logsoftmax_bwd': 1, 'hcgs_logsoftmax_bwd_fused': 1,
                     'hcgs_layernorm_fwd': 1, 'hcgs_layernorm_bwd': 1, 'hcgs_nll_fwd_bwd': 1, 'hcgs_opt_step': 1,
-                    'hcgs_opt_step_multi': 1, 'hcgs_assemble_batch': 1}
+                    'hcgs_opt_step_multi': 1, 'hcgs_assemble_batch': 1, 'hcgs_unpad_rows': 1}
 LAUNCHES = {'total': 0}
 
 
@@ -796,4 +797,19 @@ def assemble_batch(chunk, beg, length, left, max_len, out=None):
     assert out.is_contiguous() and tuple(out.shape) == (int(max_len), batch, dim)
     _check(load().hcgs_assemble_batch(_ptr(chunk), chunk.shape[0], dim, _ptr(beg), _ptr(length), _ptr(left), batch,
                                       int(max_len), _ptr(out), _stream()), 'hcgs_assemble_batch')
+    return out
+
+
+def unpad_rows(src, row_off, length, t_max, out):
+    """out[row_off[k] + t, :] = src[t * batch + k, :] for t < length[k]: per-utterance matrices, padding dropped.
+    src [t_max * batch, cols] fp32 CUDA (row stride = src.stride(0)); out [>= sum(length), cols] contiguous."""
+    _require_cuda(src, out)
+    _require_cuda_any(row_off, length)
+    assert row_off.dtype == torch.int64 and length.dtype == torch.int32 and row_off.is_contiguous() and length.is_contiguous()
+    batch = row_off.numel()
+    assert length.numel() == batch and src.dim() == 2 and src.stride(1) == 1 and src.shape[0] == int(t_max) * batch
+    cols = src.shape[1]
+    assert out.is_contiguous() and out.dim() == 2 and out.shape[1] == cols
+    _check(load().hcgs_unpad_rows(_ptr(src), src.stride(0), cols, _ptr(row_off), _ptr(length), batch, int(t_max),
+                                  _ptr(out), _stream()), 'hcgs_unpad_rows')
     return out

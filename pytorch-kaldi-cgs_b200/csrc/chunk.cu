@@ -33,6 +33,30 @@ __global__ void __launch_bounds__(256) assemble_batch_kernel(const float* __rest
     }
 }
 
+// The reverse movement at the other end of the path: rows (t, k) of a [t_max * batch, cols] result (row t * batch + k) of
+// sentence k, t < len[k], are written to rows row_off[k] + t of a packed [sum(len), cols] matrix -- every sentence one
+// contiguous [len, cols] block, padding rows dropped -- so that one device -> host copy moves exactly the matrices
+// data_io.write_mat stores (core.py:238-249).
+template <int V>
+__global__ void __launch_bounds__(256) unpad_rows_kernel(const float* __restrict__ src, int64_t ld_src, int cols,
+                                                         const int64_t* __restrict__ row_off,
+                                                         const int32_t* __restrict__ len, int batch, int64_t n_vec,
+                                                         float* __restrict__ dst) {
+    const int cv = cols / V;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_vec; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t row = i / cv;
+        const int c = (int)(i - row * cv) * V;
+        const int k = (int)(row % batch);
+        const int64_t t = row / batch;
+        if (t >= (int64_t)__ldg(len + k)) continue;
+        const int64_t d = (__ldg(row_off + k) + t) * cols + c;
+        if (V == 4)
+            *reinterpret_cast<float4*>(dst + d) = __ldg(reinterpret_cast<const float4*>(src + row * ld_src + c));
+        else
+            dst[d] = __ldg(src + row * ld_src + c);
+    }
+}
+
 }  // namespace hcgs
 
 using namespace hcgs;
@@ -55,6 +79,25 @@ extern "C" int hcgs_assemble_batch(const float* chunk, int64_t chunk_rows, int d
         assemble_batch_kernel<4><<<(unsigned)blocks, 256, 0, st>>>(chunk, chunk_rows, dim, beg, len, left, batch, n_vec, out);
     else
         assemble_batch_kernel<1><<<(unsigned)blocks, 256, 0, st>>>(chunk, chunk_rows, dim, beg, len, left, batch, n_vec, out);
+    HCGS_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int hcgs_unpad_rows(const float* src, int64_t ld_src, int cols, const int64_t* row_off, const int32_t* len,
+                               int batch, int t_max, float* dst, hcgs_stream stream) {
+    HCGS_REQUIRE(src && row_off && len && dst, "hcgs_unpad_rows: NULL argument");
+    HCGS_REQUIRE(cols >= 1 && ld_src >= cols && batch >= 1 && t_max >= 0, "hcgs_unpad_rows: bad shape");
+    const int64_t total = (int64_t)t_max * batch * cols;
+    if (total == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    const bool vec = cols % 4 == 0 && ld_src % 4 == 0 && ((uintptr_t)src & 15) == 0 && ((uintptr_t)dst & 15) == 0;
+    const int64_t n_vec = vec ? total / 4 : total;
+    int64_t blocks = (n_vec + 255) / 256;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    if (vec)
+        unpad_rows_kernel<4><<<(unsigned)blocks, 256, 0, st>>>(src, ld_src, cols, row_off, len, batch, n_vec, dst);
+    else
+        unpad_rows_kernel<1><<<(unsigned)blocks, 256, 0, st>>>(src, ld_src, cols, row_off, len, batch, n_vec, dst);
     HCGS_LAUNCH_CHECK();
     return 0;
 }

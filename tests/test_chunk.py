@@ -174,3 +174,21 @@ def test_plans_are_shared_across_model_rebuilds():
     nets2, _ = build_and_run(7)                      # other masks: new plans
     assert native.PLAN_STORE_STATS['misses'] > before['misses']
     del nets0, nets1, nets2
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('t_max,batch,cols,pad', [(9, 5, 1944, 0), (17, 33, 10, 3), (4, 1, 7, 0), (256, 64, 48, 16)])
+def test_unpad_rows_packs_every_utterance(t_max, batch, cols, pad):
+    """hcgs_unpad_rows: rows t * batch + k (t < len[k]) -> one contiguous [len[k], cols] block per utterance, padding rows
+    dropped; bit-exact against indexing, for 16-byte and scalar row widths and a strided source."""
+    g = torch.Generator().manual_seed(t_max)
+    lens = torch.randint(0 if batch > 4 else 1, t_max + 1, (batch,), generator=g)
+    lens[batch // 2] = t_max
+    src_full = torch.randn(t_max * batch, cols + pad, generator=g).cuda()
+    src = src_full[:, :cols]
+    off = torch.cat([torch.zeros(1, dtype=torch.int64), torch.cumsum(lens, 0)[:-1]])
+    out = torch.full((int(lens.sum()), cols), float('nan'), device='cuda:0')
+    native.unpad_rows(src, off.cuda(), lens.to(torch.int32).cuda(), t_max, out)
+    s3 = src.cpu().view(t_max, batch, cols)
+    want = torch.cat([s3[:int(lens[k]), k] for k in range(batch)], 0)
+    assert torch.equal(out.cpu(), want)
