@@ -399,6 +399,16 @@ int hcgs_assemble_batch(const float* chunk, int64_t chunk_rows, int dim, const i
 int hcgs_unpad_rows(const float* src, int64_t ld_src, int cols, const int64_t* row_off, const int32_t* len, int batch,
                     int t_max, float* dst, hcgs_stream stream);
 
+/* ---- guided HCGS masks on the device (guided_hcgs.py:9-76, guided_choices.py:4-30) -------------------------------------
+ * hcgs_window_abs_mean: means[i] = mean |w| over the window {r0, r1, c0, c1} = windows[4i..4i+3] (half-open), accumulated
+ *   in fp32 in row-major order and divided by the window area -- the arithmetic of the CPU AvgPool2d call the reference
+ *   makes once per block-row strip on a host copy of the weights; the block ranking (np.argsort of a few hundred means)
+ *   stays on the host, the weights never leave the device.  windows: DEVICE int32 [n_windows][4]; w: [rows, ldw] fp32.
+ * hcgs_fill_rects: out[r0:r1, c0:c1] = value for every rectangle (the kept blocks of the last level -> the 0/1 mask).   */
+int hcgs_window_abs_mean(const float* w, int64_t ldw, const int32_t* windows, int n_windows, float* means,
+                         hcgs_stream stream);
+int hcgs_fill_rects(float* out, int64_t ld, const int32_t* rects, int n_rects, float value, hcgs_stream stream);
+
 #ifdef __cplusplus
 }
 #endif

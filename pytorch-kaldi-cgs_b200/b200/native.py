@@ -102,6 +102,8 @@ SIGNATURES = {
                                     POINTER(c_void_p), POINTER(c_int64), POINTER(ctypes.c_double), c_float, c_void_p]),
     'hcgs_assemble_batch': (c_int, [_f, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, _f, c_void_p]),
     'hcgs_unpad_rows': (c_int, [_f, c_int64, c_int, c_void_p, c_void_p, c_int, c_int, _f, c_void_p]),
+    'hcgs_window_abs_mean': (c_int, [_f, c_int64, c_void_p, c_int, _f, c_void_p]),
+    'hcgs_fill_rects': (c_int, [_f, c_int64, c_void_p, c_int, c_float, c_void_p]),
 }
 
 
@@ -136,7 +138,7 @@ KERNELS_PER_CALL = {'hcgs_mask_apply': 1, 'hcgs_quantize_w': 1, 'hcgs_quantize_a
                     'hcgs_out_logsoftmax_prior_fwd': 1, 'hcgs_act_fwd': 1, 'hcgs_act_bwd': 1,
                     'hcgs_logsoftmax_fwd': 1, 'hcgs_logsoftmax_bwd': 1, 'hcgs_logsoftmax_bwd_fused': 1,
                     'hcgs_layernorm_fwd': 1, 'hcgs_layernorm_bwd': 1, 'hcgs_nll_fwd_bwd': 1, 'hcgs_opt_step': 1,
-                    'hcgs_opt_step_multi': 1, 'hcgs_assemble_batch': 1, 'hcgs_unpad_rows': 1}
+                    'hcgs_opt_step_multi': 1, 'hcgs_assemble_batch': 1, 'hcgs_unpad_rows': 1, 'hcgs_window_abs_mean': 1, 'hcgs_fill_rects': 1}
 LAUNCHES = {'total': 0}
 
 
@@ -812,4 +814,25 @@ def unpad_rows(src, row_off, length, t_max, out):
     assert out.is_contiguous() and out.dim() == 2 and out.shape[1] == cols
     _check(load().hcgs_unpad_rows(_ptr(src), src.stride(0), cols, _ptr(row_off), _ptr(length), batch, int(t_max),
                                   _ptr(out), _stream()), 'hcgs_unpad_rows')
+    return out
+
+
+def window_abs_mean(w, windows):
+    """mean |w| over each window (r0, r1, c0, c1) of the int32 CUDA tensor `windows` [n, 4]; returns a CUDA float vector."""
+    _require_cuda(w)
+    _require_cuda_any(windows)
+    assert w.dim() == 2 and w.stride(1) == 1 and windows.dtype == torch.int32 and windows.is_contiguous()
+    n = windows.shape[0]
+    means = torch.empty(n, device=w.device, dtype=torch.float32)
+    _check(load().hcgs_window_abs_mean(_ptr(w), w.stride(0), _ptr(windows), n, _ptr(means), _stream()),
+           'hcgs_window_abs_mean')
+    return means
+
+
+def fill_rects(out, rects, value=1.0):
+    _require_cuda(out)
+    _require_cuda_any(rects)
+    assert out.dim() == 2 and out.stride(1) == 1 and rects.dtype == torch.int32 and rects.is_contiguous()
+    _check(load().hcgs_fill_rects(_ptr(out), out.stride(0), _ptr(rects), rects.shape[0], float(value), _stream()),
+           'hcgs_fill_rects')
     return out

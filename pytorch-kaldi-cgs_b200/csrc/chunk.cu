@@ -101,3 +101,52 @@ extern "C" int hcgs_unpad_rows(const float* src, int64_t ld_src, int cols, const
     HCGS_LAUNCH_CHECK();
     return 0;
 }
+
+// ---- guided HCGS on the device ------------------------------------------------------------------------
+// guided_choices.guided_array_rows (guided_choices.py:4-30) ranks the column blocks of a block-row strip by the mean |W| of
+// each block, computed with torch.nn.AvgPool2d on a CPU copy of the strip -- one device -> host copy and one pooling call per
+// strip and level.  Here one launch pools every window of a level: a thread owns a window and adds its |w| in row-major
+// order in fp32 and divides by the window area, which is the CPU kernel's own arithmetic (verified bit for bit,
+// tests/test_guided_device.py), so the ranking -- still np.argsort on the few hundred means -- sees identical numbers.
+namespace hcgs {
+
+__global__ void __launch_bounds__(128) window_abs_mean_kernel(const float* __restrict__ w, int64_t ldw,
+                                                              const int32_t* __restrict__ win, int n_win,
+                                                              float* __restrict__ means) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_win) return;
+    const int r0 = win[4 * i], r1 = win[4 * i + 1], c0 = win[4 * i + 2], c1 = win[4 * i + 3];
+    float sum = 0.f;
+    for (int r = r0; r < r1; ++r) {
+        const float* row = w + (int64_t)r * ldw;
+        for (int c = c0; c < c1; ++c) sum = __fadd_rn(sum, fabsf(__ldg(row + c)));
+    }
+    means[i] = __fdiv_rn(sum, (float)((int64_t)(r1 - r0) * (c1 - c0)));
+}
+
+__global__ void __launch_bounds__(128) fill_rects_kernel(float* __restrict__ out, int64_t ld,
+                                                         const int32_t* __restrict__ rects, float value) {
+    const int r0 = rects[4 * blockIdx.x], r1 = rects[4 * blockIdx.x + 1], c0 = rects[4 * blockIdx.x + 2],
+              c1 = rects[4 * blockIdx.x + 3];
+    const int wd = c1 - c0, n = (r1 - r0) * wd;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) out[(int64_t)(r0 + i / wd) * ld + c0 + i % wd] = value;
+}
+
+}  // namespace hcgs
+
+extern "C" int hcgs_window_abs_mean(const float* w, int64_t ldw, const int32_t* windows, int n_windows, float* means,
+                                    hcgs_stream stream) {
+    HCGS_REQUIRE(w && windows && means, "hcgs_window_abs_mean: NULL argument");
+    if (n_windows <= 0) return 0;
+    hcgs::window_abs_mean_kernel<<<(n_windows + 127) / 128, 128, 0, (cudaStream_t)stream>>>(w, ldw, windows, n_windows, means);
+    HCGS_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int hcgs_fill_rects(float* out, int64_t ld, const int32_t* rects, int n_rects, float value, hcgs_stream stream) {
+    HCGS_REQUIRE(out && rects, "hcgs_fill_rects: NULL argument");
+    if (n_rects <= 0) return 0;
+    hcgs::fill_rects_kernel<<<n_rects, 128, 0, (cudaStream_t)stream>>>(out, ld, rects, value);
+    HCGS_LAUNCH_CHECK();
+    return 0;
+}
