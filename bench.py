@@ -266,7 +266,7 @@ class KernelTimers:
              'lstm_fwd', 'lstm_bwd', 'logsoftmax_fwd', 'logsoftmax_bwd', 'act_fwd', 'act_bwd', 'quantize_w',
              'quantize_act', 'nll_fwd_bwd', 'bn_fwd_il', 'bn_bwd_il', 'lstm_tc_pack', 'lstm_tc_fwd', 'lstm_tc_bwd',
              'tc_pack_nt', 'tc_gemm_nt', 'tc_pack_nn', 'tc_gemm_nn', 'tc_sddmm', 'cast_bf16', 'out_pack',
-             'out_logsoftmax_prior_fwd', 'bn_stats_il', 'logsoftmax_bwd_fused', 'tc_pack_nt_split',
+             'out_logsoftmax_prior_fwd', 'bn_stats_il', 'logsoftmax_bwd_fused', 'logsoftmax_bwd_fused_onehot', 'tc_pack_nt_split',
              'tc_gemm_nt_split', 'split_bf16']
 
     def __init__(self, names=None):

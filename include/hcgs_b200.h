@@ -343,6 +343,13 @@ int hcgs_logsoftmax_bwd(const float* dlogp, const float* logp, float* dz, int64_
  * products read ([m, ldo], pad columns zeroed).  The fp32 dz is never written.  p % 4 == 0, p <= 4096.   */
 int hcgs_logsoftmax_bwd_fused(const float* dlogp, const float* logp, int64_t m, int p, void* dz_bf16,
                               int64_t ldo, float* db, hcgs_stream stream);
+/* the same with the incoming gradient in its sparse form: ONE entry per row, entry i = (rows[i] == i, cols[i], vals[i])
+ * -- what the backward of nn.NLLLoss is (utils.forward_model cost_nll, utils.py:1931-1940: -1/m at the label column)
+ * before it is scattered into a dense [m, p] matrix.  dz[i, j] = vals[i] * ((j == cols[i]) - exp(logp[i, j])); a column
+ * outside [0, p) gives a zero row (ignore_index).  rows / cols: DEVICE int64 (the COO indices), vals: DEVICE fp32.
+ * The kernel traps when rows[i] != i.                                                                                 */
+int hcgs_logsoftmax_bwd_fused_onehot(const int64_t* rows, const int64_t* cols, const float* vals, const float* logp,
+                                     int64_t m, int p, void* dz_bf16, int64_t ldo, float* db, hcgs_stream stream);
 int hcgs_nll_fwd_bwd(const float* logp, int64_t m, int p, const float* labels, int ldlab, float scale,
                      float* dz, float* stats, hcgs_stream stream);
 

@@ -702,12 +702,27 @@ class MLPLayerTCFunction(torch.autograd.Function):
         xb, w, gamma, z, save_mean, save_invstd = ctx.saved_tensors
         N, D, O = ctx.dims
         dev = dout.device
-        dout = dout.contiguous()
         dgamma = dbeta = db = None
         if ctx.softmax and ctx.had_prior:
             raise native.NativeError('backward through a prior-normalised posterior is not defined')
-        if (ctx.softmax and not rt.use_bn and O % 4 == 0 and O <= 4096 and dout.data_ptr() % 16 == 0 and
-                ctx.out_store.data_ptr() % 16 == 0):
+        fused_ok = (ctx.softmax and not rt.use_bn and O % 4 == 0 and O <= 4096 and ctx.out_store.data_ptr() % 16 == 0)
+        if dout.is_sparse and fused_ok and dout._nnz() == N:
+            # the gradient of an NLL loss in its one-entry-per-row form (graph._NLLSparseGrad): no dense [N, O] gradient
+            # is written or read; the kernel traps if entry i is not in row i
+            idx = dout._indices()
+            dz_b = torch.empty(N, native.pad8(O), device=dev, dtype=torch.bfloat16)
+            if ctx.needs_input_grad[2]:
+                db = torch.zeros(O, device=dev, dtype=torch.float32)
+            native.logsoftmax_bwd_fused_onehot(idx[0].contiguous(), idx[1].contiguous(), dout._values().contiguous(),
+                                               ctx.out_store, dz_b, db)
+            dout = None
+        else:
+            if dout.is_sparse:
+                dout = dout.to_dense()
+            dout = dout.contiguous()
+        if dout is None:
+            pass
+        elif fused_ok and dout.data_ptr() % 16 == 0:
             # log-softmax backward, bias gradient and the bf16 operand of the dW / dX products in one pass
             dz_b = torch.empty(N, native.pad8(O), device=dev, dtype=torch.bfloat16)
             if ctx.needs_input_grad[2]:

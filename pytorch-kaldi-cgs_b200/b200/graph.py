@@ -9,6 +9,7 @@ concatenate, mse -- with the same tensor reshaping rules between sequential and 
 ``cost_l1/l2/gl`` need the regularisation helpers of utils.py and are not on the hot path.
 """
 import re
+import warnings
 
 import torch
 import torch.nn as nn
@@ -20,6 +21,37 @@ _LINE = re.compile(r'(.*)=(.*)\((.*),(.*)\)')
 def parse_model(model):
     lines = [l.strip() for l in (model.split('\n') if isinstance(model, str) else model) if l.strip()]
     return [tuple(s.strip() for s in _LINE.findall(l)[0]) for l in lines]
+
+
+class _NLLSparseGrad(torch.autograd.Function):
+    """nn.NLLLoss() (mean over the rows of -logp[i, label_i]; utils.py:1931-1940) whose backward hands the gradient on
+    as what it is -- one entry per row -- instead of scattering it into a zero-filled dense [rows, classes] matrix.  The
+    fused output layer of the bf16 build consumes that form directly (functions.MLPLayerTCFunction.backward:
+    hcgs_logsoftmax_bwd_fused_onehot); autograd densifies it by itself if it has to be added to another gradient."""
+
+    @staticmethod
+    def forward(ctx, logp, labels):
+        ctx.save_for_backward(labels)
+        ctx.shape = tuple(logp.shape)
+        return nn.functional.nll_loss(logp, labels)
+
+    @staticmethod
+    def backward(ctx, g):
+        labels, = ctx.saved_tensors
+        m, p = ctx.shape
+        idx = torch.stack([torch.arange(m, device=labels.device), labels])
+        vals = (g.reshape(1) * (-1.0 / m)).expand(m).contiguous()
+        with warnings.catch_warnings():
+            warnings.simplefilter('ignore', UserWarning)   # "invariant checks are implicitly disabled": that is the intent
+            return torch.sparse_coo_tensor(idx, vals, (m, p), check_invariants=False, is_coalesced=True), None
+
+
+def _nll(nll_module, o, labels):
+    fn = o.grad_fn
+    if (fn is not None and type(fn).__name__ == 'MLPLayerTCFunctionBackward' and o.is_cuda and o.dim() == 2 and
+            o.dtype == torch.float32 and torch.is_grad_enabled()):
+        return _NLLSparseGrad.apply(o, labels)
+    return nll_module(o, labels)
 
 
 class Graph:
@@ -61,7 +93,7 @@ class Graph:
                     o = outs[a]
                     if o.dim() == 3:
                         o = o.view(max_len * batch_size, -1)
-                    outs[out_name] = self.nll(o, self._labels(inp, b))
+                    outs[out_name] = _nll(self.nll, o, self._labels(inp, b))
             elif op == 'cost_err':
                 if to_do != 'forward':
                     o = outs[a]

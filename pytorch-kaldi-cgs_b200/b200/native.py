@@ -68,6 +68,7 @@ SIGNATURES = {
                                  _f, c_void_p]),
     'hcgs_lstm_bwd_ln': (c_int, [c_void_p, _f, _f, _f, _f, _f, c_float, c_int, c_int, c_int, _f, _f, _f, c_float, _f, _f,
                                  c_void_p]),
+    'hcgs_logsoftmax_bwd_fused_onehot': (c_int, [c_void_p, c_void_p, _f, _f, c_int64, c_int, _f, c_int64, _f, c_void_p]),
     'hcgs_gru_fwd': (c_int, [c_void_p, c_int, _f, _f, _f, c_float, c_int, c_int, c_int, _f, _f, _f, c_void_p]),
     'hcgs_gru_bwd': (c_int, [c_void_p, c_int, _f, _f, _f, _f, _f, c_float, c_int, c_int, c_int, _f, c_void_p]),
     'hcgs_lstm_tc_info': (c_int, [c_void_p, c_int, c_int, POINTER(c_int64)]),
@@ -138,7 +139,7 @@ KERNELS_PER_CALL = {'hcgs_mask_apply': 1, 'hcgs_quantize_w': 1, 'hcgs_quantize_a
                     'hcgs_out_logsoftmax_prior_fwd': 1, 'hcgs_act_fwd': 1, 'hcgs_act_bwd': 1,
                     'hcgs_logsoftmax_fwd': 1, 'hcgs_logsoftmax_bwd': 1, 'hcgs_logsoftmax_bwd_fused': 1,
                     'hcgs_layernorm_fwd': 1, 'hcgs_layernorm_bwd': 1, 'hcgs_nll_fwd_bwd': 1, 'hcgs_opt_step': 1,
-                    'hcgs_opt_step_multi': 1, 'hcgs_assemble_batch': 1, 'hcgs_unpad_rows': 1, 'hcgs_window_abs_mean': 1, 'hcgs_fill_rects': 1}
+                    'hcgs_opt_step_multi': 1, 'hcgs_assemble_batch': 1, 'hcgs_unpad_rows': 1, 'hcgs_logsoftmax_bwd_fused_onehot': 1, 'hcgs_window_abs_mean': 1, 'hcgs_fill_rects': 1}
 LAUNCHES = {'total': 0}
 
 
@@ -748,6 +749,20 @@ def logsoftmax_bwd_fused(dlogp, logp, dz_bf16, db=None):
     assert dz_bf16.shape[0] == logp.shape[0] and dz_bf16.stride(1) == 1
     _check(load().hcgs_logsoftmax_bwd_fused(_ptr(dlogp), _ptr(logp), logp.shape[0], logp.shape[1], _ptr(dz_bf16),
                                             dz_bf16.stride(0), _ptr(db), _stream()), 'hcgs_logsoftmax_bwd_fused')
+
+
+def logsoftmax_bwd_fused_onehot(rows, cols, vals, logp, dz_bf16, db=None):
+    """logsoftmax_bwd_fused for a gradient with one entry per row (COO rows == arange(m), cols, vals): the dense
+    [m, p] gradient of an NLL loss is never materialised."""
+    _require_cuda(vals, logp, db)
+    _require_cuda_any(rows, cols, dz_bf16)
+    m = logp.shape[0]
+    assert rows.dtype == torch.int64 and cols.dtype == torch.int64 and rows.numel() == m and cols.numel() == m
+    assert rows.is_contiguous() and cols.is_contiguous() and vals.is_contiguous() and vals.numel() == m
+    assert logp.is_contiguous() and dz_bf16.dtype == torch.bfloat16 and dz_bf16.shape[0] == m and dz_bf16.stride(1) == 1
+    _check(load().hcgs_logsoftmax_bwd_fused_onehot(_ptr(rows), _ptr(cols), _ptr(vals), _ptr(logp), m, logp.shape[1],
+                                                   _ptr(dz_bf16), dz_bf16.stride(0), _ptr(db), _stream()),
+           'hcgs_logsoftmax_bwd_fused_onehot')
 
 
 def nll_fwd_bwd(logp, labels, ldlab, scale, dz, stats):

@@ -114,7 +114,12 @@ template <int NV4>
 __global__ void __launch_bounds__(256, NV4 <= 16 ? 3 : 2) logsoftmax_bwd_fused_kernel(const float* __restrict__ dlogp,
                                                                    const float* __restrict__ logp, int64_t M, int P,
                                                                    __nv_bfloat16* __restrict__ dz, int64_t ldo,
-                                                                   float* __restrict__ db) {
+                                                                   float* __restrict__ db,
+                                                                   const int64_t* __restrict__ hot_row,
+                                                                   const int64_t* __restrict__ hot_col,
+                                                                   const float* __restrict__ hot_val) {
+    // hot_*: dlogp is NULL and the incoming gradient has ONE entry per row, entry m = (hot_row[m] == m, hot_col[m],
+    // hot_val[m]) -- the gradient of an NLL loss kept in its sparse form: no dense [M, P] gradient is written or read.
     constexpr bool COLREG = NV4 <= 16;
     extern __shared__ float s_col[];  // [P] column sums of this CTA (+ [8][NV4*32] float4 private slices)
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -132,22 +137,41 @@ __global__ void __launch_bounds__(256, NV4 <= 16 ? 3 : 2) logsoftmax_bwd_fused_k
         const float4* lr = reinterpret_cast<const float4*>(logp + m * P);
         // the row sum first; the second read of dlogp below hits L1 (a row is 4*P bytes, the warp just read it)
         float s = 0.f;
-#pragma unroll
-        for (int i = 0; i < NV4; ++i) {
-            const int c = (lane + 32 * i) * 4;
-            if (i < nv && c < P) {
-                const float4 d = __ldg(dr + lane + 32 * i);
-                s += (d.x + d.y) + (d.z + d.w);
+        int hot = -1;
+        if (hot_val) {
+            if (__ldg(hot_row + m) != m) __trap();   // not the one-entry-per-row form the caller promised: fail loudly
+            const int64_t hc = __ldg(hot_col + m);
+            if (hc >= 0 && hc < P) {
+                hot = (int)hc;
+                s = __ldg(hot_val + m);
             }
+        } else {
+#pragma unroll
+            for (int i = 0; i < NV4; ++i) {
+                const int c = (lane + 32 * i) * 4;
+                if (i < nv && c < P) {
+                    const float4 d = __ldg(dr + lane + 32 * i);
+                    s += (d.x + d.y) + (d.z + d.w);
+                }
+            }
+            s = warp_sum(s);
         }
-        s = warp_sum(s);
         __nv_bfloat16* orow = dz + m * ldo;
 #pragma unroll
         for (int i = 0; i < NV4; ++i) {
             const int c = (lane + 32 * i) * 4;
             if (i < nv && c < P) {
                 const float4 l = __ldcs(lr + lane + 32 * i);
-                const float4 d = __ldg(dr + lane + 32 * i);
+                float4 d = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (!hot_val) {
+                    d = __ldg(dr + lane + 32 * i);
+                } else if ((unsigned)(hot - c) < 4u) {
+                    const int k = hot - c;
+                    d.x = k == 0 ? s : 0.f;
+                    d.y = k == 1 ? s : 0.f;
+                    d.z = k == 2 ? s : 0.f;
+                    d.w = k == 3 ? s : 0.f;
+                }
                 float4 g;
                 g.x = d.x - __expf(l.x) * s;
                 g.y = d.y - __expf(l.y) * s;
@@ -193,9 +217,9 @@ __global__ void __launch_bounds__(256, NV4 <= 16 ? 3 : 2) logsoftmax_bwd_fused_k
 
 using namespace hcgs;
 
-extern "C" int hcgs_logsoftmax_bwd_fused(const float* dlogp, const float* logp, int64_t m, int p, void* dz_bf16,
-                                         int64_t ldo, float* db, hcgs_stream stream) {
-    HCGS_REQUIRE(dlogp && logp && dz_bf16, "hcgs_logsoftmax_bwd_fused: NULL argument");
+static int lsm_bwd_fused_launch(const float* dlogp, const int64_t* hot_row, const int64_t* hot_col, const float* hot_val,
+                                const float* logp, int64_t m, int p, void* dz_bf16, int64_t ldo, float* db,
+                                hcgs_stream stream) {
     HCGS_REQUIRE(p > 0 && p % 4 == 0 && p <= 4096, "hcgs_logsoftmax_bwd_fused: p = %d must be a multiple of 4, <= 4096", p);
     HCGS_REQUIRE(ldo >= p && ldo % 4 == 0, "hcgs_logsoftmax_bwd_fused: ldo = %lld must be a multiple of 4, >= p",
                  (long long)ldo);
@@ -208,14 +232,29 @@ extern "C" int hcgs_logsoftmax_bwd_fused(const float* dlogp, const float* logp, 
         const size_t smem = (size_t)((p + 3) & ~3) * sizeof(float) + (size_t)8 * 16 * 32 * sizeof(float4);
         HCGS_CHECK_CUDA(cudaFuncSetAttribute(logsoftmax_bwd_fused_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)smem));
-        logsoftmax_bwd_fused_kernel<16><<<blocks, 256, smem, st>>>(dlogp, logp, m, p, (__nv_bfloat16*)dz_bf16, ldo, db);
+        logsoftmax_bwd_fused_kernel<16><<<blocks, 256, smem, st>>>(dlogp, logp, m, p, (__nv_bfloat16*)dz_bf16, ldo, db,
+                                                                   hot_row, hot_col, hot_val);
     } else {
         const int blocks = (int)std::min<int64_t>((m + 7) / 8, 148 * 2);
         const size_t smem = (size_t)p * sizeof(float);
-        logsoftmax_bwd_fused_kernel<32><<<blocks, 256, smem, st>>>(dlogp, logp, m, p, (__nv_bfloat16*)dz_bf16, ldo, db);
+        logsoftmax_bwd_fused_kernel<32><<<blocks, 256, smem, st>>>(dlogp, logp, m, p, (__nv_bfloat16*)dz_bf16, ldo, db,
+                                                                   hot_row, hot_col, hot_val);
     }
     HCGS_LAUNCH_CHECK();
     return 0;
+}
+
+extern "C" int hcgs_logsoftmax_bwd_fused(const float* dlogp, const float* logp, int64_t m, int p, void* dz_bf16,
+                                         int64_t ldo, float* db, hcgs_stream stream) {
+    HCGS_REQUIRE(dlogp && logp && dz_bf16, "hcgs_logsoftmax_bwd_fused: NULL argument");
+    return lsm_bwd_fused_launch(dlogp, nullptr, nullptr, nullptr, logp, m, p, dz_bf16, ldo, db, stream);
+}
+
+extern "C" int hcgs_logsoftmax_bwd_fused_onehot(const int64_t* rows, const int64_t* cols, const float* vals,
+                                                const float* logp, int64_t m, int p, void* dz_bf16, int64_t ldo,
+                                                float* db, hcgs_stream stream) {
+    HCGS_REQUIRE(rows && cols && vals && logp && dz_bf16, "hcgs_logsoftmax_bwd_fused_onehot: NULL argument");
+    return lsm_bwd_fused_launch(nullptr, rows, cols, vals, logp, m, p, dz_bf16, ldo, db, stream);
 }
 
 extern "C" int hcgs_logsoftmax_fwd(const float* z, int ldz, float* out, int ldo, int64_t m, int p,

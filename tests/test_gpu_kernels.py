@@ -431,6 +431,64 @@ def test_logsoftmax_bwd_fused(M, P):
     assert (db.double() - ref.sum(0)).abs().max().item() <= 1e-4 * max(ref.sum(0).abs().max().item(), 1e-30)
 
 
+@pytest.mark.parametrize('M,P', [(517, 1944), (300, 48), (70, 3480), (9, 4)])
+def test_logsoftmax_bwd_fused_onehot_equals_dense_gradient(M, P):
+    """The NLL gradient kept as one entry per row (hcgs_logsoftmax_bwd_fused_onehot) against the same gradient scattered
+    into a dense matrix and pushed through hcgs_logsoftmax_bwd_fused: identical bf16 dz (same arithmetic per element), same
+    bias gradient; a label outside [0, P) (ignore_index) gives a zero row."""
+    from b200 import native
+    d = torch.device('cuda', 0)
+    torch.manual_seed(M * 3 + P)
+    logp = torch.log_softmax(torch.randn(M, P) * 3, 1).to(d)
+    cols = torch.randint(0, P, (M,))
+    cols[M // 2] = -100
+    vals = -torch.rand(M) / M
+    dense = torch.zeros(M, P)
+    ok = cols >= 0
+    dense[torch.arange(M)[ok], cols[ok]] = vals[ok]
+    ld = native.pad8(P)
+    dz_d = torch.full((M, ld), 7.0, device=d, dtype=torch.bfloat16)
+    dz_h = torch.full((M, ld), 7.0, device=d, dtype=torch.bfloat16)
+    db_d = torch.zeros(P, device=d)
+    db_h = torch.zeros(P, device=d)
+    native.logsoftmax_bwd_fused(dense.to(d), logp, dz_d, db_d)
+    native.logsoftmax_bwd_fused_onehot(torch.arange(M, device=d), cols.to(d), vals.to(d), logp, dz_h, db_h)
+    torch.cuda.synchronize()
+    assert torch.equal(dz_h, dz_d)
+    assert (db_h - db_d).abs().max().item() <= 1e-6 * max(db_d.abs().max().item(), 1e-30)
+    assert dz_h[M // 2].float().abs().max().item() == 0
+
+
+def test_nll_sparse_gradient_through_the_fused_output_layer():
+    """graph._NLLSparseGrad + MLPLayerTCFunction: loss and every gradient equal to the dense nn.NLLLoss path."""
+    import neural_networks as nb
+    from helpers import MLP_OPTS
+    from b200 import graph as bgraph
+    d = torch.device('cuda', 0)
+    torch.manual_seed(4)
+    np.random.seed(4)
+    opts = dict(MLP_OPTS, dnn_lay='1944', hcgs_block='64,4', hcgs_sparse='50,25', b200_precision='bf16')
+    net = nb.MLP(opts, 552).to(d).train()
+    x = torch.randn(300, 552, device=d)
+    lab = torch.randint(0, 1944, (300,), device=d)
+    res = []
+    for sparse in (True, False):
+        xi = x.clone().requires_grad_(True)
+        for p in net.parameters():
+            p.grad = None
+        o = net(xi)
+        assert type(o.grad_fn).__name__ == 'MLPLayerTCFunctionBackward'
+        loss = bgraph._nll(torch.nn.NLLLoss(), o, lab) if sparse else torch.nn.NLLLoss()(o, lab)
+        (loss * 1.5).backward()
+        res.append((loss.item(), xi.grad.clone(), {k: p.grad.clone() for k, p in net.named_parameters() if p.grad is not None}))
+    (l0, gx0, g0), (l1, gx1, g1) = res
+    assert l0 == l1
+    close(gx0, gx1, rtol=1e-6, what='dx')
+    assert set(g0) == set(g1)
+    for k in g1:
+        close(g0[k], g1[k], rtol=1e-6, what=k)
+
+
 @pytest.mark.parametrize('shape', [(7, 3, 12), (300, 550), (65, 1)])
 def test_reference_layernorm_fwd_bwd(shape):
     """hcgs_layernorm_fwd / _bwd = the reference's LayerNorm class (neural_networks.py:40-51: unbiased std, divide by
