@@ -350,6 +350,10 @@ int hcgs_logsoftmax_bwd_fused(const float* dlogp, const float* logp, int64_t m, 
  * The kernel traps when rows[i] != i.                                                                                 */
 int hcgs_logsoftmax_bwd_fused_onehot(const int64_t* rows, const int64_t* cols, const float* vals, const float* logp,
                                      int64_t m, int p, void* dz_bf16, int64_t ldo, float* db, hcgs_stream stream);
+/* hcgs_nll_err_rows: cost_nll and cost_err of one output in one pass (utils.py:1931-1952): loss_rows[i] = -logp[i, label_i]
+ * (0 for a label outside [0, p)), err_rows[i] = (first arg-max of row i != label_i); the caller takes the two means.  */
+int hcgs_nll_err_rows(const float* logp, int64_t ldl, int64_t m, int p, const int64_t* labels, float* loss_rows,
+                      float* err_rows, hcgs_stream stream);
 int hcgs_nll_fwd_bwd(const float* logp, int64_t m, int p, const float* labels, int ldlab, float scale,
                      float* dz, float* stats, hcgs_stream stream);
 

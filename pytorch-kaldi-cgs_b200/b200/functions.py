@@ -753,6 +753,9 @@ class MLPLayerTCFunction(torch.autograd.Function):
             px = rt.plan_x
             wpack = torch.empty(px.nz_tiles * 32 * 32, device=dev, dtype=torch.bfloat16)
             native.tc_pack_nn(px, [w], wpack)
-            dx = torch.empty(N, D, device=dev, dtype=torch.float32)
-            native.tc_gemm_nn(px, 1, wpack, dz_b, dx)
+            # rows padded to 16 bytes like the recurrent layers' own buffers: the gradients of several heads are added in
+            # place by autograd and the sum is then read through TMA boxes by the layer below without a repacking copy
+            dx_pad = torch.empty(N, native.pad8(D), device=dev, dtype=torch.float32)
+            native.tc_gemm_nn(px, 1, wpack, dz_b, dx_pad)
+            dx = dx_pad[:, :D]
         return dx, dw, db, dgamma, dbeta, None

@@ -24,16 +24,21 @@ def parse_model(model):
 
 
 class _NLLSparseGrad(torch.autograd.Function):
-    """nn.NLLLoss() (mean over the rows of -logp[i, label_i]; utils.py:1931-1940) whose backward hands the gradient on
-    as what it is -- one entry per row -- instead of scattering it into a zero-filled dense [rows, classes] matrix.  The
-    fused output layer of the bf16 build consumes that form directly (functions.MLPLayerTCFunction.backward:
-    hcgs_logsoftmax_bwd_fused_onehot); autograd densifies it by itself if it has to be added to another gradient."""
+    """nn.NLLLoss() (mean over the rows of -logp[i, label_i]; utils.py:1931-1940) for the fused output layer of the bf16
+    build.  Forward: ONE pass over the log-posteriors gives the per-row NLL terms and the per-row error flags of cost_err
+    (utils.py:1941-1952) -- `err_rows` is handed back through ``stash`` for the cost_err line of the same output.
+    Backward: the gradient is handed on as what it is -- one entry per row -- instead of being scattered into a
+    zero-filled dense [rows, classes] matrix; functions.MLPLayerTCFunction.backward consumes that form directly
+    (hcgs_logsoftmax_bwd_fused_onehot), and autograd densifies it by itself if it has to be added to another gradient."""
 
     @staticmethod
-    def forward(ctx, logp, labels):
+    def forward(ctx, logp, labels, stash):
+        from . import native
         ctx.save_for_backward(labels)
         ctx.shape = tuple(logp.shape)
-        return nn.functional.nll_loss(logp, labels)
+        loss_rows, err_rows = native.nll_err_rows(logp, labels)
+        stash['err_rows'] = err_rows
+        return loss_rows.mean()
 
     @staticmethod
     def backward(ctx, g):
@@ -43,14 +48,18 @@ class _NLLSparseGrad(torch.autograd.Function):
         vals = (g.reshape(1) * (-1.0 / m)).expand(m).contiguous()
         with warnings.catch_warnings():
             warnings.simplefilter('ignore', UserWarning)   # "invariant checks are implicitly disabled": that is the intent
-            return torch.sparse_coo_tensor(idx, vals, (m, p), check_invariants=False, is_coalesced=True), None
+            return torch.sparse_coo_tensor(idx, vals, (m, p), check_invariants=False, is_coalesced=True), None, None
 
 
-def _nll(nll_module, o, labels):
+def _fused_head(o):
     fn = o.grad_fn
-    if (fn is not None and type(fn).__name__ == 'MLPLayerTCFunctionBackward' and o.is_cuda and o.dim() == 2 and
-            o.dtype == torch.float32 and torch.is_grad_enabled()):
-        return _NLLSparseGrad.apply(o, labels)
+    return (fn is not None and type(fn).__name__ == 'MLPLayerTCFunctionBackward' and o.is_cuda and o.dim() == 2 and
+            o.dtype == torch.float32 and o.stride(1) == 1 and torch.is_grad_enabled())
+
+
+def _nll(nll_module, o, labels, stash=None):
+    if _fused_head(o):
+        return _NLLSparseGrad.apply(o, labels.contiguous(), stash if stash is not None else {})
     return nll_module(o, labels)
 
 
@@ -73,6 +82,7 @@ class Graph:
         for f, (a, b) in self.fea.items():
             outs[f] = inp[:, :, a:b] if inp.dim() == 3 else inp[:, a:b]
         last = forward_outs[-1] if len(forward_outs) else None
+        fused_err = {}
         for out_name, op, a, b in self.ops:
             stop = to_do == 'forward' and out_name == last
             if op == 'compute':
@@ -93,14 +103,21 @@ class Graph:
                     o = outs[a]
                     if o.dim() == 3:
                         o = o.view(max_len * batch_size, -1)
-                    outs[out_name] = _nll(self.nll, o, self._labels(inp, b))
+                    lab = self._labels(inp, b)
+                    st = {}
+                    outs[out_name] = _nll(self.nll, o, lab, st)
+                    if 'err_rows' in st:       # cost_err of the same output / labels comes out of the same pass
+                        fused_err[(a, b)] = st['err_rows']
             elif op == 'cost_err':
                 if to_do != 'forward':
                     o = outs[a]
                     if o.dim() == 3:
                         o = o.view(max_len * batch_size, -1)
-                    pred = torch.max(o, dim=1)[1]
-                    outs[out_name] = torch.mean((pred != self._labels(inp, b)).float())
+                    if (a, b) in fused_err:
+                        outs[out_name] = fused_err[(a, b)].mean()
+                    else:
+                        pred = torch.max(o, dim=1)[1]
+                        outs[out_name] = torch.mean((pred != self._labels(inp, b)).float())
             elif op == 'concatenate':
                 outs[out_name] = torch.cat((outs[a], outs[b]), outs[a].dim() - 1)
             elif op == 'mult':

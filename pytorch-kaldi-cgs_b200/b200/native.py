@@ -69,6 +69,7 @@ SIGNATURES = {
     'hcgs_lstm_bwd_ln': (c_int, [c_void_p, _f, _f, _f, _f, _f, c_float, c_int, c_int, c_int, _f, _f, _f, c_float, _f, _f,
                                  c_void_p]),
     'hcgs_logsoftmax_bwd_fused_onehot': (c_int, [c_void_p, c_void_p, _f, _f, c_int64, c_int, _f, c_int64, _f, c_void_p]),
+    'hcgs_nll_err_rows': (c_int, [_f, c_int64, c_int64, c_int, c_void_p, _f, _f, c_void_p]),
     'hcgs_gru_fwd': (c_int, [c_void_p, c_int, _f, _f, _f, c_float, c_int, c_int, c_int, _f, _f, _f, c_void_p]),
     'hcgs_gru_bwd': (c_int, [c_void_p, c_int, _f, _f, _f, _f, _f, c_float, c_int, c_int, c_int, _f, c_void_p]),
     'hcgs_lstm_tc_info': (c_int, [c_void_p, c_int, c_int, POINTER(c_int64)]),
@@ -139,7 +140,7 @@ KERNELS_PER_CALL = {'hcgs_mask_apply': 1, 'hcgs_quantize_w': 1, 'hcgs_quantize_a
                     'hcgs_out_logsoftmax_prior_fwd': 1, 'hcgs_act_fwd': 1, 'hcgs_act_bwd': 1,
                     'hcgs_logsoftmax_fwd': 1, 'hcgs_logsoftmax_bwd': 1, 'hcgs_logsoftmax_bwd_fused': 1,
                     'hcgs_layernorm_fwd': 1, 'hcgs_layernorm_bwd': 1, 'hcgs_nll_fwd_bwd': 1, 'hcgs_opt_step': 1,
-                    'hcgs_opt_step_multi': 1, 'hcgs_assemble_batch': 1, 'hcgs_unpad_rows': 1, 'hcgs_logsoftmax_bwd_fused_onehot': 1, 'hcgs_window_abs_mean': 1, 'hcgs_fill_rects': 1}
+                    'hcgs_opt_step_multi': 1, 'hcgs_assemble_batch': 1, 'hcgs_unpad_rows': 1, 'hcgs_logsoftmax_bwd_fused_onehot': 1, 'hcgs_nll_err_rows': 1, 'hcgs_window_abs_mean': 1, 'hcgs_fill_rects': 1}
 LAUNCHES = {'total': 0}
 
 
@@ -763,6 +764,20 @@ def logsoftmax_bwd_fused_onehot(rows, cols, vals, logp, dz_bf16, db=None):
     _check(load().hcgs_logsoftmax_bwd_fused_onehot(_ptr(rows), _ptr(cols), _ptr(vals), _ptr(logp), m, logp.shape[1],
                                                    _ptr(dz_bf16), dz_bf16.stride(0), _ptr(db), _stream()),
            'hcgs_logsoftmax_bwd_fused_onehot')
+
+
+def nll_err_rows(logp, labels):
+    """(-logp[i, label_i], first-argmax(logp[i]) != label_i) per row, one pass; two fp32 CUDA vectors."""
+    _require_cuda(logp)
+    _require_cuda_any(labels)
+    assert logp.dim() == 2 and logp.stride(1) == 1 and labels.dtype == torch.int64 and labels.is_contiguous()
+    m = logp.shape[0]
+    assert labels.numel() == m
+    loss_rows = torch.empty(m, device=logp.device, dtype=torch.float32)
+    err_rows = torch.empty(m, device=logp.device, dtype=torch.float32)
+    _check(load().hcgs_nll_err_rows(_ptr(logp), logp.stride(0), m, logp.shape[1], _ptr(labels), _ptr(loss_rows),
+                                    _ptr(err_rows), _stream()), 'hcgs_nll_err_rows')
+    return loss_rows, err_rows
 
 
 def nll_fwd_bwd(logp, labels, ldlab, scale, dz, stats):

@@ -213,6 +213,47 @@ __global__ void __launch_bounds__(256, NV4 <= 16 ? 3 : 2) logsoftmax_bwd_fused_k
     }
 }
 
+// cost_nll and cost_err of one output in ONE pass over the log-posteriors (utils.py:1931-1952): per row the NLL term
+// -logp[m, label] and the error flag (first arg-max != label).  Per-row results (no atomics): the two means are taken by
+// the caller over [M] values, deterministically.  One warp per row, 16-byte loads when P % 4 == 0.
+__global__ void __launch_bounds__(256) nll_err_rows_kernel(const float* __restrict__ logp, int64_t ldl, int64_t M, int P,
+                                                           const int64_t* __restrict__ labels,
+                                                           float* __restrict__ loss_rows, float* __restrict__ err_rows) {
+    const int lane = threadIdx.x & 31;
+    const int64_t wstride = (int64_t)gridDim.x * 8;
+    const bool vec = (P & 3) == 0 && (ldl & 3) == 0 && (((uintptr_t)logp) & 15) == 0;
+    for (int64_t m = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); m < M; m += wstride) {
+        const float* lr = logp + m * ldl;
+        float best = -INFINITY;
+        int besti = 0x7fffffff;
+        if (vec) {
+            for (int c = lane * 4; c < P; c += 128) {
+                const float4 v = __ldg(reinterpret_cast<const float4*>(lr + c));
+                if (v.x > best) { best = v.x; besti = c; }
+                if (v.y > best) { best = v.y; besti = c + 1; }
+                if (v.z > best) { best = v.z; besti = c + 2; }
+                if (v.w > best) { best = v.w; besti = c + 3; }
+            }
+        } else {
+            for (int c = lane; c < P; c += 32) {
+                const float v = __ldg(lr + c);
+                if (v > best) { best = v; besti = c; }
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {   // first index of the maximum (torch.max tie rule)
+            const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, besti, o);
+            if (ob > best || (ob == best && oi < besti)) { best = ob; besti = oi; }
+        }
+        if (lane == 0) {
+            const int64_t label = __ldg(labels + m);
+            loss_rows[m] = (label >= 0 && label < P) ? -__ldg(lr + label) : 0.f;
+            err_rows[m] = ((int64_t)besti != label) ? 1.f : 0.f;
+        }
+    }
+}
+
 }  // namespace hcgs
 
 using namespace hcgs;
@@ -284,6 +325,17 @@ extern "C" int hcgs_nll_fwd_bwd(const float* logp, int64_t m, int p, const float
     const int64_t blocks = (m + ROWS_PER_CTA - 1) / ROWS_PER_CTA;
     nll_fwd_bwd_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(logp, m, p, labels, ldlab, scale, dz,
                                                                           stats);
+    HCGS_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int hcgs_nll_err_rows(const float* logp, int64_t ldl, int64_t m, int p, const int64_t* labels, float* loss_rows,
+                                 float* err_rows, hcgs_stream stream) {
+    HCGS_REQUIRE(logp && labels && loss_rows && err_rows, "hcgs_nll_err_rows: NULL argument");
+    HCGS_REQUIRE(p >= 1 && ldl >= p, "hcgs_nll_err_rows: bad shape");
+    if (m <= 0) return 0;
+    const int blocks = (int)std::min<int64_t>((m + 7) / 8, 148 * 8);
+    nll_err_rows_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(logp, ldl, m, p, labels, loss_rows, err_rows);
     HCGS_LAUNCH_CHECK();
     return 0;
 }
