@@ -51,6 +51,35 @@ class _NLLSparseGrad(torch.autograd.Function):
             return torch.sparse_coo_tensor(idx, vals, (m, p), check_invariants=False, is_coalesced=True), None, None
 
 
+class _SharedInput(torch.autograd.Function):
+    """One tensor read by several nets (the LSTM output feeding the pdf and the monophone head): hands out one alias per
+    reader and adds their gradients in ONE pass straight into rows padded to 16 bytes -- the layout the recurrent layers
+    read their incoming gradient in (functions._padded_rows) -- instead of autograd's out-of-place sum followed by a
+    repacking copy."""
+
+    @staticmethod
+    def forward(ctx, x, n):
+        return tuple(x.view_as(x) for _ in range(n))
+
+    @staticmethod
+    def backward(ctx, *gs):
+        gs = [g for g in gs if g is not None]
+        if not gs:
+            return None, None
+        g0 = gs[0]
+        if len(gs) == 1 or g0.dim() != 2 or not g0.is_cuda or any(g.is_sparse or g.shape != g0.shape for g in gs):
+            tot = gs[0]
+            for g in gs[1:]:
+                tot = tot + g
+            return tot, None
+        m, d = g0.shape
+        out = torch.empty(m, (d + 7) // 8 * 8, device=g0.device, dtype=g0.dtype)[:, :d]
+        torch.add(gs[0], gs[1], out=out)
+        for g in gs[2:]:
+            out.add_(g)
+        return out, None
+
+
 def _fused_head(o):
     fn = o.grad_fn
     return (fn is not None and type(fn).__name__ == 'MLPLayerTCFunctionBackward' and o.is_cuda and o.dim() == 2 and
@@ -71,6 +100,11 @@ class Graph:
         self.ops = parse_model(model)
         self.nets, self.seq, self.fea, self.lab = nets, seq, fea, lab
         self.nll = nn.NLLLoss()
+        # how many nets read each tensor (a tensor with several readers is handed out through _SharedInput)
+        self.readers = {}
+        for _, op, _, b in self.ops:
+            if op == 'compute':
+                self.readers[b] = self.readers.get(b, 0) + 1
 
     def _labels(self, inp, name):
         col = self.lab[name]
@@ -83,6 +117,7 @@ class Graph:
             outs[f] = inp[:, :, a:b] if inp.dim() == 3 else inp[:, a:b]
         last = forward_outs[-1] if len(forward_outs) else None
         fused_err = {}
+        shared = {}
         for out_name, op, a, b in self.ops:
             stop = to_do == 'forward' and out_name == last
             if op == 'compute':
@@ -97,6 +132,10 @@ class Graph:
                         x = outs[b] = x.view(max_len * batch_size, -1)
                     if self.seq[a] and x.dim() == 2:
                         x = outs[b] = x.view(max_len, batch_size, -1)
+                if self.readers.get(b, 0) > 1 and b not in self.fea and x.is_cuda and x.dim() == 2 and x.requires_grad:
+                    if b not in shared:
+                        shared[b] = list(_SharedInput.apply(x, self.readers[b]))
+                    x = shared[b].pop()
                 outs[out_name] = self.nets[a](x)
             elif op == 'cost_nll':
                 if to_do != 'forward':
