@@ -259,6 +259,14 @@ int hcgs_lstm_tc_fwd(const hcgs_plan* plan, int cluster_size, int nb, const uint
                      int t_len, int batch, float* h_out, void* hb_out, float* c_out, float* gates_out,
                      const float* bn_mean, const float* bn_invstd, const float* const* bn_gamma,
                      const float* const* bn_beta, hcgs_stream stream);
+/* hcgs_lstm_tc_fwd_split: the same launch also writing hl_out = bf16(h - float(bf16(h))) next to hb_out = bf16(h)
+ * ([t_len*batch, ld_h] each): the two-term operand of the NEXT layer's projection (hcgs_tc_gemm_nt_split) straight out of
+ * the recurrence, instead of a separate hcgs_split_bf16 pass over the fp32 h.                                         */
+int hcgs_lstm_tc_fwd_split(const hcgs_plan* plan, int cluster_size, int nb, const uint32_t* fwd_pack,
+                           const float* pre, int ld_h, const float* drop, float drop_scalar, int act,
+                           int t_len, int batch, float* h_out, void* hb_out, void* hl_out, float* c_out,
+                           float* gates_out, const float* bn_mean, const float* bn_invstd,
+                           const float* const* bn_gamma, const float* const* bn_beta, hcgs_stream stream);
 /* tuning aid: with HCGS_TC_DEBUG=64 in the environment the recurrent kernels accumulate clock64 deltas per
  * phase (thread 0 of CTA 0); out16 receives the 16 counters of the last traced launch.              */
 int hcgs_tc_trace_read(int64_t* out16);

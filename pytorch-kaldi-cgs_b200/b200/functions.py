@@ -35,6 +35,9 @@ class LayerRuntime:
         self.q_ws = None
         self.q_us = None
         self.ln_eps = 1e-6        # eps of the in-loop LayerNorm (lstm_use_laynorm)
+        self.xl_in = None         # bf16 low term of the input rows when the layer below produced it (two-term projections)
+        self.want_hl = False      # emit the low term of this layer's output for the layer above
+        self.hl_out = None
         self.act_bits = 0         # > 0: per-step Quantize_inp of h_t inside the recurrence (lstm_quant_inp)
         self.cell = None          # GRU family: 'gru' | 'minimalgru' | 'ligru' | 'rnn'
         # tensor-core build: bf16 copy of the layer input handed over by the previous layer, and of
@@ -541,7 +544,9 @@ class LSTMLayerTCFunction(torch.autograd.Function):
             xb = None
         xl = None
         if rt.split_fwd:
-            xb, xl = _split_rows(_rows_2d(x, M, D), ldD, xb)
+            xl = rt.xl_in if (xb is not None and rt.xl_in is not None and rt.xl_in.shape == (M, ldD)) else None
+            if xl is None:      # first layer (or a foreign input): one pass over the fp32 rows
+                xb, xl = _split_rows(_rows_2d(x, M, D), ldD, xb)
         elif xb is None:
             xb = _bf16_rows(_rows_2d(x, M, D), ldD)
         px = rt.plan_x
@@ -574,9 +579,12 @@ class LSTMLayerTCFunction(torch.autograd.Function):
         if need_grad:
             c = torch.empty(M, ldH, device=dev, dtype=torch.float32)
             gates = torch.empty(M, 4 * ldH, device=dev, dtype=torch.float32)
+        # the layer above multiplies with two-term operands: its low term comes out of this recurrence as well
+        hl = torch.empty(M, ldH, device=dev, dtype=torch.bfloat16) if rt.want_hl else None
         native.lstm_tc_fwd(ph, cfg, fwd_pack, pre_raw, rt.drop, rt.drop_scalar, rt.act, T, B, h_pad.view(M, ldH), hb, c, gates,
-                           bn)
+                           bn, hl)
         rt.hb_out = hb
+        rt.hl_out = hl
         _LAST_H[0] = (h_pad, hb, h_pad._version)
         if need_grad:
             ctx.rt = rt

@@ -76,6 +76,8 @@ SIGNATURES = {
     'hcgs_lstm_tc_pack': (c_int, [c_void_p, c_int, _pp, c_int, _f, _f, c_void_p]),
     'hcgs_lstm_tc_fwd': (c_int, [c_void_p, c_int, c_int, _f, _f, c_int, _f, c_float, c_int, c_int, c_int, _f, _f, _f,
                                  _f, _f, _f, _pp, _pp, c_void_p]),
+    'hcgs_lstm_tc_fwd_split': (c_int, [c_void_p, c_int, c_int, _f, _f, c_int, _f, c_float, c_int, c_int, c_int, _f, _f,
+                                       _f, _f, _f, _f, _f, _pp, _pp, c_void_p]),
     'hcgs_lstm_tc_bwd': (c_int, [c_void_p, c_int, c_int, _f, _f, _f, _f, c_int, _f, c_float, c_int, c_int, c_int, _f,
                                  _f, c_void_p]),
     'hcgs_tc_trace_read': (c_int, [POINTER(c_int64)]),
@@ -133,7 +135,7 @@ def load():
 KERNELS_PER_CALL = {'hcgs_mask_apply': 1, 'hcgs_quantize_w': 1, 'hcgs_quantize_act': 2, 'hcgs_bsgemm_nt': 1,
                     'hcgs_bsgemm_nn': 1, 'hcgs_bs_sddmm': 1, 'hcgs_colsum': 1, 'hcgs_bn_fwd': 3, 'hcgs_bn_fwd_static': 3, 'hcgs_bn_bwd': 2, 'hcgs_bn_fwd_il': 3, 'hcgs_bn_bwd_il': 2, 'hcgs_bn_stats_il': 1,
                     'hcgs_lstm_pack': 2, 'hcgs_lstm_fwd': 1, 'hcgs_lstm_bwd': 1, 'hcgs_lstm_fwd_ln': 1, 'hcgs_lstm_bwd_ln': 1, 'hcgs_gru_fwd': 1, 'hcgs_gru_bwd': 1,
-                    'hcgs_lstm_tc_pack': 2, 'hcgs_lstm_tc_fwd': 1, 'hcgs_lstm_tc_bwd': 1,
+                    'hcgs_lstm_tc_pack': 2, 'hcgs_lstm_tc_fwd': 1, 'hcgs_lstm_tc_fwd_split': 1, 'hcgs_lstm_tc_bwd': 1,
                     'hcgs_tc_pack_nt': 1, 'hcgs_tc_gemm_nt': 1, 'hcgs_cast_bf16': 1,
                     'hcgs_tc_pack_nt_split': 1, 'hcgs_tc_gemm_nt_split': 1, 'hcgs_split_bf16': 1,
                     'hcgs_tc_pack_nn': 1, 'hcgs_tc_gemm_nn': 1, 'hcgs_tc_sddmm': 1, 'hcgs_out_pack': 1,
@@ -541,7 +543,7 @@ def pad8(n):
 
 
 def lstm_tc_fwd(plan, cfg, fwd_pack, pre, drop, drop_scalar, act, T, B, h_out=None, hb_out=None, c_out=None,
-                gates_out=None, bn=None):
+                gates_out=None, bn=None, hl_out=None):
     """pre / gates_out: [T*B, 4*ldH] fp32 gate-interleaved (column u*4+g), ldH = pad8(H);
     c_out / h_out [T*B, ldH] fp32, hb_out [T*B, ldH] bf16, pad columns zero (all optional but one of h/hb).
     bn = (mean, invstd, gammas, betas): batch norm of `pre` fused into the kernel (bn_stats_il)."""
@@ -557,6 +559,15 @@ def lstm_tc_fwd(plan, cfg, fwd_pack, pre, drop, drop_scalar, act, T, B, h_out=No
     assert pre.is_contiguous() and pre.numel() == T * B * 4 * ldH and ldH % 8 == 0 and ldH >= H
     for t, n in ((h_out, ldH), (hb_out, ldH), (c_out, ldH), (gates_out, 4 * ldH)):
         assert t is None or (t.is_contiguous() and t.numel() == T * B * n)
+    if hl_out is not None:
+        # hl_out [T*B, ldH] bf16 = bf16(h - float(bf16(h))): the low term of the next layer's two-term projection
+        _require_cuda_any(hl_out)
+        assert hb_out is not None and hl_out.is_contiguous() and hl_out.numel() == T * B * ldH
+        _check(load().hcgs_lstm_tc_fwd_split(plan.handle, cfg.cluster_size, cfg.nb, _ptr(fwd_pack), _ptr(pre), ldH,
+                                             _ptr(drop), float(drop_scalar), int(act), T, B, _ptr(h_out), _ptr(hb_out),
+                                             _ptr(hl_out), _ptr(c_out), _ptr(gates_out), _ptr(bn_mean), _ptr(bn_invstd),
+                                             _ptrs(bn_g), _ptrs(bn_b), _stream()), 'hcgs_lstm_tc_fwd_split')
+        return
     _check(load().hcgs_lstm_tc_fwd(plan.handle, cfg.cluster_size, cfg.nb, _ptr(fwd_pack), _ptr(pre), ldH, _ptr(drop),
                                    float(drop_scalar), int(act), T, B, _ptr(h_out), _ptr(hb_out), _ptr(c_out),
                                    _ptr(gates_out), _ptr(bn_mean), _ptr(bn_invstd), _ptrs(bn_g), _ptrs(bn_b),

@@ -288,7 +288,7 @@ static size_t tc_fwd2_smem(const TcPlan& t, int NB) {
     size_t b = 128;                                                   // alignment slack (TMA boxes: 128 B)
     b += (size_t)2 * NB * t.Hc * 16;                                  // pre-activation / gate stages (dense boxes)
     b += 2 * (((size_t)NB * t.Hc * 4 + 127) & ~(size_t)127);          // c and h output stages
-    b += ((size_t)NB * t.Hc * 2 + 127) & ~(size_t)127;                // dense bf16 copy of the slice
+    b += 2 * (((size_t)NB * t.Hc * 2 + 127) & ~(size_t)127);          // dense bf16 copy of the slice + its low part
     b += ((size_t)2 * t.CL * NB * HcS * 2 + 127) & ~(size_t)127;      // slice-major h double buffer (bf16)
     b += tc_align16((size_t)t.SPC * t.KS * 2 * 32 * 8);               // B fragments
     b += 3 * tc_align16((size_t)t.Hc * 16);                           // fused batch-norm coefficients
@@ -452,6 +452,7 @@ struct TcFwdArgs {
     float drop_scalar;
     float* h_out;           // [T*B][ldH] fp32 (pad columns zero) or NULL
     __nv_bfloat16* hb_out;  // [T*B][ldH] bf16 copy for the tensor-core GEMMs, or NULL
+    __nv_bfloat16* hl_out;  // [T*B][ldH] bf16(h - float(bf16(h))): second term of the next layer's two-term projection, or NULL
     float* c_out;           // [T*B][ldH] or NULL
     float* gates_out;       // [T*B][4*ldH] gate-interleaved, or NULL
     // fused batch norm of the pre-activations (all NULL = pre is used as is): z = (pre - mean) * invstd * gamma + beta
@@ -462,7 +463,7 @@ struct TcFwdArgs {
     int dbg;  // timing experiments only (HCGS_TC_DEBUG): 1 = no global stores, 2 = no prefetch, 4 = no MMA
     // TMA build: [T][B][cols] tensor maps with boxes {BW | Hc, 16, 1}; the pre / gates slice of a CTA is NBX boxes
     int BW, NBX;
-    alignas(64) CUtensorMap tm_pre, tm_gates, tm_c, tm_h, tm_hb;
+    alignas(64) CUtensorMap tm_pre, tm_gates, tm_c, tm_h, tm_hb, tm_hl;
 };
 
 // NT m16 tiles of sequences per cluster, SPW strips per warp, KSM >= k-steps per strip (compile time
@@ -578,6 +579,8 @@ __global__ void __launch_bounds__((SPW <= 2 ? TC_MAX_WARPS2 : TC_MAX_WARPS) * 32
     sp += tc_align128((size_t)NB * Hc * 4);
     __nv_bfloat16* hb_s = reinterpret_cast<__nv_bfloat16*>(sp);  // [16][Hc] dense bf16 copy for the store
     sp += tc_align128((size_t)NB * Hc * 2);
+    __nv_bfloat16* hl_s = reinterpret_cast<__nv_bfloat16*>(sp);  // [16][Hc] low part bf16(h - hb) for the store
+    sp += tc_align128((size_t)NB * Hc * 2);
     __nv_bfloat16* hbuf = reinterpret_cast<__nv_bfloat16*>(sp);  // [2][CL][NB][HcS]
     sp += tc_align128((size_t)2 * CL * NB * HcS * 2);
     uint2* wf_s = reinterpret_cast<uint2*>(sp);
@@ -620,7 +623,8 @@ __global__ void __launch_bounds__((SPW <= 2 ? TC_MAX_WARPS2 : TC_MAX_WARPS) * 32
         for (int i = tid; i < (int)(CL * slice); i += nthreads) hz[i] = 0u;  // both buffers (2*CL*slice bf16)
         for (int i = tid; i < NB * Hc; i += nthreads) c_s[i] = h_s[i] = 0.f;
         uint32_t* hbz = reinterpret_cast<uint32_t*>(hb_s);
-        for (int i = tid; i < NB * Hc / 2; i += nthreads) hbz[i] = 0u;
+        uint32_t* hlz = reinterpret_cast<uint32_t*>(hl_s);
+        for (int i = tid; i < NB * Hc / 2; i += nthreads) hbz[i] = hlz[i] = 0u;
         if (tid == 0) {
             // [0..1] h_k complete: CW compute-warp arrivals (own slice) + the arm + the peers' transaction bytes
             // [2..3] pre boxes landed   [4..5] outputs of a step complete (CW arrivals)   [6] c/h/hb stages drained
@@ -640,6 +644,7 @@ __global__ void __launch_bounds__((SPW <= 2 ? TC_MAX_WARPS2 : TC_MAX_WARPS) * 32
         if (a.c_out) asm volatile("prefetch.tensormap [%0];" ::"l"(&a.tm_c) : "memory");
         if (a.h_out) asm volatile("prefetch.tensormap [%0];" ::"l"(&a.tm_h) : "memory");
         if (a.hb_out) asm volatile("prefetch.tensormap [%0];" ::"l"(&a.tm_hb) : "memory");
+        if (a.hl_out) asm volatile("prefetch.tensormap [%0];" ::"l"(&a.tm_hl) : "memory");
     }
     fence_proxy_async();
     __syncthreads();
@@ -809,6 +814,7 @@ __global__ void __launch_bounds__((SPW <= 2 ? TC_MAX_WARPS2 : TC_MAX_WARPS) * 32
                     const __nv_bfloat16 hbv = __float2bfloat16_rn(hval);
                     hn[(size_t)bl * HcS + ul] = hbv;
                     hb_s[bl * Hc + ul] = hbv;
+                    hl_s[bl * Hc + ul] = __float2bfloat16_rn(hval - __bfloat162float(hbv));
                 }
             }
             fence_proxy_async();  // generic writes above -> visible to the TMA stores of the DMA warps
@@ -876,6 +882,7 @@ __global__ void __launch_bounds__((SPW <= 2 ? TC_MAX_WARPS2 : TC_MAX_WARPS) * 32
                 mbar_wait_park(mb_out + cur * 8, (uint32_t)((k >> 1) & 1));
                 if (nv > 0) {
                     if (a.hb_out) tma_store_3d(&a.tm_hb, u0, b0, k, smem_u32(hb_s));
+                    if (a.hl_out) tma_store_3d(&a.tm_hl, u0, b0, k, smem_u32(hl_s));
                     if (a.c_out) tma_store_3d(&a.tm_c, u0, b0, k, smem_u32(c_s));
                     if (a.h_out) tma_store_3d(&a.tm_h, u0, b0, k, smem_u32(h_s));
                     bulk_commit();
@@ -1561,11 +1568,11 @@ static int tc_max_active_clusters(const TcPlan& t, int NB, int* fwd_clusters, in
 
 }  // namespace hcgs
 
-extern "C" int hcgs_lstm_tc_fwd(const hcgs_plan* plan, int cluster_size, int nb, const uint32_t* fwd_pack,
-                                const float* pre, int ld_h, const float* drop, float drop_scalar, int act,
-                                int t_len, int batch, float* h_out, void* hb_out, float* c_out, float* gates_out,
-                                const float* bn_mean, const float* bn_invstd, const float* const* bn_gamma,
-                                const float* const* bn_beta, hcgs_stream stream) {
+static int lstm_tc_fwd_impl(const hcgs_plan* plan, int cluster_size, int nb, const uint32_t* fwd_pack,
+                            const float* pre, int ld_h, const float* drop, float drop_scalar, int act,
+                            int t_len, int batch, float* h_out, void* hb_out, void* hl_out, float* c_out,
+                            float* gates_out, const float* bn_mean, const float* bn_invstd,
+                            const float* const* bn_gamma, const float* const* bn_beta, hcgs_stream stream) {
     HCGS_REQUIRE(plan && fwd_pack && pre, "hcgs_lstm_tc_fwd: NULL argument");
     HCGS_REQUIRE((bn_mean == nullptr) == (bn_invstd == nullptr), "hcgs_lstm_tc_fwd: bn_mean and bn_invstd go together");
     HCGS_REQUIRE(h_out || hb_out, "hcgs_lstm_tc_fwd: no output requested");
@@ -1584,6 +1591,7 @@ extern "C" int hcgs_lstm_tc_fwd(const hcgs_plan* plan, int cluster_size, int nb,
     a.drop_scalar = drop_scalar;
     a.h_out = h_out;
     a.hb_out = reinterpret_cast<__nv_bfloat16*>(hb_out);
+    a.hl_out = reinterpret_cast<__nv_bfloat16*>(hl_out);
     a.c_out = c_out;
     a.gates_out = gates_out;
     a.bn_mean = bn_mean;
@@ -1617,12 +1625,33 @@ extern "C" int hcgs_lstm_tc_fwd(const hcgs_plan* plan, int cluster_size, int nb,
             if (int rc = make_tmap_3d(&a.tm_h, 4, h_out, ld, B64, T64, 4 * ld, B64 * 4 * ld, t->Hc, 16)) return rc;
         if (hb_out)
             if (int rc = make_tmap_3d(&a.tm_hb, 2, hb_out, ld, B64, T64, 2 * ld, B64 * 2 * ld, t->Hc, 16)) return rc;
+        if (hl_out)
+            if (int rc = make_tmap_3d(&a.tm_hl, 2, hl_out, ld, B64, T64, 2 * ld, B64 * 2 * ld, t->Hc, 16)) return rc;
     }
     TcFwdKernel k = tc_pick_fwd(NB / 16, t->SPW, t->KS, act);
     HCGS_REQUIRE(k != nullptr, "hcgs_lstm_tc_fwd: no kernel for nb=%d strips/warp=%d k-steps=%d", NB, t->SPW, t->KS);
     const int n_clusters = (batch + NB - 1) / NB;
     return tc_launch(k, a, n_clusters, t->CL, (t->WARPS + 2) * 32, tc_fwd_smem_v(*t, NB),
                      (cudaStream_t)stream);
+}
+
+extern "C" int hcgs_lstm_tc_fwd(const hcgs_plan* plan, int cluster_size, int nb, const uint32_t* fwd_pack,
+                                const float* pre, int ld_h, const float* drop, float drop_scalar, int act,
+                                int t_len, int batch, float* h_out, void* hb_out, float* c_out, float* gates_out,
+                                const float* bn_mean, const float* bn_invstd, const float* const* bn_gamma,
+                                const float* const* bn_beta, hcgs_stream stream) {
+    return lstm_tc_fwd_impl(plan, cluster_size, nb, fwd_pack, pre, ld_h, drop, drop_scalar, act, t_len, batch, h_out, hb_out,
+                            nullptr, c_out, gates_out, bn_mean, bn_invstd, bn_gamma, bn_beta, stream);
+}
+
+extern "C" int hcgs_lstm_tc_fwd_split(const hcgs_plan* plan, int cluster_size, int nb, const uint32_t* fwd_pack,
+                                      const float* pre, int ld_h, const float* drop, float drop_scalar, int act,
+                                      int t_len, int batch, float* h_out, void* hb_out, void* hl_out, float* c_out,
+                                      float* gates_out, const float* bn_mean, const float* bn_invstd,
+                                      const float* const* bn_gamma, const float* const* bn_beta, hcgs_stream stream) {
+    HCGS_REQUIRE(hb_out && hl_out, "hcgs_lstm_tc_fwd_split: the high and the low part go together");
+    return lstm_tc_fwd_impl(plan, cluster_size, nb, fwd_pack, pre, ld_h, drop, drop_scalar, act, t_len, batch, h_out, hb_out,
+                            hl_out, c_out, gates_out, bn_mean, bn_invstd, bn_gamma, bn_beta, stream);
 }
 
 extern "C" int hcgs_lstm_tc_bwd(const hcgs_plan* plan, int cluster_size, int nb, const uint32_t* bwd_pack,

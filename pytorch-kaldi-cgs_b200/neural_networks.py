@@ -673,7 +673,7 @@ class LSTM(nn.Module):
             raise native.NativeError('LSTM expects [T, B, in] input, got %s' % (tuple(x.shape),))
         if bool(self.lstm_use_batchnorm_inp):
             x = _input_batch_norm(self.bn0, x.reshape(x.shape[0] * x.shape[1], x.shape[2])).view(x.shape)
-        prev_hb = None
+        prev_hb = prev_hl = None
         drop_masks = None
         if self.test_flag == False:  # noqa: E712 (reference spelling)
             # the per-layer CPU draws of the reference (:843-851), in its order; taken from the one-forward-ahead
@@ -757,8 +757,11 @@ class LSTM(nn.Module):
                 gb = [None] * 8
             if _precision(self) == 'bf16':
                 rt.xb_in = prev_hb
+                rt.xl_in = prev_hl
+                rt.want_hl = rt.split_fwd and i + 1 < self.N_lstm_lay and not self.bidir
                 x = LSTMLayerTCFunction.apply(x, *ws, *us, *gb, rt)
                 prev_hb = rt.hb_out
+                prev_hl = rt.hl_out
             else:
                 if self.lstm_use_laynorm[i]:
                     rt.ln_eps = self.ln[i].eps

@@ -150,6 +150,17 @@ def test_tc_recurrent_kernels(H, B, T, blocks, drops, act, cl, nb):
                        bn=(mean.to(d), invstd.to(d), [g.to(d) for g in gam], [b.to(d) for b in bet]))
     torch.cuda.synchronize()
     check(h_b, h_a, 3e-5, 1e-2, 'fused batch norm')
+    # two-term output: hl = bf16(h - float(bf16(h))) next to hb, identical to the separate split pass, same h / hb
+    h_c = torch.empty(T * B, ldH, device=d)
+    hb_c = torch.full((T * B, ldH), 7.0, device=d, dtype=torch.bfloat16)
+    hl_c = torch.full((T * B, ldH), 7.0, device=d, dtype=torch.bfloat16)
+    native.lstm_tc_fwd(plan, cfg, fp, pre_d, drop.to(d), 1.0, code, T, B, h_c, hb_c, hl_out=hl_c)
+    hi_ref = torch.empty_like(hb_c)
+    lo_ref = torch.empty_like(hl_c)
+    native.split_bf16(h_c, hi_ref, lo_ref)
+    torch.cuda.synchronize()
+    assert torch.equal(h_c, h_pad) and torch.equal(hb_c, hb), 'h / hb with the low part requested'
+    assert torch.equal(hb_c, hi_ref) and torch.equal(hl_c, lo_ref), 'low part of h == split_bf16(h)'
     # eval variant: scalar drop, only the bf16 output
     hb2 = torch.zeros(T * B, ldH, device=d, dtype=torch.bfloat16)
     native.lstm_tc_fwd(plan, cfg, fp, pre_d, None, 0.8, code, T, B, None, hb2)
