@@ -328,8 +328,6 @@ class MLP(nn.Module):
                 self._apply_masks(i)
                 self._side_effects(i)
             ln_between = bool(self.dnn_use_laynorm[i])
-            if ln_between and self.dnn_use_batchnorm[i]:
-                raise NotImplementedError('dnn_use_laynorm together with dnn_use_batchnorm on one layer is not built')
             lin = self.wx[i]
             rt = LayerRuntime()
             rt.split_fwd = self.b200_proj_terms == 2
@@ -364,16 +362,21 @@ class MLP(nn.Module):
             beta = bn.bias if rt.use_bn else None
             fn = MLPLayerTCFunction if _precision(self) == 'bf16' else MLPLayerFunction
             if ln_between:
-                # drop(act(ln(wx(x)))) (:306-307): the linear alone, the reference's LayerNorm, then the activation
+                # drop(act(ln(wx(x)))) (:306-307) or drop(act(bn(ln(wx(x))))) (:312-314): the linear alone, the reference's
+                # LayerNorm, the batch norm over the rows when both are on, then the activation
                 soft, act_code, dmask, prior = rt.softmax, rt.act, rt.mlp_drop_mask, rt.log_prior
+                with_bn = rt.use_bn
                 rt.softmax, rt.act, rt.mlp_drop_mask, rt.log_prior = False, native.ACT_CODES['linear'], None, None
+                rt.use_bn = False
                 z = fn.apply(x, lin.weight, lin.bias, None, None, rt)
                 z = self.ln[i](z)
+                if with_bn:
+                    z = _input_batch_norm(bn, z)      # nn.BatchNorm1d semantics on [rows, features]; bumps the counter
                 x = ActDropFunction.apply(z, act_code, dmask, soft, prior)
             else:
                 x = fn.apply(x, lin.weight, lin.bias, gamma, beta, rt)
-            if rt.use_bn:
-                _bump_bn_counter(bn)
+                if rt.use_bn:
+                    _bump_bn_counter(bn)
         return x
 
     def prune_parameters(self):

@@ -263,6 +263,14 @@ def gen_laynorm_loop():
               lstm_over=dict(lstm_use_laynorm='True,False', lstm_use_batchnorm='False,True', lstm_act='tanh,relu',
                              lstm_drop='0.0,0.2'))
 
+def gen_mlp_ln_bn():
+    """dnn_use_laynorm and dnn_use_batchnorm on the same MLP layer: drop(act(bn(ln(wx(x))))) (neural_networks.py:312-314),
+    a hidden ReLU layer with both in front of the softmax layer of each head."""
+    run_model('train_mlp_ln_bn', 'train', T=6, B=4, D=12, steps=2, seed=9,
+              mlp_over=dict(dnn_lay='16,10', dnn_drop='0.0,0.0', dnn_use_batchnorm='True,False',
+                            dnn_use_laynorm='True,False', dnn_act='relu,softmax', param_quant='8,8', mlp_prune_perc='70,70'),
+              mono_over=dict(dnn_lay='16,5'))
+
 def _cpu_cuda_shim():
     """SURVEY 8(c) shim 3: sparsity/sparsity.py:1045, 1125, 1131 call .cuda() unconditionally; on this GPU-less
     host Tensor.cuda() becomes the identity (nothing else of the reference is touched)."""

@@ -399,6 +399,42 @@ def test_input_norms_and_layernorm_train_steps_match_reference_fixture():
                 o.step()
 
 
+def test_mlp_layernorm_and_batchnorm_on_one_layer_match_reference_fixture():
+    """drop(act(bn(ln(wx(x))))) (neural_networks.py:312-314): a hidden ReLU layer with dnn_use_laynorm AND
+    dnn_use_batchnorm in both heads; two reference train steps (fixture train_mlp_ln_bn.npz)."""
+    g = load_golden('train_mlp_ln_bn')
+    T, B, D, steps = [int(v) for v in g['dims']]
+    mo = dict(dnn_lay='16,10', dnn_drop='0.0,0.0', dnn_use_batchnorm='True,False', dnn_use_laynorm='True,False',
+              dnn_act='relu,softmax', param_quant='8,8', mlp_prune_perc='70,70')
+    nets, sections = build_product_nets('train', seed=9, mlp_over=mo, mono_over=dict(dnn_lay='16,5'), device='cuda')
+    for n, net in nets.items():
+        net.load_state_dict(golden_state(g, 'init', n))
+    from b200.graph import make_optimizer
+    opts = {k: make_optimizer(nets[k], s) for k, s in zip(nets, sections)}
+    graph = make_graph(nets, D)
+    drops = [torch.from_numpy(g['drop/%d' % i]) for i in range(2 * steps)]
+    with _ReplayBernoulli(drops):
+        for s in range(steps):
+            out = graph.forward(torch.from_numpy(g['inp/%d' % s]).cuda(), T, B, 'train', ['out_dnn2'])
+            for o in opts.values():
+                o.zero_grad()
+            out['loss_final'].backward()
+            assert abs(out['loss_final'].item() - g['loss/%d' % s][0]) <= 2e-5 * abs(g['loss/%d' % s][0]), s
+            close(out['out_dnn2'], g['out_dnn2/%d' % s], 2e-5, 'out_dnn2 step %d' % s)
+            if s == steps - 1:
+                cd = nets['MLP_layers']
+                close(cd.ln[0].gamma.grad, g['grad/MLP_layers/ln.0.gamma'], 2e-4, 'ln.0.gamma grad')
+                close(cd.bn[0].weight.grad, g['grad/MLP_layers/bn.0.weight'], 2e-4, 'bn.0.weight grad')
+                close(cd.bn[0].bias.grad, g['grad/MLP_layers/bn.0.bias'], 2e-4, 'bn.0.bias grad')
+                m0 = cd.hcgs[0].mask.detach().cpu()
+                close(cd.wx[0].weight.grad.cpu() * m0, torch.from_numpy(g['grad/MLP_layers/wx.0.weight']) * m0, 2e-4, 'wx.0')
+                m1 = cd.hcgs[1].mask.detach().cpu()
+                close(cd.wx[1].weight.grad.cpu() * m1, torch.from_numpy(g['grad/MLP_layers/wx.1.weight']) * m1, 2e-4, 'wx.1')
+            for o in opts.values():
+                o.step()
+    assert int(nets['MLP_layers'].bn[0].num_batches_tracked.item()) == int(g['final/MLP_layers/bn.0.num_batches_tracked'])
+
+
 def test_plan_follows_masks_replaced_by_load_state_dict():
     """a mask changed in place after the first forward (load_state_dict copies into the same storage)
     must rebuild the block index -- the packing IS the masking in the recurrent and GEMM kernels."""
