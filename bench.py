@@ -733,30 +733,40 @@ def main():
             stage_in[i % 2].copy_(host[i % n_batches], non_blocking=True)
             in_ready[i % 2].record(copy_stream)
 
+    def e2e_pass(n_steps):
+        """n_steps through the pipelined loop; returns (losses read on the host, frames)."""
+        got, frames_n = [], 0
+        upload(0)
+        for s in range(n_steps):
+            if s + 1 < n_steps:
+                upload(s + 1)
+            main_stream.wait_event(in_ready[s % 2])
+            loss = train_step(graph, opts, stage_in[s % 2], T, B, bucket)
+            in_free[s % 2].record(main_stream)
+            loss_host[s % LAG].copy_(loss.detach().reshape(1), non_blocking=True)    # D2H read of the step's result
+            loss_ready[s % LAG].record(main_stream)
+            if s >= LAG - 1:
+                r = s - (LAG - 1)
+                loss_ready[r % LAG].synchronize()
+                got.append(float(loss_host[r % LAG][0]))
+            frames_n += frames_per[s % n_batches]
+        for r in range(max(0, n_steps - (LAG - 1)), n_steps):
+            loss_ready[r % LAG].synchronize()
+            got.append(float(loss_host[r % LAG][0]))
+        return got, frames_n
+
     for ev in in_free:
         ev.record(main_stream)
     sync_all()
-    losses = []
+    # two untimed steps through the same loop: the first use of the side stream, the staging buffers and the pinned loss
+    # ring costs a one-off ~10 ms on some runs (seen as one 23.4 ms average among 22.3 ms ones)
+    e2e_pass(2)
+    for ev in in_free:
+        ev.record(main_stream)
+    sync_all()
     e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e2.record()
-    frames_e2e = 0
-    upload(0)
-    for s in range(args.steps):
-        if s + 1 < args.steps:
-            upload(s + 1)
-        main_stream.wait_event(in_ready[s % 2])
-        loss = train_step(graph, opts, stage_in[s % 2], T, B, bucket)
-        in_free[s % 2].record(main_stream)
-        loss_host[s % LAG].copy_(loss.detach().reshape(1), non_blocking=True)    # D2H read of the step's result
-        loss_ready[s % LAG].record(main_stream)
-        if s >= LAG - 1:
-            r = s - (LAG - 1)
-            loss_ready[r % LAG].synchronize()
-            losses.append(float(loss_host[r % LAG][0]))
-        frames_e2e += frames_per[s % n_batches]
-    for r in range(max(0, args.steps - (LAG - 1)), args.steps):
-        loss_ready[r % LAG].synchronize()
-        losses.append(float(loss_host[r % LAG][0]))
+    losses, frames_e2e = e2e_pass(args.steps)
     e3.record()
     sync_all()
     ms_e2e = e2.elapsed_time(e3)
