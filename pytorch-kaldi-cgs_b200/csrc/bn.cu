@@ -541,6 +541,7 @@ __global__ void __launch_bounds__(256) bn_bwd_il4_apply_kernel(const DY* __restr
     }
 #pragma unroll 4
     for (int64_t m = mbeg + warp; m < mend; m += 8) {
+        // (evict-first loads here were measured 48 % slower: the pass lives on what the reduction pass left in L2)
         const float4 d = bn_ld4<DY>(dy + m * ld + col);
         const float4 xv = __ldg(reinterpret_cast<const float4*>(x + m * ld + col));
         const float dv[4] = {d.x, d.y, d.z, d.w}, xq[4] = {xv.x, xv.y, xv.z, xv.w};
@@ -553,7 +554,7 @@ __global__ void __launch_bounds__(256) bn_bwd_il4_apply_kernel(const DY* __restr
             uint2 pk;
             pk.x = *reinterpret_cast<const unsigned*>(&lo);
             pk.y = *reinterpret_cast<const unsigned*>(&hi);
-            *reinterpret_cast<uint2*>(dxb + m * ld + col) = pk;
+            __stcs(reinterpret_cast<uint2*>(dxb + m * ld + col), pk);   // streaming store: 0.6 GB nobody re-reads from L2
         }
     }
 }
