@@ -415,7 +415,7 @@ __global__ void __launch_bounds__(128) tc_gemm_nt_kernel(const __grid_constant__
             const float4 v = *reinterpret_cast<const float4*>(st + (size_t)i * NT_EST + lane * 4);
             float* dst = a.y + (m0 + i) * a.ldy + c4;
             if (vec && c4 + 4 <= a.ldy) {
-                *reinterpret_cast<float4*>(dst) = v;
+                __stcs(reinterpret_cast<float4*>(dst), v);
             } else {
                 const float e[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
@@ -769,7 +769,7 @@ __global__ void __launch_bounds__(128) tc_gemm_nn_kernel(const __grid_constant__
         if (vec) {
 #pragma unroll
             for (int i = 0; i < 8; ++i)
-                *reinterpret_cast<float4*>(dst + 4 * i) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+                __stcs(reinterpret_cast<float4*>(dst + 4 * i), make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]));
         } else {
 #pragma unroll
             for (int i = 0; i < 32; ++i)
